@@ -1,0 +1,161 @@
+// gl64.cuh — Goldilocks field (q = 2^64 - 2^32 + 1) arithmetic for sm_100a.
+//
+// The reference's field is plonky2's GoldilocksField (research/verifiable-fhe/Cargo.toml:7,
+// src/ntt/gen_param_file.sage:118).  Representation used on the device:
+//   "canonical"  u64 in [0, q)
+//   "lazy"       any u64, standing for its residue mod q
+// Every routine states which it takes and returns; data at rest in HBM/SMEM is canonical.
+//
+// The same header compiles as plain host C++ (TFHE_EMU) so that kernels can be run by a
+// host-thread emulator in the CPU test-suite; there the PTX paths fall back to portable C.
+#pragma once
+#include <stdint.h>
+
+#if defined(__CUDACC__) && !defined(TFHE_EMU)
+#define GL_DEV __device__ __forceinline__
+#define GL_HD __host__ __device__ __forceinline__
+#else
+#define GL_DEV inline
+#define GL_HD inline
+#endif
+
+typedef uint64_t u64;
+typedef uint32_t u32;
+
+#define GL_Q 0xFFFFFFFF00000001ULL
+#define GL_EPS 0xFFFFFFFFULL  // 2^64 mod q
+
+#if defined(__CUDA_ARCH__) && !defined(TFHE_EMU) && !defined(GL_PORTABLE)
+#define GL_PTX 1
+#else
+#define GL_PTX 0
+#endif
+
+// ---- 64x64 -> 128 multiply -------------------------------------------------------------
+GL_HD void gl_mul_wide(u64 a, u64 b, u64 &lo, u64 &hi) {
+#if defined(__CUDA_ARCH__) && !defined(TFHE_EMU)
+    lo = a * b;
+    hi = __umul64hi(a, b);
+#else
+    unsigned __int128 p = (unsigned __int128)a * b;
+    lo = (u64)p;
+    hi = (u64)(p >> 64);
+#endif
+}
+
+// ---- lazy add / sub ----------------------------------------------------------------------
+// a lazy, b canonical -> lazy.  (a + b) wraps at most once; the wrap 2^64 == eps (mod q) is
+// added back and cannot wrap again because a + b - 2^64 < q.
+GL_HD u64 gl_add(u64 a, u64 b) {
+#if GL_PTX
+    u32 lo, hi, c;
+    asm("add.cc.u32 %0, %3, %5;\n\t"
+        "addc.cc.u32 %1, %4, %6;\n\t"
+        "addc.u32 %2, 0, 0;"
+        : "=r"(lo), "=r"(hi), "=r"(c)
+        : "r"((u32)a), "r"((u32)(a >> 32)), "r"((u32)b), "r"((u32)(b >> 32)));
+    // s += c * eps  (one IMAD.WIDE on the fma pipe; cannot overflow)
+    u64 s = ((u64)hi << 32) | lo;
+    asm("mad.wide.u32 %0, %1, 0xFFFFFFFF, %0;" : "+l"(s) : "r"(c));
+    return s;
+#else
+    u64 s = a + b;
+    return s + ((s < a) ? GL_EPS : 0);
+#endif
+}
+
+// a lazy, b canonical -> lazy.  A borrow means the true value is d - 2^64 == d - eps.
+GL_HD u64 gl_sub(u64 a, u64 b) {
+#if GL_PTX
+    u32 lo, hi, bw;
+    asm("sub.cc.u32 %0, %3, %5;\n\t"
+        "subc.cc.u32 %1, %4, %6;\n\t"
+        "addc.u32 %2, 0, 0;"  // CC.CF after subc.cc is the borrow-out: bw in {0,1}
+        : "=r"(lo), "=r"(hi), "=r"(bw)
+        : "r"((u32)a), "r"((u32)(a >> 32)), "r"((u32)b), "r"((u32)(b >> 32)));
+    // d - eps = d - 2^32 + 1 : hi -= bw, then + bw (IMAD.WIDE carries into hi)
+    hi -= bw;
+    u64 d = ((u64)hi << 32) | lo;
+    asm("mad.wide.u32 %0, %1, 1, %0;" : "+l"(d) : "r"(bw));
+    return d;
+#else
+    u64 d = a - b;
+    return d - ((a < b) ? GL_EPS : 0);
+#endif
+}
+
+// lazy -> canonical
+GL_HD u64 gl_canon(u64 a) { return a >= GL_Q ? a - GL_Q : a; }
+
+// canonical -> canonical
+GL_HD u64 gl_neg(u64 a) { return a ? GL_Q - a : 0; }
+
+// 128-bit (lo,hi) -> lazy.   x = lo + hl*2^64 + hh*2^96 == lo + hl*eps - hh  (mod q)
+GL_HD u64 gl_reduce128(u64 lo, u64 hi) {
+    u64 hh = hi >> 32, hl = hi & GL_EPS;
+#if GL_PTX
+    u32 l0, l1, bw;
+    asm("sub.cc.u32 %0, %3, %5;\n\t"
+        "subc.cc.u32 %1, %4, 0;\n\t"
+        "addc.u32 %2, 0, 0;"
+        : "=r"(l0), "=r"(l1), "=r"(bw)
+        : "r"((u32)lo), "r"((u32)(lo >> 32)), "r"((u32)hh));
+    l1 -= bw;
+    u64 t0 = ((u64)l1 << 32) | l0;
+    asm("mad.wide.u32 %0, %1, 1, %0;" : "+l"(t0) : "r"(bw));
+    u64 t1;
+    asm("mul.wide.u32 %0, %1, 0xFFFFFFFF;" : "=l"(t1) : "r"((u32)hl));
+    return gl_add(t0, t1);  // t1 <= (2^32-1)^2 < q
+#else
+    u64 t0 = lo - hh;
+    if (lo < hh) t0 -= GL_EPS;
+    u64 t1 = hl * GL_EPS;
+    return gl_add(t0, t1);
+#endif
+}
+
+// lazy x lazy -> lazy
+GL_HD u64 gl_mul_lazy(u64 a, u64 b) {
+    u64 lo, hi;
+    gl_mul_wide(a, b, lo, hi);
+    return gl_reduce128(lo, hi);
+}
+// lazy x lazy -> canonical
+GL_HD u64 gl_mul(u64 a, u64 b) { return gl_canon(gl_mul_lazy(a, b)); }
+
+// ---- butterflies -----------------------------------------------------------------------------
+// Cooley-Tukey (forward, crypto/poly.rs:17-22): (u, v) -> (u + v*w, u - v*w).  u,v lazy in, lazy out.
+GL_HD void gl_ct_butterfly(u64 &u, u64 &v, u64 w) {
+    u64 t = gl_mul(v, w);
+    v = gl_sub(u, t);
+    u = gl_add(u, t);
+}
+// Gentleman-Sande (inverse, crypto/poly.rs:45-50): (u, v) -> (u + v, (u - v)*w).  lazy in, lazy out.
+GL_HD void gl_gs_butterfly(u64 &u, u64 &v, u64 w) {
+    u64 vc = gl_canon(v);
+    u64 d = gl_sub(u, vc);
+    u = gl_add(u, vc);
+    v = gl_mul_lazy(d, w);
+}
+
+// ---- the reference's digit rule (vtfhe/glwe_poly.rs:28-50) ------------------------------------
+// digit `li` (0 = least significant) of canonical x for base 2^logB with L = ceil(64/logB) limbs,
+// returned as a canonical field element.  digit_i = k_i + MSB(k_{i-1}) - MSB(k_i)*B, where k_i are
+// the raw logB-bit fields of x' = (sgn ? -x : x) and sgn = bit 63 of x iff L*logB == 64.
+GL_HD u64 gl_digit(u64 x, u32 li, u32 logB, bool centred /* L*logB == 64 */) {
+    bool sgn = centred && (x >> 63);
+    u64 xc = sgn ? GL_Q - x : x;
+    u32 sh = li * logB;
+    u64 f = (xc >> sh) & ((1ULL << logB) - 1);
+    u64 msb = (f >> (logB - 1)) & 1ULL;
+    u64 prev = li ? ((xc >> (sh - 1)) & 1ULL) : 0ULL;
+    int64_t d = (int64_t)f - (int64_t)(msb << logB) + (int64_t)prev;
+    if (sgn) d = -d;
+    return d < 0 ? GL_Q + (u64)d : (u64)d;
+}
+
+// lwe.rs:28-34 / vtfhe/mod.rs:80-107: round the canonical u64 to [0, 2N]
+GL_HD u32 gl_mod_switch(u64 x, u32 logN) {
+    u64 s = x >> (64 - logN - 2);
+    return (u32)((s >> 1) + (s & 1));
+}

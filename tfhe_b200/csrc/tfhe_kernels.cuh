@@ -1,0 +1,452 @@
+// tfhe_kernels.cuh — device bodies of the TFHE hot path for sm_100a (B200).
+//
+// What is here (reference lines are under /root/reference/research/verifiable-fhe/src):
+//   * register-tiled negacyclic NTT over Goldilocks, 16 coefficients per thread, three
+//     passes with two shared-memory exchanges          (crypto/poly.rs:9-64, ntt/mod.rs:12-70)
+//   * external product / CMUX with the accumulator resident in shared memory
+//                                                      (vtfhe/ggsw_ct.rs:98-112, glev_ct.rs:92-110,
+//                                                       vtfhe/mod.rs:80-136, glwe_poly.rs:28-50)
+//   * whole blind rotation in one launch: mod-switch at entry, n CMUX iterations, optional
+//     GLWE key switch, sample extraction at exit       (ivc_based_vpbs.rs:109-124,277-371,
+//                                                       crypto/glwe.rs:96-113, lwe.rs:28-34)
+//   * batched LWE key switch                           (vtfhe/mod.rs:31-54, lev_ct.rs:63-76)
+//
+// A "team" of T = N/16 threads owns one ciphertext; TEAMS teams share a CTA (and its twiddle
+// tables).  Teams synchronise with named barriers only, so they drift freely against each
+// other and hide each other's barrier and memory latency.
+//
+// The file also compiles as host C++ (-DTFHE_EMU): tests/emu runs the same bodies on host
+// threads so that all index arithmetic is checked on the CPU box.
+#pragma once
+#include "gl64.cuh"
+
+#if defined(TFHE_EMU)
+#include <barrier>
+struct EmuBlock {
+    std::barrier<> *cta;
+    std::barrier<> *team[16];
+};
+extern thread_local EmuBlock *g_emu_blk;
+inline void cta_sync() { g_emu_blk->cta->arrive_and_wait(); }
+inline void team_sync(int team, int /*nthreads*/) { g_emu_blk->team[team]->arrive_and_wait(); }
+#define TK_DEV inline
+#define TK_UNROLL
+#else
+__device__ __forceinline__ void cta_sync() { __syncthreads(); }
+__device__ __forceinline__ void team_sync(int team, int nthreads) {
+    if (nthreads == 32)
+        __syncwarp();
+    else
+        asm volatile("bar.sync %0, %1;" ::"r"(team + 1), "r"(nthreads) : "memory");
+}
+#define TK_DEV __device__ __forceinline__
+#define TK_UNROLL _Pragma("unroll")
+#endif
+
+// ---------------------------------------------------------------------------------- tile geometry
+template <int LOGN>
+struct Tile {
+    static_assert(LOGN >= 9 && LOGN <= 12, "register-tiled NTT supports N = 512..4096");
+    static constexpr int N = 1 << LOGN;
+    static constexpr int T = N / 16;      // threads per polynomial / ciphertext
+    static constexpr int S3 = LOGN - 8;   // stages of the last forward pass
+    static constexpr int LB = LOGN - 8;   // bits of the low index in layout B
+};
+
+// exchange-buffer swizzle: XOR the bank-pair index with the next 4 address bits; makes the three
+// access patterns below conflict-free for 8-byte accesses (see DESIGN.md "shared memory")
+GL_HD int tk_swz(int p) { return p ^ ((p >> 4) & 15); }
+
+// position of register e of thread tau in the three layouts
+template <int LOGN> GL_HD int posA(int tau, int e) { return tau + Tile<LOGN>::T * e; }
+template <int LOGN> GL_HD int posB(int tau, int e) {
+    return (tau >> Tile<LOGN>::LB) * (Tile<LOGN>::N / 16) + e * (Tile<LOGN>::N / 256) + (tau & ((1 << Tile<LOGN>::LB) - 1));
+}
+template <int LOGN> GL_HD int posC(int tau, int e) { return 16 * tau + e; }
+
+// one radix-2 stage over the 16 registers; blocks of 2^SH registers, twiddle tw[block]
+template <int SH, bool INV>
+TK_DEV void tile_stage(u64 (&x)[16], const u64 *tw) {
+    constexpr int half = 1 << (SH - 1);
+    TK_UNROLL
+    for (int blk = 0; blk < (16 >> SH); blk++) {
+        const u64 w = tw[blk];
+        TK_UNROLL
+        for (int j = 0; j < half; j++) {
+            const int e0 = (blk << SH) + j;
+            if (INV)
+                gl_gs_butterfly(x[e0], x[e0 + half], w);
+            else
+                gl_ct_butterfly(x[e0], x[e0 + half], w);
+        }
+    }
+}
+
+// last forward pass / first inverse pass: stages 8..LOGN-1 on 16 consecutive coefficients
+template <int LOGN, bool INV>
+TK_DEV void tile_pass_low(u64 (&x)[16], const u64 *tw, int tau) {
+    constexpr int S3 = Tile<LOGN>::S3;
+    // stage with blocks of 2^SH registers: s' = S3 - SH, twiddle base (256 << s') + (tau << (4 - SH))
+    if constexpr (!INV) {
+        if constexpr (S3 >= 4) tile_stage<4, false>(x, tw + (256 << (S3 >= 4 ? S3 - 4 : 0)) + (tau << 0));
+        if constexpr (S3 >= 3) tile_stage<3, false>(x, tw + (256 << (S3 >= 3 ? S3 - 3 : 0)) + (tau << 1));
+        if constexpr (S3 >= 2) tile_stage<2, false>(x, tw + (256 << (S3 >= 2 ? S3 - 2 : 0)) + (tau << 2));
+        if constexpr (S3 >= 1) tile_stage<1, false>(x, tw + (256 << (S3 - 1)) + (tau << 3));
+    } else {
+        if constexpr (S3 >= 1) tile_stage<1, true>(x, tw + (256 << (S3 - 1)) + (tau << 3));
+        if constexpr (S3 >= 2) tile_stage<2, true>(x, tw + (256 << (S3 >= 2 ? S3 - 2 : 0)) + (tau << 2));
+        if constexpr (S3 >= 3) tile_stage<3, true>(x, tw + (256 << (S3 >= 3 ? S3 - 3 : 0)) + (tau << 1));
+        if constexpr (S3 >= 4) tile_stage<4, true>(x, tw + (256 << (S3 >= 4 ? S3 - 4 : 0)) + (tau << 0));
+    }
+}
+// middle pass: stages 4..7 in layout B (b = high 4 bits of the position)
+template <int LOGN, bool INV>
+TK_DEV void tile_pass_mid(u64 (&x)[16], const u64 *tw, int tau) {
+    const int b = tau >> Tile<LOGN>::LB;
+    if (!INV) {
+        tile_stage<4, false>(x, tw + 16 + b);
+        tile_stage<3, false>(x, tw + 32 + 2 * b);
+        tile_stage<2, false>(x, tw + 64 + 4 * b);
+        tile_stage<1, false>(x, tw + 128 + 8 * b);
+    } else {
+        tile_stage<1, true>(x, tw + 128 + 8 * b);
+        tile_stage<2, true>(x, tw + 64 + 4 * b);
+        tile_stage<3, true>(x, tw + 32 + 2 * b);
+        tile_stage<4, true>(x, tw + 16 + b);
+    }
+}
+// first forward pass / last inverse pass: stages 0..3 in layout A (twiddles uniform over threads)
+template <bool INV>
+TK_DEV void tile_pass_high(u64 (&x)[16], const u64 *tw) {
+    if (!INV) {
+        tile_stage<4, false>(x, tw + 1);
+        tile_stage<3, false>(x, tw + 2);
+        tile_stage<2, false>(x, tw + 4);
+        tile_stage<1, false>(x, tw + 8);
+    } else {
+        tile_stage<1, true>(x, tw + 8);
+        tile_stage<2, true>(x, tw + 4);
+        tile_stage<3, true>(x, tw + 2);
+        tile_stage<4, true>(x, tw + 1);
+    }
+}
+
+// forward NTT of one polynomial held by a team: in  x[e] = a[posA(tau,e)] (natural order)
+//                                               out x[e] = A[posC(tau,e)] (reference's bit-reversed order)
+template <int LOGN>
+TK_DEV void team_ntt_forward(u64 (&x)[16], u64 *xb0, u64 *xb1, const u64 *tw, int tau, int team) {
+    constexpr int T = Tile<LOGN>::T;
+    tile_pass_high<false>(x, tw);
+    TK_UNROLL
+    for (int e = 0; e < 16; e++) xb0[tk_swz(posA<LOGN>(tau, e))] = x[e];
+    team_sync(team, T);
+    TK_UNROLL
+    for (int e = 0; e < 16; e++) x[e] = xb0[tk_swz(posB<LOGN>(tau, e))];
+    tile_pass_mid<LOGN, false>(x, tw, tau);
+    TK_UNROLL
+    for (int e = 0; e < 16; e++) xb1[tk_swz(posB<LOGN>(tau, e))] = x[e];
+    team_sync(team, T);
+    TK_UNROLL
+    for (int e = 0; e < 16; e++) x[e] = xb1[tk_swz(posC<LOGN>(tau, e))];
+    tile_pass_low<LOGN, false>(x, tw, tau);
+}
+
+// inverse NTT WITHOUT the final 1/N: in x[e] = A[posC(tau,e)], out x[e] = N*a[posA(tau,e)] (lazy)
+template <int LOGN>
+TK_DEV void team_ntt_inverse(u64 (&x)[16], u64 *xb0, u64 *xb1, const u64 *tw, int tau, int team) {
+    constexpr int T = Tile<LOGN>::T;
+    tile_pass_low<LOGN, true>(x, tw, tau);
+    TK_UNROLL
+    for (int e = 0; e < 16; e++) xb0[tk_swz(posC<LOGN>(tau, e))] = x[e];
+    team_sync(team, T);
+    TK_UNROLL
+    for (int e = 0; e < 16; e++) x[e] = xb0[tk_swz(posB<LOGN>(tau, e))];
+    tile_pass_mid<LOGN, true>(x, tw, tau);
+    TK_UNROLL
+    for (int e = 0; e < 16; e++) xb1[tk_swz(posB<LOGN>(tau, e))] = x[e];
+    team_sync(team, T);
+    TK_UNROLL
+    for (int e = 0; e < 16; e++) x[e] = xb1[tk_swz(posA<LOGN>(tau, e))];
+    tile_pass_high<true>(x, tw);
+}
+
+// ---------------------------------------------------------------------------- batched NTT kernel
+struct NttArgs {
+    const u64 *in;
+    u64 *out;
+    const u64 *tw;   // ROOTS (forward) or INVROOTS (inverse), [N]
+    u64 scale;       // every output multiplied by this (NINV for the reference's inverse; 1 = none)
+    u32 n_polys;
+    u32 inverse;
+};
+
+template <int LOGN, int TEAMS>
+TK_DEV void ntt_batch_body(const NttArgs &a, int tid, int bid, int nblocks, unsigned char *smem_raw) {
+    constexpr int N = Tile<LOGN>::N, T = Tile<LOGN>::T;
+    u64 *tw = (u64 *)smem_raw;
+    const int team = tid / T, tau = tid % T;
+    u64 *xb0 = tw + N + team * 2 * N, *xb1 = xb0 + N;
+    for (int i = tid; i < N; i += T * TEAMS) tw[i] = a.tw[i];
+    cta_sync();
+    // polynomials are dealt round-robin to teams; every team of a CTA runs the same trip count
+    for (u32 base = (u32)bid * TEAMS; base < a.n_polys; base += (u32)nblocks * TEAMS) {
+        const u32 pi = base + team;
+        const bool live = pi < a.n_polys;
+        const u64 *src = a.in + (size_t)(live ? pi : 0) * N;
+        u64 *dst = a.out + (size_t)(live ? pi : 0) * N;
+        u64 x[16];
+        if (!a.inverse) {
+            TK_UNROLL
+            for (int e = 0; e < 16; e++) x[e] = src[posA<LOGN>(tau, e)];
+            team_ntt_forward<LOGN>(x, xb0, xb1, tw, tau, team);
+            if (live) {
+                TK_UNROLL
+                for (int e = 0; e < 16; e++)
+                    dst[posC<LOGN>(tau, e)] = (a.scale == 1) ? gl_canon(x[e]) : gl_mul(x[e], a.scale);
+            }
+        } else {
+            TK_UNROLL
+            for (int e = 0; e < 16; e++) x[e] = src[posC<LOGN>(tau, e)];
+            team_ntt_inverse<LOGN>(x, xb0, xb1, tw, tau, team);
+            if (live) {
+                TK_UNROLL
+                for (int e = 0; e < 16; e++)
+                    dst[posA<LOGN>(tau, e)] = (a.scale == 1) ? gl_canon(x[e]) : gl_mul(x[e], a.scale);
+            }
+        }
+        team_sync(team, T);  // exchange buffers are reused by the next polynomial
+    }
+}
+
+// ------------------------------------------------------------------- external product / blind rotate
+struct BRArgs {
+    u32 n;         // CMUX iterations available = small LWE dimension
+    u32 steps;     // iterations actually run (== n; fewer only for per-iteration parity tests)
+    u32 ell, logB; // gadget of the external product
+    u32 L;         // ceil(64/logB)
+    u32 B;         // ciphertexts in the batch
+    u32 out_mode;  // 0 = full sample extract [N+1]; 1 = partial extract [n_out+1]; 2 = raw accumulator [2N]
+    u32 n_out;     // partial extract length
+    const u64 *bsk;     // [n][2][ell][2][N]  NTT domain, 1/N and the minus sign of the mask GLev folded in
+    const u64 *ksk;     // one GGSW in the same format, or nullptr          (ivc_based_vpbs.rs:355-371)
+    const u64 *lwe;     // [B][n+1] ciphertexts under the small key
+    const u64 *testv;   // [n_luts][N]
+    const u32 *lut_idx; // [B] or nullptr
+    u64 *out;           // [B][out_len]
+    const u64 *tw_fwd;  // ROOTS    [N]
+    const u64 *tw_inv;  // INVROOTS [N]
+};
+
+// coefficient p of X^sh * poly (negacyclic), poly canonical in shared memory   (vtfhe/mod.rs:80-107)
+template <int LOGN>
+TK_DEV u64 rotated_coeff(const u64 *poly, int p, u32 sh) {
+    constexpr int N = 1 << LOGN;
+    const u32 i2 = ((u32)p - sh) & (2 * N - 1);
+    const u64 v = poly[i2 & (N - 1)];
+    return (i2 & N) ? gl_neg(v) : v;
+}
+
+// One GGSW (x) GLWE on the team's accumulator (k = 1).
+//   CMUX = true : acc <- acc + GGSW (x) (X^sh * acc - acc)            (vtfhe/mod.rs:119-136)
+//   CMUX = false: acc <- GGSW (x) acc                                  (ivc_based_vpbs.rs:116-121)
+template <int LOGN, bool CMUX>
+TK_DEV void team_external_product(const BRArgs &a, const u64 *ggsw, u32 sh, u64 *acc, u64 *xb0, u64 *xb1,
+                                  const u64 *tw_f, const u64 *tw_i, int tau, int team) {
+    constexpr int N = Tile<LOGN>::N, T = Tile<LOGN>::T;
+    const bool centred = (a.L * a.logB == 64);
+    u64 o0[16], o1[16];
+    TK_UNROLL
+    for (int e = 0; e < 16; e++) o0[e] = o1[e] = 0;
+
+    for (int j = 0; j < 2; j++) {
+        const u64 *poly = acc + j * N;
+        for (u32 lvl = 0; lvl < a.ell; lvl++) {
+            u64 x[16];
+            TK_UNROLL
+            for (int e = 0; e < 16; e++) {
+                const int p = posA<LOGN>(tau, e);
+                u64 d = poly[p];
+                if (CMUX) d = gl_canon(gl_sub(rotated_coeff<LOGN>(poly, p, sh), d));
+                x[e] = gl_digit(d, a.L - a.ell + lvl, a.logB, centred);   // glev_ct.rs:97-99: top ell limbs
+            }
+            team_ntt_forward<LOGN>(x, xb0, xb1, tw_f, tau, team);
+            const u64 *row0 = ggsw + ((size_t)(j * a.ell + lvl) * 2) * N + 16 * tau;
+            const u64 *row1 = row0 + N;
+            TK_UNROLL
+            for (int e = 0; e < 16; e++) {
+                o0[e] = gl_add(o0[e], gl_mul(x[e], row0[e]));
+                o1[e] = gl_add(o1[e], gl_mul(x[e], row1[e]));
+            }
+        }
+    }
+    team_ntt_inverse<LOGN>(o0, xb0, xb1, tw_i, tau, team);
+    TK_UNROLL
+    for (int e = 0; e < 16; e++) {
+        const int p = posA<LOGN>(tau, e);
+        acc[p] = CMUX ? gl_canon(gl_add(o0[e], acc[p])) : gl_canon(o0[e]);
+    }
+    team_ntt_inverse<LOGN>(o1, xb0, xb1, tw_i, tau, team);
+    TK_UNROLL
+    for (int e = 0; e < 16; e++) {
+        const int p = N + posA<LOGN>(tau, e);
+        acc[p] = CMUX ? gl_canon(gl_add(o1[e], acc[p])) : gl_canon(o1[e]);
+    }
+    team_sync(team, T);  // next iteration gathers rotated coefficients written by other threads
+}
+
+// shared memory: [tw_fwd N][tw_inv N] then per team [acc 2N][xb0 N][xb1 N]   (u64 each)
+template <int LOGN, int TEAMS>
+constexpr size_t blind_rotate_smem_bytes() {
+    return sizeof(u64) * ((size_t)2 * Tile<LOGN>::N + (size_t)TEAMS * 4 * Tile<LOGN>::N);
+}
+
+template <int LOGN, int TEAMS>
+TK_DEV void blind_rotate_body(const BRArgs &a, int tid, int bid, unsigned char *smem_raw) {
+    constexpr int N = Tile<LOGN>::N, T = Tile<LOGN>::T;
+    u64 *tw_f = (u64 *)smem_raw, *tw_i = tw_f + N;
+    const int team = tid / T, tau = tid % T;
+    u64 *acc = tw_i + N + (size_t)team * 4 * N;
+    u64 *xb0 = acc + 2 * N, *xb1 = xb0 + N;
+    for (int i = tid; i < N; i += T * TEAMS) {
+        tw_f[i] = a.tw_fwd[i];
+        tw_i[i] = a.tw_inv[i];
+    }
+    cta_sync();
+    const u32 ct = (u32)bid * TEAMS + team;
+    if (ct >= a.B) return;  // whole team leaves; only team barriers are used from here on
+
+    const u64 *lwe = a.lwe + (size_t)ct * (a.n + 1);
+    const u64 *tv = a.testv + (size_t)(a.lut_idx ? a.lut_idx[ct] : 0) * N;
+
+    // acc0 = X^{ms(-b)} * (0, testv)      ivc_based_vpbs.rs:109-124 (first_step negates the body)
+    {
+        const u32 sh0 = gl_mod_switch(gl_neg(lwe[a.n]), LOGN);
+        TK_UNROLL
+        for (int e = 0; e < 16; e++) {
+            const int p = posA<LOGN>(tau, e);
+            acc[p] = 0;
+            acc[N + p] = rotated_coeff<LOGN>(tv, p, sh0);
+        }
+    }
+    team_sync(team, T);
+
+    const size_t ggsw_len = (size_t)4 * a.ell * N;
+    u64 mask = lwe[0];
+    for (u32 i = 0; i < a.steps; i++) {
+        const u32 sh = gl_mod_switch(mask, LOGN);
+        if (i + 1 < a.steps) mask = lwe[i + 1];  // fetched one iteration ahead
+        team_external_product<LOGN, true>(a, a.bsk + i * ggsw_len, sh, acc, xb0, xb1, tw_f, tw_i, tau, team);
+    }
+    if (a.ksk) team_external_product<LOGN, false>(a, a.ksk, 0, acc, xb0, xb1, tw_f, tw_i, tau, team);
+
+    // exit: sample extraction of coefficient 0      crypto/glwe.rs:96-113
+    if (a.out_mode == 2) {
+        u64 *o = a.out + (size_t)ct * 2 * N;
+        for (int p = tau; p < 2 * N; p += T) o[p] = acc[p];
+    } else {
+        const u32 len = a.out_mode == 1 ? a.n_out : (u32)N;
+        u64 *o = a.out + (size_t)ct * (len + 1);
+        for (u32 p = tau; p < len; p += T) o[p] = p ? gl_neg(acc[N - p]) : acc[0];
+        if (tau == 0) o[len] = acc[N];
+    }
+}
+
+// ---------------------------------------------------------------------------------- LWE key switch
+// out[b] = (0,..,0,body_b) + sum_i sum_j digit_j(a_{b,i}) * KSK[i][j]         (vtfhe/mod.rs:31-54)
+// Signed digits d in [-B/2, B/2] are offset to d' = d + B/2 >= 0 so that every product is an
+// unsigned 32x32 IMAD.WIDE into two 64-bit lanes (low and high KSK halves); the offset is removed
+// once at the end with ksum[x] = sum of all KSK rows.  Exact in Z_q, hence bit-identical to the
+// reference's field arithmetic.
+struct KSArgs {
+    u32 n;       // output dimension
+    u32 kN;      // input dimension
+    u32 ell, logB, L;
+    u32 B;
+    const u64 *ksk;   // [kN][ell][n+1]
+    const u64 *ksum;  // [n+1] column sums of ksk (mod q)
+    const u64 *in;    // [B][kN+1]
+    u64 *out;         // [B][n+1]
+};
+
+GL_HD u64 ks_fold(u64 a0, u64 a1) {  // a0 + a1 * 2^32 -> canonical
+    u64 lo = a0 + (a1 << 32);
+    u64 hi = (a1 >> 32) + (lo < a0 ? 1 : 0);
+    return gl_canon(gl_reduce128(lo, hi));
+}
+
+template <int TB, int TX, int RC>
+TK_DEV void lwe_keyswitch_body(const KSArgs &a, int tid, int bx, int by, unsigned char *smem_raw) {
+    u32 *dig = (u32 *)smem_raw;  // [RC*ell][TB]
+    const u32 col = (u32)bx * TX + tid;
+    const u32 b0 = (u32)by * TB;
+    const bool centred = (a.L * a.logB == 64);
+    const u32 halfB = 1u << (a.logB - 1);
+    // rows that fit before the 64-bit lanes could overflow: each product < 2^(logB+1+32)
+    const u32 max_rows = (a.logB + 33 >= 63) ? 1u : (1u << (63 - a.logB - 33 > 20 ? 20 : 63 - a.logB - 33));
+    u64 A0[TB], A1[TB], F[TB];
+    TK_UNROLL
+    for (int b = 0; b < TB; b++) A0[b] = A1[b] = F[b] = 0;
+    u32 rows_pending = 0;
+    for (u32 c0 = 0; c0 < a.kN; c0 += RC) {
+        const u32 rc = (a.kN - c0 < RC) ? a.kN - c0 : RC;
+        cta_sync();
+        for (u32 idx = tid; idx < rc * TB; idx += TX) {
+            const u32 i = idx / TB, b = idx % TB;
+            const u64 x = (b0 + b < a.B) ? a.in[(size_t)(b0 + b) * (a.kN + 1) + c0 + i] : 0;
+            for (u32 j = 0; j < a.ell; j++) {
+                const u64 d = gl_digit(x, a.L - a.ell + j, a.logB, centred);  // canonical field element
+                const u32 ds = (d > GL_Q / 2) ? (u32)(halfB - (u32)(GL_Q - d)) : (u32)(halfB + (u32)d);
+                dig[(i * a.ell + j) * TB + b] = ds;
+            }
+        }
+        cta_sync();
+        const u32 rows = rc * a.ell;
+        for (u32 r0 = 0; r0 < rows; r0 += max_rows) {
+            const u32 r1 = (rows - r0 < max_rows) ? rows : r0 + max_rows;
+            if (rows_pending + (r1 - r0) > max_rows) {
+                TK_UNROLL
+                for (int b = 0; b < TB; b++) {
+                    F[b] = gl_add(F[b], ks_fold(A0[b], A1[b]));
+                    A0[b] = A1[b] = 0;
+                }
+                rows_pending = 0;
+            }
+            for (u32 r = r0; r < r1; r++) {
+                const u64 kv = (col <= a.n) ? a.ksk[((size_t)c0 * a.ell + r) * (a.n + 1) + col] : 0;
+                const u32 klo = (u32)kv, khi = (u32)(kv >> 32);
+                const u32 *dr = dig + r * TB;
+                TK_UNROLL
+                for (int b = 0; b < TB; b++) {
+                    A0[b] += (u64)dr[b] * klo;
+                    A1[b] += (u64)dr[b] * khi;
+                }
+            }
+            rows_pending += r1 - r0;
+        }
+    }
+    if (col <= a.n) {
+        const u64 off = gl_mul((u64)halfB, a.ksum[col]);
+        for (int b = 0; b < TB; b++) {
+            if (b0 + b >= a.B) break;
+            u64 v = gl_canon(gl_add(F[b], ks_fold(A0[b], A1[b])));
+            v = gl_canon(gl_sub(v, off));
+            if (col == a.n) v = gl_canon(gl_add(v, a.in[(size_t)(b0 + b) * (a.kN + 1) + a.kN]));
+            a.out[(size_t)(b0 + b) * (a.n + 1) + col] = v;
+        }
+    }
+}
+
+// column sums of the key-switch key: ksum[x] = sum_r ksk[r][x] mod q        (one thread per column)
+TK_DEV void ksk_colsum_body(const u64 *ksk, u64 *ksum, u32 rows, u32 cols, u32 col) {
+    if (col >= cols) return;
+    u64 s = 0;
+    for (u32 r = 0; r < rows; r++) s = gl_canon(gl_add(s, ksk[(size_t)r * cols + col]));
+    ksum[col] = s;
+}
+
+// fold 1/N and the sign of the mask GLevs into an NTT-domain GGSW array (vtfhe/ggsw_ct.rs:108-111:
+// result = GLev_k - sum_{j<k} GLev_j, and crypto/poly.rs:62-63: final * NINV).  k = 1.
+TK_DEV u64 ggsw_fold_elem(u64 v, u64 ninv, u32 glev_index /* 0 = mask, 1 = body */) {
+    const u64 s = gl_mul(v, ninv);
+    return glev_index == 0 ? gl_neg(s) : s;
+}
