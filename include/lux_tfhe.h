@@ -1,0 +1,140 @@
+/*
+ * lux_tfhe.h — C ABI of the B200-native TFHE evaluation engine (libluxtfhe_b200.so).
+ *
+ * This is the drop-in boundary for the reference's evaluation hot path.  Reference
+ * interfaces each entry point replaces (paths relative to /root/reference):
+ *
+ *   packages/wasm/src/index.ts:14-23   LuxFHE.{add,sub,eq,lt}(ct1, ct2, bootstrapKey, secretKey)
+ *   packages/wasm/src/node.ts:29-96    init()/getLuxFHE(); keys and ciphertexts as Uint8Array by value
+ *   js/v2-sdk/src/luxd/client.ts:128-147  POST /evaluate {op, left, right?, bitWidth}; ops at :34-39
+ *   research/verifiable-fhe/src/main.rs:19-67 + vtfhe/ivc_based_vpbs.rs:159-386   one PBS
+ *   research/verifiable-fhe/src/vtfhe/crypto/{poly,lwe,glwe,ggsw,mod}.rs           the pieces
+ *
+ * Differences a caller sees: the bootstrap key is uploaded ONCE (lux_load_*) and stays resident
+ * in HBM in the NTT domain instead of being passed by value on every call; every op has a batch
+ * dimension; errors are return codes + lux_last_error() instead of JS exceptions.
+ *
+ * Conventions
+ *   - every function returns LUX_OK (0) or a negative lux_status; nothing aborts the process
+ *   - all values are canonical Goldilocks elements (uint64_t < q = 2^64 - 2^32 + 1), little-endian
+ *   - layouts are the reference's flatten() orders (crypto/ggsw.rs:62-64, glev.rs:52-54, glwe.rs:133-135):
+ *       LWE  [n+1] = mask..., body          GLWE [(k+1)][N] = mask polys..., body poly
+ *       GGSW [(k+1)][ell][(k+1)][N]         BSK [n] GGSW          LWE-KSK [k*N][ell_ks][n+1]
+ *   - host pointers unless the function name ends in _device; the caller owns every buffer it
+ *     passes; the engine owns device memory; no pointer outlives the call except handles
+ *   - calls on one engine are serialised by the caller (one engine per GPU, one process per GPU)
+ *   - no CPU fallback exists: without a CUDA device lux_engine_create fails with LUX_ERR_NO_DEVICE
+ */
+#ifndef LUX_TFHE_H
+#define LUX_TFHE_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LUX_Q 0xFFFFFFFF00000001ULL
+
+typedef enum {
+    LUX_OK = 0,
+    LUX_ERR_INVALID = -1,     /* bad argument / unsupported parameter combination */
+    LUX_ERR_NO_DEVICE = -2,   /* no usable CUDA device */
+    LUX_ERR_CUDA = -3,        /* CUDA runtime error (message in lux_last_error) */
+    LUX_ERR_NO_KEY = -4,      /* evaluation key needed by the call has not been loaded */
+    LUX_ERR_OOM = -5
+} lux_status;
+
+/* order of key switch and bootstrap inside one PBS */
+#define LUX_ORDER_PBS_GLWEKS 0 /* in-tree order: mod-switch, blind rotate, GLWE key switch, partial extract
+                                  (vtfhe/ivc_based_vpbs.rs:109-124,355-371).  ct length n+1 */
+#define LUX_ORDER_LWEKS_PBS 1  /* "KS_PBS" (PARAM_MESSAGE_2_CARRY_2_KS_PBS_*, sdk/relayer/src/tfhe.ts:15):
+                                  LWE key switch, mod-switch, blind rotate, full extract.  ct length k*N+1 */
+
+/* key domains accepted by lux_load_bsk / lux_load_glwe_ksk */
+#define LUX_DOMAIN_STANDARD 0 /* coefficient domain (Ggsw::encrypt output, crypto/ggsw.rs:26-36) */
+#define LUX_DOMAIN_NTT 1      /* the reference's NTT domain (compute_bsk output, crypto/mod.rs:41-44) */
+
+typedef struct {
+    uint32_t n;       /* small LWE dimension                       main.rs:27 */
+    uint32_t N;       /* ring degree: 512, 1024, 2048 or 4096      ntt/mod.rs:9 */
+    uint32_t k;       /* GLWE dimension; the engine supports k = 1 main.rs:26 (K = k+1) */
+    uint32_t ell;     /* gadget levels of the external product     main.rs:24 */
+    uint32_t logB;    /* log2 gadget base                          main.rs:23 */
+    uint32_t ell_ks;  /* LWE key switch levels (order 1); for order 0 the GLWE-KS reuses (ell, logB) */
+    uint32_t logB_ks; /* log2 base of the LWE key switch (<= 24) */
+    uint32_t order;   /* LUX_ORDER_* */
+} lux_params;
+
+typedef struct lux_engine lux_engine;
+
+/* ---- lifecycle -------------------------------------------------------------------------------- */
+const char *lux_version(void);                                   /* replaces LuxFHE.version(), index.ts:15 */
+int lux_engine_create(const lux_params *p, int device, lux_engine **out);
+void lux_engine_destroy(lux_engine *e);
+/* message of the last failing call on this engine (or of the last failing create when e == NULL) */
+const char *lux_last_error(const lux_engine *e);
+int lux_engine_params(const lux_engine *e, lux_params *out);
+size_t lux_ct_words(const lux_engine *e);                        /* words per ciphertext entering/leaving a PBS */
+/* kernels launched by this engine since creation (bench.py's gpu_launches) */
+uint64_t lux_launch_count(const lux_engine *e);
+/* when enabled, PBS calls bracket their kernels with CUDA events on the engine's stream */
+int lux_set_timing(lux_engine *e, int enabled);
+/* device milliseconds of the last timed PBS call: out[0] = key switch kernel, out[1] = blind-rotate kernel */
+int lux_last_timing(const lux_engine *e, float out[2]);
+int lux_synchronize(lux_engine *e);
+
+/* ---- evaluation keys: uploaded once, converted to the NTT domain on the device ------------------
+ * replaces the per-call `bootstrapKey` argument of index.ts:19-22 */
+int lux_load_bsk(lux_engine *e, const uint64_t *bsk, size_t n_words, int domain);          /* crypto/mod.rs:29-45 */
+int lux_load_glwe_ksk(lux_engine *e, const uint64_t *ksk, size_t n_words, int domain);     /* crypto/ggsw.rs:38-48 */
+int lux_load_lwe_ksk(lux_engine *e, const uint64_t *ksk, size_t n_words);                  /* vtfhe/mod.rs:31-54 */
+/* multi-GPU replication: the converted keys of rank 0 are broadcast (NCCL, by the caller) as one
+ * opaque device blob and adopted by the other ranks.  bytes = lux_key_blob_bytes(). */
+size_t lux_key_blob_bytes(const lux_engine *e);
+int lux_export_keys_device(lux_engine *e, void *dev_blob, size_t bytes);
+int lux_import_keys_device(lux_engine *e, const void *dev_blob, size_t bytes);
+
+/* ---- programmable bootstrap, batched ------------------------------------------------------------
+ * lwe_in  [B][ct_words]   testvs [n_luts][N] test-vector polynomials (crypto/mod.rs:17-27)
+ * lut_idx [B] index into testvs per ciphertext, or NULL for all 0      lwe_out [B][ct_words]
+ * replaces verified_pbs's FHE arithmetic (ivc_based_vpbs.rs:277-371) */
+int lux_pbs_batch(lux_engine *e, const uint64_t *lwe_in, const uint64_t *testvs, uint32_t n_luts,
+                  const uint32_t *lut_idx, size_t B, uint64_t *lwe_out);
+/* same with every buffer already in device memory; stream = cudaStream_t or NULL for the engine's */
+int lux_pbs_batch_device(lux_engine *e, const uint64_t *d_lwe_in, const uint64_t *d_testvs, uint32_t n_luts,
+                         const uint32_t *d_lut_idx, size_t B, uint64_t *d_lwe_out, void *stream);
+
+/* test vector for a p-entry lookup table with one padding bit: p blocks of N/p copies of
+ * lut[i]*delta, pre-rotated by half a block (get_testv, crypto/mod.rs:17-27).  Host-side helper. */
+int lux_make_testv(uint32_t N, uint32_t p, uint64_t delta, const uint64_t *lut, uint64_t *out);
+uint64_t lux_delta(uint32_t plaintext_space);                    /* get_delta, crypto/lwe.rs:46-48 */
+
+/* ---- the pieces, exposed for parity checks against the reference ------------------------------- */
+/* negacyclic NTT in the reference's convention (crypto/poly.rs:9-64): forward natural -> bit-reversed,
+ * backward bit-reversed -> natural including the 1/N.  N from the engine's parameters. */
+int lux_ntt_forward(lux_engine *e, const uint64_t *in, size_t n_polys, uint64_t *out);
+int lux_ntt_backward(lux_engine *e, const uint64_t *in, size_t n_polys, uint64_t *out);
+/* standalone NTT for any power-of-two N in [8, 2048] (covers every golden vector ntt/params_*.rs) */
+int lux_ntt_any(lux_engine *e, uint32_t N, int inverse, const uint64_t *in, size_t n_polys, uint64_t *out);
+/* signed gadget digits (vtfhe/glwe_poly.rs:28-50): out [count][ceil(64/logB)] field elements, LSB limb first */
+int lux_decompose(lux_engine *e, const uint64_t *in, size_t count, uint32_t logB, uint64_t *out);
+/* mod-switch to [0, 2N] (crypto/lwe.rs:28-38) */
+int lux_mod_switch(lux_engine *e, const uint64_t *in, size_t count, uint32_t *out);
+/* LWE key switch k*N -> n (vtfhe/mod.rs:31-54): in [B][k*N+1] -> out [B][n+1] */
+int lux_lwe_keyswitch(lux_engine *e, const uint64_t *in, size_t B, uint64_t *out);
+/* blind rotation only: lwe [B][n+1] under the small key; runs `steps` CMUX iterations
+ * (steps = n for the whole rotation) and returns the raw accumulators acc_out [B][(k+1)*N]
+ * (blind_rotation_step, vtfhe/mod.rs:119-136) */
+int lux_blind_rotate(lux_engine *e, const uint64_t *lwe, const uint64_t *testvs, uint32_t n_luts,
+                     const uint32_t *lut_idx, size_t B, uint32_t steps, uint64_t *acc_out);
+/* GGSW (x) GLWE for `count` independent pairs (vtfhe/ggsw_ct.rs:98-112); ggsw in `domain` */
+int lux_external_product(lux_engine *e, const uint64_t *ggsw, int domain, const uint64_t *glwe_in, size_t count,
+                         uint64_t *glwe_out);
+
+/* ---- radix integers (euintN) over the PBS: see lux_radix.h ------------------------------------ */
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,131 @@
+// br_inst.cuh — instantiates the templated kernels for ONE ring size (LUX_LOGN) and defines its
+// launchers.  Included by br_n9.cu .. br_n12.cu, which exist only so that nvcc compiles the ring
+// sizes in parallel.
+#include "engine.h"
+
+template <int LOGN, int TEAMS>
+__global__ void __launch_bounds__(Tile<LOGN>::T *TEAMS, 1) blind_rotate_kernel(const BRArgs a) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    blind_rotate_body<LOGN, TEAMS>(a, threadIdx.x, blockIdx.x, smem);
+}
+
+template <int LOGN, int TEAMS>
+__global__ void __launch_bounds__(Tile<LOGN>::T *TEAMS, 1) ntt_batch_kernel(const NttArgs a) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    ntt_batch_body<LOGN, TEAMS>(a, threadIdx.x, blockIdx.x, gridDim.x, smem);
+}
+
+// GGSW (x) GLWE for independent pairs: team `ct` multiplies ggsw[ct] with glwe[ct]
+template <int LOGN, int TEAMS>
+__global__ void __launch_bounds__(Tile<LOGN>::T *TEAMS, 1)
+    external_product_kernel(const BRArgs a, const u64 *glwe_in, size_t ggsw_stride) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    constexpr int N = Tile<LOGN>::N, T = Tile<LOGN>::T;
+    u64 *tw_f = (u64 *)smem, *tw_i = tw_f + N;
+    const int tid = threadIdx.x, team = tid / T, tau = tid % T;
+    u64 *acc = tw_i + N + (size_t)team * 4 * N;
+    u64 *xb0 = acc + 2 * N, *xb1 = xb0 + N;
+    for (int i = tid; i < N; i += T * TEAMS) {
+        tw_f[i] = a.tw_fwd[i];
+        tw_i[i] = a.tw_inv[i];
+    }
+    __syncthreads();
+    const u32 ct = blockIdx.x * TEAMS + team;
+    if (ct >= a.B) return;
+    for (int p = tau; p < 2 * N; p += T) acc[p] = glwe_in[(size_t)ct * 2 * N + p];
+    team_sync(team, T);
+    team_external_product<LOGN, false>(a, a.bsk + (size_t)ct * ggsw_stride, 0, acc, xb0, xb1, tw_f, tw_i, tau, team);
+    for (int p = tau; p < 2 * N; p += T) a.out[(size_t)ct * 2 * N + p] = acc[p];
+}
+
+
+template <int LOGN, int TEAMS>
+static int launch_br_t(lux_engine *e, const BRArgs &a, cudaStream_t s) {
+    constexpr size_t smem = blind_rotate_smem_bytes<LOGN, TEAMS>();
+    static bool configured[64] = {};
+    if (!configured[e->device & 63]) {
+        CUDA_TRY(e, cudaFuncSetAttribute(blind_rotate_kernel<LOGN, TEAMS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured[e->device & 63] = true;
+    }
+    const u32 grid = (a.B + TEAMS - 1) / TEAMS;
+    blind_rotate_kernel<LOGN, TEAMS><<<grid, Tile<LOGN>::T * TEAMS, smem, s>>>(a);
+    e->launches++;
+    CUDA_TRY(e, cudaGetLastError());
+    return LUX_OK;
+}
+
+// ciphertexts per CTA: as few as keep the batch within one wave of CTAs, up to the SMEM limit
+static int pick_teams(const lux_engine *e, size_t B, int max_teams) {
+    if (e->force_teams > 0 && e->force_teams <= max_teams) return e->force_teams;
+    for (int t = 1; t < max_teams; t++)
+        if (B <= (size_t)e->sm_count * t) return t;
+    return max_teams;
+}
+
+template <int LOGN, int TEAMS>
+static int launch_ntt_t(lux_engine *e, const NttArgs &a, cudaStream_t s) {
+    constexpr size_t smem = sizeof(u64) * ((size_t)Tile<LOGN>::N + (size_t)TEAMS * 2 * Tile<LOGN>::N);
+    static bool configured[64] = {};
+    if (!configured[e->device & 63]) {
+        CUDA_TRY(e, cudaFuncSetAttribute(ntt_batch_kernel<LOGN, TEAMS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured[e->device & 63] = true;
+    }
+    u32 grid = (a.n_polys + TEAMS - 1) / TEAMS;
+    const u32 cap = (u32)e->sm_count * 8;
+    if (grid > cap) grid = cap;
+    if (grid == 0) return LUX_OK;
+    ntt_batch_kernel<LOGN, TEAMS><<<grid, Tile<LOGN>::T * TEAMS, smem, s>>>(a);
+    e->launches++;
+    CUDA_TRY(e, cudaGetLastError());
+    return LUX_OK;
+}
+
+template <int LOGN>
+static int launch_xp_t(lux_engine *e, const BRArgs &a, const u64 *d_glwe, size_t stride, cudaStream_t s) {
+    constexpr int TEAMS = 1;
+    constexpr size_t smem = blind_rotate_smem_bytes<LOGN, TEAMS>();
+    CUDA_TRY(e, cudaFuncSetAttribute(external_product_kernel<LOGN, TEAMS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    external_product_kernel<LOGN, TEAMS><<<a.B, Tile<LOGN>::T * TEAMS, smem, s>>>(a, d_glwe, stride);
+    e->launches++;
+    CUDA_TRY(e, cudaGetLastError());
+    return LUX_OK;
+}
+
+#define LUX_CAT_(a, b) a##b
+#define LUX_CAT(a, b) LUX_CAT_(a, b)
+
+// TEAMS variants per ring size: SMEM = 16N + 32N*TEAMS bytes <= 227 KiB
+int LUX_CAT(lux_launch_br_, LUX_LOGN)(lux_engine *e, const BRArgs &a, cudaStream_t s) {
+#if LUX_LOGN == 9
+    const int t = pick_teams(e, a.B, 12);
+    if (t <= 1) return launch_br_t<9, 1>(e, a, s);
+    if (t <= 4) return launch_br_t<9, 4>(e, a, s);
+    return launch_br_t<9, 12>(e, a, s);
+#elif LUX_LOGN == 10
+    const int t = pick_teams(e, a.B, 6);
+    if (t <= 1) return launch_br_t<10, 1>(e, a, s);
+    if (t <= 3) return launch_br_t<10, 3>(e, a, s);
+    return launch_br_t<10, 6>(e, a, s);
+#elif LUX_LOGN == 11
+    const int t = pick_teams(e, a.B, 3);
+    if (t <= 1) return launch_br_t<11, 1>(e, a, s);
+    if (t <= 2) return launch_br_t<11, 2>(e, a, s);
+    return launch_br_t<11, 3>(e, a, s);
+#else
+    return launch_br_t<12, 1>(e, a, s);
+#endif
+}
+
+int LUX_CAT(lux_launch_ntt_, LUX_LOGN)(lux_engine *e, const NttArgs &a, cudaStream_t s) {
+#if LUX_LOGN <= 10
+    return launch_ntt_t<LUX_LOGN, 4>(e, a, s);
+#elif LUX_LOGN == 11
+    return launch_ntt_t<11, 2>(e, a, s);
+#else
+    return launch_ntt_t<12, 1>(e, a, s);
+#endif
+}
+
+int LUX_CAT(lux_launch_xp_, LUX_LOGN)(lux_engine *e, const BRArgs &a, const u64 *d_glwe, size_t stride, cudaStream_t s) {
+    return launch_xp_t<LUX_LOGN>(e, a, d_glwe, stride, s);
+}

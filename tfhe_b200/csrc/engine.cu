@@ -1,0 +1,636 @@
+// engine.cu — C ABI (include/lux_tfhe.h) over the sm_100a kernels in tfhe_kernels.cuh.
+// One engine per GPU; one process per GPU.  No CPU fallback: every entry point that computes
+// launches CUDA kernels, and lux_engine_create fails without a device.
+#include "engine.h"
+
+#include <cstdio>
+#include <cstring>
+#include <new>
+
+// templated kernels (blind rotate, batched NTT, external product) are instantiated per ring size in
+// br_n{9,10,11,12}.cu (br_inst.cuh) so that they compile in parallel.
+constexpr int KS_TB = 8, KS_TX = 128, KS_RC = 64;
+__global__ void __launch_bounds__(KS_TX) lwe_keyswitch_kernel(const KSArgs a) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    lwe_keyswitch_body<KS_TB, KS_TX, KS_RC>(a, threadIdx.x, blockIdx.x, blockIdx.y, smem);
+}
+
+__global__ void ksk_colsum_kernel(const u64 *ksk, u64 *ksum, u32 rows, u32 cols) {
+    ksk_colsum_body(ksk, ksum, rows, cols, blockIdx.x * blockDim.x + threadIdx.x);
+}
+
+// [n_ggsw][2][ell][2][N]: multiply by 1/N, negate the mask GLev (index 0)
+__global__ void ggsw_fold_kernel(u64 *ggsw, size_t total, u32 glev_words, u64 ninv) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x)
+        ggsw[i] = ggsw_fold_elem(ggsw[i], ninv, (u32)((i / glev_words) & 1));
+}
+
+__global__ void decompose_kernel(const u64 *in, u64 *out, size_t count, u32 logB, u32 L) {
+    const bool centred = (L * logB == 64);
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < count * L; i += (size_t)gridDim.x * blockDim.x)
+        out[i] = gl_digit(in[i / L], (u32)(i % L), logB, centred);
+}
+
+__global__ void mod_switch_kernel(const u64 *in, u32 *out, size_t count, u32 logN) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < count; i += (size_t)gridDim.x * blockDim.x)
+        out[i] = gl_mod_switch(in[i], logN);
+}
+
+// any power-of-two N in [8, 2048]: one CTA per polynomial, one thread per butterfly, textbook
+// stage loop in shared memory (crypto/poly.rs:9-64).  Parity utility for the small golden vectors.
+__global__ void ntt_any_kernel(const u64 *in, u64 *out, const u64 *tw, u64 scale, u32 N, u32 inverse) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    u64 *a = (u64 *)smem;
+    const u32 h = threadIdx.x;
+    const u64 *src = in + (size_t)blockIdx.x * N;
+    a[h] = src[h];
+    a[h + N / 2] = src[h + N / 2];
+    __syncthreads();
+    if (!inverse) {
+        for (u32 m = 1; m < N; m <<= 1) {
+            const u32 t = N / (2 * m), i = h / t, j = 2 * i * t + (h % t);
+            u64 u = a[j], v = a[j + t];
+            gl_ct_butterfly(u, v, tw[m + i]);
+            a[j] = gl_canon(u);
+            a[j + t] = gl_canon(v);
+            __syncthreads();
+        }
+    } else {
+        for (u32 m = N / 2; m >= 1; m >>= 1) {
+            const u32 t = N / (2 * m), i = h / t, j = 2 * i * t + (h % t);
+            u64 u = a[j], v = a[j + t];
+            gl_gs_butterfly(u, v, tw[m + i]);
+            a[j] = gl_canon(u);
+            a[j + t] = gl_canon(v);
+            __syncthreads();
+        }
+    }
+    u64 *dst = out + (size_t)blockIdx.x * N;
+    dst[h] = gl_mul(a[h], scale);
+    dst[h + N / 2] = gl_mul(a[h + N / 2], scale);
+}
+
+// ------------------------------------------------------------------------------------------ helpers
+static thread_local char g_create_error[512] = "";
+
+static u32 ilog2u(u32 x) {
+    u32 l = 0;
+    while ((1u << l) < x) l++;
+    return l;
+}
+static u32 bitrev_u(u32 x, u32 bits) {
+    u32 r = 0;
+    for (u32 i = 0; i < bits; i++) r |= ((x >> i) & 1u) << (bits - 1 - i);
+    return r;
+}
+static u64 gl_pow_host(u64 a, u64 e) {
+    u64 r = 1;
+    while (e) {
+        if (e & 1) r = gl_mul(r, a);
+        a = gl_mul(a, a);
+        e >>= 1;
+    }
+    return r;
+}
+
+// NTT tables exactly as the reference derives them (ntt/gen_param_file.sage:3-10,86-88,111-112):
+// psi = 7^((q-1)/2N), ROOTS[j] = psi^bitrev(j), INVROOTS[j] = psi^-bitrev(j), NINV = 2^-logN.
+void lux_host_ntt_tables(u32 N, std::vector<u64> &roots, std::vector<u64> &invroots, u64 &ninv) {
+    const u32 logN = ilog2u(N);
+    const u64 psi = gl_pow_host(7, (GL_Q - 1) / (2ULL * N));
+    const u64 psi_inv = gl_pow_host(psi, GL_Q - 2);
+    std::vector<u64> pw(N), pwi(N);
+    pw[0] = pwi[0] = 1;
+    for (u32 j = 1; j < N; j++) {
+        pw[j] = gl_mul(pw[j - 1], psi);
+        pwi[j] = gl_mul(pwi[j - 1], psi_inv);
+    }
+    roots.resize(N);
+    invroots.resize(N);
+    for (u32 j = 0; j < N; j++) {
+        roots[j] = pw[bitrev_u(j, logN)];
+        invroots[j] = pwi[bitrev_u(j, logN)];
+    }
+    ninv = gl_pow_host(gl_pow_host(2, GL_Q - 2), logN);
+}
+
+static int ensure_scratch(lux_engine *e, int slot, size_t bytes) {
+    if (e->scratch_bytes[slot] >= bytes) return LUX_OK;
+    if (e->scratch[slot]) cudaFree(e->scratch[slot]);
+    e->scratch[slot] = nullptr;
+    e->scratch_bytes[slot] = 0;
+    size_t want = bytes + bytes / 4 + 4096;
+    cudaError_t st = cudaMalloc(&e->scratch[slot], want);
+    if (st != cudaSuccess) LUX_FAIL(e, LUX_ERR_OOM, "cudaMalloc(%zu) for scratch %d: %s", want, slot, cudaGetErrorString(st));
+    e->scratch_bytes[slot] = want;
+    return LUX_OK;
+}
+
+static size_t ggsw_words(const lux_params &p) { return (size_t)(p.k + 1) * p.ell * (p.k + 1) * p.N; }
+
+// ------------------------------------------------------------------------------------ kernel launchers
+static int launch_br(lux_engine *e, const BRArgs &a, cudaStream_t s) {
+    int rc;
+    switch (e->logN) {
+        case 9: rc = lux_launch_br_9(e, a, s); break;
+        case 10: rc = lux_launch_br_10(e, a, s); break;
+        case 11: rc = lux_launch_br_11(e, a, s); break;
+        case 12: rc = lux_launch_br_12(e, a, s); break;
+        default: LUX_FAIL(e, LUX_ERR_INVALID, "unsupported N");
+    }
+    return rc;
+}
+
+// batched NTT of n_polys device polynomials, out may alias in
+static int launch_ntt(lux_engine *e, const u64 *d_in, u64 *d_out, size_t n_polys, bool inverse, u64 scale, cudaStream_t s) {
+    NttArgs a{d_in, d_out, inverse ? e->d_tw_inv : e->d_tw_fwd, scale, (u32)n_polys, inverse ? 1u : 0u};
+    switch (e->logN) {
+        case 9: return lux_launch_ntt_9(e, a, s);
+        case 10: return lux_launch_ntt_10(e, a, s);
+        case 11: return lux_launch_ntt_11(e, a, s);
+        case 12: return lux_launch_ntt_12(e, a, s);
+    }
+    LUX_FAIL(e, LUX_ERR_INVALID, "unsupported N");
+}
+
+static int launch_ks(lux_engine *e, const u64 *d_in, u64 *d_out, size_t B, cudaStream_t s) {
+    const lux_params &p = e->p;
+    KSArgs a{p.n, p.k * p.N, p.ell_ks, p.logB_ks, e->L_ks, (u32)B, e->d_lksk, e->d_ksum, d_in, d_out};
+    const size_t smem = sizeof(u32) * KS_RC * p.ell_ks * KS_TB;
+    static bool configured[64] = {};
+    if (!configured[e->device & 63]) {
+        CUDA_TRY(e, cudaFuncSetAttribute(lwe_keyswitch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024));
+        configured[e->device & 63] = true;
+    }
+    dim3 grid((p.n + 1 + KS_TX - 1) / KS_TX, (unsigned)((B + KS_TB - 1) / KS_TB));
+    lwe_keyswitch_kernel<<<grid, KS_TX, smem, s>>>(a);
+    e->launches++;
+    CUDA_TRY(e, cudaGetLastError());
+    return LUX_OK;
+}
+
+static BRArgs make_br_args(const lux_engine *e, const u64 *d_lwe, const u64 *d_testv, const u32 *d_idx, size_t B, u64 *d_out) {
+    BRArgs a{};
+    a.n = e->p.n;
+    a.steps = e->p.n;
+    a.ell = e->p.ell;
+    a.logB = e->p.logB;
+    a.L = e->L;
+    a.B = (u32)B;
+    a.bsk = e->d_bsk;
+    a.ksk = nullptr;
+    a.lwe = d_lwe;
+    a.testv = d_testv;
+    a.lut_idx = d_idx;
+    a.out = d_out;
+    a.tw_fwd = e->d_tw_fwd;
+    a.tw_inv = e->d_tw_inv;
+    return a;
+}
+
+// --------------------------------------------------------------------------------------------- ABI
+extern "C" {
+
+const char *lux_version(void) { return "tfhe_b200 0.1.0 (sm_100a, Goldilocks exact-NTT PBS)"; }
+
+const char *lux_last_error(const lux_engine *e) { return e ? e->err : g_create_error; }
+
+int lux_engine_create(const lux_params *p, int device, lux_engine **out) {
+#define CREATE_FAIL(code, ...)                                          \
+    do {                                                                \
+        snprintf(g_create_error, sizeof(g_create_error), __VA_ARGS__);  \
+        return (code);                                                  \
+    } while (0)
+    if (!p || !out) CREATE_FAIL(LUX_ERR_INVALID, "null argument");
+    *out = nullptr;
+    if (p->k != 1) CREATE_FAIL(LUX_ERR_INVALID, "only k = 1 is supported (got %u)", p->k);
+    if (p->N != 512 && p->N != 1024 && p->N != 2048 && p->N != 4096)
+        CREATE_FAIL(LUX_ERR_INVALID, "N must be 512, 1024, 2048 or 4096 (got %u)", p->N);
+    if (p->logB < 1 || p->logB > 62 || p->ell < 1 || p->ell > (64 + p->logB - 1) / p->logB)
+        CREATE_FAIL(LUX_ERR_INVALID, "bad gadget (ell=%u, logB=%u)", p->ell, p->logB);
+    if (p->order != LUX_ORDER_PBS_GLWEKS && p->order != LUX_ORDER_LWEKS_PBS)
+        CREATE_FAIL(LUX_ERR_INVALID, "bad order %u", p->order);
+    if (p->order == LUX_ORDER_LWEKS_PBS &&
+        (p->logB_ks < 1 || p->logB_ks > 24 || p->ell_ks < 1 || p->ell_ks > (64 + p->logB_ks - 1) / p->logB_ks))
+        CREATE_FAIL(LUX_ERR_INVALID, "bad key-switch gadget (ell_ks=%u, logB_ks=%u)", p->ell_ks, p->logB_ks);
+    if (p->n < 1 || (p->order == LUX_ORDER_PBS_GLWEKS && p->n > p->N))
+        CREATE_FAIL(LUX_ERR_INVALID, "bad LWE dimension n=%u", p->n);
+    int ndev = 0;
+    cudaError_t st = cudaGetDeviceCount(&ndev);
+    if (st != cudaSuccess || ndev == 0)
+        CREATE_FAIL(LUX_ERR_NO_DEVICE, "no CUDA device: %s (this engine has no CPU fallback)",
+                    st != cudaSuccess ? cudaGetErrorString(st) : "device count is 0");
+    if (device < 0 || device >= ndev) CREATE_FAIL(LUX_ERR_INVALID, "device %d out of range [0,%d)", device, ndev);
+    if ((st = cudaSetDevice(device)) != cudaSuccess) CREATE_FAIL(LUX_ERR_CUDA, "cudaSetDevice: %s", cudaGetErrorString(st));
+    cudaDeviceProp prop;
+    if ((st = cudaGetDeviceProperties(&prop, device)) != cudaSuccess)
+        CREATE_FAIL(LUX_ERR_CUDA, "cudaGetDeviceProperties: %s", cudaGetErrorString(st));
+    if (prop.major != 10)
+        CREATE_FAIL(LUX_ERR_NO_DEVICE, "device %d is sm_%d%d; this build carries sm_100a code only", device, prop.major, prop.minor);
+
+    lux_engine *e = new (std::nothrow) lux_engine();
+    if (!e) CREATE_FAIL(LUX_ERR_OOM, "out of host memory");
+    e->p = *p;
+    e->device = device;
+    e->sm_count = prop.multiProcessorCount;
+    e->logN = ilog2u(p->N);
+    e->L = (64 + p->logB - 1) / p->logB;
+    e->L_ks = p->logB_ks ? (64 + p->logB_ks - 1) / p->logB_ks : 0;
+    std::vector<u64> roots, inv;
+    lux_host_ntt_tables(p->N, roots, inv, e->ninv);
+    bool ok = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) == cudaSuccess;
+    ok = ok && cudaMalloc(&e->d_tw_fwd, sizeof(u64) * p->N * 2) == cudaSuccess;
+    if (ok) {
+        e->d_tw_inv = e->d_tw_fwd + p->N;
+        ok = cudaMemcpy(e->d_tw_fwd, roots.data(), sizeof(u64) * p->N, cudaMemcpyHostToDevice) == cudaSuccess &&
+             cudaMemcpy(e->d_tw_inv, inv.data(), sizeof(u64) * p->N, cudaMemcpyHostToDevice) == cudaSuccess;
+    }
+    // key blob: [header 8 words][bsk][glwe ksk][lwe ksk][ksum]
+    e->bsk_words = (size_t)p->n * ggsw_words(*p);
+    e->gksk_words = p->order == LUX_ORDER_PBS_GLWEKS ? ggsw_words(*p) : 0;
+    e->lksk_words = p->order == LUX_ORDER_LWEKS_PBS ? (size_t)p->k * p->N * p->ell_ks * (p->n + 1) : 0;
+    e->ksum_words = p->order == LUX_ORDER_LWEKS_PBS ? (size_t)p->n + 1 : 0;
+    e->blob_words = 8 + e->bsk_words + e->gksk_words + e->lksk_words + e->ksum_words;
+    ok = ok && cudaMalloc(&e->d_blob, sizeof(u64) * e->blob_words) == cudaSuccess;
+    for (int i = 0; i < 4 && ok; i++) ok = cudaEventCreate(&e->ev[i]) == cudaSuccess;
+    if (!ok) {
+        snprintf(g_create_error, sizeof(g_create_error), "device allocation failed: %s", cudaGetErrorString(cudaGetLastError()));
+        lux_engine_destroy(e);
+        return LUX_ERR_OOM;
+    }
+    e->d_bsk = e->d_blob + 8;
+    e->d_gksk = e->d_bsk + e->bsk_words;
+    e->d_lksk = e->d_gksk + e->gksk_words;
+    e->d_ksum = e->d_lksk + e->lksk_words;
+    *out = e;
+    return LUX_OK;
+#undef CREATE_FAIL
+}
+
+void lux_engine_destroy(lux_engine *e) {
+    if (!e) return;
+    cudaSetDevice(e->device);
+    if (e->stream) cudaStreamSynchronize(e->stream);
+    for (int i = 0; i < LUX_SCRATCH_SLOTS; i++)
+        if (e->scratch[i]) cudaFree(e->scratch[i]);
+    for (auto &kv : e->any_tables) cudaFree(kv.second);
+    if (e->d_tw_fwd) cudaFree(e->d_tw_fwd);
+    if (e->d_blob) cudaFree(e->d_blob);
+    for (int i = 0; i < 4; i++)
+        if (e->ev[i]) cudaEventDestroy(e->ev[i]);
+    if (e->stream) cudaStreamDestroy(e->stream);
+    delete e;
+}
+
+int lux_engine_params(const lux_engine *e, lux_params *out) {
+    if (!e || !out) return LUX_ERR_INVALID;
+    *out = e->p;
+    return LUX_OK;
+}
+size_t lux_ct_words(const lux_engine *e) {
+    return e->p.order == LUX_ORDER_LWEKS_PBS ? (size_t)e->p.k * e->p.N + 1 : (size_t)e->p.n + 1;
+}
+uint64_t lux_launch_count(const lux_engine *e) { return e ? e->launches : 0; }
+int lux_set_timing(lux_engine *e, int enabled) {
+    if (!e) return LUX_ERR_INVALID;
+    e->timing = enabled != 0;
+    return LUX_OK;
+}
+int lux_last_timing(const lux_engine *e, float out[2]) {
+    if (!e || !out) return LUX_ERR_INVALID;
+    out[0] = e->last_ms[0];
+    out[1] = e->last_ms[1];
+    return LUX_OK;
+}
+int lux_synchronize(lux_engine *e) {
+    if (!e) return LUX_ERR_INVALID;
+    CUDA_TRY(e, cudaSetDevice(e->device));
+    CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    return LUX_OK;
+}
+int lux_debug_force_teams(lux_engine *e, int teams) {
+    if (!e) return LUX_ERR_INVALID;
+    e->force_teams = teams;
+    return LUX_OK;
+}
+
+// ---- keys
+static int load_ggsw_array(lux_engine *e, u64 *d_dst, const u64 *src, size_t words, size_t expect, int domain, const char *what) {
+    if (!src) LUX_FAIL(e, LUX_ERR_INVALID, "%s: null pointer", what);
+    if (words != expect) LUX_FAIL(e, LUX_ERR_INVALID, "%s: expected %zu words, got %zu", what, expect, words);
+    if (domain != LUX_DOMAIN_STANDARD && domain != LUX_DOMAIN_NTT) LUX_FAIL(e, LUX_ERR_INVALID, "%s: bad domain %d", what, domain);
+    CUDA_TRY(e, cudaSetDevice(e->device));
+    CUDA_TRY(e, cudaMemcpyAsync(d_dst, src, sizeof(u64) * words, cudaMemcpyHostToDevice, e->stream));
+    if (domain == LUX_DOMAIN_STANDARD) {
+        int rc = launch_ntt(e, d_dst, d_dst, words / e->p.N, false, 1, e->stream);  // crypto/mod.rs:41-44
+        if (rc) return rc;
+    }
+    const u32 glev_words = e->p.ell * 2 * e->p.N;
+    ggsw_fold_kernel<<<e->sm_count * 4, 256, 0, e->stream>>>(d_dst, words, glev_words, e->ninv);
+    e->launches++;
+    CUDA_TRY(e, cudaGetLastError());
+    CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    return LUX_OK;
+}
+
+int lux_load_bsk(lux_engine *e, const uint64_t *bsk, size_t n_words, int domain) {
+    if (!e) return LUX_ERR_INVALID;
+    int rc = load_ggsw_array(e, e->d_bsk, bsk, n_words, e->bsk_words, domain, "lux_load_bsk");
+    if (rc == LUX_OK) e->has_bsk = true;
+    return rc;
+}
+int lux_load_glwe_ksk(lux_engine *e, const uint64_t *ksk, size_t n_words, int domain) {
+    if (!e) return LUX_ERR_INVALID;
+    if (e->p.order != LUX_ORDER_PBS_GLWEKS) LUX_FAIL(e, LUX_ERR_INVALID, "GLWE key switch key only applies to LUX_ORDER_PBS_GLWEKS");
+    int rc = load_ggsw_array(e, e->d_gksk, ksk, n_words, e->gksk_words, domain, "lux_load_glwe_ksk");
+    if (rc == LUX_OK) e->has_gksk = true;
+    return rc;
+}
+int lux_load_lwe_ksk(lux_engine *e, const uint64_t *ksk, size_t n_words) {
+    if (!e) return LUX_ERR_INVALID;
+    if (e->p.order != LUX_ORDER_LWEKS_PBS) LUX_FAIL(e, LUX_ERR_INVALID, "LWE key switch key only applies to LUX_ORDER_LWEKS_PBS");
+    if (!ksk) LUX_FAIL(e, LUX_ERR_INVALID, "lux_load_lwe_ksk: null pointer");
+    if (n_words != e->lksk_words) LUX_FAIL(e, LUX_ERR_INVALID, "lux_load_lwe_ksk: expected %zu words, got %zu", e->lksk_words, n_words);
+    CUDA_TRY(e, cudaSetDevice(e->device));
+    CUDA_TRY(e, cudaMemcpyAsync(e->d_lksk, ksk, sizeof(u64) * n_words, cudaMemcpyHostToDevice, e->stream));
+    const u32 cols = e->p.n + 1, rows = e->p.k * e->p.N * e->p.ell_ks;
+    ksk_colsum_kernel<<<(cols + 127) / 128, 128, 0, e->stream>>>(e->d_lksk, e->d_ksum, rows, cols);
+    e->launches++;
+    CUDA_TRY(e, cudaGetLastError());
+    CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    e->has_lksk = true;
+    return LUX_OK;
+}
+
+size_t lux_key_blob_bytes(const lux_engine *e) { return e ? sizeof(u64) * e->blob_words : 0; }
+
+int lux_export_keys_device(lux_engine *e, void *dev_blob, size_t bytes) {
+    if (!e || !dev_blob) return LUX_ERR_INVALID;
+    if (bytes != sizeof(u64) * e->blob_words) LUX_FAIL(e, LUX_ERR_INVALID, "key blob is %zu bytes, got %zu", sizeof(u64) * e->blob_words, bytes);
+    CUDA_TRY(e, cudaSetDevice(e->device));
+    u64 hdr[8] = {0x4c55584b45593031ULL, e->has_bsk, e->has_gksk, e->has_lksk, e->blob_words, 0, 0, 0};
+    CUDA_TRY(e, cudaMemcpyAsync(e->d_blob, hdr, sizeof(hdr), cudaMemcpyHostToDevice, e->stream));
+    CUDA_TRY(e, cudaMemcpyAsync(dev_blob, e->d_blob, bytes, cudaMemcpyDeviceToDevice, e->stream));
+    CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    return LUX_OK;
+}
+int lux_import_keys_device(lux_engine *e, const void *dev_blob, size_t bytes) {
+    if (!e || !dev_blob) return LUX_ERR_INVALID;
+    if (bytes != sizeof(u64) * e->blob_words) LUX_FAIL(e, LUX_ERR_INVALID, "key blob is %zu bytes, got %zu", sizeof(u64) * e->blob_words, bytes);
+    CUDA_TRY(e, cudaSetDevice(e->device));
+    u64 hdr[8];
+    CUDA_TRY(e, cudaMemcpy(hdr, dev_blob, sizeof(hdr), cudaMemcpyDeviceToHost));
+    if (hdr[0] != 0x4c55584b45593031ULL || hdr[4] != e->blob_words) LUX_FAIL(e, LUX_ERR_INVALID, "key blob header mismatch");
+    CUDA_TRY(e, cudaMemcpyAsync(e->d_blob, dev_blob, bytes, cudaMemcpyDeviceToDevice, e->stream));
+    CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    e->has_bsk = hdr[1] != 0;
+    e->has_gksk = hdr[2] != 0;
+    e->has_lksk = hdr[3] != 0;
+    return LUX_OK;
+}
+
+// ---- PBS
+int lux_pbs_batch_device(lux_engine *e, const uint64_t *d_in, const uint64_t *d_testvs, uint32_t n_luts,
+                         const uint32_t *d_lut_idx, size_t B, uint64_t *d_out, void *stream) {
+    if (!e) return LUX_ERR_INVALID;
+    if (!d_in || !d_testvs || !d_out || n_luts == 0) LUX_FAIL(e, LUX_ERR_INVALID, "lux_pbs_batch_device: null/empty argument");
+    if (B == 0) return LUX_OK;
+    if (B > 0x7fffffffu) LUX_FAIL(e, LUX_ERR_INVALID, "batch too large");
+    if (!e->has_bsk) LUX_FAIL(e, LUX_ERR_NO_KEY, "bootstrap key not loaded");
+    const bool ks_first = e->p.order == LUX_ORDER_LWEKS_PBS;
+    if (ks_first && !e->has_lksk) LUX_FAIL(e, LUX_ERR_NO_KEY, "LWE key switch key not loaded");
+    if (!ks_first && !e->has_gksk) LUX_FAIL(e, LUX_ERR_NO_KEY, "GLWE key switch key not loaded");
+    CUDA_TRY(e, cudaSetDevice(e->device));
+    cudaStream_t s = stream ? (cudaStream_t)stream : e->stream;
+    const u64 *d_small = d_in;
+    if (e->timing) CUDA_TRY(e, cudaEventRecord(e->ev[0], s));
+    if (ks_first) {
+        int rc = ensure_scratch(e, 0, sizeof(u64) * B * (e->p.n + 1));
+        if (rc) return rc;
+        rc = launch_ks(e, d_in, (u64 *)e->scratch[0], B, s);
+        if (rc) return rc;
+        d_small = (const u64 *)e->scratch[0];
+    }
+    if (e->timing) CUDA_TRY(e, cudaEventRecord(e->ev[1], s));
+    BRArgs a = make_br_args(e, d_small, d_testvs, d_lut_idx, B, d_out);
+    if (ks_first) {
+        a.out_mode = 0;
+    } else {
+        a.ksk = e->d_gksk;
+        a.out_mode = 1;
+        a.n_out = e->p.n;
+    }
+    int rc = launch_br(e, a, s);
+    if (rc) return rc;
+    if (e->timing) {
+        CUDA_TRY(e, cudaEventRecord(e->ev[2], s));
+        CUDA_TRY(e, cudaEventSynchronize(e->ev[2]));
+        CUDA_TRY(e, cudaEventElapsedTime(&e->last_ms[0], e->ev[0], e->ev[1]));
+        CUDA_TRY(e, cudaEventElapsedTime(&e->last_ms[1], e->ev[1], e->ev[2]));
+    }
+    return LUX_OK;
+}
+
+int lux_pbs_batch(lux_engine *e, const uint64_t *lwe_in, const uint64_t *testvs, uint32_t n_luts,
+                  const uint32_t *lut_idx, size_t B, uint64_t *lwe_out) {
+    if (!e) return LUX_ERR_INVALID;
+    if (!lwe_in || !testvs || !lwe_out || n_luts == 0) LUX_FAIL(e, LUX_ERR_INVALID, "lux_pbs_batch: null/empty argument");
+    if (B == 0) return LUX_OK;
+    if (lut_idx)
+        for (size_t b = 0; b < B; b++)
+            if (lut_idx[b] >= n_luts) LUX_FAIL(e, LUX_ERR_INVALID, "lut_idx[%zu] = %u >= n_luts = %u", b, lut_idx[b], n_luts);
+    CUDA_TRY(e, cudaSetDevice(e->device));
+    const size_t w = lux_ct_words(e), N = e->p.N;
+    int rc;
+    if ((rc = ensure_scratch(e, 1, sizeof(u64) * B * w))) return rc;
+    if ((rc = ensure_scratch(e, 2, sizeof(u64) * B * w))) return rc;
+    if ((rc = ensure_scratch(e, 3, sizeof(u64) * n_luts * N + sizeof(u32) * B))) return rc;
+    u64 *d_in = (u64 *)e->scratch[1], *d_out = (u64 *)e->scratch[2], *d_tv = (u64 *)e->scratch[3];
+    u32 *d_idx = lut_idx ? (u32 *)(d_tv + (size_t)n_luts * N) : nullptr;
+    CUDA_TRY(e, cudaMemcpyAsync(d_in, lwe_in, sizeof(u64) * B * w, cudaMemcpyHostToDevice, e->stream));
+    CUDA_TRY(e, cudaMemcpyAsync(d_tv, testvs, sizeof(u64) * n_luts * N, cudaMemcpyHostToDevice, e->stream));
+    if (lut_idx) CUDA_TRY(e, cudaMemcpyAsync(d_idx, lut_idx, sizeof(u32) * B, cudaMemcpyHostToDevice, e->stream));
+    if ((rc = lux_pbs_batch_device(e, d_in, d_tv, n_luts, d_idx, B, d_out, nullptr))) return rc;
+    CUDA_TRY(e, cudaMemcpyAsync(lwe_out, d_out, sizeof(u64) * B * w, cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    return LUX_OK;
+}
+
+// get_testv (crypto/mod.rs:17-27): blocks of lut[i]*delta, then left_shift(block/2) = times X^-(block/2)
+int lux_make_testv(uint32_t N, uint32_t p, uint64_t delta, const uint64_t *lut, uint64_t *out) {
+    if (!lut || !out || p == 0 || N == 0 || N % p) return LUX_ERR_INVALID;
+    const u32 bs = N / p, sh = bs / 2;
+    for (u32 i = 0; i < N; i++) {
+        const u32 src = i + sh;
+        if (src < N)
+            out[i] = gl_mul(lut[src / bs] % GL_Q, delta % GL_Q);
+        else
+            out[i] = gl_neg(gl_mul(lut[(src - N) / bs] % GL_Q, delta % GL_Q));
+    }
+    return LUX_OK;
+}
+uint64_t lux_delta(uint32_t plaintext_space) { return GL_Q >> ilog2u(plaintext_space); }
+
+// ---- pieces
+static int ntt_host(lux_engine *e, const u64 *in, size_t n_polys, u64 *out, bool inverse) {
+    if (!e) return LUX_ERR_INVALID;
+    if (!in || !out) LUX_FAIL(e, LUX_ERR_INVALID, "null pointer");
+    if (n_polys == 0) return LUX_OK;
+    CUDA_TRY(e, cudaSetDevice(e->device));
+    const size_t bytes = sizeof(u64) * n_polys * e->p.N;
+    int rc = ensure_scratch(e, 1, bytes);
+    if (rc) return rc;
+    u64 *d = (u64 *)e->scratch[1];
+    CUDA_TRY(e, cudaMemcpyAsync(d, in, bytes, cudaMemcpyHostToDevice, e->stream));
+    if ((rc = launch_ntt(e, d, d, n_polys, inverse, inverse ? e->ninv : 1, e->stream))) return rc;
+    CUDA_TRY(e, cudaMemcpyAsync(out, d, bytes, cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    return LUX_OK;
+}
+int lux_ntt_forward(lux_engine *e, const uint64_t *in, size_t n_polys, uint64_t *out) { return ntt_host(e, in, n_polys, out, false); }
+int lux_ntt_backward(lux_engine *e, const uint64_t *in, size_t n_polys, uint64_t *out) { return ntt_host(e, in, n_polys, out, true); }
+
+int lux_ntt_any(lux_engine *e, uint32_t N, int inverse, const uint64_t *in, size_t n_polys, uint64_t *out) {
+    if (!e) return LUX_ERR_INVALID;
+    if (!in || !out) LUX_FAIL(e, LUX_ERR_INVALID, "null pointer");
+    if (N < 8 || N > 2048 || (N & (N - 1))) LUX_FAIL(e, LUX_ERR_INVALID, "lux_ntt_any: N must be a power of two in [8,2048]");
+    if (n_polys == 0) return LUX_OK;
+    CUDA_TRY(e, cudaSetDevice(e->device));
+    u64 ninv;
+    {
+        std::vector<u64> r, ri;
+        lux_host_ntt_tables(N, r, ri, ninv);
+        if (!e->any_tables.count(N)) {
+            u64 *d = nullptr;
+            CUDA_TRY(e, cudaMalloc(&d, sizeof(u64) * 2 * N));
+            CUDA_TRY(e, cudaMemcpy(d, r.data(), sizeof(u64) * N, cudaMemcpyHostToDevice));
+            CUDA_TRY(e, cudaMemcpy(d + N, ri.data(), sizeof(u64) * N, cudaMemcpyHostToDevice));
+            e->any_tables[N] = d;
+        }
+    }
+    const u64 *tw = e->any_tables[N] + (inverse ? N : 0);
+    const size_t bytes = sizeof(u64) * n_polys * N;
+    int rc = ensure_scratch(e, 1, bytes);
+    if (rc) return rc;
+    u64 *d = (u64 *)e->scratch[1];
+    CUDA_TRY(e, cudaMemcpyAsync(d, in, bytes, cudaMemcpyHostToDevice, e->stream));
+    ntt_any_kernel<<<(unsigned)n_polys, N / 2, sizeof(u64) * N, e->stream>>>(d, d, tw, inverse ? ninv : 1, N, inverse ? 1 : 0);
+    e->launches++;
+    CUDA_TRY(e, cudaGetLastError());
+    CUDA_TRY(e, cudaMemcpyAsync(out, d, bytes, cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    return LUX_OK;
+}
+
+int lux_decompose(lux_engine *e, const uint64_t *in, size_t count, uint32_t logB, uint64_t *out) {
+    if (!e) return LUX_ERR_INVALID;
+    if (!in || !out) LUX_FAIL(e, LUX_ERR_INVALID, "null pointer");
+    if (logB < 1 || logB > 62) LUX_FAIL(e, LUX_ERR_INVALID, "logB out of range");
+    if (count == 0) return LUX_OK;
+    const u32 L = (64 + logB - 1) / logB;
+    CUDA_TRY(e, cudaSetDevice(e->device));
+    int rc;
+    if ((rc = ensure_scratch(e, 1, sizeof(u64) * count))) return rc;
+    if ((rc = ensure_scratch(e, 2, sizeof(u64) * count * L))) return rc;
+    CUDA_TRY(e, cudaMemcpyAsync(e->scratch[1], in, sizeof(u64) * count, cudaMemcpyHostToDevice, e->stream));
+    decompose_kernel<<<e->sm_count * 4, 256, 0, e->stream>>>((const u64 *)e->scratch[1], (u64 *)e->scratch[2], count, logB, L);
+    e->launches++;
+    CUDA_TRY(e, cudaGetLastError());
+    CUDA_TRY(e, cudaMemcpyAsync(out, e->scratch[2], sizeof(u64) * count * L, cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    return LUX_OK;
+}
+
+int lux_mod_switch(lux_engine *e, const uint64_t *in, size_t count, uint32_t *out) {
+    if (!e) return LUX_ERR_INVALID;
+    if (!in || !out) LUX_FAIL(e, LUX_ERR_INVALID, "null pointer");
+    if (count == 0) return LUX_OK;
+    CUDA_TRY(e, cudaSetDevice(e->device));
+    int rc;
+    if ((rc = ensure_scratch(e, 1, sizeof(u64) * count))) return rc;
+    if ((rc = ensure_scratch(e, 2, sizeof(u32) * count))) return rc;
+    CUDA_TRY(e, cudaMemcpyAsync(e->scratch[1], in, sizeof(u64) * count, cudaMemcpyHostToDevice, e->stream));
+    mod_switch_kernel<<<e->sm_count * 4, 256, 0, e->stream>>>((const u64 *)e->scratch[1], (u32 *)e->scratch[2], count, e->logN);
+    e->launches++;
+    CUDA_TRY(e, cudaGetLastError());
+    CUDA_TRY(e, cudaMemcpyAsync(out, e->scratch[2], sizeof(u32) * count, cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    return LUX_OK;
+}
+
+int lux_lwe_keyswitch(lux_engine *e, const uint64_t *in, size_t B, uint64_t *out) {
+    if (!e) return LUX_ERR_INVALID;
+    if (!in || !out) LUX_FAIL(e, LUX_ERR_INVALID, "null pointer");
+    if (e->p.order != LUX_ORDER_LWEKS_PBS) LUX_FAIL(e, LUX_ERR_INVALID, "engine has no LWE key switch (order 0)");
+    if (!e->has_lksk) LUX_FAIL(e, LUX_ERR_NO_KEY, "LWE key switch key not loaded");
+    if (B == 0) return LUX_OK;
+    CUDA_TRY(e, cudaSetDevice(e->device));
+    const size_t wi = (size_t)e->p.k * e->p.N + 1, wo = (size_t)e->p.n + 1;
+    int rc;
+    if ((rc = ensure_scratch(e, 1, sizeof(u64) * B * wi))) return rc;
+    if ((rc = ensure_scratch(e, 2, sizeof(u64) * B * wo))) return rc;
+    CUDA_TRY(e, cudaMemcpyAsync(e->scratch[1], in, sizeof(u64) * B * wi, cudaMemcpyHostToDevice, e->stream));
+    if ((rc = launch_ks(e, (const u64 *)e->scratch[1], (u64 *)e->scratch[2], B, e->stream))) return rc;
+    CUDA_TRY(e, cudaMemcpyAsync(out, e->scratch[2], sizeof(u64) * B * wo, cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    return LUX_OK;
+}
+
+int lux_blind_rotate(lux_engine *e, const uint64_t *lwe, const uint64_t *testvs, uint32_t n_luts, const uint32_t *lut_idx,
+                     size_t B, uint32_t steps, uint64_t *acc_out) {
+    if (!e) return LUX_ERR_INVALID;
+    if (!lwe || !testvs || !acc_out || n_luts == 0) LUX_FAIL(e, LUX_ERR_INVALID, "null/empty argument");
+    if (!e->has_bsk) LUX_FAIL(e, LUX_ERR_NO_KEY, "bootstrap key not loaded");
+    if (steps > e->p.n) LUX_FAIL(e, LUX_ERR_INVALID, "steps %u > n %u", steps, e->p.n);
+    if (B == 0) return LUX_OK;
+    if (lut_idx)
+        for (size_t b = 0; b < B; b++)
+            if (lut_idx[b] >= n_luts) LUX_FAIL(e, LUX_ERR_INVALID, "lut_idx out of range");
+    CUDA_TRY(e, cudaSetDevice(e->device));
+    const size_t wi = (size_t)e->p.n + 1, N = e->p.N, wo = 2 * N;
+    int rc;
+    if ((rc = ensure_scratch(e, 1, sizeof(u64) * B * wi))) return rc;
+    if ((rc = ensure_scratch(e, 2, sizeof(u64) * B * wo))) return rc;
+    if ((rc = ensure_scratch(e, 3, sizeof(u64) * n_luts * N + sizeof(u32) * B))) return rc;
+    u64 *d_tv = (u64 *)e->scratch[3];
+    u32 *d_idx = lut_idx ? (u32 *)(d_tv + (size_t)n_luts * N) : nullptr;
+    CUDA_TRY(e, cudaMemcpyAsync(e->scratch[1], lwe, sizeof(u64) * B * wi, cudaMemcpyHostToDevice, e->stream));
+    CUDA_TRY(e, cudaMemcpyAsync(d_tv, testvs, sizeof(u64) * n_luts * N, cudaMemcpyHostToDevice, e->stream));
+    if (lut_idx) CUDA_TRY(e, cudaMemcpyAsync(d_idx, lut_idx, sizeof(u32) * B, cudaMemcpyHostToDevice, e->stream));
+    BRArgs a = make_br_args(e, (const u64 *)e->scratch[1], d_tv, d_idx, B, (u64 *)e->scratch[2]);
+    a.steps = steps;
+    a.out_mode = 2;
+    if ((rc = launch_br(e, a, e->stream))) return rc;
+    CUDA_TRY(e, cudaMemcpyAsync(acc_out, e->scratch[2], sizeof(u64) * B * wo, cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    return LUX_OK;
+}
+
+int lux_external_product(lux_engine *e, const uint64_t *ggsw, int domain, const uint64_t *glwe_in, size_t count, uint64_t *glwe_out) {
+    if (!e) return LUX_ERR_INVALID;
+    if (!ggsw || !glwe_in || !glwe_out) LUX_FAIL(e, LUX_ERR_INVALID, "null pointer");
+    if (count == 0) return LUX_OK;
+    CUDA_TRY(e, cudaSetDevice(e->device));
+    const size_t gw = ggsw_words(e->p), N = e->p.N;
+    int rc;
+    if ((rc = ensure_scratch(e, 4, sizeof(u64) * count * gw))) return rc;
+    if ((rc = ensure_scratch(e, 1, sizeof(u64) * count * 2 * N))) return rc;
+    if ((rc = ensure_scratch(e, 2, sizeof(u64) * count * 2 * N))) return rc;
+    if ((rc = load_ggsw_array(e, (u64 *)e->scratch[4], ggsw, count * gw, count * gw, domain, "lux_external_product"))) return rc;
+    CUDA_TRY(e, cudaMemcpyAsync(e->scratch[1], glwe_in, sizeof(u64) * count * 2 * N, cudaMemcpyHostToDevice, e->stream));
+    BRArgs a = make_br_args(e, nullptr, nullptr, nullptr, count, (u64 *)e->scratch[2]);
+    a.bsk = (const u64 *)e->scratch[4];
+    switch (e->logN) {
+        case 9: rc = lux_launch_xp_9(e, a, (const u64 *)e->scratch[1], gw, e->stream); break;
+        case 10: rc = lux_launch_xp_10(e, a, (const u64 *)e->scratch[1], gw, e->stream); break;
+        case 11: rc = lux_launch_xp_11(e, a, (const u64 *)e->scratch[1], gw, e->stream); break;
+        case 12: rc = lux_launch_xp_12(e, a, (const u64 *)e->scratch[1], gw, e->stream); break;
+        default: LUX_FAIL(e, LUX_ERR_INVALID, "unsupported N");
+    }
+    if (rc) return rc;
+    CUDA_TRY(e, cudaMemcpyAsync(glwe_out, e->scratch[2], sizeof(u64) * count * 2 * N, cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    return LUX_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,67 @@
+// engine.h — internal state behind the opaque lux_engine handle (include/lux_tfhe.h).
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdio>
+
+#include <map>
+#include <vector>
+
+#include "../../include/lux_tfhe.h"
+#include "tfhe_kernels.cuh"
+
+#define LUX_SCRATCH_SLOTS 8
+
+struct lux_engine {
+    lux_params p{};
+    int device = 0;
+    int sm_count = 148;
+    u32 logN = 0, L = 0, L_ks = 0;
+    u64 ninv = 0;
+    cudaStream_t stream = nullptr;
+    // NTT tables (reference convention), device
+    u64 *d_tw_fwd = nullptr, *d_tw_inv = nullptr;
+    // evaluation keys, one device blob: [header 8][bsk][glwe ksk][lwe ksk][ksum]
+    u64 *d_blob = nullptr;
+    size_t blob_words = 0, bsk_words = 0, gksk_words = 0, lksk_words = 0, ksum_words = 0;
+    u64 *d_bsk = nullptr, *d_gksk = nullptr, *d_lksk = nullptr, *d_ksum = nullptr;
+    bool has_bsk = false, has_gksk = false, has_lksk = false;
+    // grow-only device staging for the host-pointer entry points
+    void *scratch[LUX_SCRATCH_SLOTS] = {};
+    size_t scratch_bytes[LUX_SCRATCH_SLOTS] = {};
+    std::map<u32, u64 *> any_tables;  // lux_ntt_any: N -> [ROOTS | INVROOTS]
+    // accounting
+    uint64_t launches = 0;
+    bool timing = false;
+    cudaEvent_t ev[4] = {};
+    float last_ms[2] = {0.f, 0.f};
+    int force_teams = 0;  // debug/tuning override of ciphertexts per CTA
+    char err[512] = "";
+};
+
+void lux_host_ntt_tables(u32 N, std::vector<u64> &roots, std::vector<u64> &invroots, u64 &ninv);
+extern "C" int lux_debug_force_teams(lux_engine *e, int teams);
+
+#define LUX_FAIL(e, code, ...)                                  \
+    do {                                                        \
+        snprintf((e)->err, sizeof((e)->err), __VA_ARGS__);      \
+        return (code);                                          \
+    } while (0)
+
+#define CUDA_TRY(e, call)                                                                              \
+    do {                                                                                               \
+        cudaError_t _st = (call);                                                                      \
+        if (_st != cudaSuccess)                                                                        \
+            LUX_FAIL(e, LUX_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(_st), __FILE__, __LINE__); \
+    } while (0)
+
+
+// per-ring-size launchers, defined in br_n*.cu
+#define LUX_DECL_LAUNCHERS(LN)                                                                      \
+    int lux_launch_br_##LN(lux_engine *e, const BRArgs &a, cudaStream_t s);                         \
+    int lux_launch_ntt_##LN(lux_engine *e, const NttArgs &a, cudaStream_t s);                       \
+    int lux_launch_xp_##LN(lux_engine *e, const BRArgs &a, const u64 *d_glwe, size_t stride, cudaStream_t s);
+LUX_DECL_LAUNCHERS(9)
+LUX_DECL_LAUNCHERS(10)
+LUX_DECL_LAUNCHERS(11)
+LUX_DECL_LAUNCHERS(12)

@@ -1,0 +1,317 @@
+"""ctypes binding of the C ABI in include/lux_tfhe.h (libluxtfhe_b200.so).
+
+Host-side only: marshals numpy / torch buffers into the ABI.  All arithmetic happens in the CUDA
+library; nothing here computes on ciphertexts and nothing falls back to the CPU.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from pathlib import Path
+
+import numpy as np
+
+Q = 0xFFFFFFFF00000001
+ORDER_PBS_GLWEKS = 0
+ORDER_LWEKS_PBS = 1
+DOMAIN_STANDARD = 0
+DOMAIN_NTT = 1
+
+_HERE = Path(__file__).resolve().parent
+
+
+def lib_path() -> Path:
+    return _HERE / "libluxtfhe_b200.so"
+
+
+class LuxError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"lux error {code}: {msg}")
+        self.code = code
+
+
+class _CParams(C.Structure):
+    _fields_ = [(f, C.c_uint32) for f in ("n", "N", "k", "ell", "logB", "ell_ks", "logB_ks", "order")]
+
+
+@dataclass(frozen=True)
+class Params:
+    """lux_params.  (ell, logB) follow the reference's limb convention: L = ceil(64/logB) limbs of
+    logB bits counted from bit 0, the external product keeps the top `ell` (glev_ct.rs:97-99)."""
+    n: int
+    N: int
+    k: int = 1
+    ell: int = 1
+    logB: int = 8
+    ell_ks: int = 0
+    logB_ks: int = 0
+    order: int = ORDER_PBS_GLWEKS
+
+    def c(self) -> _CParams:
+        return _CParams(self.n, self.N, self.k, self.ell, self.logB, self.ell_ks, self.logB_ks, self.order)
+
+    @property
+    def ggsw_len(self) -> int:
+        return (self.k + 1) * self.ell * (self.k + 1) * self.N
+
+    @property
+    def ct_len(self) -> int:
+        return self.k * self.N + 1 if self.order == ORDER_LWEKS_PBS else self.n + 1
+
+    @property
+    def lwe_ksk_len(self) -> int:
+        return self.k * self.N * self.ell_ks * (self.n + 1)
+
+
+# S1: the reference's in-tree boolean set, research/verifiable-fhe/src/main.rs:23-30
+S1_BOOLEAN = Params(n=728, N=1024, k=1, ell=4, logB=5, ell_ks=4, logB_ks=5, order=ORDER_PBS_GLWEKS)
+# S2: shape of PARAM_MESSAGE_2_CARRY_2_KS_PBS_TUNIFORM_2M128 (sdk/relayer/src/tfhe.ts:15) over the
+# reference's Goldilocks modulus: n=918, N=2048, one 23-bit PBS digit at 2^41 (logB=41 in the limb
+# convention => L=2, top limb = bits 41..63), key switch 4 levels of 4 bits (limbs 12..15 of 16).
+S2_SHORTINT = Params(n=918, N=2048, k=1, ell=1, logB=41, ell_ks=4, logB_ks=4, order=ORDER_LWEKS_PBS)
+# small sets for fast parity tests
+TEST_SMALL_O0 = Params(n=24, N=512, k=1, ell=4, logB=8, ell_ks=4, logB_ks=8, order=ORDER_PBS_GLWEKS)
+TEST_SMALL_O1 = Params(n=24, N=512, k=1, ell=2, logB=16, ell_ks=8, logB_ks=4, order=ORDER_LWEKS_PBS)
+
+_u64p = np.ctypeslib.ndpointer(dtype=np.uint64, flags="C_CONTIGUOUS")
+_u32p = np.ctypeslib.ndpointer(dtype=np.uint32, flags="C_CONTIGUOUS")
+_lib = None
+
+# every symbol include/lux_tfhe.h declares: name -> (restype, argtypes)
+_vp, _sz, _u32, _u64, _int = C.c_void_p, C.c_size_t, C.c_uint32, C.c_uint64, C.c_int
+ABI = {
+    "lux_version": (C.c_char_p, []),
+    "lux_engine_create": (_int, [C.POINTER(_CParams), _int, C.POINTER(_vp)]),
+    "lux_engine_destroy": (None, [_vp]),
+    "lux_last_error": (C.c_char_p, [_vp]),
+    "lux_engine_params": (_int, [_vp, C.POINTER(_CParams)]),
+    "lux_ct_words": (_sz, [_vp]),
+    "lux_launch_count": (_u64, [_vp]),
+    "lux_set_timing": (_int, [_vp, _int]),
+    "lux_last_timing": (_int, [_vp, C.POINTER(C.c_float * 2)]),
+    "lux_synchronize": (_int, [_vp]),
+    "lux_load_bsk": (_int, [_vp, _u64p, _sz, _int]),
+    "lux_load_glwe_ksk": (_int, [_vp, _u64p, _sz, _int]),
+    "lux_load_lwe_ksk": (_int, [_vp, _u64p, _sz]),
+    "lux_key_blob_bytes": (_sz, [_vp]),
+    "lux_export_keys_device": (_int, [_vp, _vp, _sz]),
+    "lux_import_keys_device": (_int, [_vp, _vp, _sz]),
+    "lux_pbs_batch": (_int, [_vp, _vp, _vp, _u32, _vp, _sz, _vp]),
+    "lux_pbs_batch_device": (_int, [_vp, _vp, _vp, _u32, _vp, _sz, _vp, _vp]),
+    "lux_make_testv": (_int, [_u32, _u32, _u64, _u64p, _u64p]),
+    "lux_delta": (_u64, [_u32]),
+    "lux_ntt_forward": (_int, [_vp, _u64p, _sz, _u64p]),
+    "lux_ntt_backward": (_int, [_vp, _u64p, _sz, _u64p]),
+    "lux_ntt_any": (_int, [_vp, _u32, _int, _u64p, _sz, _u64p]),
+    "lux_decompose": (_int, [_vp, _u64p, _sz, _u32, _u64p]),
+    "lux_mod_switch": (_int, [_vp, _u64p, _sz, _u32p]),
+    "lux_lwe_keyswitch": (_int, [_vp, _u64p, _sz, _u64p]),
+    "lux_blind_rotate": (_int, [_vp, _u64p, _u64p, _u32, _vp, _sz, _u32, _u64p]),
+    "lux_external_product": (_int, [_vp, _u64p, _int, _u64p, _sz, _u64p]),
+}
+
+
+def lib():
+    """Load the CUDA library; raises if it has not been built (no fallback)."""
+    global _lib
+    if _lib is None:
+        path = lib_path()
+        if not path.exists():
+            raise LuxError(-100, f"{path} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                                 f"or `make -C tfhe_b200/csrc` (there is no CPU fallback)")
+        L = C.CDLL(str(path))
+        for name, (res, args) in ABI.items():
+            fn = getattr(L, name)
+            fn.restype = res
+            fn.argtypes = args
+        if hasattr(L, "lux_debug_force_teams"):
+            L.lux_debug_force_teams.argtypes = [_vp, _int]
+        _lib = L
+    return _lib
+
+
+def _u64arr(a) -> np.ndarray:
+    return np.ascontiguousarray(a, dtype=np.uint64)
+
+
+def make_testv(N: int, p: int, delta_: int, lut) -> np.ndarray:
+    """get_testv (crypto/mod.rs:17-27) generalised to an arbitrary p-entry table."""
+    out = np.zeros(N, np.uint64)
+    rc = lib().lux_make_testv(N, p, delta_, _u64arr(lut), out)
+    if rc:
+        raise LuxError(rc, "lux_make_testv: bad arguments")
+    return out
+
+
+def delta(space: int) -> int:
+    return lib().lux_delta(space)
+
+
+def _ptr(x):
+    """host numpy array or torch tensor -> raw address"""
+    if x is None:
+        return None
+    if isinstance(x, np.ndarray):
+        return x.ctypes.data
+    return x.data_ptr()  # torch tensor (host pinned or device)
+
+
+class Engine:
+    """One engine per GPU (lux_engine)."""
+
+    def __init__(self, params: Params, device: int = 0):
+        self.p = params
+        self._h = _vp()
+        cp = params.c()
+        rc = lib().lux_engine_create(C.byref(cp), device, C.byref(self._h))
+        if rc:
+            raise LuxError(rc, lib().lux_last_error(None).decode())
+        self.device = device
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().lux_engine_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, rc: int):
+        if rc:
+            raise LuxError(rc, lib().lux_last_error(self._h).decode())
+
+    # ---- keys ------------------------------------------------------------------------------
+    def load_bsk(self, bsk, domain=DOMAIN_STANDARD):
+        a = _u64arr(bsk).reshape(-1)
+        self._ck(lib().lux_load_bsk(self._h, a, a.size, domain))
+
+    def load_glwe_ksk(self, ksk, domain=DOMAIN_STANDARD):
+        a = _u64arr(ksk).reshape(-1)
+        self._ck(lib().lux_load_glwe_ksk(self._h, a, a.size, domain))
+
+    def load_lwe_ksk(self, ksk):
+        a = _u64arr(ksk).reshape(-1)
+        self._ck(lib().lux_load_lwe_ksk(self._h, a, a.size))
+
+    def load_keyset(self, ks):
+        """ks: any object with .bsk and .glwe_ksk / .lwe_ksk (standard domain)"""
+        self.load_bsk(ks.bsk)
+        if getattr(ks, "glwe_ksk", None) is not None:
+            self.load_glwe_ksk(ks.glwe_ksk)
+        if getattr(ks, "lwe_ksk", None) is not None:
+            self.load_lwe_ksk(ks.lwe_ksk)
+
+    @property
+    def key_blob_bytes(self) -> int:
+        return lib().lux_key_blob_bytes(self._h)
+
+    def export_keys_device(self, dev_tensor):
+        self._ck(lib().lux_export_keys_device(self._h, dev_tensor.data_ptr(), dev_tensor.numel() * dev_tensor.element_size()))
+
+    def import_keys_device(self, dev_tensor):
+        self._ck(lib().lux_import_keys_device(self._h, dev_tensor.data_ptr(), dev_tensor.numel() * dev_tensor.element_size()))
+
+    # ---- PBS ----------------------------------------------------------------------------------
+    def pbs_batch(self, lwe_in, testvs, lut_idx=None, out=None):
+        """Host buffers (numpy, or pinned torch tensors viewed as int64/uint64)."""
+        if isinstance(lwe_in, np.ndarray):
+            lwe_in = _u64arr(lwe_in).reshape(-1, self.p.ct_len)
+            B = lwe_in.shape[0]
+            if out is None:
+                out = np.empty_like(lwe_in)
+        else:
+            B = lwe_in.numel() // self.p.ct_len
+            assert out is not None
+        if isinstance(testvs, np.ndarray):
+            testvs = _u64arr(testvs).reshape(-1, self.p.N)
+            n_luts = testvs.shape[0]
+        else:
+            n_luts = testvs.numel() // self.p.N
+        if lut_idx is not None and isinstance(lut_idx, (list, tuple, np.ndarray)):
+            lut_idx = np.ascontiguousarray(lut_idx, dtype=np.uint32)
+        self._ck(lib().lux_pbs_batch(self._h, _ptr(lwe_in), _ptr(testvs), n_luts, _ptr(lut_idx), B, _ptr(out)))
+        return out
+
+    def pbs_batch_device(self, d_in, d_testvs, d_lut_idx, B: int, d_out, n_luts: int | None = None, stream=None):
+        """torch CUDA tensors (int64 storage of the u64 words); asynchronous on `stream`/engine stream."""
+        if n_luts is None:
+            n_luts = d_testvs.numel() // self.p.N
+        self._ck(lib().lux_pbs_batch_device(self._h, d_in.data_ptr(), d_testvs.data_ptr(), n_luts,
+                                            None if d_lut_idx is None else d_lut_idx.data_ptr(), B, d_out.data_ptr(),
+                                            stream))
+
+    def synchronize(self):
+        self._ck(lib().lux_synchronize(self._h))
+
+    def set_timing(self, on: bool):
+        self._ck(lib().lux_set_timing(self._h, int(on)))
+
+    def last_timing(self):
+        buf = (C.c_float * 2)()
+        self._ck(lib().lux_last_timing(self._h, C.byref(buf)))
+        return float(buf[0]), float(buf[1])
+
+    @property
+    def launch_count(self) -> int:
+        return lib().lux_launch_count(self._h)
+
+    def force_teams(self, t: int):
+        lib().lux_debug_force_teams(self._h, t)
+
+    # ---- pieces -------------------------------------------------------------------------------
+    def ntt_forward(self, polys):
+        a = _u64arr(polys).reshape(-1, self.p.N)
+        out = np.empty_like(a)
+        self._ck(lib().lux_ntt_forward(self._h, a.reshape(-1), a.shape[0], out.reshape(-1)))
+        return out
+
+    def ntt_backward(self, polys):
+        a = _u64arr(polys).reshape(-1, self.p.N)
+        out = np.empty_like(a)
+        self._ck(lib().lux_ntt_backward(self._h, a.reshape(-1), a.shape[0], out.reshape(-1)))
+        return out
+
+    def ntt_any(self, polys, N: int, inverse=False):
+        a = _u64arr(polys).reshape(-1, N)
+        out = np.empty_like(a)
+        self._ck(lib().lux_ntt_any(self._h, N, int(inverse), a.reshape(-1), a.shape[0], out.reshape(-1)))
+        return out
+
+    def decompose(self, values, logB: int):
+        a = _u64arr(values).reshape(-1)
+        L = (64 + logB - 1) // logB
+        out = np.empty((a.size, L), np.uint64)
+        self._ck(lib().lux_decompose(self._h, a, a.size, logB, out.reshape(-1)))
+        return out
+
+    def mod_switch(self, values):
+        a = _u64arr(values).reshape(-1)
+        out = np.empty(a.size, np.uint32)
+        self._ck(lib().lux_mod_switch(self._h, a, a.size, out))
+        return out
+
+    def lwe_keyswitch(self, cts):
+        a = _u64arr(cts).reshape(-1, self.p.k * self.p.N + 1)
+        out = np.empty((a.shape[0], self.p.n + 1), np.uint64)
+        self._ck(lib().lux_lwe_keyswitch(self._h, a.reshape(-1), a.shape[0], out.reshape(-1)))
+        return out
+
+    def blind_rotate(self, lwe_small, testvs, lut_idx=None, steps: int | None = None):
+        a = _u64arr(lwe_small).reshape(-1, self.p.n + 1)
+        tv = _u64arr(testvs).reshape(-1, self.p.N)
+        idx = None if lut_idx is None else np.ascontiguousarray(lut_idx, dtype=np.uint32)
+        out = np.empty((a.shape[0], 2 * self.p.N), np.uint64)
+        self._ck(lib().lux_blind_rotate(self._h, a.reshape(-1), tv.reshape(-1), tv.shape[0], _ptr(idx), a.shape[0],
+                                        self.p.n if steps is None else steps, out.reshape(-1)))
+        return out
+
+    def external_product(self, ggsw, glwe, domain=DOMAIN_STANDARD):
+        g = _u64arr(ggsw).reshape(-1, self.p.ggsw_len)
+        x = _u64arr(glwe).reshape(-1, 2 * self.p.N)
+        assert g.shape[0] == x.shape[0]
+        out = np.empty_like(x)
+        self._ck(lib().lux_external_product(self._h, g.reshape(-1), domain, x.reshape(-1), x.shape[0], out.reshape(-1)))
+        return out
