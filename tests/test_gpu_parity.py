@@ -51,6 +51,26 @@ def edge_values():
     return [0, 1, 2, Q - 1, Q - 2, 2**63, 2**63 - 1, 2**63 + 1, 2**32 - 1, 2**32, Q // 2, Q // 2 + 1, 2**52, 2**53 - 1]
 
 
+
+# ------------------------------------------------------------------------------- field arithmetic
+def test_field_ops_vs_python_ints(rig_small0):
+    """gl64.cuh's PTX carry chains against Python big-int arithmetic mod q (edge words + random)."""
+    e = rig_small0.eng
+    edge = edge_values() + [2**64 - 1, 2**64 - 2, Q, Q + 1, 2**64 - 2**32, 2**64 - 2**32 - 1, 2**33, 2**31]
+    rs = np.random.RandomState(7)
+    rnd = [int(x) for x in rs.randint(0, 2**63, size=4000, dtype=np.int64).astype(np.uint64) * np.uint64(2) + rs.randint(0, 2, size=4000).astype(np.uint64)]
+    a = [x for x in edge for _ in edge] + rnd
+    b = [y % Q for _ in edge for y in edge] + [x % Q for x in rnd[::-1]]
+    a, b = a[: len(b)], b[: len(a)]
+    got = e.field_probe(np.array(a, np.uint64), np.array(b, np.uint64))
+    n = len(a)
+    for i in range(n):
+        x, y, v = a[i], b[i], a[(i + 1) % n]
+        t = v * y % Q
+        want = [(x + y) % Q, (x - y) % Q, x * y % Q, (x + t) % Q, (x - t) % Q, (x + v) % Q, (x - v) * y % Q]
+        for r in range(7):
+            assert int(got[r, i]) == want[r], (r, hex(x), hex(y), hex(v), hex(int(got[r, i])), hex(want[r]))
+
 # ------------------------------------------------------------------------------------------- NTT
 @pytest.mark.parametrize("N", [8, 16, 32, 64, 128, 256, 512, 1024, 2048])
 def test_ntt_any_golden(golden, rig_small0, N):

@@ -36,6 +36,27 @@ __global__ void mod_switch_kernel(const u64 *in, u32 *out, size_t count, u32 log
         out[i] = gl_mod_switch(in[i], logN);
 }
 
+
+// field-arithmetic probe: a[] arbitrary u64 ("lazy"), b[] canonical; out[7][count] canonical residues of
+// a+b, a-b, a*b, and both outputs of the two butterflies (u=a, v=b', w=b) where b' = a ^ b rotated.
+__global__ void field_probe_kernel(const u64 *a, const u64 *b, u64 *out, size_t count) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < count; i += (size_t)gridDim.x * blockDim.x) {
+        const u64 x = a[i], y = b[i];
+        out[0 * count + i] = gl_canon(gl_add(x, y));
+        out[1 * count + i] = gl_canon(gl_sub(x, y));
+        out[2 * count + i] = gl_mul(x, y);
+        u64 u = x, v = a[(i + 1) % count];
+        gl_ct_butterfly(u, v, y);
+        out[3 * count + i] = gl_canon(u);
+        out[4 * count + i] = gl_canon(v);
+        u = x;
+        v = a[(i + 1) % count];
+        gl_gs_butterfly(u, v, y);
+        out[5 * count + i] = gl_canon(u);
+        out[6 * count + i] = gl_canon(v);
+    }
+}
+
 // any power-of-two N in [8, 2048]: one CTA per polynomial, one thread per butterfly, textbook
 // stage loop in shared memory (crypto/poly.rs:9-64).  Parity utility for the small golden vectors.
 __global__ void ntt_any_kernel(const u64 *in, u64 *out, const u64 *tw, u64 scale, u32 N, u32 inverse) {
@@ -629,6 +650,24 @@ int lux_external_product(lux_engine *e, const uint64_t *ggsw, int domain, const 
     }
     if (rc) return rc;
     CUDA_TRY(e, cudaMemcpyAsync(glwe_out, e->scratch[2], sizeof(u64) * count * 2 * N, cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    return LUX_OK;
+}
+
+int lux_debug_field_probe(lux_engine *e, const uint64_t *a, const uint64_t *b, size_t count, uint64_t *out) {
+    if (!e) return LUX_ERR_INVALID;
+    if (!a || !b || !out || count == 0) LUX_FAIL(e, LUX_ERR_INVALID, "null/empty argument");
+    CUDA_TRY(e, cudaSetDevice(e->device));
+    int rc;
+    if ((rc = ensure_scratch(e, 1, sizeof(u64) * count * 2))) return rc;
+    if ((rc = ensure_scratch(e, 2, sizeof(u64) * count * 7))) return rc;
+    u64 *d_a = (u64 *)e->scratch[1], *d_b = d_a + count;
+    CUDA_TRY(e, cudaMemcpyAsync(d_a, a, sizeof(u64) * count, cudaMemcpyHostToDevice, e->stream));
+    CUDA_TRY(e, cudaMemcpyAsync(d_b, b, sizeof(u64) * count, cudaMemcpyHostToDevice, e->stream));
+    field_probe_kernel<<<e->sm_count, 256, 0, e->stream>>>(d_a, d_b, (u64 *)e->scratch[2], count);
+    e->launches++;
+    CUDA_TRY(e, cudaGetLastError());
+    CUDA_TRY(e, cudaMemcpyAsync(out, e->scratch[2], sizeof(u64) * count * 7, cudaMemcpyDeviceToHost, e->stream));
     CUDA_TRY(e, cudaStreamSynchronize(e->stream));
     return LUX_OK;
 }

@@ -41,6 +41,7 @@ struct lux_engine {
 
 void lux_host_ntt_tables(u32 N, std::vector<u64> &roots, std::vector<u64> &invroots, u64 &ninv);
 extern "C" int lux_debug_force_teams(lux_engine *e, int teams);
+extern "C" int lux_debug_field_probe(lux_engine *e, const uint64_t *a, const uint64_t *b, size_t count, uint64_t *out);
 
 #define LUX_FAIL(e, code, ...)                                  \
     do {                                                        \

@@ -65,19 +65,23 @@ GL_HD u64 gl_add(u64 a, u64 b) {
 }
 
 // a lazy, b canonical -> lazy.  A borrow means the true value is d - 2^64 == d - eps.
+// `subc.u32 m, 0, 0` after the chain yields m = 0 - borrow = 0 or 0xFFFFFFFF = eps, so the
+// correction is a plain 64-bit subtract of the zero-extended mask (never borrows again: a borrow
+// implies d >= 2^64 - q + 1 > eps).
 GL_HD u64 gl_sub(u64 a, u64 b) {
 #if GL_PTX
-    u32 lo, hi, bw;
-    asm("sub.cc.u32 %0, %3, %5;\n\t"
-        "subc.cc.u32 %1, %4, %6;\n\t"
-        "addc.u32 %2, 0, 0;"  // CC.CF after subc.cc is the borrow-out: bw in {0,1}
-        : "=r"(lo), "=r"(hi), "=r"(bw)
+    u32 lo, hi;
+    asm("{\n\t"
+        ".reg .u32 m;\n\t"
+        "sub.cc.u32 %0, %2, %4;\n\t"
+        "subc.cc.u32 %1, %3, %5;\n\t"
+        "subc.u32 m, 0, 0;\n\t"
+        "sub.cc.u32 %0, %0, m;\n\t"
+        "subc.u32 %1, %1, 0;\n\t"
+        "}"
+        : "=&r"(lo), "=&r"(hi)
         : "r"((u32)a), "r"((u32)(a >> 32)), "r"((u32)b), "r"((u32)(b >> 32)));
-    // d - eps = d - 2^32 + 1 : hi -= bw, then + bw (IMAD.WIDE carries into hi)
-    hi -= bw;
-    u64 d = ((u64)hi << 32) | lo;
-    asm("mad.wide.u32 %0, %1, 1, %0;" : "+l"(d) : "r"(bw));
-    return d;
+    return ((u64)hi << 32) | lo;
 #else
     u64 d = a - b;
     return d - ((a < b) ? GL_EPS : 0);
@@ -94,15 +98,18 @@ GL_HD u64 gl_neg(u64 a) { return a ? GL_Q - a : 0; }
 GL_HD u64 gl_reduce128(u64 lo, u64 hi) {
     u64 hh = hi >> 32, hl = hi & GL_EPS;
 #if GL_PTX
-    u32 l0, l1, bw;
-    asm("sub.cc.u32 %0, %3, %5;\n\t"
-        "subc.cc.u32 %1, %4, 0;\n\t"
-        "addc.u32 %2, 0, 0;"
-        : "=r"(l0), "=r"(l1), "=r"(bw)
+    u32 l0, l1;
+    asm("{\n\t"
+        ".reg .u32 m;\n\t"
+        "sub.cc.u32 %0, %2, %4;\n\t"
+        "subc.cc.u32 %1, %3, 0;\n\t"
+        "subc.u32 m, 0, 0;\n\t"
+        "sub.cc.u32 %0, %0, m;\n\t"
+        "subc.u32 %1, %1, 0;\n\t"
+        "}"
+        : "=&r"(l0), "=&r"(l1)
         : "r"((u32)lo), "r"((u32)(lo >> 32)), "r"((u32)hh));
-    l1 -= bw;
     u64 t0 = ((u64)l1 << 32) | l0;
-    asm("mad.wide.u32 %0, %1, 1, %0;" : "+l"(t0) : "r"(bw));
     u64 t1;
     asm("mul.wide.u32 %0, %1, 0xFFFFFFFF;" : "=l"(t1) : "r"((u32)hl));
     return gl_add(t0, t1);  // t1 <= (2^32-1)^2 < q

@@ -126,6 +126,9 @@ def lib():
             fn.argtypes = args
         if hasattr(L, "lux_debug_force_teams"):
             L.lux_debug_force_teams.argtypes = [_vp, _int]
+        if hasattr(L, "lux_debug_field_probe"):
+            L.lux_debug_field_probe.argtypes = [_vp, _u64p, _u64p, _sz, _u64p]
+            L.lux_debug_field_probe.restype = _int
         _lib = L
     return _lib
 
@@ -257,6 +260,13 @@ class Engine:
     @property
     def launch_count(self) -> int:
         return lib().lux_launch_count(self._h)
+
+    def field_probe(self, a, b):
+        """device field arithmetic on raw words: rows = a+b, a-b, a*b, CT butterfly (2), GS butterfly (2)"""
+        a, b = _u64arr(a).reshape(-1), _u64arr(b).reshape(-1)
+        out = np.empty((7, a.size), np.uint64)
+        self._ck(lib().lux_debug_field_probe(self._h, a, b, a.size, out.reshape(-1)))
+        return out
 
     def force_teams(self, t: int):
         lib().lux_debug_force_teams(self._h, t)
