@@ -1,0 +1,370 @@
+#!/usr/bin/env python
+"""bench.py — PBS/s of the batched programmable bootstrap (BASELINE.json metric) on N B200s.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--batch B] [--impl ours|reference]
+
+A "step" is one pass of the hot path (LWE key switch -> blind rotate -> sample extract) over one
+batch of B ciphertexts per GPU.  Workload = BASELINE configs[1]: 4-bit shortint PBS with lookup
+tables at N=2048 (parameter shape S2, tfhe_b200.S2_SHORTINT), synthetic random ciphertexts.
+
+  value        device-resident throughput: inputs already in HBM, CUDA events on the launching stream
+  e2e          the same through the host-pointer C-ABI call lux_pbs_batch (pinned host buffers,
+               H2D + kernels + D2H inside the timed region)
+  roofline     dominant kernel (blind_rotate_kernel) against the HBM roofline (contract) — the
+               binding resource is the integer pipe, reported beside it as roofline_int
+  cpu_baseline the CPU oracle (C restatement of the reference's in-tree algorithm, OpenMP over
+               ciphertexts) on a bounded sample of the same workload, on this box's host cores
+
+Nothing here reads /root/reference.  oracle/ is used only for key/ciphertext fixtures, the parity
+spot check outside the timed region, and the cpu_baseline / --impl reference legs.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+METRIC = "pbs_per_s_batched"
+UNIT = "PBS/s"
+WORKLOAD = "C2: 4-bit shortint PBS with LUT, S2 shape (n=918, N=2048, k=1, ell=1, KS 4x4 bits), Goldilocks exact NTT"
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+# ------------------------------------------------------------------------------------ fixtures
+def make_fixture(params, seed=3):
+    """oracle-side keys (test infrastructure: keygen/encryption stay on the reference path)"""
+    import oracle as O
+
+    ctx = O.Ctx(O.Params(n=params.n, N=params.N, k=params.k, ell=params.ell, logB=params.logB,
+                         ell_ks=params.ell_ks, logB_ks=params.logB_ks, order=params.order))
+    ks = O.keygen(ctx, seed, 2.0 ** -47.8, 2.0 ** -19.8)
+    O.install_keys(ctx, ks)
+    return O, ctx, ks
+
+
+def make_inputs(O, ks, params, B, seed, p=16):
+    """B ciphertexts: the first `nreal` are real encryptions of 4-bit messages (checked after the run),
+    the rest uniform random words (throughput is data independent)."""
+    rng = O.Rng(seed)
+    delta = O.delta(2 * p)
+    luts = [list(range(16)), [(x * x) % 16 for x in range(16)], [x >> 2 for x in range(16)], [x & 3 for x in range(16)]]
+    tvs = np.stack([O.testv_lut(params.N, p, delta, lut) for lut in luts])
+    nreal = min(B, 32)
+    msgs = [int(rng.u64() % p) for _ in range(nreal)]
+    rs = np.random.RandomState(seed)
+    cts = rs.randint(0, 2 ** 63, size=(B, params.ct_len), dtype=np.int64).astype(np.uint64)
+    cts %= np.uint64(O.Q)
+    for i, m in enumerate(msgs):
+        cts[i] = O.lwe_encrypt(rng, ks.s_in, (m * delta) % O.Q, 2.0 ** -19.8)
+    idx = (np.arange(B) % len(luts)).astype(np.uint32)
+    return cts, tvs, idx, msgs, luts, delta
+
+
+# ----------------------------------------------------------------------------------- clocks
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index = index
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                       "--format=csv,noheader,nounits", "-lms", "100"], stdout=self.f, stderr=subprocess.DEVNULL)
+        except OSError:
+            self.p = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.p is None:
+            return out
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.p.kill()
+        self.f.flush()
+        rows = [r.strip().split(", ") for r in open(self.f.name) if r.strip()]
+        os.unlink(self.f.name)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in rows:
+            try:
+                sm.append(float(r[0]))
+                mx.append(float(r[1]))
+            except (ValueError, IndexError):
+                continue
+            for nme, v in zip(names, r[3:7]):
+                if v.strip().lower() == "active":
+                    reasons.add(nme)
+        if sm:
+            out.update(sm_mhz=statistics.median(sm), sm_max_mhz=max(mx), reasons=sorted(reasons), samples=len(sm))
+        return out
+
+
+# --------------------------------------------------------------------------- algorithmic work
+def work_per_pbs(p):
+    """butterflies + MACs (one modular multiply each) and key bytes"""
+    import math
+
+    logN = int(math.log2(p.N))
+    bf = p.N // 2 * logN
+    per_iter = ((p.k + 1) * p.ell + (p.k + 1)) * bf + (p.k + 1) ** 2 * p.ell * p.N
+    br = p.n * per_iter
+    ks = p.k * p.N * p.ell_ks * (p.n + 1) if p.order == 1 else ((p.k + 1) * p.ell + (p.k + 1)) * bf + (p.k + 1) ** 2 * p.ell * p.N
+    bsk_bytes = p.n * (p.k + 1) ** 2 * p.ell * p.N * 8
+    ksk_bytes = p.k * p.N * p.ell_ks * (p.n + 1) * 8 if p.order == 1 else (p.k + 1) ** 2 * p.ell * p.N * 8
+    return dict(br_modmul=br, ks_modmul=ks, bsk_bytes=bsk_bytes, ksk_bytes=ksk_bytes)
+
+
+# ------------------------------------------------------------------------------- reference arm
+def cpu_pbs_rate(O, ctx, cts, tvs, idx, budget_s=15.0):
+    """time the oracle (OpenMP over ciphertexts) on a bounded sample; returns (PBS/s, threads, sample)"""
+    threads = O.lib().orc_max_threads()
+    t0 = time.perf_counter()
+    ctx.pbs_batch(cts[:threads], tvs, idx[:threads])
+    t1 = time.perf_counter() - t0                       # one PBS per thread
+    rounds = max(1, min(8, int(budget_s / max(t1, 1e-3))))
+    nb = min(len(cts), threads * rounds)
+    t0 = time.perf_counter()
+    _, used = ctx.pbs_batch(cts[:nb], tvs, idx[:nb])
+    dt = time.perf_counter() - t0
+    return nb / dt, int(used), nb, dt
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import tfhe_b200 as T
+
+    params = T.S2_SHORTINT
+    O, ctx, ks = make_fixture(params)
+    threads = O.lib().orc_max_threads()
+    per_step = threads          # one PBS per host thread per step: a bounded sample of the B-ciphertext batch
+    cts, tvs, idx, *_ = make_inputs(O, ks, params, per_step, 4)
+    for _ in range(args.warmup):
+        ctx.pbs_batch(cts, tvs, idx)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        ctx.pbs_batch(cts, tvs, idx)
+    dt = time.perf_counter() - t0
+    v = per_step * args.steps / dt
+    sample = f"{per_step} PBS per step (1 per host thread) of the B={args.batch} batch, oracle C port, OpenMP"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u64 (Goldilocks field)", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "batch_per_step": per_step},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "note": "reference binary (Go luxfi/tfhe / wasm blob) is not in the tree and no go/node/cargo toolchain exists; "
+                "this arm is the C restatement of the in-tree algorithm (oracle/), kind=port",
+    }), flush=True)
+
+
+# ------------------------------------------------------------------------------------- our arm
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    import tfhe_b200 as T
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        log(f"note: WORLD_SIZE={world} overrides --gpus {args.gpus}")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    params = T.S2_SHORTINT
+    B = args.batch
+    eng = T.Engine(params, device=local)
+
+    # ---- evaluation keys: rank 0 converts to the NTT domain on its GPU, NCCL-broadcasts the device blob
+    O = ctx = ks = None
+    if rank == 0:
+        O, ctx, ks = make_fixture(params)
+        eng.load_keyset(ks)
+    if world > 1:
+        blob = torch.empty(eng.key_blob_bytes, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            eng.export_keys_device(blob)
+        dist.broadcast(blob, 0)
+        if rank != 0:
+            eng.import_keys_device(blob)
+        del blob
+    # ---- inputs: every rank gets its own B ciphertexts (weak scaling, no data-path collective)
+    if rank == 0:
+        cts, tvs, idx, msgs, luts, delta = make_inputs(O, ks, params, B, 4)
+    else:
+        rs = np.random.RandomState(100 + rank)
+        cts = rs.randint(0, 2 ** 63, size=(B, params.ct_len), dtype=np.int64).astype(np.uint64) % np.uint64(T.Q)
+        tvs = rs.randint(0, 2 ** 63, size=(4, params.N), dtype=np.int64).astype(np.uint64) % np.uint64(T.Q)
+        idx = (np.arange(B) % 4).astype(np.uint32)
+
+    h_in = torch.from_numpy(cts.view(np.int64)).pin_memory()
+    h_tv = torch.from_numpy(tvs.view(np.int64)).pin_memory()
+    h_idx = torch.from_numpy(idx.view(np.int32)).pin_memory()
+    h_out = torch.empty_like(h_in).pin_memory()
+    d_in, d_tv, d_idx = h_in.cuda(), h_tv.cuda(), h_idx.cuda()
+    d_out = torch.empty_like(d_in)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")   # > 126 MB L2
+    stream = torch.cuda.current_stream()
+    sptr = stream.cuda_stream
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step_device():
+        eng.pbs_batch_device(d_in, d_tv, d_idx, B, d_out, n_luts=4, stream=sptr)
+
+    # ---- device-resident timing: per-step CUDA events on the launching stream, L2 flushed between steps
+    for _ in range(args.warmup):
+        step_device()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    eng.set_timing(True)
+    l0 = eng.launch_count
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    ks_ms, br_ms = [], []
+    barrier()
+    for a, b in ev:
+        flush.zero_()                      # untimed: evicts keys and ciphertexts from L2
+        a.record(stream)
+        step_device()
+        b.record(stream)
+        b.synchronize()
+        t = eng.last_timing()
+        ks_ms.append(t[0])
+        br_ms.append(t[1])
+    barrier()
+    launches = eng.launch_count - l0
+    eng.set_timing(False)
+    total_ms = sum(a.elapsed_time(b) for a, b in ev)
+    clocks = sampler.stop() if rank == 0 else None
+    tt = torch.tensor([total_ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    total_ms = float(tt.item())
+    value = world * B * args.steps / (total_ms * 1e-3)
+
+    # ---- end to end through the host-pointer ABI call (pinned host buffers; H2D/D2H inside)
+    for _ in range(2):
+        eng.pbs_batch(h_in, h_tv, h_idx, out=h_out)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        eng.pbs_batch(h_in, h_tv, h_idx, out=h_out)       # blocking: returns after the D2H copy
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    te = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e = world * B * args.steps / float(te.item())
+    h2d = h_in.numel() * 8 + h_tv.numel() * 8 + h_idx.numel() * 4
+    d2h = h_out.numel() * 8
+
+    if rank != 0:
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        return
+
+    # ---- parity spot check (outside every timed region): device path == host path == oracle
+    got = h_out.numpy().view(np.uint64)
+    assert np.array_equal(got, d_out.cpu().numpy().view(np.uint64)), "device-resident and host-pointer paths disagree"
+    ncheck = 4
+    want, _ = ctx.pbs_batch(cts[:ncheck], tvs, idx[:ncheck])
+    assert np.array_equal(got[:ncheck], want), "GPU PBS differs from the oracle"
+    for i, m in enumerate(msgs):
+        dec = O.decode(O.lwe_decrypt(ks.s_in, got[i]), delta, 32)
+        assert dec == luts[idx[i]][m], (i, m, dec)
+
+    # ---- rooflines for the dominant kernel (blind rotate)
+    w = work_per_pbs(params)
+    peaks = {}
+    pk = ROOT / "MEASURED_PEAKS.json"
+    if pk.exists():
+        peaks = json.loads(pk.read_text())
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    wave = eng.wave_ciphertexts(B)
+    waves = -(-B // wave)
+    br_s = statistics.mean(br_ms) * 1e-3
+    br_bytes = w["bsk_bytes"] * waves + B * ((params.n + 1) * 8 + (params.k * params.N + 1) * 8)
+    imad, iadd, bfly = eng.int_peak()
+    modmul_s = B * w["br_modmul"] / br_s
+    roofline = {"bound": "hbm", "kernel": "blind_rotate_kernel", "achieved": br_bytes / br_s / 1e9, "peak": hbm_peak,
+                "unit": "GB/s", "frac": br_bytes / br_s / 1e9 / hbm_peak, "traffic": None,
+                "peak_source": "MEASURED_PEAKS.json hbm_gbs" if pk.exists() else "fallback 6650",
+                "bytes_per_launch": br_bytes, "ms_per_launch": br_s * 1e3,
+                "note": "BSK streamed once per wave of resident ciphertexts; the kernel is integer-pipe bound, see roofline_int"}
+    roofline_int = {"bound": "int32 pipe (IMAD.WIDE + IADD3)", "kernel": "blind_rotate_kernel", "achieved": modmul_s / 1e12,
+                    "peak": bfly / 1e12, "unit": "T modmul/s", "frac": modmul_s / bfly,
+                    "peak_source": "register-only Goldilocks butterfly micro-benchmark on this GPU (lux_debug_int_peak)",
+                    "imad_wide_per_s": imad, "iadd_per_s": iadd, "modmul_per_pbs": w["br_modmul"]}
+
+    # ---- CPU baseline on a bounded sample
+    cpu_v, cores, nb, dt = cpu_pbs_rate(O, ctx, cts, tvs, idx)
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u64 (Goldilocks field)", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "batch_per_gpu": B, "global_batch": B * world, "l2": "flushed between timed steps (256 MiB write)",
+                   "parallelism": f"batch-sharded x{world}, keys NCCL-broadcast once", "wave_ciphertexts": wave},
+        "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+        "gpu_launches": int(launches),
+        "kernel_ms": {"lwe_keyswitch": statistics.mean(ks_ms), "blind_rotate": statistics.mean(br_ms)},
+        "roofline": roofline, "roofline_int": roofline_int,
+        "cpu_baseline": {"value": cpu_v, "unit": UNIT, "cores": cores, "kind": "port",
+                         "sample": f"{nb} PBS of the same batch in {dt:.1f} s, oracle C port, OpenMP over ciphertexts"},
+        "clocks": clocks,
+        "parity": f"first {ncheck} outputs bit-exact vs oracle; {len(msgs)} decryptions correct",
+    }
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--batch", type=int, default=4096, help="ciphertexts per GPU per step")
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "ours":
+        log("note: timing rules want >= 3 warm-up steps")
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -78,6 +78,9 @@ int lux_engine_params(const lux_engine *e, lux_params *out);
 size_t lux_ct_words(const lux_engine *e);                        /* words per ciphertext entering/leaving a PBS */
 /* kernels launched by this engine since creation (bench.py's gpu_launches) */
 uint64_t lux_launch_count(const lux_engine *e);
+/* ciphertexts resident on the GPU at once in the blind-rotate launch chosen for a batch of B (the
+ * bootstrap key is streamed from HBM/L2 once per such wave; bench.py's roofline arithmetic) */
+size_t lux_wave_ciphertexts(const lux_engine *e, size_t B);
 /* when enabled, PBS calls bracket their kernels with CUDA events on the engine's stream */
 int lux_set_timing(lux_engine *e, int enabled);
 /* device milliseconds of the last timed PBS call: out[0] = key switch kernel, out[1] = blind-rotate kernel */

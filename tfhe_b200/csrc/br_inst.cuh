@@ -116,6 +116,21 @@ int LUX_CAT(lux_launch_br_, LUX_LOGN)(lux_engine *e, const BRArgs &a, cudaStream
 #endif
 }
 
+size_t LUX_CAT(lux_br_wave_, LUX_LOGN)(const lux_engine *e, size_t B) {
+#if LUX_LOGN == 9
+    const int t = pick_teams(e, B, 12);
+    return (size_t)e->sm_count * (t <= 1 ? 1 : t <= 4 ? 4 : 12);
+#elif LUX_LOGN == 10
+    const int t = pick_teams(e, B, 6);
+    return (size_t)e->sm_count * (t <= 1 ? 1 : t <= 3 ? 3 : 6);
+#elif LUX_LOGN == 11
+    const int t = pick_teams(e, B, 3);
+    return (size_t)e->sm_count * (t <= 1 ? 1 : t <= 2 ? 2 : 3);
+#else
+    return (size_t)e->sm_count;
+#endif
+}
+
 int LUX_CAT(lux_launch_ntt_, LUX_LOGN)(lux_engine *e, const NttArgs &a, cudaStream_t s) {
 #if LUX_LOGN <= 10
     return launch_ntt_t<LUX_LOGN, 4>(e, a, s);

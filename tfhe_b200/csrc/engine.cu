@@ -57,6 +57,41 @@ __global__ void field_probe_kernel(const u64 *a, const u64 *b, u64 *out, size_t 
     }
 }
 
+// integer-pipe micro-benchmarks (roofline denominators for the NTT/MAC work): each thread
+// runs 8 independent chains of one instruction kind, no memory traffic.
+//   kind 0: mad.wide.u32 (IMAD.WIDE.U32, fma pipe)   kind 1: 32-bit add (IADD3, alu pipe)
+//   kind 2: Goldilocks butterfly (gl_ct_butterfly) in registers = the engine's own arithmetic kernel
+template <int KIND>
+__global__ void __launch_bounds__(256) int_peak_kernel(u64 *sink, u32 iters, u64 seed) {
+    u64 x[8];
+    const u64 t = seed + blockIdx.x * 256 + threadIdx.x;
+#pragma unroll
+    for (int i = 0; i < 8; i++) x[i] = t * (2 * i + 3) + i;
+    const u32 m = (u32)(t | 1);
+    for (u32 it = 0; it < iters; it++) {
+#pragma unroll
+        for (int r = 0; r < 8; r++) {
+#pragma unroll
+            for (int i = 0; i < 8; i++) {
+                if (KIND == 0) {
+                    asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(x[i]) : "r"((u32)x[i]), "r"(m));
+                } else if (KIND == 1) {
+                    u32 lo = (u32)x[i], hi = (u32)(x[i] >> 32);
+                    asm volatile("add.u32 %0, %0, %1;" : "+r"(lo) : "r"(m));
+                    asm volatile("add.u32 %0, %0, %1;" : "+r"(hi) : "r"(lo));
+                    x[i] = ((u64)hi << 32) | lo;
+                } else {
+                    if (i & 1) gl_ct_butterfly(x[i - 1], x[i], (u64)m << 17 | r);
+                }
+            }
+        }
+    }
+    u64 acc = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) acc ^= x[i];
+    if (acc == 0x1234567) sink[0] = acc;
+}
+
 // any power-of-two N in [8, 2048]: one CTA per polynomial, one thread per butterfly, textbook
 // stage loop in shared memory (crypto/poly.rs:9-64).  Parity utility for the small golden vectors.
 __global__ void ntt_any_kernel(const u64 *in, u64 *out, const u64 *tw, u64 scale, u32 N, u32 inverse) {
@@ -312,6 +347,16 @@ size_t lux_ct_words(const lux_engine *e) {
     return e->p.order == LUX_ORDER_LWEKS_PBS ? (size_t)e->p.k * e->p.N + 1 : (size_t)e->p.n + 1;
 }
 uint64_t lux_launch_count(const lux_engine *e) { return e ? e->launches : 0; }
+size_t lux_wave_ciphertexts(const lux_engine *e, size_t B) {
+    if (!e) return 0;
+    switch (e->logN) {
+        case 9: return lux_br_wave_9(e, B);
+        case 10: return lux_br_wave_10(e, B);
+        case 11: return lux_br_wave_11(e, B);
+        case 12: return lux_br_wave_12(e, B);
+    }
+    return 0;
+}
 int lux_set_timing(lux_engine *e, int enabled) {
     if (!e) return LUX_ERR_INVALID;
     e->timing = enabled != 0;
@@ -669,6 +714,34 @@ int lux_debug_field_probe(lux_engine *e, const uint64_t *a, const uint64_t *b, s
     CUDA_TRY(e, cudaGetLastError());
     CUDA_TRY(e, cudaMemcpyAsync(out, e->scratch[2], sizeof(u64) * count * 7, cudaMemcpyDeviceToHost, e->stream));
     CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    return LUX_OK;
+}
+
+// out[0] = IMAD.WIDE.U32 per second, out[1] = 32-bit IADD per second, out[2] = Goldilocks butterflies per second
+// (register-only, whole GPU), measured with CUDA events.
+int lux_debug_int_peak(lux_engine *e, double out[3]) {
+    if (!e || !out) return LUX_ERR_INVALID;
+    CUDA_TRY(e, cudaSetDevice(e->device));
+    int rc;
+    if ((rc = ensure_scratch(e, 5, 64))) return rc;
+    const u32 iters = 4096, grid = (u32)e->sm_count * 8;
+    for (int kind = 0; kind < 3; kind++) {
+        float best = 1e30f;
+        for (int rep = 0; rep < 4; rep++) {
+            CUDA_TRY(e, cudaEventRecord(e->ev[0], e->stream));
+            if (kind == 0) int_peak_kernel<0><<<grid, 256, 0, e->stream>>>((u64 *)e->scratch[5], iters, 1);
+            if (kind == 1) int_peak_kernel<1><<<grid, 256, 0, e->stream>>>((u64 *)e->scratch[5], iters, 1);
+            if (kind == 2) int_peak_kernel<2><<<grid, 256, 0, e->stream>>>((u64 *)e->scratch[5], iters, 1);
+            e->launches++;
+            CUDA_TRY(e, cudaEventRecord(e->ev[1], e->stream));
+            CUDA_TRY(e, cudaEventSynchronize(e->ev[1]));
+            float ms;
+            CUDA_TRY(e, cudaEventElapsedTime(&ms, e->ev[0], e->ev[1]));
+            if (rep && ms < best) best = ms;
+        }
+        const double per_thread = (double)iters * 8 * (kind == 0 ? 8 : kind == 1 ? 16 : 4);
+        out[kind] = per_thread * grid * 256 / (best * 1e-3);
+    }
     return LUX_OK;
 }
 

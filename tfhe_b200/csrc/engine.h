@@ -41,6 +41,7 @@ struct lux_engine {
 
 void lux_host_ntt_tables(u32 N, std::vector<u64> &roots, std::vector<u64> &invroots, u64 &ninv);
 extern "C" int lux_debug_force_teams(lux_engine *e, int teams);
+extern "C" int lux_debug_int_peak(lux_engine *e, double out[3]);
 extern "C" int lux_debug_field_probe(lux_engine *e, const uint64_t *a, const uint64_t *b, size_t count, uint64_t *out);
 
 #define LUX_FAIL(e, code, ...)                                  \
@@ -61,6 +62,7 @@ extern "C" int lux_debug_field_probe(lux_engine *e, const uint64_t *a, const uin
 #define LUX_DECL_LAUNCHERS(LN)                                                                      \
     int lux_launch_br_##LN(lux_engine *e, const BRArgs &a, cudaStream_t s);                         \
     int lux_launch_ntt_##LN(lux_engine *e, const NttArgs &a, cudaStream_t s);                       \
+    size_t lux_br_wave_##LN(const lux_engine *e, size_t B);                                         \
     int lux_launch_xp_##LN(lux_engine *e, const BRArgs &a, const u64 *d_glwe, size_t stride, cudaStream_t s);
 LUX_DECL_LAUNCHERS(9)
 LUX_DECL_LAUNCHERS(10)

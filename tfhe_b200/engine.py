@@ -87,6 +87,7 @@ ABI = {
     "lux_engine_params": (_int, [_vp, C.POINTER(_CParams)]),
     "lux_ct_words": (_sz, [_vp]),
     "lux_launch_count": (_u64, [_vp]),
+    "lux_wave_ciphertexts": (_sz, [_vp, _sz]),
     "lux_set_timing": (_int, [_vp, _int]),
     "lux_last_timing": (_int, [_vp, C.POINTER(C.c_float * 2)]),
     "lux_synchronize": (_int, [_vp]),
@@ -126,6 +127,9 @@ def lib():
             fn.argtypes = args
         if hasattr(L, "lux_debug_force_teams"):
             L.lux_debug_force_teams.argtypes = [_vp, _int]
+        if hasattr(L, "lux_debug_int_peak"):
+            L.lux_debug_int_peak.argtypes = [_vp, C.POINTER(C.c_double * 3)]
+            L.lux_debug_int_peak.restype = _int
         if hasattr(L, "lux_debug_field_probe"):
             L.lux_debug_field_probe.argtypes = [_vp, _u64p, _u64p, _sz, _u64p]
             L.lux_debug_field_probe.restype = _int
@@ -261,12 +265,22 @@ class Engine:
     def launch_count(self) -> int:
         return lib().lux_launch_count(self._h)
 
+    def int_peak(self):
+        """measured integer-pipe rates of this GPU: (IMAD.WIDE/s, IADD/s, register-only Goldilocks butterflies/s)"""
+        buf = (C.c_double * 3)()
+        self._ck(lib().lux_debug_int_peak(self._h, C.byref(buf)))
+        return float(buf[0]), float(buf[1]), float(buf[2])
+
     def field_probe(self, a, b):
         """device field arithmetic on raw words: rows = a+b, a-b, a*b, CT butterfly (2), GS butterfly (2)"""
         a, b = _u64arr(a).reshape(-1), _u64arr(b).reshape(-1)
         out = np.empty((7, a.size), np.uint64)
         self._ck(lib().lux_debug_field_probe(self._h, a, b, a.size, out.reshape(-1)))
         return out
+
+    def wave_ciphertexts(self, B: int) -> int:
+        """ciphertexts resident on the GPU at once in the blind-rotate launch for a batch of B"""
+        return int(lib().lux_wave_ciphertexts(self._h, B))
 
     def force_teams(self, t: int):
         lib().lux_debug_force_teams(self._h, t)
