@@ -205,14 +205,9 @@ def run_ours(args):
     if rank == 0:
         O, ctx, ks = make_fixture(params)
         eng.load_keyset(ks)
-    if world > 1:
-        blob = torch.empty(eng.key_blob_bytes, dtype=torch.uint8, device="cuda")
-        if rank == 0:
-            eng.export_keys_device(blob)
-        dist.broadcast(blob, 0)
-        if rank != 0:
-            eng.import_keys_device(blob)
-        del blob
+    from tfhe_b200.sharding import replicate_keys
+
+    replicate_keys(eng, rank, world, src=0, device="cuda")
     # ---- inputs: every rank gets its own B ciphertexts (weak scaling, no data-path collective)
     if rank == 0:
         cts, tvs, idx, msgs, luts, delta = make_inputs(O, ks, params, B, 4)

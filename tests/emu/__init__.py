@@ -16,7 +16,7 @@ class BRArgs(C.Structure):
     _fields_ = [("n", C.c_uint32), ("steps", C.c_uint32), ("ell", C.c_uint32), ("logB", C.c_uint32),
                 ("L", C.c_uint32), ("B", C.c_uint32), ("out_mode", C.c_uint32), ("n_out", C.c_uint32),
                 ("bsk", C.c_void_p), ("ksk", C.c_void_p), ("lwe", C.c_void_p), ("testv", C.c_void_p),
-                ("lut_idx", C.c_void_p), ("out", C.c_void_p), ("tw_fwd", C.c_void_p), ("tw_inv", C.c_void_p)]
+                ("lut_idx", C.c_void_p), ("lut_div", C.c_uint32), ("out", C.c_void_p), ("tw_fwd", C.c_void_p), ("tw_inv", C.c_void_p)]
 
 
 class KSArgs(C.Structure):

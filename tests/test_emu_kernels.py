@@ -81,7 +81,7 @@ def test_emu_blind_rotate_matches_oracle(logn, teams, ell, logB, B, steps):
         out = np.zeros((B, out_len), np.uint64)
         a = E.BRArgs(n=n, steps=steps, ell=ell, logB=logB, L=(64 + logB - 1) // logB, B=B, out_mode=out_mode,
                      n_out=n_out, bsk=E.ptr(bsk_dev), ksk=E.ptr(ksk_dev) if with_ksk else None, lwe=E.ptr(lwe),
-                     testv=E.ptr(tvs), lut_idx=E.ptr(idx), out=E.ptr(out), tw_fwd=E.ptr(roots), tw_inv=E.ptr(inv))
+                     testv=E.ptr(tvs), lut_idx=E.ptr(idx), lut_div=1, out=E.ptr(out), tw_fwd=E.ptr(roots), tw_inv=E.ptr(inv))
         assert E.lib().emu_blind_rotate(logn, teams, a) == 0
         return out
 

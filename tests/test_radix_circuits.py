@@ -1,0 +1,158 @@
+"""CPU tests of the euintN circuits (no GPU): the programs the library publishes through
+lux_radix_program() are interpreted on plaintext integers and checked against the reference's fhEVM
+known-answer tests (tests/golden/fhevm_kats.json, harvested from
+/root/reference/tests/fhevm-suite/e2e/test/fhevmOperations/*.ts by tests/golden/make_fhevm_kats.py),
+the ERC20 vectors (encryptedERC20/EncryptedERC20.ts:64-183) and wrap-around semantics mod 2^width."""
+import json
+import random
+from pathlib import Path
+
+import pytest
+
+import tfhe_b200.radix as R
+from oracle.radix import interp_plain, join_blocks, split_blocks
+
+KATS = json.loads((Path(__file__).parent / "golden" / "fhevm_kats.json").read_text())
+LUTS = R.luts()
+SUPPORTED = set(R.OPS)
+
+
+def width_of(t: str) -> int:
+    return int(t.lstrip("eu").replace("int", ""))
+
+
+def run_plain(op, width, *operands):
+    prog = R.program(op, width)
+    nb = R.blocks(width)
+    ins = []
+    for k, v in enumerate(operands):
+        ins.append(split_blocks(v, prog.in_blocks[k]))
+    outs = interp_plain(prog, LUTS, ins)
+    assert all(0 <= b < 4 for o in outs for b in o), "outputs must be clean blocks"
+    return [join_blocks(o) for o in outs], nb
+
+
+def plain_semantics(op, a, b, width):
+    m = (1 << width) - 1
+    s = (b % width) if b is not None else 0
+    return {
+        "add": lambda: (a + b) & m, "sub": lambda: (a - b) & m, "mul": lambda: (a * b) & m, "neg": lambda: (-a) & m,
+        "eq": lambda: int(a == b), "ne": lambda: int(a != b), "lt": lambda: int(a < b), "le": lambda: int(a <= b),
+        "gt": lambda: int(a > b), "ge": lambda: int(a >= b), "min": lambda: min(a, b), "max": lambda: max(a, b),
+        "and": lambda: a & b, "or": lambda: a | b, "xor": lambda: a ^ b, "not": lambda: (~a) & m,
+        "shl": lambda: (a << s) & m, "shr": lambda: a >> s,
+        "rotl": lambda: ((a << s) | (a >> (width - s))) & m if s else a,
+        "rotr": lambda: ((a >> s) | (a << (width - s))) & m if s else a,
+    }[op]()
+
+
+def test_abi_symbols_present():
+    L = R.lib()
+    for name in R.ABI:
+        assert hasattr(L, name), name
+    assert R.blocks(64) == 32 and R.blocks(7) == 0 and R.blocks(258) == 0
+
+
+def test_kat_harvest_is_complete():
+    assert len(KATS["ops"]) == 2394
+    ops = {k["op"] for k in KATS["ops"]}
+    assert ops - SUPPORTED == {"div", "rem"}      # division by a plaintext scalar: not built
+
+
+@pytest.mark.parametrize("op", sorted(SUPPORTED))
+def test_fhevm_known_answers(op):
+    """every known-answer test of the reference for this op, through the circuit (plaintext interpretation)"""
+    cases = [k for k in KATS["ops"] if k["op"] == op]
+    assert cases
+    for k in cases:
+        types = k["types"]
+        # the suite's overloads mix widths and plaintext scalars: operands are cast to the wider type
+        width = max(width_of(t) for t in types)
+        if op in ("shl", "shr", "rotl", "rotr"):
+            width = width_of(types[0])
+        args = [int(a) for a in k["args"]]
+        (got,), _ = run_plain(op, width, *args)
+        exp = k["expected"]
+        exp = int(exp) if not isinstance(exp, bool) else int(exp)
+        assert got == exp, (k, got)
+        assert got == plain_semantics(op, args[0], args[1] if len(args) > 1 else None, width), k
+
+
+@pytest.mark.parametrize("width", [4, 8, 16, 32, 64])
+def test_wraparound_and_random(width):
+    """overflow / underflow wrap mod 2^width (not pinned by the reference's KATs) + random fuzz"""
+    m = (1 << width) - 1
+    rnd = random.Random(width)
+    edge = [0, 1, 2, 3, m, m - 1, m >> 1, (m >> 1) + 1]
+    pairs = [(a, b) for a in edge for b in edge] + [(rnd.randrange(m + 1), rnd.randrange(m + 1)) for _ in range(40)]
+    ops = sorted(SUPPORTED - {"mul"}) if width == 64 else sorted(SUPPORTED)
+    for op in ops:
+        for a, b in pairs[: (24 if width >= 32 else len(pairs))]:
+            if op in R.UNARY:
+                (got,), _ = run_plain(op, width, a)
+                assert got == plain_semantics(op, a, None, width), (op, a)
+            else:
+                (got,), _ = run_plain(op, width, a, b)
+                assert got == plain_semantics(op, a, b, width), (op, a, b)
+
+
+def test_mul64_edges():
+    m = (1 << 64) - 1
+    for a, b in [(m, m), (m, 2), (0x123456789ABCDEF0, 0x0FEDCBA987654321), (1 << 63, 2), (3, 5)]:
+        (got,), _ = run_plain("mul", 64, a, b)
+        assert got == (a * b) & m
+
+
+def test_wide_types():
+    rnd = random.Random(9)
+    for width in (128, 256):
+        m = (1 << width) - 1
+        for op in ("add", "sub", "lt", "eq", "ne", "xor", "min", "shl", "rotr"):
+            a, b = rnd.randrange(m + 1), rnd.randrange(m + 1)
+            (got,), _ = run_plain(op, width, a, b)
+            assert got == plain_semantics(op, a, b, width), (op, width)
+
+
+def test_select_program():
+    prog = R.program(R.PROG_SELECT, 16)
+    for c in (0, 1):
+        out = interp_plain(prog, LUTS, [[c], split_blocks(0xBEEF, 8), split_blocks(0x1234, 8)])
+        assert join_blocks(out[0]) == (0xBEEF if c else 0x1234)
+
+
+def test_erc20_vectors():
+    """EncryptedERC20.ts: mint 10000, transfer 1337 => 8663 / 1337; mint 1000, transfer 1337 => unchanged"""
+    prog = R.program(R.PROG_ERC20, 64)
+    rnd = random.Random(3)
+    cases = [(v["mint"], 0, v["transfer"], v["from_after"], v["to_after"]) for v in KATS["erc20"]]
+    for _ in range(30):   # balances U[0,2^40), amounts U[0,2^41)
+        f, t, a = rnd.randrange(1 << 40), rnd.randrange(1 << 40), rnd.randrange(1 << 41)
+        cases.append((f, t, a, f - a if a <= f else f, t + a if a <= f else t))
+    cases.append(((1 << 64) - 1, (1 << 64) - 1, 1, (1 << 64) - 2, 0))   # recipient wraps mod 2^64
+    for f, t, a, nf, nt in cases:
+        out = interp_plain(prog, LUTS, [split_blocks(f, 32), split_blocks(t, 32), split_blocks(a, 32)])
+        assert (join_blocks(out[0]), join_blocks(out[1])) == (nf, nt), (f, t, a)
+
+
+def test_pbs_counts_and_depths():
+    """circuit sizes reported to bench.py agree with the programs; sanity bounds on the designs"""
+    for op in ("add", "sub", "lt", "eq", "and", "mul"):
+        for width in (8, 16, 32, 64):
+            p = R.program(op, width)
+            assert p.n_pbs == R.pbs_count(op, width)
+            assert len(p.levels) == R.depth(op, width)
+    nb = 32
+    assert R.pbs_count("add", 64) == 2 * nb - 1          # ripple: carry + message per block
+    assert R.pbs_count("lt", 64) == 2 * nb - 1           # signs + pairwise tree
+    assert R.pbs_count("and", 64) == nb
+    assert R.depth("lt", 64) == 6
+    assert int(R.lib().lux_erc20_pbs_count()) == R.program(R.PROG_ERC20, 64).n_pbs
+    assert R.pbs_count("mul", 64) < 2600
+
+
+def test_every_pbs_input_stays_below_the_padding_bit():
+    """interp_plain raises if any bootstrap input leaves [0,16); drive the circuits with worst-case blocks"""
+    m = (1 << 32) - 1
+    for op in sorted(SUPPORTED - R.UNARY):
+        for a, b in [(m, m), (m, 0), (0, m), (0x55555555, 0xAAAAAAAA)]:
+            run_plain(op, 32, a, b)

@@ -170,7 +170,7 @@ void lux_host_ntt_tables(u32 N, std::vector<u64> &roots, std::vector<u64> &invro
     ninv = gl_pow_host(gl_pow_host(2, GL_Q - 2), logN);
 }
 
-static int ensure_scratch(lux_engine *e, int slot, size_t bytes) {
+int lux_ensure_scratch(lux_engine *e, int slot, size_t bytes) {
     if (e->scratch_bytes[slot] >= bytes) return LUX_OK;
     if (e->scratch[slot]) cudaFree(e->scratch[slot]);
     e->scratch[slot] = nullptr;
@@ -181,6 +181,8 @@ static int ensure_scratch(lux_engine *e, int slot, size_t bytes) {
     e->scratch_bytes[slot] = want;
     return LUX_OK;
 }
+
+static int ensure_scratch(lux_engine *e, int slot, size_t bytes) { return lux_ensure_scratch(e, slot, bytes); }
 
 static size_t ggsw_words(const lux_params &p) { return (size_t)(p.k + 1) * p.ell * (p.k + 1) * p.N; }
 
@@ -238,10 +240,51 @@ static BRArgs make_br_args(const lux_engine *e, const u64 *d_lwe, const u64 *d_t
     a.lwe = d_lwe;
     a.testv = d_testv;
     a.lut_idx = d_idx;
+    a.lut_div = 1;
     a.out = d_out;
     a.tw_fwd = e->d_tw_fwd;
     a.tw_inv = e->d_tw_inv;
     return a;
+}
+
+
+int lux_pbs_device_grouped(lux_engine *e, const u64 *d_in, const u64 *d_testvs, const u32 *d_lut_idx, u32 lut_div, size_t B,
+                           u64 *d_out, cudaStream_t s) {
+    if (B == 0) return LUX_OK;
+    if (B > 0x7fffffffu) LUX_FAIL(e, LUX_ERR_INVALID, "batch too large");
+    if (!e->has_bsk) LUX_FAIL(e, LUX_ERR_NO_KEY, "bootstrap key not loaded");
+    const bool ks_first = e->p.order == LUX_ORDER_LWEKS_PBS;
+    if (ks_first && !e->has_lksk) LUX_FAIL(e, LUX_ERR_NO_KEY, "LWE key switch key not loaded");
+    if (!ks_first && !e->has_gksk) LUX_FAIL(e, LUX_ERR_NO_KEY, "GLWE key switch key not loaded");
+    CUDA_TRY(e, cudaSetDevice(e->device));
+    const u64 *d_small = d_in;
+    if (e->timing) CUDA_TRY(e, cudaEventRecord(e->ev[0], s));
+    if (ks_first) {
+        int rc = ensure_scratch(e, 0, sizeof(u64) * B * (e->p.n + 1));
+        if (rc) return rc;
+        rc = launch_ks(e, d_in, (u64 *)e->scratch[0], B, s);
+        if (rc) return rc;
+        d_small = (const u64 *)e->scratch[0];
+    }
+    if (e->timing) CUDA_TRY(e, cudaEventRecord(e->ev[1], s));
+    BRArgs a = make_br_args(e, d_small, d_testvs, d_lut_idx, B, d_out);
+    a.lut_div = lut_div ? lut_div : 1;
+    if (ks_first) {
+        a.out_mode = 0;
+    } else {
+        a.ksk = e->d_gksk;
+        a.out_mode = 1;
+        a.n_out = e->p.n;
+    }
+    int rc = launch_br(e, a, s);
+    if (rc) return rc;
+    if (e->timing) {
+        CUDA_TRY(e, cudaEventRecord(e->ev[2], s));
+        CUDA_TRY(e, cudaEventSynchronize(e->ev[2]));
+        CUDA_TRY(e, cudaEventElapsedTime(&e->last_ms[0], e->ev[0], e->ev[1]));
+        CUDA_TRY(e, cudaEventElapsedTime(&e->last_ms[1], e->ev[1], e->ev[2]));
+    }
+    return LUX_OK;
 }
 
 // --------------------------------------------------------------------------------------------- ABI
@@ -327,6 +370,7 @@ void lux_engine_destroy(lux_engine *e) {
     if (!e) return;
     cudaSetDevice(e->device);
     if (e->stream) cudaStreamSynchronize(e->stream);
+    lux_radix_destroy(e);
     for (int i = 0; i < LUX_SCRATCH_SLOTS; i++)
         if (e->scratch[i]) cudaFree(e->scratch[i]);
     for (auto &kv : e->any_tables) cudaFree(kv.second);
@@ -460,41 +504,7 @@ int lux_pbs_batch_device(lux_engine *e, const uint64_t *d_in, const uint64_t *d_
                          const uint32_t *d_lut_idx, size_t B, uint64_t *d_out, void *stream) {
     if (!e) return LUX_ERR_INVALID;
     if (!d_in || !d_testvs || !d_out || n_luts == 0) LUX_FAIL(e, LUX_ERR_INVALID, "lux_pbs_batch_device: null/empty argument");
-    if (B == 0) return LUX_OK;
-    if (B > 0x7fffffffu) LUX_FAIL(e, LUX_ERR_INVALID, "batch too large");
-    if (!e->has_bsk) LUX_FAIL(e, LUX_ERR_NO_KEY, "bootstrap key not loaded");
-    const bool ks_first = e->p.order == LUX_ORDER_LWEKS_PBS;
-    if (ks_first && !e->has_lksk) LUX_FAIL(e, LUX_ERR_NO_KEY, "LWE key switch key not loaded");
-    if (!ks_first && !e->has_gksk) LUX_FAIL(e, LUX_ERR_NO_KEY, "GLWE key switch key not loaded");
-    CUDA_TRY(e, cudaSetDevice(e->device));
-    cudaStream_t s = stream ? (cudaStream_t)stream : e->stream;
-    const u64 *d_small = d_in;
-    if (e->timing) CUDA_TRY(e, cudaEventRecord(e->ev[0], s));
-    if (ks_first) {
-        int rc = ensure_scratch(e, 0, sizeof(u64) * B * (e->p.n + 1));
-        if (rc) return rc;
-        rc = launch_ks(e, d_in, (u64 *)e->scratch[0], B, s);
-        if (rc) return rc;
-        d_small = (const u64 *)e->scratch[0];
-    }
-    if (e->timing) CUDA_TRY(e, cudaEventRecord(e->ev[1], s));
-    BRArgs a = make_br_args(e, d_small, d_testvs, d_lut_idx, B, d_out);
-    if (ks_first) {
-        a.out_mode = 0;
-    } else {
-        a.ksk = e->d_gksk;
-        a.out_mode = 1;
-        a.n_out = e->p.n;
-    }
-    int rc = launch_br(e, a, s);
-    if (rc) return rc;
-    if (e->timing) {
-        CUDA_TRY(e, cudaEventRecord(e->ev[2], s));
-        CUDA_TRY(e, cudaEventSynchronize(e->ev[2]));
-        CUDA_TRY(e, cudaEventElapsedTime(&e->last_ms[0], e->ev[0], e->ev[1]));
-        CUDA_TRY(e, cudaEventElapsedTime(&e->last_ms[1], e->ev[1], e->ev[2]));
-    }
-    return LUX_OK;
+    return lux_pbs_device_grouped(e, d_in, d_testvs, d_lut_idx, 1, B, d_out, stream ? (cudaStream_t)stream : e->stream);
 }
 
 int lux_pbs_batch(lux_engine *e, const uint64_t *lwe_in, const uint64_t *testvs, uint32_t n_luts,

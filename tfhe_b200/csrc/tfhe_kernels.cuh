@@ -231,7 +231,8 @@ struct BRArgs {
     const u64 *ksk;     // one GGSW in the same format, or nullptr          (ivc_based_vpbs.rs:355-371)
     const u64 *lwe;     // [B][n+1] ciphertexts under the small key
     const u64 *testv;   // [n_luts][N]
-    const u32 *lut_idx; // [B] or nullptr
+    const u32 *lut_idx; // [ceil(B/lut_div)] or nullptr: ciphertext ct uses test vector lut_idx[ct / lut_div]
+    u32 lut_div;        // >= 1 (1 = one index per ciphertext; the radix layer uses one per slot of B ciphertexts)
     u64 *out;           // [B][out_len]
     const u64 *tw_fwd;  // ROOTS    [N]
     const u64 *tw_inv;  // INVROOTS [N]
@@ -316,7 +317,7 @@ TK_DEV void blind_rotate_body(const BRArgs &a, int tid, int bid, unsigned char *
     if (ct >= a.B) return;  // whole team leaves; only team barriers are used from here on
 
     const u64 *lwe = a.lwe + (size_t)ct * (a.n + 1);
-    const u64 *tv = a.testv + (size_t)(a.lut_idx ? a.lut_idx[ct] : 0) * N;
+    const u64 *tv = a.testv + (size_t)(a.lut_idx ? a.lut_idx[ct / a.lut_div] : 0) * N;
 
     // acc0 = X^{ms(-b)} * (0, testv)      ivc_based_vpbs.rs:109-124 (first_step negates the body)
     {
