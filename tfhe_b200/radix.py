@@ -153,6 +153,8 @@ class Radix:
         self.e._ck(rc)
 
     def _shape(self, a, nb):
+        if nb == 0:
+            raise LuxError(-1, "unsupported bit width (even, 2..256)")
         a = _arr(a).reshape(-1, nb, self.w)
         return a, a.shape[0]
 
