@@ -39,7 +39,7 @@ static void run_cta(int nthreads, int team_size, const std::function<void(int)> 
 template <int LOGN, int TEAMS>
 static void emu_ntt_t(const NttArgs &a, int nblocks) {
     constexpr int N = Tile<LOGN>::N, T = Tile<LOGN>::T;
-    std::vector<unsigned char> smem(sizeof(u64) * (N + TEAMS * 2 * N));
+    std::vector<unsigned char> smem(sizeof(u64) * (N + TEAMS * N));
     for (int bid = 0; bid < nblocks; bid++)
         run_cta(T * TEAMS, T, [&](int tid) { ntt_batch_body<LOGN, TEAMS>(a, tid, bid, nblocks, smem.data()); });
 }
@@ -53,6 +53,19 @@ static void emu_br_t(const BRArgs &a) {
         run_cta(T * TEAMS, T, [&](int tid) { blind_rotate_body<LOGN, TEAMS>(a, tid, bid, smem.data()); });
 }
 
+// reference-order NTT-domain GGSWs [n_ggsw][2][ell][2][N] -> resident key rows (fold + key_pos), as key_format_kernel
+template <int LOGN>
+static void to_key_t(u64 *ggsw, size_t n_polys, u32 ell, u64 ninv) {
+    constexpr int N = Tile<LOGN>::N, T = Tile<LOGN>::T;
+    std::vector<u64> tmp(N);
+    for (size_t pi = 0; pi < n_polys; pi++) {
+        u64 *poly = ggsw + pi * N;
+        const u32 glev = (u32)((pi / (2 * ell)) & 1);
+        for (int tau = 0; tau < T; tau++)
+            for (int e = 0; e < 16; e++) tmp[key_pos<LOGN>(tau, e)] = ggsw_fold_elem(poly[posC<LOGN>(tau, e)], ninv, glev);
+        memcpy(poly, tmp.data(), sizeof(u64) * N);
+    }
+}
 extern "C" {
 
 int emu_ntt(int logn, int teams, int nblocks, const u64 *in, u64 *out, const u64 *tw, u64 scale, u32 n_polys, u32 inverse) {
@@ -89,15 +102,15 @@ void emu_ksk_colsum(const u64 *ksk, u64 *ksum, u32 rows, u32 cols) {
     for (u32 c = 0; c < cols; c++) ksk_colsum_body(ksk, ksum, rows, cols, c);
 }
 
-void emu_ggsw_fold(u64 *ggsw, size_t n_ggsw, u32 ell, u32 N, u64 ninv) {
-    // layout [n_ggsw][2][ell][2][N]
-    const size_t glev = (size_t)ell * 2 * N;
-    for (size_t g = 0; g < n_ggsw; g++)
-        for (u32 j = 0; j < 2; j++)
-            for (size_t x = 0; x < glev; x++) {
-                u64 &v = ggsw[(g * 2 + j) * glev + x];
-                v = ggsw_fold_elem(v, ninv, j);
-            }
+int emu_ggsw_to_key(u64 *ggsw, size_t n_ggsw, u32 ell, u32 N, u64 ninv) {
+    const size_t n_polys = n_ggsw * 4 * ell;
+    switch (N) {
+        case 512: to_key_t<9>(ggsw, n_polys, ell, ninv); return 0;
+        case 1024: to_key_t<10>(ggsw, n_polys, ell, ninv); return 0;
+        case 2048: to_key_t<11>(ggsw, n_polys, ell, ninv); return 0;
+        case 4096: to_key_t<12>(ggsw, n_polys, ell, ninv); return 0;
+    }
+    return -1;
 }
 
 u64 emu_digit(u64 x, u32 li, u32 logB, int centred) { return gl_digit(x, li, logB, centred != 0); }

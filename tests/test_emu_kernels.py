@@ -46,7 +46,8 @@ def test_emu_ntt_matches_oracle_and_golden(golden, logn, teams, nblocks, npolys)
     if f"n{N}_testghat" in golden.files:
         assert np.array_equal(out[0], golden[f"n{N}_testghat"])
     back = np.zeros_like(polys)
-    assert E.lib().emu_ntt(logn, teams, nblocks, out.reshape(-1), back.reshape(-1), inv, ninv, npolys, 1) == 0
+    # the kernels keep ROOTS only: INVROOTS[m+i] = -ROOTS[2m-1-i] is absorbed by the inverse butterfly
+    assert E.lib().emu_ntt(logn, teams, nblocks, out.reshape(-1), back.reshape(-1), roots, ninv, npolys, 1) == 0
     assert np.array_equal(back, polys)
 
 
@@ -54,7 +55,7 @@ def _device_bsk(ctx, ggsw_std, count):
     """std-domain GGSWs -> the engine's device format, via the same fold the GPU applies."""
     p = ctx.p
     ntt = np.concatenate([O.ntt_forward(pp, ctx.roots) for pp in ggsw_std.reshape(-1, p.N)])
-    E.lib().emu_ggsw_fold(ntt, count, p.ell, p.N, ctx.ninv)
+    assert E.lib().emu_ggsw_to_key(ntt, count, p.ell, p.N, ctx.ninv) == 0
     return ntt
 
 
@@ -81,7 +82,7 @@ def test_emu_blind_rotate_matches_oracle(logn, teams, ell, logB, B, steps):
         out = np.zeros((B, out_len), np.uint64)
         a = E.BRArgs(n=n, steps=steps, ell=ell, logB=logB, L=(64 + logB - 1) // logB, B=B, out_mode=out_mode,
                      n_out=n_out, bsk=E.ptr(bsk_dev), ksk=E.ptr(ksk_dev) if with_ksk else None, lwe=E.ptr(lwe),
-                     testv=E.ptr(tvs), lut_idx=E.ptr(idx), lut_div=1, out=E.ptr(out), tw_fwd=E.ptr(roots), tw_inv=E.ptr(inv))
+                     testv=E.ptr(tvs), lut_idx=E.ptr(idx), lut_div=1, out=E.ptr(out), tw_fwd=E.ptr(roots))
         assert E.lib().emu_blind_rotate(logn, teams, a) == 0
         return out
 

@@ -21,23 +21,37 @@ __global__ void __launch_bounds__(Tile<LOGN>::T *TEAMS, 1)
     external_product_kernel(const BRArgs a, const u64 *glwe_in, size_t ggsw_stride) {
     extern __shared__ __align__(16) unsigned char smem[];
     constexpr int N = Tile<LOGN>::N, T = Tile<LOGN>::T;
-    u64 *tw_f = (u64 *)smem, *tw_i = tw_f + N;
+    u64 *tw = (u64 *)smem;
     const int tid = threadIdx.x, team = tid / T, tau = tid % T;
-    u64 *acc = tw_i + N + (size_t)team * 4 * N;
-    u64 *xb0 = acc + 2 * N, *xb1 = xb0 + N;
-    for (int i = tid; i < N; i += T * TEAMS) {
-        tw_f[i] = a.tw_fwd[i];
-        tw_i[i] = a.tw_inv[i];
-    }
+    u64 *acc = tw + N + (size_t)team * 3 * N;
+    u64 *xb = acc + 2 * N;
+    for (int i = tid; i < N; i += T * TEAMS) tw[i] = a.tw_fwd[i];
     __syncthreads();
     const u32 ct = blockIdx.x * TEAMS + team;
     if (ct >= a.B) return;
     for (int p = tau; p < 2 * N; p += T) acc[p] = glwe_in[(size_t)ct * 2 * N + p];
     team_sync(team, T);
-    team_external_product<LOGN, false>(a, a.bsk + (size_t)ct * ggsw_stride, 0, acc, xb0, xb1, tw_f, tw_i, tau, team);
+    KeyStream none{};
+    team_external_product<LOGN, false>(a, a.bsk + (size_t)ct * ggsw_stride, none, false, 0, acc, xb, tw, tau, team, tid & 31);
     for (int p = tau; p < 2 * N; p += T) a.out[(size_t)ct * 2 * N + p] = acc[p];
 }
 
+
+// NTT-domain polynomials in the reference's order -> resident key rows, in place: fold 1/N and the sign
+// of the mask GLev (vtfhe/ggsw_ct.rs:108-111, crypto/poly.rs:62-63), permute to key_pos.  One CTA per polynomial.
+template <int LOGN>
+__global__ void __launch_bounds__(Tile<LOGN>::T) key_format_kernel(u64 *polys, u32 ell, u64 ninv) {
+    constexpr int N = Tile<LOGN>::N;
+    u64 *poly = polys + (size_t)blockIdx.x * N;
+    const u32 glev = (blockIdx.x / (2 * ell)) & 1;
+    const int tau = threadIdx.x;
+    u64 x[16];
+#pragma unroll
+    for (int e = 0; e < 16; e++) x[e] = poly[posC<LOGN>(tau, e)];
+    __syncthreads();
+#pragma unroll
+    for (int e = 0; e < 16; e++) poly[key_pos<LOGN>(tau, e)] = ggsw_fold_elem(x[e], ninv, glev);
+}
 
 template <int LOGN, int TEAMS>
 static int launch_br_t(lux_engine *e, const BRArgs &a, cudaStream_t s) {
@@ -64,7 +78,7 @@ static int pick_teams(const lux_engine *e, size_t B, int max_teams) {
 
 template <int LOGN, int TEAMS>
 static int launch_ntt_t(lux_engine *e, const NttArgs &a, cudaStream_t s) {
-    constexpr size_t smem = sizeof(u64) * ((size_t)Tile<LOGN>::N + (size_t)TEAMS * 2 * Tile<LOGN>::N);
+    constexpr size_t smem = sizeof(u64) * ((size_t)Tile<LOGN>::N + (size_t)TEAMS * Tile<LOGN>::N);
     static bool configured[64] = {};
     if (!configured[e->device & 63]) {
         CUDA_TRY(e, cudaFuncSetAttribute(ntt_batch_kernel<LOGN, TEAMS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -139,6 +153,14 @@ int LUX_CAT(lux_launch_ntt_, LUX_LOGN)(lux_engine *e, const NttArgs &a, cudaStre
 #else
     return launch_ntt_t<12, 1>(e, a, s);
 #endif
+}
+
+int LUX_CAT(lux_launch_keyfmt_, LUX_LOGN)(lux_engine *e, u64 *d_polys, size_t n_polys, cudaStream_t s) {
+    if (n_polys == 0) return LUX_OK;
+    key_format_kernel<LUX_LOGN><<<(unsigned)n_polys, Tile<LUX_LOGN>::T, 0, s>>>(d_polys, e->p.ell, e->ninv);
+    e->launches++;
+    CUDA_TRY(e, cudaGetLastError());
+    return LUX_OK;
 }
 
 int LUX_CAT(lux_launch_xp_, LUX_LOGN)(lux_engine *e, const BRArgs &a, const u64 *d_glwe, size_t stride, cudaStream_t s) {

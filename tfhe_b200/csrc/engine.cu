@@ -19,12 +19,6 @@ __global__ void ksk_colsum_kernel(const u64 *ksk, u64 *ksum, u32 rows, u32 cols)
     ksk_colsum_body(ksk, ksum, rows, cols, blockIdx.x * blockDim.x + threadIdx.x);
 }
 
-// [n_ggsw][2][ell][2][N]: multiply by 1/N, negate the mask GLev (index 0)
-__global__ void ggsw_fold_kernel(u64 *ggsw, size_t total, u32 glev_words, u64 ninv) {
-    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x)
-        ggsw[i] = ggsw_fold_elem(ggsw[i], ninv, (u32)((i / glev_words) & 1));
-}
-
 __global__ void decompose_kernel(const u64 *in, u64 *out, size_t count, u32 logB, u32 L) {
     const bool centred = (L * logB == 64);
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < count * L; i += (size_t)gridDim.x * blockDim.x)
@@ -201,7 +195,7 @@ static int launch_br(lux_engine *e, const BRArgs &a, cudaStream_t s) {
 
 // batched NTT of n_polys device polynomials, out may alias in
 static int launch_ntt(lux_engine *e, const u64 *d_in, u64 *d_out, size_t n_polys, bool inverse, u64 scale, cudaStream_t s) {
-    NttArgs a{d_in, d_out, inverse ? e->d_tw_inv : e->d_tw_fwd, scale, (u32)n_polys, inverse ? 1u : 0u};
+    NttArgs a{d_in, d_out, e->d_tw_fwd, scale, (u32)n_polys, inverse ? 1u : 0u};
     switch (e->logN) {
         case 9: return lux_launch_ntt_9(e, a, s);
         case 10: return lux_launch_ntt_10(e, a, s);
@@ -243,7 +237,6 @@ static BRArgs make_br_args(const lux_engine *e, const u64 *d_lwe, const u64 *d_t
     a.lut_div = 1;
     a.out = d_out;
     a.tw_fwd = e->d_tw_fwd;
-    a.tw_inv = e->d_tw_inv;
     return a;
 }
 
@@ -435,10 +428,14 @@ static int load_ggsw_array(lux_engine *e, u64 *d_dst, const u64 *src, size_t wor
         int rc = launch_ntt(e, d_dst, d_dst, words / e->p.N, false, 1, e->stream);  // crypto/mod.rs:41-44
         if (rc) return rc;
     }
-    const u32 glev_words = e->p.ell * 2 * e->p.N;
-    ggsw_fold_kernel<<<e->sm_count * 4, 256, 0, e->stream>>>(d_dst, words, glev_words, e->ninv);
-    e->launches++;
-    CUDA_TRY(e, cudaGetLastError());
+    int rc = LUX_ERR_INVALID;   // reference NTT order -> resident key rows (fold 1/N and sign, lane-contiguous layout)
+    switch (e->logN) {
+        case 9: rc = lux_launch_keyfmt_9(e, d_dst, words / e->p.N, e->stream); break;
+        case 10: rc = lux_launch_keyfmt_10(e, d_dst, words / e->p.N, e->stream); break;
+        case 11: rc = lux_launch_keyfmt_11(e, d_dst, words / e->p.N, e->stream); break;
+        case 12: rc = lux_launch_keyfmt_12(e, d_dst, words / e->p.N, e->stream); break;
+    }
+    if (rc) return rc;
     CUDA_TRY(e, cudaStreamSynchronize(e->stream));
     return LUX_OK;
 }

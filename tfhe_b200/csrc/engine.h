@@ -69,7 +69,8 @@ extern "C" int lux_debug_field_probe(lux_engine *e, const uint64_t *a, const uin
     int lux_launch_br_##LN(lux_engine *e, const BRArgs &a, cudaStream_t s);                         \
     int lux_launch_ntt_##LN(lux_engine *e, const NttArgs &a, cudaStream_t s);                       \
     size_t lux_br_wave_##LN(const lux_engine *e, size_t B);                                         \
-    int lux_launch_xp_##LN(lux_engine *e, const BRArgs &a, const u64 *d_glwe, size_t stride, cudaStream_t s);
+    int lux_launch_xp_##LN(lux_engine *e, const BRArgs &a, const u64 *d_glwe, size_t stride, cudaStream_t s); \
+    int lux_launch_keyfmt_##LN(lux_engine *e, u64 *d_polys, size_t n_polys, cudaStream_t s);
 LUX_DECL_LAUNCHERS(9)
 LUX_DECL_LAUNCHERS(10)
 LUX_DECL_LAUNCHERS(11)

@@ -48,16 +48,21 @@ GL_HD void gl_mul_wide(u64 a, u64 b, u64 &lo, u64 &hi) {
 // added back and cannot wrap again because a + b - 2^64 < q.
 GL_HD u64 gl_add(u64 a, u64 b) {
 #if GL_PTX
-    u32 lo, hi, c;
-    asm("add.cc.u32 %0, %3, %5;\n\t"
-        "addc.cc.u32 %1, %4, %6;\n\t"
-        "addc.u32 %2, 0, 0;"
-        : "=r"(lo), "=r"(hi), "=r"(c)
+    // c = carry; s += c * eps  ==  s - c + (c << 32)   (mod 2^64; cannot wrap as a whole, see above)
+    // (the carry of an add chain must not be fed to subc: ptxas keeps borrows inverted)
+    u32 lo, hi;
+    asm("{\n\t"
+        ".reg .u32 c;\n\t"
+        "add.cc.u32 %0, %2, %4;\n\t"
+        "addc.cc.u32 %1, %3, %5;\n\t"
+        "addc.u32 c, 0, 0;\n\t"
+        "sub.cc.u32 %0, %0, c;\n\t"
+        "subc.u32 %1, %1, 0;\n\t"
+        "add.u32 %1, %1, c;\n\t"
+        "}"
+        : "=&r"(lo), "=&r"(hi)
         : "r"((u32)a), "r"((u32)(a >> 32)), "r"((u32)b), "r"((u32)(b >> 32)));
-    // s += c * eps  (one IMAD.WIDE on the fma pipe; cannot overflow)
-    u64 s = ((u64)hi << 32) | lo;
-    asm("mad.wide.u32 %0, %1, 0xFFFFFFFF, %0;" : "+l"(s) : "r"(c));
-    return s;
+    return ((u64)hi << 32) | lo;
 #else
     u64 s = a + b;
     return s + ((s < a) ? GL_EPS : 0);
@@ -89,31 +94,49 @@ GL_HD u64 gl_sub(u64 a, u64 b) {
 }
 
 // lazy -> canonical
-GL_HD u64 gl_canon(u64 a) { return a >= GL_Q ? a - GL_Q : a; }
+GL_HD u64 gl_canon(u64 a) {
+#if GL_PTX
+    // a >= q  <=>  high word all ones and low word non-zero; then a - q = (low - 1, 0)
+    u32 lo = (u32)a, hi = (u32)(a >> 32);
+    const bool p = (hi == 0xFFFFFFFFu) && (lo != 0);
+    if (p) {
+        lo -= 1;
+        hi = 0;
+    }
+    return ((u64)hi << 32) | lo;
+#else
+    return a >= GL_Q ? a - GL_Q : a;
+#endif
+}
 
 // canonical -> canonical
 GL_HD u64 gl_neg(u64 a) { return a ? GL_Q - a : 0; }
 
 // 128-bit (lo,hi) -> lazy.   x = lo + hl*2^64 + hh*2^96 == lo + hl*eps - hh  (mod q)
 GL_HD u64 gl_reduce128(u64 lo, u64 hi) {
-    u64 hh = hi >> 32, hl = hi & GL_EPS;
 #if GL_PTX
-    u32 l0, l1;
+    // t = lo + hl*eps (carry -> += eps, cannot carry again: t <= 2^64 - 2^33 then), then t -= hh
+    // (borrow -> -= eps, cannot borrow again: t > 2^64 - 2^32 then).  Corrections as in gl_add / gl_sub.
+    u32 t0, t1;
     asm("{\n\t"
         ".reg .u32 m;\n\t"
-        "sub.cc.u32 %0, %2, %4;\n\t"
-        "subc.cc.u32 %1, %3, 0;\n\t"
+        "mad.lo.cc.u32 %0, %2, 0xFFFFFFFF, %3;\n\t"
+        "madc.hi.cc.u32 %1, %2, 0xFFFFFFFF, %4;\n\t"
+        "addc.u32 m, 0, 0;\n\t"
+        "sub.cc.u32 %0, %0, m;\n\t"
+        "subc.u32 %1, %1, 0;\n\t"
+        "add.u32 %1, %1, m;\n\t"
+        "sub.cc.u32 %0, %0, %5;\n\t"
+        "subc.cc.u32 %1, %1, 0;\n\t"
         "subc.u32 m, 0, 0;\n\t"
         "sub.cc.u32 %0, %0, m;\n\t"
         "subc.u32 %1, %1, 0;\n\t"
         "}"
-        : "=&r"(l0), "=&r"(l1)
-        : "r"((u32)lo), "r"((u32)(lo >> 32)), "r"((u32)hh));
-    u64 t0 = ((u64)l1 << 32) | l0;
-    u64 t1;
-    asm("mul.wide.u32 %0, %1, 0xFFFFFFFF;" : "=l"(t1) : "r"((u32)hl));
-    return gl_add(t0, t1);  // t1 <= (2^32-1)^2 < q
+        : "=&r"(t0), "=&r"(t1)
+        : "r"((u32)hi), "r"((u32)lo), "r"((u32)(lo >> 32)), "r"((u32)(hi >> 32)));
+    return ((u64)t1 << 32) | t0;
 #else
+    u64 hh = hi >> 32, hl = hi & GL_EPS;
     u64 t0 = lo - hh;
     if (lo < hh) t0 -= GL_EPS;
     u64 t1 = hl * GL_EPS;
@@ -142,6 +165,15 @@ GL_HD void gl_gs_butterfly(u64 &u, u64 &v, u64 w) {
     u64 vc = gl_canon(v);
     u64 d = gl_sub(u, vc);
     u = gl_add(u, vc);
+    v = gl_mul_lazy(d, w);
+}
+
+// Inverse butterfly against the FORWARD table: INVROOTS[m+i] = -ROOTS[2m-1-i] (see tile_stage), so
+// (u, v) -> (u + v, (u - v) * w_inv) = (u + v, (v - u) * w) with w = ROOTS[2m-1-i].  lazy in, lazy out.
+GL_HD void gl_gs_butterfly_neg(u64 &u, u64 &v, u64 w) {
+    u64 uc = gl_canon(u);
+    u64 d = gl_sub(v, uc);
+    u = gl_add(v, uc);
     v = gl_mul_lazy(d, w);
 }
 

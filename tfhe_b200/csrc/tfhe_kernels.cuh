@@ -11,9 +11,9 @@
 //                                                       crypto/glwe.rs:96-113, lwe.rs:28-34)
 //   * batched LWE key switch                           (vtfhe/mod.rs:31-54, lev_ct.rs:63-76)
 //
-// A "team" of T = N/16 threads owns one ciphertext; TEAMS teams share a CTA (and its twiddle
-// tables).  Teams synchronise with named barriers only, so they drift freely against each
-// other and hide each other's barrier and memory latency.
+// A "team" of T = N/16 threads owns one ciphertext; TEAMS teams share a CTA, its twiddle table and
+// the staged bootstrap-key stream.  Teams synchronise internally with named barriers and with each
+// other only through the key stream's mbarriers (at most NSTAGE row pairs apart).
 //
 // The file also compiles as host C++ (-DTFHE_EMU): tests/emu runs the same bodies on host
 // threads so that all index arithmetic is checked on the CPU box.
@@ -64,18 +64,22 @@ template <int LOGN> GL_HD int posB(int tau, int e) {
 }
 template <int LOGN> GL_HD int posC(int tau, int e) { return 16 * tau + e; }
 
-// one radix-2 stage over the 16 registers; blocks of 2^SH registers, twiddle tw[block]
+// one radix-2 stage over the 16 registers; blocks of 2^SH registers.  Block `blk` of the stage uses the
+// reference's twiddle ROOTS[m + i0 + blk] (forward) or INVROOTS[m + i0 + blk] (inverse).  Only ROOTS is
+// kept on chip: INVROOTS[m + i] = psi^-bitrev(m+i) = -psi^(N - bitrev(m+i)) = -ROOTS[2m - 1 - i], and the
+// sign is absorbed by the inverse butterfly (u, v) -> (u + v, (v - u) * ROOTS[2m-1-i]).
 template <int SH, bool INV>
-TK_DEV void tile_stage(u64 (&x)[16], const u64 *tw) {
+TK_DEV void tile_stage(u64 (&x)[16], const u64 *tw, int m, int i0) {
     constexpr int half = 1 << (SH - 1);
+    const u64 *p = INV ? tw + 2 * m - 1 - i0 : tw + m + i0;
     TK_UNROLL
     for (int blk = 0; blk < (16 >> SH); blk++) {
-        const u64 w = tw[blk];
+        const u64 w = INV ? p[-blk] : p[blk];
         TK_UNROLL
         for (int j = 0; j < half; j++) {
             const int e0 = (blk << SH) + j;
             if (INV)
-                gl_gs_butterfly(x[e0], x[e0 + half], w);
+                gl_gs_butterfly_neg(x[e0], x[e0 + half], w);
             else
                 gl_ct_butterfly(x[e0], x[e0 + half], w);
         }
@@ -86,17 +90,17 @@ TK_DEV void tile_stage(u64 (&x)[16], const u64 *tw) {
 template <int LOGN, bool INV>
 TK_DEV void tile_pass_low(u64 (&x)[16], const u64 *tw, int tau) {
     constexpr int S3 = Tile<LOGN>::S3;
-    // stage with blocks of 2^SH registers: s' = S3 - SH, twiddle base (256 << s') + (tau << (4 - SH))
+    // stage with blocks of 2^SH registers: s' = S3 - SH, m = 256 << s', first block (tau << (4 - SH))
     if constexpr (!INV) {
-        if constexpr (S3 >= 4) tile_stage<4, false>(x, tw + (256 << (S3 >= 4 ? S3 - 4 : 0)) + (tau << 0));
-        if constexpr (S3 >= 3) tile_stage<3, false>(x, tw + (256 << (S3 >= 3 ? S3 - 3 : 0)) + (tau << 1));
-        if constexpr (S3 >= 2) tile_stage<2, false>(x, tw + (256 << (S3 >= 2 ? S3 - 2 : 0)) + (tau << 2));
-        if constexpr (S3 >= 1) tile_stage<1, false>(x, tw + (256 << (S3 - 1)) + (tau << 3));
+        if constexpr (S3 >= 4) tile_stage<4, false>(x, tw, 256 << (S3 >= 4 ? S3 - 4 : 0), tau << 0);
+        if constexpr (S3 >= 3) tile_stage<3, false>(x, tw, 256 << (S3 >= 3 ? S3 - 3 : 0), tau << 1);
+        if constexpr (S3 >= 2) tile_stage<2, false>(x, tw, 256 << (S3 >= 2 ? S3 - 2 : 0), tau << 2);
+        if constexpr (S3 >= 1) tile_stage<1, false>(x, tw, 256 << (S3 - 1), tau << 3);
     } else {
-        if constexpr (S3 >= 1) tile_stage<1, true>(x, tw + (256 << (S3 - 1)) + (tau << 3));
-        if constexpr (S3 >= 2) tile_stage<2, true>(x, tw + (256 << (S3 >= 2 ? S3 - 2 : 0)) + (tau << 2));
-        if constexpr (S3 >= 3) tile_stage<3, true>(x, tw + (256 << (S3 >= 3 ? S3 - 3 : 0)) + (tau << 1));
-        if constexpr (S3 >= 4) tile_stage<4, true>(x, tw + (256 << (S3 >= 4 ? S3 - 4 : 0)) + (tau << 0));
+        if constexpr (S3 >= 1) tile_stage<1, true>(x, tw, 256 << (S3 - 1), tau << 3);
+        if constexpr (S3 >= 2) tile_stage<2, true>(x, tw, 256 << (S3 >= 2 ? S3 - 2 : 0), tau << 2);
+        if constexpr (S3 >= 3) tile_stage<3, true>(x, tw, 256 << (S3 >= 3 ? S3 - 3 : 0), tau << 1);
+        if constexpr (S3 >= 4) tile_stage<4, true>(x, tw, 256 << (S3 >= 4 ? S3 - 4 : 0), tau << 0);
     }
 }
 // middle pass: stages 4..7 in layout B (b = high 4 bits of the position)
@@ -104,69 +108,75 @@ template <int LOGN, bool INV>
 TK_DEV void tile_pass_mid(u64 (&x)[16], const u64 *tw, int tau) {
     const int b = tau >> Tile<LOGN>::LB;
     if (!INV) {
-        tile_stage<4, false>(x, tw + 16 + b);
-        tile_stage<3, false>(x, tw + 32 + 2 * b);
-        tile_stage<2, false>(x, tw + 64 + 4 * b);
-        tile_stage<1, false>(x, tw + 128 + 8 * b);
+        tile_stage<4, false>(x, tw, 16, b);
+        tile_stage<3, false>(x, tw, 32, 2 * b);
+        tile_stage<2, false>(x, tw, 64, 4 * b);
+        tile_stage<1, false>(x, tw, 128, 8 * b);
     } else {
-        tile_stage<1, true>(x, tw + 128 + 8 * b);
-        tile_stage<2, true>(x, tw + 64 + 4 * b);
-        tile_stage<3, true>(x, tw + 32 + 2 * b);
-        tile_stage<4, true>(x, tw + 16 + b);
+        tile_stage<1, true>(x, tw, 128, 8 * b);
+        tile_stage<2, true>(x, tw, 64, 4 * b);
+        tile_stage<3, true>(x, tw, 32, 2 * b);
+        tile_stage<4, true>(x, tw, 16, b);
     }
 }
 // first forward pass / last inverse pass: stages 0..3 in layout A (twiddles uniform over threads)
 template <bool INV>
 TK_DEV void tile_pass_high(u64 (&x)[16], const u64 *tw) {
     if (!INV) {
-        tile_stage<4, false>(x, tw + 1);
-        tile_stage<3, false>(x, tw + 2);
-        tile_stage<2, false>(x, tw + 4);
-        tile_stage<1, false>(x, tw + 8);
+        tile_stage<4, false>(x, tw, 1, 0);
+        tile_stage<3, false>(x, tw, 2, 0);
+        tile_stage<2, false>(x, tw, 4, 0);
+        tile_stage<1, false>(x, tw, 8, 0);
     } else {
-        tile_stage<1, true>(x, tw + 8);
-        tile_stage<2, true>(x, tw + 4);
-        tile_stage<3, true>(x, tw + 2);
-        tile_stage<4, true>(x, tw + 1);
+        tile_stage<1, true>(x, tw, 8, 0);
+        tile_stage<2, true>(x, tw, 4, 0);
+        tile_stage<3, true>(x, tw, 2, 0);
+        tile_stage<4, true>(x, tw, 1, 0);
     }
 }
 
+// The exchanges of one transform go through ONE buffer xb[N] per team: the second exchange writes
+// exactly the positions the same thread read in the first one, so only the first write needs a
+// barrier against the previous user of the buffer (the leading team_sync).
+//
 // forward NTT of one polynomial held by a team: in  x[e] = a[posA(tau,e)] (natural order)
 //                                               out x[e] = A[posC(tau,e)] (reference's bit-reversed order)
 template <int LOGN>
-TK_DEV void team_ntt_forward(u64 (&x)[16], u64 *xb0, u64 *xb1, const u64 *tw, int tau, int team) {
+TK_DEV void team_ntt_forward(u64 (&x)[16], u64 *xb, const u64 *tw, int tau, int team) {
     constexpr int T = Tile<LOGN>::T;
     tile_pass_high<false>(x, tw);
-    TK_UNROLL
-    for (int e = 0; e < 16; e++) xb0[tk_swz(posA<LOGN>(tau, e))] = x[e];
     team_sync(team, T);
     TK_UNROLL
-    for (int e = 0; e < 16; e++) x[e] = xb0[tk_swz(posB<LOGN>(tau, e))];
+    for (int e = 0; e < 16; e++) xb[tk_swz(posA<LOGN>(tau, e))] = x[e];
+    team_sync(team, T);
+    TK_UNROLL
+    for (int e = 0; e < 16; e++) x[e] = xb[tk_swz(posB<LOGN>(tau, e))];
     tile_pass_mid<LOGN, false>(x, tw, tau);
     TK_UNROLL
-    for (int e = 0; e < 16; e++) xb1[tk_swz(posB<LOGN>(tau, e))] = x[e];
+    for (int e = 0; e < 16; e++) xb[tk_swz(posB<LOGN>(tau, e))] = x[e];
     team_sync(team, T);
     TK_UNROLL
-    for (int e = 0; e < 16; e++) x[e] = xb1[tk_swz(posC<LOGN>(tau, e))];
+    for (int e = 0; e < 16; e++) x[e] = xb[tk_swz(posC<LOGN>(tau, e))];
     tile_pass_low<LOGN, false>(x, tw, tau);
 }
 
 // inverse NTT WITHOUT the final 1/N: in x[e] = A[posC(tau,e)], out x[e] = N*a[posA(tau,e)] (lazy)
 template <int LOGN>
-TK_DEV void team_ntt_inverse(u64 (&x)[16], u64 *xb0, u64 *xb1, const u64 *tw, int tau, int team) {
+TK_DEV void team_ntt_inverse(u64 (&x)[16], u64 *xb, const u64 *tw, int tau, int team) {
     constexpr int T = Tile<LOGN>::T;
     tile_pass_low<LOGN, true>(x, tw, tau);
-    TK_UNROLL
-    for (int e = 0; e < 16; e++) xb0[tk_swz(posC<LOGN>(tau, e))] = x[e];
     team_sync(team, T);
     TK_UNROLL
-    for (int e = 0; e < 16; e++) x[e] = xb0[tk_swz(posB<LOGN>(tau, e))];
+    for (int e = 0; e < 16; e++) xb[tk_swz(posC<LOGN>(tau, e))] = x[e];
+    team_sync(team, T);
+    TK_UNROLL
+    for (int e = 0; e < 16; e++) x[e] = xb[tk_swz(posB<LOGN>(tau, e))];
     tile_pass_mid<LOGN, true>(x, tw, tau);
     TK_UNROLL
-    for (int e = 0; e < 16; e++) xb1[tk_swz(posB<LOGN>(tau, e))] = x[e];
+    for (int e = 0; e < 16; e++) xb[tk_swz(posB<LOGN>(tau, e))] = x[e];
     team_sync(team, T);
     TK_UNROLL
-    for (int e = 0; e < 16; e++) x[e] = xb1[tk_swz(posA<LOGN>(tau, e))];
+    for (int e = 0; e < 16; e++) x[e] = xb[tk_swz(posA<LOGN>(tau, e))];
     tile_pass_high<true>(x, tw);
 }
 
@@ -174,7 +184,7 @@ TK_DEV void team_ntt_inverse(u64 (&x)[16], u64 *xb0, u64 *xb1, const u64 *tw, in
 struct NttArgs {
     const u64 *in;
     u64 *out;
-    const u64 *tw;   // ROOTS (forward) or INVROOTS (inverse), [N]
+    const u64 *tw;   // ROOTS [N] (both directions)
     u64 scale;       // every output multiplied by this (NINV for the reference's inverse; 1 = none)
     u32 n_polys;
     u32 inverse;
@@ -185,7 +195,7 @@ TK_DEV void ntt_batch_body(const NttArgs &a, int tid, int bid, int nblocks, unsi
     constexpr int N = Tile<LOGN>::N, T = Tile<LOGN>::T;
     u64 *tw = (u64 *)smem_raw;
     const int team = tid / T, tau = tid % T;
-    u64 *xb0 = tw + N + team * 2 * N, *xb1 = xb0 + N;
+    u64 *xb = tw + N + team * N;
     for (int i = tid; i < N; i += T * TEAMS) tw[i] = a.tw[i];
     cta_sync();
     // polynomials are dealt round-robin to teams; every team of a CTA runs the same trip count
@@ -198,7 +208,7 @@ TK_DEV void ntt_batch_body(const NttArgs &a, int tid, int bid, int nblocks, unsi
         if (!a.inverse) {
             TK_UNROLL
             for (int e = 0; e < 16; e++) x[e] = src[posA<LOGN>(tau, e)];
-            team_ntt_forward<LOGN>(x, xb0, xb1, tw, tau, team);
+            team_ntt_forward<LOGN>(x, xb, tw, tau, team);
             if (live) {
                 TK_UNROLL
                 for (int e = 0; e < 16; e++)
@@ -207,18 +217,24 @@ TK_DEV void ntt_batch_body(const NttArgs &a, int tid, int bid, int nblocks, unsi
         } else {
             TK_UNROLL
             for (int e = 0; e < 16; e++) x[e] = src[posC<LOGN>(tau, e)];
-            team_ntt_inverse<LOGN>(x, xb0, xb1, tw, tau, team);
+            team_ntt_inverse<LOGN>(x, xb, tw, tau, team);
             if (live) {
                 TK_UNROLL
                 for (int e = 0; e < 16; e++)
                     dst[posA<LOGN>(tau, e)] = (a.scale == 1) ? gl_canon(x[e]) : gl_mul(x[e], a.scale);
             }
         }
-        team_sync(team, T);  // exchange buffers are reused by the next polynomial
     }
 }
 
 // ------------------------------------------------------------------- external product / blind rotate
+// Resident key format.  A GGSW is 2*ell "row pairs" (one per input polynomial j and level lvl); a row
+// pair is [row to output poly 0 : N][row to output poly 1 : N], NTT domain (reference order), with 1/N
+// and the minus sign of the mask GLev folded in.  Inside a row the element multiplying register e of
+// thread tau sits at key_pos(tau, e), so that one 16-byte access per thread and register pair is
+// contiguous across the lanes of a warp (coalesced from L2, conflict-free from shared memory).
+template <int LOGN> GL_HD int key_pos(int tau, int e) { return (e >> 1) * (2 * Tile<LOGN>::T) + 2 * tau + (e & 1); }
+
 struct BRArgs {
     u32 n;         // CMUX iterations available = small LWE dimension
     u32 steps;     // iterations actually run (== n; fewer only for per-iteration parity tests)
@@ -227,7 +243,7 @@ struct BRArgs {
     u32 B;         // ciphertexts in the batch
     u32 out_mode;  // 0 = full sample extract [N+1]; 1 = partial extract [n_out+1]; 2 = raw accumulator [2N]
     u32 n_out;     // partial extract length
-    const u64 *bsk;     // [n][2][ell][2][N]  NTT domain, 1/N and the minus sign of the mask GLev folded in
+    const u64 *bsk;     // [n][2*ell row pairs][2][N]  resident key format
     const u64 *ksk;     // one GGSW in the same format, or nullptr          (ivc_based_vpbs.rs:355-371)
     const u64 *lwe;     // [B][n+1] ciphertexts under the small key
     const u64 *testv;   // [n_luts][N]
@@ -235,7 +251,6 @@ struct BRArgs {
     u32 lut_div;        // >= 1 (1 = one index per ciphertext; the radix layer uses one per slot of B ciphertexts)
     u64 *out;           // [B][out_len]
     const u64 *tw_fwd;  // ROOTS    [N]
-    const u64 *tw_inv;  // INVROOTS [N]
 };
 
 // coefficient p of X^sh * poly (negacyclic), poly canonical in shared memory   (vtfhe/mod.rs:80-107)
@@ -247,12 +262,75 @@ TK_DEV u64 rotated_coeff(const u64 *poly, int p, u32 sh) {
     return (i2 & N) ? gl_neg(v) : v;
 }
 
+// ---- the CTA-shared stream of key row pairs -------------------------------------------------------
+// All teams of a CTA consume the same sequence of row pairs (BSK_0 .. BSK_{steps-1}, then the GLWE key
+// switch key).  One elected thread streams them from L2/HBM into a ring of NSTAGE shared-memory stages
+// with bulk asynchronous copies (cp.async.bulk -> UBLKCP) that complete on an mbarrier; every warp
+// releases a stage through a second mbarrier once it has multiplied with it, so each key byte is fetched
+// once per CTA and reused by TEAMS ciphertexts.
+template <int LOGN> struct StageCfg { static constexpr int NSTAGE = (LOGN >= 12) ? 1 : 2; };
+
+struct KeyStream {
+    u64 *stage;        // [NSTAGE][2N] shared
+    u64 *full, *empty; // [NSTAGE] mbarriers, shared
+    const u64 *bsk, *ksk;
+    u32 bsk_pairs;     // row pairs coming from bsk; the rest come from ksk
+    u32 total;         // row pairs in the whole launch
+    u32 t;             // next row pair this thread consumes
+    bool producer;
+};
+
+#if !defined(TFHE_EMU)
+__device__ __forceinline__ u32 tk_smem_addr(const void *p) { return (u32)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(u64 *bar, u32 count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(tk_smem_addr(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(u64 *bar, u32 parity) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "TK_WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra TK_DONE_%=;\n\t"
+        "bra TK_WAIT_%=;\n\t"
+        "TK_DONE_%=:\n\t"
+        "}" ::"r"(tk_smem_addr(bar)), "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(u64 *bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(tk_smem_addr(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(u64 *bar, u32 bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(tk_smem_addr(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, u32 bytes, u64 *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(tk_smem_addr(dst)),
+                 "l"(src), "r"(bytes), "r"(tk_smem_addr(bar))
+                 : "memory");
+}
+
+template <int LOGN>
+__device__ __forceinline__ void stream_issue(const KeyStream &ks, u32 t) {
+    constexpr int N = 1 << LOGN, NS = StageCfg<LOGN>::NSTAGE;
+    if (t >= ks.total) return;
+    const u64 *src = (t < ks.bsk_pairs) ? ks.bsk + (size_t)t * 2 * N : ks.ksk + (size_t)(t - ks.bsk_pairs) * 2 * N;
+    u64 *dst = ks.stage + (size_t)(t % NS) * 2 * N;
+    u64 *bar = ks.full + (t % NS);
+    constexpr u32 bytes = 2 * N * sizeof(u64), chunk = bytes / 2;
+    mbar_expect_tx(bar, bytes);
+    bulk_g2s(dst, src, chunk, bar);
+    bulk_g2s((unsigned char *)dst + chunk, (const unsigned char *)src + chunk, chunk, bar);
+}
+#endif
+
 // One GGSW (x) GLWE on the team's accumulator (k = 1).
-//   CMUX = true : acc <- acc + GGSW (x) (X^sh * acc - acc)            (vtfhe/mod.rs:119-136)
-//   CMUX = false: acc <- GGSW (x) acc                                  (ivc_based_vpbs.rs:116-121)
-template <int LOGN, bool CMUX>
-TK_DEV void team_external_product(const BRArgs &a, const u64 *ggsw, u32 sh, u64 *acc, u64 *xb0, u64 *xb1,
-                                  const u64 *tw_f, const u64 *tw_i, int tau, int team) {
+//   cmux = true : acc <- acc + GGSW (x) (X^sh * acc - acc)            (vtfhe/mod.rs:119-136)
+//   cmux = false: acc <- GGSW (x) acc                                  (ivc_based_vpbs.rs:116-121)
+// STAGED: the GGSW's row pairs are the next 2*ell entries of the CTA-shared key stream; otherwise they
+// are read from `ggsw` in global memory (independent keys per ciphertext: external_product_kernel, emulator).
+template <int LOGN, bool STAGED>
+TK_DEV void team_external_product(const BRArgs &a, const u64 *ggsw, KeyStream &ks, bool cmux, u32 sh, u64 *acc, u64 *xb,
+                                  const u64 *tw, int tau, int team, int lane) {
     constexpr int N = Tile<LOGN>::N, T = Tile<LOGN>::T;
     const bool centred = (a.L * a.logB == 64);
     u64 o0[16], o1[16];
@@ -267,54 +345,113 @@ TK_DEV void team_external_product(const BRArgs &a, const u64 *ggsw, u32 sh, u64 
             for (int e = 0; e < 16; e++) {
                 const int p = posA<LOGN>(tau, e);
                 u64 d = poly[p];
-                if (CMUX) d = gl_canon(gl_sub(rotated_coeff<LOGN>(poly, p, sh), d));
+                if (cmux) d = gl_canon(gl_sub(rotated_coeff<LOGN>(poly, p, sh), d));
                 x[e] = gl_digit(d, a.L - a.ell + lvl, a.logB, centred);   // glev_ct.rs:97-99: top ell limbs
             }
-            team_ntt_forward<LOGN>(x, xb0, xb1, tw_f, tau, team);
-            const u64 *row0 = ggsw + ((size_t)(j * a.ell + lvl) * 2) * N + 16 * tau;
-            const u64 *row1 = row0 + N;
+            team_ntt_forward<LOGN>(x, xb, tw, tau, team);
+            const u64 *rows;
+#if !defined(TFHE_EMU)
+            constexpr int NS = StageCfg<LOGN>::NSTAGE;
+            if (STAGED) {
+                mbar_wait(ks.full + (ks.t % NS), (ks.t / NS) & 1);
+                rows = ks.stage + (size_t)(ks.t % NS) * 2 * N;
+            } else
+#endif
+                rows = ggsw + ((size_t)(j * a.ell + lvl) * 2) * N;
             TK_UNROLL
-            for (int e = 0; e < 16; e++) {
-                o0[e] = gl_add(o0[e], gl_mul(x[e], row0[e]));
-                o1[e] = gl_add(o1[e], gl_mul(x[e], row1[e]));
+            for (int h = 0; h < 8; h++) {
+                // elements key_pos(tau, 2h), key_pos(tau, 2h+1) of both rows: one 16-byte access each
+                const u64 *r0 = rows + (size_t)h * 2 * T + 2 * tau;
+                const u64 *r1 = r0 + N;
+#if !defined(TFHE_EMU)
+                const ulonglong2 v0 = *reinterpret_cast<const ulonglong2 *>(r0);
+                const ulonglong2 v1 = *reinterpret_cast<const ulonglong2 *>(r1);
+                const u64 a0 = v0.x, a1 = v0.y, b0 = v1.x, b1 = v1.y;
+#else
+                const u64 a0 = r0[0], a1 = r0[1], b0 = r1[0], b1 = r1[1];
+#endif
+                o0[2 * h] = gl_add(o0[2 * h], gl_mul(x[2 * h], a0));
+                o0[2 * h + 1] = gl_add(o0[2 * h + 1], gl_mul(x[2 * h + 1], a1));
+                o1[2 * h] = gl_add(o1[2 * h], gl_mul(x[2 * h], b0));
+                o1[2 * h + 1] = gl_add(o1[2 * h + 1], gl_mul(x[2 * h + 1], b1));
             }
+#if !defined(TFHE_EMU)
+            if (STAGED) {
+                // release the stage (one arrival per warp), then the producer refills the stage that was
+                // released one step earlier with the row pair NSTAGE steps ahead of it
+                __syncwarp();
+                if (lane == 0) mbar_arrive(ks.empty + (ks.t % NS));
+                if (ks.producer && ks.t + 1 >= (u32)NS) {
+                    const u32 r = ks.t + 1 - NS;
+                    mbar_wait(ks.empty + (r % NS), (r / NS) & 1);
+                    stream_issue<LOGN>(ks, r + NS);
+                }
+                ks.t++;
+            }
+#endif
         }
     }
-    team_ntt_inverse<LOGN>(o0, xb0, xb1, tw_i, tau, team);
-    TK_UNROLL
-    for (int e = 0; e < 16; e++) {
-        const int p = posA<LOGN>(tau, e);
-        acc[p] = CMUX ? gl_canon(gl_add(o0[e], acc[p])) : gl_canon(o0[e]);
-    }
-    team_ntt_inverse<LOGN>(o1, xb0, xb1, tw_i, tau, team);
-    TK_UNROLL
-    for (int e = 0; e < 16; e++) {
-        const int p = N + posA<LOGN>(tau, e);
-        acc[p] = CMUX ? gl_canon(gl_add(o1[e], acc[p])) : gl_canon(o1[e]);
+    // both output polynomials go through ONE inverse-NTT body (the instruction footprint of the loop is
+    // what the three teams of an SM fetch over and over)
+#if !defined(TFHE_EMU)
+#pragma unroll 1
+#endif
+    for (int r = 0; r < 2; r++) {
+        team_ntt_inverse<LOGN>(o0, xb, tw, tau, team);
+        TK_UNROLL
+        for (int e = 0; e < 16; e++) {
+            const int p = r * N + posA<LOGN>(tau, e);
+            acc[p] = cmux ? gl_canon(gl_add(o0[e], acc[p])) : gl_canon(o0[e]);
+            o0[e] = o1[e];
+        }
     }
     team_sync(team, T);  // next iteration gathers rotated coefficients written by other threads
 }
 
-// shared memory: [tw_fwd N][tw_inv N] then per team [acc 2N][xb0 N][xb1 N]   (u64 each)
+// shared memory: [tw N] then per team [acc 2N][xb N], then the key ring [NSTAGE][2N] and its mbarriers
 template <int LOGN, int TEAMS>
 constexpr size_t blind_rotate_smem_bytes() {
-    return sizeof(u64) * ((size_t)2 * Tile<LOGN>::N + (size_t)TEAMS * 4 * Tile<LOGN>::N);
+    return sizeof(u64) * ((size_t)Tile<LOGN>::N + (size_t)TEAMS * 3 * Tile<LOGN>::N + (size_t)StageCfg<LOGN>::NSTAGE * 2 * Tile<LOGN>::N) + 64;
 }
 
 template <int LOGN, int TEAMS>
 TK_DEV void blind_rotate_body(const BRArgs &a, int tid, int bid, unsigned char *smem_raw) {
-    constexpr int N = Tile<LOGN>::N, T = Tile<LOGN>::T;
-    u64 *tw_f = (u64 *)smem_raw, *tw_i = tw_f + N;
-    const int team = tid / T, tau = tid % T;
-    u64 *acc = tw_i + N + (size_t)team * 4 * N;
-    u64 *xb0 = acc + 2 * N, *xb1 = xb0 + N;
-    for (int i = tid; i < N; i += T * TEAMS) {
-        tw_f[i] = a.tw_fwd[i];
-        tw_i[i] = a.tw_inv[i];
+    constexpr int N = Tile<LOGN>::N, T = Tile<LOGN>::T, NS = StageCfg<LOGN>::NSTAGE;
+    u64 *tw = (u64 *)smem_raw;
+    const int team = tid / T, tau = tid % T, lane = tid & 31;
+    u64 *acc = tw + N + (size_t)team * 3 * N;
+    u64 *xb = acc + 2 * N;
+    KeyStream ks{};
+    ks.stage = tw + N + (size_t)TEAMS * 3 * N;
+    ks.full = ks.stage + (size_t)NS * 2 * N;
+    ks.empty = ks.full + NS;
+    ks.bsk = a.bsk;
+    ks.ksk = a.ksk;
+    ks.bsk_pairs = a.steps * 2 * a.ell;
+    ks.total = ks.bsk_pairs + (a.ksk ? 2 * a.ell : 0);
+    ks.t = 0;
+    ks.producer = (tid == 0);
+    for (int i = tid; i < N; i += T * TEAMS) tw[i] = a.tw_fwd[i];
+#if !defined(TFHE_EMU)
+    {
+        const u32 left = a.B - (u32)bid * TEAMS;
+        const u32 live_teams = left < (u32)TEAMS ? left : (u32)TEAMS;
+        if (tid == 0) {
+            for (int s = 0; s < NS; s++) {
+                mbar_init(ks.full + s, 1);
+                mbar_init(ks.empty + s, live_teams * (T / 32));
+            }
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
     }
+#endif
     cta_sync();
     const u32 ct = (u32)bid * TEAMS + team;
-    if (ct >= a.B) return;  // whole team leaves; only team barriers are used from here on
+    if (ct >= a.B) return;  // whole team leaves; only team barriers and the key-stream mbarriers are used from here on
+#if !defined(TFHE_EMU)
+    if (ks.producer)
+        for (u32 t = 0; t < (u32)NS; t++) stream_issue<LOGN>(ks, t);
+#endif
 
     const u64 *lwe = a.lwe + (size_t)ct * (a.n + 1);
     const u64 *tv = a.testv + (size_t)(a.lut_idx ? a.lut_idx[ct / a.lut_div] : 0) * N;
@@ -331,14 +468,17 @@ TK_DEV void blind_rotate_body(const BRArgs &a, int tid, int bid, unsigned char *
     }
     team_sync(team, T);
 
+    // steps CMUX iterations, then (in-tree order) the GLWE key switch as one more external product: one
+    // call site, so the loop body exists once in the instruction stream
     const size_t ggsw_len = (size_t)4 * a.ell * N;
-    u64 mask = lwe[0];
-    for (u32 i = 0; i < a.steps; i++) {
-        const u32 sh = gl_mod_switch(mask, LOGN);
+    const u32 iters = a.steps + (a.ksk ? 1u : 0u);
+    u64 mask = a.steps ? lwe[0] : 0;
+    for (u32 i = 0; i < iters; i++) {
+        const bool cmux = i < a.steps;
+        const u32 sh = cmux ? gl_mod_switch(mask, LOGN) : 0;
         if (i + 1 < a.steps) mask = lwe[i + 1];  // fetched one iteration ahead
-        team_external_product<LOGN, true>(a, a.bsk + i * ggsw_len, sh, acc, xb0, xb1, tw_f, tw_i, tau, team);
+        team_external_product<LOGN, true>(a, cmux ? a.bsk + i * ggsw_len : a.ksk, ks, cmux, sh, acc, xb, tw, tau, team, lane);
     }
-    if (a.ksk) team_external_product<LOGN, false>(a, a.ksk, 0, acc, xb0, xb1, tw_f, tw_i, tau, team);
 
     // exit: sample extraction of coefficient 0      crypto/glwe.rs:96-113
     if (a.out_mode == 2) {
@@ -450,4 +590,15 @@ TK_DEV void ksk_colsum_body(const u64 *ksk, u64 *ksum, u32 rows, u32 cols, u32 c
 TK_DEV u64 ggsw_fold_elem(u64 v, u64 ninv, u32 glev_index /* 0 = mask, 1 = body */) {
     const u64 s = gl_mul(v, ninv);
     return glev_index == 0 ? gl_neg(s) : s;
+}
+
+// reference-order NTT-domain polynomial (element of thread tau, register e at posC = 16*tau + e) -> resident
+// key row: fold 1/N and sign, move to key_pos(tau, e).  `x` holds the thread's 16 elements.
+template <int LOGN>
+TK_DEV void ggsw_row_to_key_format(const u64 *src, u64 *dst, int tau, u64 ninv, u32 glev_index) {
+    u64 x[16];
+    TK_UNROLL
+    for (int e = 0; e < 16; e++) x[e] = src[posC<LOGN>(tau, e)];
+    TK_UNROLL
+    for (int e = 0; e < 16; e++) dst[key_pos<LOGN>(tau, e)] = ggsw_fold_elem(x[e], ninv, glev_index);
 }
