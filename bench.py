@@ -199,6 +199,8 @@ def run_ours(args):
     params = T.S2_SHORTINT
     B = args.batch
     eng = T.Engine(params, device=local)
+    if args.teams:
+        eng.force_teams(args.teams)      # tuning knob: ciphertexts per CTA in the blind-rotate launch
 
     # ---- evaluation keys: rank 0 converts to the NTT domain on its GPU, NCCL-broadcasts the device blob
     O = ctx = ks = None
@@ -283,6 +285,21 @@ def run_ours(args):
     h2d = h_in.numel() * 8 + h_tv.numel() * 8 + h_idx.numel() * 4
     d2h = h_out.numel() * 8
 
+    # ---- single-PBS latency (BASELINE metric's second half): one ciphertext, device-resident, CUDA events
+    lat_ms = None
+    if rank == 0:
+        la, lb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        d_one = torch.empty_like(d_in[:1])
+        lats = []
+        for i in range(6):
+            la.record(stream)
+            eng.pbs_batch_device(d_in[:1], d_tv, d_idx[:1], 1, d_one, n_luts=4, stream=sptr)
+            lb.record(stream)
+            lb.synchronize()
+            if i:
+                lats.append(la.elapsed_time(lb))
+        lat_ms = statistics.median(lats)
+
     if rank != 0:
         if world > 1:
             dist.barrier()
@@ -323,7 +340,12 @@ def run_ours(args):
                     "imad_wide_per_s": imad, "iadd_per_s": iadd, "modmul_per_pbs": w["br_modmul"]}
 
     # ---- CPU baseline on a bounded sample
-    cpu_v, cores, nb, dt = cpu_pbs_rate(O, ctx, cts, tvs, idx)
+    cpu_v, cores, nb, dt = (0.0, 0, 0, 0.0) if args.no_cpu else cpu_pbs_rate(O, ctx, cts, tvs, idx)
+    cpu_lat_ms = None
+    if not args.no_cpu:
+        t0 = time.perf_counter()
+        ctx.pbs_batch(cts[:1], tvs, idx[:1])
+        cpu_lat_ms = (time.perf_counter() - t0) * 1e3
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -336,6 +358,7 @@ def run_ours(args):
         "roofline": roofline, "roofline_int": roofline_int,
         "cpu_baseline": {"value": cpu_v, "unit": UNIT, "cores": cores, "kind": "port",
                          "sample": f"{nb} PBS of the same batch in {dt:.1f} s, oracle C port, OpenMP over ciphertexts"},
+        "latency_single_pbs_ms": {"gpu": lat_ms, "cpu_1_thread": cpu_lat_ms},
         "clocks": clocks,
         "parity": f"first {ncheck} outputs bit-exact vs oracle; {len(msgs)} decryptions correct",
     }
@@ -350,8 +373,11 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--batch", type=int, default=4096, help="ciphertexts per GPU per step")
+    ap.add_argument("--batch", type=int, default=4440,
+                    help="ciphertexts per GPU per step (default: 10 full waves of 148 SMs x 3 resident ciphertexts)")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--teams", type=int, default=0, help="force ciphertexts per CTA (tuning)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg (tuning sweeps)")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         log("note: timing rules want >= 3 warm-up steps")
