@@ -226,8 +226,12 @@ def run_ours(args):
     d_in, d_tv, d_idx = h_in.cuda(), h_tv.cuda(), h_idx.cuda()
     d_out = torch.empty_like(d_in)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")   # > 126 MB L2
-    stream = torch.cuda.current_stream()
+    # one explicit (non-default) stream for every launch and every event of this process: handle 0 would
+    # select the engine's own non-blocking stream, which events recorded on torch's default stream do not see
+    stream = torch.cuda.Stream()
+    torch.cuda.set_stream(stream)
     sptr = stream.cuda_stream
+    assert sptr != 0
 
     def barrier():
         if world > 1:
@@ -299,6 +303,8 @@ def run_ours(args):
             if i:
                 lats.append(la.elapsed_time(lb))
         lat_ms = statistics.median(lats)
+        torch.cuda.synchronize()
+        assert torch.equal(d_one[0], d_out[0]), "single-ciphertext launch disagrees with the batched launch"
 
     if rank != 0:
         if world > 1:

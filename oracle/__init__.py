@@ -99,6 +99,8 @@ def lib():
         "orc_lwe_encrypt": (None, [C.POINTER(OrcRng), u32, _u64p, u64, dbl, _u64p]),
         "orc_lwe_decrypt": (u64, [u32, _u64p, _u64p]),
         "orc_decode": (u64, [u64, u64, u32]),
+        "orc_lwe_encrypt_batch": (None, [u64, u32, _u64p, C.c_size_t, _u64p, dbl, _u64p]),
+        "orc_lwe_decrypt_batch": (None, [u32, _u64p, C.c_size_t, _u64p, _u64p]),
         "orc_glwe_encrypt": (None, [vp, C.POINTER(OrcRng), _u64p, _u64p, dbl, _u64p]),
         "orc_glwe_decrypt": (None, [vp, _u64p, _u64p, _u64p]),
         "orc_ggsw_encrypt": (None, [vp, C.POINTER(OrcRng), _u64p, _u64p, dbl, _u64p]),
@@ -373,6 +375,22 @@ def lwe_encrypt(rng: Rng, s, m: int, sigma=0.0):
 def lwe_decrypt(s, ct) -> int:
     s = u64(s)
     return lib().orc_lwe_decrypt(len(s), s, u64(ct))
+
+
+def lwe_encrypt_batch(seed: int, s, msgs, sigma=0.0) -> np.ndarray:
+    """[B][n+1] encryptions of the field elements `msgs` (already scaled by delta), OpenMP over ciphertexts"""
+    s, msgs = u64(s), u64(msgs)
+    cts = np.zeros((len(msgs), len(s) + 1), np.uint64)
+    lib().orc_lwe_encrypt_batch(seed, len(s), s, len(msgs), msgs, sigma, cts.reshape(-1))
+    return cts
+
+
+def lwe_decrypt_batch(s, cts) -> np.ndarray:
+    """noisy plaintexts (field elements) of [B][n+1] ciphertexts"""
+    s, cts = u64(s), u64(cts)
+    out = np.zeros(cts.shape[0], np.uint64)
+    lib().orc_lwe_decrypt_batch(len(s), s, cts.shape[0], cts.reshape(-1), out)
+    return out
 
 
 def decode(noisy: int, delta: int, space: int) -> int:

@@ -529,6 +529,22 @@ uint64_t orc_lwe_decrypt(uint32_t n, const uint64_t *s, const uint64_t *ct) {
     for (uint32_t i = 0; i < n; i++) ip = gl_add(ip, gl_mul(s[i], ct[i]));
     return gl_sub(ct[n], ip);
 }
+/* batched forms of the two functions above (test infrastructure for the >= 10^6-trial decryption gate,
+ * SURVEY 8d): ciphertext b is lwe.rs:50-59 under its own generator seeded with seed + b */
+void orc_lwe_encrypt_batch(uint64_t seed, uint32_t n, const uint64_t *s, size_t B, const uint64_t *msgs, double sigma,
+                           uint64_t *cts) {
+#pragma omp parallel for schedule(static)
+    for (long b = 0; b < (long)B; b++) {
+        orc_rng r;
+        orc_rng_seed(&r, seed + (uint64_t)b);
+        orc_lwe_encrypt(&r, n, s, msgs[b], sigma, cts + (size_t)b * (n + 1));
+    }
+}
+void orc_lwe_decrypt_batch(uint32_t n, const uint64_t *s, size_t B, const uint64_t *cts, uint64_t *noisy) {
+#pragma omp parallel for schedule(static)
+    for (long b = 0; b < (long)B; b++) noisy[b] = orc_lwe_decrypt(n, s, cts + (size_t)b * (n + 1));
+}
+
 /* main.rs:61-64: round(noisy/delta) mod plaintext_space (integer rounding instead of f64) */
 uint64_t orc_decode(uint64_t noisy, uint64_t delta, uint32_t plaintext_space) {
     u128 v = (u128)noisy + delta / 2;

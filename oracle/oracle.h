@@ -131,6 +131,9 @@ void orc_glwe_keygen(orc_rng *r, uint32_t N, uint32_t k, uint64_t *s);          
 void orc_glwe_partial_key(orc_rng *r, uint32_t N, uint32_t k, uint32_t nz, uint64_t *s);       /* glwe.rs:19-38 */
 void orc_lwe_encrypt(orc_rng *r, uint32_t n, const uint64_t *s, uint64_t m, double sigma, uint64_t *ct); /* lwe.rs:50-59 */
 uint64_t orc_lwe_decrypt(uint32_t n, const uint64_t *s, const uint64_t *ct);                   /* lwe.rs:62-69 */
+void orc_lwe_encrypt_batch(uint64_t seed, uint32_t n, const uint64_t *s, size_t B, const uint64_t *msgs, double sigma,
+                           uint64_t *cts);                                                        /* B x lwe.rs:50-59 */
+void orc_lwe_decrypt_batch(uint32_t n, const uint64_t *s, size_t B, const uint64_t *cts, uint64_t *noisy); /* B x :62-69 */
 uint64_t orc_decode(uint64_t noisy, uint64_t delta, uint32_t plaintext_space);                 /* main.rs:61-64 */
 void orc_glwe_encrypt(const orc_ctx *c, orc_rng *r, const uint64_t *s, const uint64_t *m, double sigma, uint64_t *ct);
 void orc_glwe_decrypt(const orc_ctx *c, const uint64_t *s, const uint64_t *ct, uint64_t *m);   /* glwe.rs:60-63 */

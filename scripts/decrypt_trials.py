@@ -1,0 +1,121 @@
+#!/usr/bin/env python
+"""Decryption-correctness gate of SURVEY 8(d) / BASELINE north_star: >= 10^6 programmable bootstraps of
+encrypted 4-bit messages at the S2 shape, every output decrypted and compared with LUT[m], and the measured
+output-noise variance compared with the bound the parameter set needs.
+
+  python scripts/decrypt_trials.py [--trials 1048576] [--chunk 65536] [--out gpurun_out/decrypt_trials.json]
+
+Ciphertexts are chained: round r's outputs (big-key LWE, PBS output noise — what a radix circuit feeds into its
+next level) are round r+1's inputs, each round through a different lookup table, so only the first round needs
+fresh encryptions.  Keys, encryption and decryption come from oracle/ (the reference path; test infrastructure).
+A sample of every round is also compared bit for bit with the CPU oracle's PBS.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import math
+import sys
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(ROOT))
+
+
+def centred(noisy: np.ndarray, expect: np.ndarray, q: int) -> np.ndarray:
+    """(noisy - expect) mod q mapped to (-q/2, q/2], as float64 fractions of q"""
+    d = (noisy.astype(object) - expect.astype(object)) % q
+    d = np.array([int(x) - q if int(x) > q // 2 else int(x) for x in d], dtype=object)
+    return (d / q).astype(np.float64)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--trials", type=int, default=1 << 20)
+    ap.add_argument("--chunk", type=int, default=1 << 16)
+    ap.add_argument("--oracle-sample", type=int, default=8, help="outputs per round compared bit-exactly with the oracle")
+    ap.add_argument("--out", default="gpurun_out/decrypt_trials.json")
+    args = ap.parse_args()
+
+    import oracle as O
+    import tfhe_b200 as T
+
+    params = T.S2_SHORTINT
+    sig_glwe, sig_lwe = 2.0 ** -47.8, 2.0 ** -19.8
+    ctx = O.Ctx(O.Params(n=params.n, N=params.N, k=params.k, ell=params.ell, logB=params.logB,
+                         ell_ks=params.ell_ks, logB_ks=params.logB_ks, order=params.order))
+    ks = O.keygen(ctx, 11, sig_glwe, sig_lwe)
+    O.install_keys(ctx, ks)
+    eng = T.Engine(params, device=0)
+    eng.load_keyset(ks)
+
+    p = 16                               # 4-bit messages, one padding bit: plaintext space 32
+    delta = O.delta(2 * p)
+    rs = np.random.RandomState(5)
+    luts = [list(range(16)), [(x * x) % 16 for x in range(16)], [x >> 2 for x in range(16)], [x & 3 for x in range(16)],
+            [(5 * x + 3) % 16 for x in range(16)], [15 - x for x in range(16)]]
+    luts += [list(map(int, rs.permutation(16))) for _ in range(10)]
+    tvs = np.stack([O.testv_lut(params.N, p, delta, lut) for lut in luts])
+    lut_arr = np.array(luts, dtype=np.int64)
+
+    B = args.chunk
+    rounds = -(-args.trials // B)
+    msgs = rs.randint(0, p, size=B).astype(np.int64)
+    t0 = time.time()
+    cts = O.lwe_encrypt_batch(1234, ks.s_in, (msgs.astype(np.uint64) * np.uint64(delta)), sig_glwe)
+    t_enc = time.time() - t0
+    failures, total, exact_checked = 0, 0, 0
+    noise_sum, noise_sq, noise_max = 0.0, 0.0, 0.0
+    t_gpu = 0.0
+    for r in range(rounds):
+        idx = ((np.arange(B) + r) % len(luts)).astype(np.uint32)
+        t0 = time.time()
+        out = eng.pbs_batch(cts, tvs, idx)
+        t_gpu += time.time() - t0
+        want_msgs = lut_arr[idx, msgs]
+        noisy = O.lwe_decrypt_batch(ks.s_in, out)
+        # decode: round(noisy / delta) mod 2p   (main.rs:59-64)
+        dec = np.array([((int(v) + delta // 2) // delta) % (2 * p) for v in noisy], dtype=np.int64)
+        bad = int(np.count_nonzero(dec != want_msgs))
+        failures += bad
+        total += B
+        e = centred(noisy, want_msgs.astype(np.uint64) * np.uint64(delta), O.Q)
+        noise_sum += float(e.sum())
+        noise_sq += float((e * e).sum())
+        noise_max = max(noise_max, float(np.abs(e).max()))
+        ns = args.oracle_sample
+        if ns:
+            want_ct, _ = ctx.pbs_batch(cts[:ns], tvs, idx[:ns])
+            assert np.array_equal(out[:ns], want_ct), f"round {r}: GPU PBS differs from the oracle"
+            exact_checked += ns
+        print(f"round {r + 1}/{rounds}: {B} PBS, {bad} wrong decryptions, running std "
+              f"{math.sqrt(max(noise_sq / total - (noise_sum / total) ** 2, 0)):.3e} q", file=sys.stderr, flush=True)
+        cts, msgs = out, dec
+    var = noise_sq / total - (noise_sum / total) ** 2
+    # decoding fails when |noise| > delta/2 = q/64; p_fail <= 2^-128 (the set's claim) needs
+    # sigma <= (1/64) / z with erfc(z / sqrt 2) = 2^-128, z = 13.11
+    z = 13.11
+    bound_std = (1.0 / 64.0) / z
+    res = {
+        "workload": "S2 shape (n=918, N=2048, k=1, ell=1), 4-bit messages + padding bit, Goldilocks exact NTT",
+        "trials": total, "wrong_decryptions": failures, "rounds": rounds, "chunk": B, "luts": len(luts),
+        "bit_exact_vs_oracle_checked": exact_checked,
+        "output_noise_std_over_q": math.sqrt(max(var, 0.0)), "output_noise_var_over_q2": var,
+        "output_noise_max_over_q": noise_max, "decode_margin_over_q": 1.0 / 64.0,
+        "bound_std_over_q_for_pfail_2^-128": bound_std, "variance_within_bound": bool(var <= bound_std ** 2),
+        "sigma_glwe": sig_glwe, "sigma_lwe": sig_lwe,
+        "seconds": {"encrypt_cpu": t_enc, "gpu_pbs_calls_wall": t_gpu},
+        "pbs_per_s_through_host_abi": total / t_gpu if t_gpu else None,
+    }
+    Path(args.out).parent.mkdir(parents=True, exist_ok=True)
+    Path(args.out).write_text(json.dumps(res, indent=1))
+    print(json.dumps(res))
+    if failures:
+        sys.exit(1)
+
+
+if __name__ == "__main__":
+    main()

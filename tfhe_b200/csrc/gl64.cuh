@@ -153,6 +153,16 @@ GL_HD u64 gl_mul_lazy(u64 a, u64 b) {
 // lazy x lazy -> canonical
 GL_HD u64 gl_mul(u64 a, u64 b) { return gl_canon(gl_mul_lazy(a, b)); }
 
+// lazy o + lazy x * lazy a -> lazy: the addend rides in the 128-bit product (x*a + o < 2^128 always), so a
+// multiply-accumulate costs one reduction and needs no canonical operand
+GL_HD u64 gl_mac(u64 o, u64 x, u64 a) {
+    u64 lo, hi;
+    gl_mul_wide(x, a, lo, hi);
+    lo += o;
+    hi += (lo < o) ? 1 : 0;
+    return gl_reduce128(lo, hi);
+}
+
 // ---- butterflies -----------------------------------------------------------------------------
 // Cooley-Tukey (forward, crypto/poly.rs:17-22): (u, v) -> (u + v*w, u - v*w).  u,v lazy in, lazy out.
 GL_HD void gl_ct_butterfly(u64 &u, u64 &v, u64 w) {

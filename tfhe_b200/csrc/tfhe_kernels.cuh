@@ -345,7 +345,8 @@ TK_DEV void team_external_product(const BRArgs &a, const u64 *ggsw, KeyStream &k
             for (int e = 0; e < 16; e++) {
                 const int p = posA<LOGN>(tau, e);
                 u64 d = poly[p];
-                if (cmux) d = gl_canon(gl_sub(rotated_coeff<LOGN>(poly, p, sh), d));
+                // both operands canonical, so gl_sub's result (a - b, plus q on borrow) already is
+                if (cmux) d = gl_sub(rotated_coeff<LOGN>(poly, p, sh), d);
                 x[e] = gl_digit(d, a.L - a.ell + lvl, a.logB, centred);   // glev_ct.rs:97-99: top ell limbs
             }
             team_ntt_forward<LOGN>(x, xb, tw, tau, team);
@@ -370,10 +371,10 @@ TK_DEV void team_external_product(const BRArgs &a, const u64 *ggsw, KeyStream &k
 #else
                 const u64 a0 = r0[0], a1 = r0[1], b0 = r1[0], b1 = r1[1];
 #endif
-                o0[2 * h] = gl_add(o0[2 * h], gl_mul(x[2 * h], a0));
-                o0[2 * h + 1] = gl_add(o0[2 * h + 1], gl_mul(x[2 * h + 1], a1));
-                o1[2 * h] = gl_add(o1[2 * h], gl_mul(x[2 * h], b0));
-                o1[2 * h + 1] = gl_add(o1[2 * h + 1], gl_mul(x[2 * h + 1], b1));
+                o0[2 * h] = gl_mac(o0[2 * h], x[2 * h], a0);
+                o0[2 * h + 1] = gl_mac(o0[2 * h + 1], x[2 * h + 1], a1);
+                o1[2 * h] = gl_mac(o1[2 * h], x[2 * h], b0);
+                o1[2 * h + 1] = gl_mac(o1[2 * h + 1], x[2 * h + 1], b1);
             }
 #if !defined(TFHE_EMU)
             if (STAGED) {

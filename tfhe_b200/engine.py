@@ -6,6 +6,7 @@ library; nothing here computes on ciphertexts and nothing falls back to the CPU.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from dataclasses import dataclass
 from pathlib import Path
 
@@ -21,7 +22,10 @@ _HERE = Path(__file__).resolve().parent
 
 
 def lib_path() -> Path:
-    return _HERE / "libluxtfhe_b200.so"
+    """The in-tree CUDA library.  LUX_TFHE_LIB selects another build of the same sources (tuning variants
+    made by scripts/build_variant.sh); it is never a different implementation."""
+    override = os.environ.get("LUX_TFHE_LIB")
+    return Path(override) if override else _HERE / "libluxtfhe_b200.so"
 
 
 class LuxError(RuntimeError):
