@@ -52,7 +52,12 @@ typedef enum {
     LUX_OP_SHR = 17,
     LUX_OP_ROTL = 18,
     LUX_OP_ROTR = 19,
-    LUX_OP_COUNT_ = 20
+    /* division by a PLAINTEXT divisor (lux_eval_scalar only): the fhEVM `div`/`rem` overloads
+     * (tests/fhevm-suite/e2e/test/fhevmOperations/fhevmOperations8.ts: `div (euint8, uint8)` ...) take a
+     * plaintext right operand; the circuit is divisor-specific (multiply by a reciprocal, shift) */
+    LUX_OP_DIV = 20,
+    LUX_OP_REM = 21,
+    LUX_OP_COUNT_ = 22
 } lux_op;
 
 /* blocks of an euint of this width (bit_width even, 2..256); 0 if unsupported */
@@ -60,10 +65,14 @@ size_t lux_radix_blocks(unsigned bit_width);
 /* 1 when the op's result is an ebool (one block per integer) */
 int lux_op_is_predicate(lux_op op);
 int lux_op_is_unary(lux_op op);
+/* 1 for ops that exist only with a plaintext right operand (div, rem) */
+int lux_op_is_scalar_only(lux_op op);
 /* programmable bootstraps one integer costs for this op and width (bench: ops/s <-> PBS/s), and the
  * number of sequential PBS levels (launch pairs) of the circuit */
 uint64_t lux_eval_pbs_count(lux_op op, unsigned bit_width);
 uint64_t lux_eval_depth(lux_op op, unsigned bit_width);
+/* same for the plaintext-operand form; for div/rem the circuit (and its size) depends on the divisor */
+uint64_t lux_eval_scalar_pbs_count(lux_op op, unsigned bit_width, uint64_t scalar);
 
 /* out = op(lhs, rhs) for `batch` independent integers; rhs = NULL for unary ops.
  * replaces LuxFHE.add/sub/eq/lt (index.ts:19-22) and POST /evaluate (client.ts:128-147) */
@@ -71,9 +80,14 @@ int lux_eval(lux_engine *e, lux_op op, unsigned bit_width, const uint64_t *lhs, 
              uint64_t *out);
 int lux_eval_device(lux_engine *e, lux_op op, unsigned bit_width, const uint64_t *d_lhs, const uint64_t *d_rhs,
                     size_t batch, uint64_t *d_out);
-/* same with a plaintext right operand per integer (the `(euintN, uintN)` overloads of the fhEVM suite) */
+/* same with a plaintext right operand per integer (the `(euintN, uintN)` overloads of the fhEVM suite);
+ * LUX_OP_DIV / LUX_OP_REM exist only in this form; a zero divisor is LUX_ERR_INVALID */
 int lux_eval_scalar(lux_engine *e, lux_op op, unsigned bit_width, const uint64_t *lhs, const uint64_t *scalars,
                     size_t batch, uint64_t *out);
+/* plaintext operands wider than 64 bits (the euint128 / euint256 div and rem overloads): scalar b is the
+ * n_limbs little-endian words scalars[b * n_limbs ..], n_limbs in 1..4.  div/rem only. */
+int lux_eval_scalar_wide(lux_engine *e, lux_op op, unsigned bit_width, const uint64_t *lhs, const uint64_t *scalars,
+                         size_t n_limbs, size_t batch, uint64_t *out);
 /* out = cond ? a : b     (FHE.select, WrappingERC20.sol:90-100); cond [batch][ct_words] ebool */
 int lux_select(lux_engine *e, unsigned bit_width, const uint64_t *cond, const uint64_t *a, const uint64_t *b,
                size_t batch, uint64_t *out);
@@ -109,6 +123,9 @@ int lux_radix_set_pool_bytes(lux_engine *e, size_t bytes);
 #define LUX_PROG_SELECT 100
 #define LUX_PROG_ERC20 101
 size_t lux_radix_program(int op, unsigned bit_width, int64_t *buf, size_t cap);
+/* the divisor-specific circuit of LUX_OP_DIV / LUX_OP_REM (other ops: same as lux_radix_program) */
+size_t lux_radix_program_scalar(int op, unsigned bit_width, const uint64_t *scalar_limbs, size_t n_limbs, int64_t *buf,
+                                size_t cap);
 /* the 16-entry table of lookup table `lut_id`; returns the number of tables when out == NULL */
 int lux_radix_lut(int lut_id, uint64_t out[16]);
 

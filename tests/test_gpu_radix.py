@@ -116,6 +116,29 @@ def test_select_and_erc20_match_cpu_interpreter(small):
     assert r.decrypt(sel) == [1337, 5]
 
 
+def test_div_rem_by_plaintext_match_cpu_interpreter(small):
+    """div / rem by a plaintext divisor (fhevmOperations8.ts overloads): per-divisor circuits, mixed divisors in
+    one call (grouped internally), bit-exact against the CPU interpreter of the same circuits"""
+    r, width = small, 8
+    vals, divs = [208, 176, 180, 255, 7, 99], [76, 180, 180, 1, 8, 76]
+    a = r.encrypt(vals, width)
+    for op in ("div", "rem"):
+        got = r.rx.eval_scalar(op, width, a, divs)
+        for i, d in enumerate(divs):
+            want = interp_cipher(r.ctx, R.program(op, width, scalar=d), r.luts, [a[i:i + 1]], r.testv, r.delta)[0]
+            assert np.array_equal(got[i:i + 1], want), (op, i)
+        assert r.decrypt(got) == [v // d if op == "div" else v % d for v, d in zip(vals, divs)]
+    with pytest.raises(T.LuxError):
+        r.rx.eval_scalar("div", width, a, [1, 2, 0, 4, 5, 6])     # zero divisor: the reference reverts
+    with pytest.raises(T.LuxError):
+        r.rx.eval("div", width, a, a)                            # encrypted divisors are not in the reference's op set
+    # wide plaintext divisor (euint128 overload)
+    m = (1 << 128) - 1
+    x, d = [340282366920938463463367979625242002479 & m, 12345678901234567890123456789], [340282366920938463463370379842289591609 & m, 98765432109876543]
+    got = r.rx.eval_scalar("rem", 128, r.encrypt(x, 128), d)
+    assert r.decrypt(got) == [xi % di for xi, di in zip(x, d)]
+
+
 def test_chunked_execution_is_identical(small):
     r, width = small, 16
     rs = np.random.RandomState(5)

@@ -22,7 +22,11 @@ def width_of(t: str) -> int:
 
 
 def run_plain(op, width, *operands):
-    prog = R.program(op, width)
+    if op in R.SCALAR_ONLY:      # plaintext divisor: divisor-specific circuit, one encrypted operand
+        prog = R.program(op, width, scalar=operands[1])
+        operands = operands[:1]
+    else:
+        prog = R.program(op, width)
     nb = R.blocks(width)
     ins = []
     for k, v in enumerate(operands):
@@ -43,6 +47,7 @@ def plain_semantics(op, a, b, width):
         "shl": lambda: (a << s) & m, "shr": lambda: a >> s,
         "rotl": lambda: ((a << s) | (a >> (width - s))) & m if s else a,
         "rotr": lambda: ((a >> s) | (a << (width - s))) & m if s else a,
+        "div": lambda: a // b, "rem": lambda: a % b,
     }[op]()
 
 
@@ -56,7 +61,7 @@ def test_abi_symbols_present():
 def test_kat_harvest_is_complete():
     assert len(KATS["ops"]) == 2394
     ops = {k["op"] for k in KATS["ops"]}
-    assert ops - SUPPORTED == {"div", "rem"}      # division by a plaintext scalar: not built
+    assert ops <= SUPPORTED                       # every op of the reference's known-answer suite has a circuit
 
 
 @pytest.mark.parametrize("op", sorted(SUPPORTED))
@@ -91,6 +96,9 @@ def test_wraparound_and_random(width):
             if op in R.UNARY:
                 (got,), _ = run_plain(op, width, a)
                 assert got == plain_semantics(op, a, None, width), (op, a)
+            elif op in R.SCALAR_ONLY and b == 0:
+                with pytest.raises(R.LuxError):      # the reference reverts on a zero plaintext divisor
+                    R.program(op, width, scalar=0)
             else:
                 (got,), _ = run_plain(op, width, a, b)
                 assert got == plain_semantics(op, a, b, width), (op, a, b)
@@ -155,4 +163,37 @@ def test_every_pbs_input_stays_below_the_padding_bit():
     m = (1 << 32) - 1
     for op in sorted(SUPPORTED - R.UNARY):
         for a, b in [(m, m), (m, 0), (0, m), (0x55555555, 0xAAAAAAAA)]:
+            if op in R.SCALAR_ONLY and b == 0:
+                continue
             run_plain(op, 32, a, b)
+
+
+@pytest.mark.parametrize("width", [8, 16, 32, 64, 128, 256])
+def test_div_rem_by_plaintext(width):
+    """x / d and x % d for plaintext divisors: powers of two (shift path), 1, divisors beyond the type's range
+    clipped by the caller, odd/even general divisors (reciprocal path), worst-case dividends"""
+    m = (1 << width) - 1
+    rnd = random.Random(100 + width)
+    divisors = [1, 2, 3, 4, 5, 6, 7, 10, 255, 256, m, m - 1, (m >> 1) + 1, (m >> 1), 1 << (width - 1), (1 << (width // 2)) + 1]
+    divisors += [rnd.randrange(1, m + 1) for _ in range(6)] + [rnd.randrange(1, 1 << (width // 3 + 1)) for _ in range(6)]
+    n = 0
+    for d in divisors:
+        if not 1 <= d <= m:
+            continue
+        xs = [0, 1, d - 1, d, d + 1, m, m - 1, (m // d) * d, (m // d) * d - 1, rnd.randrange(m + 1), rnd.randrange(m + 1)]
+        for x in xs[: (6 if width >= 128 else len(xs))]:
+            x &= m
+            (q,), _ = run_plain("div", width, x, d)
+            (r,), _ = run_plain("rem", width, x, d)
+            assert (q, r) == (x // d, x % d), (width, x, d, q, r)
+            n += 1
+    assert n > 50
+
+
+def test_div_exhaustive_small():
+    """every (x, d) pair of a 6-bit integer"""
+    for d in range(1, 64):
+        for x in range(64):
+            (q,), _ = run_plain("div", 6, x, d)
+            (r,), _ = run_plain("rem", 6, x, d)
+            assert (q, r) == (x // d, x % d), (x, d)

@@ -12,6 +12,8 @@
 #include <array>
 #include <cstring>
 #include <map>
+#include <memory>
+#include <tuple>
 #include <mutex>
 #include <stdexcept>
 #include <string>
@@ -77,6 +79,53 @@ int lut_eval(int id, int x) {
     if (id >= L_NEK0 && id < L_NEK0 + 16) return x != id - L_NEK0;
     return 0;
 }
+
+// plaintext divisors up to 256 bits (euint256 / uint256 overloads): little-endian limbs, one spare limb
+struct Wide {
+    static constexpr int L = 5;
+    u64 w[L] = {0, 0, 0, 0, 0};
+    static Wide from(const u64 *limbs, size_t n) {
+        Wide r;
+        for (size_t i = 0; i < n && i < 4; i++) r.w[i] = limbs[i];
+        return r;
+    }
+    bool is_zero() const { return !(w[0] | w[1] | w[2] | w[3] | w[4]); }
+    bool bit(unsigned i) const { return (w[i / 64] >> (i % 64)) & 1; }
+    unsigned bit_length() const {
+        for (int i = L * 64 - 1; i >= 0; i--)
+            if (bit((unsigned)i)) return (unsigned)i + 1;
+        return 0;
+    }
+    bool is_pow2() const {
+        int ones = 0;
+        for (int i = 0; i < L; i++) ones += __builtin_popcountll(w[i]);
+        return ones == 1;
+    }
+    bool ge(const Wide &o) const {
+        for (int i = L - 1; i >= 0; i--)
+            if (w[i] != o.w[i]) return w[i] > o.w[i];
+        return true;
+    }
+    void sub(const Wide &o) {
+        unsigned __int128 borrow = 0;
+        for (int i = 0; i < L; i++) {
+            const unsigned __int128 d = (unsigned __int128)w[i] - o.w[i] - borrow;
+            w[i] = (u64)d;
+            borrow = (d >> 64) & 1;
+        }
+    }
+    void shl1_or(unsigned b) {
+        for (int i = L - 1; i > 0; i--) w[i] = (w[i] << 1) | (w[i - 1] >> 63);
+        w[0] = (w[0] << 1) | b;
+    }
+    std::vector<int> base4() const {
+        std::vector<int> d;
+        const unsigned n = bit_length();
+        for (unsigned i = 0; i < n; i += 2) d.push_back((int)bit(i) | ((int)bit(i + 1) << 1));
+        return d;
+    }
+    std::array<u64, 4> key() const { return {w[0], w[1], w[2], w[3]}; }
+};
 
 // ------------------------------------------------------------------------------------------ circuits
 struct Term {
@@ -326,6 +375,83 @@ struct Builder {
         for (size_t i = 0; i < a.size(); i++) r[i] = pbs(pack(a[i], b[i]), lut);
         return r;
     }
+    // x * m for a plaintext m given as base-4 digits (least significant first), truncated to nout blocks.
+    // The digit products are linear (no bootstrap); only the column compression costs PBS.
+    std::vector<Val> scalar_mul_blocks(const std::vector<Val> &x, const std::vector<int> &mdig, int nout) {
+        std::vector<std::vector<Val>> cols(nout);
+        for (size_t i = 0; i < x.size(); i++)
+            for (size_t j = 0; j < mdig.size(); j++)
+                if (mdig[j] && (int)(i + j) < nout && !is_zero(x[i])) cols[i + j].push_back(scale(x[i], mdig[j]));
+        return ripple(cols);
+    }
+    // logical shift right by a plaintext bit count, result nout blocks
+    std::vector<Val> shr_const(const std::vector<Val> &x, unsigned bits, int nout) {
+        const int blk = (int)(bits / 2), n = (int)x.size();
+        auto at = [&](int i) { return (i >= 0 && i < n) ? x[i] : cst(0); };
+        std::vector<Val> r(nout);
+        for (int i = 0; i < nout; i++) {
+            if (!(bits & 1)) {
+                r[i] = at(blk + i);
+            } else {
+                const Val hi = at(blk + i + 1), lo = at(blk + i);
+                r[i] = (is_zero(hi) && is_zero(lo)) ? cst(0) : pbs(pack(assume(hi, 0, 3), assume(lo, 0, 3)), L_SHR1);
+            }
+        }
+        return r;
+    }
+    // x / d and x % d for a plaintext divisor d >= 1 (the fhEVM `div`/`rem` overloads take a plaintext right
+    // operand only).  Division by an invariant integer (Granlund-Montgomery): with N = bit width and
+    // l = ceil(log2 d), m = floor(2^(N+l) / d) + 1 gives floor(x * m / 2^(N+l)) = floor(x / d) for all x < 2^N.
+    void div_rem_scalar(const std::vector<Val> &x, const Wide &d, std::vector<Val> *quot, std::vector<Val> *rem) {
+        const int nb = (int)x.size();
+        const unsigned N = 2u * (unsigned)nb;
+        std::vector<Val> q(nb, cst(0));
+        const unsigned dl = d.bit_length();                          // d < 2^dl
+        if (dl > N) {
+            // divisor beyond the type's range: quotient 0, remainder x
+        } else if (d.is_pow2()) {
+            q = shr_const(x, dl - 1, nb);
+        } else {
+            const unsigned l = dl;                                   // 2^(l-1) < d < 2^l  (d is not a power of two)
+            // m = floor((2^(N+l) - 1) / d) + 1 by binary long division (remainder < d at every step)
+            const unsigned tb = N + l;                               // dividend = 2^tb - 1 = tb ones
+            std::vector<int> mbits(tb, 0);
+            Wide r;
+            for (int bit = (int)tb - 1; bit >= 0; bit--) {
+                r.shl1_or(1);
+                if (r.ge(d)) {
+                    r.sub(d);
+                    mbits[bit] = 1;
+                }
+            }
+            mbits.push_back(0);
+            for (size_t i = 0; i < mbits.size(); i++) {              // + 1
+                if (mbits[i] == 0) {
+                    mbits[i] = 1;
+                    break;
+                }
+                mbits[i] = 0;
+            }
+            std::vector<int> mdig((mbits.size() + 1) / 2, 0);
+            for (size_t i = 0; i < mbits.size(); i++) mdig[i / 2] |= mbits[i] << (i & 1);
+            while (!mdig.empty() && mdig.back() == 0) mdig.pop_back();
+            const int nprod = (int)N + 1;                            // x * m < 2^(2N+1): N + 1 blocks of two bits
+            const auto prod = scalar_mul_blocks(x, mdig, nprod);
+            q = shr_const(prod, tb, nb);
+        }
+        if (quot) *quot = q;
+        if (rem) {
+            bool qzero = true;
+            for (auto &v : q) qzero = qzero && is_zero(v);
+            if (qzero) {
+                *rem = x;
+            } else if (dl == 1) {
+                *rem = std::vector<Val>(nb, cst(0));
+            } else {
+                *rem = sub_blocks(x, scalar_mul_blocks(q, d.base4(), nb));
+            }
+        }
+    }
     // barrel shifter by an encrypted amount (taken mod 2*nb)
     std::vector<Val> shift(std::vector<Val> x, const std::vector<Val> &amt, int op) {
         const int nb = (int)x.size(), width = 2 * nb;
@@ -362,10 +488,20 @@ struct Builder {
     }
 };
 
-Program build_program(int op, unsigned bw) {
+Program build_program(int op, unsigned bw, const Wide &scalar) {
     const int nb = (int)lux_radix_blocks(bw);
     if (nb == 0) throw std::logic_error("unsupported bit width");
     Builder b;
+    if (op == LUX_OP_DIV || op == LUX_OP_REM) {   // plaintext divisor: the circuit depends on it
+        if (scalar.is_zero()) throw std::logic_error("division by zero");
+        const int l = b.add_input(nb);
+        std::vector<Val> r;
+        b.div_rem_scalar(b.operand(l), scalar, op == LUX_OP_DIV ? &r : nullptr, op == LUX_OP_REM ? &r : nullptr);
+        for (auto &v : r)
+            if (v.hi > 3) throw std::logic_error("div/rem: unclean output block");
+        b.output(r);
+        return b.finish();
+    }
     if (op == LUX_PROG_SELECT) {
         const int c = b.add_input(1), x = b.add_input(nb), y = b.add_input(nb);
         b.output(b.select(b.in(c, 0, 1), b.operand(x), b.operand(y)));
@@ -423,7 +559,19 @@ const Program &get_program(int op, unsigned bw) {
     std::lock_guard<std::mutex> lk(g_prog_mutex);
     auto key = std::make_pair(op, bw);
     auto it = g_programs.find(key);
-    if (it == g_programs.end()) it = g_programs.emplace(key, build_program(op, bw)).first;
+    if (it == g_programs.end()) it = g_programs.emplace(key, build_program(op, bw, Wide())).first;
+    return it->second;
+}
+// divisor-specific circuits (div / rem by a plaintext): bounded cache, entries stay alive while in use
+std::map<std::tuple<int, unsigned, std::array<u64, 4>>, std::shared_ptr<const Program>> g_scalar_programs;
+std::shared_ptr<const Program> get_scalar_program(int op, unsigned bw, const Wide &scalar) {
+    std::lock_guard<std::mutex> lk(g_prog_mutex);
+    auto key = std::make_tuple(op, bw, scalar.key());
+    auto it = g_scalar_programs.find(key);
+    if (it == g_scalar_programs.end()) {
+        if (g_scalar_programs.size() >= 256) g_scalar_programs.clear();
+        it = g_scalar_programs.emplace(key, std::make_shared<const Program>(build_program(op, bw, scalar))).first;
+    }
     return it->second;
 }
 
@@ -693,6 +841,7 @@ size_t lux_radix_blocks(unsigned bit_width) {
     return bit_width / 2;
 }
 int lux_op_is_predicate(lux_op op) { return op >= LUX_OP_EQ && op <= LUX_OP_GE; }
+int lux_op_is_scalar_only(lux_op op) { return op == LUX_OP_DIV || op == LUX_OP_REM; }
 int lux_op_is_unary(lux_op op) { return op == LUX_OP_NEG || op == LUX_OP_NOT; }
 
 uint64_t lux_eval_pbs_count(lux_op op, unsigned bit_width) {
@@ -705,6 +854,14 @@ uint64_t lux_eval_pbs_count(lux_op op, unsigned bit_width) {
 uint64_t lux_eval_depth(lux_op op, unsigned bit_width) {
     try {
         return get_program((int)op, bit_width).levels.size();
+    } catch (...) {
+        return 0;
+    }
+}
+uint64_t lux_eval_scalar_pbs_count(lux_op op, unsigned bit_width, uint64_t scalar) {
+    try {
+        if (lux_op_is_scalar_only(op)) return get_scalar_program((int)op, bit_width, Wide::from(&scalar, 1))->n_pbs;
+        return get_program((int)op, bit_width).n_pbs;
     } catch (...) {
         return 0;
     }
@@ -727,11 +884,17 @@ static int check_op(lux_engine *e, lux_op op, unsigned bw, const void *lhs, cons
     if (!lux_op_is_unary(op) && !rhs) LUX_FAIL(e, LUX_ERR_INVALID, "binary op needs a right operand");
     return LUX_OK;
 }
+static int reject_scalar_only(lux_engine *e, lux_op op) {
+    if (lux_op_is_scalar_only(op))
+        LUX_FAIL(e, LUX_ERR_INVALID, "div/rem take a plaintext divisor (lux_eval_scalar), as in the reference's op set");
+    return LUX_OK;
+}
 
 int lux_eval(lux_engine *e, lux_op op, unsigned bw, const uint64_t *lhs, const uint64_t *rhs, size_t batch, uint64_t *out) {
     return guarded(e, [&]() -> int {
         int rc = check_op(e, op, bw, lhs, rhs, out);
         if (rc) return rc;
+        if ((rc = reject_scalar_only(e, op))) return rc;
         const Program &p = get_program((int)op, bw);
         std::vector<const u64 *> in{lhs};
         if (!lux_op_is_unary(op)) in.push_back(rhs);
@@ -742,6 +905,7 @@ int lux_eval_device(lux_engine *e, lux_op op, unsigned bw, const uint64_t *lhs, 
     return guarded(e, [&]() -> int {
         int rc = check_op(e, op, bw, lhs, rhs, out);
         if (rc) return rc;
+        if ((rc = reject_scalar_only(e, op))) return rc;
         CUDA_TRY(e, cudaSetDevice(e->device));
         const Program &p = get_program((int)op, bw);
         std::vector<const u64 *> in{lhs};
@@ -770,13 +934,36 @@ int lux_trivial_encrypt(lux_engine *e, unsigned bw, const uint64_t *values, size
     });
 }
 
-int lux_eval_scalar(lux_engine *e, lux_op op, unsigned bw, const uint64_t *lhs, const uint64_t *scalars, size_t batch, uint64_t *out) {
+static int eval_scalar_impl(lux_engine *e, lux_op op, unsigned bw, const uint64_t *lhs, const uint64_t *scalars, size_t n_limbs,
+                            size_t batch, uint64_t *out) {
     return guarded(e, [&]() -> int {
         int rc = check_op(e, op, bw, lhs, scalars, out);
         if (rc) return rc;
         if (lux_op_is_unary(op)) LUX_FAIL(e, LUX_ERR_INVALID, "unary op has no scalar form");
         if (batch == 0) return LUX_OK;
         CUDA_TRY(e, cudaSetDevice(e->device));
+        if (lux_op_is_scalar_only(op)) {
+            // one circuit per distinct divisor: integers are grouped by divisor, each group runs as a batch
+            const size_t nb_ = lux_radix_blocks(bw), stride = nb_ * lux_ct_words(e);
+            std::map<std::array<u64, 4>, std::vector<size_t>> groups;
+            for (size_t b = 0; b < batch; b++) {
+                const Wide d = Wide::from(scalars + b * n_limbs, n_limbs);
+                if (d.is_zero()) LUX_FAIL(e, LUX_ERR_INVALID, "division by zero (integer %zu)", b);
+                groups[d.key()].push_back(b);
+            }
+            std::vector<u64> gin, gout;
+            for (auto &g : groups) {
+                const auto prog = get_scalar_program((int)op, bw, Wide::from(g.first.data(), 4));
+                const size_t n = g.second.size();
+                gin.resize(n * stride);
+                gout.resize(n * stride);
+                for (size_t i = 0; i < n; i++) std::memcpy(&gin[i * stride], lhs + g.second[i] * stride, sizeof(u64) * stride);
+                if ((rc = exec_host(e, *prog, {gin.data()}, {gout.data()}, n))) return rc;
+                for (size_t i = 0; i < n; i++) std::memcpy(out + g.second[i] * stride, &gout[i * stride], sizeof(u64) * stride);
+            }
+            return LUX_OK;
+        }
+        if (n_limbs != 1) LUX_FAIL(e, LUX_ERR_INVALID, "wide plaintext operands are supported for div/rem only");
         const Program &p = get_program((int)op, bw);
         const size_t nb = lux_radix_blocks(bw), w = lux_ct_words(e), words = batch * nb * w;
         const size_t out_words = batch * (size_t)p.out_blocks[0] * w;
@@ -794,6 +981,15 @@ int lux_eval_scalar(lux_engine *e, lux_op op, unsigned bw, const uint64_t *lhs, 
         CUDA_TRY(e, cudaStreamSynchronize(e->stream));
         return LUX_OK;
     });
+}
+
+int lux_eval_scalar(lux_engine *e, lux_op op, unsigned bw, const uint64_t *lhs, const uint64_t *scalars, size_t batch, uint64_t *out) {
+    return eval_scalar_impl(e, op, bw, lhs, scalars, 1, batch, out);
+}
+int lux_eval_scalar_wide(lux_engine *e, lux_op op, unsigned bw, const uint64_t *lhs, const uint64_t *scalars, size_t n_limbs,
+                         size_t batch, uint64_t *out) {
+    if (e && (n_limbs < 1 || n_limbs > 4)) LUX_FAIL(e, LUX_ERR_INVALID, "n_limbs must be 1..4");
+    return eval_scalar_impl(e, op, bw, lhs, scalars, n_limbs, batch, out);
 }
 
 int lux_select(lux_engine *e, unsigned bw, const uint64_t *cond, const uint64_t *a, const uint64_t *b, size_t batch, uint64_t *out) {
@@ -841,9 +1037,25 @@ int lux_erc20_transfer_device(lux_engine *e, const uint64_t *from_bal, const uin
     });
 }
 
+static size_t serialize_program(const Program &p, int64_t *buf, size_t cap);
 size_t lux_radix_program(int op, unsigned bit_width, int64_t *buf, size_t cap) {
     try {
-        const Program &p = get_program(op, bit_width);
+        return serialize_program(get_program(op, bit_width), buf, cap);
+    } catch (...) {
+        return 0;
+    }
+}
+size_t lux_radix_program_scalar(int op, unsigned bit_width, const uint64_t *scalar_limbs, size_t n_limbs, int64_t *buf, size_t cap) {
+    try {
+        if (!lux_op_is_scalar_only((lux_op)op)) return serialize_program(get_program(op, bit_width), buf, cap);
+        if (!scalar_limbs || n_limbs < 1 || n_limbs > 4) return 0;
+        return serialize_program(*get_scalar_program(op, bit_width, Wide::from(scalar_limbs, n_limbs)), buf, cap);
+    } catch (...) {
+        return 0;
+    }
+}
+static size_t serialize_program(const Program &p, int64_t *buf, size_t cap) {
+    {
         std::vector<int64_t> s;
         s.push_back((int64_t)p.in_blocks.size());
         for (int b : p.in_blocks) s.push_back(b);
@@ -870,8 +1082,6 @@ size_t lux_radix_program(int op, unsigned bit_width, int64_t *buf, size_t cap) {
             for (auto &v : o) put(v);
         if (buf && cap >= s.size()) std::memcpy(buf, s.data(), sizeof(int64_t) * s.size());
         return s.size();
-    } catch (...) {
-        return 0;
     }
 }
 

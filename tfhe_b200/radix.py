@@ -14,9 +14,10 @@ import numpy as np
 from .engine import Engine, LuxError, lib as _engine_lib
 
 OPS = {"add": 0, "sub": 1, "mul": 2, "neg": 3, "eq": 4, "ne": 5, "lt": 6, "le": 7, "gt": 8, "ge": 9, "min": 10, "max": 11,
-       "and": 12, "or": 13, "xor": 14, "not": 15, "shl": 16, "shr": 17, "rotl": 18, "rotr": 19}
+       "and": 12, "or": 13, "xor": 14, "not": 15, "shl": 16, "shr": 17, "rotl": 18, "rotr": 19, "div": 20, "rem": 21}
 PREDICATES = {"eq", "ne", "lt", "le", "gt", "ge"}
 UNARY = {"neg", "not"}
+SCALAR_ONLY = {"div", "rem"}   # plaintext right operand only (fhEVM div/rem overloads); circuit depends on the divisor
 PROG_SELECT, PROG_ERC20 = 100, 101
 BLOCK_P = 16          # plaintext values per block (2 message + 2 carry bits); padding bit on top
 
@@ -29,6 +30,10 @@ ABI = {
     "lux_radix_blocks": (_sz, [_uint]),
     "lux_op_is_predicate": (_int, [_int]),
     "lux_op_is_unary": (_int, [_int]),
+    "lux_op_is_scalar_only": (_int, [_int]),
+    "lux_eval_scalar_pbs_count": (_u64, [_int, _uint, _u64]),
+    "lux_radix_program_scalar": (_sz, [_int, _uint, _vp, _sz, _vp, _sz]),
+    "lux_eval_scalar_wide": (_int, [_vp, _int, _uint, _vp, _vp, _sz, _sz, _vp]),
     "lux_eval_pbs_count": (_u64, [_int, _uint]),
     "lux_eval_depth": (_u64, [_int, _uint]),
     "lux_eval": (_int, [_vp, _int, _uint, _vp, _vp, _sz, _vp]),
@@ -61,11 +66,17 @@ def lib():
     return L
 
 
+def _limbs(v: int, n: int) -> np.ndarray:
+    return np.array([(v >> (64 * i)) & (2**64 - 1) for i in range(n)], dtype=np.uint64)
+
+
 def blocks(bit_width: int) -> int:
     return int(lib().lux_radix_blocks(bit_width))
 
 
-def pbs_count(op: str, bit_width: int) -> int:
+def pbs_count(op: str, bit_width: int, scalar: int | None = None) -> int:
+    if scalar is not None:
+        return int(lib().lux_eval_scalar_pbs_count(OPS[op], bit_width, int(scalar) & (2**64 - 1)))
     return int(lib().lux_eval_pbs_count(OPS[op], bit_width))
 
 
@@ -92,13 +103,15 @@ class Program:
         return sum(len(lv) for lv in self.levels)
 
 
-def program(op, bit_width: int) -> Program:
+def program(op, bit_width: int, scalar: int | None = None) -> Program:
+    """the circuit of `op`; div/rem need the plaintext divisor `scalar` (the circuit is divisor-specific)"""
     code = OPS[op] if isinstance(op, str) else int(op)
-    n = lib().lux_radix_program(code, bit_width, None, 0)
+    sc = _limbs(int(scalar or 0), 4)
+    n = lib().lux_radix_program_scalar(code, bit_width, sc.ctypes.data, 4, None, 0)
     if n == 0:
-        raise LuxError(-1, f"no circuit for op {op} at width {bit_width}")
+        raise LuxError(-1, f"no circuit for op {op} at width {bit_width}" + (f", scalar {scalar}" if scalar is not None else ""))
     buf = np.zeros(n, np.int64)
-    lib().lux_radix_program(code, bit_width, buf.ctypes.data, n)
+    lib().lux_radix_program_scalar(code, bit_width, sc.ctypes.data, 4, buf.ctypes.data, n)
     s = buf.tolist()
     pos = 0
 
@@ -174,9 +187,15 @@ class Radix:
     def eval_scalar(self, op: str, bit_width: int, lhs, scalars):
         nb = blocks(bit_width)
         lhs, B = self._shape(lhs, nb)
+        out = np.empty((B, 1 if op in PREDICATES else nb, self.w), np.uint64)
+        if op in SCALAR_ONLY and bit_width > 64:
+            sc = np.concatenate([_limbs(int(s), 4) for s in scalars])
+            assert sc.size == 4 * B
+            self._ck(lib().lux_eval_scalar_wide(self.e._h, OPS[op], bit_width, lhs.ctypes.data, sc.ctypes.data, 4, B,
+                                                out.ctypes.data))
+            return out
         sc = _arr([int(s) & (2**64 - 1) for s in scalars])
         assert sc.size == B
-        out = np.empty((B, 1 if op in PREDICATES else nb, self.w), np.uint64)
         self._ck(lib().lux_eval_scalar(self.e._h, OPS[op], bit_width, lhs.ctypes.data, sc.ctypes.data, B, out.ctypes.data))
         return out
 
