@@ -135,13 +135,13 @@ def work_per_pbs(p):
 
 
 # ------------------------------------------------------------------------------- reference arm
-def cpu_pbs_rate(O, ctx, cts, tvs, idx, budget_s=15.0):
+def cpu_pbs_rate(O, ctx, cts, tvs, idx, budget_s=12.0):
     """time the oracle (OpenMP over ciphertexts) on a bounded sample; returns (PBS/s, threads, sample)"""
     threads = O.lib().orc_max_threads()
     t0 = time.perf_counter()
     ctx.pbs_batch(cts[:threads], tvs, idx[:threads])
     t1 = time.perf_counter() - t0                       # one PBS per thread
-    rounds = max(1, min(8, int(budget_s / max(t1, 1e-3))))
+    rounds = max(1, min(64, int(budget_s / max(t1, 1e-3))))   # ~budget_s seconds of CPU work on all host threads
     nb = min(len(cts), threads * rounds)
     t0 = time.perf_counter()
     _, used = ctx.pbs_batch(cts[:nb], tvs, idx[:nb])
@@ -335,8 +335,16 @@ def run_ours(args):
     br_bytes = w["bsk_bytes"] * waves + B * ((params.n + 1) * 8 + (params.k * params.N + 1) * 8)
     imad, iadd, bfly = eng.int_peak()
     modmul_s = B * w["br_modmul"] / br_s
+    # dram__bytes_read.sum + dram__bytes_write.sum of one `ncu --set full` capture of this kernel at this batch
+    # (profiles/traffic.json, written from the committed ncu summary by scripts/ncu_summary.py traffic)
+    traffic, traffic_src = None, None
+    tj = ROOT / "profiles" / "traffic.json"
+    if tj.exists():
+        t = json.loads(tj.read_text())
+        if int(t.get("batch", -1)) == B:
+            traffic, traffic_src = float(t["dram_bytes_per_launch"]), t.get("source")
     roofline = {"bound": "hbm", "kernel": "blind_rotate_kernel", "achieved": br_bytes / br_s / 1e9, "peak": hbm_peak,
-                "unit": "GB/s", "frac": br_bytes / br_s / 1e9 / hbm_peak, "traffic": None,
+                "unit": "GB/s", "frac": br_bytes / br_s / 1e9 / hbm_peak, "traffic": traffic, "traffic_source": traffic_src,
                 "peak_source": "MEASURED_PEAKS.json hbm_gbs" if pk.exists() else "fallback 6650",
                 "bytes_per_launch": br_bytes, "ms_per_launch": br_s * 1e3,
                 "note": "BSK streamed once per wave of resident ciphertexts; the kernel is integer-pipe bound, see roofline_int"}

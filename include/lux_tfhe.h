@@ -108,6 +108,26 @@ int lux_pbs_batch(lux_engine *e, const uint64_t *lwe_in, const uint64_t *testvs,
 int lux_pbs_batch_device(lux_engine *e, const uint64_t *d_lwe_in, const uint64_t *d_testvs, uint32_t n_luts,
                          const uint32_t *d_lut_idx, size_t B, uint64_t *d_lwe_out, void *stream);
 
+/* ---- boolean gates: ONE programmable bootstrap per gate (BASELINE config 1, "single boolean-gate (NAND)
+ * programmable bootstrap"; parameter set main.rs:23-30).  A bit m is the LWE encryption of m * lux_delta(4)
+ * (main.rs:48-51).  gate(a, b) = sign-bootstrap(c * (a + b) + k) + q/8 with the constant test vector q/8:
+ * the linear part and the final offset run on the device inside the call.  a, b, out: [B][ct_words].
+ * The reference's own gate layer (Go luxfi/tfhe) is out of tree; this is the textbook TFHE gate bootstrap
+ * restated over the in-tree encoding. */
+typedef enum {
+    LUX_GATE_NAND = 0,
+    LUX_GATE_AND = 1,
+    LUX_GATE_OR = 2,
+    LUX_GATE_NOR = 3,
+    LUX_GATE_XOR = 4,
+    LUX_GATE_XNOR = 5
+} lux_gate;
+int lux_gate_batch(lux_engine *e, int gate, const uint64_t *a, const uint64_t *b, size_t B, uint64_t *out);
+int lux_gate_batch_device(lux_engine *e, int gate, const uint64_t *d_a, const uint64_t *d_b, size_t B, uint64_t *d_out,
+                          void *stream);
+/* NOT is linear (delta - x): no bootstrap, host-side helper */
+int lux_gate_not(const lux_engine *e, const uint64_t *a, size_t B, uint64_t *out);
+
 /* test vector for a p-entry lookup table with one padding bit: p blocks of N/p copies of
  * lut[i]*delta, pre-rotated by half a block (get_testv, crypto/mod.rs:17-27).  Host-side helper. */
 int lux_make_testv(uint32_t N, uint32_t p, uint64_t delta, const uint64_t *lut, uint64_t *out);

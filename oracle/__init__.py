@@ -401,6 +401,28 @@ def delta(space: int) -> int:
     return lib().orc_delta(space)
 
 
+# ---- boolean gates (BASELINE config 1).  The reference's gate layer (Go luxfi/tfhe) is out of tree; this is
+# the textbook TFHE gate bootstrap over the in-tree encoding (bit m -> m * q/4, main.rs:48-51):
+#   gate(a, b) = sign-PBS(coef * (a + b) + konst) + q/8, constant test vector q/8.
+GATE_COEFFS = {"nand": (-1, 3), "and": (1, -3), "or": (1, -1), "nor": (-1, 1), "xor": (2, -2), "xnor": (-2, 2)}
+GATE_TRUTH = {"nand": lambda x, y: 1 - (x & y), "and": lambda x, y: x & y, "or": lambda x, y: x | y,
+              "nor": lambda x, y: 1 - (x | y), "xor": lambda x, y: x ^ y, "xnor": lambda x, y: 1 - (x ^ y)}
+
+
+def gate_batch(ctx: "Ctx", name: str, a, b) -> np.ndarray:
+    """[B][ct_len] x [B][ct_len] -> [B][ct_len], the oracle's PBS on the gate's linear combination"""
+    coef, kh = GATE_COEFFS[name]
+    h = Q >> 3
+    a, b = u64(a), u64(b)
+    x = ((a.astype(object) + b.astype(object)) * coef) % Q
+    x[:, -1] = (x[:, -1] + kh * h) % Q
+    tv = np.full((1, ctx.p.N), h, dtype=np.uint64)
+    out, _ = ctx.pbs_batch(x.astype(np.uint64), tv, np.zeros(len(x), np.uint32))
+    out = out.astype(object)
+    out[:, -1] = (out[:, -1] + h) % Q
+    return out.astype(np.uint64)
+
+
 @dataclass
 class KeySet:
     """A full seeded fixture: secret keys (test side only) + evaluation keys in the standard domain."""

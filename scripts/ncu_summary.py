@@ -47,5 +47,23 @@ def launches(path):
         print(f"{t:12.3f} ms {100 * t / tot:6.2f}%  n={n:4d}  avg {t / n:10.3f} ms  {k}")
 
 
+def traffic(path, batch, source):
+    """profiles/traffic.json for bench.py's roofline.traffic: DRAM bytes of the captured blind-rotate launch"""
+    import json
+    out = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(out.splitlines()))
+    hdr, units, r = rows[0], rows[1], rows[2]
+    scale = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    tot = 0.0
+    for name in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+        i = hdr.index(name)
+        tot += float(r[i].replace(",", "")) * scale[units[i]]
+    print(json.dumps({"kernel": r[hdr.index("Kernel Name")], "batch": int(batch), "dram_bytes_per_launch": tot,
+                      "source": source}))
+
+
 if __name__ == "__main__":
-    {"raw": raw, "launches": launches}[sys.argv[1]](sys.argv[2])
+    if sys.argv[1] == "traffic":
+        traffic(sys.argv[2], sys.argv[3], sys.argv[4])
+    else:
+        {"raw": raw, "launches": launches}[sys.argv[1]](sys.argv[2])

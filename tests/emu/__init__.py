@@ -16,13 +16,15 @@ class BRArgs(C.Structure):
     _fields_ = [("n", C.c_uint32), ("steps", C.c_uint32), ("ell", C.c_uint32), ("logB", C.c_uint32),
                 ("L", C.c_uint32), ("B", C.c_uint32), ("out_mode", C.c_uint32), ("n_out", C.c_uint32),
                 ("bsk", C.c_void_p), ("ksk", C.c_void_p), ("lwe", C.c_void_p), ("testv", C.c_void_p),
-                ("lut_idx", C.c_void_p), ("lut_div", C.c_uint32), ("out", C.c_void_p), ("tw_fwd", C.c_void_p)]
+                ("lut_idx", C.c_void_p), ("lut_div", C.c_uint32), ("out", C.c_void_p), ("tw_fwd", C.c_void_p),
+                ("body_add", C.c_uint64)]
 
 
 class KSArgs(C.Structure):
     _fields_ = [("n", C.c_uint32), ("kN", C.c_uint32), ("ell", C.c_uint32), ("logB", C.c_uint32),
                 ("L", C.c_uint32), ("B", C.c_uint32),
-                ("ksk", C.c_void_p), ("ksum", C.c_void_p), ("in_", C.c_void_p), ("out", C.c_void_p)]
+                ("ksk", C.c_void_p), ("ksum", C.c_void_p), ("in_", C.c_void_p), ("out", C.c_void_p),
+                ("splits", C.c_uint32), ("partial", C.c_void_p)]
 
 
 _lib = None
@@ -38,6 +40,7 @@ def lib():
         L = C.CDLL(str(_LIB))
         L.emu_ntt.argtypes = [C.c_int, C.c_int, C.c_int, _u64p, _u64p, _u64p, C.c_uint64, C.c_uint32, C.c_uint32]
         L.emu_blind_rotate.argtypes = [C.c_int, C.c_int, C.POINTER(BRArgs)]
+        L.emu_blind_rotate_split.argtypes = [C.c_int, C.c_int, C.POINTER(BRArgs)]
         L.emu_keyswitch.argtypes = [C.POINTER(KSArgs), C.c_int, C.c_int, C.c_int]
         L.emu_ksk_colsum.argtypes = [_u64p, _u64p, C.c_uint32, C.c_uint32]
         L.emu_ggsw_to_key.argtypes = [_u64p, C.c_size_t, C.c_uint32, C.c_uint32, C.c_uint64]

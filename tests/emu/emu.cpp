@@ -53,6 +53,14 @@ static void emu_br_t(const BRArgs &a) {
         run_cta(T * TEAMS, T, [&](int tid) { blind_rotate_body<LOGN, TEAMS>(a, tid, bid, smem.data()); });
 }
 
+template <int LOGN, int G>
+static void emu_br_split_t(const BRArgs &a) {
+    constexpr int T = Tile<LOGN>::T;
+    std::vector<unsigned char> smem(blind_rotate_split_smem_bytes<LOGN, G>());
+    for (u32 bid = 0; bid < a.B; bid++)
+        run_cta(T * G, T, [&](int tid) { blind_rotate_split_body<LOGN, G>(a, tid, (int)bid, smem.data()); });
+}
+
 // reference-order NTT-domain GGSWs [n_ggsw][2][ell][2][N] -> resident key rows (fold + key_pos), as key_format_kernel
 template <int LOGN>
 static void to_key_t(u64 *ggsw, size_t n_polys, u32 ell, u64 ninv) {
@@ -87,14 +95,28 @@ int emu_blind_rotate(int logn, int teams, const BRArgs *a) {
     return 0;
 }
 
+// latency-mode body: one ciphertext per CTA, G = 2*ell teams
+int emu_blind_rotate_split(int logn, int g, const BRArgs *a) {
+    if ((int)(2 * a->ell) != g) return -2;
+    if (logn == 9 && g == 2) emu_br_split_t<9, 2>(*a);
+    else if (logn == 9 && g == 4) emu_br_split_t<9, 4>(*a);
+    else if (logn == 10 && g == 8) emu_br_split_t<10, 8>(*a);
+    else return -1;
+    return 0;
+}
+
 int emu_keyswitch(const KSArgs *a, int tb, int tx, int rc) {
     if (!(tb == 4 && tx == 32 && rc == 16)) return -1;
     constexpr int TB = 4, TX = 32, RC = 16;
     std::vector<unsigned char> smem(sizeof(u32) * RC * a->ell * TB);
     const int gx = (a->n + 1 + TX - 1) / TX, gy = (a->B + TB - 1) / TB;
-    for (int by = 0; by < gy; by++)
-        for (int bx = 0; bx < gx; bx++)
-            run_cta(TX, TX, [&](int tid) { lwe_keyswitch_body<TB, TX, RC>(*a, tid, bx, by, smem.data()); });
+    const int gz = a->splits > 1 ? (int)a->splits : 1;
+    for (int bz = 0; bz < gz; bz++)
+        for (int by = 0; by < gy; by++)
+            for (int bx = 0; bx < gx; bx++)
+                run_cta(TX, TX, [&](int tid) { lwe_keyswitch_body<TB, TX, RC>(*a, tid, bx, by, smem.data(), bz); });
+    if (gz > 1)
+        for (size_t idx = 0; idx < (size_t)a->B * (a->n + 1); idx++) ks_finish_body(*a, idx);
     return 0;
 }
 

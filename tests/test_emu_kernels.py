@@ -59,7 +59,9 @@ def _device_bsk(ctx, ggsw_std, count):
     return ntt
 
 
-@pytest.mark.parametrize("logn,teams,ell,logB,B,steps", [(9, 3, 2, 16, 4, 3), (10, 2, 4, 5, 2, 2), (9, 3, 1, 41, 3, 2)])
+# teams < 0: the latency-mode body (one ciphertext per CTA, G = -teams = 2*ell teams)
+@pytest.mark.parametrize("logn,teams,ell,logB,B,steps", [(9, 3, 2, 16, 4, 3), (10, 2, 4, 5, 2, 2), (9, 3, 1, 41, 3, 2),
+                                                         (9, -4, 2, 16, 3, 3), (9, -2, 1, 41, 3, 2), (10, -8, 4, 5, 2, 2)])
 def test_emu_blind_rotate_matches_oracle(logn, teams, ell, logB, B, steps):
     N = 1 << logn
     n = 5
@@ -83,7 +85,10 @@ def test_emu_blind_rotate_matches_oracle(logn, teams, ell, logB, B, steps):
         a = E.BRArgs(n=n, steps=steps, ell=ell, logB=logB, L=(64 + logB - 1) // logB, B=B, out_mode=out_mode,
                      n_out=n_out, bsk=E.ptr(bsk_dev), ksk=E.ptr(ksk_dev) if with_ksk else None, lwe=E.ptr(lwe),
                      testv=E.ptr(tvs), lut_idx=E.ptr(idx), lut_div=1, out=E.ptr(out), tw_fwd=E.ptr(roots))
-        assert E.lib().emu_blind_rotate(logn, teams, a) == 0
+        if teams < 0:
+            assert E.lib().emu_blind_rotate_split(logn, -teams, a) == 0
+        else:
+            assert E.lib().emu_blind_rotate(logn, teams, a) == 0
         return out
 
     raw = run(steps, False, 2)
@@ -124,3 +129,12 @@ def test_emu_keyswitch_matches_oracle(logB, ell, n, kN, B):
     assert E.lib().emu_keyswitch(a, 4, 32, 16) == 0
     for b in range(B):
         assert np.array_equal(out[b], ctx.lwe_keyswitch(cts[b])), f"ct {b}"
+    # split form (small batches): input coefficients cut into slices, exact partial sums added afterwards;
+    # 3 slices of a 64-coefficient input = ranges of 32, 32, 0 (a trailing empty slice must contribute zero)
+    for splits in (2, 3):
+        out2 = np.zeros((B, n + 1), np.uint64)
+        partial = np.zeros((splits, B, n + 1), np.uint64)
+        a2 = E.KSArgs(n=n, kN=kN, ell=ell, logB=logB, L=(64 + logB - 1) // logB, B=B, ksk=E.ptr(ksk), ksum=E.ptr(ksum),
+                      in_=E.ptr(cts), out=E.ptr(out2), splits=splits, partial=E.ptr(partial))
+        assert E.lib().emu_keyswitch(a2, 4, 32, 16) == 0
+        assert np.array_equal(out2, out), splits

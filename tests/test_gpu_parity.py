@@ -229,6 +229,23 @@ def test_lwe_keyswitch_s2(rig_s2):
         assert np.array_equal(got[b], r.ctx.lwe_keyswitch(cts[b])), b
 
 
+def test_lwe_keyswitch_split_forms_agree(rig_s2, rig_small1):
+    """small batches cut the input coefficients into slices (exact partial sums, second kernel): same words"""
+    for r, B in ((rig_s2, 3), (rig_small1, 11)):
+        rng = O.Rng(15)
+        cts = np.stack([rng.field(r.p.N + 1) for _ in range(B)])
+        outs = []
+        try:
+            for n in (1, 2, 5, 0):
+                r.eng.ks_splits(n)
+                outs.append(r.eng.lwe_keyswitch(cts))
+        finally:
+            r.eng.ks_splits(0)
+        for o in outs[1:]:
+            assert np.array_equal(o, outs[0])
+        assert np.array_equal(outs[0][0], r.ctx.lwe_keyswitch(cts[0]))
+
+
 # ---------------------------------------------------------------------------------------------- whole PBS
 def _pbs_case(r: Rig, B: int, p: int, luts, seed: int, sigma: float, check: int):
     rng = O.Rng(seed)
@@ -259,6 +276,58 @@ def test_pbs_s1_boolean_bit_exact(rig_s1):
     """BASELINE config 1 parameters (main.rs:23-30), identity LUT on one bit + the NAND test vector."""
     nand_like = [1, 1]   # constant-1 block table stands for the sign test vector q/8 (SURVEY App. B)
     _pbs_case(rig_s1, 12, 2, [[0, 1], nand_like], 23, 0.0000117021618159313, 4)
+
+
+@pytest.mark.parametrize("which", ["small0", "small1", "s1"])
+def test_boolean_gates_bit_exact_and_truth_tables(which, rig_small0, rig_small1, rig_s1):
+    """BASELINE config 1: NAND (and the other two-input gates) = one sign bootstrap; the GPU gate (linear part,
+    PBS and +q/8 all on the device) against the oracle's, bit for bit, and the decrypted truth tables; at the
+    reference's own boolean parameter set with its noise (main.rs:23-30) and on both PBS orders."""
+    r = {"small0": rig_small0, "small1": rig_small1, "s1": rig_s1}[which]
+    sigma = 0.0000117021618159313 if which == "s1" else 1e-9
+    delta = O.delta(4)
+    rng = O.Rng(77)
+    xs, ys = [0, 0, 1, 1, 1, 0], [0, 1, 0, 1, 1, 0]
+    a = np.stack([O.lwe_encrypt(rng, r.ks.s_in, (x * delta) % Q, sigma) for x in xs])
+    b = np.stack([O.lwe_encrypt(rng, r.ks.s_in, (y * delta) % Q, sigma) for y in ys])
+    dec = lambda cts: [O.decode(O.lwe_decrypt(r.ks.s_in, c), delta, 4) for c in cts]
+    for name, truth in O.GATE_TRUTH.items():
+        got = r.eng.gate(name, a, b)
+        assert dec(got) == [truth(x, y) for x, y in zip(xs, ys)], name
+        if which != "s1" or name == "nand":
+            assert np.array_equal(got, O.gate_batch(r.ctx, name, a, b)), name
+    assert dec(r.eng.gate_not(a)) == [1 - x for x in xs]
+    chained = r.eng.gate("nand", r.eng.gate("nand", a, b), r.eng.gate_not(b))   # outputs feed gates again
+    assert dec(chained) == [1 - ((1 - (x & y)) & (1 - y)) for x, y in zip(xs, ys)]
+    with pytest.raises(T.LuxError):
+        r.eng._ck(T.lib().lux_gate_batch(r.eng._h, 17, a.ctypes.data, b.ctypes.data, 1, a.ctypes.data))
+
+
+@pytest.mark.parametrize("which", ["small0", "small1", "s1", "s2"])
+def test_latency_mode_equals_throughput_mode(which, rig_small0, rig_small1, rig_s1, rig_s2):
+    """the latency-mode blind rotate (one ciphertext per CTA, 2*ell teams, partial sums in shared memory) and the
+    throughput kernel produce the same words, and both equal the oracle's"""
+    r = {"small0": rig_small0, "small1": rig_small1, "s1": rig_s1, "s2": rig_s2}[which]
+    p = 2 if which == "s1" else 4
+    delta = O.delta(2 * p)
+    rng = O.Rng(91)
+    luts = [[(i + 1) % p for i in range(p)], list(range(p))]
+    tvs = np.stack([O.testv_lut(r.p.N, p, delta, lut) for lut in luts])
+    B = 7
+    msgs = [int(rng.u64() % p) for _ in range(B)]
+    idx = np.array([b % 2 for b in range(B)], dtype=np.uint32)
+    cts = np.stack([O.lwe_encrypt(rng, r.ks.s_in, (m * delta) % Q, 1e-9) for m in msgs])
+    try:
+        r.eng.split_mode(1)
+        fast = r.eng.pbs_batch(cts, tvs, idx)
+        r.eng.split_mode(0)
+        bulk = r.eng.pbs_batch(cts, tvs, idx)
+    finally:
+        r.eng.split_mode(-1)
+    assert np.array_equal(fast, bulk)
+    want, _ = r.ctx.pbs_batch(cts[:2], tvs, idx[:2])
+    assert np.array_equal(fast[:2], want)
+    assert [O.decode(O.lwe_decrypt(r.ks.s_in, c), delta, 2 * p) for c in fast] == [luts[idx[b]][msgs[b]] for b in range(B)]
 
 
 def test_pbs_s2_shortint_bit_exact(rig_s2):

@@ -249,3 +249,25 @@ def test_s1_boolean_set_with_noise():
     cts = np.stack([O.lwe_encrypt(rng, ks.s_in, (m * delta) % Q, 0.0000117021618159313) for m in (0, 1, 1, 0, 1, 0, 0, 1)])
     outs, _ = ctx.pbs_batch(cts, tv)
     assert [O.decode(O.lwe_decrypt(ks.s_in, o), delta, 2 * p) for o in outs] == [0, 1, 1, 0, 1, 0, 0, 1]
+
+
+@pytest.mark.parametrize("order", [O.ORDER_PBS_GLWEKS, O.ORDER_LWEKS_PBS])
+def test_boolean_gates_truth_tables(order):
+    """BASELINE config 1: one sign bootstrap per gate over the in-tree bit encoding m * q/4 (main.rs:48-51);
+    every gate, every input pair, outputs re-usable as inputs (NAND of NANDs)."""
+    P = O.Params(n=20, N=256, k=1, ell=4, logB=8, ell_ks=4 if order == 0 else 8, logB_ks=8, order=order)
+    ctx = O.Ctx(P)
+    ks = O.keygen(ctx, 17, 1e-12, 1e-10)
+    O.install_keys(ctx, ks)
+    delta = O.delta(4)
+    rng = O.Rng(5)
+    xs, ys = [0, 0, 1, 1], [0, 1, 0, 1]
+    a = np.stack([O.lwe_encrypt(rng, ks.s_in, (x * delta) % Q, 1e-10) for x in xs])
+    b = np.stack([O.lwe_encrypt(rng, ks.s_in, (y * delta) % Q, 1e-10) for y in ys])
+    dec = lambda cts: [O.decode(O.lwe_decrypt(ks.s_in, c), delta, 4) for c in cts]
+    for name, truth in O.GATE_TRUTH.items():
+        out = O.gate_batch(ctx, name, a, b)
+        assert dec(out) == [truth(x, y) for x, y in zip(xs, ys)], name
+    n1 = O.gate_batch(ctx, "nand", a, b)
+    n2 = O.gate_batch(ctx, "nand", n1, n1)          # NOT(NAND) = AND
+    assert dec(n2) == [x & y for x, y in zip(xs, ys)]

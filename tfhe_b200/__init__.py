@@ -6,8 +6,8 @@ ABI via ctypes.  There is no CPU fallback: importing works without a GPU (so the
 inspected), but creating an engine raises unless a B200 is present and the library is built.
 """
 from .engine import (Engine, LuxError, Params, lib, lib_path, make_testv, delta, ORDER_PBS_GLWEKS, ORDER_LWEKS_PBS,
-                     DOMAIN_STANDARD, DOMAIN_NTT, Q, S1_BOOLEAN, S2_SHORTINT, TEST_SMALL_O0, TEST_SMALL_O1)
+                     DOMAIN_STANDARD, DOMAIN_NTT, GATES, Q, S1_BOOLEAN, S2_SHORTINT, TEST_SMALL_O0, TEST_SMALL_O1)
 
 __all__ = ["Engine", "LuxError", "Params", "lib", "lib_path", "make_testv", "delta", "ORDER_PBS_GLWEKS",
-           "ORDER_LWEKS_PBS", "DOMAIN_STANDARD", "DOMAIN_NTT", "Q", "S1_BOOLEAN", "S2_SHORTINT",
+           "ORDER_LWEKS_PBS", "DOMAIN_STANDARD", "DOMAIN_NTT", "GATES", "Q", "S1_BOOLEAN", "S2_SHORTINT",
            "TEST_SMALL_O0", "TEST_SMALL_O1"]

@@ -105,11 +105,60 @@ static int launch_xp_t(lux_engine *e, const BRArgs &a, const u64 *d_glwe, size_t
     return LUX_OK;
 }
 
+// latency mode (tfhe_kernels.cuh "latency mode"): one ciphertext per CTA, G = 2*ell teams
+template <int LOGN, int G>
+__global__ void __launch_bounds__(Tile<LOGN>::T *G, 1) blind_rotate_split_kernel(const BRArgs a) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    blind_rotate_split_body<LOGN, G>(a, threadIdx.x, blockIdx.x, smem);
+}
+
+template <int LOGN, int G>
+static int launch_br_split_t(lux_engine *e, const BRArgs &a, cudaStream_t s) {
+    constexpr size_t smem = blind_rotate_split_smem_bytes<LOGN, G>();
+    static_assert(smem <= 227 * 1024 && Tile<LOGN>::T * G <= 1024, "latency-mode configuration does not fit an SM");
+    static bool configured[64] = {};
+    if (!configured[e->device & 63]) {
+        CUDA_TRY(e, cudaFuncSetAttribute(blind_rotate_split_kernel<LOGN, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured[e->device & 63] = true;
+    }
+    blind_rotate_split_kernel<LOGN, G><<<a.B, Tile<LOGN>::T * G, smem, s>>>(a);
+    e->launches++;
+    CUDA_TRY(e, cudaGetLastError());
+    return LUX_OK;
+}
+
+// 1 = launched in latency mode, 0 = not applicable (caller falls through to the throughput kernel), < 0 = error
+static int try_launch_split(lux_engine *e, const BRArgs &a, cudaStream_t s) {
+    // automatic: only when the batch leaves SMs idle anyway, and not when a tuning run pinned the team count
+    if (e->split_mode == 0 || (e->split_mode < 0 && (a.B > (u32)e->sm_count || e->force_teams > 0))) return 0;
+    int rc = 0;
+    bool done = true;
+#if LUX_LOGN <= 10
+    if (a.ell == 1) rc = launch_br_split_t<LUX_LOGN, 2>(e, a, s);
+    else if (a.ell == 2) rc = launch_br_split_t<LUX_LOGN, 4>(e, a, s);
+    else if (a.ell == 3) rc = launch_br_split_t<LUX_LOGN, 6>(e, a, s);
+    else if (a.ell == 4) rc = launch_br_split_t<LUX_LOGN, 8>(e, a, s);
+    else done = false;
+#elif LUX_LOGN == 11
+    if (a.ell == 1) rc = launch_br_split_t<11, 2>(e, a, s);
+    else if (a.ell == 2) rc = launch_br_split_t<11, 4>(e, a, s);
+    else done = false;
+#else
+    done = false;
+#endif
+    if (rc) return rc;
+    return done ? 1 : 0;
+}
+
 #define LUX_CAT_(a, b) a##b
 #define LUX_CAT(a, b) LUX_CAT_(a, b)
 
 // TEAMS variants per ring size: SMEM = 16N + 32N*TEAMS bytes <= 227 KiB
 int LUX_CAT(lux_launch_br_, LUX_LOGN)(lux_engine *e, const BRArgs &a, cudaStream_t s) {
+    {
+        const int sp = try_launch_split(e, a, s);
+        if (sp) return sp < 0 ? sp : LUX_OK;
+    }
 #if LUX_LOGN == 9
     const int t = pick_teams(e, a.B, 12);
     if (t <= 1) return launch_br_t<9, 1>(e, a, s);
@@ -131,6 +180,10 @@ int LUX_CAT(lux_launch_br_, LUX_LOGN)(lux_engine *e, const BRArgs &a, cudaStream
 }
 
 size_t LUX_CAT(lux_br_wave_, LUX_LOGN)(const lux_engine *e, size_t B) {
+    if (e->split_mode != 0 && (e->split_mode > 0 || (B <= (size_t)e->sm_count && e->force_teams <= 0))) {
+        const u32 ell = e->p.ell;
+        if ((LUX_LOGN <= 10 && ell <= 4) || (LUX_LOGN == 11 && ell <= 2)) return (size_t)e->sm_count;
+    }
 #if LUX_LOGN == 9
     const int t = pick_teams(e, B, 12);
     return (size_t)e->sm_count * (t <= 1 ? 1 : t <= 4 ? 4 : 12);

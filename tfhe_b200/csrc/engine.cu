@@ -3,6 +3,7 @@
 // launches CUDA kernels, and lux_engine_create fails without a device.
 #include "engine.h"
 
+#include <algorithm>
 #include <cstdio>
 #include <cstring>
 #include <new>
@@ -12,8 +13,9 @@
 constexpr int KS_TB = 8, KS_TX = 128, KS_RC = 64;
 __global__ void __launch_bounds__(KS_TX) lwe_keyswitch_kernel(const KSArgs a) {
     extern __shared__ __align__(16) unsigned char smem[];
-    lwe_keyswitch_body<KS_TB, KS_TX, KS_RC>(a, threadIdx.x, blockIdx.x, blockIdx.y, smem);
+    lwe_keyswitch_body<KS_TB, KS_TX, KS_RC>(a, threadIdx.x, blockIdx.x, blockIdx.y, smem, blockIdx.z);
 }
+__global__ void ks_finish_kernel(const KSArgs a) { ks_finish_body(a, blockIdx.x * (size_t)blockDim.x + threadIdx.x); }
 
 __global__ void ksk_colsum_kernel(const u64 *ksk, u64 *ksum, u32 rows, u32 cols) {
     ksk_colsum_body(ksk, ksum, rows, cols, blockIdx.x * blockDim.x + threadIdx.x);
@@ -207,7 +209,7 @@ static int launch_ntt(lux_engine *e, const u64 *d_in, u64 *d_out, size_t n_polys
 
 static int launch_ks(lux_engine *e, const u64 *d_in, u64 *d_out, size_t B, cudaStream_t s) {
     const lux_params &p = e->p;
-    KSArgs a{p.n, p.k * p.N, p.ell_ks, p.logB_ks, e->L_ks, (u32)B, e->d_lksk, e->d_ksum, d_in, d_out};
+    KSArgs a{p.n, p.k * p.N, p.ell_ks, p.logB_ks, e->L_ks, (u32)B, e->d_lksk, e->d_ksum, d_in, d_out, 1, nullptr};
     const size_t smem = sizeof(u32) * KS_RC * p.ell_ks * KS_TB;
     static bool configured[64] = {};
     if (!configured[e->device & 63]) {
@@ -215,10 +217,46 @@ static int launch_ks(lux_engine *e, const u64 *d_in, u64 *d_out, size_t B, cudaS
         configured[e->device & 63] = true;
     }
     dim3 grid((p.n + 1 + KS_TX - 1) / KS_TX, (unsigned)((B + KS_TB - 1) / KS_TB));
+    // small batches leave most SMs idle and make each CTA walk all k*N*ell_ks key rows one after the other:
+    // cut the input coefficients into slices (grid z) and add the exact partial sums in a second tiny kernel
+    const unsigned ctas = grid.x * grid.y, max_splits = (a.kN + KS_RC - 1) / KS_RC;
+    unsigned splits = ctas >= (unsigned)e->sm_count ? 1u : std::min<unsigned>(max_splits, (2u * e->sm_count + ctas - 1) / ctas);
+    if (e->ks_splits > 0) splits = std::min<unsigned>(max_splits, (unsigned)e->ks_splits);
+    if (splits > 1) {
+        int rc = ensure_scratch(e, 4, sizeof(u64) * splits * B * (p.n + 1));
+        if (rc) return rc;
+        a.splits = splits;
+        a.partial = (u64 *)e->scratch[4];
+        grid.z = splits;
+    }
     lwe_keyswitch_kernel<<<grid, KS_TX, smem, s>>>(a);
     e->launches++;
     CUDA_TRY(e, cudaGetLastError());
+    if (splits > 1) {
+        const size_t total = B * (size_t)(p.n + 1);
+        ks_finish_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(a);
+        e->launches++;
+        CUDA_TRY(e, cudaGetLastError());
+    }
     return LUX_OK;
+}
+
+// boolean gates (BASELINE config 1).  Bits are m * q/4 (main.rs:48-51: delta = q >> 2, one padding bit);
+// gate(a, b) = sign-bootstrap(coef * (a + b) + konst) + q/8 with the constant test vector q/8:
+//   x = coef*(a+b) + konst lands on +-q/8 or +-3q/8 (+-q/4 for XOR/XNOR), the bootstrap returns +q/8 on the
+//   positive half-plane and -q/8 on the negative one, and the final +q/8 maps that to q/4 or 0.
+// out[b][i] = coef * (a[b][i] + c[b][i]) (+ konst on the body), coef in {1, -1, 2, -2}
+__global__ void gate_prepare_kernel(const u64 *a, const u64 *c, u64 *out, u32 w, size_t total, int coef, u64 konst) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        u64 s = gl_canon(gl_add(a[i], c[i]));
+        if (coef == 2 || coef == -2) s = gl_canon(gl_add(s, s));
+        if (coef < 0) s = gl_neg(s);
+        if (i % w == w - 1) s = gl_canon(gl_add(s, konst));
+        out[i] = s;
+    }
+}
+__global__ void fill_kernel(u64 *p, u64 v, size_t n) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) p[i] = v;
 }
 
 static BRArgs make_br_args(const lux_engine *e, const u64 *d_lwe, const u64 *d_testv, const u32 *d_idx, size_t B, u64 *d_out) {
@@ -242,7 +280,7 @@ static BRArgs make_br_args(const lux_engine *e, const u64 *d_lwe, const u64 *d_t
 
 
 int lux_pbs_device_grouped(lux_engine *e, const u64 *d_in, const u64 *d_testvs, const u32 *d_lut_idx, u32 lut_div, size_t B,
-                           u64 *d_out, cudaStream_t s) {
+                           u64 *d_out, cudaStream_t s, u64 body_add) {
     if (B == 0) return LUX_OK;
     if (B > 0x7fffffffu) LUX_FAIL(e, LUX_ERR_INVALID, "batch too large");
     if (!e->has_bsk) LUX_FAIL(e, LUX_ERR_NO_KEY, "bootstrap key not loaded");
@@ -262,6 +300,7 @@ int lux_pbs_device_grouped(lux_engine *e, const u64 *d_in, const u64 *d_testvs, 
     if (e->timing) CUDA_TRY(e, cudaEventRecord(e->ev[1], s));
     BRArgs a = make_br_args(e, d_small, d_testvs, d_lut_idx, B, d_out);
     a.lut_div = lut_div ? lut_div : 1;
+    a.body_add = body_add;
     if (ks_first) {
         a.out_mode = 0;
     } else {
@@ -416,6 +455,16 @@ int lux_debug_force_teams(lux_engine *e, int teams) {
     e->force_teams = teams;
     return LUX_OK;
 }
+int lux_debug_ks_splits(lux_engine *e, int splits) {
+    if (!e || splits < 0) return LUX_ERR_INVALID;
+    e->ks_splits = splits;
+    return LUX_OK;
+}
+int lux_debug_split_mode(lux_engine *e, int mode) {
+    if (!e || mode < -1 || mode > 1) return LUX_ERR_INVALID;
+    e->split_mode = mode;
+    return LUX_OK;
+}
 
 // ---- keys
 static int load_ggsw_array(lux_engine *e, u64 *d_dst, const u64 *src, size_t words, size_t expect, int domain, const char *what) {
@@ -526,6 +575,72 @@ int lux_pbs_batch(lux_engine *e, const uint64_t *lwe_in, const uint64_t *testvs,
     if ((rc = lux_pbs_batch_device(e, d_in, d_tv, n_luts, d_idx, B, d_out, nullptr))) return rc;
     CUDA_TRY(e, cudaMemcpyAsync(lwe_out, d_out, sizeof(u64) * B * w, cudaMemcpyDeviceToHost, e->stream));
     CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    return LUX_OK;
+}
+
+// ---- boolean gates
+static int gate_coeffs(int gate, int *coef, u64 *konst) {
+    const u64 h = GL_Q >> 3;                       // q/8 = delta/2 (delta = q >> 2 is even)
+    const u64 h3 = gl_canon(gl_add(gl_canon(gl_add(h, h)), h));
+    switch (gate) {
+        case LUX_GATE_NAND: *coef = -1; *konst = h3; return 1;                       // {3h, h, -h}
+        case LUX_GATE_AND: *coef = 1; *konst = gl_neg(h3); return 1;                 // {-3h, -h, h}
+        case LUX_GATE_OR: *coef = 1; *konst = gl_neg(h); return 1;                   // {-h, h, 3h}
+        case LUX_GATE_NOR: *coef = -1; *konst = h; return 1;                         // {h, -h, -3h}
+        case LUX_GATE_XOR: *coef = 2; *konst = gl_neg(gl_canon(gl_add(h, h))); return 1;   // {-2h, 2h, -2h}
+        case LUX_GATE_XNOR: *coef = -2; *konst = gl_canon(gl_add(h, h)); return 1;         // {2h, -2h, 2h}
+        default: return 0;
+    }
+}
+int lux_gate_batch_device(lux_engine *e, int gate, const uint64_t *d_a, const uint64_t *d_b, size_t B, uint64_t *d_out,
+                          void *stream) {
+    if (!e) return LUX_ERR_INVALID;
+    if (!d_a || !d_b || !d_out) LUX_FAIL(e, LUX_ERR_INVALID, "lux_gate_batch_device: null argument");
+    int coef;
+    u64 konst;
+    if (!gate_coeffs(gate, &coef, &konst)) LUX_FAIL(e, LUX_ERR_INVALID, "unknown gate %d", gate);
+    if (B == 0) return LUX_OK;
+    CUDA_TRY(e, cudaSetDevice(e->device));
+    cudaStream_t s = stream ? (cudaStream_t)stream : e->stream;
+    const size_t w = lux_ct_words(e), N = e->p.N, total = B * w;
+    int rc;
+    if ((rc = ensure_scratch(e, 6, sizeof(u64) * total))) return rc;
+    if ((rc = ensure_scratch(e, 7, sizeof(u64) * N))) return rc;
+    u64 *d_x = (u64 *)e->scratch[6], *d_tv = (u64 *)e->scratch[7];
+    const unsigned grid = (unsigned)std::min<size_t>((total + 255) / 256, (size_t)e->sm_count * 16);
+    gate_prepare_kernel<<<grid, 256, 0, s>>>(d_a, d_b, d_x, (u32)w, total, coef, konst);
+    fill_kernel<<<(unsigned)((N + 255) / 256), 256, 0, s>>>(d_tv, GL_Q >> 3, N);
+    e->launches += 2;
+    CUDA_TRY(e, cudaGetLastError());
+    return lux_pbs_device_grouped(e, d_x, d_tv, nullptr, 1, B, d_out, s, GL_Q >> 3);
+}
+int lux_gate_batch(lux_engine *e, int gate, const uint64_t *a, const uint64_t *b, size_t B, uint64_t *out) {
+    if (!e) return LUX_ERR_INVALID;
+    if (!a || !b || !out) LUX_FAIL(e, LUX_ERR_INVALID, "lux_gate_batch: null argument");
+    if (B == 0) return LUX_OK;
+    CUDA_TRY(e, cudaSetDevice(e->device));
+    const size_t bytes = sizeof(u64) * B * lux_ct_words(e);
+    int rc;
+    if ((rc = ensure_scratch(e, 1, bytes))) return rc;
+    if ((rc = ensure_scratch(e, 2, bytes))) return rc;
+    if ((rc = ensure_scratch(e, 3, bytes))) return rc;
+    CUDA_TRY(e, cudaMemcpyAsync(e->scratch[1], a, bytes, cudaMemcpyHostToDevice, e->stream));
+    CUDA_TRY(e, cudaMemcpyAsync(e->scratch[3], b, bytes, cudaMemcpyHostToDevice, e->stream));
+    if ((rc = lux_gate_batch_device(e, gate, (const u64 *)e->scratch[1], (const u64 *)e->scratch[3], B, (u64 *)e->scratch[2], nullptr)))
+        return rc;
+    CUDA_TRY(e, cudaMemcpyAsync(out, e->scratch[2], bytes, cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    return LUX_OK;
+}
+// NOT needs no bootstrap: delta - x  (1 -> 0, 0 -> 1), host-side helper on [B][ct_words] words
+int lux_gate_not(const lux_engine *e, const uint64_t *a, size_t B, uint64_t *out) {
+    if (!e || !a || !out) return LUX_ERR_INVALID;
+    const size_t w = lux_ct_words(e);
+    for (size_t i = 0; i < B * w; i++) {
+        u64 v = gl_neg(a[i]);
+        if (i % w == w - 1) v = gl_canon(gl_add(v, GL_Q >> 2));
+        out[i] = v;
+    }
     return LUX_OK;
 }
 

@@ -36,6 +36,8 @@ struct lux_engine {
     cudaEvent_t ev[4] = {};
     float last_ms[2] = {0.f, 0.f};
     int force_teams = 0;  // debug/tuning override of ciphertexts per CTA
+    int ks_splits = 0;    // key-switch input slices: 0 = automatic, > 0 forced (tests)
+    int split_mode = -1;  // latency-mode blind rotate: -1 = automatic (B <= #SMs), 0 = never, 1 = always (tests)
     struct RadixState *radix = nullptr;  // euintN layer (radix.cu), created on first use
     char err[512] = "";
 };
@@ -43,10 +45,12 @@ struct lux_engine {
 void lux_host_ntt_tables(u32 N, std::vector<u64> &roots, std::vector<u64> &invroots, u64 &ninv);
 // PBS on device buffers where ciphertext ct uses test vector d_idx[ct / lut_div] (engine.cu)
 int lux_pbs_device_grouped(lux_engine *e, const u64 *d_in, const u64 *d_testvs, const u32 *d_idx, u32 lut_div, size_t B,
-                           u64 *d_out, cudaStream_t s);
+                           u64 *d_out, cudaStream_t s, u64 body_add = 0);
 int lux_ensure_scratch(lux_engine *e, int slot, size_t bytes);
 void lux_radix_destroy(lux_engine *e);  // radix.cu
 extern "C" int lux_debug_force_teams(lux_engine *e, int teams);
+extern "C" int lux_debug_split_mode(lux_engine *e, int mode);
+extern "C" int lux_debug_ks_splits(lux_engine *e, int splits);
 extern "C" int lux_debug_int_peak(lux_engine *e, double out[3]);
 extern "C" int lux_debug_field_probe(lux_engine *e, const uint64_t *a, const uint64_t *b, size_t count, uint64_t *out);
 

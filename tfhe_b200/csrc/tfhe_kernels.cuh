@@ -251,6 +251,7 @@ struct BRArgs {
     u32 lut_div;        // >= 1 (1 = one index per ciphertext; the radix layer uses one per slot of B ciphertexts)
     u64 *out;           // [B][out_len]
     const u64 *tw_fwd;  // ROOTS    [N]
+    u64 body_add;       // canonical constant added to the extracted body (boolean gates: the +q/8 after the sign bootstrap)
 };
 
 // coefficient p of X^sh * poly (negacyclic), poly canonical in shared memory   (vtfhe/mod.rs:80-107)
@@ -489,7 +490,114 @@ TK_DEV void blind_rotate_body(const BRArgs &a, int tid, int bid, unsigned char *
         const u32 len = a.out_mode == 1 ? a.n_out : (u32)N;
         u64 *o = a.out + (size_t)ct * (len + 1);
         for (u32 p = tau; p < len; p += T) o[p] = p ? gl_neg(acc[N - p]) : acc[0];
-        if (tau == 0) o[len] = acc[N];
+        if (tau == 0) o[len] = gl_canon(gl_add(acc[N], a.body_add));
+    }
+}
+
+// ---- latency mode: ONE ciphertext per CTA, its external product spread over G = 2*ell teams --------------
+// The throughput kernel above gives a ciphertext to one team, which runs the 2*ell forward and 2 inverse NTTs
+// of a CMUX one after the other.  When the batch is smaller than the GPU (B <= #SMs) that serial chain is the
+// latency of a bootstrap, so here team g = (j, lvl) transforms digit polynomial (j, lvl), multiplies it with
+// its row pair of the GGSW (read straight from L2: every team needs a different pair at the same time) and
+// leaves two partial output polynomials in shared memory; teams 0 and 1 then add up the G partials of output
+// polynomial 0 / 1, run the inverse NTT and update the accumulator.  Per CMUX the critical path is one forward
+// and one inverse NTT instead of 2*ell + 2.  Sums are exact in Z_q, so results are bit-identical to the
+// throughput kernel's.
+// shared memory: [tw N][acc 2N] then per team a 2N region: forward exchange buffer (first N), then the team's
+// partials [2][N]; inverse team r reuses half r of its own region as exchange buffer (the other inverse team
+// only reads the other half).
+template <int LOGN, int G>
+constexpr size_t blind_rotate_split_smem_bytes() {
+    return sizeof(u64) * ((size_t)3 * Tile<LOGN>::N + (size_t)G * 2 * Tile<LOGN>::N);
+}
+
+template <int LOGN, int G>
+TK_DEV void blind_rotate_split_body(const BRArgs &a, int tid, int bid, unsigned char *smem_raw) {
+    constexpr int N = Tile<LOGN>::N, T = Tile<LOGN>::T;
+    u64 *tw = (u64 *)smem_raw;
+    u64 *acc = tw + N;
+    u64 *part = acc + 2 * N;  // [G][2][N]
+    const int g = tid / T, tau = tid % T;
+    const int j = g / (int)a.ell;
+    const u32 lvl = (u32)g % a.ell;
+    u64 *mine = part + (size_t)g * 2 * N;
+    const bool centred = (a.L * a.logB == 64);
+    for (int i = tid; i < N; i += T * G) tw[i] = a.tw_fwd[i];
+    const u32 ct = (u32)bid;
+    const u64 *lwe = a.lwe + (size_t)ct * (a.n + 1);
+    const u64 *tv = a.testv + (size_t)(a.lut_idx ? a.lut_idx[ct / a.lut_div] : 0) * N;
+    {
+        const u32 sh0 = gl_mod_switch(gl_neg(lwe[a.n]), LOGN);
+        for (int p = tid; p < N; p += T * G) {
+            acc[p] = 0;
+            acc[N + p] = rotated_coeff<LOGN>(tv, p, sh0);
+        }
+    }
+    cta_sync();
+    const size_t ggsw_len = (size_t)4 * a.ell * N;
+    const u32 iters = a.steps + (a.ksk ? 1u : 0u);
+    u64 mask = a.steps ? lwe[0] : 0;
+    for (u32 i = 0; i < iters; i++) {
+        const bool cmux = i < a.steps;
+        const u32 sh = cmux ? gl_mod_switch(mask, LOGN) : 0;
+        if (i + 1 < a.steps) mask = lwe[i + 1];
+        {   // phase 1: every team, its own digit polynomial
+            const u64 *poly = acc + j * N;
+            u64 x[16];
+            TK_UNROLL
+            for (int e = 0; e < 16; e++) {
+                const int p = posA<LOGN>(tau, e);
+                u64 d = poly[p];
+                if (cmux) d = gl_sub(rotated_coeff<LOGN>(poly, p, sh), d);
+                x[e] = gl_digit(d, a.L - a.ell + lvl, a.logB, centred);
+            }
+            team_ntt_forward<LOGN>(x, mine, tw, tau, g);
+            const u64 *rows = (cmux ? a.bsk + i * ggsw_len : a.ksk) + (size_t)g * 2 * N;
+            team_sync(g, T);  // the exchange buffer is about to be overwritten with the partials
+            TK_UNROLL
+            for (int h = 0; h < 8; h++) {
+                const u64 *r0 = rows + (size_t)h * 2 * T + 2 * tau;
+                const u64 *r1 = r0 + N;
+#if !defined(TFHE_EMU)
+                const ulonglong2 v0 = *reinterpret_cast<const ulonglong2 *>(r0);
+                const ulonglong2 v1 = *reinterpret_cast<const ulonglong2 *>(r1);
+                const u64 a0 = v0.x, a1 = v0.y, b0 = v1.x, b1 = v1.y;
+#else
+                const u64 a0 = r0[0], a1 = r0[1], b0 = r1[0], b1 = r1[1];
+#endif
+                mine[(2 * h) * T + tau] = gl_mul(x[2 * h], a0);
+                mine[(2 * h + 1) * T + tau] = gl_mul(x[2 * h + 1], a1);
+                mine[N + (2 * h) * T + tau] = gl_mul(x[2 * h], b0);
+                mine[N + (2 * h + 1) * T + tau] = gl_mul(x[2 * h + 1], b1);
+            }
+        }
+        cta_sync();
+        if (g < 2) {  // phase 2: team r = g owns output polynomial r
+            u64 o[16];
+            TK_UNROLL
+            for (int e = 0; e < 16; e++) o[e] = part[(size_t)g * N + e * T + tau];
+            for (int gg = 1; gg < G; gg++) {
+                const u64 *src = part + ((size_t)gg * 2 + g) * N;
+                TK_UNROLL
+                for (int e = 0; e < 16; e++) o[e] = gl_add(o[e], src[e * T + tau]);
+            }
+            team_ntt_inverse<LOGN>(o, mine + (size_t)g * N, tw, tau, g);
+            TK_UNROLL
+            for (int e = 0; e < 16; e++) {
+                const int p = g * N + posA<LOGN>(tau, e);
+                acc[p] = cmux ? gl_canon(gl_add(o[e], acc[p])) : gl_canon(o[e]);
+            }
+        }
+        cta_sync();
+    }
+    if (a.out_mode == 2) {
+        u64 *o = a.out + (size_t)ct * 2 * N;
+        for (int p = tid; p < 2 * N; p += T * G) o[p] = acc[p];
+    } else {
+        const u32 len = a.out_mode == 1 ? a.n_out : (u32)N;
+        u64 *o = a.out + (size_t)ct * (len + 1);
+        for (u32 p = tid; p < len; p += T * G) o[p] = p ? gl_neg(acc[N - p]) : acc[0];
+        if (tid == 0) o[len] = gl_canon(gl_add(acc[N], a.body_add));
     }
 }
 
@@ -508,6 +616,8 @@ struct KSArgs {
     const u64 *ksum;  // [n+1] column sums of ksk (mod q)
     const u64 *in;    // [B][kN+1]
     u64 *out;         // [B][n+1]
+    u32 splits;       // > 1: the kN input coefficients are cut into `splits` ranges (grid z); each CTA writes its exact
+    u64 *partial;     //      partial sum to partial[z][B][n+1] and ks_finish_body adds them up (small batches: latency)
 };
 
 GL_HD u64 ks_fold(u64 a0, u64 a1) {  // a0 + a1 * 2^32 -> canonical
@@ -517,7 +627,7 @@ GL_HD u64 ks_fold(u64 a0, u64 a1) {  // a0 + a1 * 2^32 -> canonical
 }
 
 template <int TB, int TX, int RC>
-TK_DEV void lwe_keyswitch_body(const KSArgs &a, int tid, int bx, int by, unsigned char *smem_raw) {
+TK_DEV void lwe_keyswitch_body(const KSArgs &a, int tid, int bx, int by, unsigned char *smem_raw, int bz = 0) {
     u32 *dig = (u32 *)smem_raw;  // [RC*ell][TB]
     const u32 col = (u32)bx * TX + tid;
     const u32 b0 = (u32)by * TB;
@@ -529,8 +639,13 @@ TK_DEV void lwe_keyswitch_body(const KSArgs &a, int tid, int bx, int by, unsigne
     TK_UNROLL
     for (int b = 0; b < TB; b++) A0[b] = A1[b] = F[b] = 0;
     u32 rows_pending = 0;
-    for (u32 c0 = 0; c0 < a.kN; c0 += RC) {
-        const u32 rc = (a.kN - c0 < RC) ? a.kN - c0 : RC;
+    // input-coefficient range of this CTA: all of them, or slice bz of `splits` (multiples of RC)
+    const u32 nsplit = a.splits > 1 ? a.splits : 1;
+    const u32 per = ((a.kN + nsplit - 1) / nsplit + RC - 1) / RC * RC;
+    const u32 c_begin = (u32)bz * per < a.kN ? (u32)bz * per : a.kN;
+    const u32 c_end = c_begin + per < a.kN ? c_begin + per : a.kN;
+    for (u32 c0 = c_begin; c0 < c_end; c0 += RC) {
+        const u32 rc = (c_end - c0 < RC) ? c_end - c0 : RC;
         cta_sync();
         for (u32 idx = tid; idx < rc * TB; idx += TX) {
             const u32 i = idx / TB, b = idx % TB;
@@ -566,6 +681,14 @@ TK_DEV void lwe_keyswitch_body(const KSArgs &a, int tid, int bx, int by, unsigne
             rows_pending += r1 - r0;
         }
     }
+    if (nsplit > 1) {
+        if (col <= a.n)
+            for (int b = 0; b < TB; b++) {
+                if (b0 + b >= a.B) break;
+                a.partial[((size_t)bz * a.B + b0 + b) * (a.n + 1) + col] = gl_canon(gl_add(F[b], ks_fold(A0[b], A1[b])));
+            }
+        return;
+    }
     if (col <= a.n) {
         const u64 off = gl_mul((u64)halfB, a.ksum[col]);
         for (int b = 0; b < TB; b++) {
@@ -576,6 +699,20 @@ TK_DEV void lwe_keyswitch_body(const KSArgs &a, int tid, int bx, int by, unsigne
             a.out[(size_t)(b0 + b) * (a.n + 1) + col] = v;
         }
     }
+}
+
+// split key switch, second step: out[b][col] = sum_z partial[z][b][col] - halfB * ksum[col] (+ body)
+TK_DEV void ks_finish_body(const KSArgs &a, size_t idx) {
+    const u32 cols = a.n + 1;
+    if (idx >= (size_t)a.B * cols) return;
+    const u32 col = (u32)(idx % cols);
+    const size_t b = idx / cols;
+    u64 v = 0;
+    for (u32 z = 0; z < a.splits; z++) v = gl_canon(gl_add(v, a.partial[(size_t)z * a.B * cols + idx]));
+    const u64 off = gl_mul((u64)(1u << (a.logB - 1)), a.ksum[col]);
+    v = gl_canon(gl_sub(v, off));
+    if (col == a.n) v = gl_canon(gl_add(v, a.in[b * (a.kN + 1) + a.kN]));
+    a.out[idx] = v;
 }
 
 // column sums of the key-switch key: ksum[x] = sum_r ksk[r][x] mod q        (one thread per column)

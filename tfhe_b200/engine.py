@@ -67,6 +67,8 @@ class Params:
         return self.k * self.N * self.ell_ks * (self.n + 1)
 
 
+GATES = {"nand": 0, "and": 1, "or": 2, "nor": 3, "xor": 4, "xnor": 5}   # lux_gate (include/lux_tfhe.h)
+
 # S1: the reference's in-tree boolean set, research/verifiable-fhe/src/main.rs:23-30
 S1_BOOLEAN = Params(n=728, N=1024, k=1, ell=4, logB=5, ell_ks=4, logB_ks=5, order=ORDER_PBS_GLWEKS)
 # S2: shape of PARAM_MESSAGE_2_CARRY_2_KS_PBS_TUNIFORM_2M128 (sdk/relayer/src/tfhe.ts:15) over the
@@ -103,6 +105,9 @@ ABI = {
     "lux_import_keys_device": (_int, [_vp, _vp, _sz]),
     "lux_pbs_batch": (_int, [_vp, _vp, _vp, _u32, _vp, _sz, _vp]),
     "lux_pbs_batch_device": (_int, [_vp, _vp, _vp, _u32, _vp, _sz, _vp, _vp]),
+    "lux_gate_batch": (_int, [_vp, _int, _vp, _vp, _sz, _vp]),
+    "lux_gate_batch_device": (_int, [_vp, _int, _vp, _vp, _sz, _vp, _vp]),
+    "lux_gate_not": (_int, [_vp, _vp, _sz, _vp]),
     "lux_make_testv": (_int, [_u32, _u32, _u64, _u64p, _u64p]),
     "lux_delta": (_u64, [_u32]),
     "lux_ntt_forward": (_int, [_vp, _u64p, _sz, _u64p]),
@@ -131,6 +136,10 @@ def lib():
             fn.argtypes = args
         if hasattr(L, "lux_debug_force_teams"):
             L.lux_debug_force_teams.argtypes = [_vp, _int]
+        if hasattr(L, "lux_debug_split_mode"):
+            L.lux_debug_split_mode.argtypes = [_vp, _int]
+        if hasattr(L, "lux_debug_ks_splits"):
+            L.lux_debug_ks_splits.argtypes = [_vp, _int]
         if hasattr(L, "lux_debug_int_peak"):
             L.lux_debug_int_peak.argtypes = [_vp, C.POINTER(C.c_double * 3)]
             L.lux_debug_int_peak.restype = _int
@@ -246,6 +255,26 @@ class Engine:
         self._ck(lib().lux_pbs_batch(self._h, _ptr(lwe_in), _ptr(testvs), n_luts, _ptr(lut_idx), B, _ptr(out)))
         return out
 
+    # ---- boolean gates: one bootstrap each (BASELINE config 1); bits are m * delta(4) ------------
+    def gate(self, name: str, a, b):
+        """NAND / AND / OR / NOR / XOR / XNOR on [B][ct_len] host arrays of encrypted bits"""
+        a = _u64arr(a).reshape(-1, self.p.ct_len)
+        b = _u64arr(b).reshape(-1, self.p.ct_len)
+        assert a.shape == b.shape
+        out = np.empty_like(a)
+        self._ck(lib().lux_gate_batch(self._h, GATES[name.lower()], _ptr(a), _ptr(b), a.shape[0], _ptr(out)))
+        return out
+
+    def gate_device(self, name: str, d_a, d_b, B: int, d_out, stream=None):
+        self._ck(lib().lux_gate_batch_device(self._h, GATES[name.lower()], d_a.data_ptr(), d_b.data_ptr(), B,
+                                             d_out.data_ptr(), stream))
+
+    def gate_not(self, a):
+        a = _u64arr(a).reshape(-1, self.p.ct_len)
+        out = np.empty_like(a)
+        self._ck(lib().lux_gate_not(self._h, _ptr(a), a.shape[0], _ptr(out)))
+        return out
+
     def pbs_batch_device(self, d_in, d_testvs, d_lut_idx, B: int, d_out, n_luts: int | None = None, stream=None):
         """torch CUDA tensors (int64 storage of the u64 words); asynchronous on `stream`/engine stream."""
         if n_luts is None:
@@ -285,6 +314,14 @@ class Engine:
     def wave_ciphertexts(self, B: int) -> int:
         """ciphertexts resident on the GPU at once in the blind-rotate launch for a batch of B"""
         return int(lib().lux_wave_ciphertexts(self._h, B))
+
+    def split_mode(self, mode: int):
+        """latency-mode blind rotate (one ciphertext per CTA, 2*ell teams): -1 automatic (B <= #SMs), 0 never, 1 always"""
+        self._ck(lib().lux_debug_split_mode(self._h, mode))
+
+    def ks_splits(self, n: int):
+        """key-switch input slices for small batches: 0 automatic, n > 0 forced (1 = single pass)"""
+        self._ck(lib().lux_debug_ks_splits(self._h, n))
 
     def force_teams(self, t: int):
         lib().lux_debug_force_teams(self._h, t)
