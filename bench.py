@@ -168,7 +168,7 @@ def run_reference(args):
     dt = time.perf_counter() - t0
     v = per_step * args.steps / dt
     sample = f"{per_step} PBS per step (1 per host thread) of the B={args.batch} batch, oracle C port, OpenMP"
-    print(json.dumps({
+    emit({
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u64 (Goldilocks field)", "data": "synthetic",
@@ -177,7 +177,7 @@ def run_reference(args):
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "note": "reference binary (Go luxfi/tfhe / wasm blob) is not in the tree and no go/node/cargo toolchain exists; "
                 "this arm is the C restatement of the in-tree algorithm (oracle/), kind=port",
-    }), flush=True)
+    })
 
 
 # ------------------------------------------------------------------------------------- our arm
@@ -354,9 +354,11 @@ def run_ours(args):
                     "imad_wide_per_s": imad, "iadd_per_s": iadd, "modmul_per_pbs": w["br_modmul"]}
 
     # ---- CPU baseline on a bounded sample
-    cpu_v, cores, nb, dt = (0.0, 0, 0, 0.0) if args.no_cpu else cpu_pbs_rate(O, ctx, cts, tvs, idx)
+    # CPU baseline: rank 0 at N = 1 only (contract); under torchrun the host threads are pinned to 1 per rank
+    skip_cpu = args.no_cpu or world > 1
+    cpu_v, cores, nb, dt = (None, 0, 0, 0.0) if skip_cpu else cpu_pbs_rate(O, ctx, cts, tvs, idx)
     cpu_lat_ms = None
-    if not args.no_cpu:
+    if not skip_cpu:
         t0 = time.perf_counter()
         ctx.pbs_batch(cts[:1], tvs, idx[:1])
         cpu_lat_ms = (time.perf_counter() - t0) * 1e3
@@ -376,13 +378,33 @@ def run_ours(args):
         "clocks": clocks,
         "parity": f"first {ncheck} outputs bit-exact vs oracle; {len(msgs)} decryptions correct",
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
 
 
+_REAL_STDOUT = None
+
+
+def claim_stdout():
+    """stdout carries exactly ONE line, the JSON result: everything else a library prints to fd 1 (NCCL's version
+    banner, for one) is sent to stderr."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line: dict):
+    data = (json.dumps(line) + "\n").encode()
+    sys.stdout.flush()
+    os.write(_REAL_STDOUT if _REAL_STDOUT is not None else 1, data)
+
+
 def main():
+    claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
@@ -396,6 +418,10 @@ def main():
     if args.warmup < 3 and args.impl == "ours":
         log("note: timing rules want >= 3 warm-up steps")
     if args.impl == "reference":
+        # torchrun pins OMP_NUM_THREADS=1 for every rank; the reference arm runs on rank 0 alone and is meant to use
+        # all the host threads it can (must be set before the OpenMP runtime of the oracle library loads)
+        if int(os.environ.get("RANK", "0")) == 0 and "TORCHELASTIC_RUN_ID" in os.environ:
+            os.environ["OMP_NUM_THREADS"] = str(os.cpu_count() or 1)
         run_reference(args)
     else:
         run_ours(args)
