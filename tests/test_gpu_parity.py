@@ -246,6 +246,29 @@ def test_lwe_keyswitch_split_forms_agree(rig_s2, rig_small1):
         assert np.array_equal(outs[0][0], r.ctx.lwe_keyswitch(cts[0]))
 
 
+@pytest.mark.parametrize("B", [1, 129, 300])
+def test_lwe_keyswitch_tensor_core_form(rig_s2, rig_small1, B):
+    """int8 tensor-core contraction (ks_mma.cuh): same words as the integer-pipe kernel and the oracle, on ragged
+    batches (1, 129, 300 against the 128-row tile) and edge-value masks"""
+    for r in (rig_s2, rig_small1):
+        rng = O.Rng(21 + B)
+        cts = np.stack([rng.field(r.p.N + 1) for _ in range(B)])
+        cts[0, :14] = edge_values()
+        cts[B - 1, -14:] = edge_values()
+        try:
+            r.eng.ks_mode(1)
+            got = r.eng.lwe_keyswitch(cts)
+            r.eng.ks_mode(0)
+            ref = r.eng.lwe_keyswitch(cts)
+        finally:
+            r.eng.ks_mode(-1)
+        assert np.array_equal(got, ref)
+        for b in sorted({0, B // 2, B - 1}):
+            assert np.array_equal(got[b], r.ctx.lwe_keyswitch(cts[b])), b
+        if B >= 256:   # automatic dispatch takes the tensor-core form here
+            assert np.array_equal(r.eng.lwe_keyswitch(cts), got)
+
+
 # ---------------------------------------------------------------------------------------------- whole PBS
 def _pbs_case(r: Rig, B: int, p: int, luts, seed: int, sigma: float, check: int):
     rng = O.Rng(seed)

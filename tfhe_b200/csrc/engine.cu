@@ -2,6 +2,7 @@
 // One engine per GPU; one process per GPU.  No CPU fallback: every entry point that computes
 // launches CUDA kernels, and lux_engine_create fails without a device.
 #include "engine.h"
+#include "ks_mma.cuh"
 
 #include <algorithm>
 #include <cstdio>
@@ -207,8 +208,62 @@ static int launch_ntt(lux_engine *e, const u64 *d_in, u64 *d_out, size_t n_polys
     LUX_FAIL(e, LUX_ERR_INVALID, "unsupported N");
 }
 
+// the int8 tensor-core form needs signed digits that fit a byte, exact int32 byte-plane sums and whole K tiles
+static bool ks_mma_eligible(const lux_params &p) {
+    const uint64_t K = (uint64_t)p.k * p.N * p.ell_ks;
+    return p.order == LUX_ORDER_LWEKS_PBS && p.logB_ks >= 1 && p.logB_ks <= 7 && K % ksmma::BK == 0 &&
+           K * (1ull << (p.logB_ks - 1)) * 255ull < (1ull << 31);
+}
+
+// derive the K-major byte planes of the resident LWE key switch key (after a load or an import of the key blob)
+static int derive_ksk_bytes(lux_engine *e) {
+    if (!ks_mma_eligible(e->p)) return LUX_OK;
+    const lux_params &p = e->p;
+    const u32 K = p.k * p.N * p.ell_ks, cols = p.n + 1;
+    e->ks_npad = (8 * cols + ksmma::BN - 1) / ksmma::BN * ksmma::BN;
+    if (!e->d_kskT) {
+        cudaError_t st = cudaMalloc(&e->d_kskT, (size_t)e->ks_npad * K);
+        if (st != cudaSuccess) LUX_FAIL(e, LUX_ERR_OOM, "cudaMalloc(%zu) for key switch byte planes: %s", (size_t)e->ks_npad * K, cudaGetErrorString(st));
+    }
+    ksmma::ks_bytes_transpose_kernel<<<e->sm_count * 16, 256, 0, e->stream>>>(e->d_lksk, e->d_kskT, K, cols, e->ks_npad);
+    e->launches++;
+    CUDA_TRY(e, cudaGetLastError());
+    return LUX_OK;
+}
+
+static int launch_ks_mma(lux_engine *e, const u64 *d_in, u64 *d_out, size_t B, cudaStream_t s) {
+    const lux_params &p = e->p;
+    const u32 kN = p.k * p.N, K = kN * p.ell_ks;
+    const u32 mpad = (u32)((B + ksmma::BM - 1) / ksmma::BM * ksmma::BM);
+    const size_t need = (size_t)mpad * K;
+    if (e->ks_dig_bytes < need) {
+        if (e->d_ks_dig) cudaFree(e->d_ks_dig);
+        e->d_ks_dig = nullptr;
+        e->ks_dig_bytes = 0;
+        const size_t want = need + need / 4;
+        cudaError_t st = cudaMalloc(&e->d_ks_dig, want);
+        if (st != cudaSuccess) LUX_FAIL(e, LUX_ERR_OOM, "cudaMalloc(%zu) for key switch digits: %s", want, cudaGetErrorString(st));
+        e->ks_dig_bytes = want;
+    }
+    static bool configured[64] = {};
+    if (!configured[e->device & 63]) {
+        CUDA_TRY(e, cudaFuncSetAttribute(ksmma::lwe_keyswitch_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ksmma::SMEM_BYTES));
+        configured[e->device & 63] = true;
+    }
+    ksmma::ks_digits_kernel<<<e->sm_count * 8, 256, 0, s>>>(d_in, e->d_ks_dig, (u32)B, mpad, kN, p.ell_ks, p.logB_ks, e->L_ks);
+    e->launches++;
+    CUDA_TRY(e, cudaGetLastError());
+    ksmma::Args a{e->d_ks_dig, e->d_kskT, d_in, d_out, (u32)B, p.n, kN, K};
+    dim3 grid(e->ks_npad / ksmma::BN, mpad / ksmma::BM);
+    ksmma::lwe_keyswitch_mma_kernel<<<grid, ksmma::THREADS, ksmma::SMEM_BYTES, s>>>(a);
+    e->launches++;
+    CUDA_TRY(e, cudaGetLastError());
+    return LUX_OK;
+}
+
 static int launch_ks(lux_engine *e, const u64 *d_in, u64 *d_out, size_t B, cudaStream_t s) {
     const lux_params &p = e->p;
+    if (e->d_kskT && e->ks_mode != 0 && (e->ks_mode == 1 || B >= 256)) return launch_ks_mma(e, d_in, d_out, B, s);
     KSArgs a{p.n, p.k * p.N, p.ell_ks, p.logB_ks, e->L_ks, (u32)B, e->d_lksk, e->d_ksum, d_in, d_out, 1, nullptr};
     const size_t smem = sizeof(u32) * KS_RC * p.ell_ks * KS_TB;
     static bool configured[64] = {};
@@ -406,6 +461,8 @@ void lux_engine_destroy(lux_engine *e) {
     for (int i = 0; i < LUX_SCRATCH_SLOTS; i++)
         if (e->scratch[i]) cudaFree(e->scratch[i]);
     for (auto &kv : e->any_tables) cudaFree(kv.second);
+    if (e->d_kskT) cudaFree(e->d_kskT);
+    if (e->d_ks_dig) cudaFree(e->d_ks_dig);
     if (e->d_tw_fwd) cudaFree(e->d_tw_fwd);
     if (e->d_blob) cudaFree(e->d_blob);
     for (int i = 0; i < 4; i++)
@@ -458,6 +515,11 @@ int lux_debug_force_teams(lux_engine *e, int teams) {
 int lux_debug_ks_splits(lux_engine *e, int splits) {
     if (!e || splits < 0) return LUX_ERR_INVALID;
     e->ks_splits = splits;
+    return LUX_OK;
+}
+int lux_debug_ks_mode(lux_engine *e, int mode) {
+    if (!e || mode < -1 || mode > 1) return LUX_ERR_INVALID;
+    e->ks_mode = mode;
     return LUX_OK;
 }
 int lux_debug_split_mode(lux_engine *e, int mode) {
@@ -513,6 +575,8 @@ int lux_load_lwe_ksk(lux_engine *e, const uint64_t *ksk, size_t n_words) {
     ksk_colsum_kernel<<<(cols + 127) / 128, 128, 0, e->stream>>>(e->d_lksk, e->d_ksum, rows, cols);
     e->launches++;
     CUDA_TRY(e, cudaGetLastError());
+    int rc = derive_ksk_bytes(e);
+    if (rc) return rc;
     CUDA_TRY(e, cudaStreamSynchronize(e->stream));
     e->has_lksk = true;
     return LUX_OK;
@@ -538,6 +602,10 @@ int lux_import_keys_device(lux_engine *e, const void *dev_blob, size_t bytes) {
     CUDA_TRY(e, cudaMemcpy(hdr, dev_blob, sizeof(hdr), cudaMemcpyDeviceToHost));
     if (hdr[0] != 0x4c55584b45593031ULL || hdr[4] != e->blob_words) LUX_FAIL(e, LUX_ERR_INVALID, "key blob header mismatch");
     CUDA_TRY(e, cudaMemcpyAsync(e->d_blob, dev_blob, bytes, cudaMemcpyDeviceToDevice, e->stream));
+    if (hdr[3] != 0) {
+        int rc = derive_ksk_bytes(e);
+        if (rc) return rc;
+    }
     CUDA_TRY(e, cudaStreamSynchronize(e->stream));
     e->has_bsk = hdr[1] != 0;
     e->has_gksk = hdr[2] != 0;

@@ -37,6 +37,12 @@ struct lux_engine {
     float last_ms[2] = {0.f, 0.f};
     int force_teams = 0;  // debug/tuning override of ciphertexts per CTA
     int ks_splits = 0;    // key-switch input slices: 0 = automatic, > 0 forced (tests)
+    // tensor-core key switch (ks_mma.cuh): byte planes of the LWE key switch key, K-major, derived at key load
+    uint8_t *d_kskT = nullptr;
+    u32 ks_npad = 0;          // rows of d_kskT = 8 * (n + 1) rounded up to the N tile
+    int8_t *d_ks_dig = nullptr;  // grow-only [Mpad][K] digit buffer
+    size_t ks_dig_bytes = 0;
+    int ks_mode = -1;         // -1 = automatic (batches >= 256), 0 = integer-pipe kernel only, 1 = tensor-core kernel whenever eligible
     int split_mode = -1;  // latency-mode blind rotate: -1 = automatic (B <= #SMs), 0 = never, 1 = always (tests)
     struct RadixState *radix = nullptr;  // euintN layer (radix.cu), created on first use
     char err[512] = "";
@@ -51,6 +57,7 @@ void lux_radix_destroy(lux_engine *e);  // radix.cu
 extern "C" int lux_debug_force_teams(lux_engine *e, int teams);
 extern "C" int lux_debug_split_mode(lux_engine *e, int mode);
 extern "C" int lux_debug_ks_splits(lux_engine *e, int splits);
+extern "C" int lux_debug_ks_mode(lux_engine *e, int mode);
 extern "C" int lux_debug_int_peak(lux_engine *e, double out[3]);
 extern "C" int lux_debug_field_probe(lux_engine *e, const uint64_t *a, const uint64_t *b, size_t count, uint64_t *out);
 

@@ -187,6 +187,97 @@ GL_HD void gl_gs_butterfly_neg(u64 &u, u64 &v, u64 w) {
     v = gl_mul_lazy(d, w);
 }
 
+// ---- power-of-two twiddles -------------------------------------------------------------------------
+// 2 has order 192 in Z_q (2^96 = -1), so every 32nd root of unity is a power of 2^6.  The reference's first sixteen
+// table entries ROOTS[j] = psi^bitrev(j) (ntt/gen_param_file.sage:86-88) are the 32nd roots omega^bitrev4(j) with
+// omega = 7^((q-1)/32) for EVERY ring size, i.e. the twiddles of NTT stages 0..3 are these constants:
+//     ROOTS[j] = 2^gl_root_log2(j),  j < 16        (checked against the generated table in lux_engine_create)
+// and a butterfly of those stages multiplies by a shift instead of four IMAD.WIDE.
+constexpr int gl_root_log2(int j) {
+    constexpr int t[16] = {0, 48, 120, 168, 156, 12, 84, 132, 78, 126, 6, 54, 42, 90, 162, 18};
+    return t[j & 15];
+}
+
+// x * 2^S mod q for a compile-time S in [0, 96).  lazy -> lazy.
+// With S = 32a + r and y = x << r = y0 + y1 W + y2 W^2 (W = 2^32; W^2 = W - 1, W^3 = -1, W^4 = -W mod q):
+//   a = 0:  (y1:y0) + y2 * eps            a = 1:  (y0:0) + y1 * eps - y2            a = 2:  y0 * eps - (y2:y1)
+template <int S>
+GL_HD u64 gl_mul_pow2(u64 x) {
+    static_assert(S >= 0 && S < 96, "exponent must be reduced mod 96 (2^96 = -1)");
+    if (S == 0) return x;
+#if GL_PTX
+    constexpr int r = S & 31, a = S >> 5;
+    const u32 x0 = (u32)x, x1 = (u32)(x >> 32);
+    u32 y0, y1, y2;
+    if (r == 0) {
+        y0 = x0;
+        y1 = x1;
+        y2 = 0;
+    } else {
+        y0 = x0 << r;
+        y1 = __funnelshift_l(x0, x1, r);
+        y2 = x1 >> ((32 - r) & 31);
+    }
+    if (a == 1) return gl_reduce128((u64)y0 << 32, ((u64)y2 << 32) | y1);
+    u32 t0, t1;
+    if (a == 0) {
+        // carry -> += eps (cannot carry again, as in gl_reduce128)
+        asm("{\n\t"
+            ".reg .u32 m;\n\t"
+            "mad.lo.cc.u32 %0, %4, 0xFFFFFFFF, %2;\n\t"
+            "madc.hi.cc.u32 %1, %4, 0xFFFFFFFF, %3;\n\t"
+            "addc.u32 m, 0, 0;\n\t"
+            "sub.cc.u32 %0, %0, m;\n\t"
+            "subc.u32 %1, %1, 0;\n\t"
+            "add.u32 %1, %1, m;\n\t"
+            "}"
+            : "=&r"(t0), "=&r"(t1)
+            : "r"(y0), "r"(y1), "r"(y2));
+    } else {
+        // y0 * eps = (y0:0) - y0 < q; then minus (y2:y1), borrow -> -= eps (cannot borrow again, as in gl_sub)
+        asm("{\n\t"
+            ".reg .u32 m;\n\t"
+            "sub.cc.u32 %0, 0, %2;\n\t"
+            "subc.u32 %1, %2, 0;\n\t"
+            "sub.cc.u32 %0, %0, %3;\n\t"
+            "subc.cc.u32 %1, %1, %4;\n\t"
+            "subc.u32 m, 0, 0;\n\t"
+            "sub.cc.u32 %0, %0, m;\n\t"
+            "subc.u32 %1, %1, 0;\n\t"
+            "}"
+            : "=&r"(t0), "=&r"(t1)
+            : "r"(y0), "r"(y1), "r"(y2));
+    }
+    return ((u64)t1 << 32) | t0;
+#else
+    return gl_mul_lazy(x, S < 64 ? (1ULL << (S & 63)) : (GL_EPS << ((S - 64) & 31)));
+#endif
+}
+
+// the butterflies of tile_stage with w = ROOTS[j] = 2^E, E = gl_root_log2(j) in [0, 192); E >= 96 means w = -2^(E-96)
+template <int E>
+GL_HD void gl_ct_butterfly_pow2(u64 &u, u64 &v) {
+    const u64 t = gl_canon(gl_mul_pow2<E % 96>(v));
+    const u64 lo = gl_sub(u, t), hi = gl_add(u, t);
+    u = (E >= 96) ? lo : hi;
+    v = (E >= 96) ? hi : lo;
+}
+// (u, v) -> (u + v, (v - u) * w)
+template <int E>
+GL_HD void gl_gs_butterfly_neg_pow2(u64 &u, u64 &v) {
+    u64 d;
+    if (E >= 96) {  // (v - u) * -2^(E-96) = (u - v) * 2^(E-96)
+        const u64 vc = gl_canon(v);
+        d = gl_sub(u, vc);
+        u = gl_add(u, vc);
+    } else {
+        const u64 uc = gl_canon(u);
+        d = gl_sub(v, uc);
+        u = gl_add(v, uc);
+    }
+    v = gl_mul_pow2<E % 96>(d);
+}
+
 // ---- the reference's digit rule (vtfhe/glwe_poly.rs:28-50) ------------------------------------
 // digit `li` (0 = least significant) of canonical x for base 2^logB with L = ceil(64/logB) limbs,
 // returned as a canonical field element.  digit_i = k_i + MSB(k_{i-1}) - MSB(k_i)*B, where k_i are

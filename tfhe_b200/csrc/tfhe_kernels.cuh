@@ -119,9 +119,41 @@ TK_DEV void tile_pass_mid(u64 (&x)[16], const u64 *tw, int tau) {
         tile_stage<4, true>(x, tw, 16, b);
     }
 }
+// stage with compile-time power-of-two twiddles (gl64.cuh: ROOTS[j] = 2^gl_root_log2(j) for j < 16): block BLK of the
+// stage with m = M uses ROOTS[M + BLK] (forward) or, for the inverse against the forward table, ROOTS[2M - 1 - BLK]
+template <int SH, bool INV, int M, int BLK = 0>
+TK_DEV void tile_stage_pow2(u64 (&x)[16]) {
+    constexpr int half = 1 << (SH - 1);
+    constexpr int E = gl_root_log2(INV ? 2 * M - 1 - BLK : M + BLK);
+    TK_UNROLL
+    for (int j = 0; j < half; j++) {
+        const int e0 = (BLK << SH) + j;
+        if (INV)
+            gl_gs_butterfly_neg_pow2<E>(x[e0], x[e0 + half]);
+        else
+            gl_ct_butterfly_pow2<E>(x[e0], x[e0 + half]);
+    }
+    if constexpr (BLK + 1 < (16 >> SH)) tile_stage_pow2<SH, INV, M, BLK + 1>(x);
+}
+
 // first forward pass / last inverse pass: stages 0..3 in layout A (twiddles uniform over threads)
 template <bool INV>
 TK_DEV void tile_pass_high(u64 (&x)[16], const u64 *tw) {
+#if !defined(GL_NO_POW2_TWIDDLES)
+    (void)tw;
+    if (!INV) {
+        tile_stage_pow2<4, false, 1>(x);
+        tile_stage_pow2<3, false, 2>(x);
+        tile_stage_pow2<2, false, 4>(x);
+        tile_stage_pow2<1, false, 8>(x);
+    } else {
+        tile_stage_pow2<1, true, 8>(x);
+        tile_stage_pow2<2, true, 4>(x);
+        tile_stage_pow2<3, true, 2>(x);
+        tile_stage_pow2<4, true, 1>(x);
+    }
+    return;
+#endif
     if (!INV) {
         tile_stage<4, false>(x, tw, 1, 0);
         tile_stage<3, false>(x, tw, 2, 0);

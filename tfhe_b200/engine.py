@@ -140,6 +140,8 @@ def lib():
             L.lux_debug_split_mode.argtypes = [_vp, _int]
         if hasattr(L, "lux_debug_ks_splits"):
             L.lux_debug_ks_splits.argtypes = [_vp, _int]
+        if hasattr(L, "lux_debug_ks_mode"):
+            L.lux_debug_ks_mode.argtypes = [_vp, _int]
         if hasattr(L, "lux_debug_int_peak"):
             L.lux_debug_int_peak.argtypes = [_vp, C.POINTER(C.c_double * 3)]
             L.lux_debug_int_peak.restype = _int
@@ -322,6 +324,11 @@ class Engine:
     def ks_splits(self, n: int):
         """key-switch input slices for small batches: 0 automatic, n > 0 forced (1 = single pass)"""
         self._ck(lib().lux_debug_ks_splits(self._h, n))
+
+    def ks_mode(self, mode: int):
+        """LWE key switch kernel: -1 automatic (int8 tensor-core contraction for batches >= 256), 0 integer-pipe
+        kernel only, 1 tensor-core kernel whenever the parameter set is eligible"""
+        self._ck(lib().lux_debug_ks_mode(self._h, mode))
 
     def force_teams(self, t: int):
         lib().lux_debug_force_teams(self._h, t)
