@@ -424,6 +424,15 @@ int lux_engine_create(const lux_params *p, int device, lux_engine **out) {
     e->L_ks = p->logB_ks ? (64 + p->logB_ks - 1) / p->logB_ks : 0;
     std::vector<u64> roots, inv;
     lux_host_ntt_tables(p->N, roots, inv, e->ninv);
+    // the kernels hard-code the twiddles of NTT stages 0..3 as powers of two (gl64.cuh gl_root_log2): refuse to run
+    // if the generated table disagrees
+#if defined(GL_POW2_TWIDDLES)
+    for (u32 j = 0; j < 16 && j < p->N; j++)
+        if (roots[j] != gl_pow_host(2, (u64)gl_root_log2((int)j))) {
+            delete e;
+            CREATE_FAIL(LUX_ERR_INVALID, "internal: ROOTS[%u] is not 2^%d", j, gl_root_log2((int)j));
+        }
+#endif
     bool ok = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) == cudaSuccess;
     ok = ok && cudaMalloc(&e->d_tw_fwd, sizeof(u64) * p->N * 2) == cudaSuccess;
     if (ok) {

@@ -193,7 +193,7 @@ GL_HD void gl_gs_butterfly_neg(u64 &u, u64 &v, u64 w) {
 // omega = 7^((q-1)/32) for EVERY ring size, i.e. the twiddles of NTT stages 0..3 are these constants:
 //     ROOTS[j] = 2^gl_root_log2(j),  j < 16        (checked against the generated table in lux_engine_create)
 // and a butterfly of those stages multiplies by a shift instead of four IMAD.WIDE.
-constexpr int gl_root_log2(int j) {
+GL_HD constexpr int gl_root_log2(int j) {
     constexpr int t[16] = {0, 48, 120, 168, 156, 12, 84, 132, 78, 126, 6, 54, 42, 90, 162, 18};
     return t[j & 15];
 }

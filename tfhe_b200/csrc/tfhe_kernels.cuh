@@ -139,7 +139,9 @@ TK_DEV void tile_stage_pow2(u64 (&x)[16]) {
 // first forward pass / last inverse pass: stages 0..3 in layout A (twiddles uniform over threads)
 template <bool INV>
 TK_DEV void tile_pass_high(u64 (&x)[16], const u64 *tw) {
-#if !defined(GL_NO_POW2_TWIDDLES)
+    // measured on B200 (profiles/r01e_arith_variants.txt): shifts trade four IMAD.WIDE for ~1 more ALU instruction
+    // per butterfly, and the ALU pipe is the one that binds: 390.6 -> 403.9 ms.  Kept as an opt-in variant.
+#if defined(GL_POW2_TWIDDLES)
     (void)tw;
     if (!INV) {
         tile_stage_pow2<4, false, 1>(x);
