@@ -3,11 +3,17 @@
 // sizes in parallel.
 #include "engine.h"
 
-template <int LOGN, int TEAMS>
+template <int LOGN, int TEAMS, int ELL = 0, int LOGB = 0>
 __global__ void __launch_bounds__(Tile<LOGN>::T *TEAMS, 1) blind_rotate_kernel(const BRArgs a) {
     extern __shared__ __align__(16) unsigned char smem[];
-    blind_rotate_body<LOGN, TEAMS>(a, threadIdx.x, blockIdx.x, smem);
+    blind_rotate_body<LOGN, TEAMS, ELL, LOGB>(a, threadIdx.x, blockIdx.x, smem);
 }
+
+// gadgets of the named parameter sets get their own instantiation (compile-time digit rule):
+//   S2 (N = 2048): one 23-bit digit, limb convention logB = 41        S1 (N = 1024, main.rs:23-30): ell = 4, logB = 5
+template <int LOGN> struct NamedGadget { static constexpr int ELL = 0, LOGB = 0; };
+template <> struct NamedGadget<11> { static constexpr int ELL = 1, LOGB = 41; };
+template <> struct NamedGadget<10> { static constexpr int ELL = 4, LOGB = 5; };
 
 template <int LOGN, int TEAMS>
 __global__ void __launch_bounds__(Tile<LOGN>::T *TEAMS, 1) ntt_batch_kernel(const NttArgs a) {
@@ -57,12 +63,17 @@ template <int LOGN, int TEAMS>
 static int launch_br_t(lux_engine *e, const BRArgs &a, cudaStream_t s) {
     constexpr size_t smem = blind_rotate_smem_bytes<LOGN, TEAMS>();
     static bool configured[64] = {};
+    constexpr int GE = NamedGadget<LOGN>::ELL, GB = NamedGadget<LOGN>::LOGB;
     if (!configured[e->device & 63]) {
         CUDA_TRY(e, cudaFuncSetAttribute(blind_rotate_kernel<LOGN, TEAMS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        if (GE) CUDA_TRY(e, cudaFuncSetAttribute(blind_rotate_kernel<LOGN, TEAMS, GE, GB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured[e->device & 63] = true;
     }
     const u32 grid = (a.B + TEAMS - 1) / TEAMS;
-    blind_rotate_kernel<LOGN, TEAMS><<<grid, Tile<LOGN>::T * TEAMS, smem, s>>>(a);
+    if (GE && a.ell == (u32)GE && a.logB == (u32)GB && !e->generic_gadget)
+        blind_rotate_kernel<LOGN, TEAMS, GE, GB><<<grid, Tile<LOGN>::T * TEAMS, smem, s>>>(a);
+    else
+        blind_rotate_kernel<LOGN, TEAMS><<<grid, Tile<LOGN>::T * TEAMS, smem, s>>>(a);
     e->launches++;
     CUDA_TRY(e, cudaGetLastError());
     return LUX_OK;

@@ -526,6 +526,11 @@ int lux_debug_ks_splits(lux_engine *e, int splits) {
     e->ks_splits = splits;
     return LUX_OK;
 }
+int lux_debug_generic_gadget(lux_engine *e, int on) {
+    if (!e) return LUX_ERR_INVALID;
+    e->generic_gadget = on != 0;
+    return LUX_OK;
+}
 int lux_debug_ks_mode(lux_engine *e, int mode) {
     if (!e || mode < -1 || mode > 1) return LUX_ERR_INVALID;
     e->ks_mode = mode;

@@ -20,6 +20,18 @@
 #pragma once
 #include "gl64.cuh"
 
+// Lock step (TK_LOCKSTEP).  The loop body of a blind rotation is ~135 KB of straight-line SASS, four times the 32 KB
+// L1.5 instruction cache, so every team streams it from L2 once per CMUX; teams that drift apart each pay for their own
+// stream (ncu: stall_no_instruction 0.14..0.40 per issue).  Keeping the teams of a CTA at the same place of the code
+// lets them share one stream.  Level 0 = teams only meet at the key ring; 1 = CTA-wide barrier once per CMUX;
+// 2 = once per NTT; 3 = every team barrier is CTA-wide.  Measured on B200 in profiles/r01e_lockstep.txt.
+#ifndef TK_LOCKSTEP
+#define TK_LOCKSTEP 1
+#endif
+// A team handle packs the team index (low 8 bits) and, for kernels whose teams run in lock step, the number of
+// live threads of the CTA (bits 8 and up; 0 = no lock step: batched NTT, external-product kernel, emulator).
+GL_HD int tk_team(int team, int live_threads) { return team | (live_threads << 8); }
+
 #if defined(TFHE_EMU)
 #include <barrier>
 struct EmuBlock {
@@ -28,16 +40,37 @@ struct EmuBlock {
 };
 extern thread_local EmuBlock *g_emu_blk;
 inline void cta_sync() { g_emu_blk->cta->arrive_and_wait(); }
-inline void team_sync(int team, int /*nthreads*/) { g_emu_blk->team[team]->arrive_and_wait(); }
+inline void team_sync(int team, int /*nthreads*/) { g_emu_blk->team[team & 0xff]->arrive_and_wait(); }
+template <int LEVEL> inline void lockstep_point(int /*team*/) {}
+inline void team_sync_outer(int team, int nthreads) { team_sync(team, nthreads); }
 #define TK_DEV inline
 #define TK_UNROLL
 #else
 __device__ __forceinline__ void cta_sync() { __syncthreads(); }
+__device__ __forceinline__ void live_sync(int live_threads) {
+    asm volatile("bar.sync 15, %0;" ::"r"(live_threads) : "memory");
+}
 __device__ __forceinline__ void team_sync(int team, int nthreads) {
+    if (TK_LOCKSTEP >= 3 && (team >> 8)) {
+        live_sync(team >> 8);
+        return;
+    }
     if (nthreads == 32)
         __syncwarp();
     else
-        asm volatile("bar.sync %0, %1;" ::"r"(team + 1), "r"(nthreads) : "memory");
+        asm volatile("bar.sync %0, %1;" ::"r"((team & 0xff) + 1), "r"(nthreads) : "memory");
+}
+// extra CTA-wide meeting point of lock-step level LEVEL (no-op at other levels and for plain team handles)
+template <int LEVEL>
+__device__ __forceinline__ void lockstep_point(int team) {
+    if (TK_LOCKSTEP == LEVEL && (team >> 8)) live_sync(team >> 8);
+}
+// the team barrier that closes a CMUX: CTA-wide from level 1 on
+__device__ __forceinline__ void team_sync_outer(int team, int nthreads) {
+    if (TK_LOCKSTEP >= 1 && (team >> 8))
+        live_sync(team >> 8);
+    else
+        team_sync(team, nthreads);
 }
 #define TK_DEV __device__ __forceinline__
 #define TK_UNROLL _Pragma("unroll")
@@ -178,6 +211,7 @@ TK_DEV void tile_pass_high(u64 (&x)[16], const u64 *tw) {
 template <int LOGN>
 TK_DEV void team_ntt_forward(u64 (&x)[16], u64 *xb, const u64 *tw, int tau, int team) {
     constexpr int T = Tile<LOGN>::T;
+    lockstep_point<2>(team);
     tile_pass_high<false>(x, tw);
     team_sync(team, T);
     TK_UNROLL
@@ -198,6 +232,7 @@ TK_DEV void team_ntt_forward(u64 (&x)[16], u64 *xb, const u64 *tw, int tau, int 
 template <int LOGN>
 TK_DEV void team_ntt_inverse(u64 (&x)[16], u64 *xb, const u64 *tw, int tau, int team) {
     constexpr int T = Tile<LOGN>::T;
+    lockstep_point<2>(team);
     tile_pass_low<LOGN, true>(x, tw, tau);
     team_sync(team, T);
     TK_UNROLL
@@ -363,18 +398,25 @@ __device__ __forceinline__ void stream_issue(const KeyStream &ks, u32 t) {
 //   cmux = false: acc <- GGSW (x) acc                                  (ivc_based_vpbs.rs:116-121)
 // STAGED: the GGSW's row pairs are the next 2*ell entries of the CTA-shared key stream; otherwise they
 // are read from `ggsw` in global memory (independent keys per ciphertext: external_product_kernel, emulator).
-template <int LOGN, bool STAGED>
+// ELL / LOGB != 0 fix the gadget at compile time (the named parameter sets): the digit rule then folds to a few
+// shifts instead of 64-bit variable shifts and selects per coefficient.  0 = read it from BRArgs.
+template <int LOGN, bool STAGED, int ELL = 0, int LOGB = 0>
 TK_DEV void team_external_product(const BRArgs &a, const u64 *ggsw, KeyStream &ks, bool cmux, u32 sh, u64 *acc, u64 *xb,
                                   const u64 *tw, int tau, int team, int lane) {
     constexpr int N = Tile<LOGN>::N, T = Tile<LOGN>::T;
-    const bool centred = (a.L * a.logB == 64);
+    const u32 g_ell = ELL ? (u32)ELL : a.ell, g_logB = LOGB ? (u32)LOGB : a.logB;
+    const u32 g_L = LOGB ? (u32)((64 + (LOGB ? LOGB : 1) - 1) / (LOGB ? LOGB : 1)) : a.L;
+    const bool centred = (g_L * g_logB == 64);
     u64 o0[16], o1[16];
     TK_UNROLL
     for (int e = 0; e < 16; e++) o0[e] = o1[e] = 0;
 
     for (int j = 0; j < 2; j++) {
         const u64 *poly = acc + j * N;
-        for (u32 lvl = 0; lvl < a.ell; lvl++) {
+#if !defined(TFHE_EMU)
+#pragma unroll 1
+#endif
+        for (u32 lvl = 0; lvl < g_ell; lvl++) {
             u64 x[16];
             TK_UNROLL
             for (int e = 0; e < 16; e++) {
@@ -382,7 +424,7 @@ TK_DEV void team_external_product(const BRArgs &a, const u64 *ggsw, KeyStream &k
                 u64 d = poly[p];
                 // both operands canonical, so gl_sub's result (a - b, plus q on borrow) already is
                 if (cmux) d = gl_sub(rotated_coeff<LOGN>(poly, p, sh), d);
-                x[e] = gl_digit(d, a.L - a.ell + lvl, a.logB, centred);   // glev_ct.rs:97-99: top ell limbs
+                x[e] = gl_digit(d, g_L - g_ell + lvl, g_logB, centred);   // glev_ct.rs:97-99: top ell limbs
             }
             team_ntt_forward<LOGN>(x, xb, tw, tau, team);
             const u64 *rows;
@@ -393,7 +435,7 @@ TK_DEV void team_external_product(const BRArgs &a, const u64 *ggsw, KeyStream &k
                 rows = ks.stage + (size_t)(ks.t % NS) * 2 * N;
             } else
 #endif
-                rows = ggsw + ((size_t)(j * a.ell + lvl) * 2) * N;
+                rows = ggsw + ((size_t)(j * g_ell + lvl) * 2) * N;
             TK_UNROLL
             for (int h = 0; h < 8; h++) {
                 // elements key_pos(tau, 2h), key_pos(tau, 2h+1) of both rows: one 16-byte access each
@@ -441,7 +483,7 @@ TK_DEV void team_external_product(const BRArgs &a, const u64 *ggsw, KeyStream &k
             o0[e] = o1[e];
         }
     }
-    team_sync(team, T);  // next iteration gathers rotated coefficients written by other threads
+    team_sync_outer(team, T);  // next iteration gathers rotated coefficients written by other threads
 }
 
 // shared memory: [tw N] then per team [acc 2N][xb N], then the key ring [NSTAGE][2N] and its mbarriers
@@ -450,7 +492,7 @@ constexpr size_t blind_rotate_smem_bytes() {
     return sizeof(u64) * ((size_t)Tile<LOGN>::N + (size_t)TEAMS * 3 * Tile<LOGN>::N + (size_t)StageCfg<LOGN>::NSTAGE * 2 * Tile<LOGN>::N) + 64;
 }
 
-template <int LOGN, int TEAMS>
+template <int LOGN, int TEAMS, int ELL = 0, int LOGB = 0>
 TK_DEV void blind_rotate_body(const BRArgs &a, int tid, int bid, unsigned char *smem_raw) {
     constexpr int N = Tile<LOGN>::N, T = Tile<LOGN>::T, NS = StageCfg<LOGN>::NSTAGE;
     u64 *tw = (u64 *)smem_raw;
@@ -483,6 +525,13 @@ TK_DEV void blind_rotate_body(const BRArgs &a, int tid, int bid, unsigned char *
 #endif
     cta_sync();
     const u32 ct = (u32)bid * TEAMS + team;
+    // team handle for the barriers: with lock step it carries the live thread count of this CTA (ragged last CTA)
+#if !defined(TFHE_EMU)
+    // (only the compile-time-gadget instantiations: the longer runtime-gadget body measured slower in lock step)
+    const int th = tk_team(team, ELL ? (int)((a.B - (u32)bid * TEAMS < (u32)TEAMS ? a.B - (u32)bid * TEAMS : (u32)TEAMS) * T) : 0);
+#else
+    const int th = team;
+#endif
     if (ct >= a.B) return;  // whole team leaves; only team barriers and the key-stream mbarriers are used from here on
 #if !defined(TFHE_EMU)
     if (ks.producer)
@@ -502,7 +551,7 @@ TK_DEV void blind_rotate_body(const BRArgs &a, int tid, int bid, unsigned char *
             acc[N + p] = rotated_coeff<LOGN>(tv, p, sh0);
         }
     }
-    team_sync(team, T);
+    team_sync(th, T);
 
     // steps CMUX iterations, then (in-tree order) the GLWE key switch as one more external product: one
     // call site, so the loop body exists once in the instruction stream
@@ -513,7 +562,7 @@ TK_DEV void blind_rotate_body(const BRArgs &a, int tid, int bid, unsigned char *
         const bool cmux = i < a.steps;
         const u32 sh = cmux ? gl_mod_switch(mask, LOGN) : 0;
         if (i + 1 < a.steps) mask = lwe[i + 1];  // fetched one iteration ahead
-        team_external_product<LOGN, true>(a, cmux ? a.bsk + i * ggsw_len : a.ksk, ks, cmux, sh, acc, xb, tw, tau, team, lane);
+        team_external_product<LOGN, true, ELL, LOGB>(a, cmux ? a.bsk + i * ggsw_len : a.ksk, ks, cmux, sh, acc, xb, tw, tau, th, lane);
     }
 
     // exit: sample extraction of coefficient 0      crypto/glwe.rs:96-113

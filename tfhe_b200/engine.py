@@ -140,6 +140,8 @@ def lib():
             L.lux_debug_split_mode.argtypes = [_vp, _int]
         if hasattr(L, "lux_debug_ks_splits"):
             L.lux_debug_ks_splits.argtypes = [_vp, _int]
+        if hasattr(L, "lux_debug_generic_gadget"):
+            L.lux_debug_generic_gadget.argtypes = [_vp, _int]
         if hasattr(L, "lux_debug_ks_mode"):
             L.lux_debug_ks_mode.argtypes = [_vp, _int]
         if hasattr(L, "lux_debug_int_peak"):
@@ -324,6 +326,11 @@ class Engine:
     def ks_splits(self, n: int):
         """key-switch input slices for small batches: 0 automatic, n > 0 forced (1 = single pass)"""
         self._ck(lib().lux_debug_ks_splits(self._h, n))
+
+    def generic_gadget(self, on: bool):
+        """tests / A-B: run the blind-rotate instantiation that reads the gadget from its arguments even where a
+        compile-time instantiation for the named parameter set exists"""
+        self._ck(lib().lux_debug_generic_gadget(self._h, int(bool(on))))
 
     def ks_mode(self, mode: int):
         """LWE key switch kernel: -1 automatic (int8 tensor-core contraction for batches >= 256), 0 integer-pipe
