@@ -21,11 +21,11 @@ for name, params in (("S2", T.S2_SHORTINT), ("S1", T.S1_BOOLEAN)):
     rs = np.random.RandomState(1)
     tv = torch.from_numpy((rs.randint(0, 2**62, size=(1, params.N), dtype=np.int64))).cuda()
     eng.set_timing(True)
-    for B in (1, 8, 64, 148, 296, 444):
+    for B in (1, 8, 64, 74, 148, 296, 444):
         cts = torch.from_numpy(rs.randint(0, 2**62, size=(B, params.ct_len), dtype=np.int64)).cuda()
         out = torch.empty_like(cts)
         row = []
-        for mode in (0, 1):
+        for mode in (0, 1, 2):
             eng.split_mode(mode)
             ts = []
             for _ in range(4):
@@ -33,5 +33,6 @@ for name, params in (("S2", T.S2_SHORTINT), ("S1", T.S1_BOOLEAN)):
                 ts.append(eng.last_timing())
             row.append(min(t[0] for t in ts[1:]))
             row.append(min(t[1] for t in ts[1:]))
-        print(f"{name} B={B:4d}  throughput-mode ks {row[0]:7.3f} br {row[1]:8.3f} ms | latency-mode ks {row[2]:7.3f} br {row[3]:8.3f} ms", flush=True)
+        print(f"{name} B={B:4d}  throughput-mode ks {row[0]:7.3f} br {row[1]:8.3f} ms | latency-mode ks {row[2]:7.3f} br {row[3]:8.3f} ms"
+              f" | cluster-mode ks {row[4]:7.3f} br {row[5]:8.3f} ms", flush=True)
     eng.split_mode(-1)

@@ -343,11 +343,22 @@ def test_latency_mode_equals_throughput_mode(which, rig_small0, rig_small1, rig_
     try:
         r.eng.split_mode(1)
         fast = r.eng.pbs_batch(cts, tvs, idx)
+        r.eng.split_mode(2)          # one ciphertext per 2-CTA cluster, partials exchanged through distributed shared memory
+        pair = r.eng.pbs_batch(cts, tvs, idx)
         r.eng.split_mode(0)
         bulk = r.eng.pbs_batch(cts, tvs, idx)
+        r.eng.generic_gadget(True)   # runtime-gadget instantiations of all three kernels
+        r.eng.split_mode(2)
+        pair_g = r.eng.pbs_batch(cts, tvs, idx)
+        r.eng.split_mode(0)
+        bulk_g = r.eng.pbs_batch(cts, tvs, idx)
     finally:
+        r.eng.generic_gadget(False)
         r.eng.split_mode(-1)
     assert np.array_equal(fast, bulk)
+    assert np.array_equal(pair, bulk)
+    assert np.array_equal(pair_g, bulk)
+    assert np.array_equal(bulk_g, bulk)
     want, _ = r.ctx.pbs_batch(cts[:2], tvs, idx[:2])
     assert np.array_equal(fast[:2], want)
     assert [O.decode(O.lwe_decrypt(r.ks.s_in, c), delta, 2 * p) for c in fast] == [luts[idx[b]][msgs[b]] for b in range(B)]

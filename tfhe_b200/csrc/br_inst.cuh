@@ -117,10 +117,10 @@ static int launch_xp_t(lux_engine *e, const BRArgs &a, const u64 *d_glwe, size_t
 }
 
 // latency mode (tfhe_kernels.cuh "latency mode"): one ciphertext per CTA, G = 2*ell teams
-template <int LOGN, int G>
+template <int LOGN, int G, int ELL = 0, int LOGB = 0>
 __global__ void __launch_bounds__(Tile<LOGN>::T *G, 1) blind_rotate_split_kernel(const BRArgs a) {
     extern __shared__ __align__(16) unsigned char smem[];
-    blind_rotate_split_body<LOGN, G>(a, threadIdx.x, blockIdx.x, smem);
+    blind_rotate_split_body<LOGN, G, ELL, LOGB>(a, threadIdx.x, blockIdx.x, smem);
 }
 
 template <int LOGN, int G>
@@ -128,20 +128,81 @@ static int launch_br_split_t(lux_engine *e, const BRArgs &a, cudaStream_t s) {
     constexpr size_t smem = blind_rotate_split_smem_bytes<LOGN, G>();
     static_assert(smem <= 227 * 1024 && Tile<LOGN>::T * G <= 1024, "latency-mode configuration does not fit an SM");
     static bool configured[64] = {};
+    constexpr int GE = NamedGadget<LOGN>::ELL, GB = NamedGadget<LOGN>::LOGB;
+    constexpr bool NAMED = GE != 0 && G == 2 * GE;
     if (!configured[e->device & 63]) {
         CUDA_TRY(e, cudaFuncSetAttribute(blind_rotate_split_kernel<LOGN, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        if (NAMED) CUDA_TRY(e, cudaFuncSetAttribute(blind_rotate_split_kernel<LOGN, G, NAMED ? GE : 0, NAMED ? GB : 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured[e->device & 63] = true;
     }
-    blind_rotate_split_kernel<LOGN, G><<<a.B, Tile<LOGN>::T * G, smem, s>>>(a);
+    if (NAMED && a.ell == (u32)GE && a.logB == (u32)GB && !e->generic_gadget)
+        blind_rotate_split_kernel<LOGN, G, NAMED ? GE : 0, NAMED ? GB : 0><<<a.B, Tile<LOGN>::T * G, smem, s>>>(a);
+    else
+        blind_rotate_split_kernel<LOGN, G><<<a.B, Tile<LOGN>::T * G, smem, s>>>(a);
     e->launches++;
     CUDA_TRY(e, cudaGetLastError());
     return LUX_OK;
+}
+
+// cluster latency mode (tfhe_kernels.cuh "cluster latency mode"): one ciphertext per 2-CTA cluster, TPC = ell teams per CTA
+template <int LOGN, int TPC, int ELL = 0, int LOGB = 0>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Tile<LOGN>::T *TPC, 1) blind_rotate_cluster_kernel(const BRArgs a) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    blind_rotate_cluster_body<LOGN, TPC, ELL, LOGB>(a, threadIdx.x, blockIdx.x, smem);
+}
+
+template <int LOGN, int TPC>
+static int launch_br_cluster_t(lux_engine *e, const BRArgs &a, cudaStream_t s) {
+    constexpr size_t smem = blind_rotate_cluster_smem_bytes<LOGN, TPC>();
+    static_assert(smem <= 227 * 1024 && Tile<LOGN>::T * TPC <= 1024, "cluster latency-mode configuration does not fit an SM");
+    constexpr int GE = NamedGadget<LOGN>::ELL, GB = NamedGadget<LOGN>::LOGB;
+    constexpr bool NAMED = GE != 0 && TPC == GE;
+    static bool configured[64] = {};
+    if (!configured[e->device & 63]) {
+        CUDA_TRY(e, cudaFuncSetAttribute(blind_rotate_cluster_kernel<LOGN, TPC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        if (NAMED) CUDA_TRY(e, cudaFuncSetAttribute(blind_rotate_cluster_kernel<LOGN, TPC, NAMED ? GE : 0, NAMED ? GB : 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured[e->device & 63] = true;
+    }
+    if (NAMED && a.ell == (u32)GE && a.logB == (u32)GB && !e->generic_gadget)
+        blind_rotate_cluster_kernel<LOGN, TPC, NAMED ? GE : 0, NAMED ? GB : 0><<<2 * a.B, Tile<LOGN>::T * TPC, smem, s>>>(a);
+    else
+        blind_rotate_cluster_kernel<LOGN, TPC><<<2 * a.B, Tile<LOGN>::T * TPC, smem, s>>>(a);
+    e->launches++;
+    CUDA_TRY(e, cudaGetLastError());
+    return LUX_OK;
+}
+
+// 1 = launched, 0 = not applicable for this ring size / gadget
+static int try_launch_cluster(lux_engine *e, const BRArgs &a, cudaStream_t s) {
+    int rc = 0;
+    bool done = true;
+#if LUX_LOGN <= 10
+    if (a.ell == 1) rc = launch_br_cluster_t<LUX_LOGN, 1>(e, a, s);
+    else if (a.ell == 2) rc = launch_br_cluster_t<LUX_LOGN, 2>(e, a, s);
+    else if (a.ell == 3) rc = launch_br_cluster_t<LUX_LOGN, 3>(e, a, s);
+    else if (a.ell == 4) rc = launch_br_cluster_t<LUX_LOGN, 4>(e, a, s);
+    else done = false;
+#elif LUX_LOGN == 11
+    if (a.ell == 1) rc = launch_br_cluster_t<11, 1>(e, a, s);
+    else if (a.ell == 2) rc = launch_br_cluster_t<11, 2>(e, a, s);
+    else done = false;
+#else
+    if (a.ell == 1) rc = launch_br_cluster_t<12, 1>(e, a, s);
+    else done = false;
+#endif
+    if (rc) return rc;
+    return done ? 1 : 0;
 }
 
 // 1 = launched in latency mode, 0 = not applicable (caller falls through to the throughput kernel), < 0 = error
 static int try_launch_split(lux_engine *e, const BRArgs &a, cudaStream_t s) {
     // automatic: only when the batch leaves SMs idle anyway, and not when a tuning run pinned the team count
     if (e->split_mode == 0 || (e->split_mode < 0 && (a.B > (u32)e->sm_count || e->force_teams > 0))) return 0;
+    // two SMs per ciphertext while the batch leaves at least half of them idle (or when forced: mode 2)
+    if (e->split_mode == 2 || (e->split_mode < 0 && 2 * a.B <= (u32)e->sm_count)) {
+        const int c = try_launch_cluster(e, a, s);
+        if (c) return c;
+    }
     int rc = 0;
     bool done = true;
 #if LUX_LOGN <= 10
@@ -193,6 +254,9 @@ int LUX_CAT(lux_launch_br_, LUX_LOGN)(lux_engine *e, const BRArgs &a, cudaStream
 size_t LUX_CAT(lux_br_wave_, LUX_LOGN)(const lux_engine *e, size_t B) {
     if (e->split_mode != 0 && (e->split_mode > 0 || (B <= (size_t)e->sm_count && e->force_teams <= 0))) {
         const u32 ell = e->p.ell;
+        if ((e->split_mode == 2 || (e->split_mode < 0 && 2 * B <= (size_t)e->sm_count)) &&
+            ((LUX_LOGN <= 10 && ell <= 4) || (LUX_LOGN == 11 && ell <= 2) || (LUX_LOGN == 12 && ell == 1)))
+            return (size_t)e->sm_count / 2;
         if ((LUX_LOGN <= 10 && ell <= 4) || (LUX_LOGN == 11 && ell <= 2)) return (size_t)e->sm_count;
     }
 #if LUX_LOGN == 9

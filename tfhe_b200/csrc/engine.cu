@@ -537,7 +537,7 @@ int lux_debug_ks_mode(lux_engine *e, int mode) {
     return LUX_OK;
 }
 int lux_debug_split_mode(lux_engine *e, int mode) {
-    if (!e || mode < -1 || mode > 1) return LUX_ERR_INVALID;
+    if (!e || mode < -1 || mode > 2) return LUX_ERR_INVALID;
     e->split_mode = mode;
     return LUX_OK;
 }

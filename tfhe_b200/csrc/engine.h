@@ -44,7 +44,8 @@ struct lux_engine {
     size_t ks_dig_bytes = 0;
     int ks_mode = -1;         // -1 = automatic (batches >= 256), 0 = integer-pipe kernel only, 1 = tensor-core kernel whenever eligible
     bool generic_gadget = false;  // tests: run the runtime-gadget kernel even where a compile-time instantiation exists
-    int split_mode = -1;  // latency-mode blind rotate: -1 = automatic (B <= #SMs), 0 = never, 1 = always (tests)
+    int split_mode = -1;  // latency-mode blind rotate: -1 = automatic (2B <= #SMs: cluster kernel, B <= #SMs: split kernel), 0 = never,
+                          // 1 = split kernel always, 2 = cluster kernel always (tests)
     struct RadixState *radix = nullptr;  // euintN layer (radix.cu), created on first use
     char err[512] = "";
 };

@@ -594,17 +594,19 @@ constexpr size_t blind_rotate_split_smem_bytes() {
     return sizeof(u64) * ((size_t)3 * Tile<LOGN>::N + (size_t)G * 2 * Tile<LOGN>::N);
 }
 
-template <int LOGN, int G>
+template <int LOGN, int G, int ELL = 0, int LOGB = 0>
 TK_DEV void blind_rotate_split_body(const BRArgs &a, int tid, int bid, unsigned char *smem_raw) {
     constexpr int N = Tile<LOGN>::N, T = Tile<LOGN>::T;
     u64 *tw = (u64 *)smem_raw;
     u64 *acc = tw + N;
     u64 *part = acc + 2 * N;  // [G][2][N]
     const int g = tid / T, tau = tid % T;
-    const int j = g / (int)a.ell;
-    const u32 lvl = (u32)g % a.ell;
+    const u32 g_ell = ELL ? (u32)ELL : a.ell, g_logB = LOGB ? (u32)LOGB : a.logB;
+    const u32 g_L = LOGB ? (u32)((64 + (LOGB ? LOGB : 1) - 1) / (LOGB ? LOGB : 1)) : a.L;
+    const int j = g / (int)g_ell;
+    const u32 lvl = (u32)g % g_ell;
     u64 *mine = part + (size_t)g * 2 * N;
-    const bool centred = (a.L * a.logB == 64);
+    const bool centred = (g_L * g_logB == 64);
     for (int i = tid; i < N; i += T * G) tw[i] = a.tw_fwd[i];
     const u32 ct = (u32)bid;
     const u64 *lwe = a.lwe + (size_t)ct * (a.n + 1);
@@ -617,7 +619,7 @@ TK_DEV void blind_rotate_split_body(const BRArgs &a, int tid, int bid, unsigned 
         }
     }
     cta_sync();
-    const size_t ggsw_len = (size_t)4 * a.ell * N;
+    const size_t ggsw_len = (size_t)4 * g_ell * N;
     const u32 iters = a.steps + (a.ksk ? 1u : 0u);
     u64 mask = a.steps ? lwe[0] : 0;
     for (u32 i = 0; i < iters; i++) {
@@ -632,7 +634,7 @@ TK_DEV void blind_rotate_split_body(const BRArgs &a, int tid, int bid, unsigned 
                 const int p = posA<LOGN>(tau, e);
                 u64 d = poly[p];
                 if (cmux) d = gl_sub(rotated_coeff<LOGN>(poly, p, sh), d);
-                x[e] = gl_digit(d, a.L - a.ell + lvl, a.logB, centred);
+                x[e] = gl_digit(d, g_L - g_ell + lvl, g_logB, centred);
             }
             team_ntt_forward<LOGN>(x, mine, tw, tau, g);
             const u64 *rows = (cmux ? a.bsk + i * ggsw_len : a.ksk) + (size_t)g * 2 * N;
@@ -683,6 +685,143 @@ TK_DEV void blind_rotate_split_body(const BRArgs &a, int tid, int bid, unsigned 
         if (tid == 0) o[len] = gl_canon(gl_add(acc[N], a.body_add));
     }
 }
+
+// ---- cluster latency mode: ONE ciphertext per CLUSTER of two CTAs (two SMs) ------------------------------------
+// The latency-mode kernel above still runs the 2*ell forward and the 2 inverse transforms of a CMUX on one SM, whose
+// integer pipes are what bounds it.  Here CTA r of a 2-CTA thread-block cluster owns accumulator polynomial r:
+//   phase 1  its ell teams decompose (X^a * acc_r - acc_r), transform the digits and multiply them with the row pairs
+//            (r, lvl) of the GGSW: partial products towards BOTH output polynomials, left in its own shared memory;
+//   cluster barrier (release/acquire);
+//   phase 2  team 0 adds the ell local partials of output r and the ell partials of the peer CTA (read through
+//            distributed shared memory, ld.shared::cluster), runs the inverse transform and updates acc_r.
+// Partials are double-buffered by iteration parity, so one cluster barrier per CMUX orders everything: a CTA
+// overwrites buffer `par` two iterations later, after its peer passed the barrier in between, i.e. after the peer's
+// reads.  Exact sums in Z_q: same words as the other two kernels.
+// shared memory per CTA: [tw N][acc_r N] then per team [xb N][part: 2 parities x 2 outputs x N]
+#if !defined(TFHE_EMU)
+template <int LOGN, int TPC>
+constexpr size_t blind_rotate_cluster_smem_bytes() {
+    return sizeof(u64) * ((size_t)2 * Tile<LOGN>::N + (size_t)TPC * 5 * Tile<LOGN>::N);
+}
+__device__ __forceinline__ u32 cluster_ctarank() {
+    u32 r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ u32 cluster_map(const void *p, u32 rank) {
+    u32 out;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(out) : "r"(tk_smem_addr(p)), "r"(rank));
+    return out;
+}
+__device__ __forceinline__ u64 cluster_ld(u32 addr) {
+    u64 v;
+    asm volatile("ld.shared::cluster.u64 %0, [%1];" : "=l"(v) : "r"(addr) : "memory");
+    return v;
+}
+
+template <int LOGN, int TPC, int ELL = 0, int LOGB = 0>
+__device__ __forceinline__ void blind_rotate_cluster_body(const BRArgs &a, int tid, int bid, unsigned char *smem_raw) {
+    constexpr int N = Tile<LOGN>::N, T = Tile<LOGN>::T;
+    const u32 g_ell = ELL ? (u32)ELL : a.ell, g_logB = LOGB ? (u32)LOGB : a.logB;
+    const u32 g_L = LOGB ? (u32)((64 + (LOGB ? LOGB : 1) - 1) / (LOGB ? LOGB : 1)) : a.L;
+    const bool centred = (g_L * g_logB == 64);
+    const u32 r = cluster_ctarank();   // which accumulator polynomial this CTA owns (0 = mask, 1 = body)
+    const u32 ct = (u32)bid >> 1;
+    u64 *tw = (u64 *)smem_raw;
+    u64 *acc = tw + N;                 // acc_r only
+    const int lvl = tid / T, tau = tid % T;
+    u64 *xb = acc + N + (size_t)lvl * 5 * N;
+    u64 *part = xb + N;                // [2 parities][2 outputs][N]
+    for (int i = tid; i < N; i += T * TPC) tw[i] = a.tw_fwd[i];
+    const u64 *lwe = a.lwe + (size_t)ct * (a.n + 1);
+    const u64 *tv = a.testv + (size_t)(a.lut_idx ? a.lut_idx[ct / a.lut_div] : 0) * N;
+    {
+        const u32 sh0 = gl_mod_switch(gl_neg(lwe[a.n]), LOGN);
+        for (int p = tid; p < N; p += T * TPC) acc[p] = r ? rotated_coeff<LOGN>(tv, p, sh0) : 0;
+    }
+    cta_sync();
+    // peer's partial buffers towards MY output polynomial: same offsets in the peer's shared memory
+    const u32 peer_part0 = cluster_map(acc + N + N, r ^ 1u);   // team 0's `part` of the peer
+    const size_t ggsw_len = (size_t)4 * g_ell * N;
+    const u32 iters = a.steps + (a.ksk ? 1u : 0u);
+    u64 mask = a.steps ? lwe[0] : 0;
+    for (u32 i = 0; i < iters; i++) {
+        const bool cmux = i < a.steps;
+        const u32 sh = cmux ? gl_mod_switch(mask, LOGN) : 0;
+        if (i + 1 < a.steps) mask = lwe[i + 1];
+        const u32 par = i & 1u;
+        {   // phase 1: team lvl, digit polynomial (r, lvl)
+            u64 x[16];
+            TK_UNROLL
+            for (int e = 0; e < 16; e++) {
+                const int p = posA<LOGN>(tau, e);
+                u64 d = acc[p];
+                if (cmux) d = gl_sub(rotated_coeff<LOGN>(acc, p, sh), d);
+                x[e] = gl_digit(d, g_L - g_ell + (u32)lvl, g_logB, centred);
+            }
+            team_ntt_forward<LOGN>(x, xb, tw, tau, lvl);
+            const u64 *rows = (cmux ? a.bsk + i * ggsw_len : a.ksk) + ((size_t)r * g_ell + (u32)lvl) * 2 * N;
+            u64 *mine = part + (size_t)par * 2 * N;
+            TK_UNROLL
+            for (int h = 0; h < 8; h++) {
+                const u64 *r0 = rows + (size_t)h * 2 * T + 2 * tau;
+                const ulonglong2 v0 = *reinterpret_cast<const ulonglong2 *>(r0);
+                const ulonglong2 v1 = *reinterpret_cast<const ulonglong2 *>(r0 + N);
+                mine[(2 * h) * T + tau] = gl_mul(x[2 * h], v0.x);
+                mine[(2 * h + 1) * T + tau] = gl_mul(x[2 * h + 1], v0.y);
+                mine[N + (2 * h) * T + tau] = gl_mul(x[2 * h], v1.x);
+                mine[N + (2 * h + 1) * T + tau] = gl_mul(x[2 * h + 1], v1.y);
+            }
+        }
+        cluster_sync_all();
+        if (lvl == 0) {  // phase 2: output polynomial r = my partials towards r + the peer's partials towards r
+            u64 o[16];
+            const size_t off = ((size_t)par * 2 + r) * N;
+            TK_UNROLL
+            for (int e = 0; e < 16; e++) o[e] = part[off + e * T + tau];
+            for (u32 l2 = 1; l2 < g_ell; l2++) {
+                const u64 *src = part + (size_t)l2 * 5 * N + off;
+                TK_UNROLL
+                for (int e = 0; e < 16; e++) o[e] = gl_add(o[e], src[e * T + tau]);
+            }
+            for (u32 l2 = 0; l2 < g_ell; l2++) {
+                const u32 base = peer_part0 + (u32)(((size_t)l2 * 5 * N + off) * sizeof(u64));
+                u64 v[16];
+                TK_UNROLL
+                for (int e = 0; e < 16; e++) v[e] = cluster_ld(base + (u32)((e * T + tau) * sizeof(u64)));
+                TK_UNROLL
+                for (int e = 0; e < 16; e++) o[e] = gl_add(o[e], v[e]);
+            }
+            team_ntt_inverse<LOGN>(o, xb, tw, tau, 0);
+            TK_UNROLL
+            for (int e = 0; e < 16; e++) {
+                const int p = posA<LOGN>(tau, e);
+                acc[p] = cmux ? gl_canon(gl_add(o[e], acc[p])) : gl_canon(o[e]);
+            }
+        }
+        if (TPC == 1)
+            team_sync(0, T);
+        else
+            cta_sync();
+    }
+    cluster_sync_all();   // the peer may still be reading my partials of the last iteration
+    if (a.out_mode == 2) {
+        u64 *o = a.out + (size_t)ct * 2 * N + (size_t)r * N;
+        for (int p = tid; p < N; p += T * TPC) o[p] = acc[p];
+    } else {
+        const u32 len = a.out_mode == 1 ? a.n_out : (u32)N;
+        u64 *o = a.out + (size_t)ct * (len + 1);
+        if (r == 0) {
+            for (u32 p = tid; p < len; p += T * TPC) o[p] = p ? gl_neg(acc[N - p]) : acc[0];
+        } else if (tid == 0) {
+            o[len] = gl_canon(gl_add(acc[0], a.body_add));
+        }
+    }
+}
+#endif
 
 // ---------------------------------------------------------------------------------- LWE key switch
 // out[b] = (0,..,0,body_b) + sum_i sum_j digit_j(a_{b,i}) * KSK[i][j]         (vtfhe/mod.rs:31-54)
