@@ -1,0 +1,175 @@
+/**
+ * @luxfhe/b200 — TypeScript host side of the B200 evaluation engine.
+ *
+ * Mirrors the evaluation half of the reference's `LuxFHE` object
+ * (reference: packages/wasm/src/index.ts:14-23; Node loader packages/wasm/src/node.ts:29-96; HTTP twin
+ * js/v2-sdk/src/luxd/client.ts:34-39,128-147) over the N-API addon in luxfhe_b200_napi.c.  Key generation,
+ * encryption and decryption stay on the reference path (`generateKeys`, `encrypt`, `decrypt` are not here):
+ * the caller hands over evaluation keys and ciphertexts as little-endian u64 arrays (SURVEY.md 8b "wire formats").
+ *
+ * Differences a caller of the reference sees:
+ *   - `init()` returns an object bound to one GPU; the bootstrap key is uploaded ONCE (`loadKeys`) and is no
+ *     longer an argument of every call (`add(ct1, ct2, bootstrapKey, secretKey)` -> `add(ct1, ct2)`);
+ *   - every op has a `*Batch` form that takes `batch` integers in one BigUint64Array
+ *     ([batch][blocks][ctWords]); the single-ciphertext methods are the batch-of-one case;
+ *   - evaluation methods return Promises (the addon runs them on the libuv pool);
+ *   - errors keep the reference's messages where it has them ("LuxFHE not initialized. Call init() first.",
+ *     "Evaluation failed: ...").
+ */
+
+/* eslint-disable @typescript-eslint/no-var-requires */
+declare const require: (id: string) => any;
+
+export interface LuxParams {
+  n: number; N: number; k: number; ell: number; logB: number; ellKs: number; logBKs: number;
+  /** 0 = PBS then GLWE key switch (in-tree order), 1 = LWE key switch then PBS (KS_PBS sets) */
+  order: 0 | 1;
+}
+
+/** parameter sets of SURVEY.md Appendix B */
+export const S1_BOOLEAN: LuxParams = { n: 728, N: 1024, k: 1, ell: 4, logB: 5, ellKs: 4, logBKs: 5, order: 0 };
+export const S2_SHORTINT: LuxParams = { n: 918, N: 2048, k: 1, ell: 1, logB: 41, ellKs: 4, logBKs: 4, order: 1 };
+
+/** op codes of include/lux_radix.h (`lux_op`); names follow client.ts:35 and the fhEVM operator list */
+export enum Op {
+  add = 0, sub, mul, neg, eq, ne, lt, le, gt, ge, min, max, and, or, xor, not, shl, shr, rotl, rotr, div, rem,
+}
+export type OpName = keyof typeof Op;
+
+/** gate codes of include/lux_tfhe.h (`lux_gate_batch`) */
+export enum Gate { nand = 0, and, or, nor, xor, xnor }
+
+export interface EvaluationKeys {
+  /** GGSW array [n][k+1][ell][k+1][N], coefficient (0) or NTT (1) domain */
+  bootstrapKey: BigUint64Array;
+  bootstrapKeyDomain?: 0 | 1;
+  /** order 1: LWE key switch key [kN][ellKs][n+1] */
+  lweKeySwitchKey?: BigUint64Array;
+  /** order 0: one GGSW */
+  glweKeySwitchKey?: BigUint64Array;
+  glweKeySwitchKeyDomain?: 0 | 1;
+}
+
+type Handle = unknown;
+interface Native {
+  version(): string;
+  createEngine(p: LuxParams, device?: number): Handle;
+  ctWords(h: Handle): number;
+  radixBlocks(bitWidth: number): number;
+  loadKey(h: Handle, which: 0 | 1 | 2, words: BigUint64Array, domain?: number): void;
+  trivialEncrypt(h: Handle, bitWidth: number, values: BigUint64Array): BigUint64Array;
+  pbsBatch(h: Handle, lwe: BigUint64Array, tvs: BigUint64Array, nLuts: number, idx: Uint32Array | null, batch: number): Promise<BigUint64Array>;
+  evalBatch(h: Handle, op: number, bitWidth: number, lhs: BigUint64Array, rhs: BigUint64Array | null, batch: number, scalar?: number): Promise<BigUint64Array>;
+  selectBatch(h: Handle, bitWidth: number, cond: BigUint64Array, a: BigUint64Array, b: BigUint64Array, batch: number): Promise<BigUint64Array>;
+  erc20TransferBatch(h: Handle, from: BigUint64Array, to: BigUint64Array, amount: BigUint64Array, batch: number): Promise<BigUint64Array>;
+  gateBatch(h: Handle, gate: number, a: BigUint64Array, b: BigUint64Array, batch: number): Promise<BigUint64Array>;
+}
+
+let native: Native | null = null;
+let instance: LuxFHEB200 | null = null;
+
+function loadNative(): Native {
+  if (!native) native = require('./build/Release/luxfhe_b200.node') as Native;
+  return native;
+}
+
+export class LuxFHEB200 {
+  private readonly h: Handle;
+  private readonly n: Native;
+  readonly params: LuxParams;
+  readonly ctWords: number;
+
+  constructor(params: LuxParams, device = 0) {
+    this.n = loadNative();
+    this.h = this.n.createEngine(params, device);   // throws without an sm_100 device: there is no CPU fallback
+    this.params = params;
+    this.ctWords = this.n.ctWords(this.h);
+  }
+
+  version(): string { return this.n.version(); }
+
+  /** upload once; converted to the NTT domain on the device and kept resident in HBM */
+  loadKeys(keys: EvaluationKeys): void {
+    this.n.loadKey(this.h, 0, keys.bootstrapKey, keys.bootstrapKeyDomain ?? 0);
+    if (this.params.order === 1) {
+      if (!keys.lweKeySwitchKey) throw new Error('loadKeys: lweKeySwitchKey is required for KS_PBS parameter sets');
+      this.n.loadKey(this.h, 2, keys.lweKeySwitchKey);
+    } else {
+      if (!keys.glweKeySwitchKey) throw new Error('loadKeys: glweKeySwitchKey is required for PBS_KS parameter sets');
+      this.n.loadKey(this.h, 1, keys.glweKeySwitchKey, keys.glweKeySwitchKeyDomain ?? 0);
+    }
+  }
+
+  blocks(bitWidth: number): number {
+    const b = this.n.radixBlocks(bitWidth);
+    if (!b) throw new Error(`Unsupported bit width: ${bitWidth}`);
+    return b;
+  }
+
+  private batchOf(ct: BigUint64Array, bitWidth: number): number {
+    const per = this.blocks(bitWidth) * this.ctWords;
+    if (ct.length === 0 || ct.length % per !== 0) throw new Error(`ciphertext array is not a multiple of ${per} words`);
+    return ct.length / per;
+  }
+
+  /** POST /evaluate {op, left, right?, bitWidth} (client.ts:128-147) for `batch` integers at once */
+  evalBatch(op: OpName | Op, bitWidth: number, left: BigUint64Array, right: BigUint64Array | null = null): Promise<BigUint64Array> {
+    const code = typeof op === 'number' ? op : Op[op];
+    if (code === undefined) return Promise.reject(new Error(`Evaluation failed: unknown op ${String(op)}`));
+    return this.n.evalBatch(this.h, code, bitWidth, left, right, this.batchOf(left, bitWidth), 0);
+  }
+
+  /** the (euintN, uintN) overloads: one plaintext right operand per integer; div / rem exist only in this form */
+  evalScalarBatch(op: OpName | Op, bitWidth: number, left: BigUint64Array, scalars: BigUint64Array): Promise<BigUint64Array> {
+    const code = typeof op === 'number' ? op : Op[op];
+    return this.n.evalBatch(this.h, code, bitWidth, left, scalars, this.batchOf(left, bitWidth), 1);
+  }
+
+  // the reference's four methods (index.ts:19-22) as the batch-of-one case; bitWidth is explicit because the
+  // engine-native ciphertext carries no header
+  add(ct1: BigUint64Array, ct2: BigUint64Array, bitWidth: number) { return this.evalBatch(Op.add, bitWidth, ct1, ct2); }
+  sub(ct1: BigUint64Array, ct2: BigUint64Array, bitWidth: number) { return this.evalBatch(Op.sub, bitWidth, ct1, ct2); }
+  eq(ct1: BigUint64Array, ct2: BigUint64Array, bitWidth: number) { return this.evalBatch(Op.eq, bitWidth, ct1, ct2); }
+  lt(ct1: BigUint64Array, ct2: BigUint64Array, bitWidth: number) { return this.evalBatch(Op.lt, bitWidth, ct1, ct2); }
+
+  /** cond ? a : b   (FHE.select) — cond is [batch][ctWords] */
+  selectBatch(bitWidth: number, cond: BigUint64Array, a: BigUint64Array, b: BigUint64Array): Promise<BigUint64Array> {
+    return this.n.selectBatch(this.h, bitWidth, cond, a, b, this.batchOf(a, bitWidth));
+  }
+
+  /** WrappingERC20.sol:86-102 on euint64: resolves to { from, to } = new balances */
+  async erc20TransferBatch(from: BigUint64Array, to: BigUint64Array, amount: BigUint64Array): Promise<{ from: BigUint64Array; to: BigUint64Array }> {
+    const out = await this.n.erc20TransferBatch(this.h, from, to, amount, this.batchOf(from, 64));
+    return { from: out.subarray(0, out.length / 2), to: out.subarray(out.length / 2) };
+  }
+
+  /** programmable bootstrap of `batch` LWE ciphertexts with per-ciphertext lookup tables */
+  pbsBatch(lwe: BigUint64Array, testVectors: BigUint64Array, lutIdx: Uint32Array | null = null): Promise<BigUint64Array> {
+    const nLuts = testVectors.length / this.params.N;
+    return this.n.pbsBatch(this.h, lwe, testVectors, nLuts, lutIdx, lwe.length / this.ctWords);
+  }
+
+  /** boolean gates on bits encoded m * q/4 (BASELINE config 1) */
+  gateBatch(gate: Gate, a: BigUint64Array, b: BigUint64Array): Promise<BigUint64Array> {
+    return this.n.gateBatch(this.h, gate, a, b, a.length / (this.params.n + 1));
+  }
+
+  trivialEncrypt(bitWidth: number, values: BigUint64Array): BigUint64Array {
+    return this.n.trivialEncrypt(this.h, bitWidth, values);
+  }
+}
+
+/** same contract as the reference's `init()` (index.ts:40-83): memoised, resolves to the engine object */
+export async function init(params: LuxParams = S2_SHORTINT, device = 0): Promise<LuxFHEB200> {
+  if (!instance) instance = new LuxFHEB200(params, device);
+  return instance;
+}
+
+export function getLuxFHE(): LuxFHEB200 {
+  if (!instance) throw new Error('LuxFHE not initialized. Call init() first.');
+  return instance;
+}
+
+export function isInitialized(): boolean { return instance !== null; }
+
+export default init;

@@ -6,7 +6,7 @@
  *   js/v2-sdk/src/luxd/client.ts:34-39,128-147   POST /evaluate {op: add|sub|eq|lt|gt|and|or|xor|not|shl|shr, left, right?, bitWidth}
  *   examples/erc20-tutorial/contracts/WrappingERC20.sol:86-102   FHE.le / sub / add / select on euint64
  *   mocks/foundry/src/MockFHE.sol:130-508   plaintext semantics of every op
- *   tests/fhevm-suite/e2e/test/fhevmOperations/*.ts   2,394 known-answer tests (tests/golden/fhevm_kats.json)
+ *   tests/fhevm-suite/e2e/test/fhevmOperations/fhevmOperations{1..13}.ts   2,394 known-answer tests (tests/golden/fhevm_kats.json)
  * The reference's own integer layer (Go luxfi/tfhe) is not in the tree; the circuits below are this
  * library's design, their *semantics* are pinned by the known-answer tests above.
  *
