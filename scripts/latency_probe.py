@@ -33,6 +33,16 @@ for name, params in (("S2", T.S2_SHORTINT), ("S1", T.S1_BOOLEAN)):
                 ts.append(eng.last_timing())
             row.append(min(t[0] for t in ts[1:]))
             row.append(min(t[1] for t in ts[1:]))
+        if B <= 74:
+            eng.split_mode(2)
+            for regs in (16, 8, 4):
+                eng.cluster_regs(regs)
+                ts = []
+                for _ in range(4):
+                    eng.pbs_batch_device(cts, tv, None, B, out, n_luts=1)
+                    ts.append(eng.last_timing())
+                print(f"{name} B={B:4d}  cluster mode, {regs:2d} coefficients per thread: br {min(t[1] for t in ts[1:]):8.3f} ms", flush=True)
+            eng.cluster_regs(0)
         print(f"{name} B={B:4d}  throughput-mode ks {row[0]:7.3f} br {row[1]:8.3f} ms | latency-mode ks {row[2]:7.3f} br {row[3]:8.3f} ms"
               f" | cluster-mode ks {row[4]:7.3f} br {row[5]:8.3f} ms", flush=True)
     eng.split_mode(-1)

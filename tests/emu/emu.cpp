@@ -61,6 +61,14 @@ static void emu_br_split_t(const BRArgs &a) {
         run_cta(T * G, T, [&](int tid) { blind_rotate_split_body<LOGN, G>(a, tid, (int)bid, smem.data()); });
 }
 
+template <int LOGN, int R>
+static void emu_ntt_r_t(const NttArgs &a) {
+    constexpr int N = TileR<LOGN, R>::N, T = TileR<LOGN, R>::T;
+    std::vector<unsigned char> smem(sizeof(u64) * 2 * N);
+    for (u32 bid = 0; bid < a.n_polys; bid++)
+        run_cta(T, T, [&](int tid) { ntt_r_body<LOGN, R>(a, tid, (int)bid, smem.data()); });
+}
+
 // reference-order NTT-domain GGSWs [n_ggsw][2][ell][2][N] -> resident key rows (fold + key_pos), as key_format_kernel
 template <int LOGN>
 static void to_key_t(u64 *ggsw, size_t n_polys, u32 ell, u64 ninv) {
@@ -83,6 +91,20 @@ int emu_ntt(int logn, int teams, int nblocks, const u64 *in, u64 *out, const u64
     else if (logn == 11 && teams == 1) emu_ntt_t<11, 1>(a, nblocks);
     else if (logn == 11 && teams == 2) emu_ntt_t<11, 2>(a, nblocks);
     else if (logn == 12 && teams == 1) emu_ntt_t<12, 1>(a, nblocks);
+    else return -1;
+    return 0;
+}
+
+// narrow-tile transform (R = 4 or 8 registers per thread), one polynomial per CTA
+int emu_ntt_r(int logn, int r, const u64 *in, u64 *out, const u64 *tw, u64 scale, u32 n_polys, u32 inverse) {
+    NttArgs a{in, out, tw, scale, n_polys, inverse};
+    if (logn == 9 && r == 8) emu_ntt_r_t<9, 8>(a);
+    else if (logn == 9 && r == 4) emu_ntt_r_t<9, 4>(a);
+    else if (logn == 10 && r == 8) emu_ntt_r_t<10, 8>(a);
+    else if (logn == 10 && r == 4) emu_ntt_r_t<10, 4>(a);
+    else if (logn == 11 && r == 8) emu_ntt_r_t<11, 8>(a);
+    else if (logn == 11 && r == 4) emu_ntt_r_t<11, 4>(a);
+    else if (logn == 12 && r == 8) emu_ntt_r_t<12, 8>(a);
     else return -1;
     return 0;
 }

@@ -51,6 +51,26 @@ def test_emu_ntt_matches_oracle_and_golden(golden, logn, teams, nblocks, npolys)
     assert np.array_equal(back, polys)
 
 
+@pytest.mark.parametrize("logn,r", [(9, 8), (9, 4), (10, 8), (10, 4), (11, 8), (11, 4), (12, 8)])
+def test_emu_narrow_tile_ntt_matches_oracle_and_golden(golden, logn, r):
+    """the R = 4 / 8 register tiles of the latency modes: same in-place positions as the reference's transform"""
+    N = 1 << logn
+    roots, inv, ninv = O.ntt_tables(N)
+    rng = O.Rng(100 + logn + r)
+    polys = np.stack([rng.field(N) for _ in range(2)])
+    if f"n{N}_testg" in golden.files:
+        polys[0] = golden[f"n{N}_testg"]
+    out = np.zeros_like(polys)
+    assert E.lib().emu_ntt_r(logn, r, polys.reshape(-1), out.reshape(-1), roots, 1, 2, 0) == 0
+    for i in range(2):
+        assert np.array_equal(out[i], O.ntt_forward(polys[i], roots))
+    if f"n{N}_testghat" in golden.files:
+        assert np.array_equal(out[0], golden[f"n{N}_testghat"])
+    back = np.zeros_like(polys)
+    assert E.lib().emu_ntt_r(logn, r, out.reshape(-1), back.reshape(-1), roots, ninv, 2, 1) == 0
+    assert np.array_equal(back, polys)
+
+
 def _device_bsk(ctx, ggsw_std, count):
     """std-domain GGSWs -> the engine's device format, via the same fold the GPU applies."""
     p = ctx.p

@@ -345,6 +345,10 @@ def test_latency_mode_equals_throughput_mode(which, rig_small0, rig_small1, rig_
         fast = r.eng.pbs_batch(cts, tvs, idx)
         r.eng.split_mode(2)          # one ciphertext per 2-CTA cluster, partials exchanged through distributed shared memory
         pair = r.eng.pbs_batch(cts, tvs, idx)
+        for regs in (16, 8, 4):      # wide tile and the narrow tiles (8 / 4 coefficients per thread)
+            r.eng.cluster_regs(regs)
+            assert np.array_equal(r.eng.pbs_batch(cts, tvs, idx), pair), regs
+        r.eng.cluster_regs(0)
         r.eng.split_mode(0)
         bulk = r.eng.pbs_batch(cts, tvs, idx)
         r.eng.generic_gadget(True)   # runtime-gadget instantiations of all three kernels
@@ -354,6 +358,7 @@ def test_latency_mode_equals_throughput_mode(which, rig_small0, rig_small1, rig_
         bulk_g = r.eng.pbs_batch(cts, tvs, idx)
     finally:
         r.eng.generic_gadget(False)
+        r.eng.cluster_regs(0)
         r.eng.split_mode(-1)
     assert np.array_equal(fast, bulk)
     assert np.array_equal(pair, bulk)

@@ -144,32 +144,50 @@ static int launch_br_split_t(lux_engine *e, const BRArgs &a, cudaStream_t s) {
     return LUX_OK;
 }
 
-// cluster latency mode (tfhe_kernels.cuh "cluster latency mode"): one ciphertext per 2-CTA cluster, TPC = ell teams per CTA
-template <int LOGN, int TPC, int ELL = 0, int LOGB = 0>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Tile<LOGN>::T *TPC, 1) blind_rotate_cluster_kernel(const BRArgs a) {
+// cluster latency mode (tfhe_kernels.cuh "cluster latency mode"): one ciphertext per 2-CTA cluster, TPC = ell teams per
+// CTA, R coefficients per thread (N/R threads per team)
+template <int LOGN, int TPC, int ELL = 0, int LOGB = 0, int R = 16>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__((Tile<LOGN>::N / R) * TPC, 1) blind_rotate_cluster_kernel(const BRArgs a) {
     extern __shared__ __align__(16) unsigned char smem[];
-    blind_rotate_cluster_body<LOGN, TPC, ELL, LOGB>(a, threadIdx.x, blockIdx.x, smem);
+    blind_rotate_cluster_body<LOGN, TPC, ELL, LOGB, R>(a, threadIdx.x, blockIdx.x, smem);
 }
 
-template <int LOGN, int TPC>
-static int launch_br_cluster_t(lux_engine *e, const BRArgs &a, cudaStream_t s) {
+template <int LOGN, int TPC, int R>
+static int launch_br_cluster_r(lux_engine *e, const BRArgs &a, cudaStream_t s) {
     constexpr size_t smem = blind_rotate_cluster_smem_bytes<LOGN, TPC>();
-    static_assert(smem <= 227 * 1024 && Tile<LOGN>::T * TPC <= 1024, "cluster latency-mode configuration does not fit an SM");
+    constexpr int threads = (Tile<LOGN>::N / R) * TPC;
+    static_assert(smem <= 227 * 1024 && threads <= 1024, "cluster latency-mode configuration does not fit an SM");
     constexpr int GE = NamedGadget<LOGN>::ELL, GB = NamedGadget<LOGN>::LOGB;
     constexpr bool NAMED = GE != 0 && TPC == GE;
     static bool configured[64] = {};
     if (!configured[e->device & 63]) {
-        CUDA_TRY(e, cudaFuncSetAttribute(blind_rotate_cluster_kernel<LOGN, TPC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        if (NAMED) CUDA_TRY(e, cudaFuncSetAttribute(blind_rotate_cluster_kernel<LOGN, TPC, NAMED ? GE : 0, NAMED ? GB : 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        CUDA_TRY(e, cudaFuncSetAttribute(blind_rotate_cluster_kernel<LOGN, TPC, 0, 0, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        if (NAMED) CUDA_TRY(e, cudaFuncSetAttribute(blind_rotate_cluster_kernel<LOGN, TPC, NAMED ? GE : 0, NAMED ? GB : 0, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured[e->device & 63] = true;
     }
     if (NAMED && a.ell == (u32)GE && a.logB == (u32)GB && !e->generic_gadget)
-        blind_rotate_cluster_kernel<LOGN, TPC, NAMED ? GE : 0, NAMED ? GB : 0><<<2 * a.B, Tile<LOGN>::T * TPC, smem, s>>>(a);
+        blind_rotate_cluster_kernel<LOGN, TPC, NAMED ? GE : 0, NAMED ? GB : 0, R><<<2 * a.B, threads, smem, s>>>(a);
     else
-        blind_rotate_cluster_kernel<LOGN, TPC><<<2 * a.B, Tile<LOGN>::T * TPC, smem, s>>>(a);
+        blind_rotate_cluster_kernel<LOGN, TPC, 0, 0, R><<<2 * a.B, threads, smem, s>>>(a);
     e->launches++;
     CUDA_TRY(e, cudaGetLastError());
     return LUX_OK;
+}
+
+// coefficients per thread: the narrowest tile whose CTA still fits 1024 threads, unless a test pins it
+template <int LOGN, int TPC>
+static int launch_br_cluster_t(lux_engine *e, const BRArgs &a, cudaStream_t s) {
+    // measured (profiles/r01e_latency_probe.txt): 8 per thread is best with one team per CTA (S2: 12.6 / 7.87 / 7.97 ms for
+    // 16 / 8 / 4), 4 per thread with several teams (S1: 11.1 / 8.17 / 7.91 ms)
+    constexpr int T16 = Tile<LOGN>::T;
+    const int r = e->cluster_regs ? e->cluster_regs : (TPC == 1 ? 8 : 4);
+    if constexpr (T16 * 4 * TPC <= 1024) {
+        if (r == 4) return launch_br_cluster_r<LOGN, TPC, 4>(e, a, s);
+    }
+    if constexpr (T16 * 2 * TPC <= 1024) {
+        if (r == 8 || r == 4) return launch_br_cluster_r<LOGN, TPC, 8>(e, a, s);
+    }
+    return launch_br_cluster_r<LOGN, TPC, 16>(e, a, s);
 }
 
 // 1 = launched, 0 = not applicable for this ring size / gadget

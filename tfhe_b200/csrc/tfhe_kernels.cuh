@@ -249,7 +249,6 @@ TK_DEV void team_ntt_inverse(u64 (&x)[16], u64 *xb, const u64 *tw, int tau, int 
     tile_pass_high<true>(x, tw);
 }
 
-// ---------------------------------------------------------------------------- batched NTT kernel
 struct NttArgs {
     const u64 *in;
     u64 *out;
@@ -258,6 +257,125 @@ struct NttArgs {
     u32 n_polys;
     u32 inverse;
 };
+
+// ---------------------------------------------------------------- narrow tiles (latency modes): R = 4 or 8 registers
+// Same transform with R coefficients per thread and T = N/R threads per polynomial: log2(N)/log2(R) passes of
+// log2(R) stages (the last one shorter), one shared-memory exchange between passes.  A thread's share of the
+// dependent instruction stream is R/16 of the wide tile's, which is what a single bootstrap waits for.
+// Pass P works on the index bits [lo, lo + log2 R) with lo = max(logN - (P+1) log2 R, 0): register e of thread tau
+// sits at position  ((tau >> lo) << (lo + log2 R)) | (e << lo) | (tau & (2^lo - 1)).
+template <int LOGN, int R>
+struct TileR {
+    static_assert(R == 4 || R == 8, "narrow tiles have 4 or 8 registers");
+    static constexpr int LR = (R == 8) ? 3 : 2;
+    static constexpr int N = 1 << LOGN;
+    static constexpr int T = N / R;
+    static constexpr int NP = (LOGN + LR - 1) / LR;
+    GL_HD static constexpr int lo(int pass) { return LOGN - (pass + 1) * LR < 0 ? 0 : LOGN - (pass + 1) * LR; }
+};
+template <int LOGN, int R, int P>
+GL_HD int pos_r(int tau, int e) {
+    constexpr int lo = TileR<LOGN, R>::lo(P), LR = TileR<LOGN, R>::LR;
+    return ((tau >> lo) << (lo + LR)) | (e << lo) | (tau & ((1 << lo) - 1));
+}
+
+template <int R, int SH, bool INV>
+TK_DEV void tile_stage_r(u64 (&x)[R], const u64 *tw, int m, int i0) {
+    constexpr int half = 1 << (SH - 1);
+    const u64 *p = INV ? tw + 2 * m - 1 - i0 : tw + m + i0;   // see tile_stage: INVROOTS[m+i] = -ROOTS[2m-1-i]
+    TK_UNROLL
+    for (int blk = 0; blk < (R >> SH); blk++) {
+        const u64 w = INV ? p[-blk] : p[blk];
+        TK_UNROLL
+        for (int j = 0; j < half; j++) {
+            const int e0 = (blk << SH) + j;
+            if (INV)
+                gl_gs_butterfly_neg(x[e0], x[e0 + half], w);
+            else
+                gl_ct_butterfly(x[e0], x[e0 + half], w);
+        }
+    }
+}
+
+// stage S of the transform inside pass P (no-op when S is outside the pass)
+template <int LOGN, int R, int P, int S, bool INV>
+TK_DEV void pass_stage_r(u64 (&x)[R], const u64 *tw, int base) {
+    constexpr int LR = TileR<LOGN, R>::LR, lo = TileR<LOGN, R>::lo(P);
+    if constexpr (S >= P * LR && S < (P + 1) * LR && S < LOGN) tile_stage_r<R, LOGN - S - lo, INV>(x, tw, 1 << S, base >> (LOGN - S));
+}
+template <int LOGN, int R, int P, bool INV>
+TK_DEV void pass_r(u64 (&x)[R], const u64 *tw, int tau) {
+    constexpr int LR = TileR<LOGN, R>::LR;
+    const int base = pos_r<LOGN, R, P>(tau, 0);
+    if constexpr (!INV) {
+        pass_stage_r<LOGN, R, P, P * LR + 0, false>(x, tw, base);
+        pass_stage_r<LOGN, R, P, P * LR + 1, false>(x, tw, base);
+        if constexpr (LR == 3) pass_stage_r<LOGN, R, P, P * LR + 2, false>(x, tw, base);
+    } else {
+        if constexpr (LR == 3) pass_stage_r<LOGN, R, P, P * LR + 2, true>(x, tw, base);
+        pass_stage_r<LOGN, R, P, P * LR + 1, true>(x, tw, base);
+        pass_stage_r<LOGN, R, P, P * LR + 0, true>(x, tw, base);
+    }
+}
+
+// exchange from the layout of pass PF to the layout of pass PT through xb.  FIRST: the buffer may still be read by
+// its previous user, so a barrier precedes the write; later exchanges write the slots the same thread read before.
+template <int LOGN, int R, int PF, int PT, bool FIRST>
+TK_DEV void exchange_r(u64 (&x)[R], u64 *xb, int tau, int team) {
+    constexpr int T = TileR<LOGN, R>::T;
+    if (FIRST) team_sync(team, T);
+    TK_UNROLL
+    for (int e = 0; e < R; e++) xb[tk_swz(pos_r<LOGN, R, PF>(tau, e))] = x[e];
+    team_sync(team, T);
+    TK_UNROLL
+    for (int e = 0; e < R; e++) x[e] = xb[tk_swz(pos_r<LOGN, R, PT>(tau, e))];
+}
+
+// forward: in x[e] = a[pos_r<0>(tau, e)] (natural order), out x[e] = A[pos_r<NP-1>(tau, e)] = A[R tau + e]
+template <int LOGN, int R, int P = 0>
+TK_DEV void team_ntt_forward_r(u64 (&x)[R], u64 *xb, const u64 *tw, int tau, int team) {
+    pass_r<LOGN, R, P, false>(x, tw, tau);
+    if constexpr (P + 1 < TileR<LOGN, R>::NP) {
+        exchange_r<LOGN, R, P, P + 1, P == 0>(x, xb, tau, team);
+        team_ntt_forward_r<LOGN, R, P + 1>(x, xb, tw, tau, team);
+    }
+}
+// inverse WITHOUT the final 1/N: in x[e] = A[R tau + e], out x[e] = N * a[pos_r<0>(tau, e)] (lazy)
+template <int LOGN, int R, int P = TileR<LOGN, R>::NP - 1>
+TK_DEV void team_ntt_inverse_r(u64 (&x)[R], u64 *xb, const u64 *tw, int tau, int team) {
+    pass_r<LOGN, R, P, true>(x, tw, tau);
+    if constexpr (P > 0) {
+        exchange_r<LOGN, R, P, P - 1, P == TileR<LOGN, R>::NP - 1>(x, xb, tau, team);
+        team_ntt_inverse_r<LOGN, R, P - 1>(x, xb, tw, tau, team);
+    }
+}
+
+// one polynomial per CTA, narrow tile: parity utility for the emulator and the GPU tests
+template <int LOGN, int R>
+TK_DEV void ntt_r_body(const NttArgs &a, int tid, int bid, unsigned char *smem_raw) {
+    constexpr int N = TileR<LOGN, R>::N, T = TileR<LOGN, R>::T, NP = TileR<LOGN, R>::NP;
+    u64 *tw = (u64 *)smem_raw, *xb = tw + N;
+    for (int i = tid; i < N; i += T) tw[i] = a.tw[i];
+    cta_sync();
+    const u64 *src = a.in + (size_t)bid * N;
+    u64 *dst = a.out + (size_t)bid * N;
+    u64 x[R];
+    if (!a.inverse) {
+        TK_UNROLL
+        for (int e = 0; e < R; e++) x[e] = src[pos_r<LOGN, R, 0>(tid, e)];
+        team_ntt_forward_r<LOGN, R>(x, xb, tw, tid, 0);
+        TK_UNROLL
+        for (int e = 0; e < R; e++) dst[pos_r<LOGN, R, NP - 1>(tid, e)] = (a.scale == 1) ? gl_canon(x[e]) : gl_mul(x[e], a.scale);
+    } else {
+        TK_UNROLL
+        for (int e = 0; e < R; e++) x[e] = src[pos_r<LOGN, R, NP - 1>(tid, e)];
+        team_ntt_inverse_r<LOGN, R>(x, xb, tw, tid, 0);
+        TK_UNROLL
+        for (int e = 0; e < R; e++) dst[pos_r<LOGN, R, 0>(tid, e)] = (a.scale == 1) ? gl_canon(x[e]) : gl_mul(x[e], a.scale);
+    }
+}
+
+// ---------------------------------------------------------------------------- batched NTT kernel
 
 template <int LOGN, int TEAMS>
 TK_DEV void ntt_batch_body(const NttArgs &a, int tid, int bid, int nblocks, unsigned char *smem_raw) {
@@ -722,9 +840,11 @@ __device__ __forceinline__ u64 cluster_ld(u32 addr) {
     return v;
 }
 
-template <int LOGN, int TPC, int ELL = 0, int LOGB = 0>
+// R = coefficients per thread: 16 (the wide tile of the throughput kernel) or 8 / 4 (narrow tiles, R/16 of the
+// dependent instruction stream per thread and 16/R times the warps per polynomial)
+template <int LOGN, int TPC, int ELL = 0, int LOGB = 0, int R = 16>
 __device__ __forceinline__ void blind_rotate_cluster_body(const BRArgs &a, int tid, int bid, unsigned char *smem_raw) {
-    constexpr int N = Tile<LOGN>::N, T = Tile<LOGN>::T;
+    constexpr int N = Tile<LOGN>::N, T = N / R, T16 = N / 16, R16 = 16 / R;
     const u32 g_ell = ELL ? (u32)ELL : a.ell, g_logB = LOGB ? (u32)LOGB : a.logB;
     const u32 g_L = LOGB ? (u32)((64 + (LOGB ? LOGB : 1) - 1) / (LOGB ? LOGB : 1)) : a.L;
     const bool centred = (g_L * g_logB == 64);
@@ -754,20 +874,25 @@ __device__ __forceinline__ void blind_rotate_cluster_body(const BRArgs &a, int t
         if (i + 1 < a.steps) mask = lwe[i + 1];
         const u32 par = i & 1u;
         {   // phase 1: team lvl, digit polynomial (r, lvl)
-            u64 x[16];
+            u64 x[R];
             TK_UNROLL
-            for (int e = 0; e < 16; e++) {
-                const int p = posA<LOGN>(tau, e);
+            for (int e = 0; e < R; e++) {
+                const int p = e * T + tau;   // first-pass layout (posA / pos_r<0>)
                 u64 d = acc[p];
                 if (cmux) d = gl_sub(rotated_coeff<LOGN>(acc, p, sh), d);
                 x[e] = gl_digit(d, g_L - g_ell + (u32)lvl, g_logB, centred);
             }
-            team_ntt_forward<LOGN>(x, xb, tw, tau, lvl);
+            if constexpr (R == 16)
+                team_ntt_forward<LOGN>(x, xb, tw, tau, lvl);
+            else
+                team_ntt_forward_r<LOGN, R>(x, xb, tw, tau, lvl);
             const u64 *rows = (cmux ? a.bsk + i * ggsw_len : a.ksk) + ((size_t)r * g_ell + (u32)lvl) * 2 * N;
             u64 *mine = part + (size_t)par * 2 * N;
             TK_UNROLL
-            for (int h = 0; h < 8; h++) {
-                const u64 *r0 = rows + (size_t)h * 2 * T + 2 * tau;
+            for (int h = 0; h < R / 2; h++) {
+                // x[2h], x[2h+1] sit at in-place positions R*tau + 2h (+1) = element (tau / R16, (R/2)(tau % R16) + h)
+                // of the resident key format (key_pos)
+                const u64 *r0 = rows + (size_t)((R / 2) * (tau & (R16 - 1)) + h) * 2 * T16 + 2 * (tau / R16);
                 const ulonglong2 v0 = *reinterpret_cast<const ulonglong2 *>(r0);
                 const ulonglong2 v1 = *reinterpret_cast<const ulonglong2 *>(r0 + N);
                 mine[(2 * h) * T + tau] = gl_mul(x[2 * h], v0.x);
@@ -778,27 +903,30 @@ __device__ __forceinline__ void blind_rotate_cluster_body(const BRArgs &a, int t
         }
         cluster_sync_all();
         if (lvl == 0) {  // phase 2: output polynomial r = my partials towards r + the peer's partials towards r
-            u64 o[16];
+            u64 o[R];
             const size_t off = ((size_t)par * 2 + r) * N;
             TK_UNROLL
-            for (int e = 0; e < 16; e++) o[e] = part[off + e * T + tau];
+            for (int e = 0; e < R; e++) o[e] = part[off + e * T + tau];
             for (u32 l2 = 1; l2 < g_ell; l2++) {
                 const u64 *src = part + (size_t)l2 * 5 * N + off;
                 TK_UNROLL
-                for (int e = 0; e < 16; e++) o[e] = gl_add(o[e], src[e * T + tau]);
+                for (int e = 0; e < R; e++) o[e] = gl_add(o[e], src[e * T + tau]);
             }
             for (u32 l2 = 0; l2 < g_ell; l2++) {
                 const u32 base = peer_part0 + (u32)(((size_t)l2 * 5 * N + off) * sizeof(u64));
-                u64 v[16];
+                u64 v[R];
                 TK_UNROLL
-                for (int e = 0; e < 16; e++) v[e] = cluster_ld(base + (u32)((e * T + tau) * sizeof(u64)));
+                for (int e = 0; e < R; e++) v[e] = cluster_ld(base + (u32)((e * T + tau) * sizeof(u64)));
                 TK_UNROLL
-                for (int e = 0; e < 16; e++) o[e] = gl_add(o[e], v[e]);
+                for (int e = 0; e < R; e++) o[e] = gl_add(o[e], v[e]);
             }
-            team_ntt_inverse<LOGN>(o, xb, tw, tau, 0);
+            if constexpr (R == 16)
+                team_ntt_inverse<LOGN>(o, xb, tw, tau, 0);
+            else
+                team_ntt_inverse_r<LOGN, R>(o, xb, tw, tau, 0);
             TK_UNROLL
-            for (int e = 0; e < 16; e++) {
-                const int p = posA<LOGN>(tau, e);
+            for (int e = 0; e < R; e++) {
+                const int p = e * T + tau;
                 acc[p] = cmux ? gl_canon(gl_add(o[e], acc[p])) : gl_canon(o[e]);
             }
         }
