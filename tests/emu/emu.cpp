@@ -53,6 +53,15 @@ static void emu_br_t(const BRArgs &a) {
         run_cta(T * TEAMS, T, [&](int tid) { blind_rotate_body<LOGN, TEAMS>(a, tid, bid, smem.data()); });
 }
 
+template <int LOGN, int TEAMS, int R>
+static void emu_br_r_t(const BRArgs &a) {
+    constexpr int T = Tile<LOGN>::N / R;
+    std::vector<unsigned char> smem(blind_rotate_smem_bytes<LOGN, TEAMS>());
+    const int nblocks = (a.B + TEAMS - 1) / TEAMS;
+    for (int bid = 0; bid < nblocks; bid++)
+        run_cta(T * TEAMS, T, [&](int tid) { blind_rotate_body<LOGN, TEAMS, 0, 0, R>(a, tid, bid, smem.data()); });
+}
+
 template <int LOGN, int G>
 static void emu_br_split_t(const BRArgs &a) {
     constexpr int T = Tile<LOGN>::T;
@@ -110,7 +119,11 @@ int emu_ntt_r(int logn, int r, const u64 *in, u64 *out, const u64 *tw, u64 scale
 }
 
 int emu_blind_rotate(int logn, int teams, const BRArgs *a) {
-    if (logn == 9 && teams == 3) emu_br_t<9, 3>(*a);
+    // teams >= 100: narrow tile, teams = 100 * R + TEAMS
+    if (logn == 9 && teams == 803) emu_br_r_t<9, 3, 8>(*a);
+    else if (logn == 10 && teams == 802) emu_br_r_t<10, 2, 8>(*a);
+    else if (logn == 9 && teams == 403) emu_br_r_t<9, 3, 4>(*a);
+    else if (logn == 9 && teams == 3) emu_br_t<9, 3>(*a);
     else if (logn == 10 && teams == 2) emu_br_t<10, 2>(*a);
     else if (logn == 11 && teams == 2) emu_br_t<11, 2>(*a);
     else return -1;

@@ -81,7 +81,9 @@ def _device_bsk(ctx, ggsw_std, count):
 
 # teams < 0: the latency-mode body (one ciphertext per CTA, G = -teams = 2*ell teams)
 @pytest.mark.parametrize("logn,teams,ell,logB,B,steps", [(9, 3, 2, 16, 4, 3), (10, 2, 4, 5, 2, 2), (9, 3, 1, 41, 3, 2),
-                                                         (9, -4, 2, 16, 3, 3), (9, -2, 1, 41, 3, 2), (10, -8, 4, 5, 2, 2)])
+                                                         (9, -4, 2, 16, 3, 3), (9, -2, 1, 41, 3, 2), (10, -8, 4, 5, 2, 2),
+                                                         # teams >= 100: narrow tiles, 100 * R + TEAMS
+                                                         (9, 803, 2, 16, 4, 3), (10, 802, 4, 5, 3, 2), (9, 403, 1, 41, 4, 2)])
 def test_emu_blind_rotate_matches_oracle(logn, teams, ell, logB, B, steps):
     N = 1 << logn
     n = 5

@@ -369,6 +369,41 @@ def test_latency_mode_equals_throughput_mode(which, rig_small0, rig_small1, rig_
     assert [O.decode(O.lwe_decrypt(r.ks.s_in, c), delta, 2 * p) for c in fast] == [luts[idx[b]][msgs[b]] for b in range(B)]
 
 
+@pytest.mark.parametrize("which", ["s1", "s2"])
+def test_tile_widths_agree(which, rig_s1, rig_s2):
+    """throughput blind rotate of the named sets: narrow tiles (8 and 4 coefficients per thread), the wide tile
+    (16, teams in lock step) and the runtime-gadget instantiation give the same words; ragged against every
+    ciphertexts-per-CTA count; first outputs equal the oracle's"""
+    r = {"s1": rig_s1, "s2": rig_s2}[which]
+    rng = O.Rng(57)
+    B = 301
+    cts = np.stack([rng.field(r.p.ct_len) for _ in range(B)])
+    tvs = np.stack([rng.field(r.p.N) for _ in range(3)])
+    idx = np.array([b % 3 for b in range(B)], dtype=np.uint32)
+    outs = {}
+    try:
+        r.eng.split_mode(0)
+        for regs in (8, 16, 4):
+            r.eng.br_regs(regs)
+            for teams in (0, 1, 2, 3):
+                r.eng.force_teams(teams)
+                outs[(regs, teams)] = r.eng.pbs_batch(cts, tvs, idx)
+        r.eng.force_teams(0)
+        r.eng.generic_gadget(True)
+        r.eng.br_regs(16)
+        outs["generic"] = r.eng.pbs_batch(cts, tvs, idx)
+    finally:
+        r.eng.generic_gadget(False)
+        r.eng.br_regs(8)
+        r.eng.force_teams(0)
+        r.eng.split_mode(-1)
+    base = outs[(8, 0)]
+    for k, v in outs.items():
+        assert np.array_equal(v, base), k
+    want, _ = r.ctx.pbs_batch(cts[:2], tvs, idx[:2])
+    assert np.array_equal(base[:2], want)
+
+
 def test_pbs_s2_shortint_bit_exact(rig_s2):
     """BASELINE config 2 shape: 4-bit LUTs at N=2048 (identity, x^2 mod 16, carry extract, message extract)."""
     luts = [list(range(16)), [(x * x) % 16 for x in range(16)], [x >> 2 for x in range(16)], [x & 3 for x in range(16)]]

@@ -3,10 +3,10 @@
 // sizes in parallel.
 #include "engine.h"
 
-template <int LOGN, int TEAMS, int ELL = 0, int LOGB = 0>
-__global__ void __launch_bounds__(Tile<LOGN>::T *TEAMS, 1) blind_rotate_kernel(const BRArgs a) {
+template <int LOGN, int TEAMS, int ELL = 0, int LOGB = 0, int R = 16>
+__global__ void __launch_bounds__((Tile<LOGN>::N / R) * TEAMS, 1) blind_rotate_kernel(const BRArgs a) {
     extern __shared__ __align__(16) unsigned char smem[];
-    blind_rotate_body<LOGN, TEAMS, ELL, LOGB>(a, threadIdx.x, blockIdx.x, smem);
+    blind_rotate_body<LOGN, TEAMS, ELL, LOGB, R>(a, threadIdx.x, blockIdx.x, smem);
 }
 
 // gadgets of the named parameter sets get their own instantiation (compile-time digit rule):
@@ -59,6 +59,19 @@ __global__ void __launch_bounds__(Tile<LOGN>::T) key_format_kernel(u64 *polys, u
     for (int e = 0; e < 16; e++) poly[key_pos<LOGN>(tau, e)] = ggsw_fold_elem(x[e], ninv, glev);
 }
 
+template <int LOGN, int TEAMS, int GE, int GB, int R>
+static int launch_br_narrow(lux_engine *e, const BRArgs &a, cudaStream_t s, u32 grid, size_t smem) {
+    static bool configured[64] = {};
+    if (!configured[e->device & 63]) {
+        CUDA_TRY(e, cudaFuncSetAttribute(blind_rotate_kernel<LOGN, TEAMS, GE, GB, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured[e->device & 63] = true;
+    }
+    blind_rotate_kernel<LOGN, TEAMS, GE, GB, R><<<grid, (Tile<LOGN>::N / R) * TEAMS, smem, s>>>(a);
+    e->launches++;
+    CUDA_TRY(e, cudaGetLastError());
+    return LUX_OK;
+}
+
 template <int LOGN, int TEAMS>
 static int launch_br_t(lux_engine *e, const BRArgs &a, cudaStream_t s) {
     constexpr size_t smem = blind_rotate_smem_bytes<LOGN, TEAMS>();
@@ -70,6 +83,15 @@ static int launch_br_t(lux_engine *e, const BRArgs &a, cudaStream_t s) {
         configured[e->device & 63] = true;
     }
     const u32 grid = (a.B + TEAMS - 1) / TEAMS;
+    // narrow tiles (8 / 4 coefficients per thread, 2x / 4x the warps per ciphertext): named gadgets only
+    if (GE && a.ell == (u32)GE && a.logB == (u32)GB && e->br_regs != 16) {
+        if constexpr (GE != 0 && (Tile<LOGN>::N / 4) * TEAMS <= 1024) {
+            if (e->br_regs == 4) return launch_br_narrow<LOGN, TEAMS, GE, GB, 4>(e, a, s, grid, smem);
+        }
+        if constexpr (GE != 0 && (Tile<LOGN>::N / 8) * TEAMS <= 1024) {
+            return launch_br_narrow<LOGN, TEAMS, GE, GB, 8>(e, a, s, grid, smem);
+        }
+    }
     if (GE && a.ell == (u32)GE && a.logB == (u32)GB && !e->generic_gadget)
         blind_rotate_kernel<LOGN, TEAMS, GE, GB><<<grid, Tile<LOGN>::T * TEAMS, smem, s>>>(a);
     else
@@ -77,6 +99,12 @@ static int launch_br_t(lux_engine *e, const BRArgs &a, cudaStream_t s) {
     e->launches++;
     CUDA_TRY(e, cudaGetLastError());
     return LUX_OK;
+}
+
+// does this launch take the narrow-tile instantiation of a named gadget?
+static bool narrow_named(const lux_engine *e, u32 ell, u32 logB) {
+    constexpr int GE = NamedGadget<LUX_LOGN>::ELL, GB = NamedGadget<LUX_LOGN>::LOGB;
+    return GE != 0 && ell == (u32)GE && logB == (u32)GB && e->br_regs != 16;
 }
 
 // ciphertexts per CTA: as few as keep the batch within one wave of CTAs, up to the SMEM limit
@@ -260,7 +288,9 @@ int LUX_CAT(lux_launch_br_, LUX_LOGN)(lux_engine *e, const BRArgs &a, cudaStream
     if (t <= 3) return launch_br_t<10, 3>(e, a, s);
     return launch_br_t<10, 6>(e, a, s);
 #elif LUX_LOGN == 11
-    const int t = pick_teams(e, a.B, 3);
+    // narrow tile: two ciphertexts per CTA (512 threads, 128 registers, no spills) measured best: 354.8 ms against
+    // 360.5 (three per CTA) and 368.5 (wide tile, three per CTA) for 4,440 ciphertexts
+    const int t = pick_teams(e, a.B, narrow_named(e, a.ell, a.logB) ? 2 : 3);
     if (t <= 1) return launch_br_t<11, 1>(e, a, s);
     if (t <= 2) return launch_br_t<11, 2>(e, a, s);
     return launch_br_t<11, 3>(e, a, s);
@@ -284,7 +314,7 @@ size_t LUX_CAT(lux_br_wave_, LUX_LOGN)(const lux_engine *e, size_t B) {
     const int t = pick_teams(e, B, 6);
     return (size_t)e->sm_count * (t <= 1 ? 1 : t <= 3 ? 3 : 6);
 #elif LUX_LOGN == 11
-    const int t = pick_teams(e, B, 3);
+    const int t = pick_teams(e, B, narrow_named(e, e->p.ell, e->p.logB) ? 2 : 3);
     return (size_t)e->sm_count * (t <= 1 ? 1 : t <= 2 ? 2 : 3);
 #else
     return (size_t)e->sm_count;

@@ -526,6 +526,11 @@ int lux_debug_ks_splits(lux_engine *e, int splits) {
     e->ks_splits = splits;
     return LUX_OK;
 }
+int lux_debug_br_regs(lux_engine *e, int regs) {
+    if (!e || (regs != 4 && regs != 8 && regs != 16)) return LUX_ERR_INVALID;
+    e->br_regs = regs;
+    return LUX_OK;
+}
 int lux_debug_cluster_regs(lux_engine *e, int regs) {
     if (!e || (regs != 0 && regs != 4 && regs != 8 && regs != 16)) return LUX_ERR_INVALID;
     e->cluster_regs = regs;

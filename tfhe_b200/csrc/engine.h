@@ -43,6 +43,8 @@ struct lux_engine {
     int8_t *d_ks_dig = nullptr;  // grow-only [Mpad][K] digit buffer
     size_t ks_dig_bytes = 0;
     int ks_mode = -1;         // -1 = automatic (batches >= 256), 0 = integer-pipe kernel only, 1 = tensor-core kernel whenever eligible
+    int br_regs = 8;              // throughput blind rotate of the named gadgets: coefficients per thread (8 = narrow tile,
+                                  // default; 16 = wide tile; 4: tuning).  Other gadgets always run the wide tile.
     int cluster_regs = 0;         // cluster latency mode: coefficients per thread, 0 = automatic, 16 / 8 / 4 pinned (tests, tuning)
     bool generic_gadget = false;  // tests: run the runtime-gadget kernel even where a compile-time instantiation exists
     int split_mode = -1;  // latency-mode blind rotate: -1 = automatic (2B <= #SMs: cluster kernel, B <= #SMs: split kernel), 0 = never,
@@ -63,6 +65,7 @@ extern "C" int lux_debug_ks_splits(lux_engine *e, int splits);
 extern "C" int lux_debug_ks_mode(lux_engine *e, int mode);
 extern "C" int lux_debug_generic_gadget(lux_engine *e, int on);
 extern "C" int lux_debug_cluster_regs(lux_engine *e, int regs);
+extern "C" int lux_debug_br_regs(lux_engine *e, int regs);
 extern "C" int lux_debug_int_peak(lux_engine *e, double out[3]);
 extern "C" int lux_debug_field_probe(lux_engine *e, const uint64_t *a, const uint64_t *b, size_t count, uint64_t *out);
 

@@ -518,16 +518,17 @@ __device__ __forceinline__ void stream_issue(const KeyStream &ks, u32 t) {
 // are read from `ggsw` in global memory (independent keys per ciphertext: external_product_kernel, emulator).
 // ELL / LOGB != 0 fix the gadget at compile time (the named parameter sets): the digit rule then folds to a few
 // shifts instead of 64-bit variable shifts and selects per coefficient.  0 = read it from BRArgs.
-template <int LOGN, bool STAGED, int ELL = 0, int LOGB = 0>
+// R = coefficients per thread (16 = wide tile; 8 / 4 = narrow tiles with N/R threads per team)
+template <int LOGN, bool STAGED, int ELL = 0, int LOGB = 0, int R = 16>
 TK_DEV void team_external_product(const BRArgs &a, const u64 *ggsw, KeyStream &ks, bool cmux, u32 sh, u64 *acc, u64 *xb,
                                   const u64 *tw, int tau, int team, int lane) {
-    constexpr int N = Tile<LOGN>::N, T = Tile<LOGN>::T;
+    constexpr int N = Tile<LOGN>::N, T = N / R, T16 = N / 16, R16 = 16 / R;
     const u32 g_ell = ELL ? (u32)ELL : a.ell, g_logB = LOGB ? (u32)LOGB : a.logB;
     const u32 g_L = LOGB ? (u32)((64 + (LOGB ? LOGB : 1) - 1) / (LOGB ? LOGB : 1)) : a.L;
     const bool centred = (g_L * g_logB == 64);
-    u64 o0[16], o1[16];
+    u64 o0[R], o1[R];
     TK_UNROLL
-    for (int e = 0; e < 16; e++) o0[e] = o1[e] = 0;
+    for (int e = 0; e < R; e++) o0[e] = o1[e] = 0;
 
     for (int j = 0; j < 2; j++) {
         const u64 *poly = acc + j * N;
@@ -535,16 +536,19 @@ TK_DEV void team_external_product(const BRArgs &a, const u64 *ggsw, KeyStream &k
 #pragma unroll 1
 #endif
         for (u32 lvl = 0; lvl < g_ell; lvl++) {
-            u64 x[16];
+            u64 x[R];
             TK_UNROLL
-            for (int e = 0; e < 16; e++) {
-                const int p = posA<LOGN>(tau, e);
+            for (int e = 0; e < R; e++) {
+                const int p = e * T + tau;   // first-pass layout (posA / pos_r<0>)
                 u64 d = poly[p];
                 // both operands canonical, so gl_sub's result (a - b, plus q on borrow) already is
                 if (cmux) d = gl_sub(rotated_coeff<LOGN>(poly, p, sh), d);
                 x[e] = gl_digit(d, g_L - g_ell + lvl, g_logB, centred);   // glev_ct.rs:97-99: top ell limbs
             }
-            team_ntt_forward<LOGN>(x, xb, tw, tau, team);
+            if constexpr (R == 16)
+                team_ntt_forward<LOGN>(x, xb, tw, tau, team);
+            else
+                team_ntt_forward_r<LOGN, R>(x, xb, tw, tau, team);
             const u64 *rows;
 #if !defined(TFHE_EMU)
             constexpr int NS = StageCfg<LOGN>::NSTAGE;
@@ -555,9 +559,10 @@ TK_DEV void team_external_product(const BRArgs &a, const u64 *ggsw, KeyStream &k
 #endif
                 rows = ggsw + ((size_t)(j * g_ell + lvl) * 2) * N;
             TK_UNROLL
-            for (int h = 0; h < 8; h++) {
-                // elements key_pos(tau, 2h), key_pos(tau, 2h+1) of both rows: one 16-byte access each
-                const u64 *r0 = rows + (size_t)h * 2 * T + 2 * tau;
+            for (int h = 0; h < R / 2; h++) {
+                // x[2h], x[2h+1] sit at in-place positions R*tau + 2h (+1) = elements key_pos(tau / R16, (R/2)(tau % R16)
+                // + 2h (+1)) of both rows: one 16-byte access each
+                const u64 *r0 = rows + (size_t)((R / 2) * (tau & (R16 - 1)) + h) * 2 * T16 + 2 * (tau / R16);
                 const u64 *r1 = r0 + N;
 #if !defined(TFHE_EMU)
                 const ulonglong2 v0 = *reinterpret_cast<const ulonglong2 *>(r0);
@@ -593,10 +598,13 @@ TK_DEV void team_external_product(const BRArgs &a, const u64 *ggsw, KeyStream &k
 #pragma unroll 1
 #endif
     for (int r = 0; r < 2; r++) {
-        team_ntt_inverse<LOGN>(o0, xb, tw, tau, team);
+        if constexpr (R == 16)
+            team_ntt_inverse<LOGN>(o0, xb, tw, tau, team);
+        else
+            team_ntt_inverse_r<LOGN, R>(o0, xb, tw, tau, team);
         TK_UNROLL
-        for (int e = 0; e < 16; e++) {
-            const int p = r * N + posA<LOGN>(tau, e);
+        for (int e = 0; e < R; e++) {
+            const int p = r * N + e * T + tau;
             acc[p] = cmux ? gl_canon(gl_add(o0[e], acc[p])) : gl_canon(o0[e]);
             o0[e] = o1[e];
         }
@@ -610,9 +618,9 @@ constexpr size_t blind_rotate_smem_bytes() {
     return sizeof(u64) * ((size_t)Tile<LOGN>::N + (size_t)TEAMS * 3 * Tile<LOGN>::N + (size_t)StageCfg<LOGN>::NSTAGE * 2 * Tile<LOGN>::N) + 64;
 }
 
-template <int LOGN, int TEAMS, int ELL = 0, int LOGB = 0>
+template <int LOGN, int TEAMS, int ELL = 0, int LOGB = 0, int R = 16>
 TK_DEV void blind_rotate_body(const BRArgs &a, int tid, int bid, unsigned char *smem_raw) {
-    constexpr int N = Tile<LOGN>::N, T = Tile<LOGN>::T, NS = StageCfg<LOGN>::NSTAGE;
+    constexpr int N = Tile<LOGN>::N, T = N / R, NS = StageCfg<LOGN>::NSTAGE;
     u64 *tw = (u64 *)smem_raw;
     const int team = tid / T, tau = tid % T, lane = tid & 31;
     u64 *acc = tw + N + (size_t)team * 3 * N;
@@ -646,7 +654,8 @@ TK_DEV void blind_rotate_body(const BRArgs &a, int tid, int bid, unsigned char *
     // team handle for the barriers: with lock step it carries the live thread count of this CTA (ragged last CTA)
 #if !defined(TFHE_EMU)
     // (only the compile-time-gadget instantiations: the longer runtime-gadget body measured slower in lock step)
-    const int th = tk_team(team, ELL ? (int)((a.B - (u32)bid * TEAMS < (u32)TEAMS ? a.B - (u32)bid * TEAMS : (u32)TEAMS) * T) : 0);
+    // and only the wide tile: the narrow-tile body is half the size and measured faster with drifting teams)
+    const int th = tk_team(team, (ELL && R == 16) ? (int)((a.B - (u32)bid * TEAMS < (u32)TEAMS ? a.B - (u32)bid * TEAMS : (u32)TEAMS) * T) : 0);
 #else
     const int th = team;
 #endif
@@ -663,8 +672,8 @@ TK_DEV void blind_rotate_body(const BRArgs &a, int tid, int bid, unsigned char *
     {
         const u32 sh0 = gl_mod_switch(gl_neg(lwe[a.n]), LOGN);
         TK_UNROLL
-        for (int e = 0; e < 16; e++) {
-            const int p = posA<LOGN>(tau, e);
+        for (int e = 0; e < R; e++) {
+            const int p = e * T + tau;
             acc[p] = 0;
             acc[N + p] = rotated_coeff<LOGN>(tv, p, sh0);
         }
@@ -680,7 +689,7 @@ TK_DEV void blind_rotate_body(const BRArgs &a, int tid, int bid, unsigned char *
         const bool cmux = i < a.steps;
         const u32 sh = cmux ? gl_mod_switch(mask, LOGN) : 0;
         if (i + 1 < a.steps) mask = lwe[i + 1];  // fetched one iteration ahead
-        team_external_product<LOGN, true, ELL, LOGB>(a, cmux ? a.bsk + i * ggsw_len : a.ksk, ks, cmux, sh, acc, xb, tw, tau, th, lane);
+        team_external_product<LOGN, true, ELL, LOGB, R>(a, cmux ? a.bsk + i * ggsw_len : a.ksk, ks, cmux, sh, acc, xb, tw, tau, th, lane);
     }
 
     // exit: sample extraction of coefficient 0      crypto/glwe.rs:96-113

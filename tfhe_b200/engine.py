@@ -140,6 +140,8 @@ def lib():
             L.lux_debug_split_mode.argtypes = [_vp, _int]
         if hasattr(L, "lux_debug_ks_splits"):
             L.lux_debug_ks_splits.argtypes = [_vp, _int]
+        if hasattr(L, "lux_debug_br_regs"):
+            L.lux_debug_br_regs.argtypes = [_vp, _int]
         if hasattr(L, "lux_debug_cluster_regs"):
             L.lux_debug_cluster_regs.argtypes = [_vp, _int]
         if hasattr(L, "lux_debug_generic_gadget"):
@@ -328,6 +330,10 @@ class Engine:
     def ks_splits(self, n: int):
         """key-switch input slices for small batches: 0 automatic, n > 0 forced (1 = single pass)"""
         self._ck(lib().lux_debug_ks_splits(self._h, n))
+
+    def br_regs(self, regs: int):
+        """throughput blind rotate: coefficients per thread (16 = wide tile, 8 = narrow tile; named sets only)"""
+        self._ck(lib().lux_debug_br_regs(self._h, regs))
 
     def cluster_regs(self, regs: int):
         """cluster latency mode: coefficients per thread (16, 8, 4; 0 = automatic: the narrowest that fits a CTA)"""
