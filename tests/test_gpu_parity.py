@@ -236,11 +236,13 @@ def test_lwe_keyswitch_split_forms_agree(rig_s2, rig_small1):
         cts = np.stack([rng.field(r.p.N + 1) for _ in range(B)])
         outs = []
         try:
+            r.eng.ks_mode(0)          # the integer-pipe kernel (the default is the tensor-core form)
             for n in (1, 2, 5, 0):
                 r.eng.ks_splits(n)
                 outs.append(r.eng.lwe_keyswitch(cts))
         finally:
             r.eng.ks_splits(0)
+            r.eng.ks_mode(-1)
         for o in outs[1:]:
             assert np.array_equal(o, outs[0])
         assert np.array_equal(outs[0][0], r.ctx.lwe_keyswitch(cts[0]))
@@ -265,8 +267,7 @@ def test_lwe_keyswitch_tensor_core_form(rig_s2, rig_small1, B):
         assert np.array_equal(got, ref)
         for b in sorted({0, B // 2, B - 1}):
             assert np.array_equal(got[b], r.ctx.lwe_keyswitch(cts[b])), b
-        if B >= 256:   # automatic dispatch takes the tensor-core form here
-            assert np.array_equal(r.eng.lwe_keyswitch(cts), got)
+        assert np.array_equal(r.eng.lwe_keyswitch(cts), got)   # automatic dispatch takes the tensor-core form
 
 
 # ---------------------------------------------------------------------------------------------- whole PBS
@@ -343,6 +344,9 @@ def test_latency_mode_equals_throughput_mode(which, rig_small0, rig_small1, rig_
     try:
         r.eng.split_mode(1)
         fast = r.eng.pbs_batch(cts, tvs, idx)
+        r.eng.cluster_regs(16)       # the one-CTA latency kernel with the wide tile (named sets default to the narrow one)
+        assert np.array_equal(r.eng.pbs_batch(cts, tvs, idx), fast)
+        r.eng.cluster_regs(0)
         r.eng.split_mode(2)          # one ciphertext per 2-CTA cluster, partials exchanged through distributed shared memory
         pair = r.eng.pbs_batch(cts, tvs, idx)
         for regs in (16, 8, 4):      # wide tile and the narrow tiles (8 / 4 coefficients per thread)

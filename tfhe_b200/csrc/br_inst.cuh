@@ -115,6 +115,21 @@ static int pick_teams(const lux_engine *e, size_t B, int max_teams) {
     return max_teams;
 }
 
+#if LUX_LOGN == 11
+// N = 2048, narrow tile: two ciphertexts per CTA (512 threads, 128 registers, no spills) take 23.65 ms per wave of
+// 2 * #SMs, three (768 threads, 80 registers, some spills) 36.05 ms per wave of 3 * #SMs (profiles/r01e_lockstep.txt):
+// 354.8 against 360.5 ms for 4,440 ciphertexts, but 47.3 against 36.1 ms for 444.  Pick the cheaper wave plan.
+static int pick_teams_11(const lux_engine *e, size_t B, u32 ell, u32 logB) {
+    if (!narrow_named(e, ell, logB)) return pick_teams(e, B, 3);
+    if (e->force_teams >= 1 && e->force_teams <= 3) return e->force_teams;
+    const size_t sm = (size_t)e->sm_count;
+    if (B <= sm) return 1;
+    if (B <= 2 * sm) return 2;
+    const size_t w2 = (B + 2 * sm - 1) / (2 * sm), w3 = (B + 3 * sm - 1) / (3 * sm);
+    return (w2 * 2365 <= w3 * 3605) ? 2 : 3;
+}
+#endif
+
 template <int LOGN, int TEAMS>
 static int launch_ntt_t(lux_engine *e, const NttArgs &a, cudaStream_t s) {
     constexpr size_t smem = sizeof(u64) * ((size_t)Tile<LOGN>::N + (size_t)TEAMS * Tile<LOGN>::N);
@@ -145,10 +160,10 @@ static int launch_xp_t(lux_engine *e, const BRArgs &a, const u64 *d_glwe, size_t
 }
 
 // latency mode (tfhe_kernels.cuh "latency mode"): one ciphertext per CTA, G = 2*ell teams
-template <int LOGN, int G, int ELL = 0, int LOGB = 0>
-__global__ void __launch_bounds__(Tile<LOGN>::T *G, 1) blind_rotate_split_kernel(const BRArgs a) {
+template <int LOGN, int G, int ELL = 0, int LOGB = 0, int R = 16>
+__global__ void __launch_bounds__((Tile<LOGN>::N / R) * G, 1) blind_rotate_split_kernel(const BRArgs a) {
     extern __shared__ __align__(16) unsigned char smem[];
-    blind_rotate_split_body<LOGN, G, ELL, LOGB>(a, threadIdx.x, blockIdx.x, smem);
+    blind_rotate_split_body<LOGN, G, ELL, LOGB, R>(a, threadIdx.x, blockIdx.x, smem);
 }
 
 template <int LOGN, int G>
@@ -162,6 +177,20 @@ static int launch_br_split_t(lux_engine *e, const BRArgs &a, cudaStream_t s) {
         CUDA_TRY(e, cudaFuncSetAttribute(blind_rotate_split_kernel<LOGN, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         if (NAMED) CUDA_TRY(e, cudaFuncSetAttribute(blind_rotate_split_kernel<LOGN, G, NAMED ? GE : 0, NAMED ? GB : 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured[e->device & 63] = true;
+    }
+    // narrow tile (8 coefficients per thread) for the named gadgets when the CTA still fits 1024 threads
+    if constexpr (NAMED && (Tile<LOGN>::N / 8) * G <= 1024) {
+        if (a.ell == (u32)GE && a.logB == (u32)GB && !e->generic_gadget && e->cluster_regs != 16) {
+            static bool configured8[64] = {};
+            if (!configured8[e->device & 63]) {
+                CUDA_TRY(e, cudaFuncSetAttribute(blind_rotate_split_kernel<LOGN, G, GE, GB, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+                configured8[e->device & 63] = true;
+            }
+            blind_rotate_split_kernel<LOGN, G, GE, GB, 8><<<a.B, (Tile<LOGN>::N / 8) * G, smem, s>>>(a);
+            e->launches++;
+            CUDA_TRY(e, cudaGetLastError());
+            return LUX_OK;
+        }
     }
     if (NAMED && a.ell == (u32)GE && a.logB == (u32)GB && !e->generic_gadget)
         blind_rotate_split_kernel<LOGN, G, NAMED ? GE : 0, NAMED ? GB : 0><<<a.B, Tile<LOGN>::T * G, smem, s>>>(a);
@@ -288,9 +317,7 @@ int LUX_CAT(lux_launch_br_, LUX_LOGN)(lux_engine *e, const BRArgs &a, cudaStream
     if (t <= 3) return launch_br_t<10, 3>(e, a, s);
     return launch_br_t<10, 6>(e, a, s);
 #elif LUX_LOGN == 11
-    // narrow tile: two ciphertexts per CTA (512 threads, 128 registers, no spills) measured best: 354.8 ms against
-    // 360.5 (three per CTA) and 368.5 (wide tile, three per CTA) for 4,440 ciphertexts
-    const int t = pick_teams(e, a.B, narrow_named(e, a.ell, a.logB) ? 2 : 3);
+    const int t = pick_teams_11(e, a.B, a.ell, a.logB);
     if (t <= 1) return launch_br_t<11, 1>(e, a, s);
     if (t <= 2) return launch_br_t<11, 2>(e, a, s);
     return launch_br_t<11, 3>(e, a, s);
@@ -314,7 +341,7 @@ size_t LUX_CAT(lux_br_wave_, LUX_LOGN)(const lux_engine *e, size_t B) {
     const int t = pick_teams(e, B, 6);
     return (size_t)e->sm_count * (t <= 1 ? 1 : t <= 3 ? 3 : 6);
 #elif LUX_LOGN == 11
-    const int t = pick_teams(e, B, narrow_named(e, e->p.ell, e->p.logB) ? 2 : 3);
+    const int t = pick_teams_11(e, B, e->p.ell, e->p.logB);
     return (size_t)e->sm_count * (t <= 1 ? 1 : t <= 2 ? 2 : 3);
 #else
     return (size_t)e->sm_count;

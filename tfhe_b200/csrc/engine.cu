@@ -263,7 +263,9 @@ static int launch_ks_mma(lux_engine *e, const u64 *d_in, u64 *d_out, size_t B, c
 
 static int launch_ks(lux_engine *e, const u64 *d_in, u64 *d_out, size_t B, cudaStream_t s) {
     const lux_params &p = e->p;
-    if (e->d_kskT && e->ks_mode != 0 && (e->ks_mode == 1 || B >= 256)) return launch_ks_mma(e, d_in, d_out, B, s);
+    // the tensor-core form is faster at every batch size (profiles/r01e_ks_probe.txt: 0.07 ms against 0.17 ms for one
+    // ciphertext, 0.075 against 4.2 ms for 148); the integer-pipe kernel below serves parameter sets it cannot take
+    if (e->d_kskT && e->ks_mode != 0) return launch_ks_mma(e, d_in, d_out, B, s);
     KSArgs a{p.n, p.k * p.N, p.ell_ks, p.logB_ks, e->L_ks, (u32)B, e->d_lksk, e->d_ksum, d_in, d_out, 1, nullptr};
     const size_t smem = sizeof(u32) * KS_RC * p.ell_ks * KS_TB;
     static bool configured[64] = {};

@@ -42,7 +42,7 @@ struct lux_engine {
     u32 ks_npad = 0;          // rows of d_kskT = 8 * (n + 1) rounded up to the N tile
     int8_t *d_ks_dig = nullptr;  // grow-only [Mpad][K] digit buffer
     size_t ks_dig_bytes = 0;
-    int ks_mode = -1;         // -1 = automatic (batches >= 256), 0 = integer-pipe kernel only, 1 = tensor-core kernel whenever eligible
+    int ks_mode = -1;         // -1 / 1 = tensor-core kernel whenever the parameter set is eligible, 0 = integer-pipe kernel only (tests)
     int br_regs = 8;              // throughput blind rotate of the named gadgets: coefficients per thread (8 = narrow tile,
                                   // default; 16 = wide tile; 4: tuning).  Other gadgets always run the wide tile.
     int cluster_regs = 0;         // cluster latency mode: coefficients per thread, 0 = automatic, 16 / 8 / 4 pinned (tests, tuning)

@@ -456,7 +456,10 @@ TK_DEV u64 rotated_coeff(const u64 *poly, int p, u32 sh) {
 // with bulk asynchronous copies (cp.async.bulk -> UBLKCP) that complete on an mbarrier; every warp
 // releases a stage through a second mbarrier once it has multiplied with it, so each key byte is fetched
 // once per CTA and reused by TEAMS ciphertexts.
-template <int LOGN> struct StageCfg { static constexpr int NSTAGE = (LOGN >= 12) ? 1 : 2; };
+#ifndef TK_NSTAGE_11
+#define TK_NSTAGE_11 2
+#endif
+template <int LOGN> struct StageCfg { static constexpr int NSTAGE = (LOGN >= 12) ? 1 : (LOGN == 11 ? TK_NSTAGE_11 : 2); };
 
 struct KeyStream {
     u64 *stage;        // [NSTAGE][2N] shared
@@ -655,7 +658,10 @@ TK_DEV void blind_rotate_body(const BRArgs &a, int tid, int bid, unsigned char *
 #if !defined(TFHE_EMU)
     // (only the compile-time-gadget instantiations: the longer runtime-gadget body measured slower in lock step)
     // and only the wide tile: the narrow-tile body is half the size and measured faster with drifting teams)
-    const int th = tk_team(team, (ELL && R == 16) ? (int)((a.B - (u32)bid * TEAMS < (u32)TEAMS ? a.B - (u32)bid * TEAMS : (u32)TEAMS) * T) : 0);
+#ifndef TK_LOCKSTEP_NARROW
+#define TK_LOCKSTEP_NARROW 0
+#endif
+    const int th = tk_team(team, (ELL && (R == 16 || TK_LOCKSTEP_NARROW)) ? (int)((a.B - (u32)bid * TEAMS < (u32)TEAMS ? a.B - (u32)bid * TEAMS : (u32)TEAMS) * T) : 0);
 #else
     const int th = team;
 #endif
@@ -721,9 +727,9 @@ constexpr size_t blind_rotate_split_smem_bytes() {
     return sizeof(u64) * ((size_t)3 * Tile<LOGN>::N + (size_t)G * 2 * Tile<LOGN>::N);
 }
 
-template <int LOGN, int G, int ELL = 0, int LOGB = 0>
+template <int LOGN, int G, int ELL = 0, int LOGB = 0, int R = 16>
 TK_DEV void blind_rotate_split_body(const BRArgs &a, int tid, int bid, unsigned char *smem_raw) {
-    constexpr int N = Tile<LOGN>::N, T = Tile<LOGN>::T;
+    constexpr int N = Tile<LOGN>::N, T = N / R, T16 = N / 16, R16 = 16 / R;
     u64 *tw = (u64 *)smem_raw;
     u64 *acc = tw + N;
     u64 *part = acc + 2 * N;  // [G][2][N]
@@ -755,20 +761,23 @@ TK_DEV void blind_rotate_split_body(const BRArgs &a, int tid, int bid, unsigned 
         if (i + 1 < a.steps) mask = lwe[i + 1];
         {   // phase 1: every team, its own digit polynomial
             const u64 *poly = acc + j * N;
-            u64 x[16];
+            u64 x[R];
             TK_UNROLL
-            for (int e = 0; e < 16; e++) {
-                const int p = posA<LOGN>(tau, e);
+            for (int e = 0; e < R; e++) {
+                const int p = e * T + tau;
                 u64 d = poly[p];
                 if (cmux) d = gl_sub(rotated_coeff<LOGN>(poly, p, sh), d);
                 x[e] = gl_digit(d, g_L - g_ell + lvl, g_logB, centred);
             }
-            team_ntt_forward<LOGN>(x, mine, tw, tau, g);
+            if constexpr (R == 16)
+                team_ntt_forward<LOGN>(x, mine, tw, tau, g);
+            else
+                team_ntt_forward_r<LOGN, R>(x, mine, tw, tau, g);
             const u64 *rows = (cmux ? a.bsk + i * ggsw_len : a.ksk) + (size_t)g * 2 * N;
             team_sync(g, T);  // the exchange buffer is about to be overwritten with the partials
             TK_UNROLL
-            for (int h = 0; h < 8; h++) {
-                const u64 *r0 = rows + (size_t)h * 2 * T + 2 * tau;
+            for (int h = 0; h < R / 2; h++) {
+                const u64 *r0 = rows + (size_t)((R / 2) * (tau & (R16 - 1)) + h) * 2 * T16 + 2 * (tau / R16);
                 const u64 *r1 = r0 + N;
 #if !defined(TFHE_EMU)
                 const ulonglong2 v0 = *reinterpret_cast<const ulonglong2 *>(r0);
@@ -785,18 +794,21 @@ TK_DEV void blind_rotate_split_body(const BRArgs &a, int tid, int bid, unsigned 
         }
         cta_sync();
         if (g < 2) {  // phase 2: team r = g owns output polynomial r
-            u64 o[16];
+            u64 o[R];
             TK_UNROLL
-            for (int e = 0; e < 16; e++) o[e] = part[(size_t)g * N + e * T + tau];
+            for (int e = 0; e < R; e++) o[e] = part[(size_t)g * N + e * T + tau];
             for (int gg = 1; gg < G; gg++) {
                 const u64 *src = part + ((size_t)gg * 2 + g) * N;
                 TK_UNROLL
-                for (int e = 0; e < 16; e++) o[e] = gl_add(o[e], src[e * T + tau]);
+                for (int e = 0; e < R; e++) o[e] = gl_add(o[e], src[e * T + tau]);
             }
-            team_ntt_inverse<LOGN>(o, mine + (size_t)g * N, tw, tau, g);
+            if constexpr (R == 16)
+                team_ntt_inverse<LOGN>(o, mine + (size_t)g * N, tw, tau, g);
+            else
+                team_ntt_inverse_r<LOGN, R>(o, mine + (size_t)g * N, tw, tau, g);
             TK_UNROLL
-            for (int e = 0; e < 16; e++) {
-                const int p = g * N + posA<LOGN>(tau, e);
+            for (int e = 0; e < R; e++) {
+                const int p = g * N + e * T + tau;
                 acc[p] = cmux ? gl_canon(gl_add(o[e], acc[p])) : gl_canon(o[e]);
             }
         }

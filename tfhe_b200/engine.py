@@ -345,8 +345,8 @@ class Engine:
         self._ck(lib().lux_debug_generic_gadget(self._h, int(bool(on))))
 
     def ks_mode(self, mode: int):
-        """LWE key switch kernel: -1 automatic (int8 tensor-core contraction for batches >= 256), 0 integer-pipe
-        kernel only, 1 tensor-core kernel whenever the parameter set is eligible"""
+        """LWE key switch kernel: -1 / 1 int8 tensor-core contraction whenever the parameter set is eligible (default),
+        0 integer-pipe kernel only"""
         self._ck(lib().lux_debug_ks_mode(self._h, mode))
 
     def force_teams(self, t: int):
