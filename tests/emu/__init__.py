@@ -39,6 +39,7 @@ def lib():
                             str(_SRC[0])], check=True, capture_output=True)
         L = C.CDLL(str(_LIB))
         L.emu_ntt.argtypes = [C.c_int, C.c_int, C.c_int, _u64p, _u64p, _u64p, C.c_uint64, C.c_uint32, C.c_uint32]
+        L.emu_force_slow.argtypes = [C.c_int]
         L.emu_ntt_r.argtypes = [C.c_int, C.c_int, _u64p, _u64p, _u64p, C.c_uint64, C.c_uint32, C.c_uint32]
         L.emu_blind_rotate.argtypes = [C.c_int, C.c_int, C.POINTER(BRArgs)]
         L.emu_blind_rotate_split.argtypes = [C.c_int, C.c_int, C.POINTER(BRArgs)]

@@ -91,7 +91,10 @@ static void to_key_t(u64 *ggsw, size_t n_polys, u32 ell, u64 ninv) {
         memcpy(poly, tmp.data(), sizeof(u64) * N);
     }
 }
+bool g_emu_force_slow = false;
 extern "C" {
+void emu_force_slow(int on) { g_emu_force_slow = on != 0; }
+
 
 int emu_ntt(int logn, int teams, int nblocks, const u64 *in, u64 *out, const u64 *tw, u64 scale, u32 n_polys, u32 inverse) {
     NttArgs a{in, out, tw, scale, n_polys, inverse};

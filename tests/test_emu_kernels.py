@@ -51,8 +51,33 @@ def test_emu_ntt_matches_oracle_and_golden(golden, logn, teams, nblocks, npolys)
     assert np.array_equal(back, polys)
 
 
+@pytest.fixture(params=[False, True], ids=["optimistic", "exact-path"])
+def slow_path(request):
+    """narrow-tile passes run optimistic butterflies and fall back to an exact out-of-line pass when a canonicalisation
+    they skipped would have mattered; `exact-path` forces that fallback on every pass"""
+    E.lib().emu_force_slow(int(request.param))
+    yield request.param
+    E.lib().emu_force_slow(0)
+
+
+def test_emu_narrow_tile_handles_non_canonical_intermediates(slow_path):
+    """inputs chosen so that intermediate sums land in [q, 2^64): all coefficients q-1 and 2^64-1 style lazy words"""
+    logn, r = 9, 8
+    N = 1 << logn
+    roots, inv, ninv = O.ntt_tables(N)
+    polys = np.stack([np.full(N, Q - 1, np.uint64), np.arange(N, dtype=np.uint64) * np.uint64(0xFFFFFFFF) % np.uint64(Q),
+                      np.where(np.arange(N) % 2 == 0, Q - 1, 1).astype(np.uint64)])
+    out = np.zeros_like(polys)
+    assert E.lib().emu_ntt_r(logn, r, polys.reshape(-1), out.reshape(-1), roots, 1, 3, 0) == 0
+    for i in range(3):
+        assert np.array_equal(out[i], O.ntt_forward(polys[i], roots))
+    back = np.zeros_like(polys)
+    assert E.lib().emu_ntt_r(logn, r, out.reshape(-1), back.reshape(-1), roots, ninv, 3, 1) == 0
+    assert np.array_equal(back, polys)
+
+
 @pytest.mark.parametrize("logn,r", [(9, 8), (9, 4), (10, 8), (10, 4), (11, 8), (11, 4), (12, 8)])
-def test_emu_narrow_tile_ntt_matches_oracle_and_golden(golden, logn, r):
+def test_emu_narrow_tile_ntt_matches_oracle_and_golden(golden, logn, r, slow_path):
     """the R = 4 / 8 register tiles of the latency modes: same in-place positions as the reference's transform"""
     N = 1 << logn
     roots, inv, ninv = O.ntt_tables(N)

@@ -187,6 +187,25 @@ GL_HD void gl_gs_butterfly_neg(u64 &u, u64 &v, u64 w) {
     v = gl_mul_lazy(d, w);
 }
 
+// ---- optimistic butterflies -----------------------------------------------------------------------------------
+// gl_canon is 5 of the ~22 ALU instructions of a butterfly, and it changes its operand only when the operand is in
+// [q, 2^64), i.e. when its high word is 0xFFFFFFFF (probability 2^-32 on transform data).  The optimistic forms skip
+// it and instead record "the high word was all ones" in `flag` (one ISETP with an OR-ed predicate).  When the flag stays
+// clear the skipped canonicalisation was the identity, so the result is the same word for word; when it is set the
+// caller recomputes the pass with the exact forms (tfhe_kernels.cuh pass_r_slow).
+GL_HD void gl_ct_butterfly_opt(u64 &u, u64 &v, u64 w, bool &flag) {
+    const u64 t = gl_mul_lazy(v, w);
+    flag |= ((u32)(t >> 32) == 0xFFFFFFFFu);
+    v = gl_sub(u, t);
+    u = gl_add(u, t);
+}
+GL_HD void gl_gs_butterfly_neg_opt(u64 &u, u64 &v, u64 w, bool &flag) {
+    flag |= ((u32)(u >> 32) == 0xFFFFFFFFu);
+    const u64 d = gl_sub(v, u);
+    u = gl_add(v, u);
+    v = gl_mul_lazy(d, w);
+}
+
 // ---- power-of-two twiddles -------------------------------------------------------------------------
 // 2 has order 192 in Z_q (2^96 = -1), so every 32nd root of unity is a power of 2^6.  The reference's first sixteen
 // table entries ROOTS[j] = psi^bitrev(j) (ntt/gen_param_file.sage:86-88) are the 32nd roots omega^bitrev4(j) with

@@ -279,8 +279,9 @@ GL_HD int pos_r(int tau, int e) {
     return ((tau >> lo) << (lo + LR)) | (e << lo) | (tau & ((1 << lo) - 1));
 }
 
-template <int R, int SH, bool INV>
-TK_DEV void tile_stage_r(u64 (&x)[R], const u64 *tw, int m, int i0) {
+// OPT: optimistic butterflies (gl64.cuh) that skip the canonicalisation and raise `flag` when it would have mattered
+template <int R, int SH, bool INV, bool OPT>
+TK_DEV void tile_stage_r(u64 (&x)[R], const u64 *tw, int m, int i0, bool &flag) {
     constexpr int half = 1 << (SH - 1);
     const u64 *p = INV ? tw + 2 * m - 1 - i0 : tw + m + i0;   // see tile_stage: INVROOTS[m+i] = -ROOTS[2m-1-i]
     TK_UNROLL
@@ -289,63 +290,133 @@ TK_DEV void tile_stage_r(u64 (&x)[R], const u64 *tw, int m, int i0) {
         TK_UNROLL
         for (int j = 0; j < half; j++) {
             const int e0 = (blk << SH) + j;
-            if (INV)
-                gl_gs_butterfly_neg(x[e0], x[e0 + half], w);
-            else
-                gl_ct_butterfly(x[e0], x[e0 + half], w);
+            if (INV) {
+                if (OPT)
+                    gl_gs_butterfly_neg_opt(x[e0], x[e0 + half], w, flag);
+                else
+                    gl_gs_butterfly_neg(x[e0], x[e0 + half], w);
+            } else {
+                if (OPT)
+                    gl_ct_butterfly_opt(x[e0], x[e0 + half], w, flag);
+                else
+                    gl_ct_butterfly(x[e0], x[e0 + half], w);
+            }
         }
     }
 }
 
 // stage S of the transform inside pass P (no-op when S is outside the pass)
-template <int LOGN, int R, int P, int S, bool INV>
-TK_DEV void pass_stage_r(u64 (&x)[R], const u64 *tw, int base) {
+template <int LOGN, int R, int P, int S, bool INV, bool OPT>
+TK_DEV void pass_stage_r(u64 (&x)[R], const u64 *tw, int base, bool &flag) {
     constexpr int LR = TileR<LOGN, R>::LR, lo = TileR<LOGN, R>::lo(P);
-    if constexpr (S >= P * LR && S < (P + 1) * LR && S < LOGN) tile_stage_r<R, LOGN - S - lo, INV>(x, tw, 1 << S, base >> (LOGN - S));
+    if constexpr (S >= P * LR && S < (P + 1) * LR && S < LOGN)
+        tile_stage_r<R, LOGN - S - lo, INV, OPT>(x, tw, 1 << S, base >> (LOGN - S), flag);
 }
-template <int LOGN, int R, int P, bool INV>
-TK_DEV void pass_r(u64 (&x)[R], const u64 *tw, int tau) {
+template <int LOGN, int R, int P, bool INV, bool OPT>
+TK_DEV void pass_r(u64 (&x)[R], const u64 *tw, int tau, bool &flag) {
     constexpr int LR = TileR<LOGN, R>::LR;
     const int base = pos_r<LOGN, R, P>(tau, 0);
     if constexpr (!INV) {
-        pass_stage_r<LOGN, R, P, P * LR + 0, false>(x, tw, base);
-        pass_stage_r<LOGN, R, P, P * LR + 1, false>(x, tw, base);
-        if constexpr (LR == 3) pass_stage_r<LOGN, R, P, P * LR + 2, false>(x, tw, base);
+        pass_stage_r<LOGN, R, P, P * LR + 0, false, OPT>(x, tw, base, flag);
+        pass_stage_r<LOGN, R, P, P * LR + 1, false, OPT>(x, tw, base, flag);
+        if constexpr (LR == 3) pass_stage_r<LOGN, R, P, P * LR + 2, false, OPT>(x, tw, base, flag);
     } else {
-        if constexpr (LR == 3) pass_stage_r<LOGN, R, P, P * LR + 2, true>(x, tw, base);
-        pass_stage_r<LOGN, R, P, P * LR + 1, true>(x, tw, base);
-        pass_stage_r<LOGN, R, P, P * LR + 0, true>(x, tw, base);
+        if constexpr (LR == 3) pass_stage_r<LOGN, R, P, P * LR + 2, true, OPT>(x, tw, base, flag);
+        pass_stage_r<LOGN, R, P, P * LR + 1, true, OPT>(x, tw, base, flag);
+        pass_stage_r<LOGN, R, P, P * LR + 0, true, OPT>(x, tw, base, flag);
     }
 }
 
-// exchange from the layout of pass PF to the layout of pass PT through xb.  FIRST: the buffer may still be read by
-// its previous user, so a barrier precedes the write; later exchanges write the slots the same thread read before.
-template <int LOGN, int R, int PF, int PT, bool FIRST>
-TK_DEV void exchange_r(u64 (&x)[R], u64 *xb, int tau, int team) {
-    constexpr int T = TileR<LOGN, R>::T;
-    if (FIRST) team_sync(team, T);
+// The exact pass, out of line and memory to memory: recomputes pass P of a thread from its inputs, which are still
+// parked in its own slots of the exchange buffer, and leaves the outputs there.  Runs when an optimistic pass raised
+// its flag (about once per 2^32 butterflies), so it must not cost the hot loop registers or instruction-cache space.
+#if defined(TFHE_EMU)
+extern bool g_emu_force_slow;   // emulator tests: take the exact path every time
+#define TK_NOINLINE
+#define TK_FORCE_SLOW_FLAG g_emu_force_slow
+#else
+#define TK_NOINLINE __device__ __noinline__
+#if defined(TK_FORCE_SLOW)
+#define TK_FORCE_SLOW_FLAG true
+#else
+#define TK_FORCE_SLOW_FLAG false
+#endif
+#endif
+template <int LOGN, int R, int P, bool INV>
+TK_NOINLINE void pass_r_slow(u64 *xb, const u64 *tw, int tau) {
+    u64 x[R];
+    bool unused = false;
     TK_UNROLL
-    for (int e = 0; e < R; e++) xb[tk_swz(pos_r<LOGN, R, PF>(tau, e))] = x[e];
-    team_sync(team, T);
+    for (int e = 0; e < R; e++) x[e] = xb[tk_swz(pos_r<LOGN, R, P>(tau, e))];
+    pass_r<LOGN, R, P, INV, false>(x, tw, tau, unused);
     TK_UNROLL
-    for (int e = 0; e < R; e++) x[e] = xb[tk_swz(pos_r<LOGN, R, PT>(tau, e))];
+    for (int e = 0; e < R; e++) xb[tk_swz(pos_r<LOGN, R, P>(tau, e))] = x[e];
+}
+
+// one pass of a transform: optimistic, with the exact recomputation behind a (practically never taken) branch
+template <int LOGN, int R, int P, bool INV>
+TK_DEV void pass_checked_r(u64 (&x)[R], u64 *xb, const u64 *tw, int tau) {
+#if defined(TK_NO_OPT)
+    bool none = false;   // A/B: exact butterflies in line, no fallback
+    pass_r<LOGN, R, P, INV, false>(x, tw, tau, none);
+    return;
+#endif
+    bool flag = TK_FORCE_SLOW_FLAG;
+    pass_r<LOGN, R, P, INV, true>(x, tw, tau, flag);
+    if (flag) {
+        pass_r_slow<LOGN, R, P, INV>(xb, tw, tau);
+        TK_UNROLL
+        for (int e = 0; e < R; e++) x[e] = xb[tk_swz(pos_r<LOGN, R, P>(tau, e))];
+    }
+}
+
+// Every pass but the first finds its inputs parked in the thread's own slots of xb (it has just read them there), which
+// is what lets pass_checked_r recompute it; the first pass of a transform runs the exact butterflies.
+template <int LOGN, int R, int P>
+TK_DEV void park_r(const u64 (&x)[R], u64 *xb, int tau) {
+    TK_UNROLL
+    for (int e = 0; e < R; e++) xb[tk_swz(pos_r<LOGN, R, P>(tau, e))] = x[e];
+}
+template <int LOGN, int R, int P>
+TK_DEV void fetch_r(u64 (&x)[R], const u64 *xb, int tau) {
+    TK_UNROLL
+    for (int e = 0; e < R; e++) x[e] = xb[tk_swz(pos_r<LOGN, R, P>(tau, e))];
 }
 
 // forward: in x[e] = a[pos_r<0>(tau, e)] (natural order), out x[e] = A[pos_r<NP-1>(tau, e)] = A[R tau + e]
 template <int LOGN, int R, int P = 0>
 TK_DEV void team_ntt_forward_r(u64 (&x)[R], u64 *xb, const u64 *tw, int tau, int team) {
-    pass_r<LOGN, R, P, false>(x, tw, tau);
+    constexpr int T = TileR<LOGN, R>::T;
+    if constexpr (P == 0) {
+        // the first pass has its inputs in registers only: exact butterflies, nothing to park
+        bool none = false;
+        pass_r<LOGN, R, 0, false, false>(x, tw, tau, none);
+        team_sync(team, T);   // the buffer may still be read by its previous user
+    } else {
+        pass_checked_r<LOGN, R, P, false>(x, xb, tw, tau);
+    }
     if constexpr (P + 1 < TileR<LOGN, R>::NP) {
-        exchange_r<LOGN, R, P, P + 1, P == 0>(x, xb, tau, team);
+        park_r<LOGN, R, P>(x, xb, tau);
+        team_sync(team, T);
+        fetch_r<LOGN, R, P + 1>(x, xb, tau);
         team_ntt_forward_r<LOGN, R, P + 1>(x, xb, tw, tau, team);
     }
 }
 // inverse WITHOUT the final 1/N: in x[e] = A[R tau + e], out x[e] = N * a[pos_r<0>(tau, e)] (lazy)
 template <int LOGN, int R, int P = TileR<LOGN, R>::NP - 1>
 TK_DEV void team_ntt_inverse_r(u64 (&x)[R], u64 *xb, const u64 *tw, int tau, int team) {
-    pass_r<LOGN, R, P, true>(x, tw, tau);
+    constexpr int T = TileR<LOGN, R>::T;
+    if constexpr (P == TileR<LOGN, R>::NP - 1) {
+        bool none = false;
+        pass_r<LOGN, R, P, true, false>(x, tw, tau, none);
+        team_sync(team, T);
+    } else {
+        pass_checked_r<LOGN, R, P, true>(x, xb, tw, tau);
+    }
     if constexpr (P > 0) {
-        exchange_r<LOGN, R, P, P - 1, P == TileR<LOGN, R>::NP - 1>(x, xb, tau, team);
+        park_r<LOGN, R, P>(x, xb, tau);
+        team_sync(team, T);
+        fetch_r<LOGN, R, P - 1>(x, xb, tau);
         team_ntt_inverse_r<LOGN, R, P - 1>(x, xb, tw, tau, team);
     }
 }
