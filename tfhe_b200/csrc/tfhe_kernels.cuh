@@ -354,8 +354,13 @@ TK_NOINLINE void pass_r_slow(u64 *xb, const u64 *tw, int tau) {
 }
 
 // one pass of a transform: optimistic, with the exact recomputation behind a (practically never taken) branch
-template <int LOGN, int R, int P, bool INV>
+template <int LOGN, int R, int P, bool INV, bool OPT = true>
 TK_DEV void pass_checked_r(u64 (&x)[R], u64 *xb, const u64 *tw, int tau) {
+    if constexpr (!OPT) {   // latency kernels with one or two teams per CTA: the flag chain and its branch cost more
+        bool none = false;  // on their critical path than the canonicalisation (S2 cluster mode: 7.7 vs 8.1 ms)
+        pass_r<LOGN, R, P, INV, false>(x, tw, tau, none);
+        return;
+    }
 #if defined(TK_NO_OPT)
     bool none = false;   // A/B: exact butterflies in line, no fallback
     pass_r<LOGN, R, P, INV, false>(x, tw, tau, none);
@@ -384,7 +389,7 @@ TK_DEV void fetch_r(u64 (&x)[R], const u64 *xb, int tau) {
 }
 
 // forward: in x[e] = a[pos_r<0>(tau, e)] (natural order), out x[e] = A[pos_r<NP-1>(tau, e)] = A[R tau + e]
-template <int LOGN, int R, int P = 0>
+template <int LOGN, int R, bool OPT = true, int P = 0>
 TK_DEV void team_ntt_forward_r(u64 (&x)[R], u64 *xb, const u64 *tw, int tau, int team) {
     constexpr int T = TileR<LOGN, R>::T;
     if constexpr (P == 0) {
@@ -393,17 +398,17 @@ TK_DEV void team_ntt_forward_r(u64 (&x)[R], u64 *xb, const u64 *tw, int tau, int
         pass_r<LOGN, R, 0, false, false>(x, tw, tau, none);
         team_sync(team, T);   // the buffer may still be read by its previous user
     } else {
-        pass_checked_r<LOGN, R, P, false>(x, xb, tw, tau);
+        pass_checked_r<LOGN, R, P, false, OPT>(x, xb, tw, tau);
     }
     if constexpr (P + 1 < TileR<LOGN, R>::NP) {
         park_r<LOGN, R, P>(x, xb, tau);
         team_sync(team, T);
         fetch_r<LOGN, R, P + 1>(x, xb, tau);
-        team_ntt_forward_r<LOGN, R, P + 1>(x, xb, tw, tau, team);
+        team_ntt_forward_r<LOGN, R, OPT, P + 1>(x, xb, tw, tau, team);
     }
 }
 // inverse WITHOUT the final 1/N: in x[e] = A[R tau + e], out x[e] = N * a[pos_r<0>(tau, e)] (lazy)
-template <int LOGN, int R, int P = TileR<LOGN, R>::NP - 1>
+template <int LOGN, int R, bool OPT = true, int P = TileR<LOGN, R>::NP - 1>
 TK_DEV void team_ntt_inverse_r(u64 (&x)[R], u64 *xb, const u64 *tw, int tau, int team) {
     constexpr int T = TileR<LOGN, R>::T;
     if constexpr (P == TileR<LOGN, R>::NP - 1) {
@@ -411,13 +416,13 @@ TK_DEV void team_ntt_inverse_r(u64 (&x)[R], u64 *xb, const u64 *tw, int tau, int
         pass_r<LOGN, R, P, true, false>(x, tw, tau, none);
         team_sync(team, T);
     } else {
-        pass_checked_r<LOGN, R, P, true>(x, xb, tw, tau);
+        pass_checked_r<LOGN, R, P, true, OPT>(x, xb, tw, tau);
     }
     if constexpr (P > 0) {
         park_r<LOGN, R, P>(x, xb, tau);
         team_sync(team, T);
         fetch_r<LOGN, R, P - 1>(x, xb, tau);
-        team_ntt_inverse_r<LOGN, R, P - 1>(x, xb, tw, tau, team);
+        team_ntt_inverse_r<LOGN, R, OPT, P - 1>(x, xb, tw, tau, team);
     }
 }
 
@@ -843,7 +848,7 @@ TK_DEV void blind_rotate_split_body(const BRArgs &a, int tid, int bid, unsigned 
             if constexpr (R == 16)
                 team_ntt_forward<LOGN>(x, mine, tw, tau, g);
             else
-                team_ntt_forward_r<LOGN, R>(x, mine, tw, tau, g);
+                team_ntt_forward_r<LOGN, R, (G >= 4)>(x, mine, tw, tau, g);
             const u64 *rows = (cmux ? a.bsk + i * ggsw_len : a.ksk) + (size_t)g * 2 * N;
             team_sync(g, T);  // the exchange buffer is about to be overwritten with the partials
             TK_UNROLL
@@ -876,7 +881,7 @@ TK_DEV void blind_rotate_split_body(const BRArgs &a, int tid, int bid, unsigned 
             if constexpr (R == 16)
                 team_ntt_inverse<LOGN>(o, mine + (size_t)g * N, tw, tau, g);
             else
-                team_ntt_inverse_r<LOGN, R>(o, mine + (size_t)g * N, tw, tau, g);
+                team_ntt_inverse_r<LOGN, R, (G >= 4)>(o, mine + (size_t)g * N, tw, tau, g);
             TK_UNROLL
             for (int e = 0; e < R; e++) {
                 const int p = g * N + e * T + tau;
@@ -977,7 +982,7 @@ __device__ __forceinline__ void blind_rotate_cluster_body(const BRArgs &a, int t
             if constexpr (R == 16)
                 team_ntt_forward<LOGN>(x, xb, tw, tau, lvl);
             else
-                team_ntt_forward_r<LOGN, R>(x, xb, tw, tau, lvl);
+                team_ntt_forward_r<LOGN, R, (TPC >= 2)>(x, xb, tw, tau, lvl);
             const u64 *rows = (cmux ? a.bsk + i * ggsw_len : a.ksk) + ((size_t)r * g_ell + (u32)lvl) * 2 * N;
             u64 *mine = part + (size_t)par * 2 * N;
             TK_UNROLL
@@ -1015,7 +1020,7 @@ __device__ __forceinline__ void blind_rotate_cluster_body(const BRArgs &a, int t
             if constexpr (R == 16)
                 team_ntt_inverse<LOGN>(o, xb, tw, tau, 0);
             else
-                team_ntt_inverse_r<LOGN, R>(o, xb, tw, tau, 0);
+                team_ntt_inverse_r<LOGN, R, (TPC >= 2)>(o, xb, tw, tau, 0);
             TK_UNROLL
             for (int e = 0; e < R; e++) {
                 const int p = e * T + tau;
