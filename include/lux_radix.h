@@ -122,6 +122,10 @@ int lux_radix_set_pool_bytes(lux_engine *e, size_t bytes);
  * op = LUX_OP_* or LUX_PROG_SELECT / LUX_PROG_ERC20.  Returns the stream length (call with cap = 0 to size). */
 #define LUX_PROG_SELECT 100
 #define LUX_PROG_ERC20 101
+/* OR-ed into `op`: the shallow variant of the circuit (carry chains resolved by a parallel-prefix scan: log2(blocks) + 2
+ * levels instead of `blocks`, ~3.5x the bootstraps), which lux_eval* / lux_erc20_transfer* run on their own when
+ * batch * blocks <= 296, i.e. while a level fits the latency-mode kernels and depth is what costs time */
+#define LUX_PROG_SHALLOW 0x1000
 size_t lux_radix_program(int op, unsigned bit_width, int64_t *buf, size_t cap);
 /* the divisor-specific circuit of LUX_OP_DIV / LUX_OP_REM (other ops: same as lux_radix_program) */
 size_t lux_radix_program_scalar(int op, unsigned bit_width, const uint64_t *scalar_limbs, size_t n_limbs, int64_t *buf,

@@ -102,7 +102,8 @@ def main():
         la = binop(op)
         la.width = width
         ob = 1 if op in R.PREDICATES else R.blocks(width)
-        run(op, width, batch, plain, la, 2, R.pbs_count(op, width), R.depth(op, width), [ob])
+        prog = R.program(op, width, shallow=R.runs_shallow(width, batch))   # the variant the library runs for this batch
+        run(op, width, batch, plain, la, 2, prog.n_pbs, len(prog.levels), [ob])
 
     scale = 4 if args.quick else 1
     for width in (8, 16):
@@ -149,6 +150,15 @@ def main():
     m64 = (1 << 64) - 1
     run("erc20_transfer", 64, 1024 // scale, lambda f, t, a: ((f - a) & m64, (t + a) & m64) if a <= f else (f, t), erc_launch, 3,
         int(L.lux_erc20_pbs_count()), int(L.lux_erc20_depth()), [32, 32])
+
+    # single-operation latency: a batch of ONE integer (levels of a few ciphertexts take the latency-mode kernels:
+    # two SMs per ciphertext, narrow tiles); `seconds` is the latency of the operation
+    bench_binop("add", 8, 1, lambda a, b: (a + b) & 0xFF)
+    bench_binop("add", 64, 1, lambda a, b: (a + b) & m64)
+    bench_binop("lt", 64, 1, lambda a, b: int(a < b))
+    erc1 = R.program(R.PROG_ERC20, 64, shallow=True)
+    run("erc20_transfer", 64, 1, lambda f, t, a: ((f - a) & m64, (t + a) & m64) if a <= f else (f, t), erc_launch, 3,
+        erc1.n_pbs, len(erc1.levels), [32, 32])
 
     Path(args.out).parent.mkdir(parents=True, exist_ok=True)
     Path(args.out).write_text(json.dumps({"workload": "S2 shape (n=918, N=2048), one B200, device-resident operands",

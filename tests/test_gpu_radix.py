@@ -108,12 +108,40 @@ def test_select_and_erc20_match_cpu_interpreter(small):
     r = small
     f, t, a = r.encrypt([10000, 1000], 64), r.encrypt([0, 5], 64), r.encrypt([1337, 1337], 64)
     nf, nt = r.rx.erc20_transfer(f, t, a)
-    want = interp_cipher(r.ctx, R.program(R.PROG_ERC20, 64), r.luts, [f, t, a], r.testv, r.delta)
+    assert R.runs_shallow(64, 2)      # two transfers: the library runs the parallel-prefix-carry variant (8 levels)
+    want = interp_cipher(r.ctx, R.program(R.PROG_ERC20, 64, shallow=True), r.luts, [f, t, a], r.testv, r.delta)
     assert np.array_equal(nf, want[0]) and np.array_equal(nt, want[1])
     assert r.decrypt(nf) == [8663, 1000] and r.decrypt(nt) == [1337, 5]       # EncryptedERC20.ts:98,114 / :136-183
     cond = r.rx.eval("le", 64, a, f)
     sel = r.rx.select(64, cond, a, t)
     assert r.decrypt(sel) == [1337, 5]
+
+
+@pytest.mark.parametrize("op,width", [("add", 16), ("sub", 64), ("neg", 32), ("add", 128)])
+def test_shallow_and_deep_variants(small, op, width):
+    """tiny batches run the shallow (parallel-prefix carry) circuit, large ones the ripple circuit: each bit-exact
+    against the CPU interpreter of the same circuit, both decrypting to the plaintext result"""
+    r = small
+    m = (1 << width) - 1
+    rnd = np.random.RandomState(width)
+    few = [m, 1, int("0011" * (width // 4), 2)][:2 if width > 64 else 3]
+    many = [int(rnd.randint(0, 2**31)) * int(rnd.randint(0, 2**31)) & m for _ in range(300 // R.blocks(width) + 2)]
+    for vals in (few, many):
+        others = [(v * 7 + 1) & m if i else int("1101" * (width // 4), 2) for i, v in enumerate(vals)]
+        a, b = r.encrypt(vals, width), r.encrypt(others, width)
+        shallow = R.runs_shallow(width, len(vals))
+        assert shallow == (vals is few)
+        prog = R.program(op, width, shallow=shallow)
+        if op == "neg":
+            got = r.rx.eval(op, width, a)
+            want = interp_cipher(r.ctx, prog, r.luts, [a[:2]], r.testv, r.delta)[0]
+            plain = [(-v) & m for v in vals]
+        else:
+            got = r.rx.eval(op, width, a, b)
+            want = interp_cipher(r.ctx, prog, r.luts, [a[:2], b[:2]], r.testv, r.delta)[0]
+            plain = [((v + o) if op == "add" else (v - o)) & m for v, o in zip(vals, others)]
+        assert np.array_equal(got[:2], want)
+        assert r.decrypt(got) == plain
 
 
 def test_div_rem_by_plaintext_match_cpu_interpreter(small):

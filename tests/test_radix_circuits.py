@@ -142,6 +142,45 @@ def test_erc20_vectors():
         assert (join_blocks(out[0]), join_blocks(out[1])) == (nf, nt), (f, t, a)
 
 
+@pytest.mark.parametrize("width", [16, 32, 64, 128, 256])
+def test_shallow_variants_match_plain_semantics(width):
+    """the parallel-prefix-carry variants (LUX_PROG_SHALLOW, run for tiny batches): same results as the plaintext
+    semantics on the fhEVM known answers of add / sub / neg plus carry-chain edge cases, clean outputs, every PBS input
+    below the padding bit (interp_plain raises otherwise), and log depth"""
+    m = (1 << width) - 1
+    rnd = random.Random(width)
+    kat = [(k["op"], int(k["args"][0]), int(k["args"][1]) if len(k["args"]) > 1 else None) for k in KATS["ops"]
+           if k["op"] in ("add", "sub", "neg") and width_of(k["types"][0]) == width
+           and all(width_of(t) == width for t in k["types"])]
+    edge = [(m, 1), (m, m), (0, 0), (0, 1), (1, m), (m >> 1, 1), (int("01" * (width // 2), 2), int("10" * (width // 2), 2) + 1),
+            (int("0011" * (width // 4), 2), int("1100" * (width // 4), 2)), (int("0011" * (width // 4), 2), int("1101" * (width // 4), 2))]
+    edge += [(rnd.randrange(m + 1), rnd.randrange(m + 1)) for _ in range(40)]
+    for op in ("add", "sub", "neg"):
+        prog, ref = R.program(op, width, shallow=True), R.program(op, width)
+        assert len(prog.levels) <= max(4, (width // 2 - 1).bit_length() + 2) and len(prog.levels) < len(ref.levels)
+        cases = edge + [(a, b if b is not None else 0) for o, a, b in kat if o == op]
+        for a, b in cases:
+            ins = [split_blocks(a, width // 2)] + ([] if op == "neg" else [split_blocks(b, width // 2)])
+            out = interp_plain(prog, LUTS, ins)
+            assert all(0 <= d < 4 for d in out[0])
+            assert join_blocks(out[0]) == plain_semantics(op, a, b, width), (op, hex(a), hex(b))
+
+
+def test_shallow_erc20_vectors():
+    prog, ref = R.program(R.PROG_ERC20, 64, shallow=True), R.program(R.PROG_ERC20, 64)
+    assert len(prog.levels) <= 10 < len(ref.levels)
+    rnd = random.Random(4)
+    cases = [(v["mint"], 0, v["transfer"], v["from_after"], v["to_after"]) for v in KATS["erc20"]]
+    for _ in range(40):
+        f, t, a = rnd.randrange(1 << 40), rnd.randrange(1 << 40), rnd.randrange(1 << 41)
+        cases.append((f, t, a, f - a if a <= f else f, t + a if a <= f else t))
+    cases.append(((1 << 64) - 1, (1 << 64) - 1, 1, (1 << 64) - 2, 0))
+    cases.append((5, (1 << 64) - 1, 5, 0, 4))
+    for f, t, a, nf, nt in cases:
+        out = interp_plain(prog, LUTS, [split_blocks(f, 32), split_blocks(t, 32), split_blocks(a, 32)])
+        assert (join_blocks(out[0]), join_blocks(out[1])) == (nf, nt), (f, t, a)
+
+
 def test_pbs_counts_and_depths():
     """circuit sizes reported to bench.py agree with the programs; sanity bounds on the designs"""
     for op in ("add", "sub", "lt", "eq", "and", "mul"):

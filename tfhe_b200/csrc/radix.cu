@@ -30,6 +30,7 @@ enum { PRED_LT = 0, PRED_LE, PRED_GT, PRED_GE, PRED_EQ, PRED_NE, PRED_N };
 enum LutId {
     L_MSG = 0, L_CARRY, L_MUL_LO, L_MUL_HI, L_AND, L_OR, L_XOR, L_SEL_A, L_SEL_B, L_CMP, L_CMPRED, L_EQB,
     L_SHL1, L_SHR1, L_BIT0, L_BIT1,
+    L_PGN, L_GEN, L_PFX,                // parallel-prefix carries (shallow circuits)
     L_PRED_CMP0,                        // + pred: pred(sign(hi, lo))
     L_PRED_RED0 = L_PRED_CMP0 + PRED_N, // + pred: pred(reduce(sign_hi, sign_lo))
     L_EQK0 = L_PRED_RED0 + PRED_N,      // + k: x == k
@@ -71,6 +72,10 @@ int lut_eval(int id, int x) {
         case L_SHR1: return (lo >> 1) | ((hi & 1) << 1);    // x = 4*a_{i+1} + a_i
         case L_BIT0: return x & 1;
         case L_BIT1: return (x >> 1) & 1;
+        // carry state of a column sum s <= 7 that receives a carry of at most 1: 0 = none, 1 = generates, 2 = propagates
+        case L_PGN: return x >= 4 ? 1 : (x == 3 ? 2 : 0);
+        case L_GEN: return x >= 4;                      // least significant column: nothing to propagate
+        case L_PFX: return hi == 2 ? lo : hi;           // x = 4*state(upper span) + state(lower span)
         default: break;
     }
     if (id >= L_PRED_CMP0 && id < L_PRED_CMP0 + PRED_N) return pred_of_sign(id - L_PRED_CMP0, sign3(hi, lo));
@@ -158,6 +163,9 @@ struct Program {
 struct Builder {
     Program p;
     std::vector<int> in_base;
+    // shallow: resolve the final carry chain of ripple() with a parallel-prefix scan (log2(blocks) + 2 levels instead of
+    // `blocks`, about 3.5x the bootstraps): chosen for batches so small that the depth, not the count, is the time
+    bool shallow = false;
 
     int add_input(int blocks) {
         in_base.push_back(p.n_slots);
@@ -285,6 +293,33 @@ struct Builder {
             }
             cols.swap(next);
             if (!any) break;
+        }
+        if (shallow && nb >= 8) {   // below 8 columns the scan is as deep as the chain
+            // eligible when no column can emit a carry above 1: sums <= 6 (<= 7 in column 0, which receives none)
+            std::vector<Val> sum(nb);
+            bool ok = true;
+            for (int k = 0; k < nb; k++) {
+                sum[k] = cst(0);
+                for (auto &v : cols[k]) sum[k] = add(sum[k], v);
+                if (sum[k].lo < 0 || sum[k].hi > (k == 0 ? 7 : 6)) ok = false;
+            }
+            if (ok) {
+                // st[k] = carry state of the span ending at column k; after the scan st[k] is the carry OUT of column k
+                // (0 / 1): spans that start at column 0 only hold 0 or 1 because column 0 uses L_GEN
+                std::vector<Val> st(nb - 1);
+                for (int k = 0; k + 1 < nb; k++) st[k] = sum[k].hi <= 2 ? cst(0) : pbs(sum[k], k == 0 ? L_GEN : L_PGN);
+                for (int d = 1; d < nb - 1; d <<= 1) {
+                    std::vector<Val> nx = st;
+                    for (int k = d; k + 1 < nb; k++) nx[k] = pbs(pack(st[k], st[k - d]), L_PFX);
+                    st.swap(nx);
+                }
+                std::vector<Val> out(nb);
+                for (int k = 0; k < nb; k++) {
+                    const Val s = k ? add(sum[k], assume(st[k - 1], 0, 1)) : sum[k];
+                    out[k] = s.hi <= 3 ? s : pbs(s, L_MSG);
+                }
+                return out;
+            }
         }
         std::vector<Val> out(nb);
         Val carry = cst(0);
@@ -488,10 +523,11 @@ struct Builder {
     }
 };
 
-Program build_program(int op, unsigned bw, const Wide &scalar) {
+Program build_program(int op, unsigned bw, const Wide &scalar, bool shallow = false) {
     const int nb = (int)lux_radix_blocks(bw);
     if (nb == 0) throw std::logic_error("unsupported bit width");
     Builder b;
+    b.shallow = shallow;
     if (op == LUX_OP_DIV || op == LUX_OP_REM) {   // plaintext divisor: the circuit depends on it
         if (scalar.is_zero()) throw std::logic_error("division by zero");
         const int l = b.add_input(nb);
@@ -554,13 +590,20 @@ Program build_program(int op, unsigned bw, const Wide &scalar) {
 }
 
 std::mutex g_prog_mutex;
+// op | LUX_PROG_SHALLOW selects the shallow variant of a circuit (parallel-prefix carries)
 std::map<std::pair<int, unsigned>, Program> g_programs;
 const Program &get_program(int op, unsigned bw) {
     std::lock_guard<std::mutex> lk(g_prog_mutex);
     auto key = std::make_pair(op, bw);
     auto it = g_programs.find(key);
-    if (it == g_programs.end()) it = g_programs.emplace(key, build_program(op, bw, Wide())).first;
+    if (it == g_programs.end())
+        it = g_programs.emplace(key, build_program(op & ~LUX_PROG_SHALLOW, bw, Wide(), (op & LUX_PROG_SHALLOW) != 0)).first;
     return it->second;
+}
+// the variant to run for `batch` integers: depth is what costs time while a level fits the latency-mode kernels
+// (a level of the shallow carry scan has up to blocks - 1 bootstraps per integer)
+static int pick_variant(int op, unsigned bw, size_t batch) {
+    return batch * lux_radix_blocks(bw) <= 296 ? (op | LUX_PROG_SHALLOW) : op;
 }
 // divisor-specific circuits (div / rem by a plaintext): bounded cache, entries stay alive while in use
 std::map<std::tuple<int, unsigned, std::array<u64, 4>>, std::shared_ptr<const Program>> g_scalar_programs;
@@ -895,7 +938,7 @@ int lux_eval(lux_engine *e, lux_op op, unsigned bw, const uint64_t *lhs, const u
         int rc = check_op(e, op, bw, lhs, rhs, out);
         if (rc) return rc;
         if ((rc = reject_scalar_only(e, op))) return rc;
-        const Program &p = get_program((int)op, bw);
+        const Program &p = get_program(pick_variant((int)op, bw, batch), bw);
         std::vector<const u64 *> in{lhs};
         if (!lux_op_is_unary(op)) in.push_back(rhs);
         return exec_host(e, p, in, {out}, batch);
@@ -907,7 +950,7 @@ int lux_eval_device(lux_engine *e, lux_op op, unsigned bw, const uint64_t *lhs, 
         if (rc) return rc;
         if ((rc = reject_scalar_only(e, op))) return rc;
         CUDA_TRY(e, cudaSetDevice(e->device));
-        const Program &p = get_program((int)op, bw);
+        const Program &p = get_program(pick_variant((int)op, bw, batch), bw);
         std::vector<const u64 *> in{lhs};
         if (!lux_op_is_unary(op)) in.push_back(rhs);
         return exec_program(e, p, in, {out}, batch);
@@ -964,7 +1007,7 @@ static int eval_scalar_impl(lux_engine *e, lux_op op, unsigned bw, const uint64_
             return LUX_OK;
         }
         if (n_limbs != 1) LUX_FAIL(e, LUX_ERR_INVALID, "wide plaintext operands are supported for div/rem only");
-        const Program &p = get_program((int)op, bw);
+        const Program &p = get_program(pick_variant((int)op, bw, batch), bw);
         const size_t nb = lux_radix_blocks(bw), w = lux_ct_words(e), words = batch * nb * w;
         const size_t out_words = batch * (size_t)p.out_blocks[0] * w;
         if ((rc = lux_ensure_scratch(e, 1, sizeof(u64) * words))) return rc;
@@ -1025,7 +1068,7 @@ int lux_erc20_transfer(lux_engine *e, const uint64_t *from_bal, const uint64_t *
                        uint64_t *new_from, uint64_t *new_to) {
     return guarded(e, [&]() -> int {
         if (!from_bal || !to_bal || !amount || !new_from || !new_to) LUX_FAIL(e, LUX_ERR_INVALID, "lux_erc20_transfer: null argument");
-        return exec_host(e, get_program(LUX_PROG_ERC20, 64), {from_bal, to_bal, amount}, {new_from, new_to}, batch);
+        return exec_host(e, get_program(pick_variant(LUX_PROG_ERC20, 64, batch), 64), {from_bal, to_bal, amount}, {new_from, new_to}, batch);
     });
 }
 int lux_erc20_transfer_device(lux_engine *e, const uint64_t *from_bal, const uint64_t *to_bal, const uint64_t *amount, size_t batch,
@@ -1033,7 +1076,7 @@ int lux_erc20_transfer_device(lux_engine *e, const uint64_t *from_bal, const uin
     return guarded(e, [&]() -> int {
         if (!from_bal || !to_bal || !amount || !new_from || !new_to) LUX_FAIL(e, LUX_ERR_INVALID, "lux_erc20_transfer_device: null argument");
         CUDA_TRY(e, cudaSetDevice(e->device));
-        return exec_program(e, get_program(LUX_PROG_ERC20, 64), {from_bal, to_bal, amount}, {new_from, new_to}, batch);
+        return exec_program(e, get_program(pick_variant(LUX_PROG_ERC20, 64, batch), 64), {from_bal, to_bal, amount}, {new_from, new_to}, batch);
     });
 }
 

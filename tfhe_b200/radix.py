@@ -103,9 +103,20 @@ class Program:
         return sum(len(lv) for lv in self.levels)
 
 
-def program(op, bit_width: int, scalar: int | None = None) -> Program:
-    """the circuit of `op`; div/rem need the plaintext divisor `scalar` (the circuit is divisor-specific)"""
+PROG_SHALLOW = 0x1000   # lux_radix.h LUX_PROG_SHALLOW
+
+
+def runs_shallow(bit_width: int, batch: int) -> bool:
+    """does lux_eval* / lux_erc20_transfer* take the shallow variant for this batch? (radix.cu pick_variant)"""
+    return batch * blocks(bit_width) <= 296
+
+
+def program(op, bit_width: int, scalar: int | None = None, shallow: bool = False) -> Program:
+    """the circuit of `op`; div/rem need the plaintext divisor `scalar` (the circuit is divisor-specific);
+    shallow = the parallel-prefix-carry variant the library runs for very small batches"""
     code = OPS[op] if isinstance(op, str) else int(op)
+    if shallow:
+        code |= PROG_SHALLOW
     sc = _limbs(int(scalar or 0), 4)
     n = lib().lux_radix_program_scalar(code, bit_width, sc.ctypes.data, 4, None, 0)
     if n == 0:
