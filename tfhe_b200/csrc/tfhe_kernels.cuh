@@ -532,10 +532,11 @@ TK_DEV u64 rotated_coeff(const u64 *poly, int p, u32 sh) {
 // with bulk asynchronous copies (cp.async.bulk -> UBLKCP) that complete on an mbarrier; every warp
 // releases a stage through a second mbarrier once it has multiplied with it, so each key byte is fetched
 // once per CTA and reused by TEAMS ciphertexts.
-#ifndef TK_NSTAGE_11
-#define TK_NSTAGE_11 2
-#endif
-template <int LOGN> struct StageCfg { static constexpr int NSTAGE = (LOGN >= 12) ? 1 : (LOGN == 11 ? TK_NSTAGE_11 : 2); };
+// ring depth: as many stages as shared memory leaves next to TEAMS ciphertexts (16N bytes per stage): one at N = 4096,
+// three at N = 2048 with at most two ciphertexts per CTA (measured -0.5 % against two), two otherwise
+template <int LOGN, int TEAMS = 0> struct StageCfg {
+    static constexpr int NSTAGE = (LOGN >= 12) ? 1 : ((LOGN == 11 && TEAMS >= 1 && TEAMS <= 2) ? 3 : 2);
+};
 
 struct KeyStream {
     u64 *stage;        // [NSTAGE][2N] shared
@@ -576,9 +577,9 @@ __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, u32 bytes, 
                  : "memory");
 }
 
-template <int LOGN>
+template <int LOGN, int NS>
 __device__ __forceinline__ void stream_issue(const KeyStream &ks, u32 t) {
-    constexpr int N = 1 << LOGN, NS = StageCfg<LOGN>::NSTAGE;
+    constexpr int N = 1 << LOGN;
     if (t >= ks.total) return;
     const u64 *src = (t < ks.bsk_pairs) ? ks.bsk + (size_t)t * 2 * N : ks.ksk + (size_t)(t - ks.bsk_pairs) * 2 * N;
     u64 *dst = ks.stage + (size_t)(t % NS) * 2 * N;
@@ -598,7 +599,7 @@ __device__ __forceinline__ void stream_issue(const KeyStream &ks, u32 t) {
 // ELL / LOGB != 0 fix the gadget at compile time (the named parameter sets): the digit rule then folds to a few
 // shifts instead of 64-bit variable shifts and selects per coefficient.  0 = read it from BRArgs.
 // R = coefficients per thread (16 = wide tile; 8 / 4 = narrow tiles with N/R threads per team)
-template <int LOGN, bool STAGED, int ELL = 0, int LOGB = 0, int R = 16>
+template <int LOGN, bool STAGED, int ELL = 0, int LOGB = 0, int R = 16, int TEAMS = 0>
 TK_DEV void team_external_product(const BRArgs &a, const u64 *ggsw, KeyStream &ks, bool cmux, u32 sh, u64 *acc, u64 *xb,
                                   const u64 *tw, int tau, int team, int lane) {
     constexpr int N = Tile<LOGN>::N, T = N / R, T16 = N / 16, R16 = 16 / R;
@@ -630,7 +631,7 @@ TK_DEV void team_external_product(const BRArgs &a, const u64 *ggsw, KeyStream &k
                 team_ntt_forward_r<LOGN, R>(x, xb, tw, tau, team);
             const u64 *rows;
 #if !defined(TFHE_EMU)
-            constexpr int NS = StageCfg<LOGN>::NSTAGE;
+            constexpr int NS = StageCfg<LOGN, TEAMS>::NSTAGE;
             if (STAGED) {
                 mbar_wait(ks.full + (ks.t % NS), (ks.t / NS) & 1);
                 rows = ks.stage + (size_t)(ks.t % NS) * 2 * N;
@@ -664,7 +665,7 @@ TK_DEV void team_external_product(const BRArgs &a, const u64 *ggsw, KeyStream &k
                 if (ks.producer && ks.t + 1 >= (u32)NS) {
                     const u32 r = ks.t + 1 - NS;
                     mbar_wait(ks.empty + (r % NS), (r / NS) & 1);
-                    stream_issue<LOGN>(ks, r + NS);
+                    stream_issue<LOGN, NS>(ks, r + NS);
                 }
                 ks.t++;
             }
@@ -694,12 +695,12 @@ TK_DEV void team_external_product(const BRArgs &a, const u64 *ggsw, KeyStream &k
 // shared memory: [tw N] then per team [acc 2N][xb N], then the key ring [NSTAGE][2N] and its mbarriers
 template <int LOGN, int TEAMS>
 constexpr size_t blind_rotate_smem_bytes() {
-    return sizeof(u64) * ((size_t)Tile<LOGN>::N + (size_t)TEAMS * 3 * Tile<LOGN>::N + (size_t)StageCfg<LOGN>::NSTAGE * 2 * Tile<LOGN>::N) + 64;
+    return sizeof(u64) * ((size_t)Tile<LOGN>::N + (size_t)TEAMS * 3 * Tile<LOGN>::N + (size_t)StageCfg<LOGN, TEAMS>::NSTAGE * 2 * Tile<LOGN>::N) + 64;
 }
 
 template <int LOGN, int TEAMS, int ELL = 0, int LOGB = 0, int R = 16>
 TK_DEV void blind_rotate_body(const BRArgs &a, int tid, int bid, unsigned char *smem_raw) {
-    constexpr int N = Tile<LOGN>::N, T = N / R, NS = StageCfg<LOGN>::NSTAGE;
+    constexpr int N = Tile<LOGN>::N, T = N / R, NS = StageCfg<LOGN, TEAMS>::NSTAGE;
     u64 *tw = (u64 *)smem_raw;
     const int team = tid / T, tau = tid % T, lane = tid & 31;
     u64 *acc = tw + N + (size_t)team * 3 * N;
@@ -744,7 +745,7 @@ TK_DEV void blind_rotate_body(const BRArgs &a, int tid, int bid, unsigned char *
     if (ct >= a.B) return;  // whole team leaves; only team barriers and the key-stream mbarriers are used from here on
 #if !defined(TFHE_EMU)
     if (ks.producer)
-        for (u32 t = 0; t < (u32)NS; t++) stream_issue<LOGN>(ks, t);
+        for (u32 t = 0; t < (u32)NS; t++) stream_issue<LOGN, NS>(ks, t);
 #endif
 
     const u64 *lwe = a.lwe + (size_t)ct * (a.n + 1);
@@ -771,7 +772,7 @@ TK_DEV void blind_rotate_body(const BRArgs &a, int tid, int bid, unsigned char *
         const bool cmux = i < a.steps;
         const u32 sh = cmux ? gl_mod_switch(mask, LOGN) : 0;
         if (i + 1 < a.steps) mask = lwe[i + 1];  // fetched one iteration ahead
-        team_external_product<LOGN, true, ELL, LOGB, R>(a, cmux ? a.bsk + i * ggsw_len : a.ksk, ks, cmux, sh, acc, xb, tw, tau, th, lane);
+        team_external_product<LOGN, true, ELL, LOGB, R, TEAMS>(a, cmux ? a.bsk + i * ggsw_len : a.ksk, ks, cmux, sh, acc, xb, tw, tau, th, lane);
     }
 
     // exit: sample extraction of coefficient 0      crypto/glwe.rs:96-113
