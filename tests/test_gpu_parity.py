@@ -380,7 +380,7 @@ def test_tile_widths_agree(which, rig_s1, rig_s2):
     ciphertexts-per-CTA count; first outputs equal the oracle's"""
     r = {"s1": rig_s1, "s2": rig_s2}[which]
     rng = O.Rng(57)
-    B = 301
+    B = 601      # above 3 * 148, so that S1 takes its four-per-CTA plan on its own; ragged against every team count
     cts = np.stack([rng.field(r.p.ct_len) for _ in range(B)])
     tvs = np.stack([rng.field(r.p.N) for _ in range(3)])
     idx = np.array([b % 3 for b in range(B)], dtype=np.uint32)
@@ -389,7 +389,7 @@ def test_tile_widths_agree(which, rig_s1, rig_s2):
         r.eng.split_mode(0)
         for regs in (8, 16, 4):
             r.eng.br_regs(regs)
-            for teams in (0, 1, 2, 3):
+            for teams in (0, 1, 2, 3, 4, 6):
                 r.eng.force_teams(teams)
                 outs[(regs, teams)] = r.eng.pbs_batch(cts, tvs, idx)
         r.eng.force_teams(0)

@@ -115,6 +115,20 @@ static int pick_teams(const lux_engine *e, size_t B, int max_teams) {
     return max_teams;
 }
 
+#if LUX_LOGN == 10
+// N = 1024, narrow tile: four ciphertexts per CTA (512 threads, 128 registers, no spills) take 47.0 ms per wave of
+// 4 * #SMs, six (768 threads, 80 registers, spills) 72.9 ms per wave of 6 * #SMs: 705.5 against 728.7 ms for 8,880
+// gate bootstraps.  Pick the cheaper wave plan; other gadgets keep 1 / 3 / 6.
+static int pick_teams_10(const lux_engine *e, size_t B, u32 ell, u32 logB) {
+    const int t = pick_teams(e, B, 6);
+    if (!narrow_named(e, ell, logB) || t <= 3) return t;
+    if (e->force_teams > 0) return e->force_teams == 4 ? 4 : t;
+    const size_t sm = (size_t)e->sm_count;
+    const size_t w4 = (B + 4 * sm - 1) / (4 * sm), w6 = (B + 6 * sm - 1) / (6 * sm);
+    return (w4 * 470 <= w6 * 729) ? 4 : 6;
+}
+#endif
+
 #if LUX_LOGN == 11
 // N = 2048, narrow tile: two ciphertexts per CTA (512 threads, 128 registers, no spills) take 23.65 ms per wave of
 // 2 * #SMs, three (768 threads, 80 registers, some spills) 36.05 ms per wave of 3 * #SMs (profiles/r01e_lockstep.txt):
@@ -312,9 +326,10 @@ int LUX_CAT(lux_launch_br_, LUX_LOGN)(lux_engine *e, const BRArgs &a, cudaStream
     if (t <= 4) return launch_br_t<9, 4>(e, a, s);
     return launch_br_t<9, 12>(e, a, s);
 #elif LUX_LOGN == 10
-    const int t = pick_teams(e, a.B, 6);
+    const int t = pick_teams_10(e, a.B, a.ell, a.logB);
     if (t <= 1) return launch_br_t<10, 1>(e, a, s);
     if (t <= 3) return launch_br_t<10, 3>(e, a, s);
+    if (t == 4) return launch_br_t<10, 4>(e, a, s);
     return launch_br_t<10, 6>(e, a, s);
 #elif LUX_LOGN == 11
     const int t = pick_teams_11(e, a.B, a.ell, a.logB);
@@ -338,8 +353,8 @@ size_t LUX_CAT(lux_br_wave_, LUX_LOGN)(const lux_engine *e, size_t B) {
     const int t = pick_teams(e, B, 12);
     return (size_t)e->sm_count * (t <= 1 ? 1 : t <= 4 ? 4 : 12);
 #elif LUX_LOGN == 10
-    const int t = pick_teams(e, B, 6);
-    return (size_t)e->sm_count * (t <= 1 ? 1 : t <= 3 ? 3 : 6);
+    const int t = pick_teams_10(e, B, e->p.ell, e->p.logB);
+    return (size_t)e->sm_count * (t <= 1 ? 1 : t <= 3 ? 3 : t == 4 ? 4 : 6);
 #elif LUX_LOGN == 11
     const int t = pick_teams_11(e, B, e->p.ell, e->p.logB);
     return (size_t)e->sm_count * (t <= 1 ? 1 : t <= 2 ? 2 : 3);
