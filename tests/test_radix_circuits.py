@@ -236,3 +236,18 @@ def test_div_exhaustive_small():
             (q,), _ = run_plain("div", 6, x, d)
             (r,), _ = run_plain("rem", 6, x, d)
             assert (q, r) == (x // d, x % d), (x, d)
+
+
+def test_shallow_rule_and_depths():
+    """the rule lux_eval* applies by itself (radix.cu pick_variant: batch x blocks <= 296) as mirrored by
+    runs_shallow, and what the shallow variants buy: depth log2(blocks) + 2 instead of `blocks`"""
+    assert R.runs_shallow(64, 9) and not R.runs_shallow(64, 10)      # 288 / 320 blocks
+    assert R.runs_shallow(8, 74) and not R.runs_shallow(8, 75)        # 296 / 300 blocks
+    for width in (16, 32, 64):
+        nb = R.blocks(width)
+        deep, shallow = R.program("add", width), R.program("add", width, shallow=True)
+        assert len(deep.levels) == nb
+        assert len(shallow.levels) == nb.bit_length() - 1 + 2
+        assert shallow.n_pbs > deep.n_pbs
+    assert len(R.program(R.PROG_ERC20, 64, shallow=True).levels) == 8
+    assert len(R.program(R.PROG_ERC20, 64).levels) == 33
