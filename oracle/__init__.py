@@ -23,7 +23,7 @@ ORDER_LWEKS_PBS = 1
 
 def build(force: bool = False) -> Path:
     """Compile oracle.c with the committed Makefile (gcc, no CUDA)."""
-    src_mtime = max((_HERE / f).stat().st_mtime for f in ("oracle.c", "oracle.h", "Makefile"))
+    src_mtime = max((_HERE / f).stat().st_mtime for f in ("oracle.c", "oracle.h", "torus.c", "torus.h", "Makefile"))
     if force or not _LIB_PATH.exists() or _LIB_PATH.stat().st_mtime < src_mtime:
         subprocess.run(["make", "-C", str(_HERE), "-B" if force else "-s"], check=True, capture_output=True)
     return _LIB_PATH
