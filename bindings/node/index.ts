@@ -23,12 +23,16 @@ declare const require: (id: string) => any;
 export interface LuxParams {
   n: number; N: number; k: number; ell: number; logB: number; ellKs: number; logBKs: number;
   /** 0 = PBS then GLWE key switch (in-tree order), 1 = LWE key switch then PBS (KS_PBS sets) */
-  order: 0 | 1;
+  order: 0 | 1 | 2;
+  /** 0 = in-tree Goldilocks exact NTT, 1 = 2^64 torus with f64 FFT (the arithmetic of the named tfhe-rs set; ell/logB are level/base_log) */
+  arith?: 0 | 1;
 }
 
 /** parameter sets of SURVEY.md Appendix B */
 export const S1_BOOLEAN: LuxParams = { n: 728, N: 1024, k: 1, ell: 4, logB: 5, ellKs: 4, logBKs: 5, order: 0 };
 export const S2_SHORTINT: LuxParams = { n: 918, N: 2048, k: 1, ell: 1, logB: 41, ellKs: 4, logBKs: 4, order: 1 };
+/** PARAM_MESSAGE_2_CARRY_2_KS_PBS_TUNIFORM_2M128 on its own arithmetic (sdk/relayer/src/tfhe.ts:13-28) */
+export const S2_TORUS: LuxParams = { n: 918, N: 2048, k: 1, ell: 1, logB: 23, ellKs: 4, logBKs: 4, order: 1, arith: 1 };
 
 /** op codes of include/lux_radix.h (`lux_op`); names follow client.ts:35 and the fhEVM operator list */
 export enum Op {

@@ -92,7 +92,7 @@ static napi_value Version(napi_env env, napi_callback_info info) { /* LuxFHE.ver
     return s;
 }
 
-/* createEngine({n, N, k, ell, logB, ellKs, logBKs, order}, device = 0) -> handle */
+/* createEngine({n, N, k, ell, logB, ellKs, logBKs, order, arith}, device = 0) -> handle */
 static napi_value CreateEngine(napi_env env, napi_callback_info info) {
     size_t argc = 2;
     napi_value argv[2];
@@ -107,6 +107,7 @@ static napi_value CreateEngine(napi_env env, napi_callback_info info) {
     p.ell_ks = u32_prop(env, argv[0], "ellKs", 0);
     p.logB_ks = u32_prop(env, argv[0], "logBKs", 0);
     p.order = u32_prop(env, argv[0], "order", LUX_ORDER_LWEKS_PBS);
+    p.arith = u32_prop(env, argv[0], "arith", LUX_ARITH_GOLDILOCKS_NTT);
     int32_t device = 0;
     if (argc > 1 && !is_nullish(env, argv[1])) napi_get_value_int32(env, argv[1], &device);
     lux_engine *e = NULL;

@@ -51,6 +51,19 @@ typedef enum {
 #define LUX_ORDER_LWEKS_PBS 1  /* "KS_PBS" (PARAM_MESSAGE_2_CARRY_2_KS_PBS_*, sdk/relayer/src/tfhe.ts:15):
                                   LWE key switch, mod-switch, blind rotate, full extract.  ct length k*N+1 */
 
+#define LUX_ORDER_PBS_LWEKS 2  /* classic gate-bootstrap order (torus arithmetic only): mod-switch, blind rotate, full extract,
+                                  LWE key switch.  ct length n+1 */
+
+/* arithmetic of the ciphertext modulus and of the polynomial products */
+#define LUX_ARITH_GOLDILOCKS_NTT 0 /* q = 2^64 - 2^32 + 1, exact NTT: the in-tree reference arithmetic
+                                      (research/verifiable-fhe/src/vtfhe/crypto/poly.rs:9-64); bit-exact vs the reference */
+#define LUX_ARITH_TORUS64_FFT 1    /* q = 2^64 (wrapping words), f64 negacyclic FFT: the arithmetic the reference's NAMED shortint
+                                      set is defined on (PARAM_MESSAGE_2_CARRY_2_KS_PBS_TUNIFORM_2M128, sdk/relayer/src/tfhe.ts:13-28,
+                                      from the out-of-tree tfhe-rs).  (ell, logB) and (ell_ks, logB_ks) are then tfhe-rs's
+                                      (level, base_log): the decomposition keeps the TOP ell*logB bits.  Supported: N = 2048, k = 1,
+                                      ell = 1, logB <= 31, logB_ks <= 7.  Results are bit-identical to oracle/torus.c (fixed rounding
+                                      order), decrypt-exact vs any other f64-FFT implementation */
+
 /* key domains accepted by lux_load_bsk / lux_load_glwe_ksk */
 #define LUX_DOMAIN_STANDARD 0 /* coefficient domain (Ggsw::encrypt output, crypto/ggsw.rs:26-36) */
 #define LUX_DOMAIN_NTT 1      /* the reference's NTT domain (compute_bsk output, crypto/mod.rs:41-44) */
@@ -64,6 +77,7 @@ typedef struct {
     uint32_t ell_ks;  /* LWE key switch levels (order 1); for order 0 the GLWE-KS reuses (ell, logB) */
     uint32_t logB_ks; /* log2 base of the LWE key switch (<= 24) */
     uint32_t order;   /* LUX_ORDER_* */
+    uint32_t arith;   /* LUX_ARITH_* (0 = the in-tree Goldilocks arithmetic) */
 } lux_params;
 
 typedef struct lux_engine lux_engine;
@@ -132,6 +146,9 @@ int lux_gate_not(const lux_engine *e, const uint64_t *a, size_t B, uint64_t *out
  * lut[i]*delta, pre-rotated by half a block (get_testv, crypto/mod.rs:17-27).  Host-side helper. */
 int lux_make_testv(uint32_t N, uint32_t p, uint64_t delta, const uint64_t *lut, uint64_t *out);
 uint64_t lux_delta(uint32_t plaintext_space);                    /* get_delta, crypto/lwe.rs:46-48 */
+/* the same two helpers for a given LUX_ARITH_* (torus: delta = 2^64 / space, wrapping products) */
+int lux_make_testv_arith(uint32_t arith, uint32_t N, uint32_t p, uint64_t delta, const uint64_t *lut, uint64_t *out);
+uint64_t lux_delta_arith(uint32_t arith, uint32_t plaintext_space);
 
 /* ---- the pieces, exposed for parity checks against the reference ------------------------------- */
 /* negacyclic NTT in the reference's convention (crypto/poly.rs:9-64): forward natural -> bit-reversed,
@@ -154,6 +171,16 @@ int lux_blind_rotate(lux_engine *e, const uint64_t *lwe, const uint64_t *testvs,
 /* GGSW (x) GLWE for `count` independent pairs (vtfhe/ggsw_ct.rs:98-112); ggsw in `domain` */
 int lux_external_product(lux_engine *e, const uint64_t *ggsw, int domain, const uint64_t *glwe_in, size_t count,
                          uint64_t *glwe_out);
+
+/* ---- pieces of the torus / f64-FFT arithmetic (LUX_ARITH_TORUS64_FFT engines only), for parity with oracle/torus.c --- */
+/* negacyclic transform of folded polynomials: in/out [n_polys][N/2] complex (re, im) pairs of doubles; forward takes
+ * z[j] = (p[j], p[j+N/2]) in natural order and returns the evaluations in the engine's (bit-reversed) order; inverse is
+ * unnormalised (the engine folds 1/(N/2) into the key) */
+int lux_fft(lux_engine *e, const double *in, size_t n_polys, int inverse, double *out);
+/* one-level SignedDecomposer digits (tfhe-rs decomposer.rs) of the top logB bits: out [count] signed */
+int lux_torus_decompose(lux_engine *e, const uint64_t *in, size_t count, int64_t *out);
+/* the resident Fourier-domain bootstrap key as the kernels read it: out [n][32][4][32] (re, im) pairs */
+int lux_export_bsk_fourier(lux_engine *e, double *out, size_t n_doubles);
 
 /* ---- radix integers (euintN) over the PBS: see lux_radix.h ------------------------------------ */
 

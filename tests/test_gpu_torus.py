@@ -1,0 +1,212 @@
+"""GPU parity tests of the 2^64-torus / f64-FFT arithmetic (lux_params.arith = LUX_ARITH_TORUS64_FFT): the CUDA path
+through the C ABI against oracle/torus.c on the same seeded inputs.  Every comparison is BIT-EXACT: the oracle fixes the
+order and rounding of every floating-point operation and the kernels reproduce it (fft64.cuh).  Against tfhe-rs itself
+parity is unpinned (oracle/torus.h); the decrypt-exact / noise-variance criterion is tested at the end.
+Run on the B200 box: pytest -m gpu."""
+import numpy as np
+import pytest
+
+import oracle as O
+import tfhe_b200 as T
+from oracle import torus as TO
+
+pytestmark = pytest.mark.gpu
+
+
+def oparams(p: T.Params) -> TO.Params:
+    return TO.Params(n=p.n, N=p.N, k=p.k, ell=p.ell, logB=p.logB, ell_ks=p.ell_ks, logB_ks=p.logB_ks, order=p.order)
+
+
+class Rig:
+    def __init__(self, params: T.Params, seed: int, glwe_noise=TO.S2_GLWE_NOISE, lwe_noise=TO.S2_LWE_NOISE):
+        self.p = params
+        self.ctx = TO.Ctx(oparams(params))
+        self.ks = TO.keygen(self.ctx, seed, glwe_noise, lwe_noise)
+        TO.install_keys(self.ctx, self.ks)
+        self.eng = T.Engine(params)
+        self.eng.load_keyset(self.ks)
+        self.glwe_noise = glwe_noise
+
+
+@pytest.fixture(scope="module")
+def rig_small():
+    return Rig(T.TEST_SMALL_TORUS, 21)
+
+
+@pytest.fixture(scope="module")
+def rig_small_o2():
+    return Rig(T.TEST_SMALL_TORUS_O2, 22)
+
+
+@pytest.fixture(scope="module")
+def rig_s2():
+    return Rig(T.S2_TORUS, 23)
+
+
+def u64_rand(rs, shape):
+    return rs.randint(0, 2**63, size=shape, dtype=np.int64).astype(np.uint64) * np.uint64(2) + rs.randint(0, 2, size=shape).astype(np.uint64)
+
+
+def bits(a):
+    return np.ascontiguousarray(a).view(np.uint64)
+
+
+# ------------------------------------------------------------------------------------------- FFT
+def test_fft_forward_inverse_bit_exact(rig_small):
+    e, N = rig_small.eng, rig_small.p.N
+    rs = np.random.RandomState(1)
+    z = np.empty((9, N // 2), np.complex128)
+    z[:4] = rs.randint(-2**22, 2**22, size=(4, N // 2)) + 1j * rs.randint(-2**22, 2**22, size=(4, N // 2))   # digit polynomials
+    z[4:8] = (rs.standard_normal((4, N // 2)) + 1j * rs.standard_normal((4, N // 2))) * 2.0**-12            # key-like
+    z[8] = 0
+    z[8, 0] = 1.0
+    tw = TO.twiddles(N)
+    fwd = e.fft(z)
+    want = np.stack([TO.fft_forward(N, row, tw) for row in z])
+    assert np.array_equal(bits(fwd), bits(want)), "forward transform differs from oracle/torus.c"
+    inv = e.fft(fwd, inverse=True)
+    want_inv = np.stack([TO.fft_inverse(N, row, tw) for row in want])
+    assert np.array_equal(bits(inv), bits(want_inv)), "inverse transform differs from oracle/torus.c"
+    # and it IS a transform pair: inverse(forward(z)) = (N/2) z up to rounding
+    assert np.abs(inv[:4] / (N // 2) - z[:4]).max() < 1e-6
+
+
+def test_fft_is_the_negacyclic_product(rig_small):
+    """pointwise product in the transform domain = product in Z[X]/(X^N+1) (the property the external product rests on)"""
+    e, N = rig_small.eng, rig_small.p.N
+    rs = np.random.RandomState(2)
+    a = rs.randint(-50, 50, N).astype(np.int64)
+    b = np.zeros(N, np.int64)
+    b[[0, 3, N - 1]] = [2, -1, 5]
+    fold = lambda p: (p[: N // 2] + 1j * p[N // 2:]).astype(np.complex128)
+    A, Bf = e.fft(fold(a))[0], e.fft(fold(b))[0]
+    c = e.fft(A * Bf, inverse=True)[0] / (N // 2)
+    c = np.rint(np.concatenate([c.real, c.imag])).astype(np.int64)
+    ref = np.zeros(N, np.int64)
+    for j in (0, 3, N - 1):
+        rot = np.concatenate([-a[N - j:], a[: N - j]]) if j else a.copy()
+        ref += b[j] * rot
+    assert np.array_equal(c, ref)
+
+
+def test_torus_decompose_vs_oracle(rig_small):
+    e, p = rig_small.eng, rig_small.p
+    rs = np.random.RandomState(3)
+    half = 1 << (63 - p.logB)   # rounding boundary of the closest representable
+    edge = [0, 1, 2**64 - 1, 2**63, 2**63 - 1, half, half - 1, half + 1, 2**64 - half, 2**64 - half - 1,
+            (1 << 63) + half, (1 << 63) - half, (1 << 63) + half - 1, 3 << 62, (1 << (64 - p.logB)) - 1]
+    vals = np.concatenate([np.array(edge, np.uint64), u64_rand(rs, 4000)])
+    got = e.torus_decompose(vals)
+    want = np.array([TO.decompose(int(v), p.logB, 1)[0] for v in vals], np.int64)
+    assert np.array_equal(got, want)
+    rec = (got.astype(np.uint64) << np.uint64(64 - p.logB))
+    assert all(int(r) == TO.closest_representable(int(v), p.logB, 1) for r, v in zip(rec, vals))
+
+
+def test_mod_switch_vs_oracle(rig_small):
+    e, p = rig_small.eng, rig_small.p
+    rs = np.random.RandomState(4)
+    vals = np.concatenate([np.array([0, 1, 2**64 - 1, 2**63, 2**52 - 1, 2**52, 2**51], np.uint64), u64_rand(rs, 2000)])
+    got = e.mod_switch(vals)
+    assert [int(g) for g in got] == [TO.mod_switch(int(v), p.N) for v in vals]
+
+
+# ------------------------------------------------------------------------------------------- keys
+def test_bsk_fourier_rows_bit_exact(rig_small):
+    """the resident key rows are the oracle's Fourier rows (scaled, sign folded) in the ring layout [row][poly][lane]"""
+    e, p = rig_small.eng, rig_small.p
+    got = e.bsk_fourier()                                                  # [n][32 i][4][32 lane]
+    want = rig_small.ctx.bsk_fourier().reshape(p.n, 4, 32, 32)             # [n][poly][lane r][i]: index 32 r + i
+    want = np.ascontiguousarray(want.transpose(0, 3, 1, 2))
+    assert np.array_equal(bits(got), bits(want))
+
+
+def test_lwe_keyswitch_vs_oracle(rig_small):
+    e, p = rig_small.eng, rig_small.p
+    rs = np.random.RandomState(5)
+    for B in (1, 3, 130):
+        cts = u64_rand(rs, (B, p.N + 1))
+        got = e.lwe_keyswitch(cts)
+        want = np.stack([rig_small.ctx.lwe_keyswitch(c) for c in cts])
+        assert np.array_equal(got, want), B
+
+
+# ------------------------------------------------------------------------------------------- blind rotation
+@pytest.mark.parametrize("steps", [0, 1, 2, 5, None])
+def test_blind_rotate_per_iteration_bit_exact(rig_small, steps):
+    e, p = rig_small.eng, rig_small.p
+    rs = np.random.RandomState(6)
+    B = 7
+    lwe = u64_rand(rs, (B, p.n + 1))
+    lwe[0, :] = 0                       # all shifts zero
+    lwe[1, :] = 2**64 - 1               # mod switch rounds up to 2N
+    dl = T.delta(32, p.arith)
+    tvs = np.stack([T.make_testv(p.N, 16, dl, [(3 * x + s) % 16 for x in range(16)], p.arith) for s in range(3)])
+    idx = np.array([0, 1, 2, 0, 1, 2, 0], np.uint32)
+    got = e.blind_rotate(lwe, tvs, idx, steps=steps)
+    want = np.stack([rig_small.ctx.blind_rotate(lwe[b], tvs[idx[b]], steps=steps) for b in range(B)])
+    assert np.array_equal(got, want), f"accumulators differ after {steps} CMUX steps"
+
+
+@pytest.mark.parametrize("teams", [1, 2, 3])
+def test_pbs_small_bit_exact_every_team_count(rig_small, teams):
+    """whole PBS (key switch, blind rotation, extraction) against the oracle, every ciphertext of a ragged batch,
+    for each ciphertexts-per-CTA configuration of the kernel (ring depth and stage size differ between them)"""
+    e, p, ks = rig_small.eng, rig_small.p, rig_small.ks
+    e.force_teams(teams)
+    try:
+        dl = T.delta(32, p.arith)
+        lut = [(x * x + 1) % 16 for x in range(16)]
+        tv = T.make_testv(p.N, 16, dl, lut, p.arith)
+        B = 2 * teams + 1
+        msgs = np.arange(B, dtype=np.uint64) % np.uint64(16)
+        cts = TO.lwe_encrypt_batch(7, ks.s_in, msgs * np.uint64(dl), rig_small.glwe_noise)
+        got = e.pbs_batch(cts, tv)
+        want, _ = rig_small.ctx.pbs_batch(cts, tv)
+        assert np.array_equal(got, want)
+        dec = [TO.decode(int(v), dl, 32) for v in TO.lwe_decrypt_batch(ks.s_in, got)]
+        assert dec == [lut[int(m)] for m in msgs]
+    finally:
+        e.force_teams(0)
+
+
+def test_pbs_order2_bit_exact(rig_small_o2):
+    """classic order: blind rotate first, key switch last; ciphertexts under the small key"""
+    r = rig_small_o2
+    e, p, ks = r.eng, r.p, r.ks
+    dl = T.delta(32, p.arith)
+    lut = [15 - x for x in range(16)]
+    tv = T.make_testv(p.N, 16, dl, lut, p.arith)
+    msgs = np.arange(9, dtype=np.uint64)
+    cts = TO.lwe_encrypt_batch(8, ks.s_in, msgs * np.uint64(dl), 30)
+    assert cts.shape[1] == p.n + 1
+    got = e.pbs_batch(cts, tv)
+    want, _ = r.ctx.pbs_batch(cts, tv)
+    assert np.array_equal(got, want)
+    dec = [TO.decode(int(v), dl, 32) for v in TO.lwe_decrypt_batch(ks.s_in, got)]
+    assert dec == [lut[int(m)] for m in msgs]
+
+
+# ------------------------------------------------------------------------------------------- the named set
+def test_pbs_s2_bit_exact_across_the_batch(rig_s2):
+    """PARAM_MESSAGE_2_CARRY_2_KS_PBS_TUNIFORM_2M128 with its own noise: a ragged multi-wave batch; 24 ciphertexts spread
+    over the whole batch (first and last CTA, last wave, ragged tail) meet the oracle bit for bit, all of them decrypt"""
+    e, p, ks = rig_s2.eng, rig_s2.p, rig_s2.ks
+    B = 3 * 148 * 2 + 3 * 40 + 2            # two full waves of 3 per CTA, a partial wave and a ragged last CTA
+    dl = T.delta(32, p.arith)
+    luts = [[x for x in range(16)], [(x * x) % 16 for x in range(16)], [x >> 2 for x in range(16)], [x & 3 for x in range(16)]]
+    tvs = np.stack([T.make_testv(p.N, 16, dl, l, p.arith) for l in luts])
+    rs = np.random.RandomState(9)
+    msgs = rs.randint(0, 16, B).astype(np.uint64)
+    idx = rs.randint(0, 4, B).astype(np.uint32)
+    cts = TO.lwe_encrypt_batch(10, ks.s_in, msgs * np.uint64(dl), TO.S2_GLWE_NOISE)
+    got = e.pbs_batch(cts, tvs, idx)
+    noisy = TO.lwe_decrypt_batch(ks.s_in, got)
+    dec = np.array([TO.decode(int(v), dl, 32) for v in noisy])
+    want_dec = np.array([luts[i][int(m)] for i, m in zip(idx, msgs)])
+    assert np.array_equal(dec, want_dec), f"{int((dec != want_dec).sum())} wrong decryptions"
+    pick = np.unique(np.concatenate([[0, 1, 2, 3, 443, 444, 887, 888, B - 3, B - 2, B - 1], rs.randint(0, B, 13)]))
+    want, _ = rig_s2.ctx.pbs_batch(cts[pick], tvs, idx[pick])
+    assert np.array_equal(got[pick], want), "ciphertext words differ from oracle/torus.c"
+    err = np.array([TO.centered_diff(int(v), (int(w) * dl) % 2**64) for v, w in zip(noisy, want_dec)])
+    assert err.std() < 2.0**-12, err.std()     # measured 2^-14.7; a failed transform would be ~2^-2

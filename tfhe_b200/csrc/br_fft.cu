@@ -1,0 +1,161 @@
+// br_fft.cu — kernels and launchers of the 2^64-torus / f64-FFT arithmetic (fft64.cuh).
+#include "engine.h"
+#include "fft64.cuh"
+
+#include <cmath>
+#include <vector>
+
+using namespace fft64;
+
+template <int TEAMS, int NS, int RS>
+__global__ void __launch_bounds__(Cfg<TEAMS, NS, RS>::THREADS, 1) blind_rotate_fft_kernel(const __grid_constant__ Args a) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    blind_rotate_body<TEAMS, NS, RS>(a, smem);
+}
+
+constexpr int UTIL_WARPS = 4;
+constexpr size_t UTIL_SMEM = sizeof(double2) * (TWB_ENTRIES + (size_t)UTIL_WARPS * BUF_POINTS);
+
+__global__ void __launch_bounds__(32 * UTIL_WARPS) fft_probe_kernel(const __grid_constant__ Args a, const double2 *in, double2 *out, u32 n_polys, int inverse) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    double2 *twB = (double2 *)smem;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int i = threadIdx.x; i < TWB_ENTRIES; i += blockDim.x) twB[i] = a.twB[i];
+    __syncthreads();
+    double2 *buf = twB + TWB_ENTRIES + (size_t)warp * BUF_POINTS;
+    for (u32 p = blockIdx.x * UTIL_WARPS + warp; p < n_polys; p += gridDim.x * UTIL_WARPS)
+        fft_probe_body(in + (size_t)p * M, out + (size_t)p * M, inverse, buf, twB, a, lane);
+}
+
+// src [n_ggsw][4 polys][N] torus words (ell = 1: poly = j * 2 + r) -> dst [n_ggsw][32][4][32] double2
+__global__ void __launch_bounds__(32 * UTIL_WARPS) key_to_fourier_kernel(const __grid_constant__ Args a, const u64 *src, double2 *dst, u32 n_polys, double scale) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    double2 *twB = (double2 *)smem;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int i = threadIdx.x; i < TWB_ENTRIES; i += blockDim.x) twB[i] = a.twB[i];
+    __syncthreads();
+    double2 *buf = twB + TWB_ENTRIES + (size_t)warp * BUF_POINTS;
+    for (u32 p = blockIdx.x * UTIL_WARPS + warp; p < n_polys; p += gridDim.x * UTIL_WARPS)
+        key_to_fourier_body(src + (size_t)p * N, dst + (size_t)(p / 4) * 4 * M, (int)(p % 4), scale, buf, twB, a, lane);
+}
+
+// torus digits / mod switch probes (parity with oracle/torus.c tor_decompose, tor_mod_switch)
+__global__ void torus_digit_kernel(const u64 *in, long long *out, size_t count, u32 logB) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < count; i += (size_t)gridDim.x * blockDim.x) out[i] = digit1(in[i], logB);
+}
+
+// ------------------------------------------------------------------------------------------ host side
+// merged-twist twiddle tree, exactly as oracle/torus.c tor_twiddles derives it (same expression, same libm)
+static void host_twiddles(std::vector<double2> &tw) {
+    tw.assign(M, make_double2(0.0, 0.0));
+    std::vector<u32> c(M, 0);
+    c[1] = N / 2;
+    for (u32 v = 1; v < (u32)M; v++) {
+        const u32 e = c[v] / 2;
+        if (v == 1 || (v & 1) == 0) {
+            const double ang = M_PI * (double)e / (double)N;
+            tw[v].x = cos(ang);
+            tw[v].y = sin(ang);
+        } else {
+            tw[v].x = -tw[v - 1].y;
+            tw[v].y = tw[v - 1].x;
+        }
+        if (2 * v < (u32)M) {
+            c[2 * v] = e;
+            c[2 * v + 1] = e + N;
+        }
+    }
+}
+
+int lux_fft_init(lux_engine *e) {
+    std::vector<double2> tw;
+    host_twiddles(tw);
+    for (int v = 0; v < 32; v++) e->fft_twA[2 * v] = tw[v].x, e->fft_twA[2 * v + 1] = tw[v].y;
+    std::vector<double2> twB(TWB_ENTRIES);
+    for (int lane = 0; lane < 32; lane++) twB[lane] = tw[32 + lane];
+    for (int g = 2; g <= 16; g <<= 1)
+        for (int ee = 0; ee < g / 2; ee++)
+            for (int lane = 0; lane < 32; lane++) twB[16 * g + ee * 32 + lane] = tw[32 * g + lane * g + 2 * ee];
+    if (cudaMalloc(&e->d_fft_twB, sizeof(double2) * TWB_ENTRIES) != cudaSuccess) return LUX_ERR_OOM;
+    if (cudaMemcpy(e->d_fft_twB, twB.data(), sizeof(double2) * TWB_ENTRIES, cudaMemcpyHostToDevice) != cudaSuccess) return LUX_ERR_CUDA;
+    return LUX_OK;
+}
+
+static void fill_tables(const lux_engine *e, Args &a) {
+    a.twB = (const double2 *)e->d_fft_twB;
+    for (int v = 0; v < 32; v++) a.twA[v] = make_double2(e->fft_twA[2 * v], e->fft_twA[2 * v + 1]);
+}
+
+template <int TEAMS, int NS, int RS>
+static int launch_cfg(lux_engine *e, const Args &a, cudaStream_t s) {
+    using C = Cfg<TEAMS, NS, RS>;
+    static bool configured[64] = {};
+    if (!configured[e->device & 63]) {
+        CUDA_TRY(e, cudaFuncSetAttribute(blind_rotate_fft_kernel<TEAMS, NS, RS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM));
+        configured[e->device & 63] = true;
+    }
+    const unsigned grid = (a.B + TEAMS - 1) / TEAMS;
+    blind_rotate_fft_kernel<TEAMS, NS, RS><<<grid, C::THREADS, C::SMEM, s>>>(a);
+    e->launches++;
+    CUDA_TRY(e, cudaGetLastError());
+    return LUX_OK;
+}
+
+// ciphertexts per CTA: 3 (ring of 2 x 8 KiB, teams in lock step at the key rows) or 2 (ring = one whole GGSW)
+static int pick_teams(const lux_engine *e, size_t B) {
+    if (e->force_teams >= 1 && e->force_teams <= 3) return e->force_teams;
+    const size_t sms = (size_t)e->sm_count;
+    if (B <= sms) return 1;
+    if (B <= 2 * sms) return 2;
+    return e->fft_default_teams;
+}
+
+size_t lux_fft_wave(const lux_engine *e, size_t B) { return (size_t)e->sm_count * pick_teams(e, B); }
+
+int lux_fft_launch_br(lux_engine *e, Args a, cudaStream_t s) {
+    fill_tables(e, a);
+    switch (pick_teams(e, a.B)) {
+        case 1: return launch_cfg<1, 4, 8>(e, a, s);
+        case 2: return launch_cfg<2, 4, 8>(e, a, s);
+        default: return launch_cfg<3, 2, 4>(e, a, s);
+    }
+}
+
+int lux_fft_key_convert(lux_engine *e, const u64 *d_src, void *d_dst, size_t n_polys, cudaStream_t s) {
+    Args a{};
+    fill_tables(e, a);
+    static bool configured[64] = {};
+    if (!configured[e->device & 63]) {
+        CUDA_TRY(e, cudaFuncSetAttribute(key_to_fourier_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)UTIL_SMEM));
+        CUDA_TRY(e, cudaFuncSetAttribute(fft_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)UTIL_SMEM));
+        configured[e->device & 63] = true;
+    }
+    const double scale = ldexp(1.0, -64 - (LOGN - 1));
+    const unsigned grid = (unsigned)std::min<size_t>((n_polys + UTIL_WARPS - 1) / UTIL_WARPS, (size_t)e->sm_count * 2);
+    key_to_fourier_kernel<<<grid, 32 * UTIL_WARPS, UTIL_SMEM, s>>>(a, d_src, (double2 *)d_dst, (u32)n_polys, scale);
+    e->launches++;
+    CUDA_TRY(e, cudaGetLastError());
+    return LUX_OK;
+}
+
+int lux_fft_probe(lux_engine *e, const void *d_in, void *d_out, size_t n_polys, int inverse, cudaStream_t s) {
+    Args a{};
+    fill_tables(e, a);
+    static bool configured[64] = {};
+    if (!configured[e->device & 63]) {
+        CUDA_TRY(e, cudaFuncSetAttribute(fft_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)UTIL_SMEM));
+        configured[e->device & 63] = true;
+    }
+    const unsigned grid = (unsigned)std::min<size_t>((n_polys + UTIL_WARPS - 1) / UTIL_WARPS, (size_t)e->sm_count * 2);
+    fft_probe_kernel<<<grid, 32 * UTIL_WARPS, UTIL_SMEM, s>>>(a, (const double2 *)d_in, (double2 *)d_out, (u32)n_polys, inverse);
+    e->launches++;
+    CUDA_TRY(e, cudaGetLastError());
+    return LUX_OK;
+}
+
+int lux_fft_digits(lux_engine *e, const u64 *d_in, long long *d_out, size_t count, u32 logB, cudaStream_t s) {
+    torus_digit_kernel<<<(unsigned)std::min<size_t>((count + 255) / 256, 4096), 256, 0, s>>>(d_in, d_out, count, logB);
+    e->launches++;
+    CUDA_TRY(e, cudaGetLastError());
+    return LUX_OK;
+}

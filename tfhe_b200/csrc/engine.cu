@@ -211,7 +211,7 @@ static int launch_ntt(lux_engine *e, const u64 *d_in, u64 *d_out, size_t n_polys
 // the int8 tensor-core form needs signed digits that fit a byte, exact int32 byte-plane sums and whole K tiles
 static bool ks_mma_eligible(const lux_params &p) {
     const uint64_t K = (uint64_t)p.k * p.N * p.ell_ks;
-    return p.order == LUX_ORDER_LWEKS_PBS && p.logB_ks >= 1 && p.logB_ks <= 7 && K % ksmma::BK == 0 &&
+    return p.order != LUX_ORDER_PBS_GLWEKS && p.logB_ks >= 1 && p.logB_ks <= 7 && K % ksmma::BK == 0 &&
            K * (1ull << (p.logB_ks - 1)) * 255ull < (1ull << 31);
 }
 
@@ -250,10 +250,10 @@ static int launch_ks_mma(lux_engine *e, const u64 *d_in, u64 *d_out, size_t B, c
         CUDA_TRY(e, cudaFuncSetAttribute(ksmma::lwe_keyswitch_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ksmma::SMEM_BYTES));
         configured[e->device & 63] = true;
     }
-    ksmma::ks_digits_kernel<<<e->sm_count * 8, 256, 0, s>>>(d_in, e->d_ks_dig, (u32)B, mpad, kN, p.ell_ks, p.logB_ks, e->L_ks);
+    ksmma::ks_digits_kernel<<<e->sm_count * 8, 256, 0, s>>>(d_in, e->d_ks_dig, (u32)B, mpad, kN, p.ell_ks, p.logB_ks, e->L_ks, lux_is_torus(e) ? 1u : 0u);
     e->launches++;
     CUDA_TRY(e, cudaGetLastError());
-    ksmma::Args a{e->d_ks_dig, e->d_kskT, d_in, d_out, (u32)B, p.n, kN, K};
+    ksmma::Args a{e->d_ks_dig, e->d_kskT, d_in, d_out, (u32)B, p.n, kN, K, lux_is_torus(e) ? 1u : 0u};
     dim3 grid(e->ks_npad / ksmma::BN, mpad / ksmma::BM);
     ksmma::lwe_keyswitch_mma_kernel<<<grid, ksmma::THREADS, ksmma::SMEM_BYTES, s>>>(a);
     e->launches++;
@@ -265,7 +265,8 @@ static int launch_ks(lux_engine *e, const u64 *d_in, u64 *d_out, size_t B, cudaS
     const lux_params &p = e->p;
     // the tensor-core form is faster at every batch size (profiles/r01e_ks_probe.txt: 0.07 ms against 0.17 ms for one
     // ciphertext, 0.075 against 4.2 ms for 148); the integer-pipe kernel below serves parameter sets it cannot take
-    if (e->d_kskT && e->ks_mode != 0) return launch_ks_mma(e, d_in, d_out, B, s);
+    if (e->d_kskT && (e->ks_mode != 0 || lux_is_torus(e))) return launch_ks_mma(e, d_in, d_out, B, s);
+    if (lux_is_torus(e)) LUX_FAIL(e, LUX_ERR_INVALID, "torus arithmetic: key switch needs the tensor-core form (logB_ks <= 7)");
     KSArgs a{p.n, p.k * p.N, p.ell_ks, p.logB_ks, e->L_ks, (u32)B, e->d_lksk, e->d_ksum, d_in, d_out, 1, nullptr};
     const size_t smem = sizeof(u32) * KS_RC * p.ell_ks * KS_TB;
     static bool configured[64] = {};
@@ -336,12 +337,59 @@ static BRArgs make_br_args(const lux_engine *e, const u64 *d_lwe, const u64 *d_t
 }
 
 
+static fft64::Args make_fft_args(const lux_engine *e, const u64 *d_lwe, const u64 *d_testv, const u32 *d_idx, u32 lut_div, size_t B, u64 *d_out) {
+    fft64::Args a{};
+    a.n = e->p.n;
+    a.steps = e->p.n;
+    a.logB = e->p.logB;
+    a.B = (u32)B;
+    a.out_mode = 0;
+    a.lut_div = lut_div ? lut_div : 1;
+    a.bsk = (const double2 *)e->d_bsk;
+    a.lwe = d_lwe;
+    a.testv = d_testv;
+    a.lut_idx = d_idx;
+    a.out = d_out;
+    return a;
+}
+
+// PBS of the torus / f64-FFT arithmetic: order 1 = key switch, blind rotate + extract; order 2 = blind rotate + extract, key switch
+static int torus_pbs_device(lux_engine *e, const u64 *d_in, const u64 *d_testvs, const u32 *d_idx, u32 lut_div, size_t B, u64 *d_out,
+                            cudaStream_t s, u64 body_add) {
+    if (!e->has_lksk) LUX_FAIL(e, LUX_ERR_NO_KEY, "LWE key switch key not loaded");
+    CUDA_TRY(e, cudaSetDevice(e->device));
+    const bool ks_first = e->p.order == LUX_ORDER_LWEKS_PBS;
+    const size_t big = (size_t)e->p.k * e->p.N + 1, small = (size_t)e->p.n + 1;
+    int rc = ensure_scratch(e, 0, sizeof(u64) * B * (ks_first ? small : big));
+    if (rc) return rc;
+    u64 *d_mid = (u64 *)e->scratch[0];
+    if (e->timing) CUDA_TRY(e, cudaEventRecord(e->ev[0], s));
+    if (ks_first && (rc = launch_ks(e, d_in, d_mid, B, s))) return rc;
+    if (e->timing) CUDA_TRY(e, cudaEventRecord(e->ev[1], s));
+    fft64::Args a = make_fft_args(e, ks_first ? d_mid : d_in, d_testvs, d_idx, lut_div, B, ks_first ? d_out : d_mid);
+    a.body_add = body_add;
+    if ((rc = lux_fft_launch_br(e, a, s))) return rc;
+    if (e->timing) CUDA_TRY(e, cudaEventRecord(e->ev[2], s));
+    if (!ks_first && (rc = launch_ks(e, d_mid, d_out, B, s))) return rc;
+    if (e->timing) {
+        CUDA_TRY(e, cudaEventRecord(e->ev[3], s));
+        CUDA_TRY(e, cudaEventSynchronize(e->ev[3]));
+        float ks_a = 0.f, ks_b = 0.f;
+        CUDA_TRY(e, cudaEventElapsedTime(&ks_a, e->ev[0], e->ev[1]));
+        CUDA_TRY(e, cudaEventElapsedTime(&e->last_ms[1], e->ev[1], e->ev[2]));
+        CUDA_TRY(e, cudaEventElapsedTime(&ks_b, e->ev[2], e->ev[3]));
+        e->last_ms[0] = ks_a + ks_b;
+    }
+    return LUX_OK;
+}
+
 int lux_pbs_device_grouped(lux_engine *e, const u64 *d_in, const u64 *d_testvs, const u32 *d_lut_idx, u32 lut_div, size_t B,
                            u64 *d_out, cudaStream_t s, u64 body_add) {
     if (B == 0) return LUX_OK;
     if (B > 0x7fffffffu) LUX_FAIL(e, LUX_ERR_INVALID, "batch too large");
     if (!e->has_bsk) LUX_FAIL(e, LUX_ERR_NO_KEY, "bootstrap key not loaded");
     const bool ks_first = e->p.order == LUX_ORDER_LWEKS_PBS;
+    if (lux_is_torus(e)) return torus_pbs_device(e, d_in, d_testvs, d_lut_idx, lut_div, B, d_out, s, body_add);
     if (ks_first && !e->has_lksk) LUX_FAIL(e, LUX_ERR_NO_KEY, "LWE key switch key not loaded");
     if (!ks_first && !e->has_gksk) LUX_FAIL(e, LUX_ERR_NO_KEY, "GLWE key switch key not loaded");
     CUDA_TRY(e, cudaSetDevice(e->device));
@@ -379,7 +427,7 @@ int lux_pbs_device_grouped(lux_engine *e, const u64 *d_in, const u64 *d_testvs, 
 // --------------------------------------------------------------------------------------------- ABI
 extern "C" {
 
-const char *lux_version(void) { return "tfhe_b200 0.1.0 (sm_100a, Goldilocks exact-NTT PBS)"; }
+const char *lux_version(void) { return "tfhe_b200 0.2.0 (sm_100a; Goldilocks exact-NTT and 2^64-torus f64-FFT PBS)"; }
 
 const char *lux_last_error(const lux_engine *e) { return e ? e->err : g_create_error; }
 
@@ -392,6 +440,16 @@ int lux_engine_create(const lux_params *p, int device, lux_engine **out) {
     if (!p || !out) CREATE_FAIL(LUX_ERR_INVALID, "null argument");
     *out = nullptr;
     if (p->k != 1) CREATE_FAIL(LUX_ERR_INVALID, "only k = 1 is supported (got %u)", p->k);
+    if (p->arith != LUX_ARITH_GOLDILOCKS_NTT && p->arith != LUX_ARITH_TORUS64_FFT) CREATE_FAIL(LUX_ERR_INVALID, "bad arith %u", p->arith);
+    const bool torus = p->arith == LUX_ARITH_TORUS64_FFT;
+    if (torus) {
+        if (p->N != 2048) CREATE_FAIL(LUX_ERR_INVALID, "torus arithmetic: N must be 2048 (got %u)", p->N);
+        if (p->ell != 1 || p->logB < 1 || p->logB > 31) CREATE_FAIL(LUX_ERR_INVALID, "torus arithmetic: ell = 1, logB <= 31 (got %u, %u)", p->ell, p->logB);
+        if (p->order != LUX_ORDER_LWEKS_PBS && p->order != LUX_ORDER_PBS_LWEKS) CREATE_FAIL(LUX_ERR_INVALID, "torus arithmetic: order must be LUX_ORDER_LWEKS_PBS or LUX_ORDER_PBS_LWEKS");
+        if (p->logB_ks < 1 || p->ell_ks < 1 || p->ell_ks * p->logB_ks > 64 || !ks_mma_eligible(*p))
+            CREATE_FAIL(LUX_ERR_INVALID, "torus arithmetic: unsupported key-switch gadget (ell_ks=%u, logB_ks=%u)", p->ell_ks, p->logB_ks);
+        if (p->n < 1) CREATE_FAIL(LUX_ERR_INVALID, "bad LWE dimension n=%u", p->n);
+    } else {
     if (p->N != 512 && p->N != 1024 && p->N != 2048 && p->N != 4096)
         CREATE_FAIL(LUX_ERR_INVALID, "N must be 512, 1024, 2048 or 4096 (got %u)", p->N);
     if (p->logB < 1 || p->logB > 62 || p->ell < 1 || p->ell > (64 + p->logB - 1) / p->logB)
@@ -403,6 +461,7 @@ int lux_engine_create(const lux_params *p, int device, lux_engine **out) {
         CREATE_FAIL(LUX_ERR_INVALID, "bad key-switch gadget (ell_ks=%u, logB_ks=%u)", p->ell_ks, p->logB_ks);
     if (p->n < 1 || (p->order == LUX_ORDER_PBS_GLWEKS && p->n > p->N))
         CREATE_FAIL(LUX_ERR_INVALID, "bad LWE dimension n=%u", p->n);
+    }
     int ndev = 0;
     cudaError_t st = cudaGetDeviceCount(&ndev);
     if (st != cudaSuccess || ndev == 0)
@@ -445,11 +504,12 @@ int lux_engine_create(const lux_params *p, int device, lux_engine **out) {
     // key blob: [header 8 words][bsk][glwe ksk][lwe ksk][ksum]
     e->bsk_words = (size_t)p->n * ggsw_words(*p);
     e->gksk_words = p->order == LUX_ORDER_PBS_GLWEKS ? ggsw_words(*p) : 0;
-    e->lksk_words = p->order == LUX_ORDER_LWEKS_PBS ? (size_t)p->k * p->N * p->ell_ks * (p->n + 1) : 0;
-    e->ksum_words = p->order == LUX_ORDER_LWEKS_PBS ? (size_t)p->n + 1 : 0;
+    e->lksk_words = p->order != LUX_ORDER_PBS_GLWEKS ? (size_t)p->k * p->N * p->ell_ks * (p->n + 1) : 0;
+    e->ksum_words = p->order != LUX_ORDER_PBS_GLWEKS ? (size_t)p->n + 1 : 0;
     e->blob_words = 8 + e->bsk_words + e->gksk_words + e->lksk_words + e->ksum_words;
     ok = ok && cudaMalloc(&e->d_blob, sizeof(u64) * e->blob_words) == cudaSuccess;
     for (int i = 0; i < 4 && ok; i++) ok = cudaEventCreate(&e->ev[i]) == cudaSuccess;
+    if (ok && torus) ok = lux_fft_init(e) == LUX_OK;
     if (!ok) {
         snprintf(g_create_error, sizeof(g_create_error), "device allocation failed: %s", cudaGetErrorString(cudaGetLastError()));
         lux_engine_destroy(e);
@@ -474,6 +534,7 @@ void lux_engine_destroy(lux_engine *e) {
     for (auto &kv : e->any_tables) cudaFree(kv.second);
     if (e->d_kskT) cudaFree(e->d_kskT);
     if (e->d_ks_dig) cudaFree(e->d_ks_dig);
+    if (e->d_fft_twB) cudaFree(e->d_fft_twB);
     if (e->d_tw_fwd) cudaFree(e->d_tw_fwd);
     if (e->d_blob) cudaFree(e->d_blob);
     for (int i = 0; i < 4; i++)
@@ -488,11 +549,12 @@ int lux_engine_params(const lux_engine *e, lux_params *out) {
     return LUX_OK;
 }
 size_t lux_ct_words(const lux_engine *e) {
-    return e->p.order == LUX_ORDER_LWEKS_PBS ? (size_t)e->p.k * e->p.N + 1 : (size_t)e->p.n + 1;
+    return e->p.order == LUX_ORDER_LWEKS_PBS ? (size_t)e->p.k * e->p.N + 1 : (size_t)e->p.n + 1;   // orders 0 and 2: small key
 }
 uint64_t lux_launch_count(const lux_engine *e) { return e ? e->launches : 0; }
 size_t lux_wave_ciphertexts(const lux_engine *e, size_t B) {
     if (!e) return 0;
+    if (lux_is_torus(e)) return lux_fft_wave(e, B);
     switch (e->logN) {
         case 9: return lux_br_wave_9(e, B);
         case 10: return lux_br_wave_10(e, B);
@@ -577,8 +639,31 @@ static int load_ggsw_array(lux_engine *e, u64 *d_dst, const u64 *src, size_t wor
     return LUX_OK;
 }
 
+// torus arithmetic: coefficient-domain key words -> Fourier rows in the ring layout (oracle/torus.c tor_ggsw_to_fourier)
+static int load_bsk_torus(lux_engine *e, const uint64_t *bsk, size_t n_words, int domain) {
+    if (!bsk) LUX_FAIL(e, LUX_ERR_INVALID, "lux_load_bsk: null pointer");
+    if (n_words != e->bsk_words) LUX_FAIL(e, LUX_ERR_INVALID, "lux_load_bsk: expected %zu words, got %zu", e->bsk_words, n_words);
+    if (domain != LUX_DOMAIN_STANDARD) LUX_FAIL(e, LUX_ERR_INVALID, "lux_load_bsk: the torus arithmetic takes coefficient-domain keys only");
+    CUDA_TRY(e, cudaSetDevice(e->device));
+    u64 *d_tmp = nullptr;
+    cudaError_t st = cudaMalloc(&d_tmp, sizeof(u64) * n_words);
+    if (st != cudaSuccess) LUX_FAIL(e, LUX_ERR_OOM, "cudaMalloc(%zu) for key upload: %s", sizeof(u64) * n_words, cudaGetErrorString(st));
+    int rc = LUX_OK;
+    if (cudaMemcpyAsync(d_tmp, bsk, sizeof(u64) * n_words, cudaMemcpyHostToDevice, e->stream) != cudaSuccess) rc = LUX_ERR_CUDA;
+    if (rc == LUX_OK) rc = lux_fft_key_convert(e, d_tmp, e->d_bsk, n_words / e->p.N, e->stream);
+    if (cudaStreamSynchronize(e->stream) != cudaSuccess && rc == LUX_OK) rc = LUX_ERR_CUDA;
+    cudaFree(d_tmp);
+    if (rc == LUX_ERR_CUDA) LUX_FAIL(e, LUX_ERR_CUDA, "key upload failed: %s", cudaGetErrorString(cudaGetLastError()));
+    return rc;
+}
+
 int lux_load_bsk(lux_engine *e, const uint64_t *bsk, size_t n_words, int domain) {
     if (!e) return LUX_ERR_INVALID;
+    if (lux_is_torus(e)) {
+        int rc = load_bsk_torus(e, bsk, n_words, domain);
+        if (rc == LUX_OK) e->has_bsk = true;
+        return rc;
+    }
     int rc = load_ggsw_array(e, e->d_bsk, bsk, n_words, e->bsk_words, domain, "lux_load_bsk");
     if (rc == LUX_OK) e->has_bsk = true;
     return rc;
@@ -592,14 +677,16 @@ int lux_load_glwe_ksk(lux_engine *e, const uint64_t *ksk, size_t n_words, int do
 }
 int lux_load_lwe_ksk(lux_engine *e, const uint64_t *ksk, size_t n_words) {
     if (!e) return LUX_ERR_INVALID;
-    if (e->p.order != LUX_ORDER_LWEKS_PBS) LUX_FAIL(e, LUX_ERR_INVALID, "LWE key switch key only applies to LUX_ORDER_LWEKS_PBS");
+    if (e->p.order == LUX_ORDER_PBS_GLWEKS) LUX_FAIL(e, LUX_ERR_INVALID, "LWE key switch key does not apply to LUX_ORDER_PBS_GLWEKS");
     if (!ksk) LUX_FAIL(e, LUX_ERR_INVALID, "lux_load_lwe_ksk: null pointer");
     if (n_words != e->lksk_words) LUX_FAIL(e, LUX_ERR_INVALID, "lux_load_lwe_ksk: expected %zu words, got %zu", e->lksk_words, n_words);
     CUDA_TRY(e, cudaSetDevice(e->device));
     CUDA_TRY(e, cudaMemcpyAsync(e->d_lksk, ksk, sizeof(u64) * n_words, cudaMemcpyHostToDevice, e->stream));
     const u32 cols = e->p.n + 1, rows = e->p.k * e->p.N * e->p.ell_ks;
-    ksk_colsum_kernel<<<(cols + 127) / 128, 128, 0, e->stream>>>(e->d_lksk, e->d_ksum, rows, cols);
-    e->launches++;
+    if (!lux_is_torus(e)) {
+        ksk_colsum_kernel<<<(cols + 127) / 128, 128, 0, e->stream>>>(e->d_lksk, e->d_ksum, rows, cols);
+        e->launches++;
+    }
     CUDA_TRY(e, cudaGetLastError());
     int rc = derive_ksk_bytes(e);
     if (rc) return rc;
@@ -614,7 +701,7 @@ int lux_export_keys_device(lux_engine *e, void *dev_blob, size_t bytes) {
     if (!e || !dev_blob) return LUX_ERR_INVALID;
     if (bytes != sizeof(u64) * e->blob_words) LUX_FAIL(e, LUX_ERR_INVALID, "key blob is %zu bytes, got %zu", sizeof(u64) * e->blob_words, bytes);
     CUDA_TRY(e, cudaSetDevice(e->device));
-    u64 hdr[8] = {0x4c55584b45593031ULL, e->has_bsk, e->has_gksk, e->has_lksk, e->blob_words, 0, 0, 0};
+    u64 hdr[8] = {0x4c55584b45593031ULL, e->has_bsk, e->has_gksk, e->has_lksk, e->blob_words, e->p.arith, 0, 0};
     CUDA_TRY(e, cudaMemcpyAsync(e->d_blob, hdr, sizeof(hdr), cudaMemcpyHostToDevice, e->stream));
     CUDA_TRY(e, cudaMemcpyAsync(dev_blob, e->d_blob, bytes, cudaMemcpyDeviceToDevice, e->stream));
     CUDA_TRY(e, cudaStreamSynchronize(e->stream));
@@ -626,7 +713,7 @@ int lux_import_keys_device(lux_engine *e, const void *dev_blob, size_t bytes) {
     CUDA_TRY(e, cudaSetDevice(e->device));
     u64 hdr[8];
     CUDA_TRY(e, cudaMemcpy(hdr, dev_blob, sizeof(hdr), cudaMemcpyDeviceToHost));
-    if (hdr[0] != 0x4c55584b45593031ULL || hdr[4] != e->blob_words) LUX_FAIL(e, LUX_ERR_INVALID, "key blob header mismatch");
+    if (hdr[0] != 0x4c55584b45593031ULL || hdr[4] != e->blob_words || hdr[5] != e->p.arith) LUX_FAIL(e, LUX_ERR_INVALID, "key blob header mismatch");
     CUDA_TRY(e, cudaMemcpyAsync(e->d_blob, dev_blob, bytes, cudaMemcpyDeviceToDevice, e->stream));
     if (hdr[3] != 0) {
         int rc = derive_ksk_bytes(e);
@@ -752,6 +839,21 @@ int lux_make_testv(uint32_t N, uint32_t p, uint64_t delta, const uint64_t *lut, 
     return LUX_OK;
 }
 uint64_t lux_delta(uint32_t plaintext_space) { return GL_Q >> ilog2u(plaintext_space); }
+uint64_t lux_delta_arith(uint32_t arith, uint32_t plaintext_space) {
+    if (arith != LUX_ARITH_TORUS64_FFT) return lux_delta(plaintext_space);
+    const u32 l = ilog2u(plaintext_space);
+    return l == 0 ? 0 : 1ull << (64 - l);
+}
+int lux_make_testv_arith(uint32_t arith, uint32_t N, uint32_t p, uint64_t delta, const uint64_t *lut, uint64_t *out) {
+    if (arith != LUX_ARITH_TORUS64_FFT) return lux_make_testv(N, p, delta, lut, out);
+    if (!lut || !out || p == 0 || N == 0 || N % p) return LUX_ERR_INVALID;
+    const u32 bs = N / p, sh = bs / 2;
+    for (u32 i = 0; i < N; i++) {
+        const u32 src = i + sh;
+        out[i] = src < N ? lut[src / bs] * delta : (u64)0 - lut[(src - N) / bs] * delta;
+    }
+    return LUX_OK;
+}
 
 // ---- pieces
 static int ntt_host(lux_engine *e, const u64 *in, size_t n_polys, u64 *out, bool inverse) {
@@ -843,7 +945,7 @@ int lux_mod_switch(lux_engine *e, const uint64_t *in, size_t count, uint32_t *ou
 int lux_lwe_keyswitch(lux_engine *e, const uint64_t *in, size_t B, uint64_t *out) {
     if (!e) return LUX_ERR_INVALID;
     if (!in || !out) LUX_FAIL(e, LUX_ERR_INVALID, "null pointer");
-    if (e->p.order != LUX_ORDER_LWEKS_PBS) LUX_FAIL(e, LUX_ERR_INVALID, "engine has no LWE key switch (order 0)");
+    if (e->p.order == LUX_ORDER_PBS_GLWEKS) LUX_FAIL(e, LUX_ERR_INVALID, "engine has no LWE key switch (order 0)");
     if (!e->has_lksk) LUX_FAIL(e, LUX_ERR_NO_KEY, "LWE key switch key not loaded");
     if (B == 0) return LUX_OK;
     CUDA_TRY(e, cudaSetDevice(e->device));
@@ -879,17 +981,68 @@ int lux_blind_rotate(lux_engine *e, const uint64_t *lwe, const uint64_t *testvs,
     CUDA_TRY(e, cudaMemcpyAsync(e->scratch[1], lwe, sizeof(u64) * B * wi, cudaMemcpyHostToDevice, e->stream));
     CUDA_TRY(e, cudaMemcpyAsync(d_tv, testvs, sizeof(u64) * n_luts * N, cudaMemcpyHostToDevice, e->stream));
     if (lut_idx) CUDA_TRY(e, cudaMemcpyAsync(d_idx, lut_idx, sizeof(u32) * B, cudaMemcpyHostToDevice, e->stream));
+    if (lux_is_torus(e)) {
+        fft64::Args fa = make_fft_args(e, (const u64 *)e->scratch[1], d_tv, d_idx, 1, B, (u64 *)e->scratch[2]);
+        fa.steps = steps;
+        fa.out_mode = 2;
+        if ((rc = lux_fft_launch_br(e, fa, e->stream))) return rc;
+    } else {
     BRArgs a = make_br_args(e, (const u64 *)e->scratch[1], d_tv, d_idx, B, (u64 *)e->scratch[2]);
     a.steps = steps;
     a.out_mode = 2;
     if ((rc = launch_br(e, a, e->stream))) return rc;
+    }
     CUDA_TRY(e, cudaMemcpyAsync(acc_out, e->scratch[2], sizeof(u64) * B * wo, cudaMemcpyDeviceToHost, e->stream));
     CUDA_TRY(e, cudaStreamSynchronize(e->stream));
     return LUX_OK;
 }
 
+int lux_fft(lux_engine *e, const double *in, size_t n_polys, int inverse, double *out) {
+    if (!e) return LUX_ERR_INVALID;
+    if (!lux_is_torus(e)) LUX_FAIL(e, LUX_ERR_INVALID, "lux_fft: engine is not LUX_ARITH_TORUS64_FFT");
+    if (!in || !out) LUX_FAIL(e, LUX_ERR_INVALID, "null pointer");
+    if (n_polys == 0) return LUX_OK;
+    CUDA_TRY(e, cudaSetDevice(e->device));
+    const size_t bytes = sizeof(double) * n_polys * e->p.N;   // N/2 complex points
+    int rc;
+    if ((rc = ensure_scratch(e, 1, bytes))) return rc;
+    if ((rc = ensure_scratch(e, 2, bytes))) return rc;
+    CUDA_TRY(e, cudaMemcpyAsync(e->scratch[1], in, bytes, cudaMemcpyHostToDevice, e->stream));
+    if ((rc = lux_fft_probe(e, e->scratch[1], e->scratch[2], n_polys, inverse, e->stream))) return rc;
+    CUDA_TRY(e, cudaMemcpyAsync(out, e->scratch[2], bytes, cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    return LUX_OK;
+}
+
+int lux_torus_decompose(lux_engine *e, const uint64_t *in, size_t count, int64_t *out) {
+    if (!e) return LUX_ERR_INVALID;
+    if (!lux_is_torus(e)) LUX_FAIL(e, LUX_ERR_INVALID, "lux_torus_decompose: engine is not LUX_ARITH_TORUS64_FFT");
+    if (!in || !out) LUX_FAIL(e, LUX_ERR_INVALID, "null pointer");
+    if (count == 0) return LUX_OK;
+    CUDA_TRY(e, cudaSetDevice(e->device));
+    int rc;
+    if ((rc = ensure_scratch(e, 1, sizeof(u64) * count))) return rc;
+    if ((rc = ensure_scratch(e, 2, sizeof(u64) * count))) return rc;
+    CUDA_TRY(e, cudaMemcpyAsync(e->scratch[1], in, sizeof(u64) * count, cudaMemcpyHostToDevice, e->stream));
+    if ((rc = lux_fft_digits(e, (const u64 *)e->scratch[1], (long long *)e->scratch[2], count, e->p.logB, e->stream))) return rc;
+    CUDA_TRY(e, cudaMemcpyAsync(out, e->scratch[2], sizeof(u64) * count, cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    return LUX_OK;
+}
+
+int lux_export_bsk_fourier(lux_engine *e, double *out, size_t n_doubles) {
+    if (!e) return LUX_ERR_INVALID;
+    if (!lux_is_torus(e)) LUX_FAIL(e, LUX_ERR_INVALID, "lux_export_bsk_fourier: engine is not LUX_ARITH_TORUS64_FFT");
+    if (!e->has_bsk) LUX_FAIL(e, LUX_ERR_NO_KEY, "bootstrap key not loaded");
+    if (!out || n_doubles != e->bsk_words) LUX_FAIL(e, LUX_ERR_INVALID, "lux_export_bsk_fourier: expected %zu doubles", e->bsk_words);
+    CUDA_TRY(e, cudaSetDevice(e->device));
+    CUDA_TRY(e, cudaMemcpy(out, e->d_bsk, sizeof(double) * n_doubles, cudaMemcpyDeviceToHost));
+    return LUX_OK;
+}
+
 int lux_external_product(lux_engine *e, const uint64_t *ggsw, int domain, const uint64_t *glwe_in, size_t count, uint64_t *glwe_out) {
     if (!e) return LUX_ERR_INVALID;
+    if (lux_is_torus(e)) LUX_FAIL(e, LUX_ERR_INVALID, "lux_external_product: not available for the torus arithmetic (use lux_blind_rotate with steps)");
     if (!ggsw || !glwe_in || !glwe_out) LUX_FAIL(e, LUX_ERR_INVALID, "null pointer");
     if (count == 0) return LUX_OK;
     CUDA_TRY(e, cudaSetDevice(e->device));

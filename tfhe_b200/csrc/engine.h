@@ -9,6 +9,7 @@
 
 #include "../../include/lux_tfhe.h"
 #include "tfhe_kernels.cuh"
+#include "fft64.cuh"
 
 #define LUX_SCRATCH_SLOTS 8
 
@@ -49,6 +50,11 @@ struct lux_engine {
     bool generic_gadget = false;  // tests: run the runtime-gadget kernel even where a compile-time instantiation exists
     int split_mode = -1;  // latency-mode blind rotate: -1 = automatic (2B <= #SMs: cluster kernel, B <= #SMs: split kernel), 0 = never,
                           // 1 = split kernel always, 2 = cluster kernel always (tests)
+    // torus / f64-FFT arithmetic (fft64.cuh): twiddle tree nodes 0..31 as (re, im) pairs for the kernel-parameter bank,
+    // pass-B table in device memory
+    double fft_twA[64] = {};
+    void *d_fft_twB = nullptr;
+    int fft_default_teams = 3;
     struct RadixState *radix = nullptr;  // euintN layer (radix.cu), created on first use
     char err[512] = "";
 };
@@ -68,6 +74,15 @@ extern "C" int lux_debug_cluster_regs(lux_engine *e, int regs);
 extern "C" int lux_debug_br_regs(lux_engine *e, int regs);
 extern "C" int lux_debug_int_peak(lux_engine *e, double out[3]);
 extern "C" int lux_debug_field_probe(lux_engine *e, const uint64_t *a, const uint64_t *b, size_t count, uint64_t *out);
+
+// br_fft.cu
+int lux_fft_init(lux_engine *e);
+int lux_fft_launch_br(lux_engine *e, fft64::Args a, cudaStream_t s);
+size_t lux_fft_wave(const lux_engine *e, size_t B);
+int lux_fft_key_convert(lux_engine *e, const u64 *d_src, void *d_dst, size_t n_polys, cudaStream_t s);
+int lux_fft_probe(lux_engine *e, const void *d_in, void *d_out, size_t n_polys, int inverse, cudaStream_t s);
+int lux_fft_digits(lux_engine *e, const u64 *d_in, long long *d_out, size_t count, u32 logB, cudaStream_t s);
+inline bool lux_is_torus(const lux_engine *e) { return e->p.arith == LUX_ARITH_TORUS64_FFT; }
 
 #define LUX_FAIL(e, code, ...)                                  \
     do {                                                        \

@@ -1,0 +1,380 @@
+// fft64.cuh — the blind rotation on the 2^64 torus with a double-precision negacyclic FFT (sm_100a).
+//
+// This is the second arithmetic of the engine (lux_params.arith = LUX_ARITH_TORUS64_FFT): the one the reference's
+// named shortint set PARAM_MESSAGE_2_CARRY_2_KS_PBS_TUNIFORM_2M128 (sdk/relayer/src/tfhe.ts:13-28) is defined on.
+// The algorithm — SignedDecomposer digits, N/2-point complex transform with the negacyclic twist merged into the
+// twiddles, external product, CMUX loop — and every rounding it performs are specified by oracle/torus.c, which
+// this file reproduces word for word: each floating-point operation below is an explicit round-to-nearest
+// intrinsic (__fma_rn, __dadd_rn, __dmul_rn) in the oracle's order, so nothing is contracted or re-associated.
+//
+// Why FP64 (profiles/r02_arith_ubench.txt, measured on B200): the FP64 pipe issues 64 lanes/SM/clk, a complex
+// radix-2 butterfly is 6 DFMA -> 3.07 T butterflies/s against 0.545 T/s for the 64-bit Goldilocks butterfly and
+// 4.05 T/s for a 31-bit Harvey butterfly (which needs twice the transforms and 2.2x the butterflies per transform).
+//
+// Work split ("warp per polynomial").  N = 2048 -> M = 1024 complex points = 32 x 32.  ONE WARP owns one polynomial
+// of a ciphertext and keeps the whole transform in registers, 32 points per lane:
+//   column layout  x[i] = z[lane + 32 i]      pass A: the 5 stages with strides 512..32 pair registers; the twiddle
+//                                             of a butterfly depends on i only -> uniform over the warp, read from
+//                                             the kernel-parameter constant bank
+//   row layout     y[i] = z[32 lane + i]      pass B: strides 16..1; twiddles per lane, from a shared-memory table
+//                                             that holds EVEN tree nodes only (tw[2v+1] = i tw[2v], exact)
+// with ONE transpose through shared memory between the passes (padded rows: 33 x 16 B, conflict-free both ways).
+// A transform therefore crosses shared memory once instead of once per 3-4 stages: shared-memory bandwidth
+// (128 B/clk/SM), not the FP64 pipe, is what a 16-byte-per-point transform runs out of first.
+// A team = 2 warps = one ciphertext (k = 1): warp r decomposes and transforms input polynomial r, the two warps
+// swap their spectra through shared memory, and warp r accumulates, inverse-transforms and updates OUTPUT
+// polynomial r.  Warp r only ever touches accumulator polynomial r, so the CMUX needs two 64-thread barriers (around
+// the swap) and no other cross-warp synchronisation.
+// The bootstrap key streams through a ring of shared-memory stages filled by a dedicated producer warp with
+// cp.async.bulk (TMA) + mbarriers and is shared by the TEAMS ciphertexts of the CTA.
+#pragma once
+#include "tfhe_kernels.cuh"
+
+namespace fft64 {
+
+constexpr double MAGIC = 6755399441055744.0;   // 1.5 * 2^52
+constexpr double TWO51 = 2251799813685248.0;   // 2^51
+constexpr int LOGN = 11, N = 1 << LOGN, M = N / 2;   // ring degree of the named set
+constexpr int ROWP = 33;                       // padded row length of the transpose buffer (in points)
+constexpr int BUF_POINTS = 32 * ROWP;          // one warp's transpose / swap buffer
+constexpr int TWB_ENTRIES = 512;               // pass-B table: 32 (m = 32) + 32 + 64 + 128 + 256 even nodes
+
+struct Args {
+    u32 n, steps, logB, B, out_mode, lut_div;
+    const double2 *bsk;     // [n][32 rows i][4 polys (j, r)][32 lanes], Fourier domain, scaled, sign folded
+    const u64 *lwe;         // [B][n+1] under the small key
+    const u64 *testv;       // [n_luts][N]
+    const u32 *lut_idx;     // [ceil(B / lut_div)] or nullptr
+    u64 *out;               // out_mode 0: [B][N+1] sample extract; 2: [B][2N] raw accumulator
+    const double2 *twB;     // [TWB_ENTRIES] pass-B table (global; copied to shared memory)
+    u64 body_add;
+    double2 twA[32];        // tree nodes 1..31: the warp-uniform twiddles of pass A
+};
+
+// ------------------------------------------------------------------------------------------ scalars
+// oracle/torus.c tor_from_double
+__device__ __forceinline__ u64 from_double(double y) {
+    const double t = __dadd_rn(y, MAGIC);
+    const double r = __dsub_rn(t, MAGIC);
+    const double f = __dsub_rn(y, r);
+    const double h = __fma_rn(f, TWO51, MAGIC);
+    const long long v = __double_as_longlong(h) - 0x4338000000000000LL;
+    return (u64)v << 13;
+}
+// exact int32 -> double without the conversion pipe: 2^52 + 2^31 + d sits in the mantissa
+__device__ __forceinline__ double int_to_double(int d) {
+    return __dsub_rn(__hiloint2double(0x43300000, d ^ 0x80000000), 4503601774854144.0);
+}
+// oracle/torus.c tor_decompose for ONE level of logB <= 31 bits: only the high word of x matters
+__device__ __forceinline__ int digit1(u64 x, u32 logB) {
+    const u32 hi = (u32)(x >> 32);
+    const u32 res = (((hi >> (31 - logB)) + 1u) >> 1) & ((1u << logB) - 1u);
+    const u32 carry = ((res - 1u) & res) >> (logB - 1);
+    return (int)res - (int)(carry << logB);
+}
+// round(x 2N / 2^64) in [0, 2N]      crypto/lwe.rs:28-34
+__device__ __forceinline__ u32 mod_switch(u64 x) {
+    const u64 a = x >> (64 - LOGN - 2);
+    return (u32)((a >> 1) + (a & 1));
+}
+// coefficient p of X^sh * poly, wrapping negation
+__device__ __forceinline__ u64 rotated(const u64 *poly, u32 p, u32 sh) {
+    const u32 i2 = (p - sh) & (2 * N - 1);
+    const u64 v = poly[i2 & (N - 1)];
+    return (i2 & N) ? (u64)0 - v : v;
+}
+
+// ------------------------------------------------------------------------------------------ butterflies
+__device__ __forceinline__ void ct_bfly(double2 &u, double2 &v, double wr, double wi) {
+    const double tr = __fma_rn(-wi, v.y, u.x);
+    const double nr = __fma_rn(wr, v.x, tr);
+    const double ti = __fma_rn(wi, v.x, u.y);
+    const double ni = __fma_rn(wr, v.y, ti);
+    v.x = __fma_rn(2.0, u.x, -nr);
+    v.y = __fma_rn(2.0, u.y, -ni);
+    u.x = nr;
+    u.y = ni;
+}
+__device__ __forceinline__ void gs_bfly(double2 &u, double2 &v, double wr, double wi) {
+    const double sr = __dadd_rn(u.x, v.x), si = __dadd_rn(u.y, v.y);
+    const double dr = __dsub_rn(u.x, v.x), di = __dsub_rn(u.y, v.y);
+    const double m0 = __dmul_rn(di, wi), m1 = __dmul_rn(dr, wi);
+    u.x = sr;
+    u.y = si;
+    v.x = __fma_rn(dr, wr, m0);
+    v.y = __fma_rn(di, wr, -m1);
+}
+template <bool INV>
+__device__ __forceinline__ void bfly(double2 &u, double2 &v, double wr, double wi) {
+    if (INV)
+        gs_bfly(u, v, wr, wi);
+    else
+        ct_bfly(u, v, wr, wi);
+}
+
+// pass A: tree levels m = 1..16 on the column layout; node m + blk pairs registers blk*2t + jj and + t, t = 16/m
+template <bool INV>
+__device__ __forceinline__ void pass_a(double2 (&x)[32], const Args &a) {
+#pragma unroll
+    for (int s0 = 0; s0 < 5; s0++) {
+        const int s = INV ? 4 - s0 : s0;
+        const int m = 1 << s, t = 16 >> s;
+#pragma unroll
+        for (int blk = 0; blk < m; blk++) {
+            const int node = m + blk;
+            double wr, wi;
+            if (node > 1 && (node & 1)) {   // tw[2v+1] = i * tw[2v]
+                wr = -a.twA[node - 1].y;
+                wi = a.twA[node - 1].x;
+            } else {
+                wr = a.twA[node].x;
+                wi = a.twA[node].y;
+            }
+#pragma unroll
+            for (int jj = 0; jj < t; jj++) bfly<INV>(x[blk * 2 * t + jj], x[blk * 2 * t + jj + t], wr, wi);
+        }
+    }
+}
+// pass B: tree levels m = 32 g, g = 1..16, on the row layout; lane r owns nodes m + r g + b, b < g
+template <bool INV>
+__device__ __forceinline__ void pass_b(double2 (&y)[32], const double2 *twB, int lane) {
+#pragma unroll
+    for (int gi0 = 0; gi0 < 5; gi0++) {
+        const int gi = INV ? 4 - gi0 : gi0;
+        const int g = 1 << gi, t = 16 >> gi;
+        if (g == 1) {
+            const double2 w = twB[lane];
+#pragma unroll
+            for (int jj = 0; jj < 16; jj++) bfly<INV>(y[jj], y[jj + 16], w.x, w.y);
+        } else {
+#pragma unroll
+            for (int e = 0; e < g / 2; e++) {
+                const double2 w = twB[16 * g + e * 32 + lane];
+#pragma unroll
+                for (int jj = 0; jj < t; jj++) bfly<INV>(y[(2 * e) * 2 * t + jj], y[(2 * e) * 2 * t + jj + t], w.x, w.y);
+#pragma unroll
+                for (int jj = 0; jj < t; jj++) bfly<INV>(y[(2 * e + 1) * 2 * t + jj], y[(2 * e + 1) * 2 * t + jj + t], -w.y, w.x);
+            }
+        }
+    }
+}
+// transposes through the warp's padded buffer
+__device__ __forceinline__ void col_to_row(double2 (&x)[32], double2 *buf, int lane) {
+#pragma unroll
+    for (int i = 0; i < 32; i++) buf[i * ROWP + lane] = x[i];
+    __syncwarp();
+#pragma unroll
+    for (int i = 0; i < 32; i++) x[i] = buf[lane * ROWP + i];
+}
+__device__ __forceinline__ void row_to_col(double2 (&y)[32], double2 *buf, int lane) {
+#pragma unroll
+    for (int i = 0; i < 32; i++) buf[lane * ROWP + i] = y[i];
+    __syncwarp();
+#pragma unroll
+    for (int i = 0; i < 32; i++) y[i] = buf[i * ROWP + lane];
+}
+// forward: column layout in (z[lane + 32 i]), row layout out (Z[32 lane + i], oracle index order)
+__device__ __forceinline__ void fft_forward(double2 (&x)[32], double2 *buf, const double2 *twB, const Args &a, int lane) {
+    pass_a<false>(x, a);
+    col_to_row(x, buf, lane);
+    pass_b<false>(x, twB, lane);
+}
+// inverse (unnormalised): row layout in, column layout out
+__device__ __forceinline__ void fft_inverse(double2 (&y)[32], double2 *buf, const double2 *twB, const Args &a, int lane) {
+    pass_b<true>(y, twB, lane);
+    row_to_col(y, buf, lane);
+    pass_a<true>(y, a);
+}
+
+// ------------------------------------------------------------------------------------------ blind rotation
+// ring stage = RS rows of the GGSW: [RS][4 polys][32 lanes] double2 = RS * 2 KiB
+template <int TEAMS, int NS, int RS>
+struct Cfg {
+    static constexpr int CONSUMER_WARPS = 2 * TEAMS;
+    static constexpr int THREADS = 32 * (CONSUMER_WARPS + 1);
+    static constexpr int STAGE_POINTS = RS * 4 * 32;
+    static constexpr int STAGES_PER_GGSW = 32 / RS;
+    static constexpr size_t SMEM =
+        sizeof(double2) * TWB_ENTRIES + (size_t)TEAMS * (sizeof(u64) * 2 * N + sizeof(double2) * 2 * BUF_POINTS) +
+        sizeof(double2) * (size_t)NS * STAGE_POINTS + sizeof(u64) * 2 * NS + 16;
+};
+
+// multiply-accumulate of the swapped spectra with the staged key rows: out = X0 K[0][r] + X1 K[1][r], in the oracle's order
+template <int R, int RS>
+__device__ __forceinline__ void mac_rows(double2 (&y)[32], const double2 *oth, const double2 *stage, int row0, int lane) {
+#pragma unroll
+    for (int ii = 0; ii < RS; ii++) {
+        const int i = row0 + ii;   // compile-time after unrolling of the caller
+        const double2 k0 = stage[(ii * 4 + 0 + R) * 32 + lane];
+        const double2 k1 = stage[(ii * 4 + 2 + R) * 32 + lane];
+        const double2 o = oth[lane * ROWP + i];
+        const double2 x0 = R == 0 ? y[i] : o, x1 = R == 0 ? o : y[i];
+        double re = __fma_rn(x0.x, k0.x, 0.0);
+        re = __fma_rn(-x0.y, k0.y, re);
+        double im = __fma_rn(x0.x, k0.y, 0.0);
+        im = __fma_rn(x0.y, k0.x, im);
+        re = __fma_rn(x1.x, k1.x, re);
+        re = __fma_rn(-x1.y, k1.y, re);
+        im = __fma_rn(x1.x, k1.y, im);
+        im = __fma_rn(x1.y, k1.x, im);
+        y[i] = make_double2(re, im);
+    }
+}
+
+template <int R, int NS, int RS>
+__device__ __forceinline__ void mac_all(double2 (&y)[32], const double2 *oth, const double2 *ring, u64 *full, u64 *empty, u32 &t, int lane) {
+    constexpr int SP = RS * 4 * 32;
+#pragma unroll
+    for (int c = 0; c < 32 / RS; c++) {
+        const u32 s = t % NS;
+        mbar_wait(full + s, (t / NS) & 1);
+        mac_rows<R, RS>(y, oth, ring + (size_t)s * SP, c * RS, lane);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(empty + s);
+        t++;
+    }
+}
+
+template <int TEAMS, int NS, int RS>
+__device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *smem_raw) {
+    using C = Cfg<TEAMS, NS, RS>;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    double2 *twB = (double2 *)smem_raw;
+    u64 *acc_base = (u64 *)(twB + TWB_ENTRIES);
+    double2 *buf_base = (double2 *)(acc_base + (size_t)TEAMS * 2 * N);
+    double2 *ring = buf_base + (size_t)TEAMS * 2 * BUF_POINTS;
+    u64 *full = (u64 *)(ring + (size_t)NS * C::STAGE_POINTS);
+    u64 *empty = full + NS;
+
+    const u32 first_ct = blockIdx.x * TEAMS;
+    const u32 left = a.B - first_ct;
+    const u32 live_teams = left < (u32)TEAMS ? left : (u32)TEAMS;
+    for (int i = tid; i < TWB_ENTRIES; i += C::THREADS) twB[i] = a.twB[i];
+    if (tid == 0) {
+        for (int s = 0; s < NS; s++) {
+            mbar_init(full + s, 1);
+            mbar_init(empty + s, 2 * live_teams);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    const u32 total = a.steps * C::STAGES_PER_GGSW;
+
+    if (warp == C::CONSUMER_WARPS) {   // ---- producer warp: one lane streams the key rows
+        if (lane == 0) {
+            constexpr u32 bytes = (u32)(sizeof(double2) * C::STAGE_POINTS);
+            for (u32 t = 0; t < total; t++) {
+                const u32 s = t % NS;
+                if (t >= (u32)NS) mbar_wait(empty + s, ((t / NS) - 1) & 1);
+                mbar_expect_tx(full + s, bytes);
+                bulk_g2s(ring + (size_t)s * C::STAGE_POINTS, a.bsk + (size_t)t * C::STAGE_POINTS, bytes, full + s);
+            }
+        }
+        return;
+    }
+
+    const int team = warp >> 1, r = warp & 1;
+    const u32 ct = first_ct + team;
+    if (ct >= a.B) return;
+    u64 *acc = acc_base + (size_t)team * 2 * N + (size_t)r * N;   // this warp's accumulator polynomial
+    double2 *buf = buf_base + ((size_t)team * 2 + r) * BUF_POINTS;
+    const double2 *buf_oth = buf_base + ((size_t)team * 2 + (r ^ 1)) * BUF_POINTS;
+    const u64 *lwe = a.lwe + (size_t)ct * (a.n + 1);
+    const u64 *tv = a.testv + (size_t)(a.lut_idx ? a.lut_idx[ct / a.lut_div] : 0) * N;
+
+    // acc0 = X^{ms(-b)} (0, testv)      ivc_based_vpbs.rs:109-124
+    {
+        const u32 sh0 = mod_switch((u64)0 - lwe[a.n]);
+        for (int p = lane; p < N; p += 32) acc[p] = r ? rotated(tv, (u32)p, sh0) : 0;
+    }
+    __syncwarp();
+
+    u32 t = 0;
+    u64 mask = a.steps ? lwe[0] : 0;
+    const int barrier_id = 1 + team;
+#pragma unroll 1
+    for (u32 it = 0; it < a.steps; it++) {
+        const u32 sh = mod_switch(mask);
+        if (it + 1 < a.steps) mask = lwe[it + 1];
+        double2 x[32];
+        // digits of X^sh acc_r - acc_r, folded: z[q] = (d[q], d[q + M]), q = lane + 32 i
+#pragma unroll
+        for (int i = 0; i < 32; i++) {
+            const u32 q = (u32)lane + 32u * i;
+            const u64 d0 = rotated(acc, q, sh) - acc[q];
+            const u64 d1 = rotated(acc, q + M, sh) - acc[q + M];
+            x[i] = make_double2(int_to_double(digit1(d0, a.logB)), int_to_double(digit1(d1, a.logB)));
+        }
+        fft_forward(x, buf, twB, a, lane);
+        // swap spectra with the partner warp
+#pragma unroll
+        for (int i = 0; i < 32; i++) buf[lane * ROWP + i] = x[i];
+        asm volatile("bar.sync %0, 64;" ::"r"(barrier_id) : "memory");
+        if (r == 0)
+            mac_all<0, NS, RS>(x, buf_oth, ring, full, empty, t, lane);
+        else
+            mac_all<1, NS, RS>(x, buf_oth, ring, full, empty, t, lane);
+        asm volatile("bar.sync %0, 64;" ::"r"(barrier_id) : "memory");
+        fft_inverse(x, buf, twB, a, lane);
+#pragma unroll
+        for (int i = 0; i < 32; i++) {
+            const u32 q = (u32)lane + 32u * i;
+            acc[q] += from_double(x[i].x);
+            acc[q + M] += from_double(x[i].y);
+        }
+        __syncwarp();
+    }
+
+    if (a.out_mode == 2) {
+        u64 *o = a.out + (size_t)ct * 2 * N + (size_t)r * N;
+        for (int p = lane; p < N; p += 32) o[p] = acc[p];
+    } else {   // sample extraction of coefficient 0      crypto/glwe.rs:96-106
+        u64 *o = a.out + (size_t)ct * (N + 1);
+        if (r == 0) {
+            for (int p = lane; p < N; p += 32) o[p] = p ? (u64)0 - acc[N - p] : acc[0];
+        } else if (lane == 0) {
+            o[N] = acc[0] + a.body_add;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------ utility kernels
+// One warp per polynomial: forward / inverse transform of folded complex data (parity probe), in the oracle's index order.
+__device__ __forceinline__ void fft_probe_body(const double2 *in, double2 *out, int inverse, double2 *buf, const double2 *twB, const Args &a, int lane) {
+    double2 x[32];
+    if (!inverse) {
+#pragma unroll
+        for (int i = 0; i < 32; i++) x[i] = in[lane + 32 * i];
+        fft_forward(x, buf, twB, a, lane);
+#pragma unroll
+        for (int i = 0; i < 32; i++) out[32 * lane + i] = x[i];
+    } else {
+#pragma unroll
+        for (int i = 0; i < 32; i++) x[i] = in[32 * lane + i];
+        fft_inverse(x, buf, twB, a, lane);
+#pragma unroll
+        for (int i = 0; i < 32; i++) out[lane + 32 * i] = x[i];
+    }
+}
+
+// key polynomial (coefficient domain, torus words) -> Fourier row in the ring layout   oracle/torus.c tor_ggsw_to_fourier
+// poly index pi = ((ggsw * 2 + j) * ell + lvl) * 2 + r with ell = 1; destination [ggsw][row i][j*2 + r][lane]
+__device__ __forceinline__ void key_to_fourier_body(const u64 *src, double2 *dst_ggsw, int poly_in_ggsw, double scale, double2 *buf, const double2 *twB,
+                                                    const Args &a, int lane) {
+    double2 x[32];
+#pragma unroll
+    for (int i = 0; i < 32; i++) {
+        const int q = lane + 32 * i;
+        x[i] = make_double2(__dmul_rn(__ll2double_rn((long long)src[q]), scale), __dmul_rn(__ll2double_rn((long long)src[q + M]), scale));
+    }
+    fft_forward(x, buf, twB, a, lane);
+    const bool neg = (poly_in_ggsw >> 1) == 0;   // mask GLev j = 0 (k = 1)
+#pragma unroll
+    for (int i = 0; i < 32; i++) {
+        double2 v = x[i];
+        if (neg) v = make_double2(-v.x, -v.y);
+        dst_ggsw[((size_t)i * 4 + poly_in_ggsw) * 32 + lane] = v;
+    }
+}
+
+}  // namespace fft64

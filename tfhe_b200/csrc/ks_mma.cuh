@@ -33,16 +33,31 @@ struct Args {
     const u64 *in;        // [B][kN+1]   (for the body)
     u64 *out;             // [B][n+1]
     u32 B, n, kN, K;
+    u32 torus;            // 0: words are Goldilocks elements; 1: words are 2^64-torus elements (wrapping recombination)
 };
 
 // digits of the mask coefficients as signed bytes: dig[b][i*ell + j] = digit_{L-ell+j}(in[b][i])
-__global__ void ks_digits_kernel(const u64 *in, int8_t *dig, u32 B, u32 Mpad, u32 kN, u32 ell, u32 logB, u32 L) {
+// torus != 0: tfhe-rs SignedDecomposer digits of the top ell*logB bits instead (oracle/torus.c tor_decompose), least significant level first
+__global__ void ks_digits_kernel(const u64 *in, int8_t *dig, u32 B, u32 Mpad, u32 kN, u32 ell, u32 logB, u32 L, u32 torus) {
     const bool centred = (L * logB == 64);
     const size_t total = (size_t)Mpad * kN;
     for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
         const u32 b = (u32)(idx / kN), i = (u32)(idx % kN);
         const u64 x = b < B ? in[(size_t)b * (kN + 1) + i] : 0;
         int8_t *o = dig + idx * ell;
+        if (torus) {
+            const u32 rep = ell * logB;
+            u64 state = rep >= 64 ? x : (((x >> (63 - rep)) + 1) >> 1) & ((1ull << rep) - 1);
+            const u64 mask = (1ull << logB) - 1;
+            for (u32 j = 0; j < ell; j++) {
+                const u64 res = state & mask;
+                state >>= logB;
+                const u64 carry = (((res - 1ull) | state) & res) >> (logB - 1);
+                state += carry;
+                o[j] = (int8_t)((long long)res - (long long)(carry << logB));
+            }
+            continue;
+        }
         for (u32 j = 0; j < ell; j++) {
             const u64 d = gl_digit(x, L - ell + j, logB, centred);  // canonical field element, |d| <= 2^(logB-1)
             o[j] = (d > GL_Q / 2) ? (int8_t)(-(int)(u32)(GL_Q - d)) : (int8_t)(u32)d;
@@ -173,8 +188,14 @@ __global__ void __launch_bounds__(THREADS, 2) lwe_keyswitch_mma_kernel(const Arg
         const int4 hi4 = *reinterpret_cast<const int4 *>(C + row * C_STRIDE + c * 8 + 4);
         const long long P = (long long)lo4.x + ((long long)lo4.y << 8) + ((long long)lo4.z << 16) + ((long long)lo4.w << 24);
         const long long Q = (long long)hi4.x + ((long long)hi4.y << 8) + ((long long)hi4.z << 16) + ((long long)hi4.w << 24);
-        u64 v = gl_canon(gl_add(gl_mul_lazy(signed_to_field(Q), 1ULL << 32), signed_to_field(P)));
-        if (col == a.n) v = gl_canon(gl_add(v, a.in[(size_t)b * (a.kN + 1) + a.kN]));
+        u64 v;
+        if (a.torus) {
+            v = (u64)P + ((u64)Q << 32);
+            if (col == a.n) v += a.in[(size_t)b * (a.kN + 1) + a.kN];
+        } else {
+            v = gl_canon(gl_add(gl_mul_lazy(signed_to_field(Q), 1ULL << 32), signed_to_field(P)));
+            if (col == a.n) v = gl_canon(gl_add(v, a.in[(size_t)b * (a.kN + 1) + a.kN]));
+        }
         a.out[(size_t)b * cols + col] = v;
     }
 }

@@ -15,6 +15,9 @@ import numpy as np
 Q = 0xFFFFFFFF00000001
 ORDER_PBS_GLWEKS = 0
 ORDER_LWEKS_PBS = 1
+ORDER_PBS_LWEKS = 2
+ARITH_GOLDILOCKS_NTT = 0
+ARITH_TORUS64_FFT = 1
 DOMAIN_STANDARD = 0
 DOMAIN_NTT = 1
 
@@ -35,7 +38,7 @@ class LuxError(RuntimeError):
 
 
 class _CParams(C.Structure):
-    _fields_ = [(f, C.c_uint32) for f in ("n", "N", "k", "ell", "logB", "ell_ks", "logB_ks", "order")]
+    _fields_ = [(f, C.c_uint32) for f in ("n", "N", "k", "ell", "logB", "ell_ks", "logB_ks", "order", "arith")]
 
 
 @dataclass(frozen=True)
@@ -50,9 +53,14 @@ class Params:
     ell_ks: int = 0
     logB_ks: int = 0
     order: int = ORDER_PBS_GLWEKS
+    arith: int = ARITH_GOLDILOCKS_NTT   # ARITH_TORUS64_FFT: (ell, logB) are tfhe-rs's (level, base_log)
 
     def c(self) -> _CParams:
-        return _CParams(self.n, self.N, self.k, self.ell, self.logB, self.ell_ks, self.logB_ks, self.order)
+        return _CParams(self.n, self.N, self.k, self.ell, self.logB, self.ell_ks, self.logB_ks, self.order, self.arith)
+
+    @property
+    def modulus(self) -> int:
+        return 1 << 64 if self.arith == ARITH_TORUS64_FFT else Q
 
     @property
     def ggsw_len(self) -> int:
@@ -75,6 +83,11 @@ S1_BOOLEAN = Params(n=728, N=1024, k=1, ell=4, logB=5, ell_ks=4, logB_ks=5, orde
 # reference's Goldilocks modulus: n=918, N=2048, one 23-bit PBS digit at 2^41 (logB=41 in the limb
 # convention => L=2, top limb = bits 41..63), key switch 4 levels of 4 bits (limbs 12..15 of 16).
 S2_SHORTINT = Params(n=918, N=2048, k=1, ell=1, logB=41, ell_ks=4, logB_ks=4, order=ORDER_LWEKS_PBS)
+# S2 on the arithmetic the named set is defined on (tfhe-rs: 2^64 torus, f64 FFT): n = 918, N = 2048, PBS base 2^23 x 1
+# level, key switch base 2^4 x 4 levels, LWE noise TUniform(45), GLWE noise TUniform(17)   
+S2_TORUS = Params(n=918, N=2048, k=1, ell=1, logB=23, ell_ks=4, logB_ks=4, order=ORDER_LWEKS_PBS, arith=ARITH_TORUS64_FFT)
+TEST_SMALL_TORUS = Params(n=20, N=2048, k=1, ell=1, logB=23, ell_ks=4, logB_ks=4, order=ORDER_LWEKS_PBS, arith=ARITH_TORUS64_FFT)
+TEST_SMALL_TORUS_O2 = Params(n=20, N=2048, k=1, ell=1, logB=23, ell_ks=4, logB_ks=4, order=ORDER_PBS_LWEKS, arith=ARITH_TORUS64_FFT)
 # small sets for fast parity tests
 TEST_SMALL_O0 = Params(n=24, N=512, k=1, ell=4, logB=8, ell_ks=4, logB_ks=8, order=ORDER_PBS_GLWEKS)
 TEST_SMALL_O1 = Params(n=24, N=512, k=1, ell=2, logB=16, ell_ks=8, logB_ks=4, order=ORDER_LWEKS_PBS)
@@ -110,6 +123,11 @@ ABI = {
     "lux_gate_not": (_int, [_vp, _vp, _sz, _vp]),
     "lux_make_testv": (_int, [_u32, _u32, _u64, _u64p, _u64p]),
     "lux_delta": (_u64, [_u32]),
+    "lux_make_testv_arith": (_int, [_u32, _u32, _u32, _u64, _u64p, _u64p]),
+    "lux_delta_arith": (_u64, [_u32, _u32]),
+    "lux_fft": (_int, [_vp, _vp, _sz, _int, _vp]),
+    "lux_torus_decompose": (_int, [_vp, _u64p, _sz, _vp]),
+    "lux_export_bsk_fourier": (_int, [_vp, _vp, _sz]),
     "lux_ntt_forward": (_int, [_vp, _u64p, _sz, _u64p]),
     "lux_ntt_backward": (_int, [_vp, _u64p, _sz, _u64p]),
     "lux_ntt_any": (_int, [_vp, _u32, _int, _u64p, _sz, _u64p]),
@@ -162,17 +180,17 @@ def _u64arr(a) -> np.ndarray:
     return np.ascontiguousarray(a, dtype=np.uint64)
 
 
-def make_testv(N: int, p: int, delta_: int, lut) -> np.ndarray:
+def make_testv(N: int, p: int, delta_: int, lut, arith: int = ARITH_GOLDILOCKS_NTT) -> np.ndarray:
     """get_testv (crypto/mod.rs:17-27) generalised to an arbitrary p-entry table."""
     out = np.zeros(N, np.uint64)
-    rc = lib().lux_make_testv(N, p, delta_, _u64arr(lut), out)
+    rc = lib().lux_make_testv_arith(arith, N, p, delta_, _u64arr(lut), out)
     if rc:
         raise LuxError(rc, "lux_make_testv: bad arguments")
     return out
 
 
-def delta(space: int) -> int:
-    return lib().lux_delta(space)
+def delta(space: int, arith: int = ARITH_GOLDILOCKS_NTT) -> int:
+    return lib().lux_delta_arith(arith, space)
 
 
 def _ptr(x):
@@ -397,6 +415,26 @@ class Engine:
         out = np.empty((a.shape[0], 2 * self.p.N), np.uint64)
         self._ck(lib().lux_blind_rotate(self._h, a.reshape(-1), tv.reshape(-1), tv.shape[0], _ptr(idx), a.shape[0],
                                         self.p.n if steps is None else steps, out.reshape(-1)))
+        return out
+
+    # ---- pieces of the torus / f64-FFT arithmetic
+    def fft(self, z, inverse=False):
+        """[n_polys][N/2] complex128: forward natural -> engine order, or the unnormalised inverse"""
+        a = np.ascontiguousarray(z, dtype=np.complex128).reshape(-1, self.p.N // 2)
+        out = np.empty_like(a)
+        self._ck(lib().lux_fft(self._h, a.ctypes.data, a.shape[0], int(inverse), out.ctypes.data))
+        return out
+
+    def torus_decompose(self, values):
+        a = _u64arr(values).reshape(-1)
+        out = np.empty(a.size, np.int64)
+        self._ck(lib().lux_torus_decompose(self._h, a, a.size, out.ctypes.data))
+        return out
+
+    def bsk_fourier(self):
+        """resident Fourier key rows [n][32 rows][4 polys (j*2+r)][32 lanes] complex128"""
+        out = np.empty((self.p.n, 32, 4, 32), np.complex128)
+        self._ck(lib().lux_export_bsk_fourier(self._h, out.ctypes.data, out.size * 2))
         return out
 
     def external_product(self, ggsw, glwe, domain=DOMAIN_STANDARD):
