@@ -1,0 +1,35 @@
+"""Quick device-resident timing of the torus/f64-FFT PBS at S2 (random key words: throughput is data independent).
+usage: python scripts/quick_torus.py [B] [teams...]"""
+import sys, time
+from pathlib import Path
+sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+import numpy as np, torch
+import tfhe_b200 as T
+
+B = int(sys.argv[1]) if len(sys.argv) > 1 else 4440
+teams_list = [int(x) for x in sys.argv[2:]] or [0]   # teams + 10 * variant
+p = T.S2_TORUS
+eng = T.Engine(p)
+rs = np.random.RandomState(1)
+r64 = lambda n: rs.randint(0, 2**63, size=n, dtype=np.int64).astype(np.uint64) * np.uint64(2)
+eng.load_bsk(r64(p.n * p.ggsw_len))
+eng.load_lwe_ksk(r64(p.lwe_ksk_len))
+d_in = torch.from_numpy(r64(B * p.ct_len).view(np.int64)).cuda()
+d_tv = torch.from_numpy(r64(4 * p.N).view(np.int64)).cuda()
+d_idx = torch.from_numpy((np.arange(B) % 4).astype(np.int32)).cuda()
+d_out = torch.empty_like(d_in)
+s = torch.cuda.Stream(); torch.cuda.set_stream(s)
+eng.set_timing(True)
+for t in teams_list:
+    eng.force_teams(t % 10)
+    eng.fft_variant(t // 10)
+    for _ in range(2):
+        eng.pbs_batch_device(d_in, d_tv, d_idx, B, d_out, n_luts=4, stream=s.cuda_stream)
+    torch.cuda.synchronize()
+    ms = []
+    for _ in range(4):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(s); eng.pbs_batch_device(d_in, d_tv, d_idx, B, d_out, n_luts=4, stream=s.cuda_stream); b.record(s); b.synchronize()
+        ms.append(a.elapsed_time(b))
+    ks, br = eng.last_timing()
+    print(f"B={B} teams={t} wave={eng.wave_ciphertexts(B)}: {min(ms):.2f} ms best, {B/min(ms)*1e3:.0f} PBS/s  (ks {ks:.2f} ms, br {br:.2f} ms)", flush=True)

@@ -7,10 +7,10 @@
 
 using namespace fft64;
 
-template <int TEAMS, int NS, int RS>
-__global__ void __launch_bounds__(Cfg<TEAMS, NS, RS>::THREADS, 1) blind_rotate_fft_kernel(const __grid_constant__ Args a) {
+template <int TEAMS, int NS, int RS, int TWS>
+__global__ void __launch_bounds__(Cfg<TEAMS, NS, RS, TWS>::THREADS, 1) blind_rotate_fft_kernel(const __grid_constant__ Args a) {
     extern __shared__ __align__(16) unsigned char smem[];
-    blind_rotate_body<TEAMS, NS, RS>(a, smem);
+    blind_rotate_body<TEAMS, NS, RS, TWS>(a, smem);
 }
 
 constexpr int UTIL_WARPS = 4;
@@ -86,16 +86,16 @@ static void fill_tables(const lux_engine *e, Args &a) {
     for (int v = 0; v < 32; v++) a.twA[v] = make_double2(e->fft_twA[2 * v], e->fft_twA[2 * v + 1]);
 }
 
-template <int TEAMS, int NS, int RS>
+template <int TEAMS, int NS, int RS, int TWS>
 static int launch_cfg(lux_engine *e, const Args &a, cudaStream_t s) {
-    using C = Cfg<TEAMS, NS, RS>;
+    using C = Cfg<TEAMS, NS, RS, TWS>;
     static bool configured[64] = {};
     if (!configured[e->device & 63]) {
-        CUDA_TRY(e, cudaFuncSetAttribute(blind_rotate_fft_kernel<TEAMS, NS, RS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM));
+        CUDA_TRY(e, cudaFuncSetAttribute(blind_rotate_fft_kernel<TEAMS, NS, RS, TWS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM));
         configured[e->device & 63] = true;
     }
     const unsigned grid = (a.B + TEAMS - 1) / TEAMS;
-    blind_rotate_fft_kernel<TEAMS, NS, RS><<<grid, C::THREADS, C::SMEM, s>>>(a);
+    blind_rotate_fft_kernel<TEAMS, NS, RS, TWS><<<grid, C::THREADS, C::SMEM, s>>>(a);
     e->launches++;
     CUDA_TRY(e, cudaGetLastError());
     return LUX_OK;
@@ -114,10 +114,14 @@ size_t lux_fft_wave(const lux_engine *e, size_t B) { return (size_t)e->sm_count 
 
 int lux_fft_launch_br(lux_engine *e, Args a, cudaStream_t s) {
     fill_tables(e, a);
+    const int variant = e->fft_variant;
     switch (pick_teams(e, a.B)) {
-        case 1: return launch_cfg<1, 4, 8>(e, a, s);
-        case 2: return launch_cfg<2, 4, 8>(e, a, s);
-        default: return launch_cfg<3, 2, 4>(e, a, s);
+        case 1: return launch_cfg<1, 4, 8, 1>(e, a, s);
+        case 2: return launch_cfg<2, 4, 8, 1>(e, a, s);
+        default:
+            if (variant == 1) return launch_cfg<3, 2, 4, 1>(e, a, s);
+            if (variant == 2) return launch_cfg<3, 3, 4, 1>(e, a, s);
+            return launch_cfg<3, 4, 4, 0>(e, a, s);
     }
 }
 

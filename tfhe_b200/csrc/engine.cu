@@ -595,6 +595,11 @@ int lux_debug_br_regs(lux_engine *e, int regs) {
     e->br_regs = regs;
     return LUX_OK;
 }
+int lux_debug_fft_variant(lux_engine *e, int variant) {
+    if (!e) return LUX_ERR_INVALID;
+    e->fft_variant = variant;
+    return LUX_OK;
+}
 int lux_debug_cluster_regs(lux_engine *e, int regs) {
     if (!e || (regs != 0 && regs != 4 && regs != 8 && regs != 16)) return LUX_ERR_INVALID;
     e->cluster_regs = regs;

@@ -36,7 +36,7 @@ constexpr double MAGIC = 6755399441055744.0;   // 1.5 * 2^52
 constexpr double TWO51 = 2251799813685248.0;   // 2^51
 constexpr int LOGN = 11, N = 1 << LOGN, M = N / 2;   // ring degree of the named set
 constexpr int ROWP = 33;                       // padded row length of the transpose buffer (in points)
-constexpr int BUF_POINTS = 32 * ROWP;          // one warp's transpose / swap buffer
+constexpr int BUF_POINTS = 31 * ROWP + 32;     // one warp's transpose / swap buffer (the last row needs no padding)
 constexpr int TWB_ENTRIES = 512;               // pass-B table: 32 (m = 32) + 32 + 64 + 128 + 256 even nodes
 
 struct Args {
@@ -112,50 +112,127 @@ __device__ __forceinline__ void bfly(double2 &u, double2 &v, double wr, double w
         ct_bfly(u, v, wr, wi);
 }
 
+// Butterflies are issued in groups of G, LEVEL by level (all first fused multiply-adds of the group, then all second
+// ones, ...): ptxas otherwise emits each butterfly as its own chain of dependent DFMAs and a warp that is alone on its
+// scheduler waits out the FP64 latency three times per butterfly (profiles/r02a: stall_wait 20 % of samples).
+// The arithmetic per butterfly is unchanged, so results are bit-identical.
+#ifndef FFT64_GROUP
+#define FFT64_GROUP 4
+#endif
+template <bool INV, int G>
+__device__ __forceinline__ void bfly_group(double2 (&x)[32], const int (&iu)[G], const int (&iv)[G], const double (&wr)[G], const double (&wi)[G]) {
+    if (!INV) {
+        double tr[G], ti[G];
+#pragma unroll
+        for (int k = 0; k < G; k++) {
+            tr[k] = __fma_rn(-wi[k], x[iv[k]].y, x[iu[k]].x);
+            ti[k] = __fma_rn(wi[k], x[iv[k]].x, x[iu[k]].y);
+        }
+#pragma unroll
+        for (int k = 0; k < G; k++) {
+            tr[k] = __fma_rn(wr[k], x[iv[k]].x, tr[k]);
+            ti[k] = __fma_rn(wr[k], x[iv[k]].y, ti[k]);
+        }
+#pragma unroll
+        for (int k = 0; k < G; k++) {
+            x[iv[k]].x = __fma_rn(2.0, x[iu[k]].x, -tr[k]);
+            x[iv[k]].y = __fma_rn(2.0, x[iu[k]].y, -ti[k]);
+            x[iu[k]].x = tr[k];
+            x[iu[k]].y = ti[k];
+        }
+    } else {
+        double dr[G], di[G], m0[G], m1[G];
+#pragma unroll
+        for (int k = 0; k < G; k++) {
+            dr[k] = __dsub_rn(x[iu[k]].x, x[iv[k]].x);
+            di[k] = __dsub_rn(x[iu[k]].y, x[iv[k]].y);
+            x[iu[k]].x = __dadd_rn(x[iu[k]].x, x[iv[k]].x);
+            x[iu[k]].y = __dadd_rn(x[iu[k]].y, x[iv[k]].y);
+        }
+#pragma unroll
+        for (int k = 0; k < G; k++) {
+            m0[k] = __dmul_rn(di[k], wi[k]);
+            m1[k] = __dmul_rn(dr[k], wi[k]);
+        }
+#pragma unroll
+        for (int k = 0; k < G; k++) {
+            x[iv[k]].x = __fma_rn(dr[k], wr[k], m0[k]);
+            x[iv[k]].y = __fma_rn(di[k], wr[k], -m1[k]);
+        }
+    }
+}
+
 // pass A: tree levels m = 1..16 on the column layout; node m + blk pairs registers blk*2t + jj and + t, t = 16/m
 template <bool INV>
 __device__ __forceinline__ void pass_a(double2 (&x)[32], const Args &a) {
+    constexpr int G = FFT64_GROUP;
 #pragma unroll
     for (int s0 = 0; s0 < 5; s0++) {
         const int s = INV ? 4 - s0 : s0;
         const int m = 1 << s, t = 16 >> s;
 #pragma unroll
-        for (int blk = 0; blk < m; blk++) {
-            const int node = m + blk;
-            double wr, wi;
-            if (node > 1 && (node & 1)) {   // tw[2v+1] = i * tw[2v]
-                wr = -a.twA[node - 1].y;
-                wi = a.twA[node - 1].x;
-            } else {
-                wr = a.twA[node].x;
-                wi = a.twA[node].y;
-            }
+        for (int b0 = 0; b0 < 16; b0 += G) {
+            int iu[G], iv[G];
+            double wr[G], wi[G];
 #pragma unroll
-            for (int jj = 0; jj < t; jj++) bfly<INV>(x[blk * 2 * t + jj], x[blk * 2 * t + jj + t], wr, wi);
+            for (int k = 0; k < G; k++) {
+                const int b = b0 + k, blk = b / t, jj = b % t, node = m + blk;
+                iu[k] = blk * 2 * t + jj;
+                iv[k] = iu[k] + t;
+                if (node > 1 && (node & 1)) {   // tw[2v+1] = i * tw[2v]
+                    wr[k] = -a.twA[node - 1].y;
+                    wi[k] = a.twA[node - 1].x;
+                } else {
+                    wr[k] = a.twA[node].x;
+                    wi[k] = a.twA[node].y;
+                }
+            }
+            bfly_group<INV, G>(x, iu, iv, wr, wi);
         }
     }
 }
 // pass B: tree levels m = 32 g, g = 1..16, on the row layout; lane r owns nodes m + r g + b, b < g
-template <bool INV>
-__device__ __forceinline__ void pass_b(double2 (&y)[32], const double2 *twB, int lane) {
+template <bool INV, int GI>
+__device__ __forceinline__ void pass_b_stage(double2 (&y)[32], const double2 *twB, int lane) {
+    constexpr int G = FFT64_GROUP;
+    constexpr int g = 1 << GI, t = 16 >> GI, NW = g >= 2 ? g / 2 : 1;
+    double2 w[NW];
 #pragma unroll
-    for (int gi0 = 0; gi0 < 5; gi0++) {
-        const int gi = INV ? 4 - gi0 : gi0;
-        const int g = 1 << gi, t = 16 >> gi;
-        if (g == 1) {
-            const double2 w = twB[lane];
+    for (int e = 0; e < NW; e++) w[e] = twB[(g == 1 ? 0 : 16 * g) + e * 32 + lane];
 #pragma unroll
-            for (int jj = 0; jj < 16; jj++) bfly<INV>(y[jj], y[jj + 16], w.x, w.y);
-        } else {
+    for (int b0 = 0; b0 < 16; b0 += G) {
+        int iu[G], iv[G];
+        double wr[G], wi[G];
 #pragma unroll
-            for (int e = 0; e < g / 2; e++) {
-                const double2 w = twB[16 * g + e * 32 + lane];
-#pragma unroll
-                for (int jj = 0; jj < t; jj++) bfly<INV>(y[(2 * e) * 2 * t + jj], y[(2 * e) * 2 * t + jj + t], w.x, w.y);
-#pragma unroll
-                for (int jj = 0; jj < t; jj++) bfly<INV>(y[(2 * e + 1) * 2 * t + jj], y[(2 * e + 1) * 2 * t + jj + t], -w.y, w.x);
+        for (int k = 0; k < G; k++) {
+            const int b = b0 + k, blk = b / t, jj = b % t;
+            iu[k] = blk * 2 * t + jj;
+            iv[k] = iu[k] + t;
+            if (blk & 1) {
+                wr[k] = -w[blk / 2].y;
+                wi[k] = w[blk / 2].x;
+            } else {
+                wr[k] = w[blk / 2].x;
+                wi[k] = w[blk / 2].y;
             }
         }
+        bfly_group<INV, G>(y, iu, iv, wr, wi);
+    }
+}
+template <bool INV>
+__device__ __forceinline__ void pass_b(double2 (&y)[32], const double2 *twB, int lane) {
+    if (!INV) {
+        pass_b_stage<false, 0>(y, twB, lane);
+        pass_b_stage<false, 1>(y, twB, lane);
+        pass_b_stage<false, 2>(y, twB, lane);
+        pass_b_stage<false, 3>(y, twB, lane);
+        pass_b_stage<false, 4>(y, twB, lane);
+    } else {
+        pass_b_stage<true, 4>(y, twB, lane);
+        pass_b_stage<true, 3>(y, twB, lane);
+        pass_b_stage<true, 2>(y, twB, lane);
+        pass_b_stage<true, 1>(y, twB, lane);
+        pass_b_stage<true, 0>(y, twB, lane);
     }
 }
 // transposes through the warp's padded buffer
@@ -188,37 +265,55 @@ __device__ __forceinline__ void fft_inverse(double2 (&y)[32], double2 *buf, cons
 
 // ------------------------------------------------------------------------------------------ blind rotation
 // ring stage = RS rows of the GGSW: [RS][4 polys][32 lanes] double2 = RS * 2 KiB
-template <int TEAMS, int NS, int RS>
+// TWS: pass-B twiddle table in shared memory (1) or read from global memory through L1 (0: the 8 KiB go to the key ring)
+template <int TEAMS, int NS, int RS, int TWS = 1>
 struct Cfg {
     static constexpr int CONSUMER_WARPS = 2 * TEAMS;
     static constexpr int THREADS = 32 * (CONSUMER_WARPS + 1);
     static constexpr int STAGE_POINTS = RS * 4 * 32;
     static constexpr int STAGES_PER_GGSW = 32 / RS;
     static constexpr size_t SMEM =
-        sizeof(double2) * TWB_ENTRIES + (size_t)TEAMS * (sizeof(u64) * 2 * N + sizeof(double2) * 2 * BUF_POINTS) +
+        sizeof(double2) * TWB_ENTRIES * TWS + (size_t)TEAMS * (sizeof(u64) * 2 * N + sizeof(double2) * 2 * BUF_POINTS) +
         sizeof(double2) * (size_t)NS * STAGE_POINTS + sizeof(u64) * 2 * NS + 16;
 };
 
-// multiply-accumulate of the swapped spectra with the staged key rows: out = X0 K[0][r] + X1 K[1][r], in the oracle's order
+// multiply-accumulate of the swapped spectra with the staged key rows: out = X0 K[0][r] + X1 K[1][r], in the oracle's order;
+// the RS rows of a stage advance together, one fused multiply-add of each chain at a time
 template <int R, int RS>
 __device__ __forceinline__ void mac_rows(double2 (&y)[32], const double2 *oth, const double2 *stage, int row0, int lane) {
+    double2 k0[RS], k1[RS], x0[RS], x1[RS];
+    double re[RS], im[RS];
 #pragma unroll
     for (int ii = 0; ii < RS; ii++) {
         const int i = row0 + ii;   // compile-time after unrolling of the caller
-        const double2 k0 = stage[(ii * 4 + 0 + R) * 32 + lane];
-        const double2 k1 = stage[(ii * 4 + 2 + R) * 32 + lane];
+        k0[ii] = stage[(ii * 4 + 0 + R) * 32 + lane];
+        k1[ii] = stage[(ii * 4 + 2 + R) * 32 + lane];
         const double2 o = oth[lane * ROWP + i];
-        const double2 x0 = R == 0 ? y[i] : o, x1 = R == 0 ? o : y[i];
-        double re = __fma_rn(x0.x, k0.x, 0.0);
-        re = __fma_rn(-x0.y, k0.y, re);
-        double im = __fma_rn(x0.x, k0.y, 0.0);
-        im = __fma_rn(x0.y, k0.x, im);
-        re = __fma_rn(x1.x, k1.x, re);
-        re = __fma_rn(-x1.y, k1.y, re);
-        im = __fma_rn(x1.x, k1.y, im);
-        im = __fma_rn(x1.y, k1.x, im);
-        y[i] = make_double2(re, im);
+        x0[ii] = R == 0 ? y[i] : o;
+        x1[ii] = R == 0 ? o : y[i];
     }
+#pragma unroll
+    for (int ii = 0; ii < RS; ii++) {
+        re[ii] = __fma_rn(x0[ii].x, k0[ii].x, 0.0);
+        im[ii] = __fma_rn(x0[ii].x, k0[ii].y, 0.0);
+    }
+#pragma unroll
+    for (int ii = 0; ii < RS; ii++) {
+        re[ii] = __fma_rn(-x0[ii].y, k0[ii].y, re[ii]);
+        im[ii] = __fma_rn(x0[ii].y, k0[ii].x, im[ii]);
+    }
+#pragma unroll
+    for (int ii = 0; ii < RS; ii++) {
+        re[ii] = __fma_rn(x1[ii].x, k1[ii].x, re[ii]);
+        im[ii] = __fma_rn(x1[ii].x, k1[ii].y, im[ii]);
+    }
+#pragma unroll
+    for (int ii = 0; ii < RS; ii++) {
+        re[ii] = __fma_rn(-x1[ii].y, k1[ii].y, re[ii]);
+        im[ii] = __fma_rn(x1[ii].y, k1[ii].x, im[ii]);
+    }
+#pragma unroll
+    for (int ii = 0; ii < RS; ii++) y[row0 + ii] = make_double2(re[ii], im[ii]);
 }
 
 template <int R, int NS, int RS>
@@ -235,12 +330,13 @@ __device__ __forceinline__ void mac_all(double2 (&y)[32], const double2 *oth, co
     }
 }
 
-template <int TEAMS, int NS, int RS>
+template <int TEAMS, int NS, int RS, int TWS>
 __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *smem_raw) {
-    using C = Cfg<TEAMS, NS, RS>;
+    using C = Cfg<TEAMS, NS, RS, TWS>;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    double2 *twB = (double2 *)smem_raw;
-    u64 *acc_base = (u64 *)(twB + TWB_ENTRIES);
+    double2 *tw_smem = (double2 *)smem_raw;
+    const double2 *twB = TWS ? tw_smem : a.twB;
+    u64 *acc_base = (u64 *)(tw_smem + TWB_ENTRIES * TWS);
     double2 *buf_base = (double2 *)(acc_base + (size_t)TEAMS * 2 * N);
     double2 *ring = buf_base + (size_t)TEAMS * 2 * BUF_POINTS;
     u64 *full = (u64 *)(ring + (size_t)NS * C::STAGE_POINTS);
@@ -249,7 +345,8 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
     const u32 first_ct = blockIdx.x * TEAMS;
     const u32 left = a.B - first_ct;
     const u32 live_teams = left < (u32)TEAMS ? left : (u32)TEAMS;
-    for (int i = tid; i < TWB_ENTRIES; i += C::THREADS) twB[i] = a.twB[i];
+    if (TWS)
+        for (int i = tid; i < TWB_ENTRIES; i += C::THREADS) tw_smem[i] = a.twB[i];
     if (tid == 0) {
         for (int s = 0; s < NS; s++) {
             mbar_init(full + s, 1);
@@ -317,10 +414,21 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
         asm volatile("bar.sync %0, 64;" ::"r"(barrier_id) : "memory");
         fft_inverse(x, buf, twB, a, lane);
 #pragma unroll
-        for (int i = 0; i < 32; i++) {
-            const u32 q = (u32)lane + 32u * i;
-            acc[q] += from_double(x[i].x);
-            acc[q + M] += from_double(x[i].y);
+        for (int i0 = 0; i0 < 32; i0 += 4) {   // four points = eight independent conversion chains at a time
+            double t[8], f[8];
+#pragma unroll
+            for (int k = 0; k < 8; k++) t[k] = __dadd_rn((k & 1) ? x[i0 + k / 2].y : x[i0 + k / 2].x, MAGIC);
+#pragma unroll
+            for (int k = 0; k < 8; k++) t[k] = __dsub_rn(t[k], MAGIC);
+#pragma unroll
+            for (int k = 0; k < 8; k++) f[k] = __dsub_rn((k & 1) ? x[i0 + k / 2].y : x[i0 + k / 2].x, t[k]);
+#pragma unroll
+            for (int k = 0; k < 8; k++) f[k] = __fma_rn(f[k], TWO51, MAGIC);
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                const u32 q = (u32)lane + 32u * (i0 + k / 2) + ((k & 1) ? M : 0);
+                acc[q] += (u64)(__double_as_longlong(f[k]) - 0x4338000000000000LL) << 13;
+            }
         }
         __syncwarp();
     }

@@ -367,6 +367,10 @@ class Engine:
         0 integer-pipe kernel only"""
         self._ck(lib().lux_debug_ks_mode(self._h, mode))
 
+    def fft_variant(self, v: int):
+        lib().lux_debug_fft_variant.argtypes = [_vp, _int]
+        self._ck(lib().lux_debug_fft_variant(self._h, v))
+
     def force_teams(self, t: int):
         lib().lux_debug_force_teams(self._h, t)
 
