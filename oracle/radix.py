@@ -55,9 +55,10 @@ def _fmul_small(a: np.ndarray, c: int) -> np.ndarray:
     return ((a.astype(object) * c) % Q).astype(np.uint64)
 
 
-def interp_cipher(ctx, prog, luts, operands, testv_lut, delta):
-    """operands: list of arrays [B][blocks][w] (uint64).  ctx: oracle Ctx with keys installed.
-    testv_lut(lut_row) -> test vector polynomial.  Returns list of arrays [B][out_blocks][w]."""
+def interp_cipher(ctx, prog, luts, operands, testv_lut, delta, modulus=Q):
+    """operands: list of arrays [B][blocks][w] (uint64).  ctx: oracle Ctx (oracle.Ctx or oracle.torus.Ctx) with keys
+    installed; modulus = Q (Goldilocks) or 2**64 (torus).  testv_lut(lut_row) -> test vector polynomial.
+    Returns list of arrays [B][out_blocks][w]."""
     B = operands[0].shape[0]
     w = operands[0].shape[2]
     slots = {}
@@ -70,8 +71,8 @@ def interp_cipher(ctx, prog, luts, operands, testv_lut, delta):
     def lin(l):
         acc = np.zeros((B, w), dtype=object)
         for sl, c in l.terms:
-            acc = (acc + slots[sl] * c) % Q
-        acc[:, w - 1] = (acc[:, w - 1] + (l.konst % 32) * delta) % Q
+            acc = (acc + slots[sl] * c) % modulus
+        acc[:, w - 1] = (acc[:, w - 1] + (l.konst % 32) * delta) % modulus
         return acc
 
     tvs = np.stack([testv_lut(luts[i]) for i in range(len(luts))])

@@ -32,40 +32,31 @@ def centred(noisy: np.ndarray, expect: np.ndarray, q: int) -> np.ndarray:
     return (d / q).astype(np.float64)
 
 
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--trials", type=int, default=1 << 20)
-    ap.add_argument("--chunk", type=int, default=1 << 16)
-    ap.add_argument("--oracle-sample", type=int, default=8, help="outputs per round compared bit-exactly with the oracle")
-    ap.add_argument("--out", default="gpurun_out/decrypt_trials.json")
-    args = ap.parse_args()
+def run(arith="torus", trials=1 << 20, chunk=1 << 16, oracle_sample=8, verbose=True):
+    """the gate: returns the result dict (wrong_decryptions, variance, bound ...)"""
+    import bench
 
-    import oracle as O
-    import tfhe_b200 as T
-
-    params = T.S2_SHORTINT
-    sig_glwe, sig_lwe = 2.0 ** -47.8, 2.0 ** -19.8
-    ctx = O.Ctx(O.Params(n=params.n, N=params.N, k=params.k, ell=params.ell, logB=params.logB,
-                         ell_ks=params.ell_ks, logB_ks=params.logB_ks, order=params.order))
-    ks = O.keygen(ctx, 11, sig_glwe, sig_lwe)
-    O.install_keys(ctx, ks)
-    eng = T.Engine(params, device=0)
+    side = bench.make_side(arith)
+    params = side.params
+    ks = side.fixture(11)
+    eng = side.T.Engine(params, device=0)
     eng.load_keyset(ks)
+    q = side.mod
 
     p = 16                               # 4-bit messages, one padding bit: plaintext space 32
-    delta = O.delta(2 * p)
+    delta = side.delta(2 * p)
     rs = np.random.RandomState(5)
     luts = [list(range(16)), [(x * x) % 16 for x in range(16)], [x >> 2 for x in range(16)], [x & 3 for x in range(16)],
             [(5 * x + 3) % 16 for x in range(16)], [15 - x for x in range(16)]]
     luts += [list(map(int, rs.permutation(16))) for _ in range(10)]
-    tvs = np.stack([O.testv_lut(params.N, p, delta, lut) for lut in luts])
+    tvs = np.stack([side.T.make_testv(params.N, p, delta, lut, params.arith) for lut in luts])
     lut_arr = np.array(luts, dtype=np.int64)
 
-    B = args.chunk
-    rounds = -(-args.trials // B)
+    B = chunk
+    rounds = -(-trials // B)
     msgs = rs.randint(0, p, size=B).astype(np.int64)
     t0 = time.time()
-    cts = O.lwe_encrypt_batch(1234, ks.s_in, (msgs.astype(np.uint64) * np.uint64(delta)), sig_glwe)
+    cts = side.encrypt(1234, msgs)
     t_enc = time.time() - t0
     failures, total, exact_checked = 0, 0, 0
     noise_sum, noise_sq, noise_max = 0.0, 0.0, 0.0
@@ -76,44 +67,57 @@ def main():
         out = eng.pbs_batch(cts, tvs, idx)
         t_gpu += time.time() - t0
         want_msgs = lut_arr[idx, msgs]
-        noisy = O.lwe_decrypt_batch(ks.s_in, out)
+        noisy = side.O.lwe_decrypt_batch(ks.s_in, out)
         # decode: round(noisy / delta) mod 2p   (main.rs:59-64)
-        dec = np.array([((int(v) + delta // 2) // delta) % (2 * p) for v in noisy], dtype=np.int64)
+        nz = noisy.astype(object)
+        dec = np.array([((int(v) + delta // 2) // delta) % (2 * p) for v in nz], dtype=np.int64)
         bad = int(np.count_nonzero(dec != want_msgs))
         failures += bad
         total += B
-        e = centred(noisy, want_msgs.astype(np.uint64) * np.uint64(delta), O.Q)
+        e = centred(noisy, want_msgs.astype(np.uint64) * np.uint64(delta), q)
         noise_sum += float(e.sum())
         noise_sq += float((e * e).sum())
         noise_max = max(noise_max, float(np.abs(e).max()))
-        ns = args.oracle_sample
+        ns = oracle_sample
         if ns:
-            want_ct, _ = ctx.pbs_batch(cts[:ns], tvs, idx[:ns])
-            assert np.array_equal(out[:ns], want_ct), f"round {r}: GPU PBS differs from the oracle"
-            exact_checked += ns
-        print(f"round {r + 1}/{rounds}: {B} PBS, {bad} wrong decryptions, running std "
-              f"{math.sqrt(max(noise_sq / total - (noise_sum / total) ** 2, 0)):.3e} q", file=sys.stderr, flush=True)
+            pick = np.unique(np.concatenate([[0, B - 1], rs.randint(0, B, ns)]))
+            want_ct, _ = side.oracle_pbs(cts[pick], tvs, idx[pick])
+            assert np.array_equal(out[pick], want_ct), f"round {r}: GPU PBS differs from the oracle"
+            exact_checked += len(pick)
+        if verbose:
+            print(f"round {r + 1}/{rounds}: {B} PBS, {bad} wrong decryptions, running std "
+                  f"{math.sqrt(max(noise_sq / total - (noise_sum / total) ** 2, 0)):.3e} q", file=sys.stderr, flush=True)
         cts, msgs = out, dec
     var = noise_sq / total - (noise_sum / total) ** 2
     # decoding fails when |noise| > delta/2 = q/64; p_fail <= 2^-128 (the set's claim) needs
     # sigma <= (1/64) / z with erfc(z / sqrt 2) = 2^-128, z = 13.11
     z = 13.11
     bound_std = (1.0 / 64.0) / z
-    res = {
-        "workload": "S2 shape (n=918, N=2048, k=1, ell=1), 4-bit messages + padding bit, Goldilocks exact NTT",
-        "trials": total, "wrong_decryptions": failures, "rounds": rounds, "chunk": B, "luts": len(luts),
+    return {
+        "workload": side.workload + ", 4-bit messages + padding bit, outputs chained into the next round",
+        "arith": arith, "trials": total, "wrong_decryptions": failures, "rounds": rounds, "chunk": B, "luts": len(luts),
         "bit_exact_vs_oracle_checked": exact_checked,
         "output_noise_std_over_q": math.sqrt(max(var, 0.0)), "output_noise_var_over_q2": var,
         "output_noise_max_over_q": noise_max, "decode_margin_over_q": 1.0 / 64.0,
         "bound_std_over_q_for_pfail_2^-128": bound_std, "variance_within_bound": bool(var <= bound_std ** 2),
-        "sigma_glwe": sig_glwe, "sigma_lwe": sig_lwe,
         "seconds": {"encrypt_cpu": t_enc, "gpu_pbs_calls_wall": t_gpu},
         "pbs_per_s_through_host_abi": total / t_gpu if t_gpu else None,
     }
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--arith", default="torus", choices=["torus", "goldilocks"])
+    ap.add_argument("--trials", type=int, default=1 << 20)
+    ap.add_argument("--chunk", type=int, default=1 << 16)
+    ap.add_argument("--oracle-sample", type=int, default=8, help="outputs per round compared bit-exactly with the oracle")
+    ap.add_argument("--out", default="gpurun_out/decrypt_trials.json")
+    args = ap.parse_args()
+    res = run(args.arith, args.trials, args.chunk, args.oracle_sample)
     Path(args.out).parent.mkdir(parents=True, exist_ok=True)
     Path(args.out).write_text(json.dumps(res, indent=1))
     print(json.dumps(res))
-    if failures:
+    if res["wrong_decryptions"]:
         sys.exit(1)
 
 

@@ -210,3 +210,22 @@ def test_pbs_s2_bit_exact_across_the_batch(rig_s2):
     assert np.array_equal(got[pick], want), "ciphertext words differ from oracle/torus.c"
     err = np.array([TO.centered_diff(int(v), (int(w) * dl) % 2**64) for v, w in zip(noisy, want_dec)])
     assert err.std() < 2.0**-12, err.std()     # measured 2^-14.7; a failed transform would be ~2^-2
+
+
+# ------------------------------------------------------------------------------------------- the decryption gate
+@pytest.mark.parametrize("arith", ["torus", "goldilocks"])
+def test_decryption_gate_65536_trials(arith):
+    """north_star correctness bullet 3 in the driver-run suite: 65,536 chained bootstraps of encrypted 4-bit messages at
+    the named set (4 rounds, each round's outputs are the next round's inputs), zero wrong decryptions, measured output
+    noise variance within the bound p_fail <= 2^-128 needs; samples of every round bit-exact vs the oracle.
+    (scripts/decrypt_trials.py runs the same gate at >= 10^6 trials: profiles/r02_decrypt_trials_*.json)"""
+    import importlib.util
+    from pathlib import Path
+
+    spec = importlib.util.spec_from_file_location("decrypt_trials", Path(__file__).resolve().parent.parent / "scripts" / "decrypt_trials.py")
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    res = mod.run(arith, trials=65536, chunk=16384, oracle_sample=6, verbose=False)
+    assert res["trials"] == 65536 and res["wrong_decryptions"] == 0, res
+    assert res["variance_within_bound"], res
+    assert res["bit_exact_vs_oracle_checked"] >= 4 * 6

@@ -89,6 +89,25 @@ __global__ void __launch_bounds__(256) int_peak_kernel(u64 *sink, u32 iters, u64
     if (acc == 0x1234567) sink[0] = acc;
 }
 
+// FP64 pipe peak: 16 independent DFMA chains per thread, register-only (the denominator of the torus arithmetic's roofline)
+__global__ void __launch_bounds__(256) fp64_peak_kernel(double *sink, u32 iters, double seed) {
+    double x[16];
+    const double a = 1.0 + 1e-9 * (double)threadIdx.x, b = seed * 1e-9;
+#pragma unroll
+    for (int i = 0; i < 16; i++) x[i] = seed + i + blockIdx.x;
+    for (u32 it = 0; it < iters; it++) {
+#pragma unroll
+        for (int r = 0; r < 4; r++) {
+#pragma unroll
+            for (int i = 0; i < 16; i++) x[i] = __fma_rn(x[i], a, b);
+        }
+    }
+    double acc = 0;
+#pragma unroll
+    for (int i = 0; i < 16; i++) acc += x[i];
+    if (acc == 0.12345) sink[0] = acc;
+}
+
 // any power-of-two N in [8, 2048]: one CTA per polynomial, one thread per butterfly, textbook
 // stage loop in shared memory (crypto/poly.rs:9-64).  Parity utility for the small golden vectors.
 __global__ void ntt_any_kernel(const u64 *in, u64 *out, const u64 *tw, u64 scale, u32 N, u32 inverse) {
@@ -1116,6 +1135,28 @@ int lux_debug_int_peak(lux_engine *e, double out[3]) {
         const double per_thread = (double)iters * 8 * (kind == 0 ? 8 : kind == 1 ? 16 : 4);
         out[kind] = per_thread * grid * 256 / (best * 1e-3);
     }
+    return LUX_OK;
+}
+
+// out[0] = DFMA lane-operations per second (register-only, whole GPU), measured with CUDA events.
+int lux_debug_fp64_peak(lux_engine *e, double out[1]) {
+    if (!e || !out) return LUX_ERR_INVALID;
+    CUDA_TRY(e, cudaSetDevice(e->device));
+    int rc;
+    if ((rc = ensure_scratch(e, 5, 64))) return rc;
+    const u32 iters = 2048, grid = (u32)e->sm_count * 8;
+    float best = 1e30f;
+    for (int rep = 0; rep < 4; rep++) {
+        CUDA_TRY(e, cudaEventRecord(e->ev[0], e->stream));
+        fp64_peak_kernel<<<grid, 256, 0, e->stream>>>((double *)e->scratch[5], iters, 1.0);
+        e->launches++;
+        CUDA_TRY(e, cudaEventRecord(e->ev[1], e->stream));
+        CUDA_TRY(e, cudaEventSynchronize(e->ev[1]));
+        float ms;
+        CUDA_TRY(e, cudaEventElapsedTime(&ms, e->ev[0], e->ev[1]));
+        if (rep && ms < best) best = ms;
+    }
+    out[0] = (double)iters * 64 * grid * 256 / (best * 1e-3);
     return LUX_OK;
 }
 

@@ -634,6 +634,8 @@ struct LinDesc {
 };
 
 // dst[b] = sum_t coef_t * src_t[b] + konst (added to the body): one CTA per (integer b, descriptor)
+// TORUS: words are elements of Z / 2^64 (wrapping arithmetic) instead of Goldilocks residues
+template <bool TORUS>
 __global__ void __launch_bounds__(256) radix_lin_kernel(const LinDesc *descs, const LinTerm *terms, u32 w) {
     const LinDesc d = descs[blockIdx.y];
     const size_t b = blockIdx.x;
@@ -644,15 +646,19 @@ __global__ void __launch_bounds__(256) radix_lin_kernel(const LinDesc *descs, co
         for (u32 i = 0; i < d.n_terms; i++) {
             const u64 v = t[i].src[b * t[i].stride + word];
             const int c = t[i].coef;
-            const u64 m = gl_mul(v, (u64)(c < 0 ? -c : c));
-            acc = gl_canon(c < 0 ? gl_sub(acc, m) : gl_add(acc, m));
+            if (TORUS) {
+                acc += v * (u64)(long long)c;
+            } else {
+                const u64 m = gl_mul(v, (u64)(c < 0 ? -c : c));
+                acc = gl_canon(c < 0 ? gl_sub(acc, m) : gl_add(acc, m));
+            }
         }
         dst[word] = acc;
     }
 }
 
 // noise-free encryptions: out[b][i] = (0,...,0, ((values[b] >> 2i) & 3) * delta)
-__global__ void radix_trivial_kernel(const u64 *values, u32 nb, u32 w, u64 delta, u64 *out, size_t batch) {
+__global__ void radix_trivial_kernel(const u64 *values, u32 nb, u32 w, u64 delta, u64 *out, size_t batch, bool torus) {
     const size_t total = batch * nb * (size_t)w;
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
         const u32 word = (u32)(i % w);
@@ -660,7 +666,7 @@ __global__ void radix_trivial_kernel(const u64 *values, u32 nb, u32 w, u64 delta
         const u32 blk = (u32)(ct % nb);
         const u64 v = values[ct / nb];
         const u64 digit = (2 * blk < 64) ? ((v >> (2 * blk)) & 3) : 0;
-        out[i] = (word == w - 1) ? gl_mul(digit, delta) : 0;
+        out[i] = (word == w - 1) ? (torus ? digit * delta : gl_mul(digit, delta)) : 0;
     }
 }
 
@@ -694,11 +700,11 @@ int radix_init(lux_engine *e) {
     RadixState *r = new (std::nothrow) RadixState();
     if (!r) LUX_FAIL(e, LUX_ERR_OOM, "out of host memory");
     std::vector<u64> tv((size_t)L_COUNT * N);
-    const u64 delta = lux_delta(2 * RADIX_P);
+    const u64 delta = lux_delta_arith(e->p.arith, 2 * RADIX_P);
     for (int id = 0; id < L_COUNT; id++) {
         u64 lut[16];
         for (int x = 0; x < 16; x++) lut[x] = (u64)lut_eval(id, x);
-        lux_make_testv(N, RADIX_P, delta, lut, tv.data() + (size_t)id * N);
+        lux_make_testv_arith(e->p.arith, N, RADIX_P, delta, lut, tv.data() + (size_t)id * N);
     }
     cudaError_t st = cudaMalloc(&r->d_testvs, sizeof(u64) * tv.size());
     if (st == cudaSuccess) st = cudaMemcpy(r->d_testvs, tv.data(), sizeof(u64) * tv.size(), cudaMemcpyHostToDevice);
@@ -731,7 +737,7 @@ int exec_program(lux_engine *e, const Program &prog, const std::vector<const u64
     if (in.size() != prog.in_blocks.size() || out.size() != prog.out_blocks.size()) LUX_FAIL(e, LUX_ERR_INVALID, "operand count mismatch");
     RadixState *r = e->radix;
     const size_t w = lux_ct_words(e);
-    const u64 delta = lux_delta(2 * RADIX_P);
+    const u64 delta = lux_delta_arith(e->p.arith, 2 * RADIX_P);
     cudaStream_t s = e->stream;
 
     const size_t slots_per_int = prog.n_pbs + prog.max_level_pbs;
@@ -783,7 +789,7 @@ int exec_program(lux_engine *e, const Program &prog, const std::vector<const u64
             d.term_off = (u32)ti;
             d.pad = 0;
             const long km = ((v.k % 32) + 32) % 32;
-            d.konst = gl_mul((u64)km, delta);
+            d.konst = lux_is_torus(e) ? (u64)km * delta : gl_mul((u64)km, delta);
             for (auto &x : v.t) {
                 LinTerm &t = terms[ti++];
                 if (x.slot < prog.n_in_slots) {
@@ -812,7 +818,10 @@ int exec_program(lux_engine *e, const Program &prog, const std::vector<const u64
         size_t d_off = 0, l_off = 0;
         for (auto &lv : prog.levels) {
             if (lv.empty()) continue;
-            radix_lin_kernel<<<dim3((unsigned)bcur, (unsigned)lv.size()), 256, 0, s>>>(d_descs + d_off, d_terms, (u32)w);
+            if (lux_is_torus(e))
+                radix_lin_kernel<true><<<dim3((unsigned)bcur, (unsigned)lv.size()), 256, 0, s>>>(d_descs + d_off, d_terms, (u32)w);
+            else
+                radix_lin_kernel<false><<<dim3((unsigned)bcur, (unsigned)lv.size()), 256, 0, s>>>(d_descs + d_off, d_terms, (u32)w);
             e->launches++;
             CUDA_TRY(e, cudaGetLastError());
             u64 *lv_out = pool + (size_t)prog.slot_pos[lv[0].out] * bcur * w;
@@ -823,7 +832,10 @@ int exec_program(lux_engine *e, const Program &prog, const std::vector<const u64
         const size_t n_out_desc = n_desc - d_off;
         if (n_out_desc) {
             // outputs may have different block counts per operand; descriptors carry their own strides
-            radix_lin_kernel<<<dim3((unsigned)bcur, (unsigned)n_out_desc), 256, 0, s>>>(d_descs + d_off, d_terms, (u32)w);
+            if (lux_is_torus(e))
+                radix_lin_kernel<true><<<dim3((unsigned)bcur, (unsigned)n_out_desc), 256, 0, s>>>(d_descs + d_off, d_terms, (u32)w);
+            else
+                radix_lin_kernel<false><<<dim3((unsigned)bcur, (unsigned)n_out_desc), 256, 0, s>>>(d_descs + d_off, d_terms, (u32)w);
             e->launches++;
             CUDA_TRY(e, cudaGetLastError());
         }
@@ -968,7 +980,7 @@ int lux_trivial_encrypt(lux_engine *e, unsigned bw, const uint64_t *values, size
         if ((rc = lux_ensure_scratch(e, 1, sizeof(u64) * batch))) return rc;
         if ((rc = lux_ensure_scratch(e, 2, sizeof(u64) * words))) return rc;
         CUDA_TRY(e, cudaMemcpyAsync(e->scratch[1], values, sizeof(u64) * batch, cudaMemcpyHostToDevice, e->stream));
-        radix_trivial_kernel<<<e->sm_count * 8, 256, 0, e->stream>>>((const u64 *)e->scratch[1], (u32)nb, (u32)w, lux_delta(2 * RADIX_P), (u64 *)e->scratch[2], batch);
+        radix_trivial_kernel<<<e->sm_count * 8, 256, 0, e->stream>>>((const u64 *)e->scratch[1], (u32)nb, (u32)w, lux_delta_arith(e->p.arith, 2 * RADIX_P), (u64 *)e->scratch[2], batch, lux_is_torus(e));
         e->launches++;
         CUDA_TRY(e, cudaGetLastError());
         CUDA_TRY(e, cudaMemcpyAsync(out, e->scratch[2], sizeof(u64) * words, cudaMemcpyDeviceToHost, e->stream));
@@ -1016,7 +1028,7 @@ static int eval_scalar_impl(lux_engine *e, lux_op op, unsigned bw, const uint64_
         u64 *d_l = (u64 *)e->scratch[1], *d_r = (u64 *)e->scratch[3], *d_sc = d_r + words, *d_o = (u64 *)e->scratch[2];
         CUDA_TRY(e, cudaMemcpyAsync(d_l, lhs, sizeof(u64) * words, cudaMemcpyHostToDevice, e->stream));
         CUDA_TRY(e, cudaMemcpyAsync(d_sc, scalars, sizeof(u64) * batch, cudaMemcpyHostToDevice, e->stream));
-        radix_trivial_kernel<<<e->sm_count * 8, 256, 0, e->stream>>>(d_sc, (u32)nb, (u32)w, lux_delta(2 * RADIX_P), d_r, batch);
+        radix_trivial_kernel<<<e->sm_count * 8, 256, 0, e->stream>>>(d_sc, (u32)nb, (u32)w, lux_delta_arith(e->p.arith, 2 * RADIX_P), d_r, batch, lux_is_torus(e));
         e->launches++;
         CUDA_TRY(e, cudaGetLastError());
         if ((rc = exec_program(e, p, {d_l, d_r}, {d_o}, batch))) return rc;

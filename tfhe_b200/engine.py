@@ -169,6 +169,9 @@ def lib():
         if hasattr(L, "lux_debug_int_peak"):
             L.lux_debug_int_peak.argtypes = [_vp, C.POINTER(C.c_double * 3)]
             L.lux_debug_int_peak.restype = _int
+        if hasattr(L, "lux_debug_fp64_peak"):
+            L.lux_debug_fp64_peak.argtypes = [_vp, C.POINTER(C.c_double * 1)]
+            L.lux_debug_fp64_peak.restype = _int
         if hasattr(L, "lux_debug_field_probe"):
             L.lux_debug_field_probe.argtypes = [_vp, _u64p, _u64p, _sz, _u64p]
             L.lux_debug_field_probe.restype = _int
@@ -329,6 +332,12 @@ class Engine:
         buf = (C.c_double * 3)()
         self._ck(lib().lux_debug_int_peak(self._h, C.byref(buf)))
         return float(buf[0]), float(buf[1]), float(buf[2])
+
+    def fp64_peak(self) -> float:
+        """measured FP64-pipe rate of this GPU: DFMA lane-operations per second (register-only)"""
+        buf = (C.c_double * 1)()
+        self._ck(lib().lux_debug_fp64_peak(self._h, C.byref(buf)))
+        return float(buf[0])
 
     def field_probe(self, a, b):
         """device field arithmetic on raw words: rows = a+b, a-b, a*b, CT butterfly (2), GS butterfly (2)"""
