@@ -660,8 +660,8 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--batch", type=int, default=4440,
-                    help="ciphertexts per GPU per step (default 4,440 = 10 full waves of 148 SMs x 3 resident ciphertexts, torus kernel)")
+    ap.add_argument("--batch", type=int, default=4736,
+                    help="ciphertexts per GPU per step (default 4,736 = 8 full waves of 148 SMs x 4 resident ciphertexts, torus kernel)")
     ap.add_argument("--arith", default="torus", choices=["torus", "goldilocks"],
                     help="torus: 2^64 torus / f64 FFT (the named set's arithmetic, default); goldilocks: exact NTT (in-tree reference arithmetic)")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],

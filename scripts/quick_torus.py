@@ -1,13 +1,13 @@
 """Quick device-resident timing of the torus/f64-FFT PBS at S2 (random key words: throughput is data independent).
-usage: python scripts/quick_torus.py [B] [teams...]"""
-import sys, time
+usage: python scripts/quick_torus.py [B] [cfg...]     cfg = teams + 10 * variant [":" stagger_ns]"""
+import os, sys, time
 from pathlib import Path
 sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
 import numpy as np, torch
 import tfhe_b200 as T
 
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 4440
-teams_list = [int(x) for x in sys.argv[2:]] or [0]   # teams + 10 * variant
+teams_list = sys.argv[2:] or ["0"]   # teams + 10 * variant [: stagger ns]
 p = T.S2_TORUS
 eng = T.Engine(p)
 rs = np.random.RandomState(1)
@@ -20,7 +20,10 @@ d_idx = torch.from_numpy((np.arange(B) % 4).astype(np.int32)).cuda()
 d_out = torch.empty_like(d_in)
 s = torch.cuda.Stream(); torch.cuda.set_stream(s)
 eng.set_timing(True)
-for t in teams_list:
+for spec in teams_list:
+    t = int(spec.split(":")[0])
+    if ":" in spec:
+        eng.fft_stagger(int(spec.split(":")[1]))
     eng.force_teams(t % 10)
     eng.fft_variant(t // 10)
     for _ in range(2):
@@ -31,5 +34,12 @@ for t in teams_list:
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record(s); eng.pbs_batch_device(d_in, d_tv, d_idx, B, d_out, n_luts=4, stream=s.cuda_stream); b.record(s); b.synchronize()
         ms.append(a.elapsed_time(b))
+    if os.environ.get("FFT64_TRACE"):
+        eng.fft_trace()
+        eng.pbs_batch_device(d_in, d_tv, d_idx, B, d_out, n_luts=4, stream=s.cuda_stream)
+        tr = eng.fft_trace()
+        names = ["decompose", "fwd pass A", "transpose", "fwd pass B", "swap+bar", "key MAC", "bar", "inv pass B", "transpose", "inv pass A", "update"]
+        per = [v / (2 * B * p.n) for v in tr[:11]]        # cycles per warp-iteration
+        print("   phase cycles per warp-iteration: " + ", ".join(f"{n} {v:.0f}" for n, v in zip(names, per)) + f"  | total {sum(per):.0f}", flush=True)
     ks, br = eng.last_timing()
-    print(f"B={B} teams={t} wave={eng.wave_ciphertexts(B)}: {min(ms):.2f} ms best, {B/min(ms)*1e3:.0f} PBS/s  (ks {ks:.2f} ms, br {br:.2f} ms)", flush=True)
+    print(f"B={B} cfg={spec} wave={eng.wave_ciphertexts(B)}: {min(ms):.2f} ms best, {B/min(ms)*1e3:.0f} PBS/s  (ks {ks:.2f} ms, br {br:.2f} ms)", flush=True)

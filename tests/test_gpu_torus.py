@@ -148,12 +148,14 @@ def test_blind_rotate_per_iteration_bit_exact(rig_small, steps):
     assert np.array_equal(got, want), f"accumulators differ after {steps} CMUX steps"
 
 
-@pytest.mark.parametrize("teams", [1, 2, 3])
+@pytest.mark.parametrize("teams", [1, 2, 3, 13, 4, 14, 24, 34])
 def test_pbs_small_bit_exact_every_team_count(rig_small, teams):
     """whole PBS (key switch, blind rotation, extraction) against the oracle, every ciphertext of a ragged batch,
     for each ciphertexts-per-CTA configuration of the kernel (ring depth and stage size differ between them)"""
     e, p, ks = rig_small.eng, rig_small.p, rig_small.ks
+    teams, variant = teams % 10, teams // 10      # tens digit: ring depth / twiddle placement variant of the kernel
     e.force_teams(teams)
+    e.fft_variant(variant)
     try:
         dl = T.delta(32, p.arith)
         lut = [(x * x + 1) % 16 for x in range(16)]
@@ -168,6 +170,7 @@ def test_pbs_small_bit_exact_every_team_count(rig_small, teams):
         assert dec == [lut[int(m)] for m in msgs]
     finally:
         e.force_teams(0)
+        e.fft_variant(0)
 
 
 def test_pbs_order2_bit_exact(rig_small_o2):

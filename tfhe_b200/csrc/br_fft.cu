@@ -7,10 +7,10 @@
 
 using namespace fft64;
 
-template <int TEAMS, int NS, int RS, int TWS>
-__global__ void __launch_bounds__(Cfg<TEAMS, NS, RS, TWS>::THREADS, 1) blind_rotate_fft_kernel(const __grid_constant__ Args a) {
+template <int TEAMS, int NS, int RS, int TWS, int HB = 0, int GROUPS = 1, int KL = 0>
+__global__ void __launch_bounds__(Cfg<TEAMS, NS, RS, TWS, HB, GROUPS, KL>::THREADS, 1) blind_rotate_fft_kernel(const __grid_constant__ Args a) {
     extern __shared__ __align__(16) unsigned char smem[];
-    blind_rotate_body<TEAMS, NS, RS, TWS>(a, smem);
+    blind_rotate_body<TEAMS, NS, RS, TWS, HB, GROUPS, KL>(a, smem);
 }
 
 constexpr int UTIL_WARPS = 4;
@@ -86,42 +86,53 @@ static void fill_tables(const lux_engine *e, Args &a) {
     for (int v = 0; v < 32; v++) a.twA[v] = make_double2(e->fft_twA[2 * v], e->fft_twA[2 * v + 1]);
 }
 
-template <int TEAMS, int NS, int RS, int TWS>
+template <int TEAMS, int NS, int RS, int TWS, int HB = 0, int GROUPS = 1, int KL = 0>
 static int launch_cfg(lux_engine *e, const Args &a, cudaStream_t s) {
-    using C = Cfg<TEAMS, NS, RS, TWS>;
+    using C = Cfg<TEAMS, NS, RS, TWS, HB, GROUPS, KL>;
+    static_assert(C::SMEM <= 232448, "configuration exceeds the 227 KiB of shared memory a CTA can opt into");
     static bool configured[64] = {};
     if (!configured[e->device & 63]) {
-        CUDA_TRY(e, cudaFuncSetAttribute(blind_rotate_fft_kernel<TEAMS, NS, RS, TWS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM));
+        CUDA_TRY(e, cudaFuncSetAttribute(blind_rotate_fft_kernel<TEAMS, NS, RS, TWS, HB, GROUPS, KL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM));
         configured[e->device & 63] = true;
     }
     const unsigned grid = (a.B + TEAMS - 1) / TEAMS;
-    blind_rotate_fft_kernel<TEAMS, NS, RS, TWS><<<grid, C::THREADS, C::SMEM, s>>>(a);
+    blind_rotate_fft_kernel<TEAMS, NS, RS, TWS, HB, GROUPS, KL><<<grid, C::THREADS, C::SMEM, s>>>(a);
     e->launches++;
     CUDA_TRY(e, cudaGetLastError());
     return LUX_OK;
 }
 
-// ciphertexts per CTA: 3 (ring of 2 x 8 KiB, teams in lock step at the key rows) or 2 (ring = one whole GGSW)
+// Ciphertexts per CTA.  Measured on B200 at the named set (profiles/r02b_fft_phase_cycles.txt), cycles per CMUX iteration of a
+// CTA: 1 team 17.0k, 2 teams 15.3k, 3 teams 19.2k, 4 teams (half-size buffers) 22.5k.  A batch runs in
+// ceil(B / (teams x SMs)) waves, so the choice minimises waves x cycles; tiny batches spread over the SMs first.
 static int pick_teams(const lux_engine *e, size_t B) {
-    if (e->force_teams >= 1 && e->force_teams <= 3) return e->force_teams;
+    if (e->force_teams >= 1 && e->force_teams <= 4) return e->force_teams;
     const size_t sms = (size_t)e->sm_count;
     if (B <= sms) return 1;
     if (B <= 2 * sms) return 2;
-    return e->fft_default_teams;
+    const double c3 = (double)((B + 3 * sms - 1) / (3 * sms)) * 19.2, c4 = (double)((B + 4 * sms - 1) / (4 * sms)) * 22.5;
+    return c3 < c4 ? 3 : 4;
 }
 
 size_t lux_fft_wave(const lux_engine *e, size_t B) { return (size_t)e->sm_count * pick_teams(e, B); }
 
+// template arguments: <teams, ring stages, key rows per stage, twiddles in shared memory, half-size buffers, groups, no ring>
 int lux_fft_launch_br(lux_engine *e, Args a, cudaStream_t s) {
     fill_tables(e, a);
-    const int variant = e->fft_variant;
+    a.stagger_ns = (u32)e->fft_stagger_ns;
+    a.trace = (u64 *)e->d_fft_trace;
+    const int variant = e->fft_variant;   // 0 = the default of each team count; the others are the measured alternatives
     switch (pick_teams(e, a.B)) {
         case 1: return launch_cfg<1, 4, 8, 1>(e, a, s);
         case 2: return launch_cfg<2, 4, 8, 1>(e, a, s);
-        default:
-            if (variant == 1) return launch_cfg<3, 2, 4, 1>(e, a, s);
-            if (variant == 2) return launch_cfg<3, 3, 4, 1>(e, a, s);
+        case 3:
+            if (variant == 1) return launch_cfg<3, 8, 4, 1, 1>(e, a, s);      // half-size buffers, ring = one whole GGSW
             return launch_cfg<3, 4, 4, 0>(e, a, s);
+        default:
+            if (variant == 1) return launch_cfg<4, 3, 4, 1, 1>(e, a, s);      // twiddles in shared memory, ring 3 x 8 KiB
+            if (variant == 2) return launch_cfg<4, 1, 4, 1, 1, 1, 1>(e, a, s);   // no ring: key rows straight from L2 / L1
+            if (variant == 3) return launch_cfg<4, 2, 4, 0, 1, 2>(e, a, s);   // two independent groups, ring 2 x 8 KiB each
+            return launch_cfg<4, 4, 4, 0, 1>(e, a, s);                        // ring 4 x 8 KiB, twiddles through L1
     }
 }
 

@@ -619,6 +619,24 @@ int lux_debug_fft_variant(lux_engine *e, int variant) {
     e->fft_variant = variant;
     return LUX_OK;
 }
+int lux_debug_fft_stagger(lux_engine *e, int ns) {
+    if (!e || ns < 0) return LUX_ERR_INVALID;
+    e->fft_stagger_ns = ns;
+    return LUX_OK;
+}
+// returns the phase-cycle counters accumulated since the previous call and clears them (first call: allocates, enables)
+int lux_debug_fft_trace(lux_engine *e, unsigned long long out[16]) {
+    if (!e || !out) return LUX_ERR_INVALID;
+    CUDA_TRY(e, cudaSetDevice(e->device));
+    if (!e->d_fft_trace) {
+        CUDA_TRY(e, cudaMalloc(&e->d_fft_trace, 16 * sizeof(u64)));
+        CUDA_TRY(e, cudaMemset(e->d_fft_trace, 0, 16 * sizeof(u64)));
+    }
+    CUDA_TRY(e, cudaDeviceSynchronize());
+    CUDA_TRY(e, cudaMemcpy(out, e->d_fft_trace, 16 * sizeof(u64), cudaMemcpyDeviceToHost));
+    CUDA_TRY(e, cudaMemset(e->d_fft_trace, 0, 16 * sizeof(u64)));
+    return LUX_OK;
+}
 int lux_debug_cluster_regs(lux_engine *e, int regs) {
     if (!e || (regs != 0 && regs != 4 && regs != 8 && regs != 16)) return LUX_ERR_INVALID;
     e->cluster_regs = regs;

@@ -55,6 +55,8 @@ struct lux_engine {
     double fft_twA[64] = {};
     void *d_fft_twB = nullptr;
     int fft_default_teams = 3;
+    void *d_fft_trace = nullptr;  // 16 phase-cycle counters (FFT64_TRACE_BUILD builds; lux_debug_fft_trace)
+    int fft_stagger_ns = 6000;    // start delay between the groups of a CTA (kernels with GROUPS > 1)
     int fft_variant = 0;          // tuning: ring depth / twiddle placement of the 3-ciphertext kernel (br_fft.cu)
     struct RadixState *radix = nullptr;  // euintN layer (radix.cu), created on first use
     char err[512] = "";
@@ -74,6 +76,8 @@ extern "C" int lux_debug_generic_gadget(lux_engine *e, int on);
 extern "C" int lux_debug_cluster_regs(lux_engine *e, int regs);
 extern "C" int lux_debug_br_regs(lux_engine *e, int regs);
 extern "C" int lux_debug_fft_variant(lux_engine *e, int variant);
+extern "C" int lux_debug_fft_stagger(lux_engine *e, int ns);
+extern "C" int lux_debug_fft_trace(lux_engine *e, unsigned long long out[16]);
 extern "C" int lux_debug_int_peak(lux_engine *e, double out[3]);
 extern "C" int lux_debug_field_probe(lux_engine *e, const uint64_t *a, const uint64_t *b, size_t count, uint64_t *out);
 

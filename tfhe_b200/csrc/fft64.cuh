@@ -48,6 +48,8 @@ struct Args {
     u64 *out;               // out_mode 0: [B][N+1] sample extract; 2: [B][2N] raw accumulator
     const double2 *twB;     // [TWB_ENTRIES] pass-B table (global; copied to shared memory)
     u64 body_add;
+    u32 stagger_ns;         // GROUPS > 1: start delay of group g is g * stagger_ns
+    u64 *trace;             // phase-cycle counters (FFT64_TRACE_BUILD) or nullptr
     double2 twA[32];        // tree nodes 1..31: the warp-uniform twiddles of pass A
 };
 
@@ -71,6 +73,14 @@ __device__ __forceinline__ int digit1(u64 x, u32 logB) {
     const u32 res = (((hi >> (31 - logB)) + 1u) >> 1) & ((1u << logB) - 1u);
     const u32 carry = ((res - 1u) & res) >> (logB - 1);
     return (int)res - (int)(carry << logB);
+}
+// the same digit from the high word of x, as the double the transform consumes: with half = 2^(31-logB),
+// (int)(hi - half) >> (32 - logB) is the balanced digit minus one (the wrap of the 32-bit word is the reduction mod B,
+// the arithmetic shift the sign extension; tor_decompose maps B/2 to +B/2, hence the shift by one); the +1 is folded into
+// the exact int -> double constant.  Three integer instructions and one DADD instead of ten and one.
+__device__ __forceinline__ double digit1_double(u32 hi, u32 half, u32 sh) {
+    const int dm1 = (int)(hi - half) >> sh;
+    return __dsub_rn(__hiloint2double(0x43300000, dm1 ^ 0x80000000), 4503601774854143.0);   // 2^52 + 2^31 - 1
 }
 // round(x 2N / 2^64) in [0, 2N]      crypto/lwe.rs:28-34
 __device__ __forceinline__ u32 mod_switch(u64 x) {
@@ -119,8 +129,13 @@ __device__ __forceinline__ void bfly(double2 &u, double2 &v, double wr, double w
 #ifndef FFT64_GROUP
 #define FFT64_GROUP 4
 #endif
+// FFT64_ABLATE (timing experiments only, results are meaningless): bit 0 drops the butterflies, bit 1 the transposes
+#ifndef FFT64_ABLATE
+#define FFT64_ABLATE 0
+#endif
 template <bool INV, int G>
 __device__ __forceinline__ void bfly_group(double2 (&x)[32], const int (&iu)[G], const int (&iv)[G], const double (&wr)[G], const double (&wi)[G]) {
+    if (FFT64_ABLATE & 1) return;
     if (!INV) {
         double tr[G], ti[G];
 #pragma unroll
@@ -192,15 +207,17 @@ __device__ __forceinline__ void pass_a(double2 (&x)[32], const Args &a) {
     }
 }
 // pass B: tree levels m = 32 g, g = 1..16, on the row layout; lane r owns nodes m + r g + b, b < g
-template <bool INV, int GI>
+// butterflies [B0, B1) of the 16 of one stage: for g >= 2 the rows 0..15 (butterflies 0..7) and 16..31 (8..15) are independent
+template <bool INV, int GI, int B0 = 0, int B1 = 16>
 __device__ __forceinline__ void pass_b_stage(double2 (&y)[32], const double2 *twB, int lane) {
-    constexpr int G = FFT64_GROUP;
+    constexpr int G = FFT64_GROUP < (B1 - B0) ? FFT64_GROUP : (B1 - B0);
     constexpr int g = 1 << GI, t = 16 >> GI, NW = g >= 2 ? g / 2 : 1;
+    constexpr int E0 = (B0 / t) / 2, E1 = ((B1 - 1) / t) / 2 + 1;
     double2 w[NW];
 #pragma unroll
-    for (int e = 0; e < NW; e++) w[e] = twB[(g == 1 ? 0 : 16 * g) + e * 32 + lane];
+    for (int e = E0; e < E1; e++) w[e] = twB[(g == 1 ? 0 : 16 * g) + e * 32 + lane];
 #pragma unroll
-    for (int b0 = 0; b0 < 16; b0 += G) {
+    for (int b0 = B0; b0 < B1; b0 += G) {
         int iu[G], iv[G];
         double wr[G], wi[G];
 #pragma unroll
@@ -235,6 +252,14 @@ __device__ __forceinline__ void pass_b(double2 (&y)[32], const double2 *twB, int
         pass_b_stage<true, 0>(y, twB, lane);
     }
 }
+// inverse pass B without its last stage, on rows 16 H .. 16 H + 15 only (the key MAC of the other half can still be pending)
+template <int H>
+__device__ __forceinline__ void pass_b_inv_half(double2 (&y)[32], const double2 *twB, int lane) {
+    pass_b_stage<true, 4, 8 * H, 8 * H + 8>(y, twB, lane);
+    pass_b_stage<true, 3, 8 * H, 8 * H + 8>(y, twB, lane);
+    pass_b_stage<true, 2, 8 * H, 8 * H + 8>(y, twB, lane);
+    pass_b_stage<true, 1, 8 * H, 8 * H + 8>(y, twB, lane);
+}
 // transposes through the warp's padded buffer
 __device__ __forceinline__ void col_to_row(double2 (&x)[32], double2 *buf, int lane) {
 #pragma unroll
@@ -250,45 +275,97 @@ __device__ __forceinline__ void row_to_col(double2 (&y)[32], double2 *buf, int l
 #pragma unroll
     for (int i = 0; i < 32; i++) y[i] = buf[i * ROWP + lane];
 }
+// half-size buffer (HB): the real parts cross first, then the imaginary parts, through 32 x 33 doubles (8,448 B per warp
+// instead of 16,896): same bytes through the crossbar, twice the instructions; this is what lets FOUR ciphertexts (eight
+// consumer warps, two on every scheduler) live in one CTA's shared memory.  Conflict-free both ways (row stride 33 doubles).
+constexpr int ROWD = 33;
+constexpr int HBUF_BYTES = 32 * ROWD * 8;
+__device__ __forceinline__ void col_to_row_h(double2 (&x)[32], double *b, int lane) {
+    if (FFT64_ABLATE & 2) return;
+#pragma unroll
+    for (int i = 0; i < 32; i++) b[i * ROWD + lane] = x[i].x;
+    __syncwarp();
+#pragma unroll
+    for (int i = 0; i < 32; i++) x[i].x = b[lane * ROWD + i];
+    __syncwarp();
+#pragma unroll
+    for (int i = 0; i < 32; i++) b[i * ROWD + lane] = x[i].y;
+    __syncwarp();
+#pragma unroll
+    for (int i = 0; i < 32; i++) x[i].y = b[lane * ROWD + i];
+}
+__device__ __forceinline__ void row_to_col_h(double2 (&y)[32], double *b, int lane) {
+    if (FFT64_ABLATE & 2) return;
+#pragma unroll
+    for (int i = 0; i < 32; i++) b[lane * ROWD + i] = y[i].x;
+    __syncwarp();
+#pragma unroll
+    for (int i = 0; i < 32; i++) y[i].x = b[i * ROWD + lane];
+    __syncwarp();
+#pragma unroll
+    for (int i = 0; i < 32; i++) b[lane * ROWD + i] = y[i].y;
+    __syncwarp();
+#pragma unroll
+    for (int i = 0; i < 32; i++) y[i].y = b[i * ROWD + lane];
+}
 // forward: column layout in (z[lane + 32 i]), row layout out (Z[32 lane + i], oracle index order)
+template <int HB = 0>
 __device__ __forceinline__ void fft_forward(double2 (&x)[32], double2 *buf, const double2 *twB, const Args &a, int lane) {
     pass_a<false>(x, a);
-    col_to_row(x, buf, lane);
+    if (HB)
+        col_to_row_h(x, (double *)buf, lane);
+    else
+        col_to_row(x, buf, lane);
     pass_b<false>(x, twB, lane);
 }
 // inverse (unnormalised): row layout in, column layout out
+template <int HB = 0>
 __device__ __forceinline__ void fft_inverse(double2 (&y)[32], double2 *buf, const double2 *twB, const Args &a, int lane) {
     pass_b<true>(y, twB, lane);
-    row_to_col(y, buf, lane);
+    if (HB)
+        row_to_col_h(y, (double *)buf, lane);
+    else
+        row_to_col(y, buf, lane);
     pass_a<true>(y, a);
 }
 
 // ------------------------------------------------------------------------------------------ blind rotation
 // ring stage = RS rows of the GGSW: [RS][4 polys][32 lanes] double2 = RS * 2 KiB
 // TWS: pass-B twiddle table in shared memory (1) or read from global memory through L1 (0: the 8 KiB go to the key ring)
-template <int TEAMS, int NS, int RS, int TWS = 1>
+// HB: half-size per-warp buffers (transposes in two rounds, spectrum swap in two rounds of 16 rows)
+// GROUPS: the CTA's teams form GROUPS independent groups, each with its own key ring (NS stages), its own producer warp
+// and a staggered start: the groups are never in the same phase of the CMUX, so the integer (decompose), FP64 (butterflies)
+// and shared-memory (transposes) phases of one group overlap other phases of the other group instead of queueing on one pipe
+// (profiles/r02b_overlap_ubench.txt: the FP64 and shared-memory pipes run concurrently at full rate when both have work).
+// KL: no key ring at all: every warp loads its key rows straight from L2 / L1 (ld.global.nc) into registers.  Nothing then
+// couples the teams of a CTA (no shared ring, no producer warp, no mbarriers): they drift out of phase and the integer,
+// FP64 and shared-memory phases of different teams overlap.  Costs TEAMS x the L2 -> SM key traffic of the ring.
+template <int TEAMS, int NS, int RS, int TWS = 1, int HB = 0, int GROUPS = 1, int KL = 0>
 struct Cfg {
     static constexpr int CONSUMER_WARPS = 2 * TEAMS;
-    static constexpr int THREADS = 32 * (CONSUMER_WARPS + 1);
+    static constexpr int THREADS = 32 * (CONSUMER_WARPS + (KL ? 0 : GROUPS));
+    static constexpr int TEAMS_PER_GROUP = TEAMS / GROUPS;
     static constexpr int STAGE_POINTS = RS * 4 * 32;
     static constexpr int STAGES_PER_GGSW = 32 / RS;
+    static constexpr int WARP_BUF_POINTS = HB ? HBUF_BYTES / 16 : BUF_POINTS;   // in double2 units
     static constexpr size_t SMEM =
-        sizeof(double2) * TWB_ENTRIES * TWS + (size_t)TEAMS * (sizeof(u64) * 2 * N + sizeof(double2) * 2 * BUF_POINTS) +
-        sizeof(double2) * (size_t)NS * STAGE_POINTS + sizeof(u64) * 2 * NS + 16;
+        sizeof(double2) * TWB_ENTRIES * TWS + (size_t)TEAMS * (sizeof(u64) * 2 * N + sizeof(double2) * 2 * WARP_BUF_POINTS) +
+        (KL ? 0 : sizeof(double2) * (size_t)GROUPS * NS * STAGE_POINTS + sizeof(u64) * 2 * NS * GROUPS) + 16;
 };
 
 // multiply-accumulate of the swapped spectra with the staged key rows: out = X0 K[0][r] + X1 K[1][r], in the oracle's order;
 // the RS rows of a stage advance together, one fused multiply-add of each chain at a time
-template <int R, int RS>
+// HB: the partner's rows sit as [row - 16 * (row0 / 16)][lane] (half-size buffer, two rounds of 16 rows)
+template <int R, int RS, int HB = 0, int KG = 0>
 __device__ __forceinline__ void mac_rows(double2 (&y)[32], const double2 *oth, const double2 *stage, int row0, int lane) {
     double2 k0[RS], k1[RS], x0[RS], x1[RS];
     double re[RS], im[RS];
 #pragma unroll
     for (int ii = 0; ii < RS; ii++) {
         const int i = row0 + ii;   // compile-time after unrolling of the caller
-        k0[ii] = stage[(ii * 4 + 0 + R) * 32 + lane];
-        k1[ii] = stage[(ii * 4 + 2 + R) * 32 + lane];
-        const double2 o = oth[lane * ROWP + i];
+        k0[ii] = KG ? __ldg(stage + (ii * 4 + 0 + R) * 32 + lane) : stage[(ii * 4 + 0 + R) * 32 + lane];
+        k1[ii] = KG ? __ldg(stage + (ii * 4 + 2 + R) * 32 + lane) : stage[(ii * 4 + 2 + R) * 32 + lane];
+        const double2 o = HB ? oth[(i & 15) * 32 + lane] : oth[lane * ROWP + i];
         x0[ii] = R == 0 ? y[i] : o;
         x1[ii] = R == 0 ? o : y[i];
     }
@@ -316,49 +393,88 @@ __device__ __forceinline__ void mac_rows(double2 (&y)[32], const double2 *oth, c
     for (int ii = 0; ii < RS; ii++) y[row0 + ii] = make_double2(re[ii], im[ii]);
 }
 
-template <int R, int NS, int RS>
+// KL: chunks [C0, C1) of the GGSW at `ggsw` in global memory, no staging
+template <int R, int RS, int HB, int C0, int C1>
+__device__ __forceinline__ void mac_global(double2 (&y)[32], const double2 *oth, const double2 *ggsw, int lane) {
+#pragma unroll
+    for (int c = C0; c < C1; c++) mac_rows<R, RS, HB, 1>(y, oth, ggsw + (size_t)c * RS * 4 * 32, c * RS, lane);
+}
+// chunks [C0, C1) of the 32 / RS key-row chunks of one GGSW
+template <int R, int NS, int RS, int HB = 0, int C0 = 0, int C1 = 32 / RS>
 __device__ __forceinline__ void mac_all(double2 (&y)[32], const double2 *oth, const double2 *ring, u64 *full, u64 *empty, u32 &t, int lane) {
     constexpr int SP = RS * 4 * 32;
 #pragma unroll
-    for (int c = 0; c < 32 / RS; c++) {
+    for (int c = C0; c < C1; c++) {
         const u32 s = t % NS;
         mbar_wait(full + s, (t / NS) & 1);
-        mac_rows<R, RS>(y, oth, ring + (size_t)s * SP, c * RS, lane);
+        mac_rows<R, RS, HB>(y, oth, ring + (size_t)s * SP, c * RS, lane);
         __syncwarp();
         if (lane == 0) mbar_arrive(empty + s);
         t++;
     }
 }
 
-template <int TEAMS, int NS, int RS, int TWS>
+// Phase timing (builds with -DFFT64_TRACE_BUILD only): lane 0 of every consumer warp adds the cycles since its previous mark
+// to a.trace[phase]; scripts/quick_torus.py prints the table.  Phases: 0 decompose, 1 forward pass A, 2 transpose, 3 forward
+// pass B, 4 swap write + barrier, 5 key MAC (incl. waits for key rows), 6 barrier, 7 inverse pass B, 8 transpose, 9 inverse
+// pass A, 10 update.
+#ifdef FFT64_TRACE_BUILD
+#define FFT64_MARK(k)                                                                  \
+    do {                                                                               \
+        if (a.trace && lane == 0) {                                                    \
+            long long now_;                                                            \
+            asm volatile("mov.u64 %0, %%clock64;" : "=l"(now_)::"memory");             \
+            atomicAdd((unsigned long long *)a.trace + (k), (unsigned long long)(now_ - mark_)); \
+            mark_ = now_;                                                              \
+        }                                                                              \
+    } while (0)
+#else
+#define FFT64_MARK(k) \
+    do {              \
+    } while (0)
+#endif
+
+template <int TEAMS, int NS, int RS, int TWS, int HB = 0, int GROUPS = 1, int KL = 0>
 __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *smem_raw) {
-    using C = Cfg<TEAMS, NS, RS, TWS>;
+    using C = Cfg<TEAMS, NS, RS, TWS, HB, GROUPS, KL>;
+    static_assert(TEAMS % GROUPS == 0, "teams must split evenly into groups");
+    constexpr int TPG = C::TEAMS_PER_GROUP;
+    constexpr int BUF_POINTS = C::WARP_BUF_POINTS;   // shadows the full-size constant
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     double2 *tw_smem = (double2 *)smem_raw;
     const double2 *twB = TWS ? tw_smem : a.twB;
     u64 *acc_base = (u64 *)(tw_smem + TWB_ENTRIES * TWS);
     double2 *buf_base = (double2 *)(acc_base + (size_t)TEAMS * 2 * N);
-    double2 *ring = buf_base + (size_t)TEAMS * 2 * BUF_POINTS;
-    u64 *full = (u64 *)(ring + (size_t)NS * C::STAGE_POINTS);
-    u64 *empty = full + NS;
+    double2 *ring_all = buf_base + (size_t)TEAMS * 2 * BUF_POINTS;
+    u64 *full_all = (u64 *)(ring_all + (size_t)GROUPS * NS * C::STAGE_POINTS);
+    u64 *empty_all = full_all + GROUPS * NS;
 
     const u32 first_ct = blockIdx.x * TEAMS;
     const u32 left = a.B - first_ct;
     const u32 live_teams = left < (u32)TEAMS ? left : (u32)TEAMS;
     if (TWS)
         for (int i = tid; i < TWB_ENTRIES; i += C::THREADS) tw_smem[i] = a.twB[i];
-    if (tid == 0) {
-        for (int s = 0; s < NS; s++) {
-            mbar_init(full + s, 1);
-            mbar_init(empty + s, 2 * live_teams);
-        }
+    // live teams of group g: teams [g TPG, (g + 1) TPG) below live_teams
+    auto live_in_group = [&](u32 g) -> u32 {
+        const u32 lo = g * TPG;
+        return live_teams <= lo ? 0u : (live_teams - lo < (u32)TPG ? live_teams - lo : (u32)TPG);
+    };
+    if (!KL && tid == 0) {
+        for (int g = 0; g < GROUPS; g++)
+            for (int s = 0; s < NS; s++) {
+                mbar_init(full_all + g * NS + s, 1);
+                mbar_init(empty_all + g * NS + s, 2 * live_in_group(g));
+            }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
     const u32 total = a.steps * C::STAGES_PER_GGSW;
 
-    if (warp == C::CONSUMER_WARPS) {   // ---- producer warp: one lane streams the key rows
-        if (lane == 0) {
+    if (!KL && warp >= C::CONSUMER_WARPS) {   // ---- producer warps (one per group): one lane streams the key rows
+        const u32 g = warp - C::CONSUMER_WARPS;
+        double2 *ring = ring_all + (size_t)g * NS * C::STAGE_POINTS;
+        u64 *full = full_all + g * NS, *empty = empty_all + g * NS;
+        if (lane == 0 && live_in_group(g)) {
             constexpr u32 bytes = (u32)(sizeof(double2) * C::STAGE_POINTS);
             for (u32 t = 0; t < total; t++) {
                 const u32 s = t % NS;
@@ -373,6 +489,9 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
     const int team = warp >> 1, r = warp & 1;
     const u32 ct = first_ct + team;
     if (ct >= a.B) return;
+    const int grp = team / TPG;
+    const double2 *ring = ring_all + (size_t)grp * NS * C::STAGE_POINTS;
+    u64 *full = full_all + grp * NS, *empty = empty_all + grp * NS;
     u64 *acc = acc_base + (size_t)team * 2 * N + (size_t)r * N;   // this warp's accumulator polynomial
     double2 *buf = buf_base + ((size_t)team * 2 + r) * BUF_POINTS;
     const double2 *buf_oth = buf_base + ((size_t)team * 2 + (r ^ 1)) * BUF_POINTS;
@@ -389,30 +508,119 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
     u32 t = 0;
     u64 mask = a.steps ? lwe[0] : 0;
     const int barrier_id = 1 + team;
+    if (GROUPS > 1 && grp) __nanosleep(a.stagger_ns * grp);   // start the groups out of phase
+#ifdef FFT64_TRACE_BUILD
+    long long mark_ = clock64();
+#endif
+    const u32 dg_half = 1u << (31 - a.logB), dg_sh = 32 - a.logB;
+    const unsigned char *accb = (const unsigned char *)acc;
+    // own[2 i + h] = acc[lane + 32 (i + 32 h)]: this lane's coefficients stay in registers from the update of one iteration
+    // to the decomposition of the next (they take the place of x[], which is dead in between)
+    u64 own[64];
+#pragma unroll
+    for (int k = 0; k < 64; k++) own[k] = acc[lane + 32 * ((k >> 1) + 32 * (k & 1))];
 #pragma unroll 1
     for (u32 it = 0; it < a.steps; it++) {
         const u32 sh = mod_switch(mask);
         if (it + 1 < a.steps) mask = lwe[it + 1];
         double2 x[32];
-        // digits of X^sh acc_r - acc_r, folded: z[q] = (d[q], d[q + M]), q = lane + 32 i
+        // digits of X^sh acc_r - acc_r, folded: z[q] = (d[q], d[q + M]), q = lane + 32 i.
+        // Source of coefficient lane + 32 row: with sh = 32 a + b, coefficient lp + 32 ((row - ap) mod 128) of the
+        // 4096-periodic signed extension, lp = (lane - b) mod 32, ap = a + [lane < b]; rows >= 64 are the negated polynomial.
+        {
+            const u32 b = sh & 31u;
+            const u32 lp8 = (((u32)lane - b) & 31u) << 3;
+            const u32 ap8 = (((sh >> 5) + ((u32)lane < b ? 1u : 0u)) & 127u) << 8;
 #pragma unroll
-        for (int i = 0; i < 32; i++) {
-            const u32 q = (u32)lane + 32u * i;
-            const u64 d0 = rotated(acc, q, sh) - acc[q];
-            const u64 d1 = rotated(acc, q + M, sh) - acc[q + M];
-            x[i] = make_double2(int_to_double(digit1(d0, a.logB)), int_to_double(digit1(d1, a.logB)));
+            for (int i = 0; i < 32; i++) {
+                double dd[2];
+#pragma unroll
+                for (int h = 0; h < 2; h++) {
+                    const u32 tt = (u32)((i + 32 * h) << 8) - ap8;
+                    const u64 v = *(const u64 *)(accb + ((tt & 0x3F00u) | lp8));
+                    const u32 c = (tt >> 14) & 1u;
+                    const u64 d = (v ^ ((u64)0 - (u64)c)) + c - own[2 * i + h];
+                    dd[h] = digit1_double((u32)(d >> 32), dg_half, dg_sh);
+                }
+                x[i] = make_double2(dd[0], dd[1]);
+            }
         }
-        fft_forward(x, buf, twB, a, lane);
-        // swap spectra with the partner warp
-#pragma unroll
-        for (int i = 0; i < 32; i++) buf[lane * ROWP + i] = x[i];
-        asm volatile("bar.sync %0, 64;" ::"r"(barrier_id) : "memory");
-        if (r == 0)
-            mac_all<0, NS, RS>(x, buf_oth, ring, full, empty, t, lane);
+        FFT64_MARK(0);
+        pass_a<false>(x, a);
+        FFT64_MARK(1);
+        if (HB)
+            col_to_row_h(x, (double *)buf, lane);
         else
-            mac_all<1, NS, RS>(x, buf_oth, ring, full, empty, t, lane);
-        asm volatile("bar.sync %0, 64;" ::"r"(barrier_id) : "memory");
-        fft_inverse(x, buf, twB, a, lane);
+            col_to_row(x, buf, lane);
+        FFT64_MARK(2);
+        pass_b<false>(x, twB, lane);
+        FFT64_MARK(3);
+        // swap spectra with the partner warp
+        if (!HB) {
+#pragma unroll
+            for (int i = 0; i < 32; i++) buf[lane * ROWP + i] = x[i];
+            asm volatile("bar.sync %0, 64;" ::"r"(barrier_id) : "memory");
+            FFT64_MARK(4);
+            // rows 0..15, then the inverse butterflies that only involve them while the key rows of the second half
+            // stream in (the ring holds half a GGSW), then rows 16..31
+            constexpr int CH = 16 / RS;
+            if (r == 0)
+                (KL ? mac_global<0, RS, 0, 0, CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
+                    : mac_all<0, NS, RS, 0, 0, CH>(x, buf_oth, ring, full, empty, t, lane));
+            else
+                (KL ? mac_global<1, RS, 0, 0, CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
+                    : mac_all<1, NS, RS, 0, 0, CH>(x, buf_oth, ring, full, empty, t, lane));
+            pass_b_inv_half<0>(x, twB, lane);
+            if (r == 0)
+                (KL ? mac_global<0, RS, 0, CH, 2 * CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
+                    : mac_all<0, NS, RS, 0, CH, 2 * CH>(x, buf_oth, ring, full, empty, t, lane));
+            else
+                (KL ? mac_global<1, RS, 0, CH, 2 * CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
+                    : mac_all<1, NS, RS, 0, CH, 2 * CH>(x, buf_oth, ring, full, empty, t, lane));
+            FFT64_MARK(5);
+            asm volatile("bar.sync %0, 64;" ::"r"(barrier_id) : "memory");
+            FFT64_MARK(6);
+            pass_b_inv_half<1>(x, twB, lane);
+        } else {   // two rounds of 16 rows through the half-size buffers, layout [row][lane]
+            constexpr int CH = 16 / RS;
+            __syncwarp();
+#pragma unroll
+            for (int i = 0; i < 16; i++) buf[i * 32 + lane] = x[i];
+            asm volatile("bar.sync %0, 64;" ::"r"(barrier_id) : "memory");
+            FFT64_MARK(4);
+            if (r == 0)
+                (KL ? mac_global<0, RS, 1, 0, CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
+                    : mac_all<0, NS, RS, 1, 0, CH>(x, buf_oth, ring, full, empty, t, lane));
+            else
+                (KL ? mac_global<1, RS, 1, 0, CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
+                    : mac_all<1, NS, RS, 1, 0, CH>(x, buf_oth, ring, full, empty, t, lane));
+            FFT64_MARK(5);
+            asm volatile("bar.sync %0, 64;" ::"r"(barrier_id) : "memory");
+#pragma unroll
+            for (int i = 0; i < 16; i++) buf[i * 32 + lane] = x[16 + i];
+            asm volatile("bar.sync %0, 64;" ::"r"(barrier_id) : "memory");
+            FFT64_MARK(4);
+            pass_b_inv_half<0>(x, twB, lane);   // rows 0..15 are final: their inverse butterflies cover the wait for the key rows
+            if (r == 0)
+                (KL ? mac_global<0, RS, 1, CH, 2 * CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
+                    : mac_all<0, NS, RS, 1, CH, 2 * CH>(x, buf_oth, ring, full, empty, t, lane));
+            else
+                (KL ? mac_global<1, RS, 1, CH, 2 * CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
+                    : mac_all<1, NS, RS, 1, CH, 2 * CH>(x, buf_oth, ring, full, empty, t, lane));
+            FFT64_MARK(5);
+            asm volatile("bar.sync %0, 64;" ::"r"(barrier_id) : "memory");
+            FFT64_MARK(6);
+            pass_b_inv_half<1>(x, twB, lane);
+        }
+        pass_b_stage<true, 0>(x, twB, lane);
+        FFT64_MARK(7);
+        if (HB)
+            row_to_col_h(x, (double *)buf, lane);
+        else
+            row_to_col(x, buf, lane);
+        FFT64_MARK(8);
+        pass_a<true>(x, a);
+        FFT64_MARK(9);
 #pragma unroll
         for (int i0 = 0; i0 < 32; i0 += 4) {   // four points = eight independent conversion chains at a time
             double t[8], f[8];
@@ -426,11 +634,16 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
             for (int k = 0; k < 8; k++) f[k] = __fma_rn(f[k], TWO51, MAGIC);
 #pragma unroll
             for (int k = 0; k < 8; k++) {
+                // tor_from_double: (bits - 0x4338000000000000) << 13; the constant's set bits all leave the word, so the
+                // shift alone is the same value
                 const u32 q = (u32)lane + 32u * (i0 + k / 2) + ((k & 1) ? M : 0);
-                acc[q] += (u64)(__double_as_longlong(f[k]) - 0x4338000000000000LL) << 13;
+                const u64 nv = acc[q] + ((u64)__double_as_longlong(f[k]) << 13);
+                acc[q] = nv;
+                own[2 * (i0 + k / 2) + (k & 1)] = nv;
             }
         }
         __syncwarp();
+        FFT64_MARK(10);
     }
 
     if (a.out_mode == 2) {

@@ -380,6 +380,17 @@ class Engine:
         lib().lux_debug_fft_variant.argtypes = [_vp, _int]
         self._ck(lib().lux_debug_fft_variant(self._h, v))
 
+    def fft_trace(self):
+        """phase-cycle counters of the torus blind rotation since the last call (FFT64_TRACE_BUILD builds)"""
+        buf = (C.c_ulonglong * 16)()
+        lib().lux_debug_fft_trace.argtypes = [_vp, C.POINTER(C.c_ulonglong * 16)]
+        self._ck(lib().lux_debug_fft_trace(self._h, C.byref(buf)))
+        return [int(v) for v in buf]
+
+    def fft_stagger(self, ns: int):
+        lib().lux_debug_fft_stagger.argtypes = [_vp, _int]
+        self._ck(lib().lux_debug_fft_stagger(self._h, ns))
+
     def force_teams(self, t: int):
         lib().lux_debug_force_teams(self._h, t)
 
