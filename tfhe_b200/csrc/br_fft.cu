@@ -132,6 +132,7 @@ int lux_fft_launch_br(lux_engine *e, Args a, cudaStream_t s) {
             if (variant == 1) return launch_cfg<4, 3, 4, 1, 1>(e, a, s);      // twiddles in shared memory, ring 3 x 8 KiB
             if (variant == 2) return launch_cfg<4, 1, 4, 1, 1, 1, 1>(e, a, s);   // no ring: key rows straight from L2 / L1
             if (variant == 3) return launch_cfg<4, 2, 4, 0, 1, 2>(e, a, s);   // two independent groups, ring 2 x 8 KiB each
+            if (variant == 4) return launch_cfg<4, 1, 4, 1, 1, 1, 2>(e, a, s);   // no ring, CTA-wide barrier per iteration
             return launch_cfg<4, 4, 4, 0, 1>(e, a, s);                        // ring 4 x 8 KiB, twiddles through L1
     }
 }

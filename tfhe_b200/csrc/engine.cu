@@ -444,11 +444,85 @@ int lux_pbs_device_grouped(lux_engine *e, const u64 *d_in, const u64 *d_testvs, 
 }
 
 // --------------------------------------------------------------------------------------------- ABI
+static thread_local char tl_err[512] = "";
+static thread_local const lux_engine *tl_err_engine = nullptr;
+void lux_note_error(const lux_engine *e) {
+    tl_err_engine = e;
+    snprintf(tl_err, sizeof(tl_err), "%s", e->err);
+}
+
+// ---- host-pointer pipeline state (lux_pbs_batch): two copy streams, per-slot events, pinned staging grown on demand
+struct HostPipe {
+    cudaStream_t s_in = nullptr, s_out = nullptr;
+    cudaEvent_t ev_in[2] = {}, ev_k[2] = {}, ev_out[2] = {};
+    void *h_in[2] = {}, *h_out[2] = {};
+    size_t cap = 0;
+};
+static int host_pipe_init(lux_engine *e) {
+    if (e->pipe) return LUX_OK;
+    HostPipe *hp = new (std::nothrow) HostPipe();
+    if (!hp) LUX_FAIL(e, LUX_ERR_OOM, "out of host memory");
+    e->pipe = hp;
+    CUDA_TRY(e, cudaStreamCreateWithFlags(&hp->s_in, cudaStreamNonBlocking));
+    CUDA_TRY(e, cudaStreamCreateWithFlags(&hp->s_out, cudaStreamNonBlocking));
+    for (int i = 0; i < 2; i++) {
+        CUDA_TRY(e, cudaEventCreateWithFlags(&hp->ev_in[i], cudaEventDisableTiming));
+        CUDA_TRY(e, cudaEventCreateWithFlags(&hp->ev_k[i], cudaEventDisableTiming));
+        CUDA_TRY(e, cudaEventCreateWithFlags(&hp->ev_out[i], cudaEventDisableTiming));
+    }
+    return LUX_OK;
+}
+static int host_pipe_reserve(lux_engine *e, size_t bytes) {
+    HostPipe *hp = e->pipe;
+    if (hp->cap >= bytes) return LUX_OK;
+    for (int i = 0; i < 2; i++) {
+        if (hp->h_in[i]) cudaFreeHost(hp->h_in[i]);
+        if (hp->h_out[i]) cudaFreeHost(hp->h_out[i]);
+        hp->h_in[i] = hp->h_out[i] = nullptr;
+    }
+    hp->cap = 0;
+    for (int i = 0; i < 2; i++) {
+        if (cudaMallocHost(&hp->h_in[i], bytes) != cudaSuccess || cudaMallocHost(&hp->h_out[i], bytes) != cudaSuccess)
+            LUX_FAIL(e, LUX_ERR_OOM, "cudaMallocHost(%zu) for the host staging buffers failed", bytes);
+    }
+    hp->cap = bytes;
+    return LUX_OK;
+}
+static void host_pipe_destroy(lux_engine *e) {
+    HostPipe *hp = e->pipe;
+    if (!hp) return;
+    for (int i = 0; i < 2; i++) {
+        if (hp->h_in[i]) cudaFreeHost(hp->h_in[i]);
+        if (hp->h_out[i]) cudaFreeHost(hp->h_out[i]);
+        if (hp->ev_in[i]) cudaEventDestroy(hp->ev_in[i]);
+        if (hp->ev_k[i]) cudaEventDestroy(hp->ev_k[i]);
+        if (hp->ev_out[i]) cudaEventDestroy(hp->ev_out[i]);
+    }
+    if (hp->s_in) cudaStreamDestroy(hp->s_in);
+    if (hp->s_out) cudaStreamDestroy(hp->s_out);
+    delete hp;
+    e->pipe = nullptr;
+}
+// page-locked (cudaHostAlloc / cudaHostRegister) caller memory is copied from directly
+static bool host_is_pinned(const void *p) {
+    cudaPointerAttributes at{};
+    if (cudaPointerGetAttributes(&at, p) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return at.type == cudaMemoryTypeHost;
+}
+
 extern "C" {
 
 const char *lux_version(void) { return "tfhe_b200 0.2.0 (sm_100a; Goldilocks exact-NTT and 2^64-torus f64-FFT PBS)"; }
 
-const char *lux_last_error(const lux_engine *e) { return e ? e->err : g_create_error; }
+// the failing thread reads its own message (another thread's later failure on the same engine cannot overwrite it)
+const char *lux_last_error(const lux_engine *e) {
+    if (!e) return g_create_error;
+    if (tl_err_engine == e && tl_err[0]) return tl_err;
+    return e->err;
+}
 
 int lux_engine_create(const lux_params *p, int device, lux_engine **out) {
 #define CREATE_FAIL(code, ...)                                          \
@@ -545,6 +619,7 @@ int lux_engine_create(const lux_params *p, int device, lux_engine **out) {
 
 void lux_engine_destroy(lux_engine *e) {
     if (!e) return;
+    e->mtx.lock();   // a call still running on another thread finishes first; using the handle afterwards is the caller's bug
     cudaSetDevice(e->device);
     if (e->stream) cudaStreamSynchronize(e->stream);
     lux_radix_destroy(e);
@@ -559,6 +634,9 @@ void lux_engine_destroy(lux_engine *e) {
     for (int i = 0; i < 4; i++)
         if (e->ev[i]) cudaEventDestroy(e->ev[i]);
     if (e->stream) cudaStreamDestroy(e->stream);
+    if (e->d_fft_trace) cudaFree(e->d_fft_trace);
+    host_pipe_destroy(e);
+    e->mtx.unlock();
     delete e;
 }
 
@@ -583,6 +661,7 @@ size_t lux_wave_ciphertexts(const lux_engine *e, size_t B) {
     return 0;
 }
 int lux_set_timing(lux_engine *e, int enabled) {
+    LUX_LOCK(e);
     if (!e) return LUX_ERR_INVALID;
     e->timing = enabled != 0;
     return LUX_OK;
@@ -594,38 +673,45 @@ int lux_last_timing(const lux_engine *e, float out[2]) {
     return LUX_OK;
 }
 int lux_synchronize(lux_engine *e) {
+    LUX_LOCK(e);
     if (!e) return LUX_ERR_INVALID;
     CUDA_TRY(e, cudaSetDevice(e->device));
     CUDA_TRY(e, cudaStreamSynchronize(e->stream));
     return LUX_OK;
 }
 int lux_debug_force_teams(lux_engine *e, int teams) {
+    LUX_LOCK(e);
     if (!e) return LUX_ERR_INVALID;
     e->force_teams = teams;
     return LUX_OK;
 }
 int lux_debug_ks_splits(lux_engine *e, int splits) {
+    LUX_LOCK(e);
     if (!e || splits < 0) return LUX_ERR_INVALID;
     e->ks_splits = splits;
     return LUX_OK;
 }
 int lux_debug_br_regs(lux_engine *e, int regs) {
+    LUX_LOCK(e);
     if (!e || (regs != 4 && regs != 8 && regs != 16)) return LUX_ERR_INVALID;
     e->br_regs = regs;
     return LUX_OK;
 }
 int lux_debug_fft_variant(lux_engine *e, int variant) {
+    LUX_LOCK(e);
     if (!e) return LUX_ERR_INVALID;
     e->fft_variant = variant;
     return LUX_OK;
 }
 int lux_debug_fft_stagger(lux_engine *e, int ns) {
+    LUX_LOCK(e);
     if (!e || ns < 0) return LUX_ERR_INVALID;
     e->fft_stagger_ns = ns;
     return LUX_OK;
 }
 // returns the phase-cycle counters accumulated since the previous call and clears them (first call: allocates, enables)
 int lux_debug_fft_trace(lux_engine *e, unsigned long long out[16]) {
+    LUX_LOCK(e);
     if (!e || !out) return LUX_ERR_INVALID;
     CUDA_TRY(e, cudaSetDevice(e->device));
     if (!e->d_fft_trace) {
@@ -638,21 +724,25 @@ int lux_debug_fft_trace(lux_engine *e, unsigned long long out[16]) {
     return LUX_OK;
 }
 int lux_debug_cluster_regs(lux_engine *e, int regs) {
+    LUX_LOCK(e);
     if (!e || (regs != 0 && regs != 4 && regs != 8 && regs != 16)) return LUX_ERR_INVALID;
     e->cluster_regs = regs;
     return LUX_OK;
 }
 int lux_debug_generic_gadget(lux_engine *e, int on) {
+    LUX_LOCK(e);
     if (!e) return LUX_ERR_INVALID;
     e->generic_gadget = on != 0;
     return LUX_OK;
 }
 int lux_debug_ks_mode(lux_engine *e, int mode) {
+    LUX_LOCK(e);
     if (!e || mode < -1 || mode > 1) return LUX_ERR_INVALID;
     e->ks_mode = mode;
     return LUX_OK;
 }
 int lux_debug_split_mode(lux_engine *e, int mode) {
+    LUX_LOCK(e);
     if (!e || mode < -1 || mode > 2) return LUX_ERR_INVALID;
     e->split_mode = mode;
     return LUX_OK;
@@ -700,6 +790,7 @@ static int load_bsk_torus(lux_engine *e, const uint64_t *bsk, size_t n_words, in
 }
 
 int lux_load_bsk(lux_engine *e, const uint64_t *bsk, size_t n_words, int domain) {
+    LUX_LOCK(e);
     if (!e) return LUX_ERR_INVALID;
     if (lux_is_torus(e)) {
         int rc = load_bsk_torus(e, bsk, n_words, domain);
@@ -711,6 +802,7 @@ int lux_load_bsk(lux_engine *e, const uint64_t *bsk, size_t n_words, int domain)
     return rc;
 }
 int lux_load_glwe_ksk(lux_engine *e, const uint64_t *ksk, size_t n_words, int domain) {
+    LUX_LOCK(e);
     if (!e) return LUX_ERR_INVALID;
     if (e->p.order != LUX_ORDER_PBS_GLWEKS) LUX_FAIL(e, LUX_ERR_INVALID, "GLWE key switch key only applies to LUX_ORDER_PBS_GLWEKS");
     int rc = load_ggsw_array(e, e->d_gksk, ksk, n_words, e->gksk_words, domain, "lux_load_glwe_ksk");
@@ -718,6 +810,7 @@ int lux_load_glwe_ksk(lux_engine *e, const uint64_t *ksk, size_t n_words, int do
     return rc;
 }
 int lux_load_lwe_ksk(lux_engine *e, const uint64_t *ksk, size_t n_words) {
+    LUX_LOCK(e);
     if (!e) return LUX_ERR_INVALID;
     if (e->p.order == LUX_ORDER_PBS_GLWEKS) LUX_FAIL(e, LUX_ERR_INVALID, "LWE key switch key does not apply to LUX_ORDER_PBS_GLWEKS");
     if (!ksk) LUX_FAIL(e, LUX_ERR_INVALID, "lux_load_lwe_ksk: null pointer");
@@ -740,6 +833,7 @@ int lux_load_lwe_ksk(lux_engine *e, const uint64_t *ksk, size_t n_words) {
 size_t lux_key_blob_bytes(const lux_engine *e) { return e ? sizeof(u64) * e->blob_words : 0; }
 
 int lux_export_keys_device(lux_engine *e, void *dev_blob, size_t bytes) {
+    LUX_LOCK(e);
     if (!e || !dev_blob) return LUX_ERR_INVALID;
     if (bytes != sizeof(u64) * e->blob_words) LUX_FAIL(e, LUX_ERR_INVALID, "key blob is %zu bytes, got %zu", sizeof(u64) * e->blob_words, bytes);
     CUDA_TRY(e, cudaSetDevice(e->device));
@@ -750,6 +844,7 @@ int lux_export_keys_device(lux_engine *e, void *dev_blob, size_t bytes) {
     return LUX_OK;
 }
 int lux_import_keys_device(lux_engine *e, const void *dev_blob, size_t bytes) {
+    LUX_LOCK(e);
     if (!e || !dev_blob) return LUX_ERR_INVALID;
     if (bytes != sizeof(u64) * e->blob_words) LUX_FAIL(e, LUX_ERR_INVALID, "key blob is %zu bytes, got %zu", sizeof(u64) * e->blob_words, bytes);
     CUDA_TRY(e, cudaSetDevice(e->device));
@@ -771,6 +866,7 @@ int lux_import_keys_device(lux_engine *e, const void *dev_blob, size_t bytes) {
 // ---- PBS
 int lux_pbs_batch_device(lux_engine *e, const uint64_t *d_in, const uint64_t *d_testvs, uint32_t n_luts,
                          const uint32_t *d_lut_idx, size_t B, uint64_t *d_out, void *stream) {
+    LUX_LOCK(e);
     if (!e) return LUX_ERR_INVALID;
     if (!d_in || !d_testvs || !d_out || n_luts == 0) LUX_FAIL(e, LUX_ERR_INVALID, "lux_pbs_batch_device: null/empty argument");
     return lux_pbs_device_grouped(e, d_in, d_testvs, d_lut_idx, 1, B, d_out, stream ? (cudaStream_t)stream : e->stream);
@@ -778,6 +874,7 @@ int lux_pbs_batch_device(lux_engine *e, const uint64_t *d_in, const uint64_t *d_
 
 int lux_pbs_batch(lux_engine *e, const uint64_t *lwe_in, const uint64_t *testvs, uint32_t n_luts,
                   const uint32_t *lut_idx, size_t B, uint64_t *lwe_out) {
+    LUX_LOCK(e);
     if (!e) return LUX_ERR_INVALID;
     if (!lwe_in || !testvs || !lwe_out || n_luts == 0) LUX_FAIL(e, LUX_ERR_INVALID, "lux_pbs_batch: null/empty argument");
     if (B == 0) return LUX_OK;
@@ -787,16 +884,58 @@ int lux_pbs_batch(lux_engine *e, const uint64_t *lwe_in, const uint64_t *testvs,
     CUDA_TRY(e, cudaSetDevice(e->device));
     const size_t w = lux_ct_words(e), N = e->p.N;
     int rc;
-    if ((rc = ensure_scratch(e, 1, sizeof(u64) * B * w))) return rc;
-    if ((rc = ensure_scratch(e, 2, sizeof(u64) * B * w))) return rc;
+    // Chunked, double-buffered pipeline: H2D of chunk c+1 and D2H of chunk c-1 run on their own streams while chunk c is
+    // bootstrapped; pageable caller memory goes through pinned staging owned by the engine (the memcpy of the next chunk
+    // overlaps the GPU), pinned caller memory is copied from / to directly.  A chunk is a whole number of kernel waves.
+    if ((rc = host_pipe_init(e))) return rc;
+    HostPipe &hp = *e->pipe;
+    const size_t wave = lux_wave_ciphertexts(e, B);
+    size_t chunk = B;
+    if (B >= 4 * wave) chunk = 2 * wave;
+    else if (B >= 2 * wave) chunk = wave;
+    const size_t n_chunks = (B + chunk - 1) / chunk;
+    const size_t chunk_bytes = sizeof(u64) * chunk * w;
+    if ((rc = ensure_scratch(e, 1, 2 * chunk_bytes))) return rc;
+    if ((rc = ensure_scratch(e, 2, 2 * chunk_bytes))) return rc;
     if ((rc = ensure_scratch(e, 3, sizeof(u64) * n_luts * N + sizeof(u32) * B))) return rc;
-    u64 *d_in = (u64 *)e->scratch[1], *d_out = (u64 *)e->scratch[2], *d_tv = (u64 *)e->scratch[3];
+    const bool in_pinned = host_is_pinned(lwe_in), out_pinned = host_is_pinned(lwe_out);
+    if ((!in_pinned || !out_pinned) && (rc = host_pipe_reserve(e, chunk_bytes))) return rc;
+    u64 *d_tv = (u64 *)e->scratch[3];
     u32 *d_idx = lut_idx ? (u32 *)(d_tv + (size_t)n_luts * N) : nullptr;
-    CUDA_TRY(e, cudaMemcpyAsync(d_in, lwe_in, sizeof(u64) * B * w, cudaMemcpyHostToDevice, e->stream));
     CUDA_TRY(e, cudaMemcpyAsync(d_tv, testvs, sizeof(u64) * n_luts * N, cudaMemcpyHostToDevice, e->stream));
     if (lut_idx) CUDA_TRY(e, cudaMemcpyAsync(d_idx, lut_idx, sizeof(u32) * B, cudaMemcpyHostToDevice, e->stream));
-    if ((rc = lux_pbs_batch_device(e, d_in, d_tv, n_luts, d_idx, B, d_out, nullptr))) return rc;
-    CUDA_TRY(e, cudaMemcpyAsync(lwe_out, d_out, sizeof(u64) * B * w, cudaMemcpyDeviceToHost, e->stream));
+    auto retire = [&](size_t c) -> int {   // chunk c's results reach the caller's buffer
+        const int slot = (int)(c & 1);
+        CUDA_TRY(e, cudaEventSynchronize(hp.ev_out[slot]));
+        if (!out_pinned) {
+            const size_t c0 = c * chunk, nb = std::min(chunk, B - c0);
+            memcpy(lwe_out + c0 * w, hp.h_out[slot], sizeof(u64) * nb * w);
+        }
+        return LUX_OK;
+    };
+    for (size_t c = 0; c < n_chunks; c++) {
+        const int slot = (int)(c & 1);
+        const size_t c0 = c * chunk, nb = std::min(chunk, B - c0), bytes = sizeof(u64) * nb * w;
+        if (c >= 2 && (rc = retire(c - 2))) return rc;   // also frees this slot's device and staging buffers
+        u64 *d_in = (u64 *)((unsigned char *)e->scratch[1] + slot * chunk_bytes);
+        u64 *d_out = (u64 *)((unsigned char *)e->scratch[2] + slot * chunk_bytes);
+        const uint64_t *src = lwe_in + c0 * w;
+        if (!in_pinned) {
+            memcpy(hp.h_in[slot], src, bytes);
+            src = (const uint64_t *)hp.h_in[slot];
+        }
+        CUDA_TRY(e, cudaMemcpyAsync(d_in, src, bytes, cudaMemcpyHostToDevice, hp.s_in));
+        CUDA_TRY(e, cudaEventRecord(hp.ev_in[slot], hp.s_in));
+        CUDA_TRY(e, cudaStreamWaitEvent(e->stream, hp.ev_in[slot], 0));
+        if ((rc = lux_pbs_device_grouped(e, d_in, d_tv, d_idx ? d_idx + c0 : nullptr, 1, nb, d_out, e->stream))) return rc;
+        CUDA_TRY(e, cudaEventRecord(hp.ev_k[slot], e->stream));
+        CUDA_TRY(e, cudaStreamWaitEvent(hp.s_out, hp.ev_k[slot], 0));
+        uint64_t *dst = out_pinned ? lwe_out + c0 * w : (uint64_t *)hp.h_out[slot];
+        CUDA_TRY(e, cudaMemcpyAsync(dst, d_out, bytes, cudaMemcpyDeviceToHost, hp.s_out));
+        CUDA_TRY(e, cudaEventRecord(hp.ev_out[slot], hp.s_out));
+    }
+    for (size_t c = n_chunks >= 2 ? n_chunks - 2 : 0; c < n_chunks; c++)
+        if ((rc = retire(c))) return rc;
     CUDA_TRY(e, cudaStreamSynchronize(e->stream));
     return LUX_OK;
 }
@@ -817,6 +956,7 @@ static int gate_coeffs(int gate, int *coef, u64 *konst) {
 }
 int lux_gate_batch_device(lux_engine *e, int gate, const uint64_t *d_a, const uint64_t *d_b, size_t B, uint64_t *d_out,
                           void *stream) {
+    LUX_LOCK(e);
     if (!e) return LUX_ERR_INVALID;
     if (!d_a || !d_b || !d_out) LUX_FAIL(e, LUX_ERR_INVALID, "lux_gate_batch_device: null argument");
     int coef;
@@ -838,6 +978,7 @@ int lux_gate_batch_device(lux_engine *e, int gate, const uint64_t *d_a, const ui
     return lux_pbs_device_grouped(e, d_x, d_tv, nullptr, 1, B, d_out, s, GL_Q >> 3);
 }
 int lux_gate_batch(lux_engine *e, int gate, const uint64_t *a, const uint64_t *b, size_t B, uint64_t *out) {
+    LUX_LOCK(e);
     if (!e) return LUX_ERR_INVALID;
     if (!a || !b || !out) LUX_FAIL(e, LUX_ERR_INVALID, "lux_gate_batch: null argument");
     if (B == 0) return LUX_OK;
@@ -917,6 +1058,7 @@ int lux_ntt_forward(lux_engine *e, const uint64_t *in, size_t n_polys, uint64_t 
 int lux_ntt_backward(lux_engine *e, const uint64_t *in, size_t n_polys, uint64_t *out) { return ntt_host(e, in, n_polys, out, true); }
 
 int lux_ntt_any(lux_engine *e, uint32_t N, int inverse, const uint64_t *in, size_t n_polys, uint64_t *out) {
+    LUX_LOCK(e);
     if (!e) return LUX_ERR_INVALID;
     if (!in || !out) LUX_FAIL(e, LUX_ERR_INVALID, "null pointer");
     if (N < 8 || N > 2048 || (N & (N - 1))) LUX_FAIL(e, LUX_ERR_INVALID, "lux_ntt_any: N must be a power of two in [8,2048]");
@@ -949,6 +1091,7 @@ int lux_ntt_any(lux_engine *e, uint32_t N, int inverse, const uint64_t *in, size
 }
 
 int lux_decompose(lux_engine *e, const uint64_t *in, size_t count, uint32_t logB, uint64_t *out) {
+    LUX_LOCK(e);
     if (!e) return LUX_ERR_INVALID;
     if (!in || !out) LUX_FAIL(e, LUX_ERR_INVALID, "null pointer");
     if (logB < 1 || logB > 62) LUX_FAIL(e, LUX_ERR_INVALID, "logB out of range");
@@ -968,6 +1111,7 @@ int lux_decompose(lux_engine *e, const uint64_t *in, size_t count, uint32_t logB
 }
 
 int lux_mod_switch(lux_engine *e, const uint64_t *in, size_t count, uint32_t *out) {
+    LUX_LOCK(e);
     if (!e) return LUX_ERR_INVALID;
     if (!in || !out) LUX_FAIL(e, LUX_ERR_INVALID, "null pointer");
     if (count == 0) return LUX_OK;
@@ -985,6 +1129,7 @@ int lux_mod_switch(lux_engine *e, const uint64_t *in, size_t count, uint32_t *ou
 }
 
 int lux_lwe_keyswitch(lux_engine *e, const uint64_t *in, size_t B, uint64_t *out) {
+    LUX_LOCK(e);
     if (!e) return LUX_ERR_INVALID;
     if (!in || !out) LUX_FAIL(e, LUX_ERR_INVALID, "null pointer");
     if (e->p.order == LUX_ORDER_PBS_GLWEKS) LUX_FAIL(e, LUX_ERR_INVALID, "engine has no LWE key switch (order 0)");
@@ -1004,6 +1149,7 @@ int lux_lwe_keyswitch(lux_engine *e, const uint64_t *in, size_t B, uint64_t *out
 
 int lux_blind_rotate(lux_engine *e, const uint64_t *lwe, const uint64_t *testvs, uint32_t n_luts, const uint32_t *lut_idx,
                      size_t B, uint32_t steps, uint64_t *acc_out) {
+    LUX_LOCK(e);
     if (!e) return LUX_ERR_INVALID;
     if (!lwe || !testvs || !acc_out || n_luts == 0) LUX_FAIL(e, LUX_ERR_INVALID, "null/empty argument");
     if (!e->has_bsk) LUX_FAIL(e, LUX_ERR_NO_KEY, "bootstrap key not loaded");
@@ -1040,6 +1186,7 @@ int lux_blind_rotate(lux_engine *e, const uint64_t *lwe, const uint64_t *testvs,
 }
 
 int lux_fft(lux_engine *e, const double *in, size_t n_polys, int inverse, double *out) {
+    LUX_LOCK(e);
     if (!e) return LUX_ERR_INVALID;
     if (!lux_is_torus(e)) LUX_FAIL(e, LUX_ERR_INVALID, "lux_fft: engine is not LUX_ARITH_TORUS64_FFT");
     if (!in || !out) LUX_FAIL(e, LUX_ERR_INVALID, "null pointer");
@@ -1057,6 +1204,7 @@ int lux_fft(lux_engine *e, const double *in, size_t n_polys, int inverse, double
 }
 
 int lux_torus_decompose(lux_engine *e, const uint64_t *in, size_t count, int64_t *out) {
+    LUX_LOCK(e);
     if (!e) return LUX_ERR_INVALID;
     if (!lux_is_torus(e)) LUX_FAIL(e, LUX_ERR_INVALID, "lux_torus_decompose: engine is not LUX_ARITH_TORUS64_FFT");
     if (!in || !out) LUX_FAIL(e, LUX_ERR_INVALID, "null pointer");
@@ -1073,6 +1221,7 @@ int lux_torus_decompose(lux_engine *e, const uint64_t *in, size_t count, int64_t
 }
 
 int lux_export_bsk_fourier(lux_engine *e, double *out, size_t n_doubles) {
+    LUX_LOCK(e);
     if (!e) return LUX_ERR_INVALID;
     if (!lux_is_torus(e)) LUX_FAIL(e, LUX_ERR_INVALID, "lux_export_bsk_fourier: engine is not LUX_ARITH_TORUS64_FFT");
     if (!e->has_bsk) LUX_FAIL(e, LUX_ERR_NO_KEY, "bootstrap key not loaded");
@@ -1083,6 +1232,7 @@ int lux_export_bsk_fourier(lux_engine *e, double *out, size_t n_doubles) {
 }
 
 int lux_external_product(lux_engine *e, const uint64_t *ggsw, int domain, const uint64_t *glwe_in, size_t count, uint64_t *glwe_out) {
+    LUX_LOCK(e);
     if (!e) return LUX_ERR_INVALID;
     if (lux_is_torus(e)) LUX_FAIL(e, LUX_ERR_INVALID, "lux_external_product: not available for the torus arithmetic (use lux_blind_rotate with steps)");
     if (!ggsw || !glwe_in || !glwe_out) LUX_FAIL(e, LUX_ERR_INVALID, "null pointer");
@@ -1111,6 +1261,7 @@ int lux_external_product(lux_engine *e, const uint64_t *ggsw, int domain, const 
 }
 
 int lux_debug_field_probe(lux_engine *e, const uint64_t *a, const uint64_t *b, size_t count, uint64_t *out) {
+    LUX_LOCK(e);
     if (!e) return LUX_ERR_INVALID;
     if (!a || !b || !out || count == 0) LUX_FAIL(e, LUX_ERR_INVALID, "null/empty argument");
     CUDA_TRY(e, cudaSetDevice(e->device));
@@ -1131,6 +1282,7 @@ int lux_debug_field_probe(lux_engine *e, const uint64_t *a, const uint64_t *b, s
 // out[0] = IMAD.WIDE.U32 per second, out[1] = 32-bit IADD per second, out[2] = Goldilocks butterflies per second
 // (register-only, whole GPU), measured with CUDA events.
 int lux_debug_int_peak(lux_engine *e, double out[3]) {
+    LUX_LOCK(e);
     if (!e || !out) return LUX_ERR_INVALID;
     CUDA_TRY(e, cudaSetDevice(e->device));
     int rc;
@@ -1158,6 +1310,7 @@ int lux_debug_int_peak(lux_engine *e, double out[3]) {
 
 // out[0] = DFMA lane-operations per second (register-only, whole GPU), measured with CUDA events.
 int lux_debug_fp64_peak(lux_engine *e, double out[1]) {
+    LUX_LOCK(e);
     if (!e || !out) return LUX_ERR_INVALID;
     CUDA_TRY(e, cudaSetDevice(e->device));
     int rc;

@@ -5,6 +5,7 @@
 #include <cstdio>
 
 #include <map>
+#include <mutex>
 #include <vector>
 
 #include "../../include/lux_tfhe.h"
@@ -14,6 +15,10 @@
 #define LUX_SCRATCH_SLOTS 8
 
 struct lux_engine {
+    // every extern "C" entry point that takes a non-const engine holds this for its whole duration: calls on one engine
+    // from several host threads are serialised by the library ("blocking and thread-safe per engine").
+    // Recursive because host-pointer entry points call the device-pointer ones.
+    std::recursive_mutex mtx;
     lux_params p{};
     int device = 0;
     int sm_count = 148;
@@ -58,6 +63,7 @@ struct lux_engine {
     void *d_fft_trace = nullptr;  // 16 phase-cycle counters (FFT64_TRACE_BUILD builds; lux_debug_fft_trace)
     int fft_stagger_ns = 6000;    // start delay between the groups of a CTA (kernels with GROUPS > 1)
     int fft_variant = 0;          // tuning: ring depth / twiddle placement of the 3-ciphertext kernel (br_fft.cu)
+    struct HostPipe *pipe = nullptr;     // copy streams / pinned staging of the host-pointer PBS entry point (engine.cu)
     struct RadixState *radix = nullptr;  // euintN layer (radix.cu), created on first use
     char err[512] = "";
 };
@@ -90,11 +96,18 @@ int lux_fft_probe(lux_engine *e, const void *d_in, void *d_out, size_t n_polys, 
 int lux_fft_digits(lux_engine *e, const u64 *d_in, long long *d_out, size_t count, u32 logB, cudaStream_t s);
 inline bool lux_is_torus(const lux_engine *e) { return e->p.arith == LUX_ARITH_TORUS64_FFT; }
 
+// the message is kept per engine and, for lux_last_error on the failing thread, per thread
+void lux_note_error(const lux_engine *e);
 #define LUX_FAIL(e, code, ...)                                  \
     do {                                                        \
         snprintf((e)->err, sizeof((e)->err), __VA_ARGS__);      \
+        lux_note_error(e);                                      \
         return (code);                                          \
     } while (0)
+
+#define LUX_LOCK(e)                                      \
+    std::unique_lock<std::recursive_mutex> lux_lock_;    \
+    if (e) lux_lock_ = std::unique_lock<std::recursive_mutex>((e)->mtx)
 
 #define CUDA_TRY(e, call)                                                                              \
     do {                                                                                               \

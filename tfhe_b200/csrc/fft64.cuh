@@ -177,9 +177,42 @@ __device__ __forceinline__ void bfly_group(double2 (&x)[32], const int (&iu)[G],
     }
 }
 
+// Phase marks.  With a.trace set (lux_debug_fft_trace) lane 0 of every consumer warp adds the cycles since its previous mark
+// to a.trace[phase]; scripts/quick_torus.py prints the table.  Phases: 0 decompose, 1 forward pass A, 2 transpose, 3 forward
+// pass B, 4 swap write + barrier, 5 key MAC (incl. waits for key rows and the half-size inverse stages), 6 barrier, 7 inverse
+// pass B, 8 transpose, 9 inverse pass A, 10 update.
+// The marks stay in the production kernel on purpose: each one is a (never taken, uniform) branch that ends a basic block,
+// and ptxas schedules the phases separately instead of mixing them.  Measured on B200 at B = 4,736: 85.9 ms with the marks,
+// 93.0 ms without, 90.1 ms with a bare never-taken branch (profiles/r02b_fft_variants.txt).  -DFFT64_NO_MARKS removes them.
+#ifndef FFT64_SKIP_MARKS
+#define FFT64_SKIP_MARKS 0   // bit k set: phase mark k is left out (codegen experiments)
+#endif
+#ifndef FFT64_NO_MARKS
+#define FFT64_MARK(k)                                                                  \
+    do {                                                                               \
+        if (!((FFT64_SKIP_MARKS >> (k)) & 1) && a.trace && lane == 0) {                                                    \
+            long long now_;                                                            \
+            asm volatile("mov.u64 %0, %%clock64;" : "=l"(now_)::"memory");             \
+            atomicAdd((unsigned long long *)a.trace + (k), (unsigned long long)(now_ - mark_)); \
+            mark_ = now_;                                                              \
+        }                                                                              \
+    } while (0)
+#else
+#define FFT64_MARK(k) asm volatile("" ::: "memory")
+#endif
+
+// optional marks between the stages of a pass (experiment: -DFFT64_FINE_MARKS)
+#ifdef FFT64_FINE_MARKS
+#define FFT64_STAGE_MARK() FFT64_MARK(15)
+#else
+#define FFT64_STAGE_MARK() \
+    do {                   \
+    } while (0)
+#endif
+
 // pass A: tree levels m = 1..16 on the column layout; node m + blk pairs registers blk*2t + jj and + t, t = 16/m
 template <bool INV>
-__device__ __forceinline__ void pass_a(double2 (&x)[32], const Args &a) {
+__device__ __forceinline__ void pass_a(double2 (&x)[32], const Args &a, int lane, long long &mark_) {
     constexpr int G = FFT64_GROUP;
 #pragma unroll
     for (int s0 = 0; s0 < 5; s0++) {
@@ -204,6 +237,7 @@ __device__ __forceinline__ void pass_a(double2 (&x)[32], const Args &a) {
             }
             bfly_group<INV, G>(x, iu, iv, wr, wi);
         }
+        FFT64_STAGE_MARK();
     }
 }
 // pass B: tree levels m = 32 g, g = 1..16, on the row layout; lane r owns nodes m + r g + b, b < g
@@ -237,12 +271,16 @@ __device__ __forceinline__ void pass_b_stage(double2 (&y)[32], const double2 *tw
     }
 }
 template <bool INV>
-__device__ __forceinline__ void pass_b(double2 (&y)[32], const double2 *twB, int lane) {
+__device__ __forceinline__ void pass_b(double2 (&y)[32], const double2 *twB, int lane, const Args &a, long long &mark_) {
     if (!INV) {
         pass_b_stage<false, 0>(y, twB, lane);
+        FFT64_STAGE_MARK();
         pass_b_stage<false, 1>(y, twB, lane);
+        FFT64_STAGE_MARK();
         pass_b_stage<false, 2>(y, twB, lane);
+        FFT64_STAGE_MARK();
         pass_b_stage<false, 3>(y, twB, lane);
+        FFT64_STAGE_MARK();
         pass_b_stage<false, 4>(y, twB, lane);
     } else {
         pass_b_stage<true, 4>(y, twB, lane);
@@ -254,10 +292,13 @@ __device__ __forceinline__ void pass_b(double2 (&y)[32], const double2 *twB, int
 }
 // inverse pass B without its last stage, on rows 16 H .. 16 H + 15 only (the key MAC of the other half can still be pending)
 template <int H>
-__device__ __forceinline__ void pass_b_inv_half(double2 (&y)[32], const double2 *twB, int lane) {
+__device__ __forceinline__ void pass_b_inv_half(double2 (&y)[32], const double2 *twB, int lane, const Args &a, long long &mark_) {
     pass_b_stage<true, 4, 8 * H, 8 * H + 8>(y, twB, lane);
+    FFT64_STAGE_MARK();
     pass_b_stage<true, 3, 8 * H, 8 * H + 8>(y, twB, lane);
+    FFT64_STAGE_MARK();
     pass_b_stage<true, 2, 8 * H, 8 * H + 8>(y, twB, lane);
+    FFT64_STAGE_MARK();
     pass_b_stage<true, 1, 8 * H, 8 * H + 8>(y, twB, lane);
 }
 // transposes through the warp's padded buffer
@@ -311,22 +352,24 @@ __device__ __forceinline__ void row_to_col_h(double2 (&y)[32], double *b, int la
 // forward: column layout in (z[lane + 32 i]), row layout out (Z[32 lane + i], oracle index order)
 template <int HB = 0>
 __device__ __forceinline__ void fft_forward(double2 (&x)[32], double2 *buf, const double2 *twB, const Args &a, int lane) {
-    pass_a<false>(x, a);
+    long long mark_ = 0;
+    pass_a<false>(x, a, lane, mark_);
     if (HB)
         col_to_row_h(x, (double *)buf, lane);
     else
         col_to_row(x, buf, lane);
-    pass_b<false>(x, twB, lane);
+    pass_b<false>(x, twB, lane, a, mark_);
 }
 // inverse (unnormalised): row layout in, column layout out
 template <int HB = 0>
 __device__ __forceinline__ void fft_inverse(double2 (&y)[32], double2 *buf, const double2 *twB, const Args &a, int lane) {
-    pass_b<true>(y, twB, lane);
+    long long mark_ = 0;
+    pass_b<true>(y, twB, lane, a, mark_);
     if (HB)
         row_to_col_h(y, (double *)buf, lane);
     else
         row_to_col(y, buf, lane);
-    pass_a<true>(y, a);
+    pass_a<true>(y, a, lane, mark_);
 }
 
 // ------------------------------------------------------------------------------------------ blind rotation
@@ -414,26 +457,6 @@ __device__ __forceinline__ void mac_all(double2 (&y)[32], const double2 *oth, co
     }
 }
 
-// Phase timing (builds with -DFFT64_TRACE_BUILD only): lane 0 of every consumer warp adds the cycles since its previous mark
-// to a.trace[phase]; scripts/quick_torus.py prints the table.  Phases: 0 decompose, 1 forward pass A, 2 transpose, 3 forward
-// pass B, 4 swap write + barrier, 5 key MAC (incl. waits for key rows), 6 barrier, 7 inverse pass B, 8 transpose, 9 inverse
-// pass A, 10 update.
-#ifdef FFT64_TRACE_BUILD
-#define FFT64_MARK(k)                                                                  \
-    do {                                                                               \
-        if (a.trace && lane == 0) {                                                    \
-            long long now_;                                                            \
-            asm volatile("mov.u64 %0, %%clock64;" : "=l"(now_)::"memory");             \
-            atomicAdd((unsigned long long *)a.trace + (k), (unsigned long long)(now_ - mark_)); \
-            mark_ = now_;                                                              \
-        }                                                                              \
-    } while (0)
-#else
-#define FFT64_MARK(k) \
-    do {              \
-    } while (0)
-#endif
-
 template <int TEAMS, int NS, int RS, int TWS, int HB = 0, int GROUPS = 1, int KL = 0>
 __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *smem_raw) {
     using C = Cfg<TEAMS, NS, RS, TWS, HB, GROUPS, KL>;
@@ -509,9 +532,7 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
     u64 mask = a.steps ? lwe[0] : 0;
     const int barrier_id = 1 + team;
     if (GROUPS > 1 && grp) __nanosleep(a.stagger_ns * grp);   // start the groups out of phase
-#ifdef FFT64_TRACE_BUILD
-    long long mark_ = clock64();
-#endif
+    long long mark_ = a.trace ? clock64() : 0;
     const u32 dg_half = 1u << (31 - a.logB), dg_sh = 32 - a.logB;
     const unsigned char *accb = (const unsigned char *)acc;
     // own[2 i + h] = acc[lane + 32 (i + 32 h)]: this lane's coefficients stay in registers from the update of one iteration
@@ -521,6 +542,9 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
     for (int k = 0; k < 64; k++) own[k] = acc[lane + 32 * ((k >> 1) + 32 * (k & 1))];
 #pragma unroll 1
     for (u32 it = 0; it < a.steps; it++) {
+        // KL == 2: no ring, but the live consumer warps of the CTA meet once per iteration: they then ask for the same key
+        // rows at about the same time (one L2 request, L1 hits for the rest) and keep sharing instruction fetches
+        if (KL == 2) asm volatile("bar.sync 15, %0;" ::"r"(64u * live_teams) : "memory");
         const u32 sh = mod_switch(mask);
         if (it + 1 < a.steps) mask = lwe[it + 1];
         double2 x[32];
@@ -546,14 +570,14 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
             }
         }
         FFT64_MARK(0);
-        pass_a<false>(x, a);
+        pass_a<false>(x, a, lane, mark_);
         FFT64_MARK(1);
         if (HB)
             col_to_row_h(x, (double *)buf, lane);
         else
             col_to_row(x, buf, lane);
         FFT64_MARK(2);
-        pass_b<false>(x, twB, lane);
+        pass_b<false>(x, twB, lane, a, mark_);
         FFT64_MARK(3);
         // swap spectra with the partner warp
         if (!HB) {
@@ -570,7 +594,7 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
             else
                 (KL ? mac_global<1, RS, 0, 0, CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
                     : mac_all<1, NS, RS, 0, 0, CH>(x, buf_oth, ring, full, empty, t, lane));
-            pass_b_inv_half<0>(x, twB, lane);
+            pass_b_inv_half<0>(x, twB, lane, a, mark_);
             if (r == 0)
                 (KL ? mac_global<0, RS, 0, CH, 2 * CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
                     : mac_all<0, NS, RS, 0, CH, 2 * CH>(x, buf_oth, ring, full, empty, t, lane));
@@ -580,7 +604,7 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
             FFT64_MARK(5);
             asm volatile("bar.sync %0, 64;" ::"r"(barrier_id) : "memory");
             FFT64_MARK(6);
-            pass_b_inv_half<1>(x, twB, lane);
+            pass_b_inv_half<1>(x, twB, lane, a, mark_);
         } else {   // two rounds of 16 rows through the half-size buffers, layout [row][lane]
             constexpr int CH = 16 / RS;
             __syncwarp();
@@ -600,7 +624,7 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
             for (int i = 0; i < 16; i++) buf[i * 32 + lane] = x[16 + i];
             asm volatile("bar.sync %0, 64;" ::"r"(barrier_id) : "memory");
             FFT64_MARK(4);
-            pass_b_inv_half<0>(x, twB, lane);   // rows 0..15 are final: their inverse butterflies cover the wait for the key rows
+            pass_b_inv_half<0>(x, twB, lane, a, mark_);   // rows 0..15 are final: their inverse butterflies cover the wait for the key rows
             if (r == 0)
                 (KL ? mac_global<0, RS, 1, CH, 2 * CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
                     : mac_all<0, NS, RS, 1, CH, 2 * CH>(x, buf_oth, ring, full, empty, t, lane));
@@ -610,7 +634,7 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
             FFT64_MARK(5);
             asm volatile("bar.sync %0, 64;" ::"r"(barrier_id) : "memory");
             FFT64_MARK(6);
-            pass_b_inv_half<1>(x, twB, lane);
+            pass_b_inv_half<1>(x, twB, lane, a, mark_);
         }
         pass_b_stage<true, 0>(x, twB, lane);
         FFT64_MARK(7);
@@ -619,7 +643,7 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
         else
             row_to_col(x, buf, lane);
         FFT64_MARK(8);
-        pass_a<true>(x, a);
+        pass_a<true>(x, a, lane, mark_);
         FFT64_MARK(9);
 #pragma unroll
         for (int i0 = 0; i0 < 32; i0 += 4) {   // four points = eight independent conversion chains at a time

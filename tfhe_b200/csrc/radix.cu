@@ -925,6 +925,7 @@ uint64_t lux_erc20_pbs_count(void) { return get_program(LUX_PROG_ERC20, 64).n_pb
 uint64_t lux_erc20_depth(void) { return get_program(LUX_PROG_ERC20, 64).levels.size(); }
 
 int lux_radix_set_pool_bytes(lux_engine *e, size_t bytes) {
+    LUX_LOCK(e);
     if (!e || bytes == 0) return LUX_ERR_INVALID;
     int rc = radix_init(e);
     if (rc) return rc;
@@ -946,6 +947,7 @@ static int reject_scalar_only(lux_engine *e, lux_op op) {
 }
 
 int lux_eval(lux_engine *e, lux_op op, unsigned bw, const uint64_t *lhs, const uint64_t *rhs, size_t batch, uint64_t *out) {
+    LUX_LOCK(e);
     return guarded(e, [&]() -> int {
         int rc = check_op(e, op, bw, lhs, rhs, out);
         if (rc) return rc;
@@ -957,6 +959,7 @@ int lux_eval(lux_engine *e, lux_op op, unsigned bw, const uint64_t *lhs, const u
     });
 }
 int lux_eval_device(lux_engine *e, lux_op op, unsigned bw, const uint64_t *lhs, const uint64_t *rhs, size_t batch, uint64_t *out) {
+    LUX_LOCK(e);
     return guarded(e, [&]() -> int {
         int rc = check_op(e, op, bw, lhs, rhs, out);
         if (rc) return rc;
@@ -970,6 +973,7 @@ int lux_eval_device(lux_engine *e, lux_op op, unsigned bw, const uint64_t *lhs, 
 }
 
 int lux_trivial_encrypt(lux_engine *e, unsigned bw, const uint64_t *values, size_t batch, uint64_t *out) {
+    LUX_LOCK(e);
     return guarded(e, [&]() -> int {
         const size_t nb = lux_radix_blocks(bw);
         if (!nb || !values || !out) LUX_FAIL(e, LUX_ERR_INVALID, "lux_trivial_encrypt: bad argument");
@@ -1039,21 +1043,25 @@ static int eval_scalar_impl(lux_engine *e, lux_op op, unsigned bw, const uint64_
 }
 
 int lux_eval_scalar(lux_engine *e, lux_op op, unsigned bw, const uint64_t *lhs, const uint64_t *scalars, size_t batch, uint64_t *out) {
+    LUX_LOCK(e);
     return eval_scalar_impl(e, op, bw, lhs, scalars, 1, batch, out);
 }
 int lux_eval_scalar_wide(lux_engine *e, lux_op op, unsigned bw, const uint64_t *lhs, const uint64_t *scalars, size_t n_limbs,
                          size_t batch, uint64_t *out) {
+    LUX_LOCK(e);
     if (e && (n_limbs < 1 || n_limbs > 4)) LUX_FAIL(e, LUX_ERR_INVALID, "n_limbs must be 1..4");
     return eval_scalar_impl(e, op, bw, lhs, scalars, n_limbs, batch, out);
 }
 
 int lux_select(lux_engine *e, unsigned bw, const uint64_t *cond, const uint64_t *a, const uint64_t *b, size_t batch, uint64_t *out) {
+    LUX_LOCK(e);
     return guarded(e, [&]() -> int {
         if (!lux_radix_blocks(bw) || !cond || !a || !b || !out) LUX_FAIL(e, LUX_ERR_INVALID, "lux_select: bad argument");
         return exec_host(e, get_program(LUX_PROG_SELECT, bw), {cond, a, b}, {out}, batch);
     });
 }
 int lux_select_device(lux_engine *e, unsigned bw, const uint64_t *cond, const uint64_t *a, const uint64_t *b, size_t batch, uint64_t *out) {
+    LUX_LOCK(e);
     return guarded(e, [&]() -> int {
         if (!lux_radix_blocks(bw) || !cond || !a || !b || !out) LUX_FAIL(e, LUX_ERR_INVALID, "lux_select_device: bad argument");
         CUDA_TRY(e, cudaSetDevice(e->device));
@@ -1062,6 +1070,7 @@ int lux_select_device(lux_engine *e, unsigned bw, const uint64_t *cond, const ui
 }
 
 int lux_cast(lux_engine *e, unsigned from_width, unsigned to_width, const uint64_t *in, size_t batch, uint64_t *out) {
+    LUX_LOCK(e);
     return guarded(e, [&]() -> int {
         const size_t nf = lux_radix_blocks(from_width), nt = lux_radix_blocks(to_width);
         if (!nf || !nt || !in || !out) LUX_FAIL(e, LUX_ERR_INVALID, "lux_cast: bad argument");
@@ -1078,6 +1087,7 @@ int lux_cast(lux_engine *e, unsigned from_width, unsigned to_width, const uint64
 
 int lux_erc20_transfer(lux_engine *e, const uint64_t *from_bal, const uint64_t *to_bal, const uint64_t *amount, size_t batch,
                        uint64_t *new_from, uint64_t *new_to) {
+    LUX_LOCK(e);
     return guarded(e, [&]() -> int {
         if (!from_bal || !to_bal || !amount || !new_from || !new_to) LUX_FAIL(e, LUX_ERR_INVALID, "lux_erc20_transfer: null argument");
         return exec_host(e, get_program(pick_variant(LUX_PROG_ERC20, 64, batch), 64), {from_bal, to_bal, amount}, {new_from, new_to}, batch);
@@ -1085,6 +1095,7 @@ int lux_erc20_transfer(lux_engine *e, const uint64_t *from_bal, const uint64_t *
 }
 int lux_erc20_transfer_device(lux_engine *e, const uint64_t *from_bal, const uint64_t *to_bal, const uint64_t *amount, size_t batch,
                               uint64_t *new_from, uint64_t *new_to) {
+    LUX_LOCK(e);
     return guarded(e, [&]() -> int {
         if (!from_bal || !to_bal || !amount || !new_from || !new_to) LUX_FAIL(e, LUX_ERR_INVALID, "lux_erc20_transfer_device: null argument");
         CUDA_TRY(e, cudaSetDevice(e->device));
