@@ -108,6 +108,14 @@ int lux_erc20_transfer_device(lux_engine *e, const uint64_t *d_from, const uint6
 uint64_t lux_erc20_pbs_count(void);
 uint64_t lux_erc20_depth(void);
 
+/* the same three calls over every GPU of a lux_multi handle (lux_tfhe.h): shares of whole integers / transfers, one host
+ * thread per GPU, no data-path collective.  BASELINE configs[2..4]: "batch-sharded over 2/4/8 GPUs". */
+int lux_multi_eval(lux_multi *m, lux_op op, unsigned bit_width, const uint64_t *lhs, const uint64_t *rhs, size_t batch, uint64_t *out);
+int lux_multi_select(lux_multi *m, unsigned bit_width, const uint64_t *cond, const uint64_t *a, const uint64_t *b, size_t batch,
+                     uint64_t *out);
+int lux_multi_erc20_transfer(lux_multi *m, const uint64_t *from_bal, const uint64_t *to_bal, const uint64_t *amount, size_t batch,
+                             uint64_t *new_from, uint64_t *new_to);
+
 /* device memory the radix layer may use for intermediate ciphertexts (default 16 GiB); batches that need
  * more are processed in chunks */
 int lux_radix_set_pool_bytes(lux_engine *e, size_t bytes);

@@ -16,13 +16,16 @@
  *
  * Conventions
  *   - every function returns LUX_OK (0) or a negative lux_status; nothing aborts the process
- *   - all values are canonical Goldilocks elements (uint64_t < q = 2^64 - 2^32 + 1), little-endian
+ *   - all values are canonical Goldilocks elements (uint64_t < q = 2^64 - 2^32 + 1), little-endian; engines created with
+ *     arith = LUX_ARITH_TORUS64_FFT carry torus words (any uint64_t, arithmetic mod 2^64) instead
  *   - layouts are the reference's flatten() orders (crypto/ggsw.rs:62-64, glev.rs:52-54, glwe.rs:133-135):
  *       LWE  [n+1] = mask..., body          GLWE [(k+1)][N] = mask polys..., body poly
  *       GGSW [(k+1)][ell][(k+1)][N]         BSK [n] GGSW          LWE-KSK [k*N][ell_ks][n+1]
  *   - host pointers unless the function name ends in _device; the caller owns every buffer it
  *     passes; the engine owns device memory; no pointer outlives the call except handles
- *   - calls on one engine are serialised by the caller (one engine per GPU, one process per GPU)
+ *   - every entry point is blocking and thread-safe per engine: calls on one engine from several host threads are serialised
+ *     inside the library (a per-engine lock held for the whole call); calls on different engines run concurrently.
+ *     lux_last_error() returns the message of the calling thread's own last failure on that engine
  *   - no CPU fallback exists: without a CUDA device lux_engine_create fails with LUX_ERR_NO_DEVICE
  */
 #ifndef LUX_TFHE_H
@@ -111,6 +114,25 @@ int lux_load_lwe_ksk(lux_engine *e, const uint64_t *ksk, size_t n_words);       
 size_t lux_key_blob_bytes(const lux_engine *e);
 int lux_export_keys_device(lux_engine *e, void *dev_blob, size_t bytes);
 int lux_import_keys_device(lux_engine *e, const void *dev_blob, size_t bytes);
+
+/* ---- several GPUs of one box behind one handle --------------------------------------------------
+ * the boundary is create(params, n_gpus).  The reference's host (a Node process: packages/wasm/src/node.ts:29-63
+ * loads ONE evaluator; js/v2-sdk/src/luxd/client.ts:128-147 posts whole batches) has no collective library of its own, so
+ * replication and sharding happen inside this library: one engine per GPU, keys converted on GPU 0 and copied device to
+ * device to the others, every batch call slices its batch into contiguous shares (whole kernel waves where the batch is large
+ * enough) run by one host thread per GPU.  n_gpus <= 0 takes every visible device.  Calls on one handle are serialised. */
+typedef struct lux_multi lux_multi;
+int lux_engine_create_multi(const lux_params *p, int n_gpus, lux_multi **out);
+void lux_multi_destroy(lux_multi *m);
+int lux_multi_gpus(const lux_multi *m);
+lux_engine *lux_multi_engine(lux_multi *m, int i);                 /* engine of GPU i (owned by the handle) */
+const char *lux_multi_last_error(const lux_multi *m);
+int lux_multi_load_bsk(lux_multi *m, const uint64_t *bsk, size_t n_words, int domain);
+int lux_multi_load_glwe_ksk(lux_multi *m, const uint64_t *ksk, size_t n_words, int domain);
+int lux_multi_load_lwe_ksk(lux_multi *m, const uint64_t *ksk, size_t n_words);
+int lux_multi_replicate_keys(lux_multi *m);                        /* after the last load: GPU 0's resident keys -> all GPUs */
+int lux_multi_pbs_batch(lux_multi *m, const uint64_t *lwe_in, const uint64_t *testvs, uint32_t n_luts,
+                        const uint32_t *lut_idx, size_t B, uint64_t *lwe_out);
 
 /* ---- programmable bootstrap, batched ------------------------------------------------------------
  * lwe_in  [B][ct_words]   testvs [n_luts][N] test-vector polynomials (crypto/mod.rs:17-27)

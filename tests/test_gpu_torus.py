@@ -232,3 +232,69 @@ def test_decryption_gate_65536_trials(arith):
     assert res["trials"] == 65536 and res["wrong_decryptions"] == 0, res
     assert res["variance_within_bound"], res
     assert res["bit_exact_vs_oracle_checked"] >= 4 * 6
+
+
+# ------------------------------------------------------------------------------------------- boundary: threads, several GPUs
+def test_concurrent_calls_on_one_engine_are_serialised(rig_small):
+    """SURVEY 8b "blocking and thread-safe per engine": four host threads hammer ONE engine with different batches (ctypes
+    releases the GIL, so the calls really overlap); every result equals the serial one"""
+    import threading
+
+    e, p, ks = rig_small.eng, rig_small.p, rig_small.ks
+    dl = T.delta(32, p.arith)
+    tvs = np.stack([T.make_testv(p.N, 16, dl, [(x * k + 1) % 16 for x in range(16)], p.arith) for k in range(4)])
+    jobs = []
+    for t in range(4):
+        msgs = (np.arange(5 + 3 * t, dtype=np.uint64) * np.uint64(t + 1)) % np.uint64(16)
+        cts = TO.lwe_encrypt_batch(100 + t, ks.s_in, msgs * np.uint64(dl), rig_small.glwe_noise)
+        idx = (np.arange(len(msgs)) % 4).astype(np.uint32)
+        jobs.append((cts, idx, e.pbs_batch(cts, tvs, idx)))
+    got = [None] * 4
+    errs = []
+
+    def work(t):
+        try:
+            for _ in range(6):
+                got[t] = e.pbs_batch(jobs[t][0], tvs, jobs[t][1])
+        except Exception as ex:  # noqa: BLE001
+            errs.append(ex)
+
+    th = [threading.Thread(target=work, args=(t,)) for t in range(4)]
+    [x.start() for x in th]
+    [x.join() for x in th]
+    assert not errs, errs
+    for t in range(4):
+        assert np.array_equal(got[t], jobs[t][2]), f"thread {t}: concurrent result differs from the serial one"
+
+
+def test_multi_gpu_handle_matches_single_engine(rig_small):
+    """lux_engine_create_multi: keys converted on GPU 0 and copied to the others inside the library, the batch sliced over
+    the GPUs (every visible one; a 1-GPU box still runs the whole path): same words as the single-engine call, which the
+    other tests pin to the oracle.  Ragged batch so that the shares differ in size."""
+    import torch
+
+    p, ks = rig_small.p, rig_small.ks
+    n = torch.cuda.device_count()
+    m = T.MultiEngine(p, 0)
+    assert m.n_gpus == n
+    m.load_keyset(ks)
+    dl = T.delta(32, p.arith)
+    tvs = np.stack([T.make_testv(p.N, 16, dl, [(x + k) % 16 for x in range(16)], p.arith) for k in range(3)])
+    B = 7 * n + 3
+    msgs = np.arange(B, dtype=np.uint64) % np.uint64(16)
+    idx = (np.arange(B) % 3).astype(np.uint32)
+    cts = TO.lwe_encrypt_batch(77, ks.s_in, msgs * np.uint64(dl), rig_small.glwe_noise)
+    got = m.pbs_batch(cts, tvs, idx)
+    want = rig_small.eng.pbs_batch(cts, tvs, idx)
+    assert np.array_equal(got, want)
+    ora, _ = rig_small.ctx.pbs_batch(cts, tvs, idx)
+    assert np.array_equal(got, ora)
+    # euintN ops through the same handle
+    import tfhe_b200.radix as R
+    from oracle.radix import split_blocks
+    mr, sr = R.MultiRadix(m), R.Radix(rig_small.eng)
+    vals = [(37 * i + 5) & 0xFF for i in range(2 * n + 1)]
+    dig = np.array([split_blocks(v, 4) for v in vals], dtype=np.uint64).reshape(-1)
+    a = TO.lwe_encrypt_batch(78, ks.s_in, dig * np.uint64(dl), rig_small.glwe_noise).reshape(len(vals), 4, p.ct_len)
+    assert np.array_equal(mr.eval("add", 8, a, a[::-1].copy()), sr.eval("add", 8, a, a[::-1].copy()))
+    assert np.array_equal(mr.eval("lt", 8, a, a[::-1].copy()), sr.eval("lt", 8, a, a[::-1].copy()))

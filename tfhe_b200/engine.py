@@ -136,6 +136,16 @@ ABI = {
     "lux_lwe_keyswitch": (_int, [_vp, _u64p, _sz, _u64p]),
     "lux_blind_rotate": (_int, [_vp, _u64p, _u64p, _u32, _vp, _sz, _u32, _u64p]),
     "lux_external_product": (_int, [_vp, _u64p, _int, _u64p, _sz, _u64p]),
+    "lux_engine_create_multi": (_int, [C.POINTER(_CParams), _int, C.POINTER(_vp)]),
+    "lux_multi_destroy": (None, [_vp]),
+    "lux_multi_gpus": (_int, [_vp]),
+    "lux_multi_engine": (_vp, [_vp, _int]),
+    "lux_multi_last_error": (C.c_char_p, [_vp]),
+    "lux_multi_load_bsk": (_int, [_vp, _u64p, _sz, _int]),
+    "lux_multi_load_glwe_ksk": (_int, [_vp, _u64p, _sz, _int]),
+    "lux_multi_load_lwe_ksk": (_int, [_vp, _u64p, _sz]),
+    "lux_multi_replicate_keys": (_int, [_vp]),
+    "lux_multi_pbs_batch": (_int, [_vp, _vp, _vp, _u32, _vp, _sz, _vp]),
 }
 
 
@@ -467,4 +477,57 @@ class Engine:
         assert g.shape[0] == x.shape[0]
         out = np.empty_like(x)
         self._ck(lib().lux_external_product(self._h, g.reshape(-1), domain, x.reshape(-1), x.shape[0], out.reshape(-1)))
+        return out
+
+
+class MultiEngine:
+    """Several GPUs of one box behind one handle (lux_engine_create_multi): keys converted on GPU 0 and copied device to
+    device, batches sliced over the GPUs inside the library with one host thread per GPU.  No torch, no NCCL: this is the
+    path a Node / ctypes host uses.  n_gpus <= 0 takes every visible device."""
+
+    def __init__(self, params: Params, n_gpus: int = 0):
+        self.p = params
+        h = _vp()
+        cp = params.c()
+        rc = lib().lux_engine_create_multi(C.byref(cp), n_gpus, C.byref(h))
+        if rc:
+            raise LuxError(rc, lib().lux_multi_last_error(None).decode())
+        self._h = h
+
+    def __del__(self):
+        try:
+            if getattr(self, "_h", None):
+                lib().lux_multi_destroy(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+    def _ck(self, rc):
+        if rc:
+            raise LuxError(rc, lib().lux_multi_last_error(self._h).decode())
+
+    @property
+    def n_gpus(self) -> int:
+        return lib().lux_multi_gpus(self._h)
+
+    def load_keyset(self, ks):
+        """ks: any object with .bsk and .glwe_ksk / .lwe_ksk (standard domain); converts on GPU 0, replicates to all"""
+        b = _u64arr(ks.bsk).reshape(-1)
+        self._ck(lib().lux_multi_load_bsk(self._h, b, b.size, DOMAIN_STANDARD))
+        if getattr(ks, "glwe_ksk", None) is not None:
+            g = _u64arr(ks.glwe_ksk).reshape(-1)
+            self._ck(lib().lux_multi_load_glwe_ksk(self._h, g, g.size, DOMAIN_STANDARD))
+        if getattr(ks, "lwe_ksk", None) is not None:
+            k = _u64arr(ks.lwe_ksk).reshape(-1)
+            self._ck(lib().lux_multi_load_lwe_ksk(self._h, k, k.size))
+        self._ck(lib().lux_multi_replicate_keys(self._h))
+
+    def pbs_batch(self, lwe_in, testvs, lut_idx=None, out=None):
+        x = _u64arr(lwe_in).reshape(-1, self.p.ct_len)
+        tv = _u64arr(testvs).reshape(-1, self.p.N)
+        idx = None if lut_idx is None else np.ascontiguousarray(lut_idx, dtype=np.uint32)
+        if out is None:
+            out = np.empty_like(x)
+        self._ck(lib().lux_multi_pbs_batch(self._h, x.ctypes.data, tv.ctypes.data, tv.shape[0],
+                                           None if idx is None else idx.ctypes.data, x.shape[0], out.ctypes.data))
         return out

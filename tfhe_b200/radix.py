@@ -48,6 +48,9 @@ ABI = {
     "lux_erc20_pbs_count": (_u64, []),
     "lux_erc20_depth": (_u64, []),
     "lux_radix_set_pool_bytes": (_int, [_vp, _sz]),
+    "lux_multi_eval": (_int, [_vp, _int, _uint, _vp, _vp, _sz, _vp]),
+    "lux_multi_select": (_int, [_vp, _uint, _vp, _vp, _vp, _sz, _vp]),
+    "lux_multi_erc20_transfer": (_int, [_vp, _vp, _vp, _vp, _sz, _vp, _vp]),
     "lux_radix_program": (_sz, [_int, _uint, _vp, _sz]),
     "lux_radix_lut": (_int, [_int, _vp]),
 }
@@ -241,3 +244,42 @@ class Radix:
 
     def set_pool_bytes(self, n: int):
         self._ck(lib().lux_radix_set_pool_bytes(self.e._h, n))
+
+
+class MultiRadix:
+    """euintN evaluator over every GPU of a MultiEngine: shares of whole integers, sliced inside the library."""
+
+    def __init__(self, multi):
+        self.m = multi
+        self.w = multi.p.ct_len
+        lib()
+
+    def eval(self, op: str, bit_width: int, lhs, rhs=None):
+        nb = blocks(bit_width)
+        lhs = _arr(lhs).reshape(-1, nb, self.w)
+        B = lhs.shape[0]
+        rp = None
+        if op not in UNARY:
+            rhs = _arr(rhs).reshape(B, nb, self.w)
+            rp = rhs.ctypes.data
+        out = np.empty((B, 1 if op in PREDICATES else nb, self.w), np.uint64)
+        self.m._ck(lib().lux_multi_eval(self.m._h, OPS[op], bit_width, lhs.ctypes.data, rp, B, out.ctypes.data))
+        return out
+
+    def select(self, bit_width: int, cond, a, b):
+        nb = blocks(bit_width)
+        a = _arr(a).reshape(-1, nb, self.w)
+        B = a.shape[0]
+        b = _arr(b).reshape(B, nb, self.w)
+        cond = _arr(cond).reshape(B, self.w)
+        out = np.empty_like(a)
+        self.m._ck(lib().lux_multi_select(self.m._h, bit_width, cond.ctypes.data, a.ctypes.data, b.ctypes.data, B, out.ctypes.data))
+        return out
+
+    def erc20_transfer(self, from_bal, to_bal, amount):
+        f = _arr(from_bal).reshape(-1, 32, self.w)
+        B = f.shape[0]
+        t, a = _arr(to_bal).reshape(B, 32, self.w), _arr(amount).reshape(B, 32, self.w)
+        nf, nt = np.empty_like(f), np.empty_like(t)
+        self.m._ck(lib().lux_multi_erc20_transfer(self.m._h, f.ctypes.data, t.ctypes.data, a.ctypes.data, B, nf.ctypes.data, nt.ctypes.data))
+        return nf, nt
