@@ -45,7 +45,9 @@ typedef enum {
     LUX_ERR_NO_DEVICE = -2,   /* no usable CUDA device */
     LUX_ERR_CUDA = -3,        /* CUDA runtime error (message in lux_last_error) */
     LUX_ERR_NO_KEY = -4,      /* evaluation key needed by the call has not been loaded */
-    LUX_ERR_OOM = -5
+    LUX_ERR_OOM = -5,
+    LUX_ERR_FORMAT = -6,      /* serialized container: bad magic, version, length or checksum */
+    LUX_ERR_MISMATCH = -7     /* serialized container is valid but for another parameter set / arithmetic / kind */
 } lux_status;
 
 /* order of key switch and bootstrap inside one PBS */
@@ -133,6 +135,35 @@ int lux_multi_load_lwe_ksk(lux_multi *m, const uint64_t *ksk, size_t n_words);
 int lux_multi_replicate_keys(lux_multi *m);                        /* after the last load: GPU 0's resident keys -> all GPUs */
 int lux_multi_pbs_batch(lux_multi *m, const uint64_t *lwe_in, const uint64_t *testvs, uint32_t n_luts,
                         const uint32_t *lut_idx, size_t B, uint64_t *lwe_out);
+
+/* ---- serialized keys and ciphertexts ------------------------------------------------------------
+ * The reference moves keys and ciphertexts BY VALUE as opaque bytes (packages/wasm/src/node.ts:65-96 Uint8Array,
+ * js/v2-sdk/src/luxd/client.ts:128-147,232-244 number[]).  The producers of those bytes (Go luxfi/tfhe, tfhe-rs safe_serialize)
+ * are out of tree, so this is the engine's own container, not a converter: an 80-byte little-endian header (magic, version,
+ * kind, lux_params, aux, count, payload length, CRC-32 of payload and of header) followed by the words of the layouts above.
+ * aux = bit width for LUX_BLOB_RADIX (0 for LUX_BLOB_LWE), LUX_DOMAIN_* for keys.  Host-only, no GPU needed. */
+typedef enum {
+    LUX_BLOB_LWE = 1,       /* count LWE ciphertexts [count][ct_words] */
+    LUX_BLOB_RADIX = 2,     /* count euintN integers [count][blocks][ct_words], aux = N */
+    LUX_BLOB_BSK = 3,
+    LUX_BLOB_GLWE_KSK = 4,
+    LUX_BLOB_LWE_KSK = 5
+} lux_blob_kind;
+typedef struct {
+    uint32_t version, kind;
+    lux_params params;
+    uint32_t aux;
+    uint64_t count, payload_words;
+} lux_blob_info;
+size_t lux_serialized_bytes(const lux_params *p, uint32_t kind, uint32_t aux, uint64_t count);    /* 0 = invalid combination */
+int lux_serialize(const lux_params *p, uint32_t kind, uint32_t aux, uint64_t count, const uint64_t *words, uint8_t *out, size_t cap);
+int lux_blob_inspect(const uint8_t *blob, size_t bytes, lux_blob_info *info);                     /* header only */
+/* checks header, payload CRC and, when given, that the container matches `expect` / `expect_kind` (LUX_ERR_MISMATCH
+ * otherwise); copies the payload to words_out when it is not NULL */
+int lux_deserialize(const uint8_t *blob, size_t bytes, const lux_params *expect, uint32_t expect_kind, uint64_t *words_out,
+                    size_t cap_words, lux_blob_info *info);
+/* a serialized evaluation key -> this engine; a key of another parameter set or arithmetic is refused */
+int lux_load_key_blob(lux_engine *e, const uint8_t *blob, size_t bytes);
 
 /* ---- programmable bootstrap, batched ------------------------------------------------------------
  * lwe_in  [B][ct_words]   testvs [n_luts][N] test-vector polynomials (crypto/mod.rs:17-27)

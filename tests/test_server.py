@@ -158,3 +158,74 @@ def test_server_drives_the_gpu_engine():
         httpd.shutdown()
         co.close()
         httpd.server_close()
+
+
+def test_hostile_requests_are_rejected_cheaply(srv):
+    """a JSON integer as an operand must not become bytes(int) (that many zero bytes), a boolean is not a
+    bit width, an unknown op is refused before it can open a coalescing window, and the body size is capped"""
+    url, co = srv
+    co2 = S.EvalCoalescer(plain_eval, blocks, W, window_s=0.01, max_batch=4)
+    try:
+        for bad in (20_000_000_000, "AAAA", {"0": 1}, [256] * (4 * W * 8), [-1] * (4 * W * 8), [0.5] * (4 * W * 8), [1, 2, 3]):
+            with pytest.raises(S.BadRequest):
+                co2.parse("add", 8, bad, list(enc(1, 8)))
+        with pytest.raises(S.BadRequest):
+            co2.parse("add", True, list(enc(1, 8)), list(enc(1, 8)))
+        with pytest.raises(S.BadRequest):
+            co2.parse("frobnicate", 8, list(enc(1, 8)), list(enc(1, 8)))
+        lhs, rhs = co2.parse("add", 8, list(enc(3, 8)), list(enc(4, 8)))
+        assert lhs.shape == (4, W) and int(lhs[0, 0]) == 3
+    finally:
+        co2.close()
+    n_before = len(co.batches)
+    req = urllib.request.Request(url + "/evaluate", data=json.dumps({"op": "add", "bitWidth": 8, "left": 20_000_000_000,
+                                                                       "right": list(enc(1, 8))}).encode(), method="POST")
+    with pytest.raises(urllib.error.HTTPError) as ei:
+        urllib.request.urlopen(req, timeout=10)
+    assert ei.value.code == 400
+    big = urllib.request.Request(url + "/evaluate", data=b"x" * (2 * S.MAX_BLOCKS * W * 8 * 4 + 5000), method="POST")
+    with pytest.raises((urllib.error.HTTPError, urllib.error.URLError, ConnectionError)) as ei:
+        urllib.request.urlopen(big, timeout=10)
+    if isinstance(ei.value, urllib.error.HTTPError):
+        assert ei.value.code == 413
+    assert len(co.batches) == n_before          # nothing reached the evaluator
+
+
+def test_serialized_containers_in_and_out():
+    """operands may be self-describing containers (lux_serialize): the server checks parameter set, kind and width and
+    answers with a container; a container of another width or parameter set is a 400, not a garbage result"""
+    import tfhe_b200 as T
+    from tfhe_b200 import engine as E
+
+    P = T.Params(n=3, N=512, k=1, ell=2, logB=16, ell_ks=8, logB_ks=4, order=T.ORDER_PBS_GLWEKS)   # ct words = n + 1 = 4
+    w = P.ct_len
+
+    def ev(op, bw, lhs, rhs):
+        out = lhs.copy()
+        out[:, :, 0] = (lhs[:, :, 0] + rhs[:, :, 0]) % 4
+        return out[:, :1] if op in S.PREDICATES else out
+
+    co = S.EvalCoalescer(ev, blocks, w, window_s=0.01, max_batch=8, params=P)
+    try:
+        a = np.zeros((4, w), np.uint64)
+        a[:, 0] = [1, 2, 3, 0]
+        b = np.ones((4, w), np.uint64)
+        ca, cb = E.serialize(P, E.BLOB_RADIX, a, 8, 1), E.serialize(P, E.BLOB_RADIX, b, 8, 1)
+        out = co.submit("add", 8, list(ca), list(cb)).result(timeout=10)
+        words, info = E.deserialize(out, P, E.BLOB_RADIX)
+        assert info["aux"] == 8 and words.reshape(4, w)[:, 0].tolist() == [2, 3, 0, 1]
+        raw = co.submit("add", 8, list(a.tobytes()), list(b.tobytes())).result(timeout=10)       # bare words still work
+        assert np.frombuffer(raw, "<u8").reshape(4, w)[:, 0].tolist() == [2, 3, 0, 1]
+        pred = co.submit("lt", 8, list(ca), list(cb)).result(timeout=10)
+        assert E.deserialize(pred, P, E.BLOB_RADIX)[1]["aux"] == 2
+        with pytest.raises(S.BadRequest):
+            co.submit("add", 16, list(ca), list(cb))                      # width in the request != width in the container
+        other = T.Params(**{**P.__dict__, "logB": 15})
+        with pytest.raises(S.BadRequest):
+            co.submit("add", 8, list(E.serialize(other, E.BLOB_RADIX, a, 8, 1)), list(cb))
+        bad = bytearray(ca)
+        bad[200] ^= 1
+        with pytest.raises(S.BadRequest):
+            co.submit("add", 8, list(bad), list(cb))
+    finally:
+        co.close()

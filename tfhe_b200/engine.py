@@ -136,6 +136,11 @@ ABI = {
     "lux_lwe_keyswitch": (_int, [_vp, _u64p, _sz, _u64p]),
     "lux_blind_rotate": (_int, [_vp, _u64p, _u64p, _u32, _vp, _sz, _u32, _u64p]),
     "lux_external_product": (_int, [_vp, _u64p, _int, _u64p, _sz, _u64p]),
+    "lux_serialized_bytes": (_sz, [C.POINTER(_CParams), _u32, _u32, _u64]),
+    "lux_serialize": (_int, [C.POINTER(_CParams), _u32, _u32, _u64, _vp, _vp, _sz]),
+    "lux_blob_inspect": (_int, [_vp, _sz, _vp]),
+    "lux_deserialize": (_int, [_vp, _sz, _vp, _u32, _vp, _sz, _vp]),
+    "lux_load_key_blob": (_int, [_vp, _vp, _sz]),
     "lux_engine_create_multi": (_int, [C.POINTER(_CParams), _int, C.POINTER(_vp)]),
     "lux_multi_destroy": (None, [_vp]),
     "lux_multi_gpus": (_int, [_vp]),
@@ -262,6 +267,12 @@ class Engine:
             self.load_glwe_ksk(ks.glwe_ksk)
         if getattr(ks, "lwe_ksk", None) is not None:
             self.load_lwe_ksk(ks.lwe_ksk)
+
+    def load_key_blob(self, blob: bytes):
+        """one serialized evaluation key (serialize(..., BLOB_BSK / BLOB_LWE_KSK / BLOB_GLWE_KSK)): refused unless it was
+        made for this engine's parameter set and arithmetic"""
+        buf = np.frombuffer(blob, np.uint8)
+        self._ck(lib().lux_load_key_blob(self._h, buf.ctypes.data, buf.size))
 
     @property
     def key_blob_bytes(self) -> int:
@@ -478,6 +489,50 @@ class Engine:
         out = np.empty_like(x)
         self._ck(lib().lux_external_product(self._h, g.reshape(-1), domain, x.reshape(-1), x.shape[0], out.reshape(-1)))
         return out
+
+
+# ---- serialized containers (include/lux_tfhe.h "serialized keys and ciphertexts"); host-only ----------------------------
+BLOB_LWE, BLOB_RADIX, BLOB_BSK, BLOB_GLWE_KSK, BLOB_LWE_KSK = 1, 2, 3, 4, 5
+ERR_FORMAT, ERR_MISMATCH = -6, -7
+
+
+class _CBlobInfo(C.Structure):
+    _fields_ = [("version", C.c_uint32), ("kind", C.c_uint32), ("params", _CParams), ("aux", C.c_uint32),
+                ("count", C.c_uint64), ("payload_words", C.c_uint64)]
+
+
+def serialize(params: Params, kind: int, words, aux: int = 0, count: int = 1) -> bytes:
+    """words of `count` objects of `kind` -> one self-describing container (bytes)"""
+    w = _u64arr(words).reshape(-1)
+    cp = params.c()
+    n = lib().lux_serialized_bytes(C.byref(cp), kind, aux, count)
+    if n == 0 or n != 80 + 8 * w.size:
+        raise LuxError(-1, f"{w.size} words do not make {count} object(s) of kind {kind} (aux {aux}) at these parameters")
+    out = np.empty(n, np.uint8)
+    rc = lib().lux_serialize(C.byref(cp), kind, aux, count, w.ctypes.data, out.ctypes.data, n)
+    if rc:
+        raise LuxError(rc, "lux_serialize failed")
+    return out.tobytes()
+
+
+def deserialize(blob: bytes, expect: Params | None = None, expect_kind: int = 0):
+    """-> (words, info dict); raises LuxError(ERR_FORMAT) for a damaged container, LuxError(ERR_MISMATCH) for a valid
+    one that belongs to another parameter set / arithmetic / kind"""
+    buf = np.frombuffer(blob, np.uint8)
+    info = _CBlobInfo()
+    rc = lib().lux_blob_inspect(buf.ctypes.data, buf.size, C.byref(info))
+    if rc:
+        raise LuxError(rc, "not a valid container (bad magic, version, length or header checksum)")
+    out = np.empty(info.payload_words, np.uint64)
+    cp = expect.c() if expect is not None else None
+    rc = lib().lux_deserialize(buf.ctypes.data, buf.size, C.byref(cp) if cp is not None else None, expect_kind,
+                               out.ctypes.data, out.size, C.byref(info))
+    if rc:
+        raise LuxError(rc, "container is for another parameter set / arithmetic / kind" if rc == ERR_MISMATCH
+                       else "container payload is damaged (checksum)")
+    p = info.params
+    return out, {"version": info.version, "kind": info.kind, "aux": info.aux, "count": info.count,
+                 "params": Params(p.n, p.N, p.k, p.ell, p.logB, p.ell_ks, p.logB_ks, p.order, p.arith)}
 
 
 class MultiEngine:

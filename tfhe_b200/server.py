@@ -28,6 +28,9 @@ import numpy as np
 # op names of client.ts:35 plus the rest of lux_radix.h's lux_op (same spelling as tfhe_b200.radix.OPS)
 UNARY = {"neg", "not"}
 PREDICATES = {"eq", "ne", "lt", "le", "gt", "ge"}
+OPS = {"add", "sub", "mul", "neg", "eq", "ne", "lt", "le", "gt", "ge", "min", "max", "and", "or", "xor", "not", "shl", "shr",
+       "rotl", "rotr"}       # encrypted-operand ops of lux_radix.h (div / rem take a plaintext divisor: not an /evaluate op)
+MAX_BLOCKS = 128             # euint256: the largest ciphertext an /evaluate request can carry
 
 
 class BadRequest(ValueError):
@@ -40,8 +43,9 @@ class EvalCoalescer:
     `evaluate(op, bit_width, lhs, rhs_or_None) -> out` is the batch evaluator ([batch][blocks][w] u64 arrays);
     the GPU server passes `Radix.eval`, the CPU tests pass a plaintext stand-in."""
 
-    def __init__(self, evaluate, blocks, ct_words, window_s=0.002, max_batch=4096):
+    def __init__(self, evaluate, blocks, ct_words, window_s=0.002, max_batch=4096, params=None):
         self._evaluate, self._blocks, self.w = evaluate, blocks, ct_words
+        self.params = params       # engine parameter set: operands may then be serialized containers (lux_serialize)
         self.window_s, self.max_batch = window_s, max_batch
         self._q: queue.Queue = queue.Queue()
         self.batches = []          # sizes of the batches evaluated so far (introspection for tests / metrics)
@@ -55,21 +59,50 @@ class EvalCoalescer:
     # ---- request side -----------------------------------------------------------------------------------
     def parse(self, op, bit_width, left, right):
         """validate one request, bytes -> u64 words; raises BadRequest with the text the client shows"""
-        nb = self._blocks(int(bit_width)) if isinstance(bit_width, int) else 0
+        return self._parse(op, bit_width, left, right)[:2]
+
+    def _parse(self, op, bit_width, left, right):
+        # bool is an int subclass: True must not pass for bitWidth 1
+        nb = self._blocks(bit_width) if isinstance(bit_width, int) and not isinstance(bit_width, bool) else 0
         if not nb:
             raise BadRequest(f"unsupported bitWidth {bit_width!r}")
-        if not isinstance(op, str):
-            raise BadRequest("op must be a string")
+        if not isinstance(op, str) or op not in OPS:
+            raise BadRequest(f"unknown op {op!r}")     # rejected here, before the request can open a coalescing window
         want = nb * self.w * 8
 
         def words(name, v):
-            try:
+            # only a JSON array of exactly `want` byte values (or want + 80: a serialized container) is accepted:
+            # bytes(int) would ALLOCATE that many bytes (a one-request memory DoS), a str or dict is not a ciphertext
+            if isinstance(v, (bytes, bytearray)):
                 b = bytes(v)
-            except (TypeError, ValueError):
+            elif isinstance(v, (list, tuple)):
+                if len(v) != want and not (self.params is not None and len(v) == want + 80):
+                    raise BadRequest(f"{name} has {len(v)} bytes, a euint{bit_width} ciphertext has {want}")
+                try:
+                    arr = np.asarray(v)
+                    if arr.dtype.kind not in "iu" or arr.ndim != 1 or arr.min(initial=0) < 0 or arr.max(initial=0) > 255:
+                        raise ValueError
+                    b = arr.astype(np.uint8).tobytes()
+                except (TypeError, ValueError, OverflowError):
+                    raise BadRequest(f"{name} must be an array of bytes")
+            else:
                 raise BadRequest(f"{name} must be an array of bytes")
+            if self.params is not None and len(b) == want + 80 and b[:8] == b"LUXFHE\r\n":
+                # self-describing container: parameter set, arithmetic, kind and width are checked, not assumed
+                from . import engine as E
+                try:
+                    wds, info = E.deserialize(b, self.params, E.BLOB_RADIX)
+                except E.LuxError as ex:
+                    raise BadRequest(f"{name}: {ex}")
+                if info["aux"] != bit_width or info["count"] != 1:
+                    raise BadRequest(f"{name} is a container of {info['count']} euint{info['aux']}, the request says one euint{bit_width}")
+                containers.append(name)
+                return wds.reshape(nb, self.w)
             if len(b) != want:
                 raise BadRequest(f"{name} has {len(b)} bytes, a euint{bit_width} ciphertext has {want}")
             return np.frombuffer(b, dtype="<u8").reshape(nb, self.w)
+
+        containers = []
 
         lhs = words("left", left)
         if op in UNARY:
@@ -80,13 +113,27 @@ class EvalCoalescer:
             if right is None:
                 raise BadRequest(f"op {op} needs a right operand")
             rhs = words("right", right)
-        return lhs, rhs
+        return lhs, rhs, bool(containers)
 
     def submit(self, op, bit_width, left, right=None) -> Future:
-        lhs, rhs = self.parse(op, bit_width, left, right)
-        fut: Future = Future()
-        self._q.put((op, int(bit_width), lhs, rhs, fut))
-        return fut
+        lhs, rhs, wrap = self._parse(op, bit_width, left, right)
+        inner: Future = Future()
+        self._q.put((op, int(bit_width), lhs, rhs, inner))
+        if not wrap:
+            return inner
+        # operands came as containers: the answer goes back as one (a predicate is a euint2, i.e. one block)
+        outer: Future = Future()
+
+        def done(f):
+            try:
+                from . import engine as E
+                raw = np.frombuffer(f.result(), dtype="<u8")
+                outer.set_result(E.serialize(self.params, E.BLOB_RADIX, raw, 2 if op in PREDICATES else int(bit_width), 1))
+            except Exception as ex:  # noqa: BLE001
+                outer.set_exception(ex)
+
+        inner.add_done_callback(done)
+        return outer
 
     # ---- worker -----------------------------------------------------------------------------------------
     def _run(self):
@@ -161,7 +208,16 @@ def make_handler(coalescer: EvalCoalescer, public_key_path=None, version="tfhe_b
                 self._send(404, b"not found", "text/plain")
 
         def do_POST(self):
-            n = int(self.headers.get("Content-Length", "0"))
+            try:
+                n = int(self.headers.get("Content-Length", "0"))
+            except ValueError:
+                n = -1
+            # a request is two euint256 operands as JSON byte arrays (<= 4 characters per byte) plus a little framing
+            limit = 2 * MAX_BLOCKS * coalescer.w * 8 * 4 + 4096
+            if n < 0 or n > limit:
+                self._send(413, f"request body of {n} bytes exceeds the {limit}-byte limit".encode(), "text/plain")
+                self.close_connection = True
+                return
             body = self.rfile.read(n)
             if self.path in ("/encrypt", "/decrypt", "/threshold/decrypt", "/verify"):
                 self._send(501, b"key generation, encryption and decryption stay on the reference path", "text/plain")
@@ -194,7 +250,7 @@ def serve(engine, host="127.0.0.1", port=8448, window_s=0.002, max_batch=4096, p
             raise BadRequest(f"unknown op {op}")
         return rx.eval(op, bw, lhs, rhs)
 
-    co = EvalCoalescer(evaluate, R.blocks, engine.p.ct_len, window_s, max_batch)
+    co = EvalCoalescer(evaluate, R.blocks, engine.p.ct_len, window_s, max_batch, params=engine.p)
     srv = ThreadingHTTPServer((host, port), make_handler(co, public_key_path))
     try:
         srv.serve_forever()

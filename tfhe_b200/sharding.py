@@ -36,9 +36,17 @@ def replicate_keys(engine, rank: int, world: int, src: int = 0, device=None):
     import torch.distributed as dist
 
     blob = torch.empty(engine.key_blob_bytes, dtype=torch.uint8, device=device if device is not None else "cuda")
+    on_gpu = blob.is_cuda
     if rank == src:
-        engine.export_keys_device(blob)
+        engine.export_keys_device(blob)       # synchronises the engine's own stream before returning
+    # the broadcast is ordered on torch's CURRENT stream only, the engine reads the blob on its own non-blocking stream
+    # (and its header through the legacy default stream): without these two synchronisations the import could race the
+    # NCCL copy whenever the caller runs under a non-default torch stream and load partial keys without any error
+    if on_gpu:
+        torch.cuda.current_stream().synchronize()
     dist.broadcast(blob, src)
+    if on_gpu:
+        torch.cuda.current_stream().synchronize()
     if rank != src:
         engine.import_keys_device(blob)
 
