@@ -8,17 +8,21 @@
  * the caller hands over evaluation keys and ciphertexts as little-endian u64 arrays (SURVEY.md 8b "wire formats").
  *
  * Differences a caller of the reference sees:
- *   - `init()` returns an object bound to one GPU; the bootstrap key is uploaded ONCE (`loadKeys`) and is no
- *     longer an argument of every call (`add(ct1, ct2, bootstrapKey, secretKey)` -> `add(ct1, ct2)`);
+ *   - `init()` returns an object bound to one GPU, or to several with `params.gpus` (the library replicates the keys and
+ *     slices every batch itself); the bootstrap key is uploaded ONCE (`loadKeys`), which returns the handle that takes the
+ *     place of the `bootstrapKey` string: `add(ct1, ct2, bootstrapKey, secretKey)` keeps its name and arity, with
+ *     ciphertexts as base64 strings of the engine's self-describing container and `secretKey` ignored;
  *   - every op has a `*Batch` form that takes `batch` integers in one BigUint64Array
  *     ([batch][blocks][ctWords]); the single-ciphertext methods are the batch-of-one case;
- *   - evaluation methods return Promises (the addon runs them on the libuv pool);
+ *   - evaluation methods return Promises (the addon runs them on the libuv pool; several un-awaited calls on one engine
+ *     are safe: the library serialises them per engine);
  *   - errors keep the reference's messages where it has them ("LuxFHE not initialized. Call init() first.",
  *     "Evaluation failed: ...").
  */
 
 /* eslint-disable @typescript-eslint/no-var-requires */
 declare const require: (id: string) => any;
+declare const Buffer: any;
 
 export interface LuxParams {
   n: number; N: number; k: number; ell: number; logB: number; ellKs: number; logBKs: number;
@@ -26,6 +30,8 @@ export interface LuxParams {
   order: 0 | 1 | 2;
   /** 0 = in-tree Goldilocks exact NTT, 1 = 2^64 torus with f64 FFT (the arithmetic of the named tfhe-rs set; ell/logB are level/base_log) */
   arith?: 0 | 1;
+  /** >= 1: one handle over that many GPUs of the box (0xFFFFFFFF = all visible); absent / 0: the single GPU `device` */
+  gpus?: number;
 }
 
 /** parameter sets of SURVEY.md Appendix B */
@@ -69,6 +75,60 @@ interface Native {
   gateBatch(h: Handle, gate: number, a: BigUint64Array, b: BigUint64Array, batch: number): Promise<BigUint64Array>;
 }
 
+/** stands for the reference's `bootstrapKey: string` argument once the keys live on the GPU */
+export interface KeyHandle { readonly id: number }
+let keyIds = 0;
+
+// ---- the engine's serialized container (tfhe_b200/csrc/serial.cu): 80-byte little-endian header + u64 words ----------------
+const MAGIC = [0x4c, 0x55, 0x58, 0x46, 0x48, 0x45, 0x0d, 0x0a];   // "LUXFHE\r\n"
+const BLOB_RADIX = 2;
+let crcTable: Uint32Array | null = null;
+function crc32(bytes: Uint8Array): number {
+  if (!crcTable) {
+    crcTable = new Uint32Array(256);
+    for (let i = 0; i < 256; i++) {
+      let c = i;
+      for (let k = 0; k < 8; k++) c = (c & 1) ? (0xedb88320 ^ (c >>> 1)) : (c >>> 1);
+      crcTable[i] = c >>> 0;
+    }
+  }
+  let crc = 0xffffffff;
+  for (let i = 0; i < bytes.length; i++) crc = crcTable[(crc ^ bytes[i]) & 0xff] ^ (crc >>> 8);
+  return (crc ^ 0xffffffff) >>> 0;
+}
+function paramWords(p: LuxParams): number[] {
+  return [p.n, p.N, p.k, p.ell, p.logB, p.ellKs, p.logBKs, p.order, p.arith ?? 0];
+}
+export function encodeContainer(p: LuxParams, bitWidth: number, count: number, words: BigUint64Array): Uint8Array {
+  const out = new Uint8Array(80 + words.length * 8);
+  const dv = new DataView(out.buffer);
+  out.set(MAGIC, 0);
+  dv.setUint32(8, 1, true);
+  dv.setUint32(12, BLOB_RADIX, true);
+  paramWords(p).forEach((v, i) => dv.setUint32(16 + 4 * i, v, true));
+  dv.setUint32(52, bitWidth, true);
+  dv.setBigUint64(56, BigInt(count), true);
+  dv.setBigUint64(64, BigInt(words.length), true);
+  out.set(new Uint8Array(words.buffer, words.byteOffset, words.length * 8), 80);
+  dv.setUint32(72, crc32(out.subarray(80)), true);
+  dv.setUint32(76, crc32(out.subarray(0, 76)), true);
+  return out;
+}
+export function decodeContainer(bytes: Uint8Array, expect: LuxParams): { bitWidth: number; count: number; words: BigUint64Array } {
+  const dv = new DataView(bytes.buffer, bytes.byteOffset, bytes.byteLength);
+  if (bytes.length < 80 || MAGIC.some((m, i) => bytes[i] !== m) || dv.getUint32(8, true) !== 1 ||
+      dv.getUint32(76, true) !== crc32(bytes.subarray(0, 76)))
+    throw new Error('Evaluation failed: not a serialized LuxFHE ciphertext');
+  if (dv.getUint32(12, true) !== BLOB_RADIX || paramWords(expect).some((v, i) => dv.getUint32(16 + 4 * i, true) !== v))
+    throw new Error('Evaluation failed: ciphertext belongs to another parameter set or arithmetic');
+  const nWords = Number(dv.getBigUint64(64, true));
+  if (bytes.length !== 80 + nWords * 8 || dv.getUint32(72, true) !== crc32(bytes.subarray(80)))
+    throw new Error('Evaluation failed: ciphertext is damaged (length / checksum)');
+  const words = new BigUint64Array(nWords);       // copy: the payload of a base64-decoded Buffer is not 8-byte aligned
+  new Uint8Array(words.buffer).set(bytes.subarray(80));
+  return { bitWidth: dv.getUint32(52, true), count: Number(dv.getBigUint64(56, true)), words };
+}
+
 let native: Native | null = null;
 let instance: LuxFHEB200 | null = null;
 
@@ -92,8 +152,12 @@ export class LuxFHEB200 {
 
   version(): string { return this.n.version(); }
 
-  /** upload once; converted to the NTT domain on the device and kept resident in HBM */
-  loadKeys(keys: EvaluationKeys): void {
+  private keyHandle: KeyHandle | null = null;
+
+  /** upload once; converted on the device and kept resident in HBM.  Returns the handle that stands for the reference's
+   *  per-call `bootstrapKey` string. */
+  loadKeys(keys: EvaluationKeys): KeyHandle {
+    this.keyHandle = { id: ++keyIds };
     this.n.loadKey(this.h, 0, keys.bootstrapKey, keys.bootstrapKeyDomain ?? 0);
     if (this.params.order === 1) {
       if (!keys.lweKeySwitchKey) throw new Error('loadKeys: lweKeySwitchKey is required for KS_PBS parameter sets');
@@ -102,6 +166,7 @@ export class LuxFHEB200 {
       if (!keys.glweKeySwitchKey) throw new Error('loadKeys: glweKeySwitchKey is required for PBS_KS parameter sets');
       this.n.loadKey(this.h, 1, keys.glweKeySwitchKey, keys.glweKeySwitchKeyDomain ?? 0);
     }
+    return this.keyHandle;
   }
 
   blocks(bitWidth: number): number {
@@ -129,12 +194,36 @@ export class LuxFHEB200 {
     return this.n.evalBatch(this.h, code, bitWidth, left, scalars, this.batchOf(left, bitWidth), 1);
   }
 
-  // the reference's four methods (index.ts:19-22) as the batch-of-one case; bitWidth is explicit because the
-  // engine-native ciphertext carries no header
-  add(ct1: BigUint64Array, ct2: BigUint64Array, bitWidth: number) { return this.evalBatch(Op.add, bitWidth, ct1, ct2); }
-  sub(ct1: BigUint64Array, ct2: BigUint64Array, bitWidth: number) { return this.evalBatch(Op.sub, bitWidth, ct1, ct2); }
-  eq(ct1: BigUint64Array, ct2: BigUint64Array, bitWidth: number) { return this.evalBatch(Op.eq, bitWidth, ct1, ct2); }
-  lt(ct1: BigUint64Array, ct2: BigUint64Array, bitWidth: number) { return this.evalBatch(Op.lt, bitWidth, ct1, ct2); }
+  // ---- the reference's four methods, same names AND arity (packages/wasm/src/index.ts:19-22):
+  //        add(ct1, ct2, bootstrapKey, secretKey): string
+  // ct1 / ct2 are serialized ciphertexts exactly as the reference passes them (strings), here the base64 of the
+  // engine's self-describing container (lux_serialize, include/lux_tfhe.h): the bit width is read from its header and the
+  // parameter set is checked against this engine.  `bootstrapKey` is the handle returned by loadKeys() (keys are resident
+  // on the GPU, not re-sent per call) and is only checked for identity; `secretKey` is accepted and ignored (the
+  // reference's wasm build needs it to re-encrypt, the server-key evaluation here never sees secrets).  The one change
+  // that cannot be avoided: the result is a Promise<string>, because the GPU work runs off the event loop.
+  add(ct1: string, ct2: string, bootstrapKey?: KeyHandle, _secretKey?: unknown) { return this.op2(Op.add, ct1, ct2, bootstrapKey); }
+  sub(ct1: string, ct2: string, bootstrapKey?: KeyHandle, _secretKey?: unknown) { return this.op2(Op.sub, ct1, ct2, bootstrapKey); }
+  eq(ct1: string, ct2: string, bootstrapKey?: KeyHandle, _secretKey?: unknown) { return this.op2(Op.eq, ct1, ct2, bootstrapKey); }
+  lt(ct1: string, ct2: string, bootstrapKey?: KeyHandle, _secretKey?: unknown) { return this.op2(Op.lt, ct1, ct2, bootstrapKey); }
+
+  private async op2(op: Op, ct1: string, ct2: string, key?: KeyHandle): Promise<string> {
+    if (key !== undefined && key !== this.keyHandle) throw new Error('Evaluation failed: bootstrapKey is not the handle returned by loadKeys()');
+    const a = decodeContainer(Buffer.from(ct1, 'base64'), this.params);
+    const b = decodeContainer(Buffer.from(ct2, 'base64'), this.params);
+    if (a.bitWidth !== b.bitWidth || a.count !== b.count) throw new Error('Evaluation failed: operands differ in width or count');
+    const out = await this.evalBatch(op, a.bitWidth, a.words, b.words);
+    const predicate = op >= Op.eq && op <= Op.ge;
+    return Buffer.from(encodeContainer(this.params, predicate ? 2 : a.bitWidth, a.count, out)).toString('base64');
+  }
+
+  /** wrap engine-native words ([count][blocks][ctWords]) as the string form add/sub/eq/lt take */
+  toCiphertext(bitWidth: number, words: BigUint64Array): string {
+    return Buffer.from(encodeContainer(this.params, bitWidth, this.batchOf(words, bitWidth), words)).toString('base64');
+  }
+  fromCiphertext(ct: string): { bitWidth: number; count: number; words: BigUint64Array } {
+    return decodeContainer(Buffer.from(ct, 'base64'), this.params);
+  }
 
   /** cond ? a : b   (FHE.select) — cond is [batch][ctWords] */
   selectBatch(bitWidth: number, cond: BigUint64Array, a: BigUint64Array, b: BigUint64Array): Promise<BigUint64Array> {

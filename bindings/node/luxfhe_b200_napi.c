@@ -11,8 +11,9 @@
  * return Promises and run on the libuv pool (napi_async_work), so Node's loop is never blocked; errors are JS
  * exceptions / rejections carrying lux_last_error().
  *
- * Not loadable in the build image (no node): tests/test_node_addon.py compiles it against node_api_decl.h and checks
- * the registration symbol and that every lux_* symbol it needs is exported by the library.
+ * Not loadable in the build image (no node): tests/test_node_addon.py compiles it against node_api_decl.h, checks the
+ * registration symbol and that every lux_* symbol it needs is exported by the library, and RUNS it on the GPU box inside
+ * tests/napi_host/fake_napi.c, a minimal N-API host whose async work runs on real threads (two concurrent jobs per handle).
  */
 #if defined(__has_include)
 #if __has_include(<node_api.h>)
@@ -45,19 +46,37 @@ static napi_value undefined(napi_env env) {
     return u;
 }
 
+/* what a JS handle points at: one engine (one GPU) or a multi-GPU handle (lux_engine_create_multi); `e` is always usable for
+ * parameter queries (GPU 0's engine of a multi handle).  The library serialises calls per engine, so several un-awaited
+ * Promises on one handle are safe; every queued job also holds a reference to the handle, so the finalizer cannot run
+ * while work is in flight. */
+typedef struct {
+    lux_engine *e;
+    lux_multi *m;
+} handle_t;
+
 static void engine_finalize(napi_env env, void *data, void *hint) {
     (void)env;
     (void)hint;
-    lux_engine_destroy((lux_engine *)data);
+    handle_t *h = (handle_t *)data;
+    if (h->m)
+        lux_multi_destroy(h->m);
+    else
+        lux_engine_destroy(h->e);
+    free(h);
 }
 
-static lux_engine *engine_arg(napi_env env, napi_value v) {
+static handle_t *handle_arg(napi_env env, napi_value v) {
     void *p = NULL;
     if (napi_get_value_external(env, v, &p) != napi_ok || !p) {
         napi_throw_error(env, NULL, "LuxFHE not initialized: pass the handle returned by createEngine()");
         return NULL;
     }
-    return (lux_engine *)p;
+    return (handle_t *)p;
+}
+static lux_engine *engine_arg(napi_env env, napi_value v) {
+    handle_t *h = handle_arg(env, v);
+    return h ? h->e : NULL;
 }
 
 /* BigUint64Array -> (pointer, words); zero copy */
@@ -110,12 +129,26 @@ static napi_value CreateEngine(napi_env env, napi_callback_info info) {
     p.arith = u32_prop(env, argv[0], "arith", LUX_ARITH_GOLDILOCKS_NTT);
     int32_t device = 0;
     if (argc > 1 && !is_nullish(env, argv[1])) napi_get_value_int32(env, argv[1], &device);
-    lux_engine *e = NULL;
-    const int rc = lux_engine_create(&p, device, &e);
-    if (rc != LUX_OK) THROW(env, "createEngine failed (%d): %s", rc, lux_last_error(NULL));
+    const uint32_t gpus = u32_prop(env, argv[0], "gpus", 0);   /* gpus >= 1: one handle over that many GPUs (0xFFFFFFFF: all) */
+    handle_t *hd = (handle_t *)calloc(1, sizeof(handle_t));
+    if (!hd) THROW(env, "out of memory");
+    if (gpus) {
+        const int rc = lux_engine_create_multi(&p, gpus == 0xFFFFFFFFu ? 0 : (int)gpus, &hd->m);
+        if (rc != LUX_OK) {
+            free(hd);
+            THROW(env, "createEngine failed (%d): %s", rc, lux_multi_last_error(NULL));
+        }
+        hd->e = lux_multi_engine(hd->m, 0);
+    } else {
+        const int rc = lux_engine_create(&p, device, &hd->e);
+        if (rc != LUX_OK) {
+            free(hd);
+            THROW(env, "createEngine failed (%d): %s", rc, lux_last_error(NULL));
+        }
+    }
     napi_value h;
-    if (napi_create_external(env, e, engine_finalize, NULL, &h) != napi_ok) {
-        lux_engine_destroy(e);
+    if (napi_create_external(env, hd, engine_finalize, NULL, &h) != napi_ok) {
+        engine_finalize(env, hd, NULL);
         THROW(env, "napi_create_external failed");
     }
     return h;
@@ -149,22 +182,30 @@ static napi_value LoadKey(napi_env env, napi_callback_info info) {
     napi_value argv[4];
     napi_get_cb_info(env, info, &argc, argv, NULL, NULL);
     if (argc < 3) THROW(env, "loadKey(handle, which, words, domain?)");
-    lux_engine *e = engine_arg(env, argv[0]);
-    if (!e) return NULL;
+    handle_t *hd = handle_arg(env, argv[0]);
+    if (!hd) return NULL;
+    lux_engine *e = hd->e;
     uint32_t which = 0, domain = LUX_DOMAIN_STANDARD;
     napi_get_value_uint32(env, argv[1], &which);
     const uint64_t *w = u64_arg(env, argv[2], &words);
     if (!w) THROW(env, "loadKey: key must be a BigUint64Array");
     if (argc > 3 && !is_nullish(env, argv[3])) napi_get_value_uint32(env, argv[3], &domain);
     int rc;
+    if (which > 2) THROW(env, "loadKey: which must be 0, 1 or 2");
+    if (hd->m) {   /* converted on GPU 0, then copied device to device to every other GPU of the handle */
+        rc = which == 0 ? lux_multi_load_bsk(hd->m, w, words, (int)domain)
+             : which == 1 ? lux_multi_load_glwe_ksk(hd->m, w, words, (int)domain)
+                          : lux_multi_load_lwe_ksk(hd->m, w, words);
+        if (rc == LUX_OK) rc = lux_multi_replicate_keys(hd->m);
+        if (rc != LUX_OK) THROW(env, "loadKey failed (%d): %s", rc, lux_multi_last_error(hd->m));
+        return undefined(env);
+    }
     if (which == 0)
         rc = lux_load_bsk(e, w, words, (int)domain);
     else if (which == 1)
         rc = lux_load_glwe_ksk(e, w, words, (int)domain);
-    else if (which == 2)
-        rc = lux_load_lwe_ksk(e, w, words);
     else
-        THROW(env, "loadKey: which must be 0, 1 or 2");
+        rc = lux_load_lwe_ksk(e, w, words);
     if (rc != LUX_OK) THROW(env, "loadKey failed (%d): %s", rc, lux_last_error(e));
     return undefined(env);
 }
@@ -198,6 +239,7 @@ typedef enum { JOB_PBS, JOB_EVAL, JOB_EVAL_SCALAR, JOB_SELECT, JOB_ERC20, JOB_GA
 typedef struct {
     job_kind kind;
     lux_engine *e;
+    lux_multi *m;               /* non-NULL: the handle spans several GPUs, the library slices the batch */
     const uint64_t *in[3];      /* operand views (kept alive by refs) */
     const uint32_t *idx;        /* PBS: lut index per ciphertext, or NULL */
     uint64_t *out;              /* result ArrayBuffer data */
@@ -205,7 +247,7 @@ typedef struct {
     uint32_t op, bit_width, n_luts;
     int rc;
     char err[512];
-    napi_ref refs[5];
+    napi_ref refs[6];
     int n_refs;
     napi_ref out_ref;
     napi_deferred deferred;
@@ -215,6 +257,18 @@ typedef struct {
 static void job_execute(napi_env env, void *data) { /* worker thread: no N-API calls here */
     (void)env;
     job_t *j = (job_t *)data;
+    if (j->m && (j->kind == JOB_PBS || j->kind == JOB_EVAL || j->kind == JOB_SELECT || j->kind == JOB_ERC20)) {
+        switch (j->kind) {
+            case JOB_PBS: j->rc = lux_multi_pbs_batch(j->m, j->in[0], j->in[1], j->n_luts, j->idx, j->batch, j->out); break;
+            case JOB_EVAL: j->rc = lux_multi_eval(j->m, (lux_op)j->op, j->bit_width, j->in[0], j->in[1], j->batch, j->out); break;
+            case JOB_SELECT: j->rc = lux_multi_select(j->m, j->bit_width, j->in[0], j->in[1], j->in[2], j->batch, j->out); break;
+            default:
+                j->rc = lux_multi_erc20_transfer(j->m, j->in[0], j->in[1], j->in[2], j->batch, j->out, j->out + j->out_words / 2);
+                break;
+        }
+        if (j->rc != LUX_OK) snprintf(j->err, sizeof(j->err), "lux error %d: %s", j->rc, lux_multi_last_error(j->m));
+        return;
+    }
     switch (j->kind) {
         case JOB_PBS: j->rc = lux_pbs_batch(j->e, j->in[0], j->in[1], j->n_luts, j->idx, j->batch, j->out); break;
         case JOB_EVAL: j->rc = lux_eval(j->e, (lux_op)j->op, j->bit_width, j->in[0], j->in[1], j->batch, j->out); break;
@@ -247,7 +301,7 @@ static void job_complete(napi_env env, napi_status status, void *data) {
 }
 
 static void job_hold(napi_env env, job_t *j, napi_value v) {
-    if (j->n_refs < 5 && napi_create_reference(env, v, 1, &j->refs[j->n_refs]) == napi_ok) j->n_refs++;
+    if (j->n_refs < 6 && napi_create_reference(env, v, 1, &j->refs[j->n_refs]) == napi_ok) j->n_refs++;
 }
 
 /* allocate the result array, queue the job, return its Promise */
@@ -270,13 +324,21 @@ static napi_value job_submit(napi_env env, job_t *j, const char *name) {
     return promise;
 }
 
-static job_t *job_new(job_kind kind, lux_engine *e) {
-    job_t *j = (job_t *)calloc(1, sizeof(job_t));
+/* the job keeps the JS handle alive (its finalizer destroys the engine) until the completion callback has run */
+static job_t *job_new(napi_env env, job_kind kind, napi_value handle) {
+    handle_t *hd = handle_arg(env, handle);
+    job_t *j = hd ? (job_t *)calloc(1, sizeof(job_t)) : NULL;
     if (j) {
         j->kind = kind;
-        j->e = e;
+        j->e = hd->e;
+        j->m = hd->m;
+        job_hold(env, j, handle);
     }
     return j;
+}
+static void job_abandon(napi_env env, job_t *j) {
+    for (int i = 0; i < j->n_refs; i++) napi_delete_reference(env, j->refs[i]);
+    free(j);
 }
 
 /* pbsBatch(handle, lweIn, testVectors, nLuts, lutIdx: Uint32Array | null, batch) -> Promise<BigUint64Array> */
@@ -307,7 +369,7 @@ static napi_value PbsBatch(napi_env env, napi_callback_info info) {
         for (size_t b = 0; b < len; b++)
             if (idx[b] >= n_luts) THROW(env, "pbsBatch: lutIdx[%zu] out of range", b);
     }
-    job_t *j = job_new(JOB_PBS, e);
+    job_t *j = job_new(env, JOB_PBS, argv[0]);
     if (!j) THROW(env, "out of memory");
     j->in[0] = in;
     j->in[1] = tv;
@@ -345,7 +407,7 @@ static napi_value EvalBatch(napi_env env, napi_callback_info info) {
     if (lux_op_is_unary((lux_op)op) ? rhs != NULL : (!rhs || w_r != (scalar ? (size_t)batch : want)))
         THROW(env, "evalBatch: rhs does not match op %u", op);
     if (lux_op_is_scalar_only((lux_op)op) && !scalar) THROW(env, "evalBatch: op %u needs a plaintext right operand (scalar = true)", op);
-    job_t *j = job_new(scalar ? JOB_EVAL_SCALAR : JOB_EVAL, e);
+    job_t *j = job_new(env, scalar ? JOB_EVAL_SCALAR : JOB_EVAL, argv[0]);
     if (!j) THROW(env, "out of memory");
     j->in[0] = lhs;
     j->in[1] = rhs;
@@ -370,11 +432,11 @@ static napi_value SelectBatch(napi_env env, napi_callback_info info) {
     napi_get_value_uint32(env, argv[1], &bw);
     napi_get_value_uint32(env, argv[5], &batch);
     const size_t blocks = lux_radix_blocks(bw), cw = lux_ct_words(e);
-    job_t *j = job_new(JOB_SELECT, e);
+    job_t *j = job_new(env, JOB_SELECT, argv[0]);
     if (!j) THROW(env, "out of memory");
     for (int i = 0; i < 3; i++) j->in[i] = u64_arg(env, argv[2 + i], &w[i]);
     if (!blocks || !j->in[0] || !j->in[1] || !j->in[2] || w[0] != (size_t)batch * cw || w[1] != (size_t)batch * blocks * cw || w[2] != w[1]) {
-        free(j);
+        job_abandon(env, j);
         THROW(env, "selectBatch: operand sizes do not match bitWidth %u and batch %u", bw, batch);
     }
     j->bit_width = bw;
@@ -396,11 +458,11 @@ static napi_value Erc20TransferBatch(napi_env env, napi_callback_info info) {
     uint32_t batch = 0;
     napi_get_value_uint32(env, argv[4], &batch);
     const size_t want = (size_t)batch * lux_radix_blocks(64) * lux_ct_words(e);
-    job_t *j = job_new(JOB_ERC20, e);
+    job_t *j = job_new(env, JOB_ERC20, argv[0]);
     if (!j) THROW(env, "out of memory");
     for (int i = 0; i < 3; i++) j->in[i] = u64_arg(env, argv[1 + i], &w[i]);
     if (!j->in[0] || !j->in[1] || !j->in[2] || w[0] != want || w[1] != want || w[2] != want) {
-        free(j);
+        job_abandon(env, j);
         THROW(env, "erc20TransferBatch: every operand must hold %zu words", want);
     }
     j->batch = batch;
@@ -423,12 +485,12 @@ static napi_value GateBatch(napi_env env, napi_callback_info info) {
     lux_params p;
     lux_engine_params(e, &p);
     const size_t want = (size_t)batch * (p.n + 1);
-    job_t *j = job_new(JOB_GATE, e);
+    job_t *j = job_new(env, JOB_GATE, argv[0]);
     if (!j) THROW(env, "out of memory");
     j->in[0] = u64_arg(env, argv[2], &w[0]);
     j->in[1] = u64_arg(env, argv[3], &w[1]);
     if (!j->in[0] || !j->in[1] || w[0] != want || w[1] != want) {
-        free(j);
+        job_abandon(env, j);
         THROW(env, "gateBatch: operands must hold %zu words", want);
     }
     j->op = gate;
