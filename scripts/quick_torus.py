@@ -20,6 +20,18 @@ d_idx = torch.from_numpy((np.arange(B) % 4).astype(np.int32)).cuda()
 d_out = torch.empty_like(d_in)
 s = torch.cuda.Stream(); torch.cuda.set_stream(s)
 eng.set_timing(True)
+if os.environ.get("LAT"):   # small-batch latency: B in LAT (comma list), cfg from the command line
+    for b in [int(x) for x in os.environ["LAT"].split(",")]:
+        for spec in teams_list:
+            t = int(spec.split(":")[0])
+            eng.force_teams(t % 10); eng.fft_variant(t // 10)
+            ms = []
+            for _ in range(5):
+                a, e2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record(s); eng.pbs_batch_device(d_in[:b], d_tv, d_idx[:b], b, d_out[:b], n_luts=4, stream=s.cuda_stream); e2.record(s); e2.synchronize()
+                ms.append(a.elapsed_time(e2))
+            print(f"latency B={b} cfg={spec}: {min(ms[1:]):.3f} ms", flush=True)
+    sys.exit(0)
 for spec in teams_list:
     t = int(spec.split(":")[0])
     if ":" in spec:

@@ -468,3 +468,22 @@ def test_key_blob_roundtrip(rig_small1):
     cts = np.stack([rng.field(r.p.ct_len) for _ in range(5)])
     tv = rng.field(r.p.N)
     assert np.array_equal(e2.pbs_batch(cts, tv), r.eng.pbs_batch(cts, tv))
+
+
+@pytest.mark.parametrize("which,B", [("s1", 5920 + 5), ("s2", 4440 + 3)])
+def test_whole_batch_random_indices_meet_the_oracle(which, B, rig_s1, rig_s2):
+    """at the real parameter sets and the bench batch sizes (plus a ragged tail) the oracle sees 16
+    ciphertexts at random indices over the WHOLE batch — first and last CTA, later waves, the ragged last CTA, the key ring
+    after wrap-around — not only the head; every variant-independent index arithmetic (ct, lut_idx, output offset) is
+    under test here."""
+    r = {"s1": rig_s1, "s2": rig_s2}[which]
+    rs = np.random.RandomState(B)
+    cts = (rs.randint(0, 2**63, size=(B, r.p.ct_len), dtype=np.int64).astype(np.uint64) % np.uint64(Q))
+    tvs = (rs.randint(0, 2**63, size=(5, r.p.N), dtype=np.int64).astype(np.uint64) % np.uint64(Q))
+    idx = rs.randint(0, 5, B).astype(np.uint32)
+    got = r.eng.pbs_batch(cts, tvs, idx)
+    wave = r.eng.wave_ciphertexts(B)
+    last_wave = (B - 1) // wave * wave
+    pick = np.unique(np.concatenate([[0, 1, wave - 1, wave, last_wave, B - 2, B - 1], rs.randint(0, B, 9)]))
+    want, _ = r.ctx.pbs_batch(cts[pick], tvs, idx[pick])
+    assert np.array_equal(got[pick], want), "GPU PBS differs from the oracle away from the head of the batch"

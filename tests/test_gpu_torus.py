@@ -215,6 +215,23 @@ def test_pbs_s2_bit_exact_across_the_batch(rig_s2):
     assert err.std() < 2.0**-12, err.std()     # measured 2^-14.7; a failed transform would be ~2^-2
 
 
+def test_pbs_s2_bench_batch_random_indices(rig_s2):
+    """the bench batch of the default kernel (8 waves of 4 x 148) plus a ragged tail: 16 ciphertexts at random indices over
+    the whole batch (every wave boundary, last CTA) bit-exact vs the oracle"""
+    e, p = rig_s2.eng, rig_s2.p
+    B = 4736 + 7
+    rs = np.random.RandomState(4)
+    cts = u64_rand(rs, (B, p.ct_len))
+    tvs = u64_rand(rs, (4, p.N))
+    idx = rs.randint(0, 4, B).astype(np.uint32)
+    got = e.pbs_batch(cts, tvs, idx)
+    wave = e.wave_ciphertexts(B)
+    assert wave == 4 * 148
+    pick = np.unique(np.concatenate([[0, wave - 1, wave, 7 * wave, 8 * wave, B - 1], rs.randint(0, B, 10)]))
+    want, _ = rig_s2.ctx.pbs_batch(cts[pick], tvs, idx[pick])
+    assert np.array_equal(got[pick], want)
+
+
 # ------------------------------------------------------------------------------------------- the decryption gate
 @pytest.mark.parametrize("arith", ["torus", "goldilocks"])
 def test_decryption_gate_65536_trials(arith):

@@ -7,10 +7,10 @@
 
 using namespace fft64;
 
-template <int TEAMS, int NS, int RS, int TWS, int HB = 0, int GROUPS = 1, int KL = 0>
+template <int TEAMS, int NS, int RS, int TWS, int HB = 0, int GROUPS = 1, int KL = 0, int MK = 1>
 __global__ void __launch_bounds__(Cfg<TEAMS, NS, RS, TWS, HB, GROUPS, KL>::THREADS, 1) blind_rotate_fft_kernel(const __grid_constant__ Args a) {
     extern __shared__ __align__(16) unsigned char smem[];
-    blind_rotate_body<TEAMS, NS, RS, TWS, HB, GROUPS, KL>(a, smem);
+    blind_rotate_body<TEAMS, NS, RS, TWS, HB, GROUPS, KL, MK>(a, smem);
 }
 
 constexpr int UTIL_WARPS = 4;
@@ -86,17 +86,17 @@ static void fill_tables(const lux_engine *e, Args &a) {
     for (int v = 0; v < 32; v++) a.twA[v] = make_double2(e->fft_twA[2 * v], e->fft_twA[2 * v + 1]);
 }
 
-template <int TEAMS, int NS, int RS, int TWS, int HB = 0, int GROUPS = 1, int KL = 0>
+template <int TEAMS, int NS, int RS, int TWS, int HB = 0, int GROUPS = 1, int KL = 0, int MK = 1>
 static int launch_cfg(lux_engine *e, const Args &a, cudaStream_t s) {
     using C = Cfg<TEAMS, NS, RS, TWS, HB, GROUPS, KL>;
     static_assert(C::SMEM <= 232448, "configuration exceeds the 227 KiB of shared memory a CTA can opt into");
     static bool configured[64] = {};
     if (!configured[e->device & 63]) {
-        CUDA_TRY(e, cudaFuncSetAttribute(blind_rotate_fft_kernel<TEAMS, NS, RS, TWS, HB, GROUPS, KL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM));
+        CUDA_TRY(e, cudaFuncSetAttribute(blind_rotate_fft_kernel<TEAMS, NS, RS, TWS, HB, GROUPS, KL, MK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM));
         configured[e->device & 63] = true;
     }
     const unsigned grid = (a.B + TEAMS - 1) / TEAMS;
-    blind_rotate_fft_kernel<TEAMS, NS, RS, TWS, HB, GROUPS, KL><<<grid, C::THREADS, C::SMEM, s>>>(a);
+    blind_rotate_fft_kernel<TEAMS, NS, RS, TWS, HB, GROUPS, KL, MK><<<grid, C::THREADS, C::SMEM, s>>>(a);
     e->launches++;
     CUDA_TRY(e, cudaGetLastError());
     return LUX_OK;
@@ -123,8 +123,12 @@ int lux_fft_launch_br(lux_engine *e, Args a, cudaStream_t s) {
     a.trace = (u64 *)e->d_fft_trace;
     const int variant = e->fft_variant;   // 0 = the default of each team count; the others are the measured alternatives
     switch (pick_teams(e, a.B)) {
-        case 1: return launch_cfg<1, 4, 8, 1>(e, a, s);
-        case 2: return launch_cfg<2, 4, 8, 1>(e, a, s);
+        case 1:   // a warp alone on its scheduler: free instruction schedule (no phase marks)
+            if (variant == 1) return launch_cfg<1, 4, 8, 1>(e, a, s);
+            return launch_cfg<1, 4, 8, 1, 0, 1, 0, 0>(e, a, s);
+        case 2:   // one warp per scheduler as well: 7.73 ms without the marks, 8.35 ms with them at B = 296
+            if (variant == 1) return launch_cfg<2, 4, 8, 1>(e, a, s);
+            return launch_cfg<2, 4, 8, 1, 0, 1, 0, 0>(e, a, s);
         case 3:
             if (variant == 1) return launch_cfg<3, 8, 4, 1, 1>(e, a, s);      // half-size buffers, ring = one whole GGSW
             return launch_cfg<3, 4, 4, 0>(e, a, s);

@@ -184,13 +184,15 @@ __device__ __forceinline__ void bfly_group(double2 (&x)[32], const int (&iu)[G],
 // The marks stay in the production kernel on purpose: each one is a (never taken, uniform) branch that ends a basic block,
 // and ptxas schedules the phases separately instead of mixing them.  Measured on B200 at B = 4,736: 85.9 ms with the marks,
 // 93.0 ms without, 90.1 ms with a bare never-taken branch (profiles/r02b_fft_variants.txt).  -DFFT64_NO_MARKS removes them.
+// MK (a template argument of everything that contains marks) = 0 compiles them out of one instantiation: a warp that is
+// alone on its scheduler (one ciphertext per CTA, the latency case) is faster with the free schedule.
 #ifndef FFT64_SKIP_MARKS
 #define FFT64_SKIP_MARKS 0   // bit k set: phase mark k is left out (codegen experiments)
 #endif
 #ifndef FFT64_NO_MARKS
 #define FFT64_MARK(k)                                                                  \
     do {                                                                               \
-        if (!((FFT64_SKIP_MARKS >> (k)) & 1) && a.trace && lane == 0) {                                                    \
+        if (MK && !((FFT64_SKIP_MARKS >> (k)) & 1) && a.trace && lane == 0) {                                                    \
             long long now_;                                                            \
             asm volatile("mov.u64 %0, %%clock64;" : "=l"(now_)::"memory");             \
             atomicAdd((unsigned long long *)a.trace + (k), (unsigned long long)(now_ - mark_)); \
@@ -211,7 +213,7 @@ __device__ __forceinline__ void bfly_group(double2 (&x)[32], const int (&iu)[G],
 #endif
 
 // pass A: tree levels m = 1..16 on the column layout; node m + blk pairs registers blk*2t + jj and + t, t = 16/m
-template <bool INV>
+template <bool INV, int MK = 1>
 __device__ __forceinline__ void pass_a(double2 (&x)[32], const Args &a, int lane, long long &mark_) {
     constexpr int G = FFT64_GROUP;
 #pragma unroll
@@ -270,7 +272,7 @@ __device__ __forceinline__ void pass_b_stage(double2 (&y)[32], const double2 *tw
         bfly_group<INV, G>(y, iu, iv, wr, wi);
     }
 }
-template <bool INV>
+template <bool INV, int MK = 1>
 __device__ __forceinline__ void pass_b(double2 (&y)[32], const double2 *twB, int lane, const Args &a, long long &mark_) {
     if (!INV) {
         pass_b_stage<false, 0>(y, twB, lane);
@@ -291,7 +293,7 @@ __device__ __forceinline__ void pass_b(double2 (&y)[32], const double2 *twB, int
     }
 }
 // inverse pass B without its last stage, on rows 16 H .. 16 H + 15 only (the key MAC of the other half can still be pending)
-template <int H>
+template <int H, int MK = 1>
 __device__ __forceinline__ void pass_b_inv_half(double2 (&y)[32], const double2 *twB, int lane, const Args &a, long long &mark_) {
     pass_b_stage<true, 4, 8 * H, 8 * H + 8>(y, twB, lane);
     FFT64_STAGE_MARK();
@@ -457,7 +459,7 @@ __device__ __forceinline__ void mac_all(double2 (&y)[32], const double2 *oth, co
     }
 }
 
-template <int TEAMS, int NS, int RS, int TWS, int HB = 0, int GROUPS = 1, int KL = 0>
+template <int TEAMS, int NS, int RS, int TWS, int HB = 0, int GROUPS = 1, int KL = 0, int MK = 1>
 __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *smem_raw) {
     using C = Cfg<TEAMS, NS, RS, TWS, HB, GROUPS, KL>;
     static_assert(TEAMS % GROUPS == 0, "teams must split evenly into groups");
@@ -570,14 +572,14 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
             }
         }
         FFT64_MARK(0);
-        pass_a<false>(x, a, lane, mark_);
+        pass_a<false, MK>(x, a, lane, mark_);
         FFT64_MARK(1);
         if (HB)
             col_to_row_h(x, (double *)buf, lane);
         else
             col_to_row(x, buf, lane);
         FFT64_MARK(2);
-        pass_b<false>(x, twB, lane, a, mark_);
+        pass_b<false, MK>(x, twB, lane, a, mark_);
         FFT64_MARK(3);
         // swap spectra with the partner warp
         if (!HB) {
@@ -594,7 +596,7 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
             else
                 (KL ? mac_global<1, RS, 0, 0, CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
                     : mac_all<1, NS, RS, 0, 0, CH>(x, buf_oth, ring, full, empty, t, lane));
-            pass_b_inv_half<0>(x, twB, lane, a, mark_);
+            pass_b_inv_half<0, MK>(x, twB, lane, a, mark_);
             if (r == 0)
                 (KL ? mac_global<0, RS, 0, CH, 2 * CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
                     : mac_all<0, NS, RS, 0, CH, 2 * CH>(x, buf_oth, ring, full, empty, t, lane));
@@ -604,7 +606,7 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
             FFT64_MARK(5);
             asm volatile("bar.sync %0, 64;" ::"r"(barrier_id) : "memory");
             FFT64_MARK(6);
-            pass_b_inv_half<1>(x, twB, lane, a, mark_);
+            pass_b_inv_half<1, MK>(x, twB, lane, a, mark_);
         } else {   // two rounds of 16 rows through the half-size buffers, layout [row][lane]
             constexpr int CH = 16 / RS;
             __syncwarp();
@@ -624,7 +626,7 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
             for (int i = 0; i < 16; i++) buf[i * 32 + lane] = x[16 + i];
             asm volatile("bar.sync %0, 64;" ::"r"(barrier_id) : "memory");
             FFT64_MARK(4);
-            pass_b_inv_half<0>(x, twB, lane, a, mark_);   // rows 0..15 are final: their inverse butterflies cover the wait for the key rows
+            pass_b_inv_half<0, MK>(x, twB, lane, a, mark_);   // rows 0..15 are final: their inverse butterflies cover the wait for the key rows
             if (r == 0)
                 (KL ? mac_global<0, RS, 1, CH, 2 * CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
                     : mac_all<0, NS, RS, 1, CH, 2 * CH>(x, buf_oth, ring, full, empty, t, lane));
@@ -634,7 +636,7 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
             FFT64_MARK(5);
             asm volatile("bar.sync %0, 64;" ::"r"(barrier_id) : "memory");
             FFT64_MARK(6);
-            pass_b_inv_half<1>(x, twB, lane, a, mark_);
+            pass_b_inv_half<1, MK>(x, twB, lane, a, mark_);
         }
         pass_b_stage<true, 0>(x, twB, lane);
         FFT64_MARK(7);
@@ -643,7 +645,7 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
         else
             row_to_col(x, buf, lane);
         FFT64_MARK(8);
-        pass_a<true>(x, a, lane, mark_);
+        pass_a<true, MK>(x, a, lane, mark_);
         FFT64_MARK(9);
 #pragma unroll
         for (int i0 = 0; i0 < 32; i0 += 4) {   // four points = eight independent conversion chains at a time
