@@ -148,7 +148,7 @@ def test_blind_rotate_per_iteration_bit_exact(rig_small, steps):
     assert np.array_equal(got, want), f"accumulators differ after {steps} CMUX steps"
 
 
-@pytest.mark.parametrize("teams", [1, 2, 3, 13, 4, 14, 24, 34])
+@pytest.mark.parametrize("teams", [1, 2, 3, 13, 4, 14, 24, 34, 54])
 def test_pbs_small_bit_exact_every_team_count(rig_small, teams):
     """whole PBS (key switch, blind rotation, extraction) against the oracle, every ciphertext of a ragged batch,
     for each ciphertexts-per-CTA configuration of the kernel (ring depth and stage size differ between them)"""

@@ -10,6 +10,19 @@ using namespace fft64;
 template <int TEAMS, int NS, int RS, int TWS, int HB = 0, int GROUPS = 1, int KL = 0, int MK = 1>
 __global__ void __launch_bounds__(Cfg<TEAMS, NS, RS, TWS, HB, GROUPS, KL>::THREADS, 1) blind_rotate_fft_kernel(const __grid_constant__ Args a) {
     extern __shared__ __align__(16) unsigned char smem[];
+    if (KL == 3) {   // tensor memory as the key cache: all 512 columns, taken and returned by warp 0 of EVERY CTA
+        __shared__ u32 tmem_slot;
+        if (threadIdx.x < 32) tmem_alloc_512(&tmem_slot);
+        tmem_fence_before();
+        __syncthreads();
+        tmem_fence_after();
+        const u32 tbase = tmem_slot;
+        blind_rotate_body<TEAMS, NS, RS, TWS, HB, GROUPS, KL, MK>(a, smem, tbase);   // its early exits return to here
+        tmem_fence_before();
+        __syncthreads();
+        if (threadIdx.x < 32) tmem_free_512(tbase);
+        return;
+    }
     blind_rotate_body<TEAMS, NS, RS, TWS, HB, GROUPS, KL, MK>(a, smem);
 }
 
@@ -137,6 +150,10 @@ int lux_fft_launch_br(lux_engine *e, Args a, cudaStream_t s) {
             if (variant == 2) return launch_cfg<4, 1, 4, 1, 1, 1, 1>(e, a, s);   // no ring: key rows straight from L2 / L1
             if (variant == 3) return launch_cfg<4, 2, 4, 0, 1, 2>(e, a, s);   // two independent groups, ring 2 x 8 KiB each
             if (variant == 4) return launch_cfg<4, 1, 4, 1, 1, 1, 2>(e, a, s);   // no ring, CTA-wide barrier per iteration
+            if (variant == 5) {   // key rows through tensor memory (four producer warps); refill paced at 400 ns per two rows unless set
+                if (e->fft_stagger_ns == 6000) a.stagger_ns = 400;
+                return launch_cfg<4, 1, 4, 1, 1, 1, 3>(e, a, s);
+            }
             return launch_cfg<4, 4, 4, 0, 1>(e, a, s);                        // ring 4 x 8 KiB, twiddles through L1
     }
 }

@@ -192,7 +192,7 @@ __device__ __forceinline__ void bfly_group(double2 (&x)[32], const int (&iu)[G],
 #ifndef FFT64_NO_MARKS
 #define FFT64_MARK(k)                                                                  \
     do {                                                                               \
-        if (MK && !((FFT64_SKIP_MARKS >> (k)) & 1) && a.trace && lane == 0) {                                                    \
+        if ((MK & 1) && !((FFT64_SKIP_MARKS >> (k)) & 1) && a.trace && lane == 0) {                                                    \
             long long now_;                                                            \
             asm volatile("mov.u64 %0, %%clock64;" : "=l"(now_)::"memory");             \
             atomicAdd((unsigned long long *)a.trace + (k), (unsigned long long)(now_ - mark_)); \
@@ -215,7 +215,7 @@ __device__ __forceinline__ void bfly_group(double2 (&x)[32], const int (&iu)[G],
 // pass A: tree levels m = 1..16 on the column layout; node m + blk pairs registers blk*2t + jj and + t, t = 16/m
 template <bool INV, int MK = 1>
 __device__ __forceinline__ void pass_a(double2 (&x)[32], const Args &a, int lane, long long &mark_) {
-    constexpr int G = FFT64_GROUP;
+    constexpr int G = (MK & 2) ? 8 : FFT64_GROUP;   // MK bit 1: groups of 8 (a warp alone on its scheduler hides the FP64 latency itself)
 #pragma unroll
     for (int s0 = 0; s0 < 5; s0++) {
         const int s = INV ? 4 - s0 : s0;
@@ -244,9 +244,10 @@ __device__ __forceinline__ void pass_a(double2 (&x)[32], const Args &a, int lane
 }
 // pass B: tree levels m = 32 g, g = 1..16, on the row layout; lane r owns nodes m + r g + b, b < g
 // butterflies [B0, B1) of the 16 of one stage: for g >= 2 the rows 0..15 (butterflies 0..7) and 16..31 (8..15) are independent
-template <bool INV, int GI, int B0 = 0, int B1 = 16>
+template <bool INV, int GI, int B0 = 0, int B1 = 16, int MK = 1>
 __device__ __forceinline__ void pass_b_stage(double2 (&y)[32], const double2 *twB, int lane) {
-    constexpr int G = FFT64_GROUP < (B1 - B0) ? FFT64_GROUP : (B1 - B0);
+    constexpr int G0 = (MK & 2) ? 8 : FFT64_GROUP;
+    constexpr int G = G0 < (B1 - B0) ? G0 : (B1 - B0);
     constexpr int g = 1 << GI, t = 16 >> GI, NW = g >= 2 ? g / 2 : 1;
     constexpr int E0 = (B0 / t) / 2, E1 = ((B1 - 1) / t) / 2 + 1;
     double2 w[NW];
@@ -275,33 +276,33 @@ __device__ __forceinline__ void pass_b_stage(double2 (&y)[32], const double2 *tw
 template <bool INV, int MK = 1>
 __device__ __forceinline__ void pass_b(double2 (&y)[32], const double2 *twB, int lane, const Args &a, long long &mark_) {
     if (!INV) {
-        pass_b_stage<false, 0>(y, twB, lane);
+        pass_b_stage<false, 0, 0, 16, MK>(y, twB, lane);
         FFT64_STAGE_MARK();
-        pass_b_stage<false, 1>(y, twB, lane);
+        pass_b_stage<false, 1, 0, 16, MK>(y, twB, lane);
         FFT64_STAGE_MARK();
-        pass_b_stage<false, 2>(y, twB, lane);
+        pass_b_stage<false, 2, 0, 16, MK>(y, twB, lane);
         FFT64_STAGE_MARK();
-        pass_b_stage<false, 3>(y, twB, lane);
+        pass_b_stage<false, 3, 0, 16, MK>(y, twB, lane);
         FFT64_STAGE_MARK();
-        pass_b_stage<false, 4>(y, twB, lane);
+        pass_b_stage<false, 4, 0, 16, MK>(y, twB, lane);
     } else {
-        pass_b_stage<true, 4>(y, twB, lane);
-        pass_b_stage<true, 3>(y, twB, lane);
-        pass_b_stage<true, 2>(y, twB, lane);
-        pass_b_stage<true, 1>(y, twB, lane);
-        pass_b_stage<true, 0>(y, twB, lane);
+        pass_b_stage<true, 4, 0, 16, MK>(y, twB, lane);
+        pass_b_stage<true, 3, 0, 16, MK>(y, twB, lane);
+        pass_b_stage<true, 2, 0, 16, MK>(y, twB, lane);
+        pass_b_stage<true, 1, 0, 16, MK>(y, twB, lane);
+        pass_b_stage<true, 0, 0, 16, MK>(y, twB, lane);
     }
 }
 // inverse pass B without its last stage, on rows 16 H .. 16 H + 15 only (the key MAC of the other half can still be pending)
 template <int H, int MK = 1>
 __device__ __forceinline__ void pass_b_inv_half(double2 (&y)[32], const double2 *twB, int lane, const Args &a, long long &mark_) {
-    pass_b_stage<true, 4, 8 * H, 8 * H + 8>(y, twB, lane);
+    pass_b_stage<true, 4, 8 * H, 8 * H + 8, MK>(y, twB, lane);
     FFT64_STAGE_MARK();
-    pass_b_stage<true, 3, 8 * H, 8 * H + 8>(y, twB, lane);
+    pass_b_stage<true, 3, 8 * H, 8 * H + 8, MK>(y, twB, lane);
     FFT64_STAGE_MARK();
-    pass_b_stage<true, 2, 8 * H, 8 * H + 8>(y, twB, lane);
+    pass_b_stage<true, 2, 8 * H, 8 * H + 8, MK>(y, twB, lane);
     FFT64_STAGE_MARK();
-    pass_b_stage<true, 1, 8 * H, 8 * H + 8>(y, twB, lane);
+    pass_b_stage<true, 1, 8 * H, 8 * H + 8, MK>(y, twB, lane);
 }
 // transposes through the warp's padded buffer
 __device__ __forceinline__ void col_to_row(double2 (&x)[32], double2 *buf, int lane) {
@@ -388,28 +389,76 @@ __device__ __forceinline__ void fft_inverse(double2 (&y)[32], double2 *buf, cons
 template <int TEAMS, int NS, int RS, int TWS = 1, int HB = 0, int GROUPS = 1, int KL = 0>
 struct Cfg {
     static constexpr int CONSUMER_WARPS = 2 * TEAMS;
-    static constexpr int THREADS = 32 * (CONSUMER_WARPS + (KL ? 0 : GROUPS));
+    static constexpr int THREADS = 32 * (CONSUMER_WARPS + (KL == 3 ? 4 : KL ? 0 : GROUPS));   // KL == 3: one producer warp per lane quadrant
     static constexpr int TEAMS_PER_GROUP = TEAMS / GROUPS;
     static constexpr int STAGE_POINTS = RS * 4 * 32;
     static constexpr int STAGES_PER_GGSW = 32 / RS;
     static constexpr int WARP_BUF_POINTS = HB ? HBUF_BYTES / 16 : BUF_POINTS;   // in double2 units
     static constexpr size_t SMEM =
         sizeof(double2) * TWB_ENTRIES * TWS + (size_t)TEAMS * (sizeof(u64) * 2 * N + sizeof(double2) * 2 * WARP_BUF_POINTS) +
-        (KL ? 0 : sizeof(double2) * (size_t)GROUPS * NS * STAGE_POINTS + sizeof(u64) * 2 * NS * GROUPS) + 16;
+        (KL == 3 ? sizeof(u64) * 16 : KL ? 0 : sizeof(double2) * (size_t)GROUPS * NS * STAGE_POINTS + sizeof(u64) * 2 * NS * GROUPS) + 16;
 };
+
+// ------------------------------------------------------------------------------------------ tensor memory as the key cache
+// KL == 3: the Fourier key does not pass through shared memory at all.  Tensor memory (256 KB per SM, 128 lanes x 512
+// 32-bit columns, a datapath of its own: tcgen05.ld / tcgen05.st) holds, for every lane quadrant, two whole GGSWs of the key
+// column that quadrant's consumer warps need (a warp reaches only the lanes 32 (warp % 4) .. +31, and warp parity = output
+// polynomial r, so a quadrant serves ONE r: 32 rows x 2 (j) x 4 words = 256 columns per GGSW, double-buffered in 512).
+// Column of (buffer b, row i, j, word c) = 256 b + 8 i + 4 j + c.  Four producer warps (one per quadrant) load the rows of
+// the NEXT iteration straight from L2 (ld.global.nc, lane-contiguous 512-byte rows) and tcgen05.st them while the consumers
+// transform; the consumers tcgen05.ld two rows at a time in the key MAC.  The crossbar loses a third of the MAC's traffic
+// (64 of 96 LDS.128 per warp), the ring, its waits and its lock step with it.
+__device__ __forceinline__ void tmem_ld16(u32 taddr, u32 (&v)[16]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]),
+          "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_st16(u32 taddr, const u32 (&v)[16]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};" ::"r"(taddr),
+        "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]), "r"(v[9]), "r"(v[10]),
+        "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15])
+        : "memory");
+}
+__device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void tmem_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tmem_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+// whole-CTA allocation of all 512 columns by one warp (the kernel wrapper calls these around the body: every CTA must free
+// what it took, or the next CTA on the SM spins on its allocation for ever)
+__device__ __forceinline__ void tmem_alloc_512(u32 *smem_slot) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(tk_smem_addr(smem_slot)) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_free_512(u32 taddr) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(taddr) : "memory");
+}
 
 // multiply-accumulate of the swapped spectra with the staged key rows: out = X0 K[0][r] + X1 K[1][r], in the oracle's order;
 // the RS rows of a stage advance together, one fused multiply-add of each chain at a time
 // HB: the partner's rows sit as [row - 16 * (row0 / 16)][lane] (half-size buffer, two rounds of 16 rows)
 template <int R, int RS, int HB = 0, int KG = 0>
-__device__ __forceinline__ void mac_rows(double2 (&y)[32], const double2 *oth, const double2 *stage, int row0, int lane) {
+__device__ __forceinline__ void mac_rows(double2 (&y)[32], const double2 *oth, const double2 *stage, int row0, int lane,
+                                         const u32 *kw = nullptr) {
     double2 k0[RS], k1[RS], x0[RS], x1[RS];
     double re[RS], im[RS];
+    // KG == 2: kw = the 16 words of two rows (RS == 2) of this quadrant's key column, already loaded from tensor memory
+    static_assert(KG != 2 || RS == 2, "tensor-memory key rows come two at a time");
 #pragma unroll
     for (int ii = 0; ii < RS; ii++) {
         const int i = row0 + ii;   // compile-time after unrolling of the caller
-        k0[ii] = KG ? __ldg(stage + (ii * 4 + 0 + R) * 32 + lane) : stage[(ii * 4 + 0 + R) * 32 + lane];
-        k1[ii] = KG ? __ldg(stage + (ii * 4 + 2 + R) * 32 + lane) : stage[(ii * 4 + 2 + R) * 32 + lane];
+        if (KG == 2) {
+            k0[ii] = make_double2(__hiloint2double((int)kw[(ii & 1) * 8 + 1], (int)kw[(ii & 1) * 8 + 0]),
+                                  __hiloint2double((int)kw[(ii & 1) * 8 + 3], (int)kw[(ii & 1) * 8 + 2]));
+            k1[ii] = make_double2(__hiloint2double((int)kw[(ii & 1) * 8 + 5], (int)kw[(ii & 1) * 8 + 4]),
+                                  __hiloint2double((int)kw[(ii & 1) * 8 + 7], (int)kw[(ii & 1) * 8 + 6]));
+        } else {
+            k0[ii] = KG ? __ldg(stage + (ii * 4 + 0 + R) * 32 + lane) : stage[(ii * 4 + 0 + R) * 32 + lane];
+            k1[ii] = KG ? __ldg(stage + (ii * 4 + 2 + R) * 32 + lane) : stage[(ii * 4 + 2 + R) * 32 + lane];
+        }
         const double2 o = HB ? oth[(i & 15) * 32 + lane] : oth[lane * ROWP + i];
         x0[ii] = R == 0 ? y[i] : o;
         x1[ii] = R == 0 ? o : y[i];
@@ -444,6 +493,25 @@ __device__ __forceinline__ void mac_global(double2 (&y)[32], const double2 *oth,
 #pragma unroll
     for (int c = C0; c < C1; c++) mac_rows<R, RS, HB, 1>(y, oth, ggsw + (size_t)c * RS * 4 * 32, c * RS, lane);
 }
+// KL == 3: chunks [C0, C1) of two rows each from tensor memory (taddr = quadrant lane base + buffer column base)
+// The loads are software-pipelined: the two rows of chunk c + 1 are requested before the multiply-adds of chunk c
+// (tcgen05.wait::ld waits for every earlier load of the thread, so the wait sits right before the next request).
+template <int R, int HB, int C0, int C1>
+__device__ __forceinline__ void mac_tmem(double2 (&y)[32], const double2 *oth, u32 taddr, int lane) {
+    u32 ka[16], kb[16];
+    tmem_ld16(taddr + 16u * C0, ka);
+#pragma unroll
+    for (int c = C0; c < C1; c += 2) {
+        tmem_wait_ld();
+        if (c + 1 < C1) tmem_ld16(taddr + 16u * (c + 1), kb);
+        mac_rows<R, 2, HB, 2>(y, oth, nullptr, c * 2, lane, ka);
+        if (c + 1 < C1) {
+            tmem_wait_ld();
+            if (c + 2 < C1) tmem_ld16(taddr + 16u * (c + 2), ka);
+            mac_rows<R, 2, HB, 2>(y, oth, nullptr, (c + 1) * 2, lane, kb);
+        }
+    }
+}
 // chunks [C0, C1) of the 32 / RS key-row chunks of one GGSW
 template <int R, int NS, int RS, int HB = 0, int C0 = 0, int C1 = 32 / RS>
 __device__ __forceinline__ void mac_all(double2 (&y)[32], const double2 *oth, const double2 *ring, u64 *full, u64 *empty, u32 &t, int lane) {
@@ -460,7 +528,7 @@ __device__ __forceinline__ void mac_all(double2 (&y)[32], const double2 *oth, co
 }
 
 template <int TEAMS, int NS, int RS, int TWS, int HB = 0, int GROUPS = 1, int KL = 0, int MK = 1>
-__device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *smem_raw) {
+__device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *smem_raw, u32 tmem_base = 0) {
     using C = Cfg<TEAMS, NS, RS, TWS, HB, GROUPS, KL>;
     static_assert(TEAMS % GROUPS == 0, "teams must split evenly into groups");
     constexpr int TPG = C::TEAMS_PER_GROUP;
@@ -484,6 +552,21 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
         const u32 lo = g * TPG;
         return live_teams <= lo ? 0u : (live_teams - lo < (u32)TPG ? live_teams - lo : (u32)TPG);
     };
+    // KL == 3: full / empty barrier of (quadrant q, buffer b) at index 2 q + b, in the place of the ring's barriers
+    u64 *tfull = (u64 *)ring_all, *tempty = tfull + 8;
+    auto quadrant_consumers = [&](u32 q) -> u32 {   // live consumer warps w = q, q + 4, ... of this CTA
+        u32 c = 0;
+        for (u32 w = q; w < (u32)C::CONSUMER_WARPS; w += 4) c += (w >> 1) < live_teams ? 1u : 0u;
+        return c;
+    };
+    if (KL == 3 && tid == 0) {
+        for (u32 q = 0; q < 4; q++)
+            for (u32 b = 0; b < 2; b++) {
+                mbar_init(tfull + 2 * q + b, 1);
+                mbar_init(tempty + 2 * q + b, quadrant_consumers(q) ? quadrant_consumers(q) : 1);
+            }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
     if (!KL && tid == 0) {
         for (int g = 0; g < GROUPS; g++)
             for (int s = 0; s < NS; s++) {
@@ -495,6 +578,39 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
     __syncthreads();
     const u32 total = a.steps * C::STAGES_PER_GGSW;
 
+    if (KL == 3 && warp >= C::CONSUMER_WARPS) {   // ---- tensor-memory producers: warp CONSUMER_WARPS + q feeds quadrant q
+        const u32 q = warp - C::CONSUMER_WARPS, pr = q & 1;
+        if (quadrant_consumers(q) == 0) return;
+        const u32 tq = tmem_base + ((32u * q) << 16);
+#pragma unroll 1
+        for (u32 it = 0; it < a.steps; it++) {
+            const u32 b = it & 1;
+            if (it >= 2) mbar_wait(tempty + 2 * q + b, ((it >> 1) - 1) & 1);
+            tmem_fence_after();
+            const double2 *g = a.bsk + (size_t)it * 32 * 4 * 32;
+#pragma unroll 4
+            for (int i0 = 0; i0 < 32; i0 += 2) {
+                u32 v[16];
+#pragma unroll
+                for (int ii = 0; ii < 2; ii++)
+#pragma unroll
+                    for (int j = 0; j < 2; j++) {
+                        const double2 k = __ldg(g + ((i0 + ii) * 4 + 2 * j + pr) * 32 + lane);
+                        v[ii * 8 + j * 4 + 0] = (u32)__double2loint(k.x);
+                        v[ii * 8 + j * 4 + 1] = (u32)__double2hiint(k.x);
+                        v[ii * 8 + j * 4 + 2] = (u32)__double2loint(k.y);
+                        v[ii * 8 + j * 4 + 3] = (u32)__double2hiint(k.y);
+                    }
+                tmem_st16(tq + 256u * b + 8u * (u32)i0, v);
+                if (a.stagger_ns) __nanosleep(a.stagger_ns);   // spread the refill over the iteration instead of one burst after the MAC
+            }
+            tmem_wait_st();
+            tmem_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tfull + 2 * q + b);
+        }
+        return;
+    }
     if (!KL && warp >= C::CONSUMER_WARPS) {   // ---- producer warps (one per group): one lane streams the key rows
         const u32 g = warp - C::CONSUMER_WARPS;
         double2 *ring = ring_all + (size_t)g * NS * C::STAGE_POINTS;
@@ -533,6 +649,7 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
     u32 t = 0;
     u64 mask = a.steps ? lwe[0] : 0;
     const int barrier_id = 1 + team;
+    const u32 tq = tmem_base + ((32u * ((u32)warp & 3u)) << 16);   // KL == 3: this warp's lane quadrant of tensor memory
     if (GROUPS > 1 && grp) __nanosleep(a.stagger_ns * grp);   // start the groups out of phase
     long long mark_ = a.trace ? clock64() : 0;
     const u32 dg_half = 1u << (31 - a.logB), dg_sh = 32 - a.logB;
@@ -546,7 +663,7 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
     for (u32 it = 0; it < a.steps; it++) {
         // KL == 2: no ring, but the live consumer warps of the CTA meet once per iteration: they then ask for the same key
         // rows at about the same time (one L2 request, L1 hits for the rest) and keep sharing instruction fetches
-        if (KL == 2) asm volatile("bar.sync 15, %0;" ::"r"(64u * live_teams) : "memory");
+        if (KL == 2 || KL == 3) asm volatile("bar.sync 15, %0;" ::"r"(64u * live_teams) : "memory");
         const u32 sh = mod_switch(mask);
         if (it + 1 < a.steps) mask = lwe[it + 1];
         double2 x[32];
@@ -581,6 +698,10 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
         FFT64_MARK(2);
         pass_b<false, MK>(x, twB, lane, a, mark_);
         FFT64_MARK(3);
+        if (KL == 3) {   // this iteration's key rows sit in buffer it & 1 of the quadrant (stored during the previous iteration)
+            mbar_wait(tfull + 2 * ((u32)warp & 3u) + (it & 1u), (it >> 1) & 1u);
+            tmem_fence_after();
+        }
         // swap spectra with the partner warp
         if (!HB) {
 #pragma unroll
@@ -591,17 +712,21 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
             // stream in (the ring holds half a GGSW), then rows 16..31
             constexpr int CH = 16 / RS;
             if (r == 0)
-                (KL ? mac_global<0, RS, 0, 0, CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
+                (KL == 3 ? mac_tmem<0, 0, (0) * RS / 2, (CH) * RS / 2>(x, buf_oth, tq + 256u * (it & 1u), lane)
+                 : KL ? mac_global<0, RS, 0, 0, CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
                     : mac_all<0, NS, RS, 0, 0, CH>(x, buf_oth, ring, full, empty, t, lane));
             else
-                (KL ? mac_global<1, RS, 0, 0, CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
+                (KL == 3 ? mac_tmem<1, 0, (0) * RS / 2, (CH) * RS / 2>(x, buf_oth, tq + 256u * (it & 1u), lane)
+                 : KL ? mac_global<1, RS, 0, 0, CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
                     : mac_all<1, NS, RS, 0, 0, CH>(x, buf_oth, ring, full, empty, t, lane));
             pass_b_inv_half<0, MK>(x, twB, lane, a, mark_);
             if (r == 0)
-                (KL ? mac_global<0, RS, 0, CH, 2 * CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
+                (KL == 3 ? mac_tmem<0, 0, (CH) * RS / 2, (2 * CH) * RS / 2>(x, buf_oth, tq + 256u * (it & 1u), lane)
+                 : KL ? mac_global<0, RS, 0, CH, 2 * CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
                     : mac_all<0, NS, RS, 0, CH, 2 * CH>(x, buf_oth, ring, full, empty, t, lane));
             else
-                (KL ? mac_global<1, RS, 0, CH, 2 * CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
+                (KL == 3 ? mac_tmem<1, 0, (CH) * RS / 2, (2 * CH) * RS / 2>(x, buf_oth, tq + 256u * (it & 1u), lane)
+                 : KL ? mac_global<1, RS, 0, CH, 2 * CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
                     : mac_all<1, NS, RS, 0, CH, 2 * CH>(x, buf_oth, ring, full, empty, t, lane));
             FFT64_MARK(5);
             asm volatile("bar.sync %0, 64;" ::"r"(barrier_id) : "memory");
@@ -615,10 +740,12 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
             asm volatile("bar.sync %0, 64;" ::"r"(barrier_id) : "memory");
             FFT64_MARK(4);
             if (r == 0)
-                (KL ? mac_global<0, RS, 1, 0, CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
+                (KL == 3 ? mac_tmem<0, 1, (0) * RS / 2, (CH) * RS / 2>(x, buf_oth, tq + 256u * (it & 1u), lane)
+                 : KL ? mac_global<0, RS, 1, 0, CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
                     : mac_all<0, NS, RS, 1, 0, CH>(x, buf_oth, ring, full, empty, t, lane));
             else
-                (KL ? mac_global<1, RS, 1, 0, CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
+                (KL == 3 ? mac_tmem<1, 1, (0) * RS / 2, (CH) * RS / 2>(x, buf_oth, tq + 256u * (it & 1u), lane)
+                 : KL ? mac_global<1, RS, 1, 0, CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
                     : mac_all<1, NS, RS, 1, 0, CH>(x, buf_oth, ring, full, empty, t, lane));
             FFT64_MARK(5);
             asm volatile("bar.sync %0, 64;" ::"r"(barrier_id) : "memory");
@@ -628,17 +755,24 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
             FFT64_MARK(4);
             pass_b_inv_half<0, MK>(x, twB, lane, a, mark_);   // rows 0..15 are final: their inverse butterflies cover the wait for the key rows
             if (r == 0)
-                (KL ? mac_global<0, RS, 1, CH, 2 * CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
+                (KL == 3 ? mac_tmem<0, 1, (CH) * RS / 2, (2 * CH) * RS / 2>(x, buf_oth, tq + 256u * (it & 1u), lane)
+                 : KL ? mac_global<0, RS, 1, CH, 2 * CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
                     : mac_all<0, NS, RS, 1, CH, 2 * CH>(x, buf_oth, ring, full, empty, t, lane));
             else
-                (KL ? mac_global<1, RS, 1, CH, 2 * CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
+                (KL == 3 ? mac_tmem<1, 1, (CH) * RS / 2, (2 * CH) * RS / 2>(x, buf_oth, tq + 256u * (it & 1u), lane)
+                 : KL ? mac_global<1, RS, 1, CH, 2 * CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
                     : mac_all<1, NS, RS, 1, CH, 2 * CH>(x, buf_oth, ring, full, empty, t, lane));
             FFT64_MARK(5);
             asm volatile("bar.sync %0, 64;" ::"r"(barrier_id) : "memory");
             FFT64_MARK(6);
             pass_b_inv_half<1, MK>(x, twB, lane, a, mark_);
         }
-        pass_b_stage<true, 0>(x, twB, lane);
+        if (KL == 3) {   // the buffer may be refilled (with the rows of iteration it + 2)
+            tmem_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tempty + 2 * ((u32)warp & 3u) + (it & 1u));
+        }
+        pass_b_stage<true, 0, 0, 16, MK>(x, twB, lane);
         FFT64_MARK(7);
         if (HB)
             row_to_col_h(x, (double *)buf, lane);
