@@ -512,10 +512,88 @@ __device__ __forceinline__ void mac_tmem(double2 (&y)[32], const double2 *oth, u
         }
     }
 }
-// chunks [C0, C1) of the 32 / RS key-row chunks of one GGSW
+// two rows of one ring stage (and the partner's two rows) in registers: the unit of the software-pipelined MAC below
+struct KeyRows2 {
+    double2 k0[2], k1[2], o[2];
+};
+template <int R, int HB>
+__device__ __forceinline__ void load_rows2(KeyRows2 &d, const double2 *stage, const double2 *oth, int ii0, int row, int lane) {
+#pragma unroll
+    for (int ii = 0; ii < 2; ii++) {
+        d.k0[ii] = stage[((ii0 + ii) * 4 + 0 + R) * 32 + lane];
+        d.k1[ii] = stage[((ii0 + ii) * 4 + 2 + R) * 32 + lane];
+        d.o[ii] = HB ? oth[((row + ii) & 15) * 32 + lane] : oth[lane * ROWP + row + ii];
+    }
+}
+// out = X0 K[0][r] + X1 K[1][r] for rows row, row + 1: per point the oracle's chain of four fused multiply-adds
+template <int R>
+__device__ __forceinline__ void mac_rows2(double2 (&y)[32], const KeyRows2 &d, int row) {
+    double re[2], im[2];
+    double2 x0[2], x1[2];
+#pragma unroll
+    for (int ii = 0; ii < 2; ii++) {
+        x0[ii] = R == 0 ? y[row + ii] : d.o[ii];
+        x1[ii] = R == 0 ? d.o[ii] : y[row + ii];
+    }
+#pragma unroll
+    for (int ii = 0; ii < 2; ii++) {
+        re[ii] = __fma_rn(x0[ii].x, d.k0[ii].x, 0.0);
+        im[ii] = __fma_rn(x0[ii].x, d.k0[ii].y, 0.0);
+    }
+#pragma unroll
+    for (int ii = 0; ii < 2; ii++) {
+        re[ii] = __fma_rn(-x0[ii].y, d.k0[ii].y, re[ii]);
+        im[ii] = __fma_rn(x0[ii].y, d.k0[ii].x, im[ii]);
+    }
+#pragma unroll
+    for (int ii = 0; ii < 2; ii++) {
+        re[ii] = __fma_rn(x1[ii].x, d.k1[ii].x, re[ii]);
+        im[ii] = __fma_rn(x1[ii].x, d.k1[ii].y, im[ii]);
+    }
+#pragma unroll
+    for (int ii = 0; ii < 2; ii++) {
+        re[ii] = __fma_rn(-x1[ii].y, d.k1[ii].y, re[ii]);
+        im[ii] = __fma_rn(x1[ii].y, d.k1[ii].x, im[ii]);
+    }
+#pragma unroll
+    for (int ii = 0; ii < 2; ii++) y[row + ii] = make_double2(re[ii], im[ii]);
+}
+// chunks [C0, C1) of the 32 / RS key-row chunks of one GGSW.
+// -DFFT64_MAC_PIPE=1 (RS == 4): software-pipelined — the loads of the next two rows (key rows and partner rows, the next
+// stage's full barrier first where they are its rows) are issued before the multiply-adds of the current two, so the
+// shared-memory latency of the MAC (ncu: 10 % of all stall samples sit on the first multiply-add of a chunk) overlaps the
+// FP64 work.  Measured: the MAC phase drops from 5.75 k to 4.9 k cycles but the 48 extra live registers slow every other
+// phase (94.5 ms vs 85.8 ms at B = 4,736): off by default (profiles/r02b_fft_variants.txt).
+#ifndef FFT64_MAC_PIPE
+#define FFT64_MAC_PIPE 0
+#endif
 template <int R, int NS, int RS, int HB = 0, int C0 = 0, int C1 = 32 / RS>
 __device__ __forceinline__ void mac_all(double2 (&y)[32], const double2 *oth, const double2 *ring, u64 *full, u64 *empty, u32 &t, int lane) {
     constexpr int SP = RS * 4 * 32;
+    if (FFT64_MAC_PIPE && RS == 4) {
+        KeyRows2 A, B;
+        u32 s = t % NS;
+        mbar_wait(full + s, (t / NS) & 1);
+        const double2 *stage = ring + (size_t)s * SP;
+        load_rows2<R, HB>(A, stage, oth, 0, C0 * RS, lane);
+#pragma unroll
+        for (int c = C0; c < C1; c++) {
+            load_rows2<R, HB>(B, stage, oth, 2, c * RS + 2, lane);
+            mac_rows2<R>(y, A, c * RS);
+            const u32 s_cur = s;
+            if (c + 1 < C1) {
+                s = (t + 1) % NS;
+                mbar_wait(full + s, ((t + 1) / NS) & 1);
+                stage = ring + (size_t)s * SP;
+                load_rows2<R, HB>(A, stage, oth, 0, (c + 1) * RS, lane);
+            }
+            mac_rows2<R>(y, B, c * RS + 2);
+            __syncwarp();
+            if (lane == 0) mbar_arrive(empty + s_cur);
+            t++;
+        }
+        return;
+    }
 #pragma unroll
     for (int c = C0; c < C1; c++) {
         const u32 s = t % NS;
