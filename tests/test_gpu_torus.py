@@ -148,6 +148,63 @@ def test_blind_rotate_per_iteration_bit_exact(rig_small, steps):
     assert np.array_equal(got, want), f"accumulators differ after {steps} CMUX steps"
 
 
+@pytest.mark.parametrize("steps", [0, 1, 3, None])
+def test_latency_kernel_equals_throughput_kernel_and_oracle(rig_small, steps):
+    """the latency form (fft64_lat.cuh: one ciphertext per CTA, eight warps, taken by default when B <= #SMs) against the
+    warp-per-polynomial form and the oracle, accumulators after `steps` CMUX iterations, bit for bit"""
+    e, p = rig_small.eng, rig_small.p
+    rs = np.random.RandomState(16)
+    B = 5
+    lwe = u64_rand(rs, (B, p.n + 1))
+    lwe[0, :] = 0
+    lwe[1, :] = 2**64 - 1
+    tvs = u64_rand(rs, (2, p.N))
+    idx = np.array([0, 1, 1, 0, 1], np.uint32)
+    try:
+        e.fft_lat_mode(1)
+        lat = e.blind_rotate(lwe, tvs, idx, steps=steps)
+        e.fft_lat_mode(0)
+        thr = e.blind_rotate(lwe, tvs, idx, steps=steps)
+    finally:
+        e.fft_lat_mode(-1)
+    want = np.stack([rig_small.ctx.blind_rotate(lwe[b], tvs[idx[b]], steps=steps) for b in range(B)])
+    assert np.array_equal(lat, want), "latency kernel differs from oracle/torus.c"
+    assert np.array_equal(thr, want), "throughput kernel differs from oracle/torus.c"
+
+
+def test_latency_kernel_whole_pbs_both_orders_and_large_batch(rig_small, rig_small_o2, rig_s2):
+    """whole PBS through the latency kernel: both orders at the test set, a batch larger than the SM count forced through it
+    (grid > #SMs), and the named set (single ciphertext and a ragged small batch) against the oracle"""
+    for r, B in ((rig_small, 1), (rig_small, 301), (rig_small_o2, 9)):
+        e, p = r.eng, r.p
+        rs = np.random.RandomState(17 + B)
+        cts = u64_rand(rs, (B, p.ct_len))
+        tvs = u64_rand(rs, (3, p.N))
+        idx = rs.randint(0, 3, B).astype(np.uint32)
+        try:
+            e.fft_lat_mode(1)
+            got = e.pbs_batch(cts, tvs, idx)
+        finally:
+            e.fft_lat_mode(-1)
+        pick = np.unique(np.concatenate([[0, B - 1], rs.randint(0, B, 6)]))
+        want, _ = r.ctx.pbs_batch(cts[pick], tvs, idx[pick])
+        assert np.array_equal(got[pick], want), (p.order, B)
+    e, p = rig_s2.eng, rig_s2.p
+    rs = np.random.RandomState(18)
+    for B in (1, 11):
+        cts = u64_rand(rs, (B, p.ct_len))
+        tvs = u64_rand(rs, (2, p.N))
+        idx = rs.randint(0, 2, B).astype(np.uint32)
+        got = e.pbs_batch(cts, tvs, idx)            # default mode: B <= #SMs takes the latency kernel
+        e.fft_lat_mode(0)
+        try:
+            thr = e.pbs_batch(cts, tvs, idx)
+        finally:
+            e.fft_lat_mode(-1)
+        want, _ = rig_s2.ctx.pbs_batch(cts, tvs, idx)
+        assert np.array_equal(got, want) and np.array_equal(thr, want), B
+
+
 @pytest.mark.parametrize("teams", [1, 2, 3, 13, 4, 14, 24, 34, 54])
 def test_pbs_small_bit_exact_every_team_count(rig_small, teams):
     """whole PBS (key switch, blind rotation, extraction) against the oracle, every ciphertext of a ragged batch,

@@ -1,6 +1,7 @@
 // br_fft.cu — kernels and launchers of the 2^64-torus / f64-FFT arithmetic (fft64.cuh).
 #include "engine.h"
 #include "fft64.cuh"
+#include "fft64_lat.cuh"
 
 #include <cmath>
 #include <vector>
@@ -24,6 +25,11 @@ __global__ void __launch_bounds__(Cfg<TEAMS, NS, RS, TWS, HB, GROUPS, KL>::THREA
         return;
     }
     blind_rotate_body<TEAMS, NS, RS, TWS, HB, GROUPS, KL, MK>(a, smem);
+}
+
+__global__ void __launch_bounds__(LAT_THREADS, 1) blind_rotate_fft_lat_kernel(const __grid_constant__ LatArgs la) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    blind_rotate_lat_body(la, smem);
 }
 
 constexpr int UTIL_WARPS = 4;
@@ -91,6 +97,9 @@ int lux_fft_init(lux_engine *e) {
             for (int lane = 0; lane < 32; lane++) twB[16 * g + ee * 32 + lane] = tw[32 * g + lane * g + 2 * ee];
     if (cudaMalloc(&e->d_fft_twB, sizeof(double2) * TWB_ENTRIES) != cudaSuccess) return LUX_ERR_OOM;
     if (cudaMemcpy(e->d_fft_twB, twB.data(), sizeof(double2) * TWB_ENTRIES, cudaMemcpyHostToDevice) != cudaSuccess) return LUX_ERR_CUDA;
+    // the whole tree for the latency kernel (fft64_lat.cuh): node v at index v, the same doubles
+    if (cudaMalloc(&e->d_fft_twFull, sizeof(double2) * M) != cudaSuccess) return LUX_ERR_OOM;
+    if (cudaMemcpy(e->d_fft_twFull, tw.data(), sizeof(double2) * M, cudaMemcpyHostToDevice) != cudaSuccess) return LUX_ERR_CUDA;
     return LUX_OK;
 }
 
@@ -135,6 +144,19 @@ int lux_fft_launch_br(lux_engine *e, Args a, cudaStream_t s) {
     a.stagger_ns = (u32)e->fft_stagger_ns;
     a.trace = (u64 *)e->d_fft_trace;
     const int variant = e->fft_variant;   // 0 = the default of each team count; the others are the measured alternatives
+    // a batch that leaves SMs idle anyway: one ciphertext per CTA, eight warps per ciphertext (fft64_lat.cuh)
+    if ((e->fft_lat_mode == 1 || (e->fft_lat_mode < 0 && e->force_teams == 0 && a.B <= (u32)e->sm_count)) && a.B > 0) {
+        static bool configured[64] = {};
+        if (!configured[e->device & 63]) {
+            CUDA_TRY(e, cudaFuncSetAttribute(blind_rotate_fft_lat_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LAT_SMEM));
+            configured[e->device & 63] = true;
+        }
+        LatArgs la{a, (const double2 *)e->d_fft_twFull};
+        blind_rotate_fft_lat_kernel<<<a.B, LAT_THREADS, LAT_SMEM, s>>>(la);
+        e->launches++;
+        CUDA_TRY(e, cudaGetLastError());
+        return LUX_OK;
+    }
     switch (pick_teams(e, a.B)) {
         case 1:   // a warp alone on its scheduler: free instruction schedule (no phase marks)
             if (variant == 1) return launch_cfg<1, 4, 8, 1>(e, a, s);

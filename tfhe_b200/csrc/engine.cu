@@ -629,6 +629,7 @@ void lux_engine_destroy(lux_engine *e) {
     if (e->d_kskT) cudaFree(e->d_kskT);
     if (e->d_ks_dig) cudaFree(e->d_ks_dig);
     if (e->d_fft_twB) cudaFree(e->d_fft_twB);
+    if (e->d_fft_twFull) cudaFree(e->d_fft_twFull);
     if (e->d_tw_fwd) cudaFree(e->d_tw_fwd);
     if (e->d_blob) cudaFree(e->d_blob);
     for (int i = 0; i < 4; i++)
@@ -701,6 +702,11 @@ int lux_debug_fft_variant(lux_engine *e, int variant) {
     LUX_LOCK(e);
     if (!e) return LUX_ERR_INVALID;
     e->fft_variant = variant;
+    return LUX_OK;
+}
+int lux_debug_fft_lat_mode(lux_engine *e, int mode) {
+    if (!e || mode < -1 || mode > 1) return LUX_ERR_INVALID;
+    e->fft_lat_mode = mode;
     return LUX_OK;
 }
 int lux_debug_fft_stagger(lux_engine *e, int ns) {

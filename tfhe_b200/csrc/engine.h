@@ -59,6 +59,8 @@ struct lux_engine {
     // pass-B table in device memory
     double fft_twA[64] = {};
     void *d_fft_twB = nullptr;
+    void *d_fft_twFull = nullptr;   // whole twiddle tree (latency kernel)
+    int fft_lat_mode = -1;          // -1 = latency kernel when B <= #SMs, 0 = never, 1 = always (tests)
     int fft_default_teams = 3;
     void *d_fft_trace = nullptr;  // 16 phase-cycle counters (FFT64_TRACE_BUILD builds; lux_debug_fft_trace)
     int fft_stagger_ns = 6000;    // start delay between the groups of a CTA (kernels with GROUPS > 1)
@@ -83,6 +85,7 @@ extern "C" int lux_debug_cluster_regs(lux_engine *e, int regs);
 extern "C" int lux_debug_br_regs(lux_engine *e, int regs);
 extern "C" int lux_debug_fft_variant(lux_engine *e, int variant);
 extern "C" int lux_debug_fft_stagger(lux_engine *e, int ns);
+extern "C" int lux_debug_fft_lat_mode(lux_engine *e, int mode);
 extern "C" int lux_debug_fft_trace(lux_engine *e, unsigned long long out[16]);
 extern "C" int lux_debug_int_peak(lux_engine *e, double out[3]);
 extern "C" int lux_debug_field_probe(lux_engine *e, const uint64_t *a, const uint64_t *b, size_t count, uint64_t *out);

@@ -408,6 +408,11 @@ class Engine:
         self._ck(lib().lux_debug_fft_trace(self._h, C.byref(buf)))
         return [int(v) for v in buf]
 
+    def fft_lat_mode(self, mode: int):
+        """-1 = latency kernel (one ciphertext per CTA, eight warps) when the batch leaves SMs idle, 0 = never, 1 = always"""
+        lib().lux_debug_fft_lat_mode.argtypes = [_vp, _int]
+        self._ck(lib().lux_debug_fft_lat_mode(self._h, mode))
+
     def fft_stagger(self, ns: int):
         lib().lux_debug_fft_stagger.argtypes = [_vp, _int]
         self._ck(lib().lux_debug_fft_stagger(self._h, ns))
