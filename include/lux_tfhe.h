@@ -174,6 +174,23 @@ int lux_pbs_batch(lux_engine *e, const uint64_t *lwe_in, const uint64_t *testvs,
 /* same with every buffer already in device memory; stream = cudaStream_t or NULL for the engine's */
 int lux_pbs_batch_device(lux_engine *e, const uint64_t *d_lwe_in, const uint64_t *d_testvs, uint32_t n_luts,
                          const uint32_t *d_lut_idx, size_t B, uint64_t *d_lwe_out, void *stream);
+/* lux_pbs_batch_device that ALLOCATES NOTHING.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * lux_pbs_batch_device keeps the key-switched ciphertexts and the key switch's digit matrix in engine-owned scratch that it
+ * grows with cudaMalloc; this variant keeps them in one file-scope `static __device__` array of LUX_STATIC_SCRATCH_BYTES inside
+ * the library (every GPU that loads the library holds it until exit) and calls no cudaMalloc / cudaFree / allocating
+ * library routine.  Same arguments, same result words as lux_pbs_batch_device.  Limits:
+ *  - LUX_ARITH_TORUS64_FFT engines only, with the bootstrap key and the LWE key switch key loaded;
+ *  - the batch must fit the array: ceil(B/128)*128 * k*N*ell_ks bytes of digits (rounded up to 256) plus
+ *    B * (n+1) words (order LWEKS_PBS) or B * (k*N+1) words (order PBS_GLWEKS); at the named S2 set that is B <= 1024.
+ *    A larger batch is refused with LUX_ERR_INVALID and a message that states the bytes needed, the limit and the largest B;
+ *  - every call on a GPU, from any engine, shares the array, and it keeps the last call's contents (nothing in it has to start
+ *    at zero: every word the kernels read is written earlier in the same call).  Calls that overlap ON THE GPU (two streams,
+ *    two engines on one device) race; calls on one engine are serialised on the host like every other entry point, so pass the
+ *    same stream, or order the streams yourself. */
+#define LUX_STATIC_SCRATCH_BYTES (16u << 20)
+int lux_pbs_batch_device_static(lux_engine *e, const uint64_t *d_lwe_in, const uint64_t *d_testvs, uint32_t n_luts,
+                                const uint32_t *d_lut_idx, size_t B, uint64_t *d_lwe_out, void *stream);
 
 /* ---- boolean gates: ONE programmable bootstrap per gate (BASELINE config 1, "single boolean-gate (NAND)
  * programmable bootstrap"; parameter set main.rs:23-30).  A bit m is the LWE encryption of m * lux_delta(4)

@@ -878,6 +878,76 @@ int lux_pbs_batch_device(lux_engine *e, const uint64_t *d_in, const uint64_t *d_
     return lux_pbs_device_grouped(e, d_in, d_testvs, d_lut_idx, 1, B, d_out, stream ? (cudaStream_t)stream : e->stream);
 }
 
+// ---- PBS that allocates nothing (include/lux_tfhe.h, lux_pbs_batch_device_static; no counterpart in the reference).
+// The scratch of torus_pbs_device — the key switch's digit matrix and the ciphertexts
+// between key switch and blind rotation — lives in this file-scope device array instead of cudaMalloc'ed engine scratch.
+// In host code `g_static_scratch` is only a stand-in for the symbol: its device address is taken once per device, with that
+// device current, by cudaGetSymbolAddress below, and that pointer is what the kernels get.
+static __device__ __align__(256) unsigned char g_static_scratch[LUX_STATIC_SCRATCH_BYTES];
+static unsigned char *g_static_scratch_ptr[64] = {};
+static std::mutex g_static_scratch_mtx;
+
+static int static_scratch_ptr(lux_engine *e, unsigned char **out) {
+    if (e->device < 0 || e->device >= 64) LUX_FAIL(e, LUX_ERR_INVALID, "device ordinal %d outside the static scratch table", e->device);
+    std::lock_guard<std::mutex> lk(g_static_scratch_mtx);
+    if (!g_static_scratch_ptr[e->device]) {
+        void *p = nullptr;
+        cudaError_t st = cudaGetSymbolAddress(&p, g_static_scratch);
+        if (st != cudaSuccess || !p) LUX_FAIL(e, LUX_ERR_CUDA, "cudaGetSymbolAddress(static scratch) on GPU %d: %s", e->device, cudaGetErrorString(st));
+        CUDA_TRY(e, cudaFuncSetAttribute(ksmma::lwe_keyswitch_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ksmma::SMEM_BYTES));
+        g_static_scratch_ptr[e->device] = (unsigned char *)p;
+    }
+    *out = g_static_scratch_ptr[e->device];
+    return LUX_OK;
+}
+
+int lux_pbs_batch_device_static(lux_engine *e, const uint64_t *d_in, const uint64_t *d_testvs, uint32_t n_luts,
+                                const uint32_t *d_lut_idx, size_t B, uint64_t *d_out, void *stream) {
+    LUX_LOCK(e);
+    if (!e) return LUX_ERR_INVALID;
+    if (!d_in || !d_testvs || !d_out || n_luts == 0) LUX_FAIL(e, LUX_ERR_INVALID, "lux_pbs_batch_device_static: null/empty argument");
+    if (!lux_is_torus(e)) LUX_FAIL(e, LUX_ERR_INVALID, "lux_pbs_batch_device_static: LUX_ARITH_TORUS64_FFT engines only");
+    if (!e->has_bsk) LUX_FAIL(e, LUX_ERR_NO_KEY, "bootstrap key not loaded");
+    if (!e->has_lksk || !e->d_kskT) LUX_FAIL(e, LUX_ERR_NO_KEY, "LWE key switch key not loaded");
+    if (B == 0) return LUX_OK;
+    const lux_params &p = e->p;
+    const bool ks_first = p.order == LUX_ORDER_LWEKS_PBS;
+    const size_t kN = (size_t)p.k * p.N, K = kN * p.ell_ks, mid_words = ks_first ? (size_t)p.n + 1 : kN + 1;
+    auto dig_bytes = [&](size_t b) { return ((b + ksmma::BM - 1) / ksmma::BM * ksmma::BM * K + 255) / 256 * 256; };
+    const size_t need = dig_bytes(B) + sizeof(u64) * B * mid_words;
+    if (B > 0x7fffffffu || need > LUX_STATIC_SCRATCH_BYTES) {
+        size_t bmax = 0;
+        while (dig_bytes(bmax + 1) + sizeof(u64) * (bmax + 1) * mid_words <= LUX_STATIC_SCRATCH_BYTES) bmax++;
+        LUX_FAIL(e, LUX_ERR_INVALID, "lux_pbs_batch_device_static: a batch of %zu needs %zu bytes of scratch, the static array holds %u "
+                 "(largest batch at this parameter set: %zu); split the batch or call lux_pbs_batch_device", B, need,
+                 (unsigned)LUX_STATIC_SCRATCH_BYTES, bmax);
+    }
+    CUDA_TRY(e, cudaSetDevice(e->device));
+    unsigned char *base = nullptr;
+    int rc = static_scratch_ptr(e, &base);
+    if (rc) return rc;
+    cudaStream_t s = stream ? (cudaStream_t)stream : e->stream;
+    int8_t *d_dig = (int8_t *)base;                       // [Mpad][K]; ks_digits_kernel writes every row, the padding rows as zero
+    u64 *d_mid = (u64 *)(base + dig_bytes(B));            // [B][mid_words]; every word written before it is read
+    const u32 mpad = (u32)((B + ksmma::BM - 1) / ksmma::BM * ksmma::BM);
+    auto key_switch = [&](const u64 *src, u64 *dst) -> int {
+        ksmma::ks_digits_kernel<<<e->sm_count * 8, 256, 0, s>>>(src, d_dig, (u32)B, mpad, (u32)kN, p.ell_ks, p.logB_ks, e->L_ks, 1u);
+        e->launches++;
+        CUDA_TRY(e, cudaGetLastError());
+        ksmma::Args ka{d_dig, e->d_kskT, src, dst, (u32)B, p.n, (u32)kN, (u32)K, 1u};
+        dim3 grid(e->ks_npad / ksmma::BN, mpad / ksmma::BM);
+        ksmma::lwe_keyswitch_mma_kernel<<<grid, ksmma::THREADS, ksmma::SMEM_BYTES, s>>>(ka);
+        e->launches++;
+        CUDA_TRY(e, cudaGetLastError());
+        return LUX_OK;
+    };
+    if (ks_first && (rc = key_switch(d_in, d_mid))) return rc;
+    fft64::Args a = make_fft_args(e, ks_first ? d_mid : d_in, d_testvs, d_lut_idx, 1, B, ks_first ? d_out : d_mid);
+    if ((rc = lux_fft_launch_br(e, a, s))) return rc;
+    if (!ks_first && (rc = key_switch(d_mid, d_out))) return rc;
+    return LUX_OK;
+}
+
 int lux_pbs_batch(lux_engine *e, const uint64_t *lwe_in, const uint64_t *testvs, uint32_t n_luts,
                   const uint32_t *lut_idx, size_t B, uint64_t *lwe_out) {
     LUX_LOCK(e);

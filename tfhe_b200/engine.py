@@ -118,6 +118,7 @@ ABI = {
     "lux_import_keys_device": (_int, [_vp, _vp, _sz]),
     "lux_pbs_batch": (_int, [_vp, _vp, _vp, _u32, _vp, _sz, _vp]),
     "lux_pbs_batch_device": (_int, [_vp, _vp, _vp, _u32, _vp, _sz, _vp, _vp]),
+    "lux_pbs_batch_device_static": (_int, [_vp, _vp, _vp, _u32, _vp, _sz, _vp, _vp]),
     "lux_gate_batch": (_int, [_vp, _int, _vp, _vp, _sz, _vp]),
     "lux_gate_batch_device": (_int, [_vp, _int, _vp, _vp, _sz, _vp, _vp]),
     "lux_gate_not": (_int, [_vp, _vp, _sz, _vp]),
@@ -332,6 +333,15 @@ class Engine:
         self._ck(lib().lux_pbs_batch_device(self._h, d_in.data_ptr(), d_testvs.data_ptr(), n_luts,
                                             None if d_lut_idx is None else d_lut_idx.data_ptr(), B, d_out.data_ptr(),
                                             stream))
+
+    def pbs_batch_device_static(self, d_in, d_testvs, d_lut_idx, B: int, d_out, n_luts: int | None = None, stream=None):
+        """pbs_batch_device without any allocation inside the library (lux_pbs_batch_device_static: scratch in a static
+        device array of 16 MiB; torus engines, B <= 1024 at the named set; overlapping calls on one GPU race)."""
+        if n_luts is None:
+            n_luts = d_testvs.numel() // self.p.N
+        self._ck(lib().lux_pbs_batch_device_static(self._h, d_in.data_ptr(), d_testvs.data_ptr(), n_luts,
+                                                   None if d_lut_idx is None else d_lut_idx.data_ptr(), B, d_out.data_ptr(),
+                                                   stream))
 
     def synchronize(self):
         self._ck(lib().lux_synchronize(self._h))
