@@ -160,15 +160,21 @@ def test_latency_kernel_equals_throughput_kernel_and_oracle(rig_small, steps):
     lwe[1, :] = 2**64 - 1
     tvs = u64_rand(rs, (2, p.N))
     idx = np.array([0, 1, 1, 0, 1], np.uint32)
+    lat = {}
     try:
         e.fft_lat_mode(1)
-        lat = e.blind_rotate(lwe, tvs, idx, steps=steps)
+        for variant in (0, 1, 2, 3):          # accumulator in registers / late key request (fft64_lat.cuh, V)
+            e.fft_variant(variant)
+            lat[variant] = e.blind_rotate(lwe, tvs, idx, steps=steps)
+        e.fft_variant(0)
         e.fft_lat_mode(0)
         thr = e.blind_rotate(lwe, tvs, idx, steps=steps)
     finally:
+        e.fft_variant(0)
         e.fft_lat_mode(-1)
     want = np.stack([rig_small.ctx.blind_rotate(lwe[b], tvs[idx[b]], steps=steps) for b in range(B)])
-    assert np.array_equal(lat, want), "latency kernel differs from oracle/torus.c"
+    for variant, got in lat.items():
+        assert np.array_equal(got, want), f"latency kernel (variant {variant}) differs from oracle/torus.c"
     assert np.array_equal(thr, want), "throughput kernel differs from oracle/torus.c"
 
 

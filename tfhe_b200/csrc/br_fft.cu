@@ -27,9 +27,23 @@ __global__ void __launch_bounds__(Cfg<TEAMS, NS, RS, TWS, HB, GROUPS, KL>::THREA
     blind_rotate_body<TEAMS, NS, RS, TWS, HB, GROUPS, KL, MK>(a, smem);
 }
 
+template <int V>
 __global__ void __launch_bounds__(LAT_THREADS, 1) blind_rotate_fft_lat_kernel(const __grid_constant__ LatArgs la) {
     extern __shared__ __align__(16) unsigned char smem[];
-    blind_rotate_lat_body(la, smem);
+    blind_rotate_lat_body<V>(la, smem);
+}
+
+template <int V>
+static int launch_lat(lux_engine *e, const LatArgs &la, cudaStream_t s) {
+    static bool configured[64] = {};
+    if (!configured[e->device & 63]) {
+        CUDA_TRY(e, cudaFuncSetAttribute(blind_rotate_fft_lat_kernel<V>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LAT_SMEM));
+        configured[e->device & 63] = true;
+    }
+    blind_rotate_fft_lat_kernel<V><<<la.a.B, LAT_THREADS, LAT_SMEM, s>>>(la);
+    e->launches++;
+    CUDA_TRY(e, cudaGetLastError());
+    return LUX_OK;
 }
 
 constexpr int UTIL_WARPS = 4;
@@ -146,16 +160,13 @@ int lux_fft_launch_br(lux_engine *e, Args a, cudaStream_t s) {
     const int variant = e->fft_variant;   // 0 = the default of each team count; the others are the measured alternatives
     // a batch that leaves SMs idle anyway: one ciphertext per CTA, eight warps per ciphertext (fft64_lat.cuh)
     if ((e->fft_lat_mode == 1 || (e->fft_lat_mode < 0 && e->force_teams == 0 && a.B <= (u32)e->sm_count)) && a.B > 0) {
-        static bool configured[64] = {};
-        if (!configured[e->device & 63]) {
-            CUDA_TRY(e, cudaFuncSetAttribute(blind_rotate_fft_lat_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LAT_SMEM));
-            configured[e->device & 63] = true;
-        }
         LatArgs la{a, (const double2 *)e->d_fft_twFull};
-        blind_rotate_fft_lat_kernel<<<a.B, LAT_THREADS, LAT_SMEM, s>>>(la);
-        e->launches++;
-        CUDA_TRY(e, cudaGetLastError());
-        return LUX_OK;
+        switch (variant) {   // measured alternatives (scripts/quick_torus.py, cfg = 10 x variant)
+            case 1: return launch_lat<1>(e, la, s);
+            case 2: return launch_lat<2>(e, la, s);
+            case 3: return launch_lat<3>(e, la, s);
+            default: return launch_lat<0>(e, la, s);
+        }
     }
     switch (pick_teams(e, a.B)) {
         case 1:   // a warp alone on its scheduler: free instruction schedule (no phase marks)

@@ -27,7 +27,8 @@ namespace fft64 {
 
 constexpr int LAT_THREADS = 256;
 constexpr int LAT_PAD_POINTS = M;   // exchange buffer: no padding, XOR-swizzled (lat_pad)
-constexpr size_t LAT_SMEM = sizeof(u64) * 2 * N + sizeof(double2) * (size_t)(M + 6 * LAT_PAD_POINTS) + 16;
+constexpr int LAT_TWM = 128 + 256 + 512;   // levels 7, 8, 9 of the twiddle tree once more, lane-major for layout M
+constexpr size_t LAT_SMEM = sizeof(u64) * 2 * N + sizeof(double2) * (size_t)(M + LAT_TWM + 6 * LAT_PAD_POINTS) + 16;
 
 struct LatArgs {
     Args a;
@@ -56,12 +57,16 @@ __device__ __forceinline__ void lat_pass3(double2 (&x)[8], const double2 *tw, co
 
 __device__ __forceinline__ void group_sync(int id) { asm volatile("bar.sync %0, 128;" ::"r"(id) : "memory"); }
 
+// V bit 0: the thread's own 16 accumulator coefficients stay in registers (F1 and I4 cover the same points)
+// V bit 1: the key rows are requested after the second forward pass instead of at the top of the iteration
+template <int V>
 __device__ __forceinline__ void blind_rotate_lat_body(const LatArgs &la, unsigned char *smem_raw) {
     const Args &a = la.a;
     const int tid = threadIdx.x, r = tid >> 7, t = tid & 127, lane = tid & 31, w4 = t >> 5;
     u64 *acc_all = (u64 *)smem_raw;
     double2 *tw = (double2 *)(acc_all + 2 * N);
-    double2 *bufs = tw + M;                                   // [group][3][LAT_PAD_POINTS]
+    double2 *twM = tw + M;                                    // level L = 7..9: node 2^L + lane * 2^(L-5) + rest at (2^L - 128) + 32 rest + lane
+    double2 *bufs = twM + LAT_TWM;                            // [group][3][LAT_PAD_POINTS]
     double2 *b0 = bufs + (size_t)(r * 3 + 0) * LAT_PAD_POINTS, *b1 = bufs + (size_t)(r * 3 + 1) * LAT_PAD_POINTS,
             *bx = bufs + (size_t)(r * 3 + 2) * LAT_PAD_POINTS;
     const double2 *bx0 = bufs + (size_t)2 * LAT_PAD_POINTS, *bx1 = bufs + (size_t)5 * LAT_PAD_POINTS;
@@ -71,6 +76,12 @@ __device__ __forceinline__ void blind_rotate_lat_body(const LatArgs &la, unsigne
     const u64 *tv = a.testv + (size_t)(a.lut_idx ? a.lut_idx[ct / a.lut_div] : 0) * N;
 
     for (int i = tid; i < M; i += LAT_THREADS) tw[i] = la.tw_full[i];
+    // layout M reads node 2^L + lane * 2^(L-5) + rest: in tree order the 32 lanes of a load sit 2^(L-5) * 16 bytes apart (an
+    // 8-way bank conflict at level 9); the copy below puts them side by side
+    for (int i = tid; i < LAT_TWM; i += LAT_THREADS) {
+        const int L = i < 128 ? 7 : i < 384 ? 8 : 9, o = i - ((1 << L) - 128), ln = o & 31, rest = o >> 5;
+        twM[i] = la.tw_full[(1 << L) + (ln << (L - 5)) + rest];
+    }
     {   // acc0 = X^{ms(-b)} (0, testv)
         const u32 sh0 = mod_switch((u64)0 - lwe[a.n]);
         for (int p = t; p < N; p += 128) acc[p] = r ? rotated(tv, (u32)p, sh0) : 0;
@@ -79,13 +90,21 @@ __device__ __forceinline__ void blind_rotate_lat_body(const LatArgs &la, unsigne
 
     const u32 dg_half = 1u << (31 - a.logB), dg_sh = 32 - a.logB;
     u64 mask = a.steps ? lwe[0] : 0;
+    u64 own[16];   // V & 1: acc[128 reg + t] and acc[128 reg + t + M], reg = 0..7
+    if (V & 1) {
+#pragma unroll
+        for (int reg = 0; reg < 8; reg++) {
+            own[2 * reg] = acc[128 * reg + t];
+            own[2 * reg + 1] = acc[128 * reg + t + M];
+        }
+    }
 #pragma unroll 1
     for (u32 it = 0; it < a.steps; it++) {
         const u32 sh = mod_switch(mask);
         if (it + 1 < a.steps) mask = lwe[it + 1];
-        // key rows of this thread's MAC points (layout M), requested now, used after the forward transform
+        // key rows of this thread's MAC points (layout M), requested early, used after the forward transform
         double2 k0[8], k1[8];
-        {
+        auto request_keys = [&]() {
             const double2 *g = a.bsk + (size_t)it * 32 * 4 * 32;
 #pragma unroll
             for (int reg = 0; reg < 8; reg++) {
@@ -93,14 +112,15 @@ __device__ __forceinline__ void blind_rotate_lat_body(const LatArgs &la, unsigne
                 k0[reg] = __ldg(g + (row * 4 + 0 + r) * 32 + lane);
                 k1[reg] = __ldg(g + (row * 4 + 2 + r) * 32 + lane);
             }
-        }
+        };
+        if (!(V & 2)) request_keys();
         double2 x[8];
         // F1 points q = 128 reg + t: digits of X^sh acc - acc at coefficients q and q + M
 #pragma unroll
         for (int reg = 0; reg < 8; reg++) {
             const u32 q = 128u * reg + (u32)t;
-            const u64 d0 = rotated(acc, q, sh) - acc[q];
-            const u64 d1 = rotated(acc, q + M, sh) - acc[q + M];
+            const u64 d0 = rotated(acc, q, sh) - ((V & 1) ? own[2 * reg] : acc[q]);
+            const u64 d1 = rotated(acc, q + M, sh) - ((V & 1) ? own[2 * reg + 1] : acc[q + M]);
             x[reg] = make_double2(digit1_double((u32)(d0 >> 32), dg_half, dg_sh), digit1_double((u32)(d1 >> 32), dg_half, dg_sh));
         }
         {   // levels 0,1,2: register bits 2,1,0 <-> index bits 9,8,7; node = 2^j + (reg >> (3 - j))
@@ -120,6 +140,7 @@ __device__ __forceinline__ void blind_rotate_lat_body(const LatArgs &la, unsigne
             for (int reg = 0; reg < 8; reg++) b1[lat_pad(128 * hi + 16 * reg + lo)] = x[reg];
         }
         group_sync(1 + r);
+        if (V & 2) request_keys();
         {   // F3: q = 16 hi + 2 reg + lo
             const int hi = t >> 1, lo = t & 1;
 #pragma unroll
@@ -140,7 +161,7 @@ __device__ __forceinline__ void blind_rotate_lat_body(const LatArgs &la, unsigne
             }
 #pragma unroll
             for (int reg = 0; reg < 8; reg += 2) {
-                const double2 wv = tw[512 + ((qb + reg) >> 1)];
+                const double2 wv = twM[384 + 32 * (4 * w4 + (reg >> 1)) + lane];
                 ct_bfly(x0[reg], x0[reg + 1], wv.x, wv.y);
                 ct_bfly(x1[reg], x1[reg + 1], wv.x, wv.y);
             }
@@ -156,7 +177,8 @@ __device__ __forceinline__ void blind_rotate_lat_body(const LatArgs &la, unsigne
                 x[reg] = make_double2(re, im);
             }
             const int bit[3] = {0, 1, 2};   // levels 9, 8, 7 <-> register bits 0, 1, 2
-            lat_pass3<true>(x, tw, bit, [qb](int j, int reg) { return (512 >> j) + ((qb + reg) >> (1 + j)); });
+            // node (512 >> j) + ((qb + reg) >> (1 + j)) of the tree, from the lane-major copy
+            lat_pass3<true>(x, twM, bit, [w4, lane](int j, int reg) { return ((512 >> j) - 128) + 32 * (((8 * w4 + reg) >> (1 + j))) + lane; });
 #pragma unroll
             for (int reg = 0; reg < 8; reg++) b0[lat_pad(qb + reg)] = x[reg];
         }
@@ -190,8 +212,16 @@ __device__ __forceinline__ void blind_rotate_lat_body(const LatArgs &la, unsigne
 #pragma unroll
             for (int reg = 0; reg < 8; reg++) {
                 const u32 q = 512u * (reg & 1) + 128u * (reg >> 1) + (u32)t;
-                acc[q] += from_double(x[reg].x);
-                acc[q + M] += from_double(x[reg].y);
+                if (V & 1) {   // point q is F1's register 4 (reg & 1) + (reg >> 1)
+                    const int f = 4 * (reg & 1) + (reg >> 1);
+                    own[2 * f] += from_double(x[reg].x);
+                    own[2 * f + 1] += from_double(x[reg].y);
+                    acc[q] = own[2 * f];
+                    acc[q + M] = own[2 * f + 1];
+                } else {
+                    acc[q] += from_double(x[reg].x);
+                    acc[q + M] += from_double(x[reg].y);
+                }
             }
         }
         group_sync(1 + r);   // the next decomposition gathers rotated coefficients written by other threads of the group
