@@ -31,6 +31,13 @@ if os.environ.get("LAT"):   # small-batch latency: B in LAT (comma list), cfg fr
                 a.record(s); eng.pbs_batch_device(d_in[:b], d_tv, d_idx[:b], b, d_out[:b], n_luts=4, stream=s.cuda_stream); e2.record(s); e2.synchronize()
                 ms.append(a.elapsed_time(e2))
             print(f"latency B={b} cfg={spec}: {min(ms[1:]):.3f} ms", flush=True)
+            if os.environ.get("FFT64_TRACE") and t // 10 == 4:   # the latency kernel's phase marks (variant 4)
+                eng.fft_trace()
+                eng.pbs_batch_device(d_in[:b], d_tv, d_idx[:b], b, d_out[:b], n_luts=4, stream=s.cuda_stream)
+                tr = eng.fft_trace()
+                names = ["decompose", "F1", "bar", "F2", "bar", "F3", "sync", "M", "sync", "I2", "bar", "I3", "bar", "I4+update", "bar"]
+                per = [v / (8 * b * p.n) for v in tr[:15]]
+                print("   cycles per warp-iteration: " + ", ".join(f"{n} {v:.0f}" for n, v in zip(names, per)) + f"  | total {sum(per):.0f}", flush=True)
     sys.exit(0)
 for spec in teams_list:
     t = int(spec.split(":")[0])

@@ -165,6 +165,7 @@ int lux_fft_launch_br(lux_engine *e, Args a, cudaStream_t s) {
             case 1: return launch_lat<1>(e, la, s);
             case 2: return launch_lat<2>(e, la, s);
             case 3: return launch_lat<3>(e, la, s);
+            case 4: return launch_lat<4>(e, la, s);   // phase marks (lux_debug_fft_trace)
             default: return launch_lat<0>(e, la, s);
         }
     }

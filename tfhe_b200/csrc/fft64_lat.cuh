@@ -59,6 +59,15 @@ __device__ __forceinline__ void group_sync(int id) { asm volatile("bar.sync %0, 
 
 // V bit 0: the thread's own 16 accumulator coefficients stay in registers (F1 and I4 cover the same points)
 // V bit 1: the key rows are requested after the second forward pass instead of at the top of the iteration
+// V bit 2: phase marks — lane 0 of every warp adds the cycles since its previous mark to a.trace[phase] (lux_debug_fft_trace)
+#define LAT_MARK(k)                                                                              \
+    do {                                                                                         \
+        if ((V & 4) && a.trace && lane == 0) {                                                   \
+            const long long now_ = clock64();                                                    \
+            atomicAdd((unsigned long long *)a.trace + (k), (unsigned long long)(now_ - mark_));  \
+            mark_ = now_;                                                                        \
+        }                                                                                        \
+    } while (0)
 template <int V>
 __device__ __forceinline__ void blind_rotate_lat_body(const LatArgs &la, unsigned char *smem_raw) {
     const Args &a = la.a;
@@ -98,6 +107,7 @@ __device__ __forceinline__ void blind_rotate_lat_body(const LatArgs &la, unsigne
             own[2 * reg + 1] = acc[128 * reg + t + M];
         }
     }
+    long long mark_ = (V & 4) ? clock64() : 0;
 #pragma unroll 1
     for (u32 it = 0; it < a.steps; it++) {
         const u32 sh = mod_switch(mask);
@@ -123,13 +133,16 @@ __device__ __forceinline__ void blind_rotate_lat_body(const LatArgs &la, unsigne
             const u64 d1 = rotated(acc, q + M, sh) - ((V & 1) ? own[2 * reg + 1] : acc[q + M]);
             x[reg] = make_double2(digit1_double((u32)(d0 >> 32), dg_half, dg_sh), digit1_double((u32)(d1 >> 32), dg_half, dg_sh));
         }
+        LAT_MARK(0);
         {   // levels 0,1,2: register bits 2,1,0 <-> index bits 9,8,7; node = 2^j + (reg >> (3 - j))
             const int bit[3] = {2, 1, 0};
             lat_pass3<false>(x, tw, bit, [](int j, int reg) { return (1 << j) + (reg >> (3 - j)); });
         }
 #pragma unroll
         for (int reg = 0; reg < 8; reg++) b0[lat_pad(128 * reg + t)] = x[reg];
+        LAT_MARK(1);
         group_sync(1 + r);
+        LAT_MARK(2);
         {   // F2: q = 128 hi + 16 reg + lo
             const int hi = t >> 4, lo = t & 15;
 #pragma unroll
@@ -139,7 +152,9 @@ __device__ __forceinline__ void blind_rotate_lat_body(const LatArgs &la, unsigne
 #pragma unroll
             for (int reg = 0; reg < 8; reg++) b1[lat_pad(128 * hi + 16 * reg + lo)] = x[reg];
         }
+        LAT_MARK(3);
         group_sync(1 + r);
+        LAT_MARK(4);
         if (V & 2) request_keys();
         {   // F3: q = 16 hi + 2 reg + lo
             const int hi = t >> 1, lo = t & 1;
@@ -150,7 +165,9 @@ __device__ __forceinline__ void blind_rotate_lat_body(const LatArgs &la, unsigne
 #pragma unroll
             for (int reg = 0; reg < 8; reg++) bx[lat_pad(16 * hi + 2 * reg + lo)] = x[reg];
         }
+        LAT_MARK(5);
         __syncthreads();   // both spectra (before their last level) are published
+        LAT_MARK(6);
         {   // layout M: q = 32 lane + 8 w4 + reg; level 9 on X0 and X1, MAC with key column r, inverse levels 9, 8, 7
             double2 x0[8], x1[8];
             const int qb = 32 * lane + 8 * w4;
@@ -182,7 +199,9 @@ __device__ __forceinline__ void blind_rotate_lat_body(const LatArgs &la, unsigne
 #pragma unroll
             for (int reg = 0; reg < 8; reg++) b0[lat_pad(qb + reg)] = x[reg];
         }
+        LAT_MARK(7);
         __syncthreads();   // also: every read of the published spectra is done before bx is written again
+        LAT_MARK(8);
         {   // I2: q = 64 hi + 8 reg + lo, levels 6, 5, 4 <-> register bits 0, 1, 2
             const int hi = t >> 3, lo = t & 7;
 #pragma unroll
@@ -192,7 +211,9 @@ __device__ __forceinline__ void blind_rotate_lat_body(const LatArgs &la, unsigne
 #pragma unroll
             for (int reg = 0; reg < 8; reg++) b1[lat_pad(64 * hi + 8 * reg + lo)] = x[reg];
         }
+        LAT_MARK(9);
         group_sync(1 + r);
+        LAT_MARK(10);
         {   // I3: q = 512 hi + 64 reg + lo, levels 3, 2, 1 <-> register bits 0, 1, 2
             const int hi = t >> 6, lo = t & 63;
 #pragma unroll
@@ -202,7 +223,9 @@ __device__ __forceinline__ void blind_rotate_lat_body(const LatArgs &la, unsigne
 #pragma unroll
             for (int reg = 0; reg < 8; reg++) b0[lat_pad(512 * hi + 64 * reg + lo)] = x[reg];
         }
+        LAT_MARK(11);
         group_sync(1 + r);
+        LAT_MARK(12);
         {   // I4: q = 512 (reg & 1) + 128 (reg >> 1) + t, level 0 <-> register bit 0, then acc += torus(x)
 #pragma unroll
             for (int reg = 0; reg < 8; reg++) x[reg] = b0[lat_pad(512 * (reg & 1) + 128 * (reg >> 1) + t)];
@@ -224,7 +247,9 @@ __device__ __forceinline__ void blind_rotate_lat_body(const LatArgs &la, unsigne
                 }
             }
         }
+        LAT_MARK(13);
         group_sync(1 + r);   // the next decomposition gathers rotated coefficients written by other threads of the group
+        LAT_MARK(14);
     }
 
     if (a.out_mode == 2) {
