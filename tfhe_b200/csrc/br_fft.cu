@@ -8,7 +8,7 @@
 
 using namespace fft64;
 
-template <int TEAMS, int NS, int RS, int TWS, int HB = 0, int GROUPS = 1, int KL = 0, int MK = 1>
+template <int TEAMS, int NS, int RS, int TWS, int HB = 0, int GROUPS = 1, int KL = 0, int MK = 1, int LAG = 0>
 __global__ void __launch_bounds__(Cfg<TEAMS, NS, RS, TWS, HB, GROUPS, KL>::THREADS, 1) blind_rotate_fft_kernel(const __grid_constant__ Args a) {
     extern __shared__ __align__(16) unsigned char smem[];
     if (KL == 3) {   // tensor memory as the key cache: all 512 columns, taken and returned by warp 0 of EVERY CTA
@@ -24,7 +24,7 @@ __global__ void __launch_bounds__(Cfg<TEAMS, NS, RS, TWS, HB, GROUPS, KL>::THREA
         if (threadIdx.x < 32) tmem_free_512(tbase);
         return;
     }
-    blind_rotate_body<TEAMS, NS, RS, TWS, HB, GROUPS, KL, MK>(a, smem);
+    blind_rotate_body<TEAMS, NS, RS, TWS, HB, GROUPS, KL, MK, LAG>(a, smem);
 }
 
 template <int V>
@@ -122,17 +122,17 @@ static void fill_tables(const lux_engine *e, Args &a) {
     for (int v = 0; v < 32; v++) a.twA[v] = make_double2(e->fft_twA[2 * v], e->fft_twA[2 * v + 1]);
 }
 
-template <int TEAMS, int NS, int RS, int TWS, int HB = 0, int GROUPS = 1, int KL = 0, int MK = 1>
+template <int TEAMS, int NS, int RS, int TWS, int HB = 0, int GROUPS = 1, int KL = 0, int MK = 1, int LAG = 0>
 static int launch_cfg(lux_engine *e, const Args &a, cudaStream_t s) {
     using C = Cfg<TEAMS, NS, RS, TWS, HB, GROUPS, KL>;
     static_assert(C::SMEM <= 232448, "configuration exceeds the 227 KiB of shared memory a CTA can opt into");
     static bool configured[64] = {};
     if (!configured[e->device & 63]) {
-        CUDA_TRY(e, cudaFuncSetAttribute(blind_rotate_fft_kernel<TEAMS, NS, RS, TWS, HB, GROUPS, KL, MK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM));
+        CUDA_TRY(e, cudaFuncSetAttribute(blind_rotate_fft_kernel<TEAMS, NS, RS, TWS, HB, GROUPS, KL, MK, LAG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM));
         configured[e->device & 63] = true;
     }
     const unsigned grid = (a.B + TEAMS - 1) / TEAMS;
-    blind_rotate_fft_kernel<TEAMS, NS, RS, TWS, HB, GROUPS, KL, MK><<<grid, C::THREADS, C::SMEM, s>>>(a);
+    blind_rotate_fft_kernel<TEAMS, NS, RS, TWS, HB, GROUPS, KL, MK, LAG><<<grid, C::THREADS, C::SMEM, s>>>(a);
     e->launches++;
     CUDA_TRY(e, cudaGetLastError());
     return LUX_OK;
@@ -187,6 +187,15 @@ int lux_fft_launch_br(lux_engine *e, Args a, cudaStream_t s) {
             if (variant == 5) {   // key rows through tensor memory (four producer warps); refill paced at 400 ns per two rows unless set
                 if (e->fft_stagger_ns == 6000) a.stagger_ns = 400;
                 return launch_cfg<4, 1, 4, 1, 1, 1, 3>(e, a, s);
+            }
+            // LAG experiments (fft64.cuh): the upper two teams run behind the lower two; stagger = delay in cycles (6, 7) or
+            // 10 x leader point + trailer point of the two coupling barriers (8)
+            if (variant == 6) return launch_cfg<4, 4, 4, 0, 1, 1, 0, 1, 1>(e, a, s);   // ring + start delay
+            if (variant == 7) return launch_cfg<4, 1, 4, 1, 1, 1, 1, 1, 1>(e, a, s);   // no ring + start delay
+            if (variant == 8) {   // no ring + coupled offset; a point code that names no mark would leave the barriers unmatched
+                auto ok = [](u32 k) { return k == 0 || k == 1 || k == 3 || (k >= 6 && k <= 9); };
+                if (!ok(a.stagger_ns / 10) || !ok(a.stagger_ns % 10) || a.stagger_ns >= 100) a.stagger_ns = 16;
+                return launch_cfg<4, 1, 4, 1, 1, 1, 1, 1, 2>(e, a, s);
             }
             return launch_cfg<4, 4, 4, 0, 1>(e, a, s);                        // ring 4 x 8 KiB, twiddles through L1
     }

@@ -605,7 +605,12 @@ __device__ __forceinline__ void mac_all(double2 (&y)[32], const double2 *oth, co
     }
 }
 
-template <int TEAMS, int NS, int RS, int TWS, int HB = 0, int GROUPS = 1, int KL = 0, int MK = 1>
+// LAG (experiments, profiles/r02d_lag.txt): the teams of the upper half of a full CTA (the second warp of every scheduler)
+// run BEHIND the lower half instead of in lock step with it, so that a scheduler's two warps are in different phases (one in
+// an FP64 phase, the other in a shared-memory or integer phase).  LAG = 1: a start delay of a.stagger_ns cycles only;
+// LAG = 2: the offset is also held by two named barriers (13: a trailer starts iteration i after the leaders passed point
+// a.stagger_ns / 10 of iteration i; 14: a leader starts iteration i + 1 after the trailers passed point a.stagger_ns % 10 of i).
+template <int TEAMS, int NS, int RS, int TWS, int HB = 0, int GROUPS = 1, int KL = 0, int MK = 1, int LAG = 0>
 __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *smem_raw, u32 tmem_base = 0) {
     using C = Cfg<TEAMS, NS, RS, TWS, HB, GROUPS, KL>;
     static_assert(TEAMS % GROUPS == 0, "teams must split evenly into groups");
@@ -729,6 +734,22 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
     const int barrier_id = 1 + team;
     const u32 tq = tmem_base + ((32u * ((u32)warp & 3u)) << 16);   // KL == 3: this warp's lane quadrant of tensor memory
     if (GROUPS > 1 && grp) __nanosleep(a.stagger_ns * grp);   // start the groups out of phase
+    const bool lag_on = LAG && live_teams == (u32)TEAMS && TEAMS >= 2;
+    const bool trailer = lag_on && team >= TEAMS / 2, leader = lag_on && team < TEAMS / 2;
+    const u32 lag_x = a.stagger_ns / 10, lag_y = a.stagger_ns % 10;
+    constexpr u32 LAG_THREADS = 64u * TEAMS;
+    if (LAG == 1 && trailer) {
+        const long long c0 = clock64();
+        while (clock64() - c0 < (long long)a.stagger_ns) {
+        }
+    }
+#define FFT64_LAG_POINT(k)                                                                                                   \
+    do {                                                                                                                     \
+        if (LAG == 2) {                                                                                                      \
+            if (leader && lag_x == (k)) asm volatile("bar.arrive 13, %0;" ::"r"(LAG_THREADS) : "memory");                    \
+            if (trailer && lag_y == (k) && it + 1 < a.steps) asm volatile("bar.arrive 14, %0;" ::"r"(LAG_THREADS) : "memory"); \
+        }                                                                                                                    \
+    } while (0)
     long long mark_ = a.trace ? clock64() : 0;
     const u32 dg_half = 1u << (31 - a.logB), dg_sh = 32 - a.logB;
     const unsigned char *accb = (const unsigned char *)acc;
@@ -742,6 +763,10 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
         // KL == 2: no ring, but the live consumer warps of the CTA meet once per iteration: they then ask for the same key
         // rows at about the same time (one L2 request, L1 hits for the rest) and keep sharing instruction fetches
         if (KL == 2 || KL == 3) asm volatile("bar.sync 15, %0;" ::"r"(64u * live_teams) : "memory");
+        if (LAG == 2) {
+            if (trailer) asm volatile("bar.sync 13, %0;" ::"r"(LAG_THREADS) : "memory");
+            if (leader && it) asm volatile("bar.sync 14, %0;" ::"r"(LAG_THREADS) : "memory");
+        }
         const u32 sh = mod_switch(mask);
         if (it + 1 < a.steps) mask = lwe[it + 1];
         double2 x[32];
@@ -767,8 +792,10 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
             }
         }
         FFT64_MARK(0);
+        FFT64_LAG_POINT(0);
         pass_a<false, MK>(x, a, lane, mark_);
         FFT64_MARK(1);
+        FFT64_LAG_POINT(1);
         if (HB)
             col_to_row_h(x, (double *)buf, lane);
         else
@@ -776,6 +803,7 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
         FFT64_MARK(2);
         pass_b<false, MK>(x, twB, lane, a, mark_);
         FFT64_MARK(3);
+        FFT64_LAG_POINT(3);
         if (KL == 3) {   // this iteration's key rows sit in buffer it & 1 of the quadrant (stored during the previous iteration)
             mbar_wait(tfull + 2 * ((u32)warp & 3u) + (it & 1u), (it >> 1) & 1u);
             tmem_fence_after();
@@ -809,6 +837,7 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
             FFT64_MARK(5);
             asm volatile("bar.sync %0, 64;" ::"r"(barrier_id) : "memory");
             FFT64_MARK(6);
+            FFT64_LAG_POINT(6);
             pass_b_inv_half<1, MK>(x, twB, lane, a, mark_);
         } else {   // two rounds of 16 rows through the half-size buffers, layout [row][lane]
             constexpr int CH = 16 / RS;
@@ -843,6 +872,7 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
             FFT64_MARK(5);
             asm volatile("bar.sync %0, 64;" ::"r"(barrier_id) : "memory");
             FFT64_MARK(6);
+            FFT64_LAG_POINT(6);
             pass_b_inv_half<1, MK>(x, twB, lane, a, mark_);
         }
         if (KL == 3) {   // the buffer may be refilled (with the rows of iteration it + 2)
@@ -852,13 +882,16 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
         }
         pass_b_stage<true, 0, 0, 16, MK>(x, twB, lane);
         FFT64_MARK(7);
+        FFT64_LAG_POINT(7);
         if (HB)
             row_to_col_h(x, (double *)buf, lane);
         else
             row_to_col(x, buf, lane);
         FFT64_MARK(8);
+        FFT64_LAG_POINT(8);
         pass_a<true, MK>(x, a, lane, mark_);
         FFT64_MARK(9);
+        FFT64_LAG_POINT(9);
 #pragma unroll
         for (int i0 = 0; i0 < 32; i0 += 4) {   // four points = eight independent conversion chains at a time
             double t[8], f[8];
