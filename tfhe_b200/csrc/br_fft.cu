@@ -197,6 +197,7 @@ int lux_fft_launch_br(lux_engine *e, Args a, cudaStream_t s) {
                 if (!ok(a.stagger_ns / 10) || !ok(a.stagger_ns % 10) || a.stagger_ns >= 100) a.stagger_ns = 16;
                 return launch_cfg<4, 1, 4, 1, 1, 1, 1, 1, 2>(e, a, s);
             }
+            if (variant == 9) return launch_cfg<4, 4, 4, 0, 1, 1, 4>(e, a, s);   // ring fed by consumer warp 0: eight warps, up to 255 registers
             return launch_cfg<4, 4, 4, 0, 1>(e, a, s);                        // ring 4 x 8 KiB, twiddles through L1
     }
 }

@@ -386,6 +386,8 @@ __device__ __forceinline__ void fft_inverse(double2 (&y)[32], double2 *buf, cons
 // KL: no key ring at all: every warp loads its key rows straight from L2 / L1 (ld.global.nc) into registers.  Nothing then
 // couples the teams of a CTA (no shared ring, no producer warp, no mbarriers): they drift out of phase and the integer,
 // FP64 and shared-memory phases of different teams overlap.  Costs TEAMS x the L2 -> SM key traffic of the ring.
+// KL == 4: the ring WITHOUT a producer warp: lane 0 of consumer warp 0 issues the bulk copies (RingFeed below).  A ninth warp
+// puts three warps on one scheduler, and a scheduler's 16 K registers then allow 168 per thread; eight warps may use 255.
 template <int TEAMS, int NS, int RS, int TWS = 1, int HB = 0, int GROUPS = 1, int KL = 0>
 struct Cfg {
     static constexpr int CONSUMER_WARPS = 2 * TEAMS;
@@ -396,7 +398,7 @@ struct Cfg {
     static constexpr int WARP_BUF_POINTS = HB ? HBUF_BYTES / 16 : BUF_POINTS;   // in double2 units
     static constexpr size_t SMEM =
         sizeof(double2) * TWB_ENTRIES * TWS + (size_t)TEAMS * (sizeof(u64) * 2 * N + sizeof(double2) * 2 * WARP_BUF_POINTS) +
-        (KL == 3 ? sizeof(u64) * 16 : KL ? 0 : sizeof(double2) * (size_t)GROUPS * NS * STAGE_POINTS + sizeof(u64) * 2 * NS * GROUPS) + 16;
+        (KL == 3 ? sizeof(u64) * 16 : (KL && KL != 4) ? 0 : sizeof(double2) * (size_t)GROUPS * NS * STAGE_POINTS + sizeof(u64) * 2 * NS * GROUPS + (KL == 4 ? sizeof(u32) * NS : 0)) + 16;
 };
 
 // ------------------------------------------------------------------------------------------ tensor memory as the key cache
@@ -558,6 +560,44 @@ __device__ __forceinline__ void mac_rows2(double2 (&y)[32], const KeyRows2 &d, i
 #pragma unroll
     for (int ii = 0; ii < 2; ii++) y[row + ii] = make_double2(re[ii], im[ii]);
 }
+
+// KL == 4: the key ring fed by its consumers.  Piece f of the key goes into stage f % NS once every consumer warp has
+// released piece f - NS, and the warp whose arrival completes that phase of the stage's `empty` barrier is the one that
+// requests it: after its own arrival a warp tests the phase (it can only be the phase it arrived in, or complete) and, if
+// complete, claims the refill with a compare-and-swap on claim[stage] (= the piece the stage holds or has been promised), so
+// exactly one lane issues the bulk copy, at the moment the stage becomes free — no producer warp, no polling.
+struct RingFeed {
+    const double2 *bsk;
+    double2 *ring;
+    u32 *claim;
+    u32 total;
+};
+__device__ __forceinline__ bool mbar_test(u64 *bar, u32 parity) {
+    u32 ok;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t"
+        "}"
+        : "=r"(ok)
+        : "r"(tk_smem_addr(bar)), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+template <int NS, int SP>
+__device__ __forceinline__ void feed_issue(const RingFeed &fd, u32 f, u64 *full) {
+    constexpr u32 bytes = (u32)(sizeof(double2) * SP);
+    const u32 s = f % NS;
+    mbar_expect_tx(full + s, bytes);
+    bulk_g2s(fd.ring + (size_t)s * SP, fd.bsk + (size_t)f * SP, bytes, full + s);
+}
+// lane 0 of a consumer warp, right after its arrival on empty[t % NS] for piece t
+template <int NS, int SP>
+__device__ __forceinline__ void feed_after_release(const RingFeed &fd, u32 t, u64 *full, u64 *empty) {
+    const u32 s = t % NS, f = t + NS;
+    if (f < fd.total && mbar_test(empty + s, (t / NS) & 1) && atomicCAS(fd.claim + s, t, f) == t) feed_issue<NS, SP>(fd, f, full);
+}
 // chunks [C0, C1) of the 32 / RS key-row chunks of one GGSW.
 // -DFFT64_MAC_PIPE=1 (RS == 4): software-pipelined — the loads of the next two rows (key rows and partner rows, the next
 // stage's full barrier first where they are its rows) are issued before the multiply-adds of the current two, so the
@@ -568,7 +608,8 @@ __device__ __forceinline__ void mac_rows2(double2 (&y)[32], const KeyRows2 &d, i
 #define FFT64_MAC_PIPE 0
 #endif
 template <int R, int NS, int RS, int HB = 0, int C0 = 0, int C1 = 32 / RS>
-__device__ __forceinline__ void mac_all(double2 (&y)[32], const double2 *oth, const double2 *ring, u64 *full, u64 *empty, u32 &t, int lane) {
+__device__ __forceinline__ void mac_all(double2 (&y)[32], const double2 *oth, const double2 *ring, u64 *full, u64 *empty, u32 &t, int lane,
+                                        const RingFeed *fd = nullptr) {
     constexpr int SP = RS * 4 * 32;
     if (FFT64_MAC_PIPE && RS == 4) {
         KeyRows2 A, B;
@@ -589,7 +630,10 @@ __device__ __forceinline__ void mac_all(double2 (&y)[32], const double2 *oth, co
             }
             mac_rows2<R>(y, B, c * RS + 2);
             __syncwarp();
-            if (lane == 0) mbar_arrive(empty + s_cur);
+            if (lane == 0) {
+                mbar_arrive(empty + s_cur);
+                if (fd) feed_after_release<NS, SP>(*fd, t, full, empty);
+            }
             t++;
         }
         return;
@@ -600,7 +644,10 @@ __device__ __forceinline__ void mac_all(double2 (&y)[32], const double2 *oth, co
         mbar_wait(full + s, (t / NS) & 1);
         mac_rows<R, RS, HB>(y, oth, ring + (size_t)s * SP, c * RS, lane);
         __syncwarp();
-        if (lane == 0) mbar_arrive(empty + s);
+        if (lane == 0) {
+            mbar_arrive(empty + s);
+            if (fd) feed_after_release<NS, SP>(*fd, t, full, empty);
+        }
         t++;
     }
 }
@@ -650,7 +697,7 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
             }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (!KL && tid == 0) {
+    if ((!KL || KL == 4) && tid == 0) {
         for (int g = 0; g < GROUPS; g++)
             for (int s = 0; s < NS; s++) {
                 mbar_init(full_all + g * NS + s, 1);
@@ -658,8 +705,15 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
             }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    __syncthreads();
     const u32 total = a.steps * C::STAGES_PER_GGSW;
+    if (KL == 4 && tid == 0) {   // the first NS pieces; claim[s] = the piece stage s holds
+        const RingFeed f0{a.bsk, ring_all, (u32 *)(empty_all + GROUPS * NS), total};
+        for (u32 f = 0; f < (u32)NS && f < total; f++) {
+            f0.claim[f] = f;
+            feed_issue<NS, C::STAGE_POINTS>(f0, f, full_all);
+        }
+    }
+    __syncthreads();
 
     if (KL == 3 && warp >= C::CONSUMER_WARPS) {   // ---- tensor-memory producers: warp CONSUMER_WARPS + q feeds quadrant q
         const u32 q = warp - C::CONSUMER_WARPS, pr = q & 1;
@@ -730,6 +784,8 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
     __syncwarp();
 
     u32 t = 0;
+    const RingFeed feed{a.bsk, ring_all, (u32 *)(empty_all + GROUPS * NS), total};
+    const RingFeed *fdp = KL == 4 ? &feed : nullptr;
     u64 mask = a.steps ? lwe[0] : 0;
     const int barrier_id = 1 + team;
     const u32 tq = tmem_base + ((32u * ((u32)warp & 3u)) << 16);   // KL == 3: this warp's lane quadrant of tensor memory
@@ -819,21 +875,21 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
             constexpr int CH = 16 / RS;
             if (r == 0)
                 (KL == 3 ? mac_tmem<0, 0, (0) * RS / 2, (CH) * RS / 2>(x, buf_oth, tq + 256u * (it & 1u), lane)
-                 : KL ? mac_global<0, RS, 0, 0, CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
-                    : mac_all<0, NS, RS, 0, 0, CH>(x, buf_oth, ring, full, empty, t, lane));
+                 : (KL && KL != 4) ? mac_global<0, RS, 0, 0, CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
+                    : mac_all<0, NS, RS, 0, 0, CH>(x, buf_oth, ring, full, empty, t, lane, fdp));
             else
                 (KL == 3 ? mac_tmem<1, 0, (0) * RS / 2, (CH) * RS / 2>(x, buf_oth, tq + 256u * (it & 1u), lane)
-                 : KL ? mac_global<1, RS, 0, 0, CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
-                    : mac_all<1, NS, RS, 0, 0, CH>(x, buf_oth, ring, full, empty, t, lane));
+                 : (KL && KL != 4) ? mac_global<1, RS, 0, 0, CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
+                    : mac_all<1, NS, RS, 0, 0, CH>(x, buf_oth, ring, full, empty, t, lane, fdp));
             pass_b_inv_half<0, MK>(x, twB, lane, a, mark_);
             if (r == 0)
                 (KL == 3 ? mac_tmem<0, 0, (CH) * RS / 2, (2 * CH) * RS / 2>(x, buf_oth, tq + 256u * (it & 1u), lane)
-                 : KL ? mac_global<0, RS, 0, CH, 2 * CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
-                    : mac_all<0, NS, RS, 0, CH, 2 * CH>(x, buf_oth, ring, full, empty, t, lane));
+                 : (KL && KL != 4) ? mac_global<0, RS, 0, CH, 2 * CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
+                    : mac_all<0, NS, RS, 0, CH, 2 * CH>(x, buf_oth, ring, full, empty, t, lane, fdp));
             else
                 (KL == 3 ? mac_tmem<1, 0, (CH) * RS / 2, (2 * CH) * RS / 2>(x, buf_oth, tq + 256u * (it & 1u), lane)
-                 : KL ? mac_global<1, RS, 0, CH, 2 * CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
-                    : mac_all<1, NS, RS, 0, CH, 2 * CH>(x, buf_oth, ring, full, empty, t, lane));
+                 : (KL && KL != 4) ? mac_global<1, RS, 0, CH, 2 * CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
+                    : mac_all<1, NS, RS, 0, CH, 2 * CH>(x, buf_oth, ring, full, empty, t, lane, fdp));
             FFT64_MARK(5);
             asm volatile("bar.sync %0, 64;" ::"r"(barrier_id) : "memory");
             FFT64_MARK(6);
@@ -848,12 +904,12 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
             FFT64_MARK(4);
             if (r == 0)
                 (KL == 3 ? mac_tmem<0, 1, (0) * RS / 2, (CH) * RS / 2>(x, buf_oth, tq + 256u * (it & 1u), lane)
-                 : KL ? mac_global<0, RS, 1, 0, CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
-                    : mac_all<0, NS, RS, 1, 0, CH>(x, buf_oth, ring, full, empty, t, lane));
+                 : (KL && KL != 4) ? mac_global<0, RS, 1, 0, CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
+                    : mac_all<0, NS, RS, 1, 0, CH>(x, buf_oth, ring, full, empty, t, lane, fdp));
             else
                 (KL == 3 ? mac_tmem<1, 1, (0) * RS / 2, (CH) * RS / 2>(x, buf_oth, tq + 256u * (it & 1u), lane)
-                 : KL ? mac_global<1, RS, 1, 0, CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
-                    : mac_all<1, NS, RS, 1, 0, CH>(x, buf_oth, ring, full, empty, t, lane));
+                 : (KL && KL != 4) ? mac_global<1, RS, 1, 0, CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
+                    : mac_all<1, NS, RS, 1, 0, CH>(x, buf_oth, ring, full, empty, t, lane, fdp));
             FFT64_MARK(5);
             asm volatile("bar.sync %0, 64;" ::"r"(barrier_id) : "memory");
 #pragma unroll
@@ -863,12 +919,12 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
             pass_b_inv_half<0, MK>(x, twB, lane, a, mark_);   // rows 0..15 are final: their inverse butterflies cover the wait for the key rows
             if (r == 0)
                 (KL == 3 ? mac_tmem<0, 1, (CH) * RS / 2, (2 * CH) * RS / 2>(x, buf_oth, tq + 256u * (it & 1u), lane)
-                 : KL ? mac_global<0, RS, 1, CH, 2 * CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
-                    : mac_all<0, NS, RS, 1, CH, 2 * CH>(x, buf_oth, ring, full, empty, t, lane));
+                 : (KL && KL != 4) ? mac_global<0, RS, 1, CH, 2 * CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
+                    : mac_all<0, NS, RS, 1, CH, 2 * CH>(x, buf_oth, ring, full, empty, t, lane, fdp));
             else
                 (KL == 3 ? mac_tmem<1, 1, (CH) * RS / 2, (2 * CH) * RS / 2>(x, buf_oth, tq + 256u * (it & 1u), lane)
-                 : KL ? mac_global<1, RS, 1, CH, 2 * CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
-                    : mac_all<1, NS, RS, 1, CH, 2 * CH>(x, buf_oth, ring, full, empty, t, lane));
+                 : (KL && KL != 4) ? mac_global<1, RS, 1, CH, 2 * CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
+                    : mac_all<1, NS, RS, 1, CH, 2 * CH>(x, buf_oth, ring, full, empty, t, lane, fdp));
             FFT64_MARK(5);
             asm volatile("bar.sync %0, 64;" ::"r"(barrier_id) : "memory");
             FFT64_MARK(6);
