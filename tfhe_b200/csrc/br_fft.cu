@@ -11,7 +11,7 @@ using namespace fft64;
 template <int TEAMS, int NS, int RS, int TWS, int HB = 0, int GROUPS = 1, int KL = 0, int MK = 1, int LAG = 0>
 __global__ void __launch_bounds__(Cfg<TEAMS, NS, RS, TWS, HB, GROUPS, KL>::THREADS, 1) blind_rotate_fft_kernel(const __grid_constant__ Args a) {
     extern __shared__ __align__(16) unsigned char smem[];
-    if (KL == 3) {   // tensor memory as the key cache: all 512 columns, taken and returned by warp 0 of EVERY CTA
+    if (KL == 3 || KL == 5) {   // tensor memory as the key cache: all 512 columns, taken and returned by warp 0 of EVERY CTA
         __shared__ u32 tmem_slot;
         if (threadIdx.x < 32) tmem_alloc_512(&tmem_slot);
         tmem_fence_before();
@@ -197,6 +197,11 @@ int lux_fft_launch_br(lux_engine *e, Args a, cudaStream_t s) {
                 if (!ok(a.stagger_ns / 10) || !ok(a.stagger_ns % 10) || a.stagger_ns >= 100) a.stagger_ns = 16;
                 return launch_cfg<4, 1, 4, 1, 1, 1, 1, 1, 2>(e, a, s);
             }
+            // key through tensor memory, filled by TMA + tcgen05.cp (no thread touches the key before its tcgen05.ld)
+            if (variant >= 10 && variant <= 12 && e->fft_stagger_ns == 6000) a.stagger_ns = 0;   // pacing in ns per 8 KiB piece (fft_stagger)
+            if (variant == 10) return launch_cfg<4, 2, 4, 1, 1, 1, 5>(e, a, s);   // staging 2 x 8 KiB, twiddles in shared memory
+            if (variant == 11) return launch_cfg<4, 4, 4, 0, 1, 1, 5>(e, a, s);   // staging 4 x 8 KiB, twiddles through L1
+            if (variant == 12) return launch_cfg<4, 3, 4, 1, 1, 1, 5>(e, a, s);   // staging 3 x 8 KiB, twiddles in shared memory
             if (variant == 9) return launch_cfg<4, 4, 4, 0, 1, 1, 4>(e, a, s);   // ring fed by consumer warp 0: eight warps, up to 255 registers
             return launch_cfg<4, 4, 4, 0, 1>(e, a, s);                        // ring 4 x 8 KiB, twiddles through L1
     }

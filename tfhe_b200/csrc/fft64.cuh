@@ -386,19 +386,24 @@ __device__ __forceinline__ void fft_inverse(double2 (&y)[32], double2 *buf, cons
 // KL: no key ring at all: every warp loads its key rows straight from L2 / L1 (ld.global.nc) into registers.  Nothing then
 // couples the teams of a CTA (no shared ring, no producer warp, no mbarriers): they drift out of phase and the integer,
 // FP64 and shared-memory phases of different teams overlap.  Costs TEAMS x the L2 -> SM key traffic of the ring.
+// KL == 5: tensor memory as the key cache, filled by the copy engines: the producer warp streams the key into a small staging
+// ring with cp.async.bulk and moves every staged piece on with tcgen05.cp (shared -> tensor memory, 64 lanes x 128 bit with
+// the warpx2::02_13 multicast: the 32 lanes of key column r = 0 land in lane quadrants 0 and 2, those of r = 1 in 1 and 3 -
+// exactly the quadrants of the consumer warps that need them); completion comes back through tcgen05.commit on mbarriers.
+// No thread's registers or load/store unit touch the key until a consumer's tcgen05.ld (mac_tmem).
 // KL == 4: the ring WITHOUT a producer warp: lane 0 of consumer warp 0 issues the bulk copies (RingFeed below).  A ninth warp
 // puts three warps on one scheduler, and a scheduler's 16 K registers then allow 168 per thread; eight warps may use 255.
 template <int TEAMS, int NS, int RS, int TWS = 1, int HB = 0, int GROUPS = 1, int KL = 0>
 struct Cfg {
     static constexpr int CONSUMER_WARPS = 2 * TEAMS;
-    static constexpr int THREADS = 32 * (CONSUMER_WARPS + (KL == 3 ? 4 : KL ? 0 : GROUPS));   // KL == 3: one producer warp per lane quadrant
+    static constexpr int THREADS = 32 * (CONSUMER_WARPS + (KL == 3 ? 4 : KL == 5 ? 1 : KL ? 0 : GROUPS));   // KL == 3: one producer warp per lane quadrant
     static constexpr int TEAMS_PER_GROUP = TEAMS / GROUPS;
     static constexpr int STAGE_POINTS = RS * 4 * 32;
     static constexpr int STAGES_PER_GGSW = 32 / RS;
     static constexpr int WARP_BUF_POINTS = HB ? HBUF_BYTES / 16 : BUF_POINTS;   // in double2 units
     static constexpr size_t SMEM =
         sizeof(double2) * TWB_ENTRIES * TWS + (size_t)TEAMS * (sizeof(u64) * 2 * N + sizeof(double2) * 2 * WARP_BUF_POINTS) +
-        (KL == 3 ? sizeof(u64) * 16 : (KL && KL != 4) ? 0 : sizeof(double2) * (size_t)GROUPS * NS * STAGE_POINTS + sizeof(u64) * 2 * NS * GROUPS + (KL == 4 ? sizeof(u32) * NS : 0)) + 16;
+        (KL == 3 ? sizeof(u64) * 16 : KL == 5 ? sizeof(double2) * (size_t)NS * STAGE_POINTS + sizeof(u64) * (2 * NS + 4) : (KL && KL != 4) ? 0 : sizeof(double2) * (size_t)GROUPS * NS * STAGE_POINTS + sizeof(u64) * 2 * NS * GROUPS + (KL == 4 ? sizeof(u32) * NS : 0)) + 16;
 };
 
 // ------------------------------------------------------------------------------------------ tensor memory as the key cache
@@ -437,6 +442,17 @@ __device__ __forceinline__ void tmem_alloc_512(u32 *smem_slot) {
 }
 __device__ __forceinline__ void tmem_free_512(u32 taddr) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(taddr) : "memory");
+}
+
+// shared -> tensor memory: 64 rows of 16 bytes (contiguous: no swizzle, 8-row core matrices 128 bytes apart); rows 0..31 go to
+// lanes 0..31 of quadrants 0 and 2, rows 32..63 to quadrants 1 and 3, four columns from taddr (scripts/ubench/tcgen05_cp_probe.cu)
+__device__ __forceinline__ void tmem_cp_64x128(u32 taddr, const void *smem_src) {
+    const u64 desc = (u64)((tk_smem_addr(smem_src) >> 4) & 0x3FFFu) | ((u64)8 << 32) | ((u64)1 << 46);
+    asm volatile("tcgen05.cp.cta_group::1.64x128b.warpx2::02_13 [%0], %1;" ::"r"(taddr), "l"(desc) : "memory");
+}
+// the mbarrier gets one arrival when every tcgen05 operation this thread issued before has completed
+__device__ __forceinline__ void tmem_commit(u64 *bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(tk_smem_addr(bar)) : "memory");
 }
 
 // multiply-accumulate of the swapped spectra with the staged key rows: out = X0 K[0][r] + X1 K[1][r], in the oracle's order;
@@ -652,7 +668,7 @@ __device__ __forceinline__ void mac_all(double2 (&y)[32], const double2 *oth, co
     }
 }
 
-// LAG (experiments, profiles/r02d_lag.txt): the teams of the upper half of a full CTA (the second warp of every scheduler)
+// LAG (experiments, profiles/r02d_overlap_variants.txt): the teams of the upper half of a full CTA (the second warp of every scheduler)
 // run BEHIND the lower half instead of in lock step with it, so that a scheduler's two warps are in different phases (one in
 // an FP64 phase, the other in a shared-memory or integer phase).  LAG = 1: a start delay of a.stagger_ns cycles only;
 // LAG = 2: the offset is also held by two named barriers (13: a trailer starts iteration i after the leaders passed point
@@ -695,6 +711,17 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
                 mbar_init(tfull + 2 * q + b, 1);
                 mbar_init(tempty + 2 * q + b, quadrant_consumers(q) ? quadrant_consumers(q) : 1);
             }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (KL == 5 && tid == 0) {   // staging ring: full (TMA bytes) / empty (tcgen05.commit); key buffers: tfull (commit) / tempty (consumer warps)
+        for (int s = 0; s < NS; s++) {
+            mbar_init(full_all + s, 1);
+            mbar_init(empty_all + s, 1);
+        }
+        for (int b = 0; b < 2; b++) {
+            mbar_init(empty_all + NS + b, 1);
+            mbar_init(empty_all + NS + 2 + b, 2 * live_teams);
+        }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if ((!KL || KL == 4) && tid == 0) {
@@ -745,6 +772,38 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
             tmem_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(tfull + 2 * q + b);
+        }
+        return;
+    }
+    if (KL == 5 && warp >= C::CONSUMER_WARPS) {   // ---- one lane: key -> staging ring (TMA) -> tensor memory (tcgen05.cp)
+        if (lane == 0) {
+            constexpr u32 bytes = (u32)(sizeof(double2) * C::STAGE_POINTS);
+            constexpr u32 SPG = C::STAGES_PER_GGSW;
+            u64 *tfull5 = empty_all + NS, *tempty5 = empty_all + NS + 2;
+            u32 issued = 0;
+            const u32 total5 = a.stagger_ns == 7777u ? (total < 2 * SPG ? total : 2 * SPG) : total;
+            for (u32 t = 0; t < total5; t++) {
+                while (issued < total5 && issued < t + (u32)NS) {   // keep the staging ring requested NS pieces ahead
+                    const u32 s2 = issued % NS;
+                    if (issued >= (u32)NS) mbar_wait(empty_all + s2, ((issued / NS) - 1) & 1);
+                    mbar_expect_tx(full_all + s2, bytes);
+                    bulk_g2s(ring_all + (size_t)s2 * C::STAGE_POINTS, a.bsk + (size_t)issued * C::STAGE_POINTS, bytes, full_all + s2);
+                    issued++;
+                }
+                const u32 s = t % NS, itp = t / SPG, c = t % SPG, b = itp & 1;
+                if (c == 0 && itp >= 2) mbar_wait(tempty5 + b, ((itp >> 1) - 1) & 1);   // the consumers are done with GGSW itp - 2
+                mbar_wait(full_all + s, (t / NS) & 1);
+                tmem_fence_after();
+                const double2 *st = ring_all + (size_t)s * C::STAGE_POINTS;
+#pragma unroll
+                for (int ii = 0; ii < RS; ii++)
+#pragma unroll
+                    for (int j = 0; j < 2; j++)
+                        tmem_cp_64x128(tmem_base + 256u * b + 8u * (c * RS + ii) + 4u * j, st + (ii * 4 + 2 * j) * 32);
+                tmem_commit(empty_all + s);
+                if (c == SPG - 1) tmem_commit(tfull5 + b);
+                if (a.stagger_ns) __nanosleep(a.stagger_ns);   // pace the refill over the iteration instead of one burst after the MAC
+            }
         }
         return;
     }
@@ -818,7 +877,7 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
     for (u32 it = 0; it < a.steps; it++) {
         // KL == 2: no ring, but the live consumer warps of the CTA meet once per iteration: they then ask for the same key
         // rows at about the same time (one L2 request, L1 hits for the rest) and keep sharing instruction fetches
-        if (KL == 2 || KL == 3) asm volatile("bar.sync 15, %0;" ::"r"(64u * live_teams) : "memory");
+        if (KL == 2 || KL == 3 || KL == 5) asm volatile("bar.sync 15, %0;" ::"r"(64u * live_teams) : "memory");
         if (LAG == 2) {
             if (trailer) asm volatile("bar.sync 13, %0;" ::"r"(LAG_THREADS) : "memory");
             if (leader && it) asm volatile("bar.sync 14, %0;" ::"r"(LAG_THREADS) : "memory");
@@ -864,6 +923,10 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
             mbar_wait(tfull + 2 * ((u32)warp & 3u) + (it & 1u), (it >> 1) & 1u);
             tmem_fence_after();
         }
+        if (KL == 5 && (a.stagger_ns != 7777u || it < 2)) {   // 7777: timing experiment, the refill stops after two GGSWs (wrong results)
+            mbar_wait(empty_all + NS + (it & 1u), (it >> 1) & 1u);
+            tmem_fence_after();
+        }
         // swap spectra with the partner warp
         if (!HB) {
 #pragma unroll
@@ -874,20 +937,20 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
             // stream in (the ring holds half a GGSW), then rows 16..31
             constexpr int CH = 16 / RS;
             if (r == 0)
-                (KL == 3 ? mac_tmem<0, 0, (0) * RS / 2, (CH) * RS / 2>(x, buf_oth, tq + 256u * (it & 1u), lane)
+                ((KL == 3 || KL == 5) ? mac_tmem<0, 0, (0) * RS / 2, (CH) * RS / 2>(x, buf_oth, tq + 256u * (it & 1u), lane)
                  : (KL && KL != 4) ? mac_global<0, RS, 0, 0, CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
                     : mac_all<0, NS, RS, 0, 0, CH>(x, buf_oth, ring, full, empty, t, lane, fdp));
             else
-                (KL == 3 ? mac_tmem<1, 0, (0) * RS / 2, (CH) * RS / 2>(x, buf_oth, tq + 256u * (it & 1u), lane)
+                ((KL == 3 || KL == 5) ? mac_tmem<1, 0, (0) * RS / 2, (CH) * RS / 2>(x, buf_oth, tq + 256u * (it & 1u), lane)
                  : (KL && KL != 4) ? mac_global<1, RS, 0, 0, CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
                     : mac_all<1, NS, RS, 0, 0, CH>(x, buf_oth, ring, full, empty, t, lane, fdp));
             pass_b_inv_half<0, MK>(x, twB, lane, a, mark_);
             if (r == 0)
-                (KL == 3 ? mac_tmem<0, 0, (CH) * RS / 2, (2 * CH) * RS / 2>(x, buf_oth, tq + 256u * (it & 1u), lane)
+                ((KL == 3 || KL == 5) ? mac_tmem<0, 0, (CH) * RS / 2, (2 * CH) * RS / 2>(x, buf_oth, tq + 256u * (it & 1u), lane)
                  : (KL && KL != 4) ? mac_global<0, RS, 0, CH, 2 * CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
                     : mac_all<0, NS, RS, 0, CH, 2 * CH>(x, buf_oth, ring, full, empty, t, lane, fdp));
             else
-                (KL == 3 ? mac_tmem<1, 0, (CH) * RS / 2, (2 * CH) * RS / 2>(x, buf_oth, tq + 256u * (it & 1u), lane)
+                ((KL == 3 || KL == 5) ? mac_tmem<1, 0, (CH) * RS / 2, (2 * CH) * RS / 2>(x, buf_oth, tq + 256u * (it & 1u), lane)
                  : (KL && KL != 4) ? mac_global<1, RS, 0, CH, 2 * CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
                     : mac_all<1, NS, RS, 0, CH, 2 * CH>(x, buf_oth, ring, full, empty, t, lane, fdp));
             FFT64_MARK(5);
@@ -903,11 +966,11 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
             asm volatile("bar.sync %0, 64;" ::"r"(barrier_id) : "memory");
             FFT64_MARK(4);
             if (r == 0)
-                (KL == 3 ? mac_tmem<0, 1, (0) * RS / 2, (CH) * RS / 2>(x, buf_oth, tq + 256u * (it & 1u), lane)
+                ((KL == 3 || KL == 5) ? mac_tmem<0, 1, (0) * RS / 2, (CH) * RS / 2>(x, buf_oth, tq + 256u * (it & 1u), lane)
                  : (KL && KL != 4) ? mac_global<0, RS, 1, 0, CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
                     : mac_all<0, NS, RS, 1, 0, CH>(x, buf_oth, ring, full, empty, t, lane, fdp));
             else
-                (KL == 3 ? mac_tmem<1, 1, (0) * RS / 2, (CH) * RS / 2>(x, buf_oth, tq + 256u * (it & 1u), lane)
+                ((KL == 3 || KL == 5) ? mac_tmem<1, 1, (0) * RS / 2, (CH) * RS / 2>(x, buf_oth, tq + 256u * (it & 1u), lane)
                  : (KL && KL != 4) ? mac_global<1, RS, 1, 0, CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
                     : mac_all<1, NS, RS, 1, 0, CH>(x, buf_oth, ring, full, empty, t, lane, fdp));
             FFT64_MARK(5);
@@ -918,11 +981,11 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
             FFT64_MARK(4);
             pass_b_inv_half<0, MK>(x, twB, lane, a, mark_);   // rows 0..15 are final: their inverse butterflies cover the wait for the key rows
             if (r == 0)
-                (KL == 3 ? mac_tmem<0, 1, (CH) * RS / 2, (2 * CH) * RS / 2>(x, buf_oth, tq + 256u * (it & 1u), lane)
+                ((KL == 3 || KL == 5) ? mac_tmem<0, 1, (CH) * RS / 2, (2 * CH) * RS / 2>(x, buf_oth, tq + 256u * (it & 1u), lane)
                  : (KL && KL != 4) ? mac_global<0, RS, 1, CH, 2 * CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
                     : mac_all<0, NS, RS, 1, CH, 2 * CH>(x, buf_oth, ring, full, empty, t, lane, fdp));
             else
-                (KL == 3 ? mac_tmem<1, 1, (CH) * RS / 2, (2 * CH) * RS / 2>(x, buf_oth, tq + 256u * (it & 1u), lane)
+                ((KL == 3 || KL == 5) ? mac_tmem<1, 1, (CH) * RS / 2, (2 * CH) * RS / 2>(x, buf_oth, tq + 256u * (it & 1u), lane)
                  : (KL && KL != 4) ? mac_global<1, RS, 1, CH, 2 * CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
                     : mac_all<1, NS, RS, 1, CH, 2 * CH>(x, buf_oth, ring, full, empty, t, lane, fdp));
             FFT64_MARK(5);
@@ -935,6 +998,11 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
             tmem_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(tempty + 2 * ((u32)warp & 3u) + (it & 1u));
+        }
+        if (KL == 5) {
+            tmem_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(empty_all + NS + 2 + (it & 1u));
         }
         pass_b_stage<true, 0, 0, 16, MK>(x, twB, lane);
         FFT64_MARK(7);
