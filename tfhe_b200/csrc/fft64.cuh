@@ -186,13 +186,17 @@ __device__ __forceinline__ void bfly_group(double2 (&x)[32], const int (&iu)[G],
 // 93.0 ms without, 90.1 ms with a bare never-taken branch (profiles/r02b_fft_variants.txt).  -DFFT64_NO_MARKS removes them.
 // MK (a template argument of everything that contains marks) = 0 compiles them out of one instantiation: a warp that is
 // alone on its scheduler (one ciphertext per CTA, the latency case) is faster with the free schedule.
+// MK >> 4 = marks left out of that instantiation (bit k = mark k).  Which boundaries ptxas should see is an empirical matter
+// per kernel (profiles/r02d_mark_sweep.txt): the four-ciphertext kernel is 4.1 % faster without marks 1, 7 and 8 (forward pass A
+// flows into its transpose, the inverse pass B into the transpose and the inverse pass A: 386 << 4), the three-ciphertext kernel
+// 5 % slower with the same mask.
 #ifndef FFT64_SKIP_MARKS
 #define FFT64_SKIP_MARKS 0   // bit k set: phase mark k is left out (codegen experiments)
 #endif
 #ifndef FFT64_NO_MARKS
 #define FFT64_MARK(k)                                                                  \
     do {                                                                               \
-        if ((MK & 1) && !((FFT64_SKIP_MARKS >> (k)) & 1) && a.trace && lane == 0) {                                                    \
+        if ((MK & 1) && !(((FFT64_SKIP_MARKS | (MK >> 4)) >> (k)) & 1) && a.trace && lane == 0) {                                      \
             long long now_;                                                            \
             asm volatile("mov.u64 %0, %%clock64;" : "=l"(now_)::"memory");             \
             atomicAdd((unsigned long long *)a.trace + (k), (unsigned long long)(now_ - mark_)); \
