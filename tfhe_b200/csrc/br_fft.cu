@@ -139,14 +139,14 @@ static int launch_cfg(lux_engine *e, const Args &a, cudaStream_t s) {
 }
 
 // Ciphertexts per CTA.  Measured on B200 at the named set (profiles/r02b_fft_phase_cycles.txt), cycles per CMUX iteration of a
-// CTA: 1 team 17.0k, 2 teams 15.3k, 3 teams 18.6k, 4 teams (half-size buffers) 22.0k.  A batch runs in
+// CTA: 1 team 17.0k, 2 teams 15.3k, 3 teams 18.6k, 4 teams (half-size buffers) 21.5k.  A batch runs in
 // ceil(B / (teams x SMs)) waves, so the choice minimises waves x cycles; tiny batches spread over the SMs first.
 static int pick_teams(const lux_engine *e, size_t B) {
     if (e->force_teams >= 1 && e->force_teams <= 4) return e->force_teams;
     const size_t sms = (size_t)e->sm_count;
     if (B <= sms) return 1;
     if (B <= 2 * sms) return 2;
-    const double c3 = (double)((B + 3 * sms - 1) / (3 * sms)) * 18.6, c4 = (double)((B + 4 * sms - 1) / (4 * sms)) * 22.0;
+    const double c3 = (double)((B + 3 * sms - 1) / (3 * sms)) * 18.6, c4 = (double)((B + 4 * sms - 1) / (4 * sms)) * 21.5;
     return c3 < c4 ? 3 : 4;
 }
 
@@ -179,7 +179,8 @@ int lux_fft_launch_br(lux_engine *e, Args a, cudaStream_t s) {
         case 3:
             if (variant == 1) return launch_cfg<3, 8, 4, 1, 1>(e, a, s);      // half-size buffers, ring = one whole GGSW
             if (variant == 13) return launch_cfg<3, 4, 4, 0>(e, a, s);        // every phase mark
-            return launch_cfg<3, 4, 4, 0, 0, 1, 0, 1 | (384 << 4)>(e, a, s);   // marks 7, 8 left out: 48.2k -> 49.6k PBS/s at B = 4,440
+            if (variant == 14) return launch_cfg<3, 4, 4, 0, 0, 1, 0, 1 | (384 << 4)>(e, a, s);   // the lighter decomposition
+            return launch_cfg<3, 4, 4, 0, 0, 1, 0, 1 | 4 | (384 << 4)>(e, a, s);   // marks 7, 8 left out: 48.2k -> 49.6k PBS/s at B = 4,440
         default:
             if (variant == 1) return launch_cfg<4, 3, 4, 1, 1>(e, a, s);      // twiddles in shared memory, ring 3 x 8 KiB
             if (variant == 2) return launch_cfg<4, 1, 4, 1, 1, 1, 1>(e, a, s);   // no ring: key rows straight from L2 / L1

@@ -82,6 +82,13 @@ __device__ __forceinline__ double digit1_double(u32 hi, u32 half, u32 sh) {
     const int dm1 = (int)(hi - half) >> sh;
     return __dsub_rn(__hiloint2double(0x43300000, dm1 ^ 0x80000000), 4503601774854143.0);   // 2^52 + 2^31 - 1
 }
+// the same digit when the rounding offset is already IN the word: hi_off = hi - half + 2^31 (the caller folds that constant into
+// the subtraction that produces hi, where the carry chain has a free operand).  The +2^31 turns the arithmetic shift into a
+// logical one, (hi_off >> sh) = digit - 1 + 2^(31 - sh) exactly, and the magic constant takes the offset back out: one shift and
+// one DADD per coefficient.  magic = 2^52 + 2^(31 - sh) - 1.
+__device__ __forceinline__ double digit1_double_off(u32 hi_off, u32 sh, double magic) {
+    return __dsub_rn(__hiloint2double(0x43300000, (int)(hi_off >> sh)), magic);
+}
 // round(x 2N / 2^64) in [0, 2N]      crypto/lwe.rs:28-34
 __device__ __forceinline__ u32 mod_switch(u64 x) {
     const u64 a = x >> (64 - LOGN - 2);
@@ -870,13 +877,18 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
         }                                                                                                                    \
     } while (0)
     long long mark_ = a.trace ? clock64() : 0;
+    // MK bit 2: the older decomposition arithmetic (the three-ciphertext kernel, whose six warps leave the ALU pipe slack, is
+    // 3 % faster with it: profiles/r02d_mark_sweep.txt)
+    constexpr bool OLD_DEC = (MK & 4) != 0;
     const u32 dg_half = 1u << (31 - a.logB), dg_sh = 32 - a.logB;
+    const u64 dg_off = (u64)(0x80000000u - dg_half) << 32;                                   // folded into the subtraction below
+    const double dg_magic = 4503599627370496.0 + (double)(1u << (31 - dg_sh)) - 1.0;         // 2^52 + 2^(31 - sh) - 1
     const unsigned char *accb = (const unsigned char *)acc;
-    // own[2 i + h] = acc[lane + 32 (i + 32 h)]: this lane's coefficients stay in registers from the update of one iteration
+    // own[2 i + h] = acc[lane + 32 (i + 32 h)] - dg_off: this lane's coefficients stay in registers from the update of one iteration
     // to the decomposition of the next (they take the place of x[], which is dead in between)
     u64 own[64];
 #pragma unroll
-    for (int k = 0; k < 64; k++) own[k] = acc[lane + 32 * ((k >> 1) + 32 * (k & 1))];
+    for (int k = 0; k < 64; k++) own[k] = acc[lane + 32 * ((k >> 1) + 32 * (k & 1))] - (OLD_DEC ? (u64)0 : dg_off);
 #pragma unroll 1
     for (u32 it = 0; it < a.steps; it++) {
         // KL == 2: no ring, but the live consumer warps of the CTA meet once per iteration: they then ask for the same key
@@ -895,19 +907,39 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
         {
             const u32 b = sh & 31u;
             const u32 lp8 = (((u32)lane - b) & 31u) << 3;
-            const u32 ap8 = (((sh >> 5) + ((u32)lane < b ? 1u : 0u)) & 127u) << 8;
+            if (OLD_DEC) {   // the form of the first half of round 2: 12 ALU instructions per coefficient
+                const u32 ap8 = (((sh >> 5) + ((u32)lane < b ? 1u : 0u)) & 127u) << 8;
+#pragma unroll
+                for (int i = 0; i < 32; i++) {
+                    double dd[2];
+#pragma unroll
+                    for (int h = 0; h < 2; h++) {
+                        const u32 tt = (u32)((i + 32 * h) << 8) - ap8;
+                        const u64 v = *(const u64 *)(accb + ((tt & 0x3F00u) | lp8));
+                        const u32 c = (tt >> 14) & 1u;
+                        const u64 d = (v ^ ((u64)0 - (u64)c)) + c - own[2 * i + h];
+                        dd[h] = digit1_double((u32)(d >> 32), dg_half, dg_sh);
+                    }
+                    x[i] = make_double2(dd[0], dd[1]);
+                }
+            } else {
+            // the row counter lives in the TOP seven bits of a word (row << 25): its wrap mod 128 is the word's own, bit 31 says
+            // "negated half", so one arithmetic shift gives the negation mask (0 / -1) and (v ^ m) - m is the conditional negation
+            const u32 ap25 = ((sh >> 5) + ((u32)lane < b ? 1u : 0u)) << 25;
 #pragma unroll
             for (int i = 0; i < 32; i++) {
                 double dd[2];
 #pragma unroll
                 for (int h = 0; h < 2; h++) {
-                    const u32 tt = (u32)((i + 32 * h) << 8) - ap8;
-                    const u64 v = *(const u64 *)(accb + ((tt & 0x3F00u) | lp8));
-                    const u32 c = (tt >> 14) & 1u;
-                    const u64 d = (v ^ ((u64)0 - (u64)c)) + c - own[2 * i + h];
-                    dd[h] = digit1_double((u32)(d >> 32), dg_half, dg_sh);
+                    const u32 tt = ((u32)(i + 32 * h) << 25) - ap25;
+                    const u64 v = *(const u64 *)(accb + (((tt >> 17) & 0x3F00u) | lp8));
+                    const u32 m32 = (u32)((int)tt >> 31);
+                    const u64 m = ((u64)m32 << 32) | m32;
+                    const u64 d = (v ^ m) - m - own[2 * i + h];   // own[] already carries -dg_off
+                    dd[h] = digit1_double_off((u32)(d >> 32), dg_sh, dg_magic);
                 }
                 x[i] = make_double2(dd[0], dd[1]);
+            }
             }
         }
         FFT64_MARK(0);
@@ -1038,7 +1070,14 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
                 const u32 q = (u32)lane + 32u * (i0 + k / 2) + ((k & 1) ? M : 0);
                 const u64 nv = acc[q] + ((u64)__double_as_longlong(f[k]) << 13);
                 acc[q] = nv;
-                own[2 * (i0 + k / 2) + (k & 1)] = nv;
+                // the digit's rounding offset rides in the register copy: one add on the high word here, where shared memory binds,
+                // instead of one in the ALU-bound decomposition (the empty asm keeps ptxas from sinking it back there)
+                u64 ov = nv;
+                if (!OLD_DEC) {
+                    ov = nv - dg_off;
+                    asm volatile("" : "+l"(ov));
+                }
+                own[2 * (i0 + k / 2) + (k & 1)] = ov;
             }
         }
         __syncwarp();
