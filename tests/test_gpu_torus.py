@@ -211,7 +211,7 @@ def test_latency_kernel_whole_pbs_both_orders_and_large_batch(rig_small, rig_sma
         assert np.array_equal(got, want) and np.array_equal(thr, want), B
 
 
-@pytest.mark.parametrize("teams", [1, 2, 3, 13, 4, 14, 24, 34, 54, 64, 74, 84, 94, 104, 114, 124, 134])
+@pytest.mark.parametrize("teams", [1, 2, 3, 13, 4, 14, 24, 34, 54, 64, 74, 84, 94, 104, 114, 124, 134, 154, 164, 174, 204, 214])
 def test_pbs_small_bit_exact_every_team_count(rig_small, teams):
     """whole PBS (key switch, blind rotation, extraction) against the oracle, every ciphertext of a ragged batch,
     for each ciphertexts-per-CTA configuration of the kernel (ring depth and stage size differ between them)"""

@@ -11,14 +11,14 @@ using namespace fft64;
 template <int TEAMS, int NS, int RS, int TWS, int HB = 0, int GROUPS = 1, int KL = 0, int MK = 1, int LAG = 0>
 __global__ void __launch_bounds__(Cfg<TEAMS, NS, RS, TWS, HB, GROUPS, KL>::THREADS, 1) blind_rotate_fft_kernel(const __grid_constant__ Args a) {
     extern __shared__ __align__(16) unsigned char smem[];
-    if (KL == 3 || KL == 5) {   // tensor memory as the key cache: all 512 columns, taken and returned by warp 0 of EVERY CTA
+    if (KL == 3 || KL == 5 || (MK & 16)) {   // tensor memory (key cache / accumulator mirror): all 512 columns, taken and returned by warp 0 of EVERY CTA
         __shared__ u32 tmem_slot;
         if (threadIdx.x < 32) tmem_alloc_512(&tmem_slot);
         tmem_fence_before();
         __syncthreads();
         tmem_fence_after();
         const u32 tbase = tmem_slot;
-        blind_rotate_body<TEAMS, NS, RS, TWS, HB, GROUPS, KL, MK>(a, smem, tbase);   // its early exits return to here
+        blind_rotate_body<TEAMS, NS, RS, TWS, HB, GROUPS, KL, MK, LAG>(a, smem, tbase);   // its early exits return to here
         tmem_fence_before();
         __syncthreads();
         if (threadIdx.x < 32) tmem_free_512(tbase);
@@ -179,8 +179,8 @@ int lux_fft_launch_br(lux_engine *e, Args a, cudaStream_t s) {
         case 3:
             if (variant == 1) return launch_cfg<3, 8, 4, 1, 1>(e, a, s);      // half-size buffers, ring = one whole GGSW
             if (variant == 13) return launch_cfg<3, 4, 4, 0>(e, a, s);        // every phase mark
-            if (variant == 14) return launch_cfg<3, 4, 4, 0, 0, 1, 0, 1 | (384 << 4)>(e, a, s);   // the lighter decomposition
-            return launch_cfg<3, 4, 4, 0, 0, 1, 0, 1 | 4 | (384 << 4)>(e, a, s);   // marks 7, 8 left out: 48.2k -> 49.6k PBS/s at B = 4,440
+            if (variant == 14) return launch_cfg<3, 4, 4, 0, 0, 1, 0, 1 | (384 << 8)>(e, a, s);   // the lighter decomposition
+            return launch_cfg<3, 4, 4, 0, 0, 1, 0, 1 | 4 | (384 << 8)>(e, a, s);   // marks 7, 8 left out: 48.2k -> 49.6k PBS/s at B = 4,440
         default:
             if (variant == 1) return launch_cfg<4, 3, 4, 1, 1>(e, a, s);      // twiddles in shared memory, ring 3 x 8 KiB
             if (variant == 2) return launch_cfg<4, 1, 4, 1, 1, 1, 1>(e, a, s);   // no ring: key rows straight from L2 / L1
@@ -206,7 +206,14 @@ int lux_fft_launch_br(lux_engine *e, Args a, cudaStream_t s) {
             if (variant == 12) return launch_cfg<4, 3, 4, 1, 1, 1, 5>(e, a, s);   // staging 3 x 8 KiB, twiddles in shared memory
             if (variant == 9) return launch_cfg<4, 4, 4, 0, 1, 1, 4>(e, a, s);   // ring fed by consumer warp 0: eight warps, up to 255 registers
             if (variant == 13) return launch_cfg<4, 4, 4, 0, 1>(e, a, s);     // every phase mark (the default until r02d)
-            return launch_cfg<4, 4, 4, 0, 1, 1, 0, 1 | (386 << 4)>(e, a, s);  // ring 4 x 8 KiB, twiddles through L1, marks 1, 7, 8 left out
+            if (variant == 20) return launch_cfg<4, 4, 4, 0, 1, 1, 0, 1 | 16 | (386 << 8)>(e, a, s);   // accumulator mirror in tensor memory
+            if (variant == 21) return launch_cfg<4, 4, 4, 0, 1, 1, 0, 1 | 16>(e, a, s);
+            if (variant == 15) return launch_cfg<4, 4, 4, 0, 1, 1, 0, 1 | 8 | (386 << 8)>(e, a, s);   // butterfly stages inside the key MAC
+            if (variant == 16) return launch_cfg<4, 4, 4, 0, 1, 1, 0, 1 | 8>(e, a, s);                // same, every mark
+            if (variant == 17) return launch_cfg<4, 4, 4, 0, 1, 1, 4, 1 | 8 | (386 << 8)>(e, a, s);   // same on the consumer-fed ring (230 registers)
+            if (variant == 18) return launch_cfg<4, 4, 4, 0, 1, 1, 4, 1 | 8>(e, a, s);
+            if (variant == 19) return launch_cfg<4, 4, 4, 0, 1, 1, 4, 1 | (386 << 8)>(e, a, s);       // consumer-fed ring, marks 1, 7, 8 out
+            return launch_cfg<4, 4, 4, 0, 1, 1, 0, 1 | (386 << 8)>(e, a, s);  // ring 4 x 8 KiB, twiddles through L1, marks 1, 7, 8 left out
     }
 }
 

@@ -29,6 +29,7 @@
 // cp.async.bulk (TMA) + mbarriers and is shared by the TEAMS ciphertexts of the CTA.
 #pragma once
 #include "tfhe_kernels.cuh"
+#include <type_traits>
 
 namespace fft64 {
 
@@ -193,9 +194,9 @@ __device__ __forceinline__ void bfly_group(double2 (&x)[32], const int (&iu)[G],
 // 93.0 ms without, 90.1 ms with a bare never-taken branch (profiles/r02b_fft_variants.txt).  -DFFT64_NO_MARKS removes them.
 // MK (a template argument of everything that contains marks) = 0 compiles them out of one instantiation: a warp that is
 // alone on its scheduler (one ciphertext per CTA, the latency case) is faster with the free schedule.
-// MK >> 4 = marks left out of that instantiation (bit k = mark k).  Which boundaries ptxas should see is an empirical matter
+// MK >> 8 = marks left out of that instantiation (bit k = mark k).  Which boundaries ptxas should see is an empirical matter
 // per kernel (profiles/r02d_mark_sweep.txt): the four-ciphertext kernel is 4.1 % faster without marks 1, 7 and 8 (forward pass A
-// flows into its transpose, the inverse pass B into the transpose and the inverse pass A: 386 << 4), the three-ciphertext kernel
+// flows into its transpose, the inverse pass B into the transpose and the inverse pass A: 386 << 8), the three-ciphertext kernel
 // 5 % slower with the same mask.
 #ifndef FFT64_SKIP_MARKS
 #define FFT64_SKIP_MARKS 0   // bit k set: phase mark k is left out (codegen experiments)
@@ -203,7 +204,7 @@ __device__ __forceinline__ void bfly_group(double2 (&x)[32], const int (&iu)[G],
 #ifndef FFT64_NO_MARKS
 #define FFT64_MARK(k)                                                                  \
     do {                                                                               \
-        if ((MK & 1) && !(((FFT64_SKIP_MARKS | (MK >> 4)) >> (k)) & 1) && a.trace && lane == 0) {                                      \
+        if ((MK & 1) && !(((FFT64_SKIP_MARKS | (MK >> 8)) >> (k)) & 1) && a.trace && lane == 0) {                                      \
             long long now_;                                                            \
             asm volatile("mov.u64 %0, %%clock64;" : "=l"(now_)::"memory");             \
             atomicAdd((unsigned long long *)a.trace + (k), (unsigned long long)(now_ - mark_)); \
@@ -469,9 +470,13 @@ __device__ __forceinline__ void tmem_commit(u64 *bar) {
 // multiply-accumulate of the swapped spectra with the staged key rows: out = X0 K[0][r] + X1 K[1][r], in the oracle's order;
 // the RS rows of a stage advance together, one fused multiply-add of each chain at a time
 // HB: the partner's rows sit as [row - 16 * (row0 / 16)][lane] (half-size buffer, two rounds of 16 rows)
-template <int R, int RS, int HB = 0, int KG = 0>
+// IL (interleave, RS == 4 only): a butterfly stage on the OTHER sixteen rows is issued between the loads of this chunk and its
+// multiply-adds, so that the FP64 pipe works while the key rows cross the shared-memory crossbar (in lock step all warps of the
+// SM otherwise load at the same time and multiply at the same time).  IL = 1: forward stage ILS of rows 16..31 (butterflies
+// 8..15; the chunk's own rows are 0..15); IL = 2: inverse stage ILS of rows 0..15 (the chunk's rows are 16..31).
+template <int R, int RS, int HB = 0, int KG = 0, int IL = 0, int ILS = 0, int MK = 1>
 __device__ __forceinline__ void mac_rows(double2 (&y)[32], const double2 *oth, const double2 *stage, int row0, int lane,
-                                         const u32 *kw = nullptr) {
+                                         const u32 *kw = nullptr, const double2 *twB = nullptr) {
     double2 k0[RS], k1[RS], x0[RS], x1[RS];
     double re[RS], im[RS];
     // KG == 2: kw = the 16 words of two rows (RS == 2) of this quadrant's key column, already loaded from tensor memory
@@ -492,6 +497,8 @@ __device__ __forceinline__ void mac_rows(double2 (&y)[32], const double2 *oth, c
         x0[ii] = R == 0 ? y[i] : o;
         x1[ii] = R == 0 ? o : y[i];
     }
+    if (IL == 1) pass_b_stage<false, ILS, 8, 16, MK>(y, twB, lane);
+    if (IL == 2) pass_b_stage<true, ILS, 0, 8, MK>(y, twB, lane);
 #pragma unroll
     for (int ii = 0; ii < RS; ii++) {
         re[ii] = __fma_rn(x0[ii].x, k0[ii].x, 0.0);
@@ -634,9 +641,10 @@ __device__ __forceinline__ void feed_after_release(const RingFeed &fd, u32 t, u6
 #ifndef FFT64_MAC_PIPE
 #define FFT64_MAC_PIPE 0
 #endif
-template <int R, int NS, int RS, int HB = 0, int C0 = 0, int C1 = 32 / RS>
+// IL (RS == 4, four chunks): chunk c carries forward stage 1 + c of rows 16..31 (IL = 1) or inverse stage 4 - c of rows 0..15 (IL = 2)
+template <int R, int NS, int RS, int HB = 0, int C0 = 0, int C1 = 32 / RS, int IL = 0, int MK = 1>
 __device__ __forceinline__ void mac_all(double2 (&y)[32], const double2 *oth, const double2 *ring, u64 *full, u64 *empty, u32 &t, int lane,
-                                        const RingFeed *fd = nullptr) {
+                                        const RingFeed *fd = nullptr, const double2 *twB = nullptr) {
     constexpr int SP = RS * 4 * 32;
     if (FFT64_MAC_PIPE && RS == 4) {
         KeyRows2 A, B;
@@ -663,6 +671,26 @@ __device__ __forceinline__ void mac_all(double2 (&y)[32], const double2 *oth, co
             }
             t++;
         }
+        return;
+    }
+    if constexpr (IL != 0) {
+        static_assert(RS == 4 && C1 - C0 == 4, "the interleave pairs four chunks with four butterfly stages");
+        auto chunk = [&](auto cc) {
+            constexpr int c = decltype(cc)::value;
+            const u32 s = t % NS;
+            mbar_wait(full + s, (t / NS) & 1);
+            mac_rows<R, RS, HB, 0, IL, (IL == 1 ? 1 + c : 4 - c), MK>(y, oth, ring + (size_t)s * SP, (C0 + c) * RS, lane, nullptr, twB);
+            __syncwarp();
+            if (lane == 0) {
+                mbar_arrive(empty + s);
+                if (fd) feed_after_release<NS, SP>(*fd, t, full, empty);
+            }
+            t++;
+        };
+        chunk(std::integral_constant<int, 0>{});
+        chunk(std::integral_constant<int, 1>{});
+        chunk(std::integral_constant<int, 2>{});
+        chunk(std::integral_constant<int, 3>{});
         return;
     }
 #pragma unroll
@@ -880,6 +908,11 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
     // MK bit 2: the older decomposition arithmetic (the three-ciphertext kernel, whose six warps leave the ALU pipe slack, is
     // 3 % faster with it: profiles/r02d_mark_sweep.txt)
     constexpr bool OLD_DEC = (MK & 4) != 0;
+    // MK bit 4: the update reads the old accumulator value from TENSOR MEMORY instead of shared memory (a mirror of this lane's 64
+    // coefficients: 128 columns per warp, the two warps of a lane quadrant side by side; written back with tcgen05.st): shared
+    // memory then only sees the store that the next iteration's rotated gather needs, 64 LDS.64 per lane and iteration fewer
+    constexpr bool TMACC = (MK & 16) != 0;
+    const u32 tacc = tmem_base + ((32u * ((u32)warp & 3u)) << 16) + ((u32)warp >= 4u ? 128u : 0u);
     const u32 dg_half = 1u << (31 - a.logB), dg_sh = 32 - a.logB;
     const u64 dg_off = (u64)(0x80000000u - dg_half) << 32;                                   // folded into the subtraction below
     const double dg_magic = 4503599627370496.0 + (double)(1u << (31 - dg_sh)) - 1.0;         // 2^52 + 2^(31 - sh) - 1
@@ -889,6 +922,20 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
     u64 own[64];
 #pragma unroll
     for (int k = 0; k < 64; k++) own[k] = acc[lane + 32 * ((k >> 1) + 32 * (k & 1))] - (OLD_DEC ? (u64)0 : dg_off);
+    if (TMACC) {
+#pragma unroll
+        for (int c = 0; c < 8; c++) {
+            u32 tv[16];
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                const u64 v = acc[lane + 32 * (((8 * c + k) >> 1) + 32 * (k & 1))];
+                tv[2 * k] = (u32)v;
+                tv[2 * k + 1] = (u32)(v >> 32);
+            }
+            tmem_st16(tacc + 16u * c, tv);
+        }
+        tmem_wait_st();
+    }
 #pragma unroll 1
     for (u32 it = 0; it < a.steps; it++) {
         // KL == 2: no ring, but the live consumer warps of the CTA meet once per iteration: they then ask for the same key
@@ -952,7 +999,18 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
         else
             col_to_row(x, buf, lane);
         FFT64_MARK(2);
-        pass_b<false, MK>(x, twB, lane, a, mark_);
+        // MK bit 3 (ring kernels with half-size buffers, four chunks per half): forward stages 1..4 of rows 16..31 are issued inside
+        // the first half of the key MAC and inverse stages 4..1 of rows 0..15 inside the second half (mac_rows, IL)
+        constexpr bool ILV = (MK & 8) != 0 && HB == 1 && RS == 4 && (KL == 0 || KL == 4);
+        if constexpr (ILV) {
+            pass_b_stage<false, 0, 0, 16, MK>(x, twB, lane);
+            pass_b_stage<false, 1, 0, 8, MK>(x, twB, lane);
+            pass_b_stage<false, 2, 0, 8, MK>(x, twB, lane);
+            pass_b_stage<false, 3, 0, 8, MK>(x, twB, lane);
+            pass_b_stage<false, 4, 0, 8, MK>(x, twB, lane);
+        } else {
+            pass_b<false, MK>(x, twB, lane, a, mark_);
+        }
         FFT64_MARK(3);
         FFT64_LAG_POINT(3);
         if (KL == 3) {   // this iteration's key rows sit in buffer it & 1 of the quadrant (stored during the previous iteration)
@@ -1001,6 +1059,12 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
             for (int i = 0; i < 16; i++) buf[i * 32 + lane] = x[i];
             asm volatile("bar.sync %0, 64;" ::"r"(barrier_id) : "memory");
             FFT64_MARK(4);
+            if constexpr (ILV) {
+                if (r == 0)
+                    mac_all<0, NS, RS, 1, 0, CH, 1, MK>(x, buf_oth, ring, full, empty, t, lane, fdp, twB);
+                else
+                    mac_all<1, NS, RS, 1, 0, CH, 1, MK>(x, buf_oth, ring, full, empty, t, lane, fdp, twB);
+            } else
             if (r == 0)
                 ((KL == 3 || KL == 5) ? mac_tmem<0, 1, (0) * RS / 2, (CH) * RS / 2>(x, buf_oth, tq + 256u * (it & 1u), lane)
                  : (KL && KL != 4) ? mac_global<0, RS, 1, 0, CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
@@ -1015,6 +1079,12 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
             for (int i = 0; i < 16; i++) buf[i * 32 + lane] = x[16 + i];
             asm volatile("bar.sync %0, 64;" ::"r"(barrier_id) : "memory");
             FFT64_MARK(4);
+            if constexpr (ILV) {
+                if (r == 0)
+                    mac_all<0, NS, RS, 1, CH, 2 * CH, 2, MK>(x, buf_oth, ring, full, empty, t, lane, fdp, twB);
+                else
+                    mac_all<1, NS, RS, 1, CH, 2 * CH, 2, MK>(x, buf_oth, ring, full, empty, t, lane, fdp, twB);
+            } else {
             pass_b_inv_half<0, MK>(x, twB, lane, a, mark_);   // rows 0..15 are final: their inverse butterflies cover the wait for the key rows
             if (r == 0)
                 ((KL == 3 || KL == 5) ? mac_tmem<0, 1, (CH) * RS / 2, (2 * CH) * RS / 2>(x, buf_oth, tq + 256u * (it & 1u), lane)
@@ -1024,6 +1094,7 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
                 ((KL == 3 || KL == 5) ? mac_tmem<1, 1, (CH) * RS / 2, (2 * CH) * RS / 2>(x, buf_oth, tq + 256u * (it & 1u), lane)
                  : (KL && KL != 4) ? mac_global<1, RS, 1, CH, 2 * CH>(x, buf_oth, a.bsk + (size_t)it * 32 * 4 * 32, lane)
                     : mac_all<1, NS, RS, 1, CH, 2 * CH>(x, buf_oth, ring, full, empty, t, lane, fdp));
+            }
             FFT64_MARK(5);
             asm volatile("bar.sync %0, 64;" ::"r"(barrier_id) : "memory");
             FFT64_MARK(6);
@@ -1055,6 +1126,8 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
 #pragma unroll
         for (int i0 = 0; i0 < 32; i0 += 4) {   // four points = eight independent conversion chains at a time
             double t[8], f[8];
+            u32 tv[16];
+            if (TMACC) tmem_ld16(tacc + 4u * i0, tv);   // own indices 2 i0 .. 2 i0 + 7 = columns 4 i0 .. 4 i0 + 15
 #pragma unroll
             for (int k = 0; k < 8; k++) t[k] = __dadd_rn((k & 1) ? x[i0 + k / 2].y : x[i0 + k / 2].x, MAGIC);
 #pragma unroll
@@ -1063,13 +1136,19 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
             for (int k = 0; k < 8; k++) f[k] = __dsub_rn((k & 1) ? x[i0 + k / 2].y : x[i0 + k / 2].x, t[k]);
 #pragma unroll
             for (int k = 0; k < 8; k++) f[k] = __fma_rn(f[k], TWO51, MAGIC);
+            if (TMACC) tmem_wait_ld();
 #pragma unroll
             for (int k = 0; k < 8; k++) {
                 // tor_from_double: (bits - 0x4338000000000000) << 13; the constant's set bits all leave the word, so the
                 // shift alone is the same value
                 const u32 q = (u32)lane + 32u * (i0 + k / 2) + ((k & 1) ? M : 0);
-                const u64 nv = acc[q] + ((u64)__double_as_longlong(f[k]) << 13);
+                const u64 old = TMACC ? (((u64)tv[2 * k + 1] << 32) | tv[2 * k]) : acc[q];
+                const u64 nv = old + ((u64)__double_as_longlong(f[k]) << 13);
                 acc[q] = nv;
+                if (TMACC) {
+                    tv[2 * k] = (u32)nv;
+                    tv[2 * k + 1] = (u32)(nv >> 32);
+                }
                 // the digit's rounding offset rides in the register copy: one add on the high word here, where shared memory binds,
                 // instead of one in the ALU-bound decomposition (the empty asm keeps ptxas from sinking it back there)
                 u64 ov = nv;
@@ -1079,7 +1158,9 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
                 }
                 own[2 * (i0 + k / 2) + (k & 1)] = ov;
             }
+            if (TMACC) tmem_st16(tacc + 4u * i0, tv);
         }
+        if (TMACC) tmem_wait_st();
         __syncwarp();
         FFT64_MARK(10);
     }
