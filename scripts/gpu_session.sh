@@ -12,6 +12,7 @@
 #   radix          scripts/bench_radix.py (C3-C5 op rates, single process)
 #   latency        scripts/latency_probe.py
 #   ubench         scripts/ubench/ubench_arith.cu
+#   ks             key switch parity tests + scripts/ks_probe.py (mma.sync vs tcgen05 form)
 set -u
 mkdir -p gpurun_out
 NCU_B=${NCU_B:-4440}
@@ -31,6 +32,8 @@ for stage in "$@"; do
     gate) timeout 1200 python scripts/decrypt_trials.py --arith torus --out gpurun_out/decrypt_trials_torus.json > gpurun_out/gate_torus.log 2>&1; echo "gate torus rc=$?"; tail -1 gpurun_out/gate_torus.log | cut -c1-600
           timeout 1200 python scripts/decrypt_trials.py --arith goldilocks --out gpurun_out/decrypt_trials_goldilocks.json > gpurun_out/gate_gold.log 2>&1; echo "gate goldilocks rc=$?";;
     radix) timeout 900 python scripts/bench_radix.py ${RADIX_ARGS:-} > gpurun_out/bench_radix.jsonl 2> gpurun_out/bench_radix.err; echo "radix rc=$?"; tail -3 gpurun_out/bench_radix.err; cut -c1-300 gpurun_out/bench_radix.jsonl;;
+    ks) timeout 240 python -m pytest tests/test_gpu_torus.py tests/test_gpu_parity.py -m gpu -x -q -k "keyswitch" > gpurun_out/pytest_ks.log 2>&1; echo "pytest ks rc=$? $(tail -3 gpurun_out/pytest_ks.log)"
+        timeout 240 python scripts/ks_probe.py torus > gpurun_out/ks_probe.txt 2>&1; echo "ks probe rc=$?"; tail -12 gpurun_out/ks_probe.txt;;
     latency) timeout 300 python scripts/latency_probe.py > gpurun_out/latency_probe.txt 2>&1; echo "latency rc=$?"; tail -8 gpurun_out/latency_probe.txt;;
     ubench) (cd scripts/ubench && nvcc -O3 -std=c++17 -gencode arch=compute_100a,code=sm_100a -o /tmp/ubench_arith ubench_arith.cu && /tmp/ubench_arith) > gpurun_out/arith_ubench.txt 2>&1; echo "ubench rc=$?";;
     *) echo "unknown stage $stage";;

@@ -270,6 +270,30 @@ def test_lwe_keyswitch_tensor_core_form(rig_s2, rig_small1, B):
         assert np.array_equal(r.eng.lwe_keyswitch(cts), got)   # automatic dispatch takes the tensor-core form
 
 
+@pytest.mark.parametrize("B", [1, 129, 300])
+def test_lwe_keyswitch_tcgen05_form(rig_s2, rig_small1, B):
+    """tcgen05.mma.kind::i8 kernel (ks_tc5.cuh) on the Goldilocks words: equal to the mma.sync kernel, the integer-pipe kernel
+    and the oracle"""
+    for r in (rig_s2, rig_small1):
+        rng = O.Rng(41 + B)
+        cts = np.stack([rng.field(r.p.N + 1) for _ in range(B)])
+        cts[0, :14] = edge_values()
+        cts[B - 1, -14:] = edge_values()
+        try:
+            r.eng.ks_mode(2)
+            got = r.eng.lwe_keyswitch(cts)
+            r.eng.ks_mode(1)
+            ref = r.eng.lwe_keyswitch(cts)
+            r.eng.ks_mode(0)
+            ref0 = r.eng.lwe_keyswitch(cts)
+        finally:
+            r.eng.ks_mode(-1)
+        assert np.array_equal(got, ref)
+        assert np.array_equal(got, ref0)
+        for b in sorted({0, B // 2, B - 1}):
+            assert np.array_equal(got[b], r.ctx.lwe_keyswitch(cts[b])), b
+
+
 # ---------------------------------------------------------------------------------------------- whole PBS
 def _pbs_case(r: Rig, B: int, p: int, luts, seed: int, sigma: float, check: int):
     rng = O.Rng(seed)

@@ -131,6 +131,31 @@ def test_lwe_keyswitch_vs_oracle(rig_small):
         assert np.array_equal(got, want), B
 
 
+@pytest.mark.parametrize("which", ["small", "s2"])
+def test_lwe_keyswitch_tcgen05_form(rig_small, rig_s2, which):
+    """tcgen05.mma.kind::i8 kernel with tensor-memory accumulators (ks_tc5.cuh): the same words as the mma.sync kernel and
+    the oracle, on ragged batches (against the 128-row tile, one and several tiles per CTA) and on edge-value masks"""
+    r = rig_small if which == "small" else rig_s2
+    e, p = r.eng, r.p
+    rs = np.random.RandomState(31)
+    for B in ((1, 129, 300, 1500) if which == "small" else (1, 129, 1400)):   # 1400 at the named set: 319 tiles, three per CTA on some SMs
+        cts = u64_rand(rs, (B, p.k * p.N + 1))
+        cts[0, :6] = np.array([0, 1, 2**63, 2**63 - 1, 2**64 - 1, 2**59], np.uint64)
+        cts[B - 1, -7:-1] = np.array([2**64 - 1, 2**63 + 1, 2**60 - 1, 2**60, 7, 0], np.uint64)
+        try:
+            e.ks_mode(2)
+            got = e.lwe_keyswitch(cts)
+            again = e.lwe_keyswitch(cts)
+            e.ks_mode(1)
+            ref = e.lwe_keyswitch(cts)
+        finally:
+            e.ks_mode(-1)
+        assert np.array_equal(got, ref), B
+        assert np.array_equal(again, ref), B
+        for b in sorted({0, B // 2, B - 1}):
+            assert np.array_equal(got[b], r.ctx.lwe_keyswitch(cts[b])), (B, b)
+
+
 # ------------------------------------------------------------------------------------------- blind rotation
 @pytest.mark.parametrize("steps", [0, 1, 2, 5, None])
 def test_blind_rotate_per_iteration_bit_exact(rig_small, steps):

@@ -3,6 +3,7 @@
 // launches CUDA kernels, and lux_engine_create fails without a device.
 #include "engine.h"
 #include "ks_mma.cuh"
+#include "ks_tc5.cuh"
 
 #include <algorithm>
 #include <cstdio>
@@ -247,14 +248,24 @@ static int derive_ksk_bytes(lux_engine *e) {
     ksmma::ks_bytes_transpose_kernel<<<e->sm_count * 16, 256, 0, e->stream>>>(e->d_lksk, e->d_kskT, K, cols, e->ks_npad);
     e->launches++;
     CUDA_TRY(e, cudaGetLastError());
+    // the tcgen05 form reads the same planes as 256 x 128 stage tiles in the tensor core's shared-memory image
+    e->ks_npad5 = (8 * cols + kstc5::BN - 1) / kstc5::BN * kstc5::BN;
+    if (!e->d_kskT5) {
+        cudaError_t st = cudaMalloc(&e->d_kskT5, (size_t)e->ks_npad5 * K);
+        if (st != cudaSuccess) LUX_FAIL(e, LUX_ERR_OOM, "cudaMalloc(%zu) for key switch stage tiles: %s", (size_t)e->ks_npad5 * K, cudaGetErrorString(st));
+    }
+    kstc5::ks_bytes_tiled_kernel<<<e->sm_count * 16, 256, 0, e->stream>>>(e->d_lksk, e->d_kskT5, K, cols, e->ks_npad5);
+    e->launches++;
+    CUDA_TRY(e, cudaGetLastError());
     return LUX_OK;
 }
 
-static int launch_ks_mma(lux_engine *e, const u64 *d_in, u64 *d_out, size_t B, cudaStream_t s) {
+static int launch_ks_mma(lux_engine *e, const u64 *d_in, u64 *d_out, size_t B, cudaStream_t s, bool tc5) {
     const lux_params &p = e->p;
     const u32 kN = p.k * p.N, K = kN * p.ell_ks;
     const u32 mpad = (u32)((B + ksmma::BM - 1) / ksmma::BM * ksmma::BM);
     const size_t need = (size_t)mpad * K;
+    static_assert(ksmma::BM == kstc5::BM && ksmma::BK == kstc5::BK, "both forms pad the batch and K alike");
     if (e->ks_dig_bytes < need) {
         if (e->d_ks_dig) cudaFree(e->d_ks_dig);
         e->d_ks_dig = nullptr;
@@ -267,7 +278,19 @@ static int launch_ks_mma(lux_engine *e, const u64 *d_in, u64 *d_out, size_t B, c
     static bool configured[64] = {};
     if (!configured[e->device & 63]) {
         CUDA_TRY(e, cudaFuncSetAttribute(ksmma::lwe_keyswitch_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ksmma::SMEM_BYTES));
+        CUDA_TRY(e, cudaFuncSetAttribute(kstc5::lwe_keyswitch_tc5_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kstc5::SMEM_BYTES));
         configured[e->device & 63] = true;
+    }
+    if (tc5) {
+        kstc5::ks_digits_tiled_kernel<<<e->sm_count * 8, 256, 0, s>>>(d_in, e->d_ks_dig, (u32)B, mpad, kN, p.ell_ks, p.logB_ks, e->L_ks, lux_is_torus(e) ? 1u : 0u);
+        e->launches++;
+        CUDA_TRY(e, cudaGetLastError());
+        kstc5::Args a{e->d_ks_dig, e->d_kskT5, d_in, d_out, (u32)B, p.n, kN, K, lux_is_torus(e) ? 1u : 0u, mpad / kstc5::BM, e->ks_npad5 / kstc5::BN};
+        const u32 tiles = a.mtiles * a.ntiles;
+        kstc5::lwe_keyswitch_tc5_kernel<<<std::min<u32>(tiles, (u32)e->sm_count), kstc5::THREADS, kstc5::SMEM_BYTES, s>>>(a);
+        e->launches++;
+        CUDA_TRY(e, cudaGetLastError());
+        return LUX_OK;
     }
     ksmma::ks_digits_kernel<<<e->sm_count * 8, 256, 0, s>>>(d_in, e->d_ks_dig, (u32)B, mpad, kN, p.ell_ks, p.logB_ks, e->L_ks, lux_is_torus(e) ? 1u : 0u);
     e->launches++;
@@ -282,9 +305,11 @@ static int launch_ks_mma(lux_engine *e, const u64 *d_in, u64 *d_out, size_t B, c
 
 static int launch_ks(lux_engine *e, const u64 *d_in, u64 *d_out, size_t B, cudaStream_t s) {
     const lux_params &p = e->p;
-    // the tensor-core form is faster at every batch size (profiles/r01e_ks_probe.txt: 0.07 ms against 0.17 ms for one
-    // ciphertext, 0.075 against 4.2 ms for 148); the integer-pipe kernel below serves parameter sets it cannot take
-    if (e->d_kskT && (e->ks_mode != 0 || lux_is_torus(e))) return launch_ks_mma(e, d_in, d_out, B, s);
+    // the tensor-core forms are faster at every batch size (profiles/r01e_ks_probe.txt: 0.07 ms against 0.17 ms for one
+    // ciphertext, 0.075 against 4.2 ms for 148), and of the two the tcgen05 / tensor-memory kernel (ks_tc5.cuh) again at every
+    // batch size (profiles/r02e_ks_probe.txt: 0.039 against 0.075 ms for one ciphertext, 0.251 against 0.780 ms for 4,440);
+    // the integer-pipe kernel below serves parameter sets they cannot take
+    if (e->d_kskT && (e->ks_mode != 0 || lux_is_torus(e))) return launch_ks_mma(e, d_in, d_out, B, s, e->ks_mode != 1 && e->d_kskT5);
     if (lux_is_torus(e)) LUX_FAIL(e, LUX_ERR_INVALID, "torus arithmetic: key switch needs the tensor-core form (logB_ks <= 7)");
     KSArgs a{p.n, p.k * p.N, p.ell_ks, p.logB_ks, e->L_ks, (u32)B, e->d_lksk, e->d_ksum, d_in, d_out, 1, nullptr};
     const size_t smem = sizeof(u32) * KS_RC * p.ell_ks * KS_TB;
@@ -627,6 +652,7 @@ void lux_engine_destroy(lux_engine *e) {
         if (e->scratch[i]) cudaFree(e->scratch[i]);
     for (auto &kv : e->any_tables) cudaFree(kv.second);
     if (e->d_kskT) cudaFree(e->d_kskT);
+    if (e->d_kskT5) cudaFree(e->d_kskT5);
     if (e->d_ks_dig) cudaFree(e->d_ks_dig);
     if (e->d_fft_twB) cudaFree(e->d_fft_twB);
     if (e->d_fft_twFull) cudaFree(e->d_fft_twFull);
@@ -743,7 +769,7 @@ int lux_debug_generic_gadget(lux_engine *e, int on) {
 }
 int lux_debug_ks_mode(lux_engine *e, int mode) {
     LUX_LOCK(e);
-    if (!e || mode < -1 || mode > 1) return LUX_ERR_INVALID;
+    if (!e || mode < -1 || mode > 2) return LUX_ERR_INVALID;
     e->ks_mode = mode;
     return LUX_OK;
 }

@@ -48,7 +48,10 @@ struct lux_engine {
     u32 ks_npad = 0;          // rows of d_kskT = 8 * (n + 1) rounded up to the N tile
     int8_t *d_ks_dig = nullptr;  // grow-only [Mpad][K] digit buffer
     size_t ks_dig_bytes = 0;
-    int ks_mode = -1;         // -1 / 1 = tensor-core kernel whenever the parameter set is eligible, 0 = integer-pipe kernel only (tests)
+    int ks_mode = -1;         // -1 = automatic (tcgen05 kernel whenever the parameter set is eligible), 0 = integer-pipe
+                              // kernel only, 1 = mma.sync kernel, 2 = tcgen05 kernel (tests)
+    uint8_t *d_kskT5 = nullptr;  // the same byte planes cut into 256 x 128 swizzled stage tiles (ks_tc5.cuh)
+    u32 ks_npad5 = 0;
     int br_regs = 8;              // throughput blind rotate of the named gadgets: coefficients per thread (8 = narrow tile,
                                   // default; 16 = wide tile; 4: tuning).  Other gadgets always run the wide tile.
     int cluster_regs = 0;         // cluster latency mode: coefficients per thread, 0 = automatic, 16 / 8 / 4 pinned (tests, tuning)

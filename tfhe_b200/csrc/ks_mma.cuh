@@ -15,9 +15,8 @@
 //   dig  [Mpad][K]  s8, K contiguous   (ks_digits_kernel, per call; rows >= B are zero)
 //   kskT [Npad][K]  u8, K contiguous   (ks_bytes_transpose_kernel, once per key load; kskT[8c+byte][r] = byte of KSK[r][c])
 // Both are "K-major", i.e. the row.col form of mma.sync.m16n8k32 with plain (non-transposing) ldmatrix.
-// Legacy mma.sync is used on purpose: the contraction is 0.27 T MAC per 4,440-ciphertext batch, far below what
-// even the legacy IMMA path delivers in a millisecond, so a tcgen05/TMEM pipeline would buy nothing measurable
-// for 5 % of the step.
+// This is the mma.sync form: since round 2 the default is the tcgen05 / tensor-memory kernel in ks_tc5.cuh (3.1x faster at
+// B = 4,440); this one stays as its checker (lux_debug_ks_mode 1) and as the kernel of lux_pbs_batch_device_static.
 #pragma once
 #include "gl64.cuh"
 

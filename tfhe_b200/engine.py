@@ -403,8 +403,8 @@ class Engine:
         self._ck(lib().lux_debug_generic_gadget(self._h, int(bool(on))))
 
     def ks_mode(self, mode: int):
-        """LWE key switch kernel: -1 / 1 int8 tensor-core contraction whenever the parameter set is eligible (default),
-        0 integer-pipe kernel only"""
+        """LWE key switch kernel: -1 automatic (int8 tensor-core contraction whenever the parameter set is eligible),
+        0 integer-pipe kernel only, 1 mma.sync kernel (ks_mma.cuh), 2 tcgen05 / tensor-memory kernel (ks_tc5.cuh)"""
         self._ck(lib().lux_debug_ks_mode(self._h, mode))
 
     def fft_variant(self, v: int):
