@@ -12,6 +12,7 @@
 #   radix          scripts/bench_radix.py (C3-C5 op rates, single process)
 #   latency        scripts/latency_probe.py
 #   ubench         scripts/ubench/ubench_arith.cu
+#   ncu_ks         ncu --set full of the tcgen05 key switch at B=$NCU_B
 #   ks             key switch parity tests + scripts/ks_probe.py (mma.sync vs tcgen05 form)
 set -u
 mkdir -p gpurun_out
@@ -34,6 +35,7 @@ for stage in "$@"; do
     radix) timeout 900 python scripts/bench_radix.py ${RADIX_ARGS:-} > gpurun_out/bench_radix.jsonl 2> gpurun_out/bench_radix.err; echo "radix rc=$?"; tail -3 gpurun_out/bench_radix.err; cut -c1-300 gpurun_out/bench_radix.jsonl;;
     ks) timeout 240 python -m pytest tests/test_gpu_torus.py tests/test_gpu_parity.py -m gpu -x -q -k "keyswitch" > gpurun_out/pytest_ks.log 2>&1; echo "pytest ks rc=$? $(tail -3 gpurun_out/pytest_ks.log)"
         timeout 240 python scripts/ks_probe.py torus > gpurun_out/ks_probe.txt 2>&1; echo "ks probe rc=$?"; tail -12 gpurun_out/ks_probe.txt;;
+    ncu_ks) timeout 600 ncu --set full --import-source on --clock-control none -k regex:lwe_keyswitch_tc5 -s 2 -c 1 -f -o gpurun_out/ks_tc5_full python scripts/quick_torus.py $NCU_B 0 > gpurun_out/ncu_ks.log 2>&1; echo "ncu ks rc=$?";;
     latency) timeout 300 python scripts/latency_probe.py > gpurun_out/latency_probe.txt 2>&1; echo "latency rc=$?"; tail -8 gpurun_out/latency_probe.txt;;
     ubench) (cd scripts/ubench && nvcc -O3 -std=c++17 -gencode arch=compute_100a,code=sm_100a -o /tmp/ubench_arith ubench_arith.cu && /tmp/ubench_arith) > gpurun_out/arith_ubench.txt 2>&1; echo "ubench rc=$?";;
     *) echo "unknown stage $stage";;
