@@ -250,4 +250,4 @@ def test_shallow_rule_and_depths():
         assert len(shallow.levels) == nb.bit_length() - 1 + 2
         assert shallow.n_pbs > deep.n_pbs
     assert len(R.program(R.PROG_ERC20, 64, shallow=True).levels) == 8
-    assert len(R.program(R.PROG_ERC20, 64).levels) == 33
+    assert len(R.program(R.PROG_ERC20, 64).levels) == 6 + 1 + 32   # le, the one select, then the two chains side by side

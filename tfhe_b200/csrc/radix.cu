@@ -547,8 +547,18 @@ Program build_program(int op, unsigned bw, const Wide &scalar, bool shallow = fa
         const int from = b.add_input(nb), to = b.add_input(nb), amt = b.add_input(nb);
         const auto f = b.operand(from), t = b.operand(to), a = b.operand(amt);
         const Val ok = b.compare(a, f, PRED_LE);
-        b.output(b.select(ok, b.sub_blocks(f, a), f));
-        b.output(b.select(ok, b.add_blocks(t, a), t));
+        if (shallow) {   // few transfers: depth is the time.  The contract's form, call for call: both arithmetic chains
+                         // run beside the comparison and the selects come last (8 levels, 317 bootstraps)
+            b.output(b.select(ok, b.sub_blocks(f, a), f));
+            b.output(b.select(ok, b.add_blocks(t, a), t));
+        } else {         // many transfers: the count is the time.  select(ok, f - a, f) = f - select(ok, a, 0) and
+                         // select(ok, t + a, t) = t + select(ok, a, 0) for every input (mod 2^64): ONE select against the
+                         // constant 0 (one bootstrap per block) feeds both chains: 221 bootstraps, same plaintexts
+            const std::vector<Val> zero(nb, Builder::cst(0));
+            const auto moved = b.select(ok, a, zero);
+            b.output(b.sub_blocks(f, moved));
+            b.output(b.add_blocks(t, moved));
+        }
         return b.finish();
     }
     const int l = b.add_input(nb);
