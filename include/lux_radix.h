@@ -140,6 +140,10 @@ size_t lux_radix_program_scalar(int op, unsigned bit_width, const uint64_t *scal
                                 size_t cap);
 /* the 16-entry table of lookup table `lut_id`; returns the number of tables when out == NULL */
 int lux_radix_lut(int lut_id, uint64_t out[16]);
+/* 1 when table `lut_id` is a signed table: its circuits feed it x in (-16, 16) and rely on the negacyclic extension
+   T(x) = -T(x + 16) of the blind rotation for x < 0 (the padding bit is the sign bit); every other table is only ever fed
+   x in [0, 16).  Test infrastructure (the CPU interpreters of oracle/radix.py) needs it to mirror that rule. */
+int lux_radix_lut_signed(int lut_id);
 
 #ifdef __cplusplus
 }

@@ -26,9 +26,10 @@ def join_blocks(blocks) -> int:
     return sum(int(b) << (2 * i) for i, b in enumerate(blocks))
 
 
-def interp_plain(prog, luts, operands):
+def interp_plain(prog, luts, operands, signed=()):
     """operands: list of block lists (ints).  Returns list of output block lists.  Raises if a PBS input
-    leaves [0,16) (the padding bit would be hit)."""
+    leaves [0,16) (the padding bit would be hit) — except for the tables listed in `signed` (lux_radix_lut_signed),
+    which circuits feed with x in (-16, 16): a blind rotation is negacyclic, so x < 0 reads -T(x + 16)."""
     slots = {}
     s = 0
     for blocks in operands:
@@ -43,6 +44,9 @@ def interp_plain(prog, luts, operands):
         new = {}
         for lut, out, l in lv:
             x = lin(l)
+            if lut in signed and -BLOCK_P < x < 0:
+                new[out] = -int(luts[lut][x + BLOCK_P])
+                continue
             if not 0 <= x < BLOCK_P:
                 raise ValueError(f"PBS input {x} outside [0,16)")
             new[out] = int(luts[lut][x])

@@ -10,10 +10,15 @@ from pathlib import Path
 import pytest
 
 import tfhe_b200.radix as R
-from oracle.radix import interp_plain, join_blocks, split_blocks
+from oracle.radix import interp_plain as _interp_plain, join_blocks, split_blocks
 
 KATS = json.loads((Path(__file__).parent / "golden" / "fhevm_kats.json").read_text())
 LUTS = R.luts()
+SIGNED = R.signed_luts()   # tables fed with x in (-16, 16): lux_radix_lut_signed
+
+
+def interp_plain(prog, luts, operands):
+    return _interp_plain(prog, luts, operands, SIGNED)
 SUPPORTED = set(R.OPS)
 
 
@@ -166,6 +171,30 @@ def test_shallow_variants_match_plain_semantics(width):
             assert join_blocks(out[0]) == plain_semantics(op, a, b, width), (op, hex(a), hex(b))
 
 
+@pytest.mark.parametrize("op", ["lt", "le", "gt", "ge", "min", "max"])
+def test_ordering_on_block_pairs(op):
+    """the comparison reads TWO blocks per bootstrap through the signed table (difference in [-15, 15], padding bit = sign):
+    exhaustive at 2 / 4 / 6 bits (one block, one pair, a pair and a lone block), random and adjacent values at 10 / 64 / 256
+    bits, for both circuit variants"""
+    assert SIGNED and all(LUTS[i][0] == 0 for i in SIGNED)      # a signed table is odd: T(0) = 0
+    rnd = random.Random(11)
+    for width in (2, 4, 6, 10, 64, 256):
+        nb = width // 2
+        if width <= 6:
+            cases = [(a, b) for a in range(1 << width) for b in range(1 << width)]
+        else:
+            cases = [(rnd.randrange(1 << width), rnd.randrange(1 << width)) for _ in range(60)]
+            for _ in range(60):   # equal, adjacent, and differing in one block only
+                a = rnd.randrange(1, (1 << width) - 1)
+                k = rnd.randrange(nb)
+                cases += [(a, a), (a, a + 1), (a + 1, a), (a, a ^ (rnd.randrange(1, 4) << (2 * k)))]
+        for shallow in (False, True):
+            prog = R.program(op, width, shallow=shallow)
+            for a, b in cases:
+                out = interp_plain(prog, LUTS, [split_blocks(a, nb), split_blocks(b, nb)])
+                assert join_blocks(out[0]) == plain_semantics(op, a, b, width), (op, width, a, b)
+
+
 def test_shallow_erc20_vectors():
     prog, ref = R.program(R.PROG_ERC20, 64, shallow=True), R.program(R.PROG_ERC20, 64)
     assert len(prog.levels) <= 10 < len(ref.levels)
@@ -190,9 +219,9 @@ def test_pbs_counts_and_depths():
             assert len(p.levels) == R.depth(op, width)
     nb = 32
     assert R.pbs_count("add", 64) == 2 * nb - 1          # ripple: carry + message per block
-    assert R.pbs_count("lt", 64) == 2 * nb - 1           # signs + pairwise tree
+    assert R.pbs_count("lt", 64) == nb - 1               # signs of block PAIRS (signed table) + pairwise tree
     assert R.pbs_count("and", 64) == nb
-    assert R.depth("lt", 64) == 6
+    assert R.depth("lt", 64) == 5
     assert int(R.lib().lux_erc20_pbs_count()) == R.program(R.PROG_ERC20, 64).n_pbs
     assert R.pbs_count("mul", 64) < 2600
 
@@ -250,4 +279,4 @@ def test_shallow_rule_and_depths():
         assert len(shallow.levels) == nb.bit_length() - 1 + 2
         assert shallow.n_pbs > deep.n_pbs
     assert len(R.program(R.PROG_ERC20, 64, shallow=True).levels) == 8
-    assert len(R.program(R.PROG_ERC20, 64).levels) == 6 + 1 + 32   # le, the one select, then the two chains side by side
+    assert len(R.program(R.PROG_ERC20, 64).levels) == 5 + 1 + 32   # le, the one select, then the two chains side by side

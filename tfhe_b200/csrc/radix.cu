@@ -25,7 +25,9 @@
 namespace {
 
 // ------------------------------------------------------------------------------------ lookup tables
-// every table maps x in [0,16) (2 message + 2 carry bits) to [0,16); bivariate tables read x = 4*hi + lo
+// every table maps x in [0,16) (2 message + 2 carry bits) to [0,16); bivariate tables read x = 4*hi + lo.
+// A blind rotation is negacyclic: an input in (-16, 0) (padding bit set) reads -T(x + 16).  Tables marked signed
+// (lut_signed) are designed for that and may be fed x in (-16, 16); every other table must stay below the padding bit.
 enum { PRED_LT = 0, PRED_LE, PRED_GT, PRED_GE, PRED_EQ, PRED_NE, PRED_N };
 enum LutId {
     L_MSG = 0, L_CARRY, L_MUL_LO, L_MUL_HI, L_AND, L_OR, L_XOR, L_SEL_A, L_SEL_B, L_CMP, L_CMPRED, L_EQB,
@@ -35,8 +37,10 @@ enum LutId {
     L_PRED_RED0 = L_PRED_CMP0 + PRED_N, // + pred: pred(reduce(sign_hi, sign_lo))
     L_EQK0 = L_PRED_RED0 + PRED_N,      // + k: x == k
     L_NEK0 = L_EQK0 + 16,               // + k: x != k
-    L_COUNT = L_NEK0 + 16
+    L_SIGN2 = L_NEK0 + 16,              // signed: sign(x) in {-1, 0, 1} for x in (-16, 16): T(0) = 0, T(1..15) = 1
+    L_COUNT
 };
+bool lut_signed(int id) { return id == L_SIGN2; }
 
 int sign3(int a, int b) { return a < b ? 0 : (a == b ? 1 : 2); }
 int cmpred(int x) {
@@ -54,8 +58,10 @@ int pred_of_sign(int pred, int s) {
     }
 }
 int lut_eval(int id, int x) {
+    if (x < 0) return -lut_eval(id, x + 16);   // the negacyclic extension (signed tables only: Builder::pbs checks)
     const int hi = x >> 2, lo = x & 3;
     switch (id) {
+        case L_SIGN2: return x != 0;
         case L_MSG: return x & 3;
         case L_CARRY: return x >> 2;
         case L_MUL_LO: return (hi * lo) & 3;
@@ -225,9 +231,9 @@ struct Builder {
     static Val pack(const Val &hi, const Val &lo) { return add(scale(hi, 4), lo); }  // bivariate input 4*hi + lo
 
     Val pbs(const Val &v, int lut) {
-        if (v.lo < 0 || v.hi > 15) throw std::logic_error("radix circuit: PBS input out of [0,15]");
+        if (v.lo < (lut_signed(lut) ? -15 : 0) || v.hi > 15) throw std::logic_error("radix circuit: PBS input out of range");
         if (v.t.empty()) return cst(lut_eval(lut, (int)v.k));
-        long lo = 15, hi = 0;
+        long lo = 15, hi = -15;
         for (long x = v.lo; x <= v.hi; x++) {
             lo = std::min<long>(lo, lut_eval(lut, (int)x));
             hi = std::max<long>(hi, lut_eval(lut, (int)x));
@@ -365,17 +371,26 @@ struct Builder {
         return ripple(cols);
     }
     // ordering predicates: per-block signs, pairwise tree, predicate folded into the last table
+    // First level: TWO blocks per bootstrap.  The difference 4 (a1 - b1) + (a0 - b0) of a pair of blocks is linear and lies
+    // in [-15, 15]; the signed table L_SIGN2 returns its sign through the negacyclic extension (the padding bit is the sign
+    // bit), +1 turns it into the 0 / 1 / 2 = less / equal / greater code of L_CMP.  nb / 2 + (nb / 2 - 1) bootstraps
+    // instead of nb + (nb - 1).
     Val compare(const std::vector<Val> &a, const std::vector<Val> &b, int pred) {
         const int nb = (int)a.size();
         if (nb == 1) return pbs(pack(a[0], b[0]), L_PRED_CMP0 + pred);
-        std::vector<Val> s(nb);
-        for (int i = 0; i < nb; i++) s[i] = pbs(pack(a[i], b[i]), L_CMP);
+        std::vector<Val> s;
+        for (int i = 0; i + 1 < nb; i += 2) {
+            const Val d = add(scale(sub(assume(a[i + 1], 0, 3), assume(b[i + 1], 0, 3)), 4), sub(assume(a[i], 0, 3), assume(b[i], 0, 3)));
+            s.push_back(assume(add(pbs(d, L_SIGN2), cst(1)), 0, 2));
+        }
+        if (nb & 1) s.push_back(pbs(pack(a[nb - 1], b[nb - 1]), L_CMP));
         while (s.size() > 2) {
             std::vector<Val> n;
             for (size_t i = 0; i + 1 < s.size(); i += 2) n.push_back(pbs(pack(s[i + 1], s[i]), L_CMPRED));
             if (s.size() & 1) n.push_back(s.back());
             s.swap(n);
         }
+        if (s.size() == 1) return pbs(pack(cst(1), s[0]), L_PRED_RED0 + pred);   // "upper part equal": the sign of the one pair decides
         return pbs(pack(s[1], s[0]), L_PRED_RED0 + pred);
     }
     Val equal(const std::vector<Val> &a, const std::vector<Val> &b, bool negate) {
@@ -1167,5 +1182,6 @@ int lux_radix_lut(int lut_id, uint64_t out[16]) {
     for (int x = 0; x < 16; x++) out[x] = (uint64_t)lut_eval(lut_id, x);
     return LUX_OK;
 }
+int lux_radix_lut_signed(int lut_id) { return lut_id >= 0 && lut_id < L_COUNT && lut_signed(lut_id) ? 1 : 0; }
 
 }  // extern "C"

@@ -53,6 +53,7 @@ ABI = {
     "lux_multi_erc20_transfer": (_int, [_vp, _vp, _vp, _vp, _sz, _vp, _vp]),
     "lux_radix_program": (_sz, [_int, _uint, _vp, _sz]),
     "lux_radix_lut": (_int, [_int, _vp]),
+    "lux_radix_lut_signed": (_int, [_int]),
 }
 _bound = False
 
@@ -161,6 +162,11 @@ def luts() -> np.ndarray:
         rc = lib().lux_radix_lut(i, t[i].ctypes.data)
         assert rc == 0
     return t
+
+
+def signed_luts() -> set:
+    """ids of the tables that circuits feed with x in (-16, 16) (negacyclic extension T(x) = -T(x + 16))"""
+    return {i for i in range(lib().lux_radix_lut(0, None)) if lib().lux_radix_lut_signed(i)}
 
 
 # ---- evaluation -------------------------------------------------------------------------------------
