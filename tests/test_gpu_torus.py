@@ -320,6 +320,35 @@ def test_pbs_s2_bench_batch_random_indices(rig_s2):
     assert np.array_equal(got[pick], want)
 
 
+def test_pbs_s2_whole_waves_plus_tail_launch(rig_s2):
+    """a batch that is not a whole number of waves runs as whole waves (four ciphertexts per CTA) + a tail launch of its own
+    (latency kernel up to 148 ciphertexts, two per CTA up to 296, three up to 444): same words as the single launch, and the
+    ciphertexts either side of the cut, the lookup-table indices included, bit-exact vs the oracle"""
+    e, p = rig_s2.eng, rig_s2.p
+    rs = np.random.RandomState(44)
+    wave = 4 * 148
+    for tail in (1, 100, 250, 420):
+        B = wave + tail
+        cts = u64_rand(rs, (B, p.ct_len))
+        tvs = u64_rand(rs, (4, p.N))
+        idx = rs.randint(0, 4, B).astype(np.uint32)
+        n0 = e.launch_count
+        got = e.pbs_batch(cts, tvs, idx)
+        n_split = e.launch_count - n0
+        try:
+            e.fft_tail_split(False)
+            n0 = e.launch_count
+            one = e.pbs_batch(cts, tvs, idx)
+            n_one = e.launch_count - n0
+        finally:
+            e.fft_tail_split(True)
+        assert n_split == n_one + 1, (tail, n_split, n_one)       # the tail really was a launch of its own
+        assert np.array_equal(got, one), tail
+        pick = np.unique([0, wave - 1, wave, B - 1, wave + tail // 2])
+        want, _ = rig_s2.ctx.pbs_batch(cts[pick], tvs, idx[pick])
+        assert np.array_equal(got[pick], want), tail
+
+
 # ------------------------------------------------------------------------------------------- the decryption gate
 @pytest.mark.parametrize("arith", ["torus", "goldilocks"])
 def test_decryption_gate_65536_trials(arith):

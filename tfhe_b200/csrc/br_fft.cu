@@ -40,7 +40,7 @@ static int launch_lat(lux_engine *e, const LatArgs &la, cudaStream_t s) {
         CUDA_TRY(e, cudaFuncSetAttribute(blind_rotate_fft_lat_kernel<V>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LAT_SMEM));
         configured[e->device & 63] = true;
     }
-    blind_rotate_fft_lat_kernel<V><<<la.a.B, LAT_THREADS, LAT_SMEM, s>>>(la);
+    blind_rotate_fft_lat_kernel<V><<<la.a.B - la.a.ct0, LAT_THREADS, LAT_SMEM, s>>>(la);
     e->launches++;
     CUDA_TRY(e, cudaGetLastError());
     return LUX_OK;
@@ -131,7 +131,7 @@ static int launch_cfg(lux_engine *e, const Args &a, cudaStream_t s) {
         CUDA_TRY(e, cudaFuncSetAttribute(blind_rotate_fft_kernel<TEAMS, NS, RS, TWS, HB, GROUPS, KL, MK, LAG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM));
         configured[e->device & 63] = true;
     }
-    const unsigned grid = (a.B + TEAMS - 1) / TEAMS;
+    const unsigned grid = (a.B - a.ct0 + TEAMS - 1) / TEAMS;
     blind_rotate_fft_kernel<TEAMS, NS, RS, TWS, HB, GROUPS, KL, MK, LAG><<<grid, C::THREADS, C::SMEM, s>>>(a);
     e->launches++;
     CUDA_TRY(e, cudaGetLastError());
@@ -152,14 +152,13 @@ static int pick_teams(const lux_engine *e, size_t B) {
 
 size_t lux_fft_wave(const lux_engine *e, size_t B) { return (size_t)e->sm_count * pick_teams(e, B); }
 
+// one launch over the ciphertexts [a.ct0, a.B)
 // template arguments: <teams, ring stages, key rows per stage, twiddles in shared memory, half-size buffers, groups, no ring>
-int lux_fft_launch_br(lux_engine *e, Args a, cudaStream_t s) {
-    fill_tables(e, a);
-    a.stagger_ns = (u32)e->fft_stagger_ns;
-    a.trace = (u64 *)e->d_fft_trace;
+static int launch_br_range(lux_engine *e, Args a, cudaStream_t s) {
+    const u32 count = a.B - a.ct0;
     const int variant = e->fft_variant;   // 0 = the default of each team count; the others are the measured alternatives
     // a batch that leaves SMs idle anyway: one ciphertext per CTA, eight warps per ciphertext (fft64_lat.cuh)
-    if ((e->fft_lat_mode == 1 || (e->fft_lat_mode < 0 && e->force_teams == 0 && a.B <= (u32)e->sm_count)) && a.B > 0) {
+    if ((e->fft_lat_mode == 1 || (e->fft_lat_mode < 0 && e->force_teams == 0 && count <= (u32)e->sm_count)) && count > 0) {
         LatArgs la{a, (const double2 *)e->d_fft_twFull};
         switch (variant) {   // measured alternatives (scripts/quick_torus.py, cfg = 10 x variant)
             case 1: return launch_lat<1>(e, la, s);
@@ -169,7 +168,9 @@ int lux_fft_launch_br(lux_engine *e, Args a, cudaStream_t s) {
             default: return launch_lat<0>(e, la, s);
         }
     }
-    switch (pick_teams(e, a.B)) {
+    const int teams = pick_teams(e, count);
+    if (teams >= 4 && a.ct0 != 0) LUX_FAIL(e, LUX_ERR_INVALID, "internal: the four-per-CTA kernel starts at ciphertext 0");
+    switch (teams) {
         case 1:   // a warp alone on its scheduler: free instruction schedule (no phase marks)
             if (variant == 1) return launch_cfg<1, 4, 8, 1>(e, a, s);
             return launch_cfg<1, 4, 8, 1, 0, 1, 0, 0>(e, a, s);
@@ -215,6 +216,40 @@ int lux_fft_launch_br(lux_engine *e, Args a, cudaStream_t s) {
             if (variant == 19) return launch_cfg<4, 4, 4, 0, 1, 1, 4, 1 | (386 << 8)>(e, a, s);       // consumer-fed ring, marks 1, 7, 8 out
             return launch_cfg<4, 4, 4, 0, 1, 1, 0, 1 | (386 << 8)>(e, a, s);  // ring 4 x 8 KiB, twiddles through L1, marks 1, 7, 8 left out
     }
+}
+
+// Cycles per CMUX iteration of a CTA by ciphertexts per CTA (profiles/r02b_fft_phase_cycles.txt, r02c_latency.txt, r02d):
+// latency kernel 8.2k (one per CTA, up to #SMs ciphertexts), 2 -> 15.3k, 3 -> 18.6k, 4 -> 21.5k.
+static double range_cost(const lux_engine *e, size_t count) {
+    const size_t sms = (size_t)e->sm_count;
+    if (count == 0) return 0.0;
+    if (count <= sms) return 8.2;
+    if (count <= 2 * sms) return 15.3;
+    const double c3 = (double)((count + 3 * sms - 1) / (3 * sms)) * 18.6, c4 = (double)((count + 4 * sms - 1) / (4 * sms)) * 21.5;
+    return c3 < c4 ? c3 : c4;
+}
+
+// A batch that is not a whole number of waves: the whole waves run four ciphertexts per CTA, the rest runs as a launch of its
+// own with the kernel that suits ITS size (a level of a radix circuit is nodes x integers ciphertexts, rarely a multiple of
+// 592; 5,000 = 8 waves + 264, and 264 ciphertexts on 132 CTAs of two finish in 15.3k cycles per iteration instead of 21.5k).
+// Same words either way: every kernel computes a ciphertext independently of its neighbours.
+int lux_fft_launch_br(lux_engine *e, Args a, cudaStream_t s) {
+    fill_tables(e, a);
+    a.stagger_ns = (u32)e->fft_stagger_ns;
+    a.trace = (u64 *)e->d_fft_trace;
+    const size_t count = a.B - a.ct0, wave4 = (size_t)4 * e->sm_count;
+    if (e->fft_tail_split && e->force_teams == 0 && e->fft_variant == 0 && e->fft_lat_mode < 0 && count > wave4 && count % wave4) {
+        const size_t tail = count % wave4, full = count / wave4;
+        if ((double)full * 21.5 + range_cost(e, tail) < range_cost(e, count)) {
+            Args m = a, t = a;
+            m.B = a.ct0 + (u32)(count - tail);
+            t.ct0 = m.B;
+            int rc = launch_br_range(e, m, s);
+            if (rc) return rc;
+            return launch_br_range(e, t, s);
+        }
+    }
+    return launch_br_range(e, a, s);
 }
 
 int lux_fft_key_convert(lux_engine *e, const u64 *d_src, void *d_dst, size_t n_polys, cudaStream_t s) {

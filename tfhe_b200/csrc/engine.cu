@@ -735,6 +735,12 @@ int lux_debug_fft_lat_mode(lux_engine *e, int mode) {
     e->fft_lat_mode = mode;
     return LUX_OK;
 }
+int lux_debug_fft_tail_split(lux_engine *e, int on) {
+    LUX_LOCK(e);
+    if (!e) return LUX_ERR_INVALID;
+    e->fft_tail_split = on != 0;
+    return LUX_OK;
+}
 int lux_debug_fft_stagger(lux_engine *e, int ns) {
     LUX_LOCK(e);
     if (!e || ns < 0) return LUX_ERR_INVALID;

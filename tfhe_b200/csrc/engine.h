@@ -65,6 +65,7 @@ struct lux_engine {
     void *d_fft_twFull = nullptr;   // whole twiddle tree (latency kernel)
     int fft_lat_mode = -1;          // -1 = latency kernel when B <= #SMs, 0 = never, 1 = always (tests)
     int fft_default_teams = 3;
+    int fft_tail_split = 1;         // cut a batch into whole waves + a tail launch of its own (br_fft.cu); 0 = one launch (tests, A/B)
     void *d_fft_trace = nullptr;  // 16 phase-cycle counters (FFT64_TRACE_BUILD builds; lux_debug_fft_trace)
     int fft_stagger_ns = 6000;    // start delay between the groups of a CTA (kernels with GROUPS > 1)
     int fft_variant = 0;          // tuning: ring depth / twiddle placement of the 3-ciphertext kernel (br_fft.cu)
@@ -89,6 +90,7 @@ extern "C" int lux_debug_br_regs(lux_engine *e, int regs);
 extern "C" int lux_debug_fft_variant(lux_engine *e, int variant);
 extern "C" int lux_debug_fft_stagger(lux_engine *e, int ns);
 extern "C" int lux_debug_fft_lat_mode(lux_engine *e, int mode);
+extern "C" int lux_debug_fft_tail_split(lux_engine *e, int on);
 extern "C" int lux_debug_fft_trace(lux_engine *e, unsigned long long out[16]);
 extern "C" int lux_debug_int_peak(lux_engine *e, double out[3]);
 extern "C" int lux_debug_field_probe(lux_engine *e, const uint64_t *a, const uint64_t *b, size_t count, uint64_t *out);

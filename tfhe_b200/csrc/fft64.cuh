@@ -52,6 +52,10 @@ struct Args {
     u32 stagger_ns;         // GROUPS > 1: start delay of group g is g * stagger_ns
     u64 *trace;             // phase-cycle counters (FFT64_TRACE_BUILD) or nullptr
     double2 twA[32];        // tree nodes 1..31: the warp-uniform twiddles of pass A
+    u32 ct0;                // first ciphertext of THIS launch; B is one past its last.  A batch may be cut into a run of whole
+                            // waves and a tail with fewer ciphertexts per CTA (br_fft.cu lux_fft_launch_br): only the kernels a
+                            // tail can take (latency kernel, one to three ciphertexts per CTA) read it; the four-per-CTA kernel
+                            // always starts at ciphertext 0 and is compiled exactly as before (last member for the same reason)
 };
 
 // ------------------------------------------------------------------------------------------ scalars
@@ -727,7 +731,7 @@ __device__ __forceinline__ void blind_rotate_body(const Args &a, unsigned char *
     u64 *full_all = (u64 *)(ring_all + (size_t)GROUPS * NS * C::STAGE_POINTS);
     u64 *empty_all = full_all + GROUPS * NS;
 
-    const u32 first_ct = blockIdx.x * TEAMS;
+    const u32 first_ct = (TEAMS < 4 ? a.ct0 : 0u) + blockIdx.x * TEAMS;
     const u32 left = a.B - first_ct;
     const u32 live_teams = left < (u32)TEAMS ? left : (u32)TEAMS;
     if (TWS)

@@ -79,7 +79,7 @@ __device__ __forceinline__ void blind_rotate_lat_body(const LatArgs &la, unsigne
     double2 *b0 = bufs + (size_t)(r * 3 + 0) * LAT_PAD_POINTS, *b1 = bufs + (size_t)(r * 3 + 1) * LAT_PAD_POINTS,
             *bx = bufs + (size_t)(r * 3 + 2) * LAT_PAD_POINTS;
     const double2 *bx0 = bufs + (size_t)2 * LAT_PAD_POINTS, *bx1 = bufs + (size_t)5 * LAT_PAD_POINTS;
-    const u32 ct = blockIdx.x;
+    const u32 ct = a.ct0 + blockIdx.x;
     u64 *acc = acc_all + (size_t)r * N;
     const u64 *lwe = a.lwe + (size_t)ct * (a.n + 1);
     const u64 *tv = a.testv + (size_t)(a.lut_idx ? a.lut_idx[ct / a.lut_div] : 0) * N;

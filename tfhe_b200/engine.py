@@ -423,6 +423,12 @@ class Engine:
         lib().lux_debug_fft_lat_mode.argtypes = [_vp, _int]
         self._ck(lib().lux_debug_fft_lat_mode(self._h, mode))
 
+    def fft_tail_split(self, on: bool):
+        """torus blind rotation of a batch that is not a whole number of waves: whole waves + a tail launch of its own
+        (default) or one launch (A/B, tests)"""
+        lib().lux_debug_fft_tail_split.argtypes = [_vp, _int]
+        self._ck(lib().lux_debug_fft_tail_split(self._h, int(bool(on))))
+
     def fft_stagger(self, ns: int):
         lib().lux_debug_fft_stagger.argtypes = [_vp, _int]
         self._ck(lib().lux_debug_fft_stagger(self._h, ns))
