@@ -134,6 +134,8 @@ int lux_radix_set_pool_bytes(lux_engine *e, size_t bytes);
  * levels instead of `blocks`, ~3.5x the bootstraps), which lux_eval* / lux_erc20_transfer* run on their own when
  * batch * blocks <= 296, i.e. while a level fits the latency-mode kernels and depth is what costs time */
 #define LUX_PROG_SHALLOW 0x1000
+/* op | LUX_PROG_NODUAL: the variant without dual tables (see lux_radix_lut_dual) */
+#define LUX_PROG_NODUAL 0x2000
 size_t lux_radix_program(int op, unsigned bit_width, int64_t *buf, size_t cap);
 /* the divisor-specific circuit of LUX_OP_DIV / LUX_OP_REM (other ops: same as lux_radix_program) */
 size_t lux_radix_program_scalar(int op, unsigned bit_width, const uint64_t *scalar_limbs, size_t n_limbs, int64_t *buf,
@@ -144,6 +146,10 @@ int lux_radix_lut(int lut_id, uint64_t out[16]);
    T(x) = -T(x + 16) of the blind rotation for x < 0 (the padding bit is the sign bit); every other table is only ever fed
    x in [0, 16).  Test infrastructure (the CPU interpreters of oracle/radix.py) needs it to mirror that rule. */
 int lux_radix_lut_signed(int lut_id);
+/* 1 when table `lut_id` is a dual table (many-LUT bootstrap): its node has TWO output slots, out and out + 1, read from ONE
+   blind rotation at coefficient 0 and at coefficient N/16 of the accumulator, i.e. T(x) and T(x + 1) for the (even) input x.
+   Programs with such nodes run on engines of order LUX_ORDER_LWEKS_PBS; the others take the LUX_PROG_NODUAL variant. */
+int lux_radix_lut_dual(int lut_id);
 
 #ifdef __cplusplus
 }

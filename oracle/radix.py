@@ -26,10 +26,11 @@ def join_blocks(blocks) -> int:
     return sum(int(b) << (2 * i) for i, b in enumerate(blocks))
 
 
-def interp_plain(prog, luts, operands, signed=()):
+def interp_plain(prog, luts, operands, signed=(), dual=()):
     """operands: list of block lists (ints).  Returns list of output block lists.  Raises if a PBS input
     leaves [0,16) (the padding bit would be hit) — except for the tables listed in `signed` (lux_radix_lut_signed),
-    which circuits feed with x in (-16, 16): a blind rotation is negacyclic, so x < 0 reads -T(x + 16)."""
+    which circuits feed with x in (-16, 16): a blind rotation is negacyclic, so x < 0 reads -T(x + 16).
+    Tables listed in `dual` (lux_radix_lut_dual) write two slots from one bootstrap: T(x) to `out`, T(x + 1) to `out + 1`."""
     slots = {}
     s = 0
     for blocks in operands:
@@ -50,6 +51,10 @@ def interp_plain(prog, luts, operands, signed=()):
             if not 0 <= x < BLOCK_P:
                 raise ValueError(f"PBS input {x} outside [0,16)")
             new[out] = int(luts[lut][x])
+            if lut in dual:
+                if x & 1:
+                    raise ValueError(f"dual table read at odd input {x}")
+                new[out + 1] = int(luts[lut][x + 1])
         slots.update(new)
     return [[lin(l) for l in o] for o in prog.outs]
 
@@ -59,9 +64,23 @@ def _fmul_small(a: np.ndarray, c: int) -> np.ndarray:
     return ((a.astype(object) * c) % Q).astype(np.uint64)
 
 
-def interp_cipher(ctx, prog, luts, operands, testv_lut, delta, modulus=Q):
+def sample_extract(acc, c: int, modulus: int):
+    """LWE sample of coefficient c of the accumulator (mask | body), crypto/glwe.rs:96-106 generalised from c = 0:
+    a'_p = mask[c - p] for p <= c, -mask[N + c - p] for p > c; b' = body[c]"""
+    N = acc.shape[0] // 2
+    mask, body = acc[:N].astype(object), acc[N:].astype(object)
+    out = np.empty(N + 1, dtype=object)
+    for p in range(N):
+        out[p] = mask[c - p] if p <= c else (modulus - mask[N + c - p]) % modulus
+    out[N] = body[c]
+    return out.astype(np.uint64)
+
+
+def interp_cipher(ctx, prog, luts, operands, testv_lut, delta, modulus=Q, dual=()):
     """operands: list of arrays [B][blocks][w] (uint64).  ctx: oracle Ctx (oracle.Ctx or oracle.torus.Ctx) with keys
     installed; modulus = Q (Goldilocks) or 2**64 (torus).  testv_lut(lut_row) -> test vector polynomial.
+    A level that holds a table listed in `dual` is evaluated the way the executor does it: key switch, blind rotation to the
+    raw accumulator, then one sample extraction per output (coefficient 0, and N/16 for the second output of a dual table).
     Returns list of arrays [B][out_blocks][w]."""
     B = operands[0].shape[0]
     w = operands[0].shape[2]
@@ -84,6 +103,16 @@ def interp_cipher(ctx, prog, luts, operands, testv_lut, delta, modulus=Q):
         if not lv:
             continue
         x = np.concatenate([lin(l) for _, _, l in lv]).astype(np.uint64)           # slot-major, like the GPU
+        if any(lut in dual for lut, _, _ in lv):
+            if getattr(ctx.p, "order", 1) != 1:
+                raise ValueError("dual tables: key-switch-first order only (take the program variant with dual=False)")
+            N = tvs.shape[1]
+            for j, (lut, out, _) in enumerate(lv):
+                accs = [ctx.blind_rotate(ctx.lwe_keyswitch(x[j * B + b]), tvs[lut]) for b in range(B)]
+                slots[out] = np.stack([sample_extract(a, 0, modulus) for a in accs]).astype(object)
+                if lut in dual:
+                    slots[out + 1] = np.stack([sample_extract(a, N // BLOCK_P, modulus) for a in accs]).astype(object)
+            continue
         idx = np.repeat(np.array([lut for lut, _, _ in lv], dtype=np.uint32), B)
         y, _ = ctx.pbs_batch(x, tvs, idx)
         for j, (_, out, _) in enumerate(lv):

@@ -38,6 +38,7 @@ class Rig:
         self.delta = O.delta(32)
         self.rng = O.Rng(seed + 1000)
         self.luts = R.luts()
+        self.dual = R.dual_luts()
 
     def encrypt(self, values, width):
         nb = R.blocks(width)
@@ -86,10 +87,10 @@ def test_ciphertexts_match_cpu_interpreter(small, op):
     prog = R.program(op, width)
     if op in R.UNARY:
         got = r.rx.eval(op, width, a)
-        want = interp_cipher(r.ctx, prog, r.luts, [a], r.testv, r.delta)[0]
+        want = interp_cipher(r.ctx, prog, r.luts, [a], r.testv, r.delta, dual=r.dual)[0]
     else:
         got = r.rx.eval(op, width, a, b)
-        want = interp_cipher(r.ctx, prog, r.luts, [a, b], r.testv, r.delta)[0]
+        want = interp_cipher(r.ctx, prog, r.luts, [a, b], r.testv, r.delta, dual=r.dual)[0]
     assert np.array_equal(got, want)
 
 
@@ -99,7 +100,8 @@ def test_ciphertexts_match_order0(small0):
     a, b = r.encrypt([9, 250, 77], width), r.encrypt([8, 17, 77], width)
     for op in ("add", "le"):
         got = r.rx.eval(op, width, a, b)
-        want = interp_cipher(r.ctx, R.program(op, width), r.luts, [a, b], r.testv, r.delta)[0]
+        prog = R.program(op, width, dual=False)   # engines of this order run the variant without dual tables (pick_variant)
+        want = interp_cipher(r.ctx, prog, r.luts, [a, b], r.testv, r.delta, dual=r.dual)[0]
         assert np.array_equal(got, want), op
     assert r.decrypt(r.rx.eval("add", width, a, b)) == [17, 11, 154]
 
@@ -109,7 +111,7 @@ def test_select_and_erc20_match_cpu_interpreter(small):
     f, t, a = r.encrypt([10000, 1000], 64), r.encrypt([0, 5], 64), r.encrypt([1337, 1337], 64)
     nf, nt = r.rx.erc20_transfer(f, t, a)
     assert R.runs_shallow(64, 2)      # two transfers: the library runs the parallel-prefix-carry variant (8 levels)
-    want = interp_cipher(r.ctx, R.program(R.PROG_ERC20, 64, shallow=True), r.luts, [f, t, a], r.testv, r.delta)
+    want = interp_cipher(r.ctx, R.program(R.PROG_ERC20, 64, shallow=True), r.luts, [f, t, a], r.testv, r.delta, dual=r.dual)
     assert np.array_equal(nf, want[0]) and np.array_equal(nt, want[1])
     assert r.decrypt(nf) == [8663, 1000] and r.decrypt(nt) == [1337, 5]       # EncryptedERC20.ts:98,114 / :136-183
     cond = r.rx.eval("le", 64, a, f)
@@ -134,11 +136,11 @@ def test_shallow_and_deep_variants(small, op, width):
         prog = R.program(op, width, shallow=shallow)
         if op == "neg":
             got = r.rx.eval(op, width, a)
-            want = interp_cipher(r.ctx, prog, r.luts, [a[:2]], r.testv, r.delta)[0]
+            want = interp_cipher(r.ctx, prog, r.luts, [a[:2]], r.testv, r.delta, dual=r.dual)[0]
             plain = [(-v) & m for v in vals]
         else:
             got = r.rx.eval(op, width, a, b)
-            want = interp_cipher(r.ctx, prog, r.luts, [a[:2], b[:2]], r.testv, r.delta)[0]
+            want = interp_cipher(r.ctx, prog, r.luts, [a[:2], b[:2]], r.testv, r.delta, dual=r.dual)[0]
             plain = [((v + o) if op == "add" else (v - o)) & m for v, o in zip(vals, others)]
         assert np.array_equal(got[:2], want)
         assert r.decrypt(got) == plain
@@ -153,7 +155,7 @@ def test_div_rem_by_plaintext_match_cpu_interpreter(small):
     for op in ("div", "rem"):
         got = r.rx.eval_scalar(op, width, a, divs)
         for i, d in enumerate(divs):
-            want = interp_cipher(r.ctx, R.program(op, width, scalar=d), r.luts, [a[i:i + 1]], r.testv, r.delta)[0]
+            want = interp_cipher(r.ctx, R.program(op, width, scalar=d), r.luts, [a[i:i + 1]], r.testv, r.delta, dual=r.dual)[0]
             assert np.array_equal(got[i:i + 1], want), (op, i)
         assert r.decrypt(got) == [v // d if op == "div" else v % d for v, d in zip(vals, divs)]
     with pytest.raises(T.LuxError):
@@ -272,7 +274,7 @@ def test_s2_add8_bit_exact_and_ops_decrypt(s2):
     av, bv = [71, 200], [66, 100]
     a, b = r.encrypt(av, width), r.encrypt(bv, width)
     got = r.rx.eval("add", width, a, b)
-    want = interp_cipher(r.ctx, R.program("add", width), r.luts, [a, b], r.testv, r.delta)[0]
+    want = interp_cipher(r.ctx, R.program("add", width), r.luts, [a, b], r.testv, r.delta, dual=r.dual)[0]
     assert np.array_equal(got, want)
     assert r.decrypt(got) == [137, (200 + 100) & 255]             # fhevmOperations1.ts:137-150 + wrap
     assert r.decrypt(r.rx.eval("lt", width, a, b)) == [0, 0]

@@ -31,6 +31,7 @@ class Rig:
         self.delta = T.delta(32, params.arith)
         self.seed = seed + 1000
         self.luts = R.luts()
+        self.dual = R.dual_luts()
 
     def encrypt(self, values, width):
         nb = R.blocks(width)
@@ -68,10 +69,10 @@ def test_torus_ciphertexts_match_cpu_interpreter(small, op):
     prog = R.program(op, width, shallow=R.runs_shallow(width, len(a_vals)))
     if op in R.UNARY:
         got = r.rx.eval(op, width, a)
-        want = interp_cipher(r.ctx, prog, r.luts, [a], r.testv, r.delta, MOD)[0]
+        want = interp_cipher(r.ctx, prog, r.luts, [a], r.testv, r.delta, MOD, dual=r.dual)[0]
     else:
         got = r.rx.eval(op, width, a, b)
-        want = interp_cipher(r.ctx, prog, r.luts, [a, b], r.testv, r.delta, MOD)[0]
+        want = interp_cipher(r.ctx, prog, r.luts, [a, b], r.testv, r.delta, MOD, dual=r.dual)[0]
     assert np.array_equal(got, want)
 
 
@@ -79,7 +80,7 @@ def test_torus_erc20_matches_cpu_interpreter(small):
     r = small
     f, t, a = r.encrypt([10000, 1000], 64), r.encrypt([0, 5], 64), r.encrypt([1337, 1337], 64)
     nf, nt = r.rx.erc20_transfer(f, t, a)
-    want = interp_cipher(r.ctx, R.program(R.PROG_ERC20, 64, shallow=R.runs_shallow(64, 2)), r.luts, [f, t, a], r.testv, r.delta, MOD)
+    want = interp_cipher(r.ctx, R.program(R.PROG_ERC20, 64, shallow=R.runs_shallow(64, 2)), r.luts, [f, t, a], r.testv, r.delta, MOD, dual=r.dual)
     assert np.array_equal(nf, want[0]) and np.array_equal(nt, want[1])
     assert r.decrypt(nf) == [8663, 1000] and r.decrypt(nt) == [1337, 5]       # EncryptedERC20.ts:98,114
     tr = r.rx.trivial_encrypt(16, [4242, 65535])
@@ -93,7 +94,7 @@ def test_torus_s2_named_set_with_noise(s2):
     av, bv = [71, 200], [66, 100]
     a, b = r.encrypt(av, width), r.encrypt(bv, width)
     got = r.rx.eval("add", width, a, b)
-    want = interp_cipher(r.ctx, R.program("add", width, shallow=True), r.luts, [a, b], r.testv, r.delta, MOD)[0]
+    want = interp_cipher(r.ctx, R.program("add", width, shallow=True), r.luts, [a, b], r.testv, r.delta, MOD, dual=r.dual)[0]
     assert np.array_equal(got, want)
     assert r.decrypt(got) == [137, (200 + 100) & 255]
     assert r.decrypt(r.rx.eval("lt", width, a, b)) == [0, 0]

@@ -15,10 +15,11 @@ from oracle.radix import interp_plain as _interp_plain, join_blocks, split_block
 KATS = json.loads((Path(__file__).parent / "golden" / "fhevm_kats.json").read_text())
 LUTS = R.luts()
 SIGNED = R.signed_luts()   # tables fed with x in (-16, 16): lux_radix_lut_signed
+DUAL = R.dual_luts()       # tables whose nodes write two slots from one bootstrap: lux_radix_lut_dual
 
 
 def interp_plain(prog, luts, operands):
-    return _interp_plain(prog, luts, operands, SIGNED)
+    return _interp_plain(prog, luts, operands, SIGNED, DUAL)
 SUPPORTED = set(R.OPS)
 
 
@@ -195,6 +196,26 @@ def test_ordering_on_block_pairs(op):
                 assert join_blocks(out[0]) == plain_semantics(op, a, b, width), (op, width, a, b)
 
 
+@pytest.mark.parametrize("op", ["add", "sub", "neg", "mul", "le"])
+def test_dual_and_plain_variants_agree(op):
+    """message and carry of a column sum <= 7 from ONE bootstrap (dual table, input doubled, second output one box further)
+    against the variant with a bootstrap each: same plaintext results, fewer bootstraps, every dual read at an even input"""
+    assert DUAL
+    rnd = random.Random(12)
+    for width in (8, 16, 64):
+        nb = width // 2
+        for shallow in (False, True):
+            d, n = R.program(op, width, shallow=shallow), R.program(op, width, shallow=shallow, dual=False)
+            assert d.n_pbs <= n.n_pbs and not any(lut in DUAL for lv in n.levels for lut, _, _ in lv)
+            if op in ("add", "sub", "neg") and not shallow:
+                assert d.n_pbs == nb and n.n_pbs == 2 * nb - 1
+            for _ in range(25):
+                a, b = rnd.randrange(1 << width), rnd.randrange(1 << width)
+                ins = [split_blocks(a, nb)] + ([] if op == "neg" else [split_blocks(b, nb)])
+                got = join_blocks(interp_plain(d, LUTS, ins)[0])
+                assert got == join_blocks(interp_plain(n, LUTS, ins)[0]) == plain_semantics(op, a, b, width), (op, width, a, b)
+
+
 def test_shallow_erc20_vectors():
     prog, ref = R.program(R.PROG_ERC20, 64, shallow=True), R.program(R.PROG_ERC20, 64)
     assert len(prog.levels) <= 10 < len(ref.levels)
@@ -218,7 +239,8 @@ def test_pbs_counts_and_depths():
             assert p.n_pbs == R.pbs_count(op, width)
             assert len(p.levels) == R.depth(op, width)
     nb = 32
-    assert R.pbs_count("add", 64) == 2 * nb - 1          # ripple: carry + message per block
+    assert R.pbs_count("add", 64) == nb                  # ripple: message AND carry of a block from one bootstrap (dual table)
+    assert R.program("add", 64, dual=False).n_pbs == 2 * nb - 1   # engines of the other orders: carry + message per block
     assert R.pbs_count("lt", 64) == nb - 1               # signs of block PAIRS (signed table) + pairwise tree
     assert R.pbs_count("and", 64) == nb
     assert R.depth("lt", 64) == 5

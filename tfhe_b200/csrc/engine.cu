@@ -427,6 +427,31 @@ static int torus_pbs_device(lux_engine *e, const u64 *d_in, const u64 *d_testvs,
     return LUX_OK;
 }
 
+// key switch + blind rotation with the raw accumulators out ([B][2N]) instead of one extracted sample: the radix layer reads
+// several coefficients of an accumulator itself (dual tables, radix.cu).  Engines of order LUX_ORDER_LWEKS_PBS only.
+int lux_pbs_device_glwe(lux_engine *e, const u64 *d_in, const u64 *d_testvs, const u32 *d_lut_idx, u32 lut_div, size_t B, u64 *d_glwe,
+                        cudaStream_t s) {
+    if (B == 0) return LUX_OK;
+    if (B > 0x7fffffffu) LUX_FAIL(e, LUX_ERR_INVALID, "batch too large");
+    if (e->p.order != LUX_ORDER_LWEKS_PBS) LUX_FAIL(e, LUX_ERR_INVALID, "accumulator output needs the key-switch-first order");
+    if (!e->has_bsk) LUX_FAIL(e, LUX_ERR_NO_KEY, "bootstrap key not loaded");
+    if (!e->has_lksk) LUX_FAIL(e, LUX_ERR_NO_KEY, "LWE key switch key not loaded");
+    CUDA_TRY(e, cudaSetDevice(e->device));
+    int rc = ensure_scratch(e, 0, sizeof(u64) * B * (e->p.n + 1));
+    if (rc) return rc;
+    u64 *d_small = (u64 *)e->scratch[0];
+    if ((rc = launch_ks(e, d_in, d_small, B, s))) return rc;
+    if (lux_is_torus(e)) {
+        fft64::Args a = make_fft_args(e, d_small, d_testvs, d_lut_idx, lut_div, B, d_glwe);
+        a.out_mode = 2;
+        return lux_fft_launch_br(e, a, s);
+    }
+    BRArgs a = make_br_args(e, d_small, d_testvs, d_lut_idx, B, d_glwe);
+    a.lut_div = lut_div ? lut_div : 1;
+    a.out_mode = 2;
+    return launch_br(e, a, s);
+}
+
 int lux_pbs_device_grouped(lux_engine *e, const u64 *d_in, const u64 *d_testvs, const u32 *d_lut_idx, u32 lut_div, size_t B,
                            u64 *d_out, cudaStream_t s, u64 body_add) {
     if (B == 0) return LUX_OK;

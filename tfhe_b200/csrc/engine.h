@@ -12,7 +12,7 @@
 #include "tfhe_kernels.cuh"
 #include "fft64.cuh"
 
-#define LUX_SCRATCH_SLOTS 8
+#define LUX_SCRATCH_SLOTS 10
 
 struct lux_engine {
     // every extern "C" entry point that takes a non-const engine holds this for its whole duration: calls on one engine
@@ -76,6 +76,7 @@ struct lux_engine {
 
 void lux_host_ntt_tables(u32 N, std::vector<u64> &roots, std::vector<u64> &invroots, u64 &ninv);
 // PBS on device buffers where ciphertext ct uses test vector d_idx[ct / lut_div] (engine.cu)
+int lux_pbs_device_glwe(lux_engine *e, const u64 *d_in, const u64 *d_testvs, const u32 *d_idx, u32 lut_div, size_t B, u64 *d_glwe, cudaStream_t s);
 int lux_pbs_device_grouped(lux_engine *e, const u64 *d_in, const u64 *d_testvs, const u32 *d_idx, u32 lut_div, size_t B,
                            u64 *d_out, cudaStream_t s, u64 body_add = 0);
 int lux_ensure_scratch(lux_engine *e, int slot, size_t bytes);

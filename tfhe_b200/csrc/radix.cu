@@ -38,9 +38,12 @@ enum LutId {
     L_EQK0 = L_PRED_RED0 + PRED_N,      // + k: x == k
     L_NEK0 = L_EQK0 + 16,               // + k: x != k
     L_SIGN2 = L_NEK0 + 16,              // signed: sign(x) in {-1, 0, 1} for x in (-16, 16): T(0) = 0, T(1..15) = 1
+    L_MC,                               // dual: message AND carry of a sum s <= 7 from ONE blind rotation, input 2 s:
+                                        // T(2 s) = s & 3 (read at coefficient 0), T(2 s + 1) = s >> 2 (read one box further)
     L_COUNT
 };
 bool lut_signed(int id) { return id == L_SIGN2; }
+bool lut_dual(int id) { return id == L_MC; }
 
 int sign3(int a, int b) { return a < b ? 0 : (a == b ? 1 : 2); }
 int cmpred(int x) {
@@ -62,6 +65,7 @@ int lut_eval(int id, int x) {
     const int hi = x >> 2, lo = x & 3;
     switch (id) {
         case L_SIGN2: return x != 0;
+        case L_MC: return (x & 1) ? ((x >> 1) >> 2) : ((x >> 1) & 3);
         case L_MSG: return x & 3;
         case L_CARRY: return x >> 2;
         case L_MUL_LO: return (hi * lo) & 3;
@@ -153,7 +157,7 @@ struct Val {
 struct PbsNode {
     Val in;
     int lut;
-    int out;
+    int out;        // first output slot; a dual table (lut_dual) also writes slot out + 1
 };
 struct Program {
     std::vector<int> in_blocks, out_blocks;
@@ -163,7 +167,9 @@ struct Program {
     std::vector<std::vector<Val>> outs;
     // execution plan
     std::vector<int> slot_pos;  // pool position of a PBS-output slot (level-contiguous); -1 for inputs
-    size_t n_pbs = 0, max_level_pbs = 0;
+    size_t n_pbs = 0, max_level_pbs = 0;   // bootstraps (= blind rotations)
+    size_t n_pos = 0;                      // pool positions = bootstrap outputs (a dual table has two)
+    bool has_dual = false;
 };
 
 struct Builder {
@@ -172,6 +178,11 @@ struct Builder {
     // shallow: resolve the final carry chain of ripple() with a parallel-prefix scan (log2(blocks) + 2 levels instead of
     // `blocks`, about 3.5x the bootstraps): chosen for batches so small that the depth, not the count, is the time
     bool shallow = false;
+    // dual: message and carry of a column sum <= 7 come out of ONE blind rotation (many-LUT bootstrap): the sum uses three of
+    // the four bits below the padding bit, so the input is doubled (linear), the test vector interleaves the two tables box by
+    // box, and the executor extracts coefficient 0 (message) and coefficient N/16 (carry) of the same accumulator.  Only
+    // engines whose bootstraps start with the key switch run these programs (pick_variant).
+    bool dual = true;
 
     int add_input(int blocks) {
         in_base.push_back(p.n_slots);
@@ -249,6 +260,31 @@ struct Builder {
         r.hi = hi;
         return r;
     }
+    // (message, carry) of v <= 7
+    std::pair<Val, Val> msg_carry(const Val &v, bool want_carry) {
+        if (!want_carry) return {pbs(v, L_MSG), cst(0)};
+        if (!dual || v.hi > 7 || v.lo < 0) return {pbs(v, L_MSG), pbs(v, L_CARRY)};
+        if (v.t.empty()) return {cst(v.k & 3), cst(v.k >> 2)};
+        const Val in2 = scale(v, 2);
+        const int slot = p.n_slots;
+        p.n_slots += 2;
+        p.slot_level.push_back(v.level + 1);
+        p.slot_level.push_back(v.level + 1);
+        if ((int)p.levels.size() <= v.level) p.levels.resize(v.level + 1);
+        p.levels[v.level].push_back({in2, L_MC, slot});
+        p.has_dual = true;
+        Val m, c;
+        m.t.push_back({slot, 1});
+        c.t.push_back({slot + 1, 1});
+        m.level = c.level = v.level + 1;
+        m.lo = c.lo = 15;
+        m.hi = c.hi = 0;
+        for (long x = v.lo; x <= v.hi; x++) {
+            m.lo = std::min<long>(m.lo, x & 3), m.hi = std::max<long>(m.hi, x & 3);
+            c.lo = std::min<long>(c.lo, x >> 2), c.hi = std::max<long>(c.hi, x >> 2);
+        }
+        return {m, c};
+    }
     void output(std::vector<Val> blocks) {
         p.out_blocks.push_back((int)blocks.size());
         p.outs.push_back(std::move(blocks));
@@ -257,10 +293,14 @@ struct Builder {
         p.slot_pos.assign(p.n_slots, -1);
         int pos = 0;
         for (auto &lv : p.levels) {
-            for (auto &n : lv) p.slot_pos[n.out] = pos++;
+            for (auto &n : lv) {
+                p.slot_pos[n.out] = pos++;
+                if (lut_dual(n.lut)) p.slot_pos[n.out + 1] = pos++;
+            }
             p.max_level_pbs = std::max(p.max_level_pbs, lv.size());
+            p.n_pbs += lv.size();
         }
-        p.n_pbs = (size_t)pos;
+        p.n_pos = (size_t)pos;
         return std::move(p);
     }
 
@@ -292,8 +332,9 @@ struct Builder {
                     if (s.hi <= 3) {
                         next[k].push_back(s);
                     } else {
-                        next[k].push_back(pbs(s, L_MSG));
-                        if (k + 1 < nb) next[k + 1].push_back(pbs(s, L_CARRY));
+                        const auto mc = msg_carry(s, k + 1 < nb);
+                        next[k].push_back(mc.first);
+                        if (k + 1 < nb) next[k + 1].push_back(mc.second);
                     }
                 }
             }
@@ -336,8 +377,9 @@ struct Builder {
                 out[k] = s;
                 carry = cst(0);
             } else {
-                out[k] = pbs(s, L_MSG);
-                carry = (k + 1 < nb) ? pbs(s, L_CARRY) : cst(0);
+                const auto mc = msg_carry(s, k + 1 < nb);
+                out[k] = mc.first;
+                carry = mc.second;
             }
         }
         return out;
@@ -538,11 +580,12 @@ struct Builder {
     }
 };
 
-Program build_program(int op, unsigned bw, const Wide &scalar, bool shallow = false) {
+Program build_program(int op, unsigned bw, const Wide &scalar, bool shallow = false, bool dual = false) {
     const int nb = (int)lux_radix_blocks(bw);
     if (nb == 0) throw std::logic_error("unsupported bit width");
     Builder b;
     b.shallow = shallow;
+    b.dual = dual;
     if (op == LUX_OP_DIV || op == LUX_OP_REM) {   // plaintext divisor: the circuit depends on it
         if (scalar.is_zero()) throw std::logic_error("division by zero");
         const int l = b.add_input(nb);
@@ -615,19 +658,21 @@ Program build_program(int op, unsigned bw, const Wide &scalar, bool shallow = fa
 }
 
 std::mutex g_prog_mutex;
-// op | LUX_PROG_SHALLOW selects the shallow variant of a circuit (parallel-prefix carries)
+// op | LUX_PROG_SHALLOW selects the shallow variant of a circuit (parallel-prefix carries); op | LUX_PROG_NODUAL the variant
+// without dual tables (one bootstrap per message and per carry), for engines whose bootstraps do not start with the key switch
 std::map<std::pair<int, unsigned>, Program> g_programs;
 const Program &get_program(int op, unsigned bw) {
     std::lock_guard<std::mutex> lk(g_prog_mutex);
     auto key = std::make_pair(op, bw);
     auto it = g_programs.find(key);
     if (it == g_programs.end())
-        it = g_programs.emplace(key, build_program(op & ~LUX_PROG_SHALLOW, bw, Wide(), (op & LUX_PROG_SHALLOW) != 0)).first;
+        it = g_programs.emplace(key, build_program(op & ~(LUX_PROG_SHALLOW | LUX_PROG_NODUAL), bw, Wide(), (op & LUX_PROG_SHALLOW) != 0, (op & LUX_PROG_NODUAL) == 0)).first;
     return it->second;
 }
 // the variant to run for `batch` integers: depth is what costs time while a level fits the latency-mode kernels
 // (a level of the shallow carry scan has up to blocks - 1 bootstraps per integer)
-static int pick_variant(int op, unsigned bw, size_t batch) {
+static int pick_variant(const lux_engine *e, int op, unsigned bw, size_t batch) {
+    if (e->p.order != LUX_ORDER_LWEKS_PBS) op |= LUX_PROG_NODUAL;
     return batch * lux_radix_blocks(bw) <= 296 ? (op | LUX_PROG_SHALLOW) : op;
 }
 // divisor-specific circuits (div / rem by a plaintext): bounded cache, entries stay alive while in use
@@ -679,6 +724,33 @@ __global__ void __launch_bounds__(256) radix_lin_kernel(const LinDesc *descs, co
             }
         }
         dst[word] = acc;
+    }
+}
+
+// sample extraction of coefficient o * cstep (o = 0 .. n_out-1) of the accumulators of a level: node j of the level, integer b.
+// LWE sample of coefficient c of (mask, body):  a'_p = mask[c - p] for p <= c, -mask[N + c - p] for p > c;  b' = body[c]
+// (crypto/glwe.rs:96-106 is the case c = 0).  A dual table reads T(x) at coefficient 0 and T(x + 1) one box (N/16) further.
+struct ExtDesc {
+    u32 pos;     // pool position of the node's first output
+    u32 n_out;   // 1, or 2 for a dual table
+};
+template <bool TORUS>
+__global__ void __launch_bounds__(256) radix_extract_kernel(const u64 *glwe, const ExtDesc *descs, u64 *pool, u32 bcur, u32 N, u32 cstep) {
+    const ExtDesc d = descs[blockIdx.y];
+    const size_t b = blockIdx.x;
+    const u64 *mask = glwe + ((size_t)blockIdx.y * bcur + b) * 2 * N, *body = mask + N;
+    for (u32 o = 0; o < d.n_out; o++) {
+        const u32 c = o * cstep;
+        u64 *dst = pool + ((size_t)(d.pos + o) * bcur + b) * (N + 1);
+        for (u32 p = threadIdx.x; p < N; p += blockDim.x) {
+            if (p <= c) {
+                dst[p] = mask[c - p];
+            } else {
+                const u64 v = mask[N + c - p];
+                dst[p] = TORUS ? (u64)0 - v : gl_neg(v);
+            }
+        }
+        if (threadIdx.x == 0) dst[N] = body[c];
     }
 }
 
@@ -765,7 +837,8 @@ int exec_program(lux_engine *e, const Program &prog, const std::vector<const u64
     const u64 delta = lux_delta_arith(e->p.arith, 2 * RADIX_P);
     cudaStream_t s = e->stream;
 
-    const size_t slots_per_int = prog.n_pbs + prog.max_level_pbs;
+    if (prog.has_dual && e->p.order != LUX_ORDER_LWEKS_PBS) LUX_FAIL(e, LUX_ERR_INVALID, "internal: dual tables need the key-switch-first order");
+    const size_t slots_per_int = prog.n_pos + prog.max_level_pbs;
     const size_t bytes_per_int = std::max<size_t>(1, slots_per_int) * w * sizeof(u64);
     size_t bc = std::max<size_t>(1, std::min(batch, r->pool_cap / bytes_per_int));
     if (prog.max_level_pbs * bc > 0x7fffffffu) bc = 0x7fffffffu / prog.max_level_pbs;
@@ -785,13 +858,30 @@ int exec_program(lux_engine *e, const Program &prog, const std::vector<const u64
     }
     const size_t off_terms = sizeof(LinDesc) * n_desc;
     const size_t off_luts = off_terms + sizeof(LinTerm) * n_terms;
-    const size_t stage_bytes = off_luts + sizeof(u32) * n_luts;
+    const size_t off_ext = (off_luts + sizeof(u32) * n_luts + 15) / 16 * 16;
+    const size_t stage_bytes = off_ext + sizeof(ExtDesc) * n_luts;
     if ((rc = ensure_stage(e, stage_bytes))) return rc;
     if ((rc = lux_ensure_scratch(e, 7, stage_bytes))) return rc;
     unsigned char *d_stage = (unsigned char *)e->scratch[7];
     const LinDesc *d_descs = (const LinDesc *)d_stage;
     const LinTerm *d_terms = (const LinTerm *)(d_stage + off_terms);
     const u32 *d_luts = (const u32 *)(d_stage + off_luts);
+    const ExtDesc *d_ext = (const ExtDesc *)(d_stage + off_ext);
+    // levels with a dual table go through raw accumulators ([nodes x integers][2N]) and radix_extract_kernel, in runs of nodes
+    // that keep that buffer below 2 GiB
+    size_t glwe_nodes = 0;
+    if (prog.has_dual) {
+        const size_t per_node = bc * 2 * (size_t)e->p.N * sizeof(u64);
+        size_t most = 0;
+        for (auto &lv : prog.levels) {
+            bool dual = false;
+            for (auto &n : lv) dual = dual || lut_dual(n.lut);
+            if (dual) most = std::max(most, lv.size());
+        }
+        glwe_nodes = std::max<size_t>(1, std::min(most, ((size_t)2 << 30) / per_node));
+        if ((rc = lux_ensure_scratch(e, 8, glwe_nodes * per_node))) return rc;
+    }
+    u64 *d_glwe = (u64 *)e->scratch[8];
 
     std::vector<int> slot_operand(prog.n_in_slots), slot_block(prog.n_in_slots);
     for (size_t k = 0, sl = 0; k < prog.in_blocks.size(); k++)
@@ -805,6 +895,7 @@ int exec_program(lux_engine *e, const Program &prog, const std::vector<const u64
         LinDesc *descs = (LinDesc *)r->h_stage;
         LinTerm *terms = (LinTerm *)((unsigned char *)r->h_stage + off_terms);
         u32 *luts = (u32 *)((unsigned char *)r->h_stage + off_luts);
+        ExtDesc *ext = (ExtDesc *)((unsigned char *)r->h_stage + off_ext);
         size_t di = 0, ti = 0, li = 0;
         auto emit = [&](const Val &v, u64 *dst, u32 dst_stride) {
             LinDesc &d = descs[di++];
@@ -828,10 +919,11 @@ int exec_program(lux_engine *e, const Program &prog, const std::vector<const u64
                 t.coef = (int)x.coef;
             }
         };
-        u64 *pbs_in = pool + prog.n_pbs * bcur * w;
+        u64 *pbs_in = pool + prog.n_pos * bcur * w;
         for (auto &lv : prog.levels)
             for (size_t j = 0; j < lv.size(); j++) {
                 emit(lv[j].in, pbs_in + j * bcur * w, (u32)w);
+                ext[li] = ExtDesc{(u32)prog.slot_pos[lv[j].out], lut_dual(lv[j].lut) ? 2u : 1u};
                 luts[li++] = (u32)lv[j].lut;
             }
         for (size_t k = 0; k < prog.outs.size(); k++) {
@@ -849,8 +941,23 @@ int exec_program(lux_engine *e, const Program &prog, const std::vector<const u64
                 radix_lin_kernel<false><<<dim3((unsigned)bcur, (unsigned)lv.size()), 256, 0, s>>>(d_descs + d_off, d_terms, (u32)w);
             e->launches++;
             CUDA_TRY(e, cudaGetLastError());
-            u64 *lv_out = pool + (size_t)prog.slot_pos[lv[0].out] * bcur * w;
-            if ((rc = lux_pbs_device_grouped(e, pbs_in, r->d_testvs, d_luts + l_off, (u32)bcur, lv.size() * bcur, lv_out, s))) return rc;
+            bool dual = false;
+            for (auto &n : lv) dual = dual || lut_dual(n.lut);
+            if (dual) {
+                for (size_t j0 = 0; j0 < lv.size(); j0 += glwe_nodes) {
+                    const size_t nj = std::min(glwe_nodes, lv.size() - j0);
+                    if ((rc = lux_pbs_device_glwe(e, pbs_in + j0 * bcur * w, r->d_testvs, d_luts + l_off + j0, (u32)bcur, nj * bcur, d_glwe, s))) return rc;
+                    if (lux_is_torus(e))
+                        radix_extract_kernel<true><<<dim3((unsigned)bcur, (unsigned)nj), 256, 0, s>>>(d_glwe, d_ext + l_off + j0, pool, (u32)bcur, e->p.N, e->p.N / RADIX_P);
+                    else
+                        radix_extract_kernel<false><<<dim3((unsigned)bcur, (unsigned)nj), 256, 0, s>>>(d_glwe, d_ext + l_off + j0, pool, (u32)bcur, e->p.N, e->p.N / RADIX_P);
+                    e->launches++;
+                    CUDA_TRY(e, cudaGetLastError());
+                }
+            } else {
+                u64 *lv_out = pool + (size_t)prog.slot_pos[lv[0].out] * bcur * w;
+                if ((rc = lux_pbs_device_grouped(e, pbs_in, r->d_testvs, d_luts + l_off, (u32)bcur, lv.size() * bcur, lv_out, s))) return rc;
+            }
             d_off += lv.size();
             l_off += lv.size();
         }
@@ -977,7 +1084,7 @@ int lux_eval(lux_engine *e, lux_op op, unsigned bw, const uint64_t *lhs, const u
         int rc = check_op(e, op, bw, lhs, rhs, out);
         if (rc) return rc;
         if ((rc = reject_scalar_only(e, op))) return rc;
-        const Program &p = get_program(pick_variant((int)op, bw, batch), bw);
+        const Program &p = get_program(pick_variant(e, (int)op, bw, batch), bw);
         std::vector<const u64 *> in{lhs};
         if (!lux_op_is_unary(op)) in.push_back(rhs);
         return exec_host(e, p, in, {out}, batch);
@@ -990,7 +1097,7 @@ int lux_eval_device(lux_engine *e, lux_op op, unsigned bw, const uint64_t *lhs, 
         if (rc) return rc;
         if ((rc = reject_scalar_only(e, op))) return rc;
         CUDA_TRY(e, cudaSetDevice(e->device));
-        const Program &p = get_program(pick_variant((int)op, bw, batch), bw);
+        const Program &p = get_program(pick_variant(e, (int)op, bw, batch), bw);
         std::vector<const u64 *> in{lhs};
         if (!lux_op_is_unary(op)) in.push_back(rhs);
         return exec_program(e, p, in, {out}, batch);
@@ -1048,7 +1155,7 @@ static int eval_scalar_impl(lux_engine *e, lux_op op, unsigned bw, const uint64_
             return LUX_OK;
         }
         if (n_limbs != 1) LUX_FAIL(e, LUX_ERR_INVALID, "wide plaintext operands are supported for div/rem only");
-        const Program &p = get_program(pick_variant((int)op, bw, batch), bw);
+        const Program &p = get_program(pick_variant(e, (int)op, bw, batch), bw);
         const size_t nb = lux_radix_blocks(bw), w = lux_ct_words(e), words = batch * nb * w;
         const size_t out_words = batch * (size_t)p.out_blocks[0] * w;
         if ((rc = lux_ensure_scratch(e, 1, sizeof(u64) * words))) return rc;
@@ -1115,7 +1222,7 @@ int lux_erc20_transfer(lux_engine *e, const uint64_t *from_bal, const uint64_t *
     LUX_LOCK(e);
     return guarded(e, [&]() -> int {
         if (!from_bal || !to_bal || !amount || !new_from || !new_to) LUX_FAIL(e, LUX_ERR_INVALID, "lux_erc20_transfer: null argument");
-        return exec_host(e, get_program(pick_variant(LUX_PROG_ERC20, 64, batch), 64), {from_bal, to_bal, amount}, {new_from, new_to}, batch);
+        return exec_host(e, get_program(pick_variant(e, LUX_PROG_ERC20, 64, batch), 64), {from_bal, to_bal, amount}, {new_from, new_to}, batch);
     });
 }
 int lux_erc20_transfer_device(lux_engine *e, const uint64_t *from_bal, const uint64_t *to_bal, const uint64_t *amount, size_t batch,
@@ -1124,7 +1231,7 @@ int lux_erc20_transfer_device(lux_engine *e, const uint64_t *from_bal, const uin
     return guarded(e, [&]() -> int {
         if (!from_bal || !to_bal || !amount || !new_from || !new_to) LUX_FAIL(e, LUX_ERR_INVALID, "lux_erc20_transfer_device: null argument");
         CUDA_TRY(e, cudaSetDevice(e->device));
-        return exec_program(e, get_program(pick_variant(LUX_PROG_ERC20, 64, batch), 64), {from_bal, to_bal, amount}, {new_from, new_to}, batch);
+        return exec_program(e, get_program(pick_variant(e, LUX_PROG_ERC20, 64, batch), 64), {from_bal, to_bal, amount}, {new_from, new_to}, batch);
     });
 }
 
@@ -1183,5 +1290,6 @@ int lux_radix_lut(int lut_id, uint64_t out[16]) {
     return LUX_OK;
 }
 int lux_radix_lut_signed(int lut_id) { return lut_id >= 0 && lut_id < L_COUNT && lut_signed(lut_id) ? 1 : 0; }
+int lux_radix_lut_dual(int lut_id) { return lut_id >= 0 && lut_id < L_COUNT && lut_dual(lut_id) ? 1 : 0; }
 
 }  // extern "C"

@@ -54,6 +54,7 @@ ABI = {
     "lux_radix_program": (_sz, [_int, _uint, _vp, _sz]),
     "lux_radix_lut": (_int, [_int, _vp]),
     "lux_radix_lut_signed": (_int, [_int]),
+    "lux_radix_lut_dual": (_int, [_int]),
 }
 _bound = False
 
@@ -108,6 +109,7 @@ class Program:
 
 
 PROG_SHALLOW = 0x1000   # lux_radix.h LUX_PROG_SHALLOW
+PROG_NODUAL = 0x2000    # lux_radix.h LUX_PROG_NODUAL
 
 
 def runs_shallow(bit_width: int, batch: int) -> bool:
@@ -115,12 +117,15 @@ def runs_shallow(bit_width: int, batch: int) -> bool:
     return batch * blocks(bit_width) <= 296
 
 
-def program(op, bit_width: int, scalar: int | None = None, shallow: bool = False) -> Program:
+def program(op, bit_width: int, scalar: int | None = None, shallow: bool = False, dual: bool = True) -> Program:
     """the circuit of `op`; div/rem need the plaintext divisor `scalar` (the circuit is divisor-specific);
-    shallow = the parallel-prefix-carry variant the library runs for very small batches"""
+    shallow = the parallel-prefix-carry variant the library runs for very small batches; dual = False: the variant without
+    dual tables that engines whose bootstraps do not start with the key switch run"""
     code = OPS[op] if isinstance(op, str) else int(op)
     if shallow:
         code |= PROG_SHALLOW
+    if not dual:
+        code |= PROG_NODUAL
     sc = _limbs(int(scalar or 0), 4)
     n = lib().lux_radix_program_scalar(code, bit_width, sc.ctypes.data, 4, None, 0)
     if n == 0:
@@ -162,6 +167,11 @@ def luts() -> np.ndarray:
         rc = lib().lux_radix_lut(i, t[i].ctypes.data)
         assert rc == 0
     return t
+
+
+def dual_luts() -> set:
+    """ids of the dual tables: their nodes write slots out and out + 1 from one blind rotation (lux_radix_lut_dual)"""
+    return {i for i in range(lib().lux_radix_lut(0, None)) if lib().lux_radix_lut_dual(i)}
 
 
 def signed_luts() -> set:
