@@ -7,6 +7,7 @@
 #   bench          headline bench + reference arm    bench_gold    the Goldilocks arithmetic on the same shape
 #   quick          scripts/quick_torus.py $QUICK_ARGS (device-resident kernel timing; teams/variant sweeps)
 #   ncu_fft        ncu --set full (+source) of the torus blind rotation at B=$NCU_B (default 4440) + launch list of the bench
+#   launches       ncu launch list (gpu__time_duration) of the bench command
 #   traffic        DRAM bytes of the dominant kernel at the bench batch
 #   gate           scripts/decrypt_trials.py (>= 10^6 trials), torus then goldilocks
 #   radix          scripts/bench_radix.py (C3-C5 op rates, single process)
@@ -29,6 +30,7 @@ for stage in "$@"; do
     ncu_fft)
       timeout 900 ncu --set full --import-source on --clock-control none -k regex:blind_rotate_fft -s 2 -c 1 -f -o gpurun_out/fft_full python scripts/quick_torus.py $NCU_B 0 > gpurun_out/ncu_fft.log 2>&1; echo "ncu full rc=$?"
       timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv python bench.py --steps 2 --warmup 3 --no-cpu --c5 0 > gpurun_out/ncu_launches.log 2>&1; echo "ncu launches rc=$?";;
+    launches) timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv python bench.py --steps 2 --warmup 3 --no-cpu --c5 0 > gpurun_out/ncu_launches.log 2>&1; echo "ncu launches rc=$?";;
     traffic) timeout 600 ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum --clock-control none -k regex:blind_rotate_fft -s 3 -c 1 -f -o gpurun_out/prof_traffic python bench.py --steps 2 --warmup 3 --no-cpu --c5 0 > gpurun_out/ncu_traffic.log 2>&1; echo "ncu traffic rc=$?";;
     gate) timeout 1200 python scripts/decrypt_trials.py --arith torus --out gpurun_out/decrypt_trials_torus.json > gpurun_out/gate_torus.log 2>&1; echo "gate torus rc=$?"; tail -1 gpurun_out/gate_torus.log | cut -c1-600
           timeout 1200 python scripts/decrypt_trials.py --arith goldilocks --out gpurun_out/decrypt_trials_goldilocks.json > gpurun_out/gate_gold.log 2>&1; echo "gate goldilocks rc=$?";;
