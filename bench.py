@@ -667,7 +667,7 @@ def main():
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="weak: --batch per GPU; strong: --global-batch split over the GPUs (ragged)")
     ap.add_argument("--global-batch", type=int, default=65120, help="strong scaling: total ciphertexts per step")
-    ap.add_argument("--c5", type=int, default=148, help="ERC20 transfers per GPU in the C5 slice (0 = skip)")
+    ap.add_argument("--c5", type=int, default=296, help="ERC20 transfers per GPU in the C5 slice (0 = skip)")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--teams", type=int, default=0, help="force ciphertexts per CTA (tuning)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg (tuning sweeps)")
