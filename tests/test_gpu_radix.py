@@ -178,8 +178,10 @@ def test_chunked_execution_is_identical(small):
     per_int = (R.pbs_count("mul", width) + 40) * r.p.ct_len * 8
     r.rx.set_pool_bytes(per_int * 5)                    # forces 5 chunks of <= 5 integers
     chunked = r.rx.eval("mul", width, a, b)
+    r.rx.set_pool_bytes(r.p.N * 16 * 3)                 # one integer per chunk, accumulator buffer of three nodes: the levels
+    runs = r.rx.eval("mul", width, a[:4], b[:4])        # with dual tables run as several node runs
     r.rx.set_pool_bytes(16 << 30)
-    assert np.array_equal(whole, chunked)
+    assert np.array_equal(whole, chunked) and np.array_equal(whole[:4], runs)
     assert r.decrypt(whole) == [(x * y) & 0xFFFF for x, y in zip(av, bv)]
 
 

@@ -868,7 +868,7 @@ int exec_program(lux_engine *e, const Program &prog, const std::vector<const u64
     const u32 *d_luts = (const u32 *)(d_stage + off_luts);
     const ExtDesc *d_ext = (const ExtDesc *)(d_stage + off_ext);
     // levels with a dual table go through raw accumulators ([nodes x integers][2N]) and radix_extract_kernel, in runs of nodes
-    // that keep that buffer below 2 GiB
+    // that keep that buffer below 2 GiB (and below the pool limit a caller set)
     size_t glwe_nodes = 0;
     if (prog.has_dual) {
         const size_t per_node = bc * 2 * (size_t)e->p.N * sizeof(u64);
@@ -878,7 +878,7 @@ int exec_program(lux_engine *e, const Program &prog, const std::vector<const u64
             for (auto &n : lv) dual = dual || lut_dual(n.lut);
             if (dual) most = std::max(most, lv.size());
         }
-        glwe_nodes = std::max<size_t>(1, std::min(most, ((size_t)2 << 30) / per_node));
+        glwe_nodes = std::max<size_t>(1, std::min(most, std::min<size_t>((size_t)2 << 30, r->pool_cap) / per_node));
         if ((rc = lux_ensure_scratch(e, 8, glwe_nodes * per_node))) return rc;
     }
     u64 *d_glwe = (u64 *)e->scratch[8];
