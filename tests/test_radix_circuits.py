@@ -172,7 +172,7 @@ def test_shallow_variants_match_plain_semantics(width):
             assert join_blocks(out[0]) == plain_semantics(op, a, b, width), (op, hex(a), hex(b))
 
 
-@pytest.mark.parametrize("op", ["lt", "le", "gt", "ge", "min", "max"])
+@pytest.mark.parametrize("op", ["lt", "le", "gt", "ge", "min", "max", "eq", "ne"])
 def test_ordering_on_block_pairs(op):
     """the comparison reads TWO blocks per bootstrap through the signed table (difference in [-15, 15], padding bit = sign):
     exhaustive at 2 / 4 / 6 bits (one block, one pair, a pair and a lone block), random and adjacent values at 10 / 64 / 256

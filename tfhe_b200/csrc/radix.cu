@@ -435,22 +435,27 @@ struct Builder {
         if (s.size() == 1) return pbs(pack(cst(1), s[0]), L_PRED_RED0 + pred);   // "upper part equal": the sign of the one pair decides
         return pbs(pack(s[1], s[0]), L_PRED_RED0 + pred);
     }
+    // Equality through the signed table as well.  z = sign(4 (a1 - b1) + (a0 - b0)) in {-1, 0, 1} is non-zero iff the pair of
+    // blocks differs; three such flags combine without cancellation in balanced ternary, 9 z2 + 3 z1 + z0 in [-13, 13], whose
+    // sign is again a flag; the last one or two flags, shifted to 3 z1 + z0 + 5 in [1, 9], meet the plain table x == 5 (or
+    // x != 5).  euint64: 16 + 6 + 2 + 1 = 25 bootstraps (32 + 3 + 1 with one block per bootstrap).
     Val equal(const std::vector<Val> &a, const std::vector<Val> &b, bool negate) {
-        std::vector<Val> s;
-        for (size_t i = 0; i < a.size(); i++) s.push_back(pbs(pack(a[i], b[i]), L_EQB));
-        while (s.size() > 15) {
+        const int nb = (int)a.size();
+        auto diff = [&](int i) { return sub(assume(a[i], 0, 3), assume(b[i], 0, 3)); };
+        std::vector<Val> z;
+        for (int i = 0; i + 1 < nb; i += 2) z.push_back(pbs(add(scale(diff(i + 1), 4), diff(i)), L_SIGN2));
+        if (nb & 1) z.push_back(nb == 1 ? diff(0) : pbs(diff(nb - 1), L_SIGN2));
+        while (z.size() > 2) {
             std::vector<Val> n;
-            for (size_t i = 0; i < s.size(); i += 15) {
-                Val sum = cst(0);
-                size_t c = 0;
-                for (; c < 15 && i + c < s.size(); c++) sum = add(sum, s[i + c]);
-                n.push_back(pbs(sum, L_EQK0 + (int)c));
-            }
-            s.swap(n);
+            size_t i = 0;
+            for (; i + 2 < z.size(); i += 3) n.push_back(pbs(add(add(scale(z[i + 2], 9), scale(z[i + 1], 3)), z[i]), L_SIGN2));
+            for (; i < z.size(); i++) n.push_back(z[i]);
+            z.swap(n);
         }
-        Val sum = cst(0);
-        for (auto &v : s) sum = add(sum, v);
-        return pbs(sum, (negate ? L_NEK0 : L_EQK0) + (int)s.size());
+        // one flag (nb == 1: the raw difference in [-3, 3]) or two: x = 3 z1 + z0 + 5 (one: z0 + 5) equals 5 iff all are zero
+        Val x = z.size() == 2 ? add(scale(z[1], 3), z[0]) : z[0];
+        x = add(x, cst(5));
+        return pbs(x, (negate ? L_NEK0 : L_EQK0) + 5);
     }
     std::vector<Val> select(const Val &c, const std::vector<Val> &a, const std::vector<Val> &b) {
         std::vector<Val> r(a.size());
