@@ -138,7 +138,7 @@ def test_lwe_keyswitch_tcgen05_form(rig_small, rig_s2, which):
     r = rig_small if which == "small" else rig_s2
     e, p = r.eng, r.p
     rs = np.random.RandomState(31)
-    for B in ((1, 129, 300, 1500) if which == "small" else (1, 129, 1400)):   # 1400 at the named set: 319 tiles, three per CTA on some SMs
+    for B in ((1, 129, 300, 1500) if which == "small" else (1, 129, 1400, 4440)):   # 1400 at the named set: 319 tiles, three per CTA on some SMs; 4440: 1,015 tiles
         cts = u64_rand(rs, (B, p.k * p.N + 1))
         cts[0, :6] = np.array([0, 1, 2**63, 2**63 - 1, 2**64 - 1, 2**59], np.uint64)
         cts[B - 1, -7:-1] = np.array([2**64 - 1, 2**63 + 1, 2**60 - 1, 2**60, 7, 0], np.uint64)

@@ -196,7 +196,7 @@ def test_ordering_on_block_pairs(op):
                 assert join_blocks(out[0]) == plain_semantics(op, a, b, width), (op, width, a, b)
 
 
-@pytest.mark.parametrize("op", ["add", "sub", "neg", "mul", "le"])
+@pytest.mark.parametrize("op", ["add", "sub", "neg", "mul", "le", "shl", "shr", "rotl", "rotr"])
 def test_dual_and_plain_variants_agree(op):
     """message and carry of a column sum <= 7 from ONE bootstrap (dual table, input doubled, second output one box further)
     against the variant with a bootstrap each: same plaintext results, fewer bootstraps, every dual read at an even input"""

@@ -40,10 +40,12 @@ enum LutId {
     L_SIGN2 = L_NEK0 + 16,              // signed: sign(x) in {-1, 0, 1} for x in (-16, 16): T(0) = 0, T(1..15) = 1
     L_MC,                               // dual: message AND carry of a sum s <= 7 from ONE blind rotation, input 2 s:
                                         // T(2 s) = s & 3 (read at coefficient 0), T(2 s + 1) = s >> 2 (read one box further)
+    L_SEL2,                             // dual: both branches of a select on the SAME block, input 2 (4 c + v):
+                                        // T(even) = c ? v : 0 (read at coefficient 0), T(odd) = c ? 0 : v (one box further)
     L_COUNT
 };
 bool lut_signed(int id) { return id == L_SIGN2; }
-bool lut_dual(int id) { return id == L_MC; }
+bool lut_dual(int id) { return id == L_MC || id == L_SEL2; }
 
 int sign3(int a, int b) { return a < b ? 0 : (a == b ? 1 : 2); }
 int cmpred(int x) {
@@ -66,6 +68,7 @@ int lut_eval(int id, int x) {
     switch (id) {
         case L_SIGN2: return x != 0;
         case L_MC: return (x & 1) ? ((x >> 1) >> 2) : ((x >> 1) & 3);
+        case L_SEL2: return (((x >> 3) & 1) != (x & 1)) ? ((x >> 1) & 3) : 0;   // x = 2 (4 c + v) + odd: c ? v : 0 | c ? 0 : v
         case L_MSG: return x & 3;
         case L_CARRY: return x >> 2;
         case L_MUL_LO: return (hi * lo) & 3;
@@ -264,14 +267,19 @@ struct Builder {
     std::pair<Val, Val> msg_carry(const Val &v, bool want_carry) {
         if (!want_carry) return {pbs(v, L_MSG), cst(0)};
         if (!dual || v.hi > 7 || v.lo < 0) return {pbs(v, L_MSG), pbs(v, L_CARRY)};
-        if (v.t.empty()) return {cst(v.k & 3), cst(v.k >> 2)};
+        return pbs_dual(v, L_MC);
+    }
+    // both outputs of dual table `lut` on v in [0, 7]: T(2 v) and T(2 v + 1) from one blind rotation
+    std::pair<Val, Val> pbs_dual(const Val &v, int lut) {
+        if (v.lo < 0 || v.hi > 7) throw std::logic_error("radix circuit: dual table input out of [0,7]");
+        if (v.t.empty()) return {cst(lut_eval(lut, (int)(2 * v.k))), cst(lut_eval(lut, (int)(2 * v.k + 1)))};
         const Val in2 = scale(v, 2);
         const int slot = p.n_slots;
         p.n_slots += 2;
         p.slot_level.push_back(v.level + 1);
         p.slot_level.push_back(v.level + 1);
         if ((int)p.levels.size() <= v.level) p.levels.resize(v.level + 1);
-        p.levels[v.level].push_back({in2, L_MC, slot});
+        p.levels[v.level].push_back({in2, lut, slot});
         p.has_dual = true;
         Val m, c;
         m.t.push_back({slot, 1});
@@ -280,8 +288,9 @@ struct Builder {
         m.lo = c.lo = 15;
         m.hi = c.hi = 0;
         for (long x = v.lo; x <= v.hi; x++) {
-            m.lo = std::min<long>(m.lo, x & 3), m.hi = std::max<long>(m.hi, x & 3);
-            c.lo = std::min<long>(c.lo, x >> 2), c.hi = std::max<long>(c.hi, x >> 2);
+            const long e0 = lut_eval(lut, (int)(2 * x)), e1 = lut_eval(lut, (int)(2 * x + 1));
+            m.lo = std::min(m.lo, e0), m.hi = std::max(m.hi, e0);
+            c.lo = std::min(c.lo, e1), c.hi = std::max(c.hi, e1);
         }
         return {m, c};
     }
@@ -578,6 +587,25 @@ struct Builder {
                     else
                         sh[i] = (j >= 0 && j < nb) ? x[j] : cst(0);
                 }
+            }
+            if (dual && t > 0) {
+                // block-granular stage: sh[i] is another block of x itself, so "taken" (c ? v : 0) and "kept" (c ? 0 : v)
+                // of every block come out of ONE blind rotation on 4 c + v (dual table L_SEL2); x'[i] = taken[j(i)] + kept[i]
+                std::vector<Val> taken(nb), kept(nb);
+                for (int i = 0; i < nb; i++) {
+                    const auto tk = pbs_dual(pack(bit, assume(x[i], 0, 3)), L_SEL2);
+                    taken[i] = tk.first;
+                    kept[i] = tk.second;
+                }
+                const int d = 1 << (t - 1);
+                std::vector<Val> nx(nb);
+                for (int i = 0; i < nb; i++) {
+                    int j = left ? i - d : i + d;
+                    if (rot) j = ((j % nb) + nb) % nb;
+                    nx[i] = (j >= 0 && j < nb) ? assume(add(taken[j], kept[i]), 0, 3) : kept[i];   // the two are mutually exclusive
+                }
+                x.swap(nx);
+                continue;
             }
             x = select(bit, sh, x);
         }
