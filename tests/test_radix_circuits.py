@@ -241,9 +241,9 @@ def test_pbs_counts_and_depths():
     nb = 32
     assert R.pbs_count("add", 64) == nb                  # ripple: message AND carry of a block from one bootstrap (dual table)
     assert R.program("add", 64, dual=False).n_pbs == 2 * nb - 1   # engines of the other orders: carry + message per block
-    assert R.pbs_count("lt", 64) == nb - 1               # signs of block PAIRS (signed table) + pairwise tree
+    assert R.pbs_count("lt", 64) == 16 + 5 + 2 + 1       # signs of block PAIRS (signed table), three flags per reduction step
     assert R.pbs_count("and", 64) == nb
-    assert R.depth("lt", 64) == 5
+    assert R.depth("lt", 64) == 4
     assert int(R.lib().lux_erc20_pbs_count()) == R.program(R.PROG_ERC20, 64).n_pbs
     assert R.pbs_count("mul", 64) < 2600
 
@@ -301,4 +301,4 @@ def test_shallow_rule_and_depths():
         assert len(shallow.levels) == nb.bit_length() - 1 + 2
         assert shallow.n_pbs > deep.n_pbs
     assert len(R.program(R.PROG_ERC20, 64, shallow=True).levels) == 8
-    assert len(R.program(R.PROG_ERC20, 64).levels) == 5 + 1 + 32   # le, the one select, then the two chains side by side
+    assert len(R.program(R.PROG_ERC20, 64).levels) == 4 + 1 + 32   # le, the one select, then the two chains side by side

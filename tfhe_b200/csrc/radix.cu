@@ -40,7 +40,8 @@ enum LutId {
     L_SIGN2 = L_NEK0 + 16,              // signed: sign(x) in {-1, 0, 1} for x in (-16, 16): T(0) = 0, T(1..15) = 1
     L_MC,                               // dual: message AND carry of a sum s <= 7 from ONE blind rotation, input 2 s:
                                         // T(2 s) = s & 3 (read at coefficient 0), T(2 s + 1) = s >> 2 (read one box further)
-    L_SEL2,                             // dual: both branches of a select on the SAME block, input 2 (4 c + v):
+    L_PRED_V0,                          // + pred: pred(sign(x - 5)) for the shifted flag combination x = 3 z1 + z0 + 5
+    L_SEL2 = L_PRED_V0 + PRED_N,        // dual: both branches of a select on the SAME block, input 2 (4 c + v):
                                         // T(even) = c ? v : 0 (read at coefficient 0), T(odd) = c ? 0 : v (one box further)
     L_COUNT
 };
@@ -93,6 +94,7 @@ int lut_eval(int id, int x) {
     }
     if (id >= L_PRED_CMP0 && id < L_PRED_CMP0 + PRED_N) return pred_of_sign(id - L_PRED_CMP0, sign3(hi, lo));
     if (id >= L_PRED_RED0 && id < L_PRED_RED0 + PRED_N) return pred_of_sign(id - L_PRED_RED0, cmpred(x));
+    if (id >= L_PRED_V0 && id < L_PRED_V0 + PRED_N) return pred_of_sign(id - L_PRED_V0, x < 5 ? 0 : (x == 5 ? 1 : 2));
     if (id >= L_EQK0 && id < L_EQK0 + 16) return x == id - L_EQK0;
     if (id >= L_NEK0 && id < L_NEK0 + 16) return x != id - L_NEK0;
     return 0;
@@ -423,26 +425,26 @@ struct Builder {
     }
     // ordering predicates: per-block signs, pairwise tree, predicate folded into the last table
     // First level: TWO blocks per bootstrap.  The difference 4 (a1 - b1) + (a0 - b0) of a pair of blocks is linear and lies
-    // in [-15, 15]; the signed table L_SIGN2 returns its sign through the negacyclic extension (the padding bit is the sign
-    // bit), +1 turns it into the 0 / 1 / 2 = less / equal / greater code of L_CMP.  nb / 2 + (nb / 2 - 1) bootstraps
-    // instead of nb + (nb - 1).
+    // in [-15, 15]; the signed table L_SIGN2 returns its sign z in {-1, 0, 1} through the negacyclic extension (the padding
+    // bit is the sign bit).  Reduction: THREE flags per bootstrap — 9 z2 + 3 z1 + z0 in [-13, 13] has the sign of its most
+    // significant non-zero flag (|3 z1 + z0| <= 4 < 9), i.e. the lexicographic order of the three parts, and L_SIGN2 gives it
+    // back as a flag.  The last one or two flags, shifted to 3 z1 + z0 + 5 in [1, 9], meet the plain table pred(sign(x - 5)).
+    // euint64: 16 + 5 + 2 + 1 = 24 bootstraps in 4 levels (one block per sign and a pairwise tree: 63 in 6).
     Val compare(const std::vector<Val> &a, const std::vector<Val> &b, int pred) {
         const int nb = (int)a.size();
-        if (nb == 1) return pbs(pack(a[0], b[0]), L_PRED_CMP0 + pred);
-        std::vector<Val> s;
-        for (int i = 0; i + 1 < nb; i += 2) {
-            const Val d = add(scale(sub(assume(a[i + 1], 0, 3), assume(b[i + 1], 0, 3)), 4), sub(assume(a[i], 0, 3), assume(b[i], 0, 3)));
-            s.push_back(assume(add(pbs(d, L_SIGN2), cst(1)), 0, 2));
-        }
-        if (nb & 1) s.push_back(pbs(pack(a[nb - 1], b[nb - 1]), L_CMP));
-        while (s.size() > 2) {
+        auto diff = [&](int i) { return sub(assume(a[i], 0, 3), assume(b[i], 0, 3)); };
+        std::vector<Val> z;
+        for (int i = 0; i + 1 < nb; i += 2) z.push_back(pbs(add(scale(diff(i + 1), 4), diff(i)), L_SIGN2));
+        if (nb & 1) z.push_back(nb == 1 ? diff(0) : pbs(diff(nb - 1), L_SIGN2));
+        while (z.size() > 2) {   // least significant first; a group's most significant flag weighs 9
             std::vector<Val> n;
-            for (size_t i = 0; i + 1 < s.size(); i += 2) n.push_back(pbs(pack(s[i + 1], s[i]), L_CMPRED));
-            if (s.size() & 1) n.push_back(s.back());
-            s.swap(n);
+            size_t i = 0;
+            for (; i + 2 < z.size(); i += 3) n.push_back(pbs(add(add(scale(z[i + 2], 9), scale(z[i + 1], 3)), z[i]), L_SIGN2));
+            for (; i < z.size(); i++) n.push_back(z[i]);
+            z.swap(n);
         }
-        if (s.size() == 1) return pbs(pack(cst(1), s[0]), L_PRED_RED0 + pred);   // "upper part equal": the sign of the one pair decides
-        return pbs(pack(s[1], s[0]), L_PRED_RED0 + pred);
+        Val x = z.size() == 2 ? add(scale(z[1], 3), z[0]) : z[0];   // nb == 1: the raw difference in [-3, 3]
+        return pbs(add(x, cst(5)), L_PRED_V0 + pred);
     }
     // Equality through the signed table as well.  z = sign(4 (a1 - b1) + (a0 - b0)) in {-1, 0, 1} is non-zero iff the pair of
     // blocks differs; three such flags combine without cancellation in balanced ternary, 9 z2 + 3 z1 + z0 in [-13, 13], whose
