@@ -43,10 +43,12 @@ enum LutId {
     L_PRED_V0,                          // + pred: pred(sign(x - 5)) for the shifted flag combination x = 3 z1 + z0 + 5
     L_SEL2 = L_PRED_V0 + PRED_N,        // dual: both branches of a select on the SAME block, input 2 (4 c + v):
                                         // T(even) = c ? v : 0 (read at coefficient 0), T(odd) = c ? 0 : v (one box further)
+    L_SELB,                             // dual: the two BITS of a block under a condition, input 2 (4 c + v):
+                                        // T(even) = c ? v & 1 : 0, T(odd) = c ? v >> 1 : 0
     L_COUNT
 };
 bool lut_signed(int id) { return id == L_SIGN2; }
-bool lut_dual(int id) { return id == L_MC || id == L_SEL2; }
+bool lut_dual(int id) { return id == L_MC || id == L_SEL2 || id == L_SELB; }
 
 int sign3(int a, int b) { return a < b ? 0 : (a == b ? 1 : 2); }
 int cmpred(int x) {
@@ -69,6 +71,7 @@ int lut_eval(int id, int x) {
     switch (id) {
         case L_SIGN2: return x != 0;
         case L_MC: return (x & 1) ? ((x >> 1) >> 2) : ((x >> 1) & 3);
+        case L_SELB: return ((x >> 3) & 1) ? ((x & 1) ? (((x >> 1) & 3) >> 1) : (((x >> 1) & 3) & 1)) : 0;
         case L_SEL2: return (((x >> 3) & 1) != (x & 1)) ? ((x >> 1) & 3) : 0;   // x = 2 (4 c + v) + odd: c ? v : 0 | c ? 0 : v
         case L_MSG: return x & 3;
         case L_CARRY: return x >> 2;
@@ -569,6 +572,54 @@ struct Builder {
         const bool left = (op == LUX_OP_SHL || op == LUX_OP_ROTL), rot = (op == LUX_OP_ROTL || op == LUX_OP_ROTR);
         for (int t = 0; t < nbits; t++) {
             const Val bit = pbs(amt[t / 2], (t & 1) ? L_BIT1 : L_BIT0);
+            if (dual && t == 0) {
+                // one-bit stage: x'[i] = c ? (neighbouring bits) : x[i].  The shifted block is 2 (low bit of one block) + (high
+                // bit of its neighbour), and c ? bit : 0 of both bits of a block come out of ONE blind rotation (dual table
+                // L_SELB); with "kept" (c ? 0 : v, L_SEL_B) that is two bootstraps per block instead of three
+                std::vector<Val> lo(nb), hi(nb), kept(nb);
+                for (int i = 0; i < nb; i++) {
+                    const Val in = pack(bit, assume(x[i], 0, 3));
+                    const auto b2 = pbs_dual(in, L_SELB);
+                    lo[i] = b2.first;
+                    hi[i] = b2.second;
+                    kept[i] = pbs(in, L_SEL_B);
+                }
+                std::vector<Val> nx(nb);
+                for (int i = 0; i < nb; i++) {
+                    Val v = kept[i];
+                    if (left) {   // 2 (x[i] & 1) + (x[i-1] >> 1)
+                        v = add(v, scale(lo[i], 2));
+                        const int j = i ? i - 1 : (rot ? nb - 1 : -1);
+                        if (j >= 0) v = add(v, hi[j]);
+                    } else {      // (x[i] >> 1) + 2 (x[i+1] & 1)
+                        v = add(v, hi[i]);
+                        const int j = (i + 1 < nb) ? i + 1 : (rot ? 0 : -1);
+                        if (j >= 0) v = add(v, scale(lo[j], 2));
+                    }
+                    nx[i] = assume(v, 0, 3);   // kept and the shifted bits are mutually exclusive
+                }
+                x.swap(nx);
+                continue;
+            }
+            if (dual && t > 0) {
+                // block-granular stage: sh[i] is another block of x itself, so "taken" (c ? v : 0) and "kept" (c ? 0 : v)
+                // of every block come out of ONE blind rotation on 4 c + v (dual table L_SEL2); x'[i] = taken[j(i)] + kept[i]
+                std::vector<Val> taken(nb), kept(nb);
+                for (int i = 0; i < nb; i++) {
+                    const auto tk = pbs_dual(pack(bit, assume(x[i], 0, 3)), L_SEL2);
+                    taken[i] = tk.first;
+                    kept[i] = tk.second;
+                }
+                const int d = 1 << (t - 1);
+                std::vector<Val> nx(nb);
+                for (int i = 0; i < nb; i++) {
+                    int j = left ? i - d : i + d;
+                    if (rot) j = ((j % nb) + nb) % nb;
+                    nx[i] = (j >= 0 && j < nb) ? assume(add(taken[j], kept[i]), 0, 3) : kept[i];   // the two are mutually exclusive
+                }
+                x.swap(nx);
+                continue;
+            }
             std::vector<Val> sh(nb);
             if (t == 0) {
                 for (int i = 0; i < nb; i++) {
@@ -589,25 +640,6 @@ struct Builder {
                     else
                         sh[i] = (j >= 0 && j < nb) ? x[j] : cst(0);
                 }
-            }
-            if (dual && t > 0) {
-                // block-granular stage: sh[i] is another block of x itself, so "taken" (c ? v : 0) and "kept" (c ? 0 : v)
-                // of every block come out of ONE blind rotation on 4 c + v (dual table L_SEL2); x'[i] = taken[j(i)] + kept[i]
-                std::vector<Val> taken(nb), kept(nb);
-                for (int i = 0; i < nb; i++) {
-                    const auto tk = pbs_dual(pack(bit, assume(x[i], 0, 3)), L_SEL2);
-                    taken[i] = tk.first;
-                    kept[i] = tk.second;
-                }
-                const int d = 1 << (t - 1);
-                std::vector<Val> nx(nb);
-                for (int i = 0; i < nb; i++) {
-                    int j = left ? i - d : i + d;
-                    if (rot) j = ((j % nb) + nb) % nb;
-                    nx[i] = (j >= 0 && j < nb) ? assume(add(taken[j], kept[i]), 0, 3) : kept[i];   // the two are mutually exclusive
-                }
-                x.swap(nx);
-                continue;
             }
             x = select(bit, sh, x);
         }
