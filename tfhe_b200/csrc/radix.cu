@@ -744,13 +744,13 @@ static int pick_variant(const lux_engine *e, int op, unsigned bw, size_t batch) 
 }
 // divisor-specific circuits (div / rem by a plaintext): bounded cache, entries stay alive while in use
 std::map<std::tuple<int, unsigned, std::array<u64, 4>>, std::shared_ptr<const Program>> g_scalar_programs;
-std::shared_ptr<const Program> get_scalar_program(int op, unsigned bw, const Wide &scalar) {
+std::shared_ptr<const Program> get_scalar_program(int op, unsigned bw, const Wide &scalar, bool dual = true) {
     std::lock_guard<std::mutex> lk(g_prog_mutex);
-    auto key = std::make_tuple(op, bw, scalar.key());
+    auto key = std::make_tuple(dual ? op : (op | LUX_PROG_NODUAL), bw, scalar.key());
     auto it = g_scalar_programs.find(key);
     if (it == g_scalar_programs.end()) {
         if (g_scalar_programs.size() >= 256) g_scalar_programs.clear();
-        it = g_scalar_programs.emplace(key, std::make_shared<const Program>(build_program(op, bw, scalar))).first;
+        it = g_scalar_programs.emplace(key, std::make_shared<const Program>(build_program(op, bw, scalar, false, dual))).first;
     }
     return it->second;
 }
@@ -1211,7 +1211,7 @@ static int eval_scalar_impl(lux_engine *e, lux_op op, unsigned bw, const uint64_
             }
             std::vector<u64> gin, gout;
             for (auto &g : groups) {
-                const auto prog = get_scalar_program((int)op, bw, Wide::from(g.first.data(), 4));
+                const auto prog = get_scalar_program((int)op, bw, Wide::from(g.first.data(), 4), e->p.order == LUX_ORDER_LWEKS_PBS);
                 const size_t n = g.second.size();
                 gin.resize(n * stride);
                 gout.resize(n * stride);
@@ -1312,9 +1312,10 @@ size_t lux_radix_program(int op, unsigned bit_width, int64_t *buf, size_t cap) {
 }
 size_t lux_radix_program_scalar(int op, unsigned bit_width, const uint64_t *scalar_limbs, size_t n_limbs, int64_t *buf, size_t cap) {
     try {
-        if (!lux_op_is_scalar_only((lux_op)op)) return serialize_program(get_program(op, bit_width), buf, cap);
+        const int base = op & ~(LUX_PROG_SHALLOW | LUX_PROG_NODUAL);
+        if (!lux_op_is_scalar_only((lux_op)base)) return serialize_program(get_program(op, bit_width), buf, cap);
         if (!scalar_limbs || n_limbs < 1 || n_limbs > 4) return 0;
-        return serialize_program(*get_scalar_program(op, bit_width, Wide::from(scalar_limbs, n_limbs)), buf, cap);
+        return serialize_program(*get_scalar_program(base, bit_width, Wide::from(scalar_limbs, n_limbs), (op & LUX_PROG_NODUAL) == 0), buf, cap);
     } catch (...) {
         return 0;
     }
