@@ -30,12 +30,10 @@ namespace {
 // (lut_signed) are designed for that and may be fed x in (-16, 16); every other table must stay below the padding bit.
 enum { PRED_LT = 0, PRED_LE, PRED_GT, PRED_GE, PRED_EQ, PRED_NE, PRED_N };
 enum LutId {
-    L_MSG = 0, L_CARRY, L_MUL_LO, L_MUL_HI, L_AND, L_OR, L_XOR, L_SEL_A, L_SEL_B, L_CMP, L_CMPRED, L_EQB,
+    L_MSG = 0, L_CARRY, L_MUL_LO, L_MUL_HI, L_AND, L_OR, L_XOR, L_SEL_A, L_SEL_B,
     L_SHL1, L_SHR1, L_BIT0, L_BIT1,
     L_PGN, L_GEN, L_PFX,                // parallel-prefix carries (shallow circuits)
-    L_PRED_CMP0,                        // + pred: pred(sign(hi, lo))
-    L_PRED_RED0 = L_PRED_CMP0 + PRED_N, // + pred: pred(reduce(sign_hi, sign_lo))
-    L_EQK0 = L_PRED_RED0 + PRED_N,      // + k: x == k
+    L_EQK0,                             // + k: x == k
     L_NEK0 = L_EQK0 + 16,               // + k: x != k
     L_SIGN2 = L_NEK0 + 16,              // signed: sign(x) in {-1, 0, 1} for x in (-16, 16): T(0) = 0, T(1..15) = 1
     L_MC,                               // dual: message AND carry of a sum s <= 7 from ONE blind rotation, input 2 s:
@@ -50,11 +48,6 @@ enum LutId {
 bool lut_signed(int id) { return id == L_SIGN2; }
 bool lut_dual(int id) { return id == L_MC || id == L_SEL2 || id == L_SELB; }
 
-int sign3(int a, int b) { return a < b ? 0 : (a == b ? 1 : 2); }
-int cmpred(int x) {
-    const int hi = x >> 2, lo = x & 3;
-    return hi != 1 ? hi : lo;
-}
 int pred_of_sign(int pred, int s) {
     switch (pred) {
         case PRED_LT: return s == 0;
@@ -82,9 +75,6 @@ int lut_eval(int id, int x) {
         case L_XOR: return hi ^ lo;
         case L_SEL_A: return (hi & 1) ? lo : 0;   // x = 4*cond + a
         case L_SEL_B: return (hi & 1) ? 0 : lo;   // x = 4*cond + b
-        case L_CMP: return sign3(hi, lo);
-        case L_CMPRED: return cmpred(x);
-        case L_EQB: return hi == lo;
         case L_SHL1: return ((hi << 1) | (lo >> 1)) & 3;    // x = 4*a_i + a_{i-1}
         case L_SHR1: return (lo >> 1) | ((hi & 1) << 1);    // x = 4*a_{i+1} + a_i
         case L_BIT0: return x & 1;
@@ -95,8 +85,6 @@ int lut_eval(int id, int x) {
         case L_PFX: return hi == 2 ? lo : hi;           // x = 4*state(upper span) + state(lower span)
         default: break;
     }
-    if (id >= L_PRED_CMP0 && id < L_PRED_CMP0 + PRED_N) return pred_of_sign(id - L_PRED_CMP0, sign3(hi, lo));
-    if (id >= L_PRED_RED0 && id < L_PRED_RED0 + PRED_N) return pred_of_sign(id - L_PRED_RED0, cmpred(x));
     if (id >= L_PRED_V0 && id < L_PRED_V0 + PRED_N) return pred_of_sign(id - L_PRED_V0, x < 5 ? 0 : (x == 5 ? 1 : 2));
     if (id >= L_EQK0 && id < L_EQK0 + 16) return x == id - L_EQK0;
     if (id >= L_NEK0 && id < L_NEK0 + 16) return x != id - L_NEK0;
